@@ -1,0 +1,466 @@
+// fricc_capi.cu -- the extern "C" surface declared in include/fricc_b200.h.
+#include <algorithm>
+#include <numeric>
+
+#include "fricc_common.cuh"
+#include "fricc_contract.cuh"
+#include "fricc_fri.cuh"
+#include "fricc_select.cuh"
+
+namespace fricc {
+const std::string& last_error();
+void set_stream(cudaStream_t s);
+int64_t launches();
+void reset_device_cache();
+}  // namespace fricc
+
+using namespace fricc;
+
+namespace {
+
+Sampling parse_sampling(const char* s) {
+  if (s && strcmp(s, "pivotal") == 0) return Sampling::Pivotal;
+  if (s && strcmp(s, "systematic") == 0) return Sampling::Systematic;
+  // the reference's check (fri_utils.cpp:443-444) can never fire; an unknown method leaves S empty
+  return Sampling::None;
+}
+
+int64_t prod4(const int64_t d[4]) { return d[0] * d[1] * d[2] * d[3]; }
+
+// number of elements spanned by a strided 4-D view with non-negative strides (the pointer addresses element 0,0,0,0)
+int64_t span_of(const int64_t shape[4], const int64_t strides[4]) {
+  int64_t s = 1;
+  for (int i = 0; i < 4; i++) {
+    if (shape[i] <= 0) return 0;
+    if (strides[i] < 0) fail(FRICC_EINVAL, "negative strides are not supported at the C-ABI (make the array contiguous)");
+    s += (shape[i] - 1) * strides[i];
+  }
+  return s;
+}
+
+void build_from_compressed(fricc_st* t, Compressed& c) {
+  t->nnz = c.m;
+  t->flat = std::move(c.flat);
+  t->vals = std::move(c.vals);
+  t->layouts.clear();
+  t->host_valid = false;
+}
+
+void ensure_host(fricc_st* t) {
+  if (t->host_valid) return;
+  t->h_flat.resize((size_t)t->nnz);
+  t->h_vals.resize((size_t)t->nnz);
+  if (t->nnz > 0) {
+    FRICC_CUDA(cudaMemcpyAsync(t->h_flat.data(), t->flat.p, (size_t)t->nnz * 8, cudaMemcpyDeviceToHost, stream()));
+    FRICC_CUDA(cudaMemcpyAsync(t->h_vals.data(), t->vals.p, (size_t)t->nnz * 8, cudaMemcpyDeviceToHost, stream()));
+    FRICC_CUDA(cudaStreamSynchronize(stream()));
+  }
+  t->host_valid = true;
+}
+
+void check_handle(fricc_st_t t) {
+  if (!t) fail(FRICC_EINVAL, "null SparseTensor4d handle");
+}
+
+int create_impl(const double* tensor, int mem, const int64_t dims[4], int64_t m, const char* compression,
+                const char* sampling_method, int verbose, const DrawSource& draws, int64_t* n_consumed,
+                fricc_st_t* out) {
+  FRICC_API_BEGIN
+  if (!tensor || !dims || !out || !compression) fail(FRICC_EINVAL, "null argument");
+  for (int i = 0; i < 4; i++)
+    if (dims[i] <= 0) fail(FRICC_EINVAL, "dims must be positive");
+  const int64_t n = prod4(dims);
+  if (m < 0 || m > n)
+    fail(FRICC_EINVAL, "Bad m value: need 0 <= m <= tensor size (m=%lld, size=%lld)", (long long)m, (long long)n);
+  const bool largest = strcmp(compression, "largest") == 0;
+  const bool fri = strcmp(compression, "fri") == 0;
+  if (!largest && !fri)
+    fail(FRICC_EINVAL, "The compression method you chose (%s) isn't supported: compression must be 'largest' or 'fri'",
+         compression);
+  DevIn<double> x(tensor, mem, (size_t)n);
+  Compressed c;
+  if (largest) compress_largest(x.p, n, m, c);
+  else compress_fri(x.p, n, m, parse_sampling(sampling_method), draws, verbose != 0, c);
+  if (n_consumed) *n_consumed = c.consumed;
+  fricc_st* t = new fricc_st();
+  for (int i = 0; i < 4; i++) t->dims[i] = dims[i];
+  build_from_compressed(t, c);
+  FRICC_CUDA(cudaStreamSynchronize(stream()));  // staged input must outlive the kernels that read it
+  *out = t;
+  FRICC_API_END
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* fricc_last_error(void) { return fricc::last_error().c_str(); }
+const char* fricc_version(void) { return "fricc_b200 0.1 (sm_100a)"; }
+
+int fricc_device_count(int* count) {
+  FRICC_API_BEGIN
+  int c = 0;
+  cudaError_t e = cudaGetDeviceCount(&c);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    c = 0;
+  }
+  *count = c;
+  FRICC_API_END
+}
+int fricc_set_device(int device) {
+  FRICC_API_BEGIN
+  FRICC_CUDA(cudaSetDevice(device));
+  fricc::reset_device_cache();
+  FRICC_API_END
+}
+int fricc_set_stream(void* s) {
+  fricc::set_stream(reinterpret_cast<cudaStream_t>(s));
+  return FRICC_OK;
+}
+int fricc_stream_synchronize(void) {
+  FRICC_API_BEGIN
+  FRICC_CUDA(cudaStreamSynchronize(stream()));
+  FRICC_API_END
+}
+int64_t fricc_kernel_launches(void) { return fricc::launches(); }
+
+int fricc_srand(uint32_t seed) {
+  rand_seed(seed);
+  return FRICC_OK;
+}
+int fricc_rand_fill(int32_t* out, int64_t n) {
+  FRICC_API_BEGIN
+  if (n < 0 || (!out && n > 0)) fail(FRICC_EINVAL, "bad arguments");
+  rand_fill(out, n);
+  FRICC_API_END
+}
+int64_t fricc_rand_consumed(void) { return rand_consumed(); }
+
+// ---- SparseTensor4d ------------------------------------------------------------------------------------------
+int fricc_st_create_empty(const int64_t dims[4], int64_t nnz, fricc_st_t* out) {
+  FRICC_API_BEGIN
+  if (!dims || !out || nnz < 0) fail(FRICC_EINVAL, "bad arguments");
+  fricc_st* t = new fricc_st();
+  for (int i = 0; i < 4; i++) t->dims[i] = dims[i];
+  t->nnz = nnz;
+  t->flat.alloc((size_t)std::max<int64_t>(nnz, 1));
+  t->vals.alloc((size_t)std::max<int64_t>(nnz, 1));
+  t->flat.zero();
+  t->vals.zero();
+  *out = t;
+  FRICC_API_END
+}
+
+int fricc_st_create(const double* tensor, int mem, const int64_t dims[4], int64_t m, const char* compression,
+                    const char* sampling_method, int verbose, fricc_st_t* out) {
+  DrawSource ds;
+  ds.from_stream = true;
+  return create_impl(tensor, mem, dims, m, compression, sampling_method, verbose, ds, nullptr, out);
+}
+
+int fricc_st_create_with_draws(const double* tensor, int mem, const int64_t dims[4], int64_t m,
+                               const char* compression, const char* sampling_method, int verbose, const int32_t* draws,
+                               int64_t n_draws, int64_t* n_consumed, fricc_st_t* out) {
+  DrawSource ds;
+  ds.from_stream = false;
+  ds.host = draws;
+  ds.n = draws ? n_draws : 0;
+  return create_impl(tensor, mem, dims, m, compression, sampling_method, verbose, ds, n_consumed, out);
+}
+
+int fricc_st_create_from_coo(const int64_t* flat_idx, const double* vals, int mem, const int64_t dims[4], int64_t m,
+                             fricc_st_t* out) {
+  FRICC_API_BEGIN
+  if (!dims || !out || m < 0 || (m > 0 && (!flat_idx || !vals))) fail(FRICC_EINVAL, "bad arguments");
+  fricc_st* t = new fricc_st();
+  for (int i = 0; i < 4; i++) t->dims[i] = dims[i];
+  t->nnz = m;
+  t->flat.alloc((size_t)std::max<int64_t>(m, 1));
+  t->vals.alloc((size_t)std::max<int64_t>(m, 1));
+  if (m > 0) {
+    cudaMemcpyKind kind = mem == FRICC_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+    FRICC_CUDA(cudaMemcpyAsync(t->flat.p, flat_idx, (size_t)m * 8, kind, stream()));
+    FRICC_CUDA(cudaMemcpyAsync(t->vals.p, vals, (size_t)m * 8, kind, stream()));
+    FRICC_CUDA(cudaStreamSynchronize(stream()));
+  }
+  *out = t;
+  FRICC_API_END
+}
+
+int fricc_st_destroy(fricc_st_t t) {
+  FRICC_API_BEGIN
+  delete t;
+  FRICC_API_END
+}
+
+int fricc_st_size(fricc_st_t t, int64_t* nnz) {
+  FRICC_API_BEGIN
+  check_handle(t);
+  *nnz = t->nnz;
+  FRICC_API_END
+}
+int fricc_st_dims(fricc_st_t t, int64_t dims[4]) {
+  FRICC_API_BEGIN
+  check_handle(t);
+  for (int i = 0; i < 4; i++) dims[i] = t->dims[i];
+  FRICC_API_END
+}
+
+int fricc_st_get_element(fricc_st_t t, int64_t mi, int64_t idx[4], double* value) {
+  FRICC_API_BEGIN
+  check_handle(t);
+  if (mi < 0 || mi >= t->nnz) fail(FRICC_ERANGE, "Index you requested is larger than the specified size");
+  ensure_host(t);
+  int64_t f = t->h_flat[(size_t)mi];
+  const int64_t* d = t->dims;
+  // unpack_idx (sparse_tensor.hpp:108-125)
+  idx[0] = f / (d[1] * d[2] * d[3]);
+  idx[1] = f % (d[1] * d[2] * d[3]) / (d[2] * d[3]);
+  idx[2] = f % (d[2] * d[3]) / d[3];
+  idx[3] = f % d[3];
+  *value = t->h_vals[(size_t)mi];
+  FRICC_API_END
+}
+
+int fricc_st_set_element(fricc_st_t t, int64_t mi, int64_t flat_idx, double value) {
+  FRICC_API_BEGIN
+  check_handle(t);
+  if (mi < 0 || mi >= t->nnz) fail(FRICC_ERANGE, "Index you requested is larger than the specified size");
+  if (flat_idx < 0 || flat_idx >= prod4(t->dims)) fail(FRICC_ERANGE, "Indices are out of range for given tensor");
+  FRICC_CUDA(cudaMemcpyAsync(t->flat.p + mi, &flat_idx, 8, cudaMemcpyHostToDevice, stream()));
+  FRICC_CUDA(cudaMemcpyAsync(t->vals.p + mi, &value, 8, cudaMemcpyHostToDevice, stream()));
+  FRICC_CUDA(cudaStreamSynchronize(stream()));
+  t->layouts.clear();
+  t->host_valid = false;
+  FRICC_API_END
+}
+
+int fricc_st_export(fricc_st_t t, int64_t* flat_idx, double* vals, int mem) {
+  FRICC_API_BEGIN
+  check_handle(t);
+  if (t->nnz > 0) {
+    cudaMemcpyKind kind = mem == FRICC_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
+    if (flat_idx) FRICC_CUDA(cudaMemcpyAsync(flat_idx, t->flat.p, (size_t)t->nnz * 8, kind, stream()));
+    if (vals) FRICC_CUDA(cudaMemcpyAsync(vals, t->vals.p, (size_t)t->nnz * 8, kind, stream()));
+    FRICC_CUDA(cudaStreamSynchronize(stream()));
+  }
+  FRICC_API_END
+}
+
+// ---- contractions --------------------------------------------------------------------------------------------
+int fricc_contract(const double* W, int w_mem, const int64_t w_shape[4], const int64_t w_strides[4], fricc_st_t T,
+                   double* out, int out_mem, const int64_t out_shape[4], const int64_t out_strides[4],
+                   const char* term) {
+  FRICC_API_BEGIN
+  check_handle(T);
+  if (!W || !out || !w_shape || !w_strides || !out_shape || !out_strides) fail(FRICC_EINVAL, "null argument");
+  const TermSpec* ts = find_term(term);
+  if (!ts) fail(FRICC_EINVAL, "CASE NOT IMPLEMENTED: unknown contraction term '%s'", term ? term : "(null)");
+  const int64_t* d = T->dims;
+  // shape agreement (the reference indexes unchecked; here a mismatch is an error instead of a wild read)
+  for (int q = 0; q < 2; q++) {
+    if (w_shape[ts->wK[q]] != d[ts->tK[q]])
+      fail(FRICC_EINVAL, "term %s (%s): W axis %d has extent %lld, T axis %d has %lld", ts->name, ts->einsum, ts->wK[q],
+           (long long)w_shape[ts->wK[q]], ts->tK[q], (long long)d[ts->tK[q]]);
+    if (out_shape[ts->oR[q]] != d[ts->tR[q]])
+      fail(FRICC_EINVAL, "term %s (%s): out axis %d has extent %lld, T axis %d has %lld", ts->name, ts->einsum,
+           ts->oR[q], (long long)out_shape[ts->oR[q]], ts->tR[q], (long long)d[ts->tR[q]]);
+    if (out_shape[ts->oL[q]] != w_shape[ts->wL[q]])
+      fail(FRICC_EINVAL, "term %s (%s): out axis %d has extent %lld, W axis %d has %lld", ts->name, ts->einsum,
+           ts->oL[q], (long long)out_shape[ts->oL[q]], ts->wL[q], (long long)w_shape[ts->wL[q]]);
+  }
+  const int64_t nK1 = w_shape[ts->wK[0]], nK2 = w_shape[ts->wK[1]];
+  const int64_t nL1 = w_shape[ts->wL[0]], nL2 = w_shape[ts->wL[1]];
+  const int64_t nK = nK1 * nK2, nL = nL1 * nL2;
+  if (nK == 0 || nL == 0 || T->nnz == 0) return FRICC_OK;
+
+  const int64_t w_span = span_of(w_shape, w_strides);
+  const int64_t o_span = span_of(out_shape, out_strides);
+  DevIn<double> Wd(W, w_mem, (size_t)w_span);
+
+  // is W already the [K1][K2][L1][L2] row-major panel?  then stream it in place
+  const bool in_place = w_strides[ts->wL[1]] == 1 && w_strides[ts->wL[0]] == nL2 && w_strides[ts->wK[1]] == nL &&
+                        w_strides[ts->wK[0]] == nK2 * nL;
+  DevBuf<double> panel;
+  const double* Wp = Wd.p;
+  if (!in_place) {
+    panel.alloc((size_t)(nK * nL));
+    permute_w(Wd.p, w_shape, w_strides, *ts, 0, nL, panel.p);
+    Wp = panel.p;
+  }
+
+  DevBuf<double> out_stage;
+  double* od = out;
+  if (out_mem != FRICC_DEVICE) {
+    out_stage.alloc((size_t)o_span);
+    out_stage.from_host(out, (size_t)o_span);
+    od = out_stage.p;
+  }
+  Layout& lay = get_layout(T, *ts);
+  OutMap om;
+  om.nR2 = d[ts->tR[1]];
+  om.nL2 = nL2;
+  om.sR1 = out_strides[ts->oR[0]];
+  om.sR2 = out_strides[ts->oR[1]];
+  om.sL1 = out_strides[ts->oL[0]];
+  om.sL2 = out_strides[ts->oL[1]];
+  spmm(lay, Wp, nL, 0, nL, od, om, ts->scale);
+  if (out_mem != FRICC_DEVICE) out_stage.to_host(out, (size_t)o_span);
+  else FRICC_CUDA(cudaStreamSynchronize(stream()));  // staged W / panel are released after this call
+  FRICC_API_END
+}
+
+int fricc_permute_w(const double* W, int w_mem, const int64_t w_shape[4], const int64_t w_strides[4], const char* term,
+                    int64_t l_begin, int64_t l_count, double* Wp_dev) {
+  FRICC_API_BEGIN
+  const TermSpec* ts = find_term(term);
+  if (!ts) fail(FRICC_EINVAL, "CASE NOT IMPLEMENTED: unknown contraction term '%s'", term ? term : "(null)");
+  const int64_t nL = w_shape[ts->wL[0]] * w_shape[ts->wL[1]];
+  if (l_begin < 0 || l_count < 0 || l_begin + l_count > nL) fail(FRICC_EINVAL, "column range out of bounds");
+  DevIn<double> Wd(W, w_mem, (size_t)span_of(w_shape, w_strides));
+  permute_w(Wd.p, w_shape, w_strides, *ts, l_begin, l_count, Wp_dev);
+  FRICC_CUDA(cudaStreamSynchronize(stream()));
+  FRICC_API_END
+}
+
+int fricc_contract_panel(const double* Wp_dev, int64_t l_begin, int64_t l_count, fricc_st_t T, double* out_panel_dev,
+                         const char* term) {
+  FRICC_API_BEGIN
+  check_handle(T);
+  const TermSpec* ts = find_term(term);
+  if (!ts) fail(FRICC_EINVAL, "CASE NOT IMPLEMENTED: unknown contraction term '%s'", term ? term : "(null)");
+  if (!Wp_dev || !out_panel_dev || l_count < 0) fail(FRICC_EINVAL, "bad arguments");
+  if (T->nnz == 0 || l_count == 0) return FRICC_OK;
+  Layout& lay = get_layout(T, *ts);
+  // out panel is [R][l_count] row-major: address = R*l_count + (l - l_begin)
+  OutMap om;
+  om.nR2 = 1;
+  om.nL2 = 1;
+  om.sR1 = l_count;
+  om.sR2 = 0;
+  om.sL1 = 1;
+  om.sL2 = 0;
+  // l = l_begin + col is mapped through sL1; shift the base so that column l_begin lands at offset 0
+  spmm(lay, Wp_dev, l_count, l_begin, l_count, out_panel_dev - l_begin, om, ts->scale);
+  FRICC_API_END
+}
+
+// ---- stage-wise utilities ------------------------------------------------------------------------------------
+int fricc_one_norm(const double* x, int mem, int64_t n, double* norm) {
+  FRICC_API_BEGIN
+  if (n < 0 || !norm || (n > 0 && !x)) fail(FRICC_EINVAL, "bad arguments");
+  DevIn<double> xd(x, mem, (size_t)n);
+  *norm = one_norm_sequential(xd.p, n);
+  FRICC_API_END
+}
+
+int fricc_argsort(const double* x, int mem, int64_t n, int64_t m, int64_t* idx_out) {
+  FRICC_API_BEGIN
+  if (n < 0 || m < 0 || m > n || (m > 0 && !idx_out)) fail(FRICC_EINVAL, "argsort: need 0 <= m <= N");
+  DevIn<double> xd(x, mem, (size_t)n);
+  TopM top;
+  select_top_m(xd.p, n, m, top);
+  if (m > 0) top.idx.to_host(reinterpret_cast<uint64_t*>(idx_out), (size_t)m);
+  FRICC_CUDA(cudaStreamSynchronize(stream()));
+  FRICC_API_END
+}
+
+int fricc_get_d_largest(const double* x, int mem, int64_t n, int64_t n_sample, int64_t* D_out, int64_t* n_D,
+                        double* remaining_norm) {
+  FRICC_API_BEGIN
+  if (n < 0 || n_sample < 0 || n_sample > n || !n_D || !remaining_norm) fail(FRICC_EINVAL, "get_d_largest: bad arguments");
+  DevIn<double> xd(x, mem, (size_t)n);
+  double norm = one_norm_sequential(xd.p, n);
+  TopM top;
+  select_top_m(xd.p, n, n_sample, top);
+  int64_t nD = 0;
+  double r = norm;
+  if (n_sample > 0) d_greedy(top, norm, &nD, &r);
+  if (nD > 0 && D_out) top.idx.to_host(reinterpret_cast<uint64_t*>(D_out), (size_t)nD);
+  FRICC_CUDA(cudaStreamSynchronize(stream()));
+  *n_D = nD;
+  *remaining_norm = r;
+  FRICC_API_END
+}
+
+int fricc_make_probability_vector(const double* x, int mem, int64_t n, int64_t n_sample, const int64_t* D_host,
+                                  int64_t n_D, double remaining_norm, double* p_out, int p_mem) {
+  FRICC_API_BEGIN
+  if (n < 0 || n_D < 0 || (n > 0 && (!x || !p_out))) fail(FRICC_EINVAL, "bad arguments");
+  DevIn<double> xd(x, mem, (size_t)n);
+  for (int64_t i = 0; i < n_D; i++)
+    if (D_host[i] < 0 || D_host[i] >= n) fail(FRICC_ERANGE, "D index out of range");
+  DevIn<int64_t> Dd(D_host, FRICC_HOST, (size_t)n_D);
+  DevBuf<double> pstage;
+  double* pd = p_out;
+  if (p_mem != FRICC_DEVICE) {
+    pstage.alloc((size_t)n);
+    pd = pstage.p;
+  }
+  // copy out even on failure?  no: the reference exits before returning anything
+  make_probability_vector(xd.p, n, n_sample, Dd.p, n_D, remaining_norm, pd);
+  if (p_mem != FRICC_DEVICE && n > 0) pstage.to_host(p_out, (size_t)n);
+  FRICC_CUDA(cudaStreamSynchronize(stream()));
+  FRICC_API_END
+}
+
+static int sample_impl(bool pivotal, int64_t n_sample, const double* probs, int mem, int64_t n, const int32_t* draws,
+                       int64_t n_draws, int64_t* n_consumed, int64_t* S_out) {
+  FRICC_API_BEGIN
+  if (n < 0 || n_sample < 0 || (n > 0 && !probs) || (n_sample > 0 && !S_out)) fail(FRICC_EINVAL, "bad arguments");
+  DevIn<double> pd(probs, mem, (size_t)n);
+  DrawSource ds;
+  ds.from_stream = (draws == nullptr);
+  ds.host = draws;
+  ds.n = draws ? n_draws : 0;
+  DevBuf<int64_t> S((size_t)std::max<int64_t>(n_sample, 1));
+  int64_t consumed = 0;
+  if (pivotal) sample_pivotal_probs(n_sample, pd.p, n, ds, &consumed, S.p);
+  else sample_systematic_probs(n_sample, pd.p, n, ds, &consumed, S.p);
+  if (n_sample > 0) S.to_host(S_out, (size_t)n_sample);
+  FRICC_CUDA(cudaStreamSynchronize(stream()));
+  if (n_consumed) *n_consumed = consumed;
+  FRICC_API_END
+}
+
+int fricc_sample_pivotal(int64_t n_sample, const double* probs, int mem, int64_t n, const int32_t* draws,
+                         int64_t n_draws, int64_t* n_consumed, int64_t* S_out) {
+  return sample_impl(true, n_sample, probs, mem, n, draws, n_draws, n_consumed, S_out);
+}
+int fricc_sample_systematic(int64_t n_sample, const double* probs, int mem, int64_t n, const int32_t* draws,
+                            int64_t n_draws, int64_t* n_consumed, int64_t* S_out) {
+  return sample_impl(false, n_sample, probs, mem, n, draws, n_draws, n_consumed, S_out);
+}
+
+int fricc_fri_compression(const double* x, int mem, int64_t n, int64_t n_sample, const char* sampling_method,
+                          int verbose, const int32_t* draws, int64_t n_draws, int64_t* n_consumed, int64_t* idx_out,
+                          double* vals_out) {
+  FRICC_API_BEGIN
+  if (n < 0 || n_sample < 0 || n_sample > n) fail(FRICC_EINVAL, "fri_compression: need 0 <= n_sample <= N");
+  DevIn<double> xd(x, mem, (size_t)n);
+  DrawSource ds;
+  ds.from_stream = (draws == nullptr);
+  ds.host = draws;
+  ds.n = draws ? n_draws : 0;
+  Compressed c;
+  compress_fri(xd.p, n, n_sample, parse_sampling(sampling_method), ds, verbose != 0, c);
+  if (n_sample > 0) {
+    c.flat.to_host(idx_out, (size_t)n_sample);
+    c.vals.to_host(vals_out, (size_t)n_sample);
+  }
+  FRICC_CUDA(cudaStreamSynchronize(stream()));
+  if (n_consumed) *n_consumed = c.consumed;
+  FRICC_API_END
+}
+
+int fricc_key_histogram(const double* x_dev, int64_t n, int shift, uint64_t prefix, int prefix_bits,
+                        unsigned long long* hist_dev) {
+  FRICC_API_BEGIN
+  if (shift != 0 && shift != 3 && shift != 15 && shift != 27 && shift != 39 && shift != 51)
+    fail(FRICC_EINVAL, "shift must be one of 51,39,27,15,3,0");
+  key_histogram(x_dev, n, shift, shift == 0 ? 7u : 4095u, prefix, prefix_bits, hist_dev);
+  FRICC_API_END
+}
+
+}  // extern "C"

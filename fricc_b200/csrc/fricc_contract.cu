@@ -1,0 +1,274 @@
+// fricc_contract.cu -- SparseTensor4d x dense contractions as ONE primitive: bucketed sparse-row x dense-panel SpMM.
+//
+// The reference implements 11 terms (/root/reference/src/sparse_tensor.cpp:12-346) with the same loop nest: an OpenMP
+// loop over an owner pair R of output indices; every owner scans ALL m stored entries for the ones that belong to it
+// (o^2*m or o*v*m index tests) and then walks W with a large stride.  Here the entries are bucketed by R once
+// (sort by (R,K), CSR row pointers), W is brought into a [K][L] row-major panel so that the row a nonzero needs is
+// contiguous, and one kernel does   out[R, L] += scale * sum_{e in bucket R} val_e * Wp[K_e, L]
+// with the accumulators in registers and exactly one read-modify-write of each output element (no atomics).
+#include "fricc_contract.cuh"
+
+#include <algorithm>
+
+#include "fricc_sort.cuh"
+
+namespace fricc {
+
+// ---------------------------------------------------------------------------------------------------------------
+// term table (every row cites the reference kernel it replaces).  T entry idx = (idx0..idx3).
+// ---------------------------------------------------------------------------------------------------------------
+static const TermSpec kTerms[] = {
+    // name   tR      tK      wK      wL      oR      oL     scale  einsum
+    // sparse_tensor.cpp:40-86    out(i,j,a,b) += W(a,b,c,d) * t(i,j,c,d)
+    {"2323", {0, 1}, {2, 3}, {2, 3}, {0, 1}, {0, 1}, {2, 3}, 1.0, "abcd,ijcd->ijab"},
+    // sparse_tensor.cpp:12-37    out(i,j,a,b) += W(k,l,i,j) * t(k,l,a,b)
+    {"0101", {2, 3}, {0, 1}, {0, 1}, {2, 3}, {2, 3}, {0, 1}, 1.0, "klij,klab->ijab"},
+    // sparse_tensor.cpp:205-230  out(k,l,i,j) += ovov(k,c,l,d) * t(i,j,c,d)
+    {"1323", {0, 1}, {2, 3}, {1, 3}, {0, 2}, {2, 3}, {0, 1}, 1.0, "kcld,ijcd->klij"},
+    // sparse_tensor.cpp:89-115   out(i,j,a,b) += 2 * W(a,k,i,c) * t(k,j,c,b)      R=(b,j) K=(k,c) L=(a,i)
+    {"1302", {3, 1}, {0, 2}, {1, 3}, {0, 2}, {3, 1}, {2, 0}, 2.0, "2*akic,kjcb->ijab"},
+    // sparse_tensor.cpp:118-144  out(i,j,a,b) -= W(a,k,c,i) * t(k,j,c,b)          R=(b,j) K=(k,c) L=(a,i)
+    {"1202", {3, 1}, {0, 2}, {1, 2}, {0, 3}, {3, 1}, {2, 0}, -1.0, "-akci,kjcb->ijab"},
+    // sparse_tensor.cpp:147-173  out(i,j,a,b) += W(a,k,i,c) * t(k,j,b,c)          R=(b,j) K=(k,c) L=(a,i)
+    {"1303", {2, 1}, {0, 3}, {1, 3}, {0, 2}, {3, 1}, {2, 0}, 1.0, "akic,kjbc->ijab"},
+    // sparse_tensor.cpp:176-202  out(i,j,a,b) += W(b,k,c,i) * t(k,j,a,c)          R=(a,j) K=(k,c) L=(b,i)
+    {"1203", {2, 1}, {0, 3}, {1, 2}, {0, 3}, {2, 1}, {3, 0}, 1.0, "bkci,kjac->ijab"},
+    // sparse_tensor.cpp:233-259  out(a,k,i,c) -= 0.5 * ovov(l,d,k,c) * t(i,l,d,a) R=(a,i) K=(l,d) L=(k,c)
+    {"0112", {3, 0}, {1, 2}, {0, 1}, {2, 3}, {0, 2}, {1, 3}, -0.5, "-0.5*ldkc,ilda->akic"},
+    // sparse_tensor.cpp:262-289  out(a,k,i,c) -= 0.5 * ovov(l,c,k,d) * t(i,l,a,d) R=(a,i) K=(l,d) L=(k,c)
+    {"0313", {2, 0}, {1, 3}, {0, 3}, {2, 1}, {0, 2}, {1, 3}, -0.5, "-0.5*lckd,ilad->akic"},
+    // sparse_tensor.cpp:292-317  out(a,k,i,c) += ovov(l,d,k,c) * t(i,l,a,d)       R=(a,i) K=(l,d) L=(k,c)
+    {"0113", {2, 0}, {1, 3}, {0, 1}, {2, 3}, {0, 2}, {1, 3}, 1.0, "ldkc,ilad->akic"},
+    // sparse_tensor.cpp:320-346  out(a,k,c,i) -= 0.5 * ovov(l,c,k,d) * t(i,l,d,a) R=(a,i) K=(l,d) L=(k,c)
+    {"0312", {3, 0}, {1, 2}, {0, 3}, {2, 1}, {0, 3}, {1, 2}, -0.5, "-0.5*lckd,ilda->akci"},
+    // experimental 2323 variants (sparse_tensor.cpp:389-459): same sum, different CPU threading
+    {"taskloop", {0, 1}, {2, 3}, {2, 3}, {0, 1}, {0, 1}, {2, 3}, 1.0, "abcd,ijcd->ijab"},
+    {"atomic", {0, 1}, {2, 3}, {2, 3}, {0, 1}, {0, 1}, {2, 3}, 1.0, "abcd,ijcd->ijab"},
+};
+
+const TermSpec* find_term(const char* name) {
+  if (!name) return nullptr;
+  for (const TermSpec& t : kTerms)
+    if (strcmp(t.name, name) == 0) return &t;
+  return nullptr;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// layout: entries -> (R*nK + K, value) -> sort -> CSR
+// ---------------------------------------------------------------------------------------------------------------
+struct Dims4 {
+  int64_t d[4];
+};
+
+__global__ void make_keys_kernel(const int64_t* __restrict__ flat, const double* __restrict__ vals, int64_t m, Dims4 dm,
+                                 int r0, int r1, int k0, int k1, uint64_t* __restrict__ keys,
+                                 uint64_t* __restrict__ pay) {
+  int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= m) return;
+  int64_t f = flat[e];
+  int64_t ix[4];
+  ix[3] = f % dm.d[3]; f /= dm.d[3];
+  ix[2] = f % dm.d[2]; f /= dm.d[2];
+  ix[1] = f % dm.d[1]; f /= dm.d[1];
+  ix[0] = f;
+  int64_t R = ix[r0] * dm.d[r1] + ix[r1];
+  int64_t K = ix[k0] * dm.d[k1] + ix[k1];
+  int64_t nK = dm.d[k0] * dm.d[k1];
+  keys[e] = (uint64_t)(R * nK + K);
+  pay[e] = (uint64_t)__double_as_longlong(vals[e]);
+}
+
+__global__ void split_keys_kernel(const uint64_t* __restrict__ keys, const uint64_t* __restrict__ pay, int64_t m,
+                                  int64_t nK, uint32_t* __restrict__ kidx, double* __restrict__ vals) {
+  int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= m) return;
+  kidx[e] = (uint32_t)(keys[e] % (uint64_t)nK);
+  vals[e] = __longlong_as_double((long long)pay[e]);
+}
+
+// rowptr[R] = first sorted position whose key >= R*nK   (R = 0..nR)
+__global__ void rowptr_kernel(const uint64_t* __restrict__ keys, int64_t m, int64_t nK, int64_t nR,
+                              int64_t* __restrict__ rowptr) {
+  int64_t R = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (R > nR) return;
+  uint64_t target = (uint64_t)R * (uint64_t)nK;
+  int64_t lo = 0, hi = m;
+  while (lo < hi) {
+    int64_t mid = (lo + hi) >> 1;
+    if (keys[mid] < target) lo = mid + 1;
+    else hi = mid;
+  }
+  rowptr[R] = lo;
+}
+
+Layout& get_layout(fricc_st* T, const TermSpec& ts) {
+  for (Layout& l : T->layouts)
+    if (l.r0 == ts.tR[0] && l.r1 == ts.tR[1]) return l;
+  T->layouts.emplace_back();
+  Layout& lay = T->layouts.back();
+  lay.r0 = ts.tR[0];
+  lay.r1 = ts.tR[1];
+  const int64_t* d = T->dims;
+  lay.nR = d[ts.tR[0]] * d[ts.tR[1]];
+  lay.nK = d[ts.tK[0]] * d[ts.tK[1]];
+  if (lay.nK >= ((int64_t)1 << 32)) fail(FRICC_EINVAL, "contracted pair too large for 32-bit packing");
+  const int64_t m = T->nnz;
+  lay.rowptr.alloc((size_t)lay.nR + 1);
+  lay.kidx.alloc((size_t)std::max<int64_t>(m, 1));
+  lay.vals.alloc((size_t)std::max<int64_t>(m, 1));
+  if (m == 0) {
+    lay.rowptr.zero();
+    return lay;
+  }
+  DevBuf<uint64_t> ka((size_t)m), kb((size_t)m), pa((size_t)m), pb((size_t)m);
+  Dims4 dm{{d[0], d[1], d[2], d[3]}};
+  unsigned g = (unsigned)ceil_div(m, 256);
+  FRICC_LAUNCH(make_keys_kernel, g, 256, 0, T->flat.p, T->vals.p, m, dm, ts.tR[0], ts.tR[1], ts.tK[0], ts.tK[1], ka.p, pa.p);
+  int bits = 1;
+  while (bits < 63 && ((int64_t)1 << bits) < lay.nR * lay.nK) bits++;
+  std::vector<Digit> digits;
+  for (int s = 0; s < bits; s += 8) digits.push_back(Digit{0, s, 0});
+  uint64_t* kk[2] = {ka.p, kb.p};
+  uint64_t* pp[2] = {pa.p, pb.p};
+  int r = radix_sort_pairs(kk, pp, m, digits);  // stable: duplicates keep their storage order
+  FRICC_LAUNCH(split_keys_kernel, g, 256, 0, kk[r], pp[r], m, lay.nK, lay.kidx.p, lay.vals.p);
+  FRICC_LAUNCH(rowptr_kernel, (unsigned)ceil_div(lay.nR + 1, 256), 256, 0, kk[r], m, lay.nK, lay.nR, lay.rowptr.p);
+  return lay;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// W -> panel
+// ---------------------------------------------------------------------------------------------------------------
+struct PermArgs {
+  int64_t sK1, sK2, sL1, sL2;  // element strides of W along (K major, K minor, L major, L minor)
+  int64_t nK1, nK2, nL2;
+  int64_t l_begin, l_count;
+};
+
+__global__ void permute_gather_kernel(const double* __restrict__ W, PermArgs a, int64_t total, double* __restrict__ Wp) {
+  int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  int64_t K = idx / a.l_count, c = idx - K * a.l_count;
+  int64_t l = a.l_begin + c;
+  int64_t src = (K / a.nK2) * a.sK1 + (K % a.nK2) * a.sK2 + (l / a.nL2) * a.sL1 + (l % a.nL2) * a.sL2;
+  Wp[idx] = W[src];
+}
+
+// K-minor axis contiguous in W: 32x32 shared-memory transpose, coalesced on both sides
+__global__ void __launch_bounds__(256)
+permute_tiled_kernel(const double* __restrict__ W, PermArgs a, double* __restrict__ Wp) {
+  __shared__ double tile[32][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int64_t k1 = blockIdx.z;
+  const int64_t k2_0 = (int64_t)blockIdx.y * 32, c0 = (int64_t)blockIdx.x * 32;
+  for (int r = ty; r < 32; r += 8) {
+    int64_t c = c0 + r, k2 = k2_0 + tx;
+    if (c < a.l_count && k2 < a.nK2) {
+      int64_t l = a.l_begin + c;
+      tile[r][tx] = W[k1 * a.sK1 + k2 * a.sK2 + (l / a.nL2) * a.sL1 + (l % a.nL2) * a.sL2];
+    }
+  }
+  __syncthreads();
+  for (int r = ty; r < 32; r += 8) {
+    int64_t k2 = k2_0 + r, c = c0 + tx;
+    if (c < a.l_count && k2 < a.nK2) Wp[(k1 * a.nK2 + k2) * a.l_count + c] = tile[tx][r];
+  }
+}
+
+void permute_w(const double* W, const int64_t shape[4], const int64_t strides[4], const TermSpec& ts, int64_t l_begin,
+               int64_t l_count, double* Wp) {
+  PermArgs a;
+  a.sK1 = strides[ts.wK[0]]; a.sK2 = strides[ts.wK[1]];
+  a.sL1 = strides[ts.wL[0]]; a.sL2 = strides[ts.wL[1]];
+  a.nK1 = shape[ts.wK[0]]; a.nK2 = shape[ts.wK[1]];
+  a.nL2 = shape[ts.wL[1]];
+  a.l_begin = l_begin; a.l_count = l_count;
+  const int64_t nK = a.nK1 * a.nK2;
+  if (nK == 0 || l_count == 0) return;
+  if (a.sK2 == 1 && a.sL2 != 1 && a.nK1 <= 65535 && ceil_div(a.nK2, 32) <= 65535) {
+    dim3 grid((unsigned)ceil_div(l_count, 32), (unsigned)ceil_div(a.nK2, 32), (unsigned)a.nK1);
+    FRICC_LAUNCH(permute_tiled_kernel, grid, 256, 0, W, a, Wp);
+  } else {
+    int64_t total = nK * l_count;
+    FRICC_LAUNCH(permute_gather_kernel, (unsigned)ceil_div(total, 256), 256, 0, W, a, total, Wp);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// SpMM: one CTA = one bucket R x one tile of L columns; register accumulators; rows of Wp streamed with vector loads
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int SPMM_CHUNK = 256;
+
+template <int VEC>
+__global__ void __launch_bounds__(256)
+spmm_rows_kernel(const int64_t* __restrict__ rowptr, const uint32_t* __restrict__ kidx, const double* __restrict__ vals,
+                 const double* __restrict__ Wp, int64_t ldw, int64_t l_begin, int64_t l_count, double* __restrict__ out,
+                 OutMap om, double scale) {
+  __shared__ uint32_t sk[SPMM_CHUNK];
+  __shared__ double sv[SPMM_CHUNK];
+  const int64_t R = blockIdx.x;
+  const int64_t e0 = rowptr[R], e1 = rowptr[R + 1];
+  if (e0 == e1) return;
+  const int64_t col = ((int64_t)blockIdx.y * blockDim.x + threadIdx.x) * VEC;
+  const bool active = col < l_count;
+  const double* wcol = Wp + col;
+  double acc[VEC];
+#pragma unroll
+  for (int v = 0; v < VEC; v++) acc[v] = 0.0;
+
+  for (int64_t c = e0; c < e1; c += SPMM_CHUNK) {
+    const int cnt = (int)min((int64_t)SPMM_CHUNK, e1 - c);
+    __syncthreads();
+    for (int t = threadIdx.x; t < cnt; t += blockDim.x) {
+      sk[t] = kidx[c + t];
+      sv[t] = vals[c + t];
+    }
+    __syncthreads();
+    if (active) {
+#pragma unroll 8
+      for (int t = 0; t < cnt; t++) {
+        const double* wp = wcol + (int64_t)sk[t] * ldw;
+        const double s = sv[t];
+        if (VEC == 2) {
+          double2 w = __ldg(reinterpret_cast<const double2*>(wp));
+          acc[0] = fma(s, w.x, acc[0]);
+          acc[VEC - 1] = fma(s, w.y, acc[VEC - 1]);
+        } else {
+          acc[0] = fma(s, __ldg(wp), acc[0]);
+        }
+      }
+    }
+  }
+  if (active) {
+    const int64_t r1 = R / om.nR2, r2 = R - r1 * om.nR2;
+    const int64_t rbase = r1 * om.sR1 + r2 * om.sR2;
+#pragma unroll
+    for (int v = 0; v < VEC; v++) {
+      int64_t l = l_begin + col + v;
+      int64_t l1 = l / om.nL2, l2 = l - l1 * om.nL2;
+      int64_t o = rbase + l1 * om.sL1 + l2 * om.sL2;
+      out[o] += scale * acc[v];
+    }
+  }
+}
+
+void spmm(const Layout& lay, const double* Wp, int64_t ldw, int64_t l_begin, int64_t l_count, double* out,
+          const OutMap& om, double scale) {
+  if (lay.nR == 0 || l_count == 0) return;
+  bool vec2 = (ldw % 2 == 0) && (l_count % 2 == 0) && ((reinterpret_cast<uintptr_t>(Wp) & 15) == 0);
+  int vec = vec2 ? 2 : 1;
+  int64_t threads_needed = ceil_div(l_count, vec);
+  int threads = 32;
+  while (threads < 256 && threads < threads_needed) threads <<= 1;
+  int64_t tiles = ceil_div(threads_needed, threads);
+  if (tiles > 65535) fail(FRICC_EINVAL, "spmm: free pair too large (%lld columns)", (long long)l_count);
+  dim3 grid((unsigned)lay.nR, (unsigned)tiles);
+  if (vec2)
+    FRICC_LAUNCH(spmm_rows_kernel<2>, grid, threads, 0, lay.rowptr.p, lay.kidx.p, lay.vals.p, Wp, ldw, l_begin, l_count,
+                 out, om, scale);
+  else
+    FRICC_LAUNCH(spmm_rows_kernel<1>, grid, threads, 0, lay.rowptr.p, lay.kidx.p, lay.vals.p, Wp, ldw, l_begin, l_count,
+                 out, om, scale);
+}
+
+}  // namespace fricc

@@ -1,0 +1,40 @@
+// fricc_contract.cuh -- bucketed sparse-row x dense-panel contractions -- see fricc_contract.cu
+#pragma once
+#include "fricc_common.cuh"
+
+namespace fricc {
+
+// One contraction term of the reference's dispatcher (/root/reference/src/sparse_tensor.cpp:349-382), expressed as
+//      out[R, L] += scale * sum_K T[R, K] * W[K, L]
+// by naming which axes of T (dims o,o,v,v), of W and of out play the roles R (owner pair), K (contracted pair) and
+// L (free pair).  Each pair is ordered (major, minor).
+struct TermSpec {
+  const char* name;
+  int tR[2];   // T axes forming R
+  int tK[2];   // T axes forming K
+  int wK[2];   // W axes carrying K (same order as tK)
+  int wL[2];   // W axes carrying L
+  int oR[2];   // out axes carrying R (same order as tR)
+  int oL[2];   // out axes carrying L (same order as wL)
+  double scale;
+  const char* einsum;  // the caller's formula, for documentation and error messages
+};
+
+const TermSpec* find_term(const char* name);
+
+// bucketed layout of T for owner pair (tR) / contracted pair (tK); cached in the handle
+Layout& get_layout(fricc_st* T, const TermSpec& ts);
+
+// W (4-D, element strides) -> panel Wp[K][l_count] for the L columns [l_begin, l_begin + l_count)
+void permute_w(const double* W_dev, const int64_t shape[4], const int64_t strides[4], const TermSpec& ts,
+               int64_t l_begin, int64_t l_count, double* Wp_dev);
+
+// out[r1*sr1 + r2*sr2 + l1*sl1 + l2*sl2] += scale * sum_e vals[e] * Wp[kidx[e]][l - l_begin]
+struct OutMap {
+  int64_t nR2, nL2;      // minor extents of the R and L pairs
+  int64_t sR1, sR2, sL1, sL2;  // element strides of out along (R major, R minor, L major, L minor)
+};
+void spmm(const Layout& lay, const double* Wp_dev, int64_t ldw, int64_t l_begin, int64_t l_count, double* out_dev,
+          const OutMap& om, double scale);
+
+}  // namespace fricc

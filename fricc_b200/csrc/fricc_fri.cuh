@@ -1,0 +1,59 @@
+// fricc_fri.cuh -- FRI compression stages (reference: /root/reference/src/fri_utils.cpp) -- see fricc_fri.cu
+#pragma once
+#include "fricc_common.cuh"
+#include "fricc_select.cuh"
+
+namespace fricc {
+
+enum class Sampling { Pivotal = 0, Systematic = 1, None = 2 };
+
+// where the uniform draws come from: a caller buffer (host) or the library's glibc-compatible stream
+struct DrawSource {
+  const int32_t* host = nullptr;  // draws[t] = value of the t-th rand() call
+  int64_t n = 0;
+  bool from_stream = true;
+};
+
+struct Compressed {
+  int64_t m = 0;
+  int64_t nD = 0;            // |D|
+  double remaining_norm = 0; // r after the greedy subtraction
+  int64_t consumed = 0;      // draws the reference would have consumed
+  DevBuf<int64_t> flat;      // [m]  [D..., S...]
+  DevBuf<double> vals;       // [m]
+};
+
+// exact sequential-order sums (bit-identical to a left-to-right fp64 accumulation)
+double one_norm_sequential(const double* x_dev, int64_t n);
+
+// get_d_largest on a sorted candidate list
+void d_greedy(const TopM& top, double norm, int64_t* nD, double* remaining_norm);
+
+// make_probability_vector (materialised; stage-wise API only -- the compression itself never stores p)
+void make_probability_vector(const double* x_dev, int64_t n, int64_t n_sample, const int64_t* D_dev, int64_t nD,
+                             double remaining_norm, double* p_dev);
+
+// samplers on an explicit probability vector (stage-wise API); S_dev has n_sample entries
+void sample_systematic_probs(int64_t n_sample, const double* p_dev, int64_t n, const DrawSource& draws,
+                             int64_t* consumed, int64_t* S_dev);
+void sample_pivotal_probs(int64_t n_sample, const double* p_dev, int64_t n, const DrawSource& draws, int64_t* consumed,
+                          int64_t* S_dev);
+
+// the two compressions behind SparseTensor4d's constructor
+void compress_largest(const double* x_dev, int64_t n, int64_t m, Compressed& out);
+void compress_fri(const double* x_dev, int64_t n, int64_t m, Sampling method, const DrawSource& draws, bool verbose,
+                  Compressed& out);
+
+// glibc-compatible rand() stream (host side)
+void rand_seed(uint32_t seed);
+void rand_fill(int32_t* out, int64_t n);  // advances
+int64_t rand_consumed();
+struct RandSnapshot {
+  uint32_t ring[31];
+  int64_t i;
+  int64_t consumed;
+};
+RandSnapshot rand_snapshot();
+void rand_restore(const RandSnapshot& s);
+
+}  // namespace fricc

@@ -1,0 +1,132 @@
+/*
+ * fricc_b200.h -- C-ABI of libfricc_b200.so: the B200 (sm_100a) implementation of fri-cc's FRI-CCSD inner loop.
+ *
+ * This is the drop-in boundary.  Every entry point below replaces one symbol of the reference's pybind11
+ * module `py_rccsd` (/root/reference/src/py_rccsd.cpp:16-55) or one of the C++ functions behind it; the
+ * reference interface each one stands in for is cited next to it.  Signatures use plain pointers, sizes and
+ * NUL-terminated strings only -- no torch, numpy or C++ types -- so the library can be bound from ctypes
+ * (fricc_b200/py_rccsd.py does), pybind11, cffi or anything else.  INTEGRATION.md shows the reference-side stub.
+ *
+ * Conventions
+ *   - every function returns an int status: FRICC_OK (0) or a negative FRICC_E* code; fricc_last_error() returns a
+ *     human-readable message for the calling thread's last failure.  Nothing here ever calls exit(): the
+ *     conditions under which the reference prints to stderr and exits become error codes.
+ *   - array arguments carry a `mem` tag: FRICC_HOST (ordinary host memory; the library stages it through the GPU,
+ *     copies are part of the call) or FRICC_DEVICE (a CUDA device pointer on the current device; zero-copy).
+ *   - all work is issued on the stream set with fricc_set_stream() (default: the legacy default stream) and every
+ *     call that returns results to host memory synchronises that stream before returning.
+ *   - indices are int64_t (the reference uses size_t), values are IEEE binary64.
+ *   - there is NO CPU fallback: without a usable CUDA device every compute entry point returns FRICC_ECUDA.
+ */
+#ifndef FRICC_B200_H
+#define FRICC_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FRICC_OK 0
+#define FRICC_EINVAL (-1)    /* bad argument (unknown term/compression/method string, m > N, ndim, null ptr) */
+#define FRICC_ECUDA (-2)     /* CUDA runtime error or no device                                               */
+#define FRICC_EPROB (-3)     /* a probability exceeded 1 (reference: fri_utils.cpp:383-395 exits)             */
+#define FRICC_EPIVOTAL (-4)  /* pivotal acceptance probability out of [0,1] (fri_utils.cpp:84-94 exits)       */
+#define FRICC_ECOUNT (-5)    /* sampler produced the wrong number of samples (fri_utils.cpp:110-124 exits)    */
+#define FRICC_EDRAWS (-6)    /* caller-supplied draw buffer too short                                         */
+#define FRICC_ERANGE (-7)    /* element index out of range                                                    */
+
+#define FRICC_HOST 0
+#define FRICC_DEVICE 1
+
+typedef struct fricc_st* fricc_st_t; /* opaque SparseTensor4d handle (device-resident COO + cached bucketed layouts) */
+
+/* ---- library / runtime ------------------------------------------------------------------------------------- */
+const char* fricc_last_error(void);
+const char* fricc_version(void);
+int fricc_device_count(int* count);
+int fricc_set_device(int device);
+int fricc_set_stream(void* cuda_stream);      /* cudaStream_t of the caller (e.g. torch's current stream); NULL = default */
+int fricc_stream_synchronize(void);
+/* number of kernels this library has launched since load (bench.py's "gpu_launches" evidence) */
+int64_t fricc_kernel_launches(void);
+
+/* ---- uniform draws ------------------------------------------------------------------------------------------
+ * The reference draws from libc rand() (fri_utils.cpp:47,74): one draw per systematic compression, one per visited
+ * element for pivotal.  The library keeps an equivalent process-wide stream: glibc's TYPE_3 additive-feedback
+ * generator, unseeded == srand(1), advanced by exactly the number of draws the reference would have consumed.   */
+int fricc_srand(uint32_t seed);                                  /* == libc srand(seed)                           */
+int fricc_rand_fill(int32_t* out_host, int64_t n);               /* next n values of rand(); advances the stream  */
+int64_t fricc_rand_consumed(void);                               /* draws consumed since the last fricc_srand     */
+
+/* ---- SparseTensor4d (reference: include/sparse_tensor.hpp:13-100, src/py_rccsd.cpp:32-47) -------------------- */
+/* ctor #1 (sparse_tensor.hpp:27-31): nnz zero entries */
+int fricc_st_create_empty(const int64_t dims[4], int64_t nnz, fricc_st_t* out);
+/* ctor #2 (sparse_tensor.hpp:33-77): compress a dense C-contiguous tensor of prod(dims) doubles to m entries.
+ * compression: "fri" | "largest"; sampling_method: "pivotal" | "systematic"; verbose: print the 5-row stage table
+ * (fri_utils.cpp:509-519).  Draws come from the library stream (above).                                          */
+int fricc_st_create(const double* tensor, int mem, const int64_t dims[4], int64_t m, const char* compression,
+                    const char* sampling_method, int verbose, fricc_st_t* out);
+/* same, with caller-supplied integer draws in [0, 2^31-1] (host memory; draws[t] is what the t-th rand() call would
+ * return); n_consumed (may be NULL) receives how many the reference would have consumed.                         */
+int fricc_st_create_with_draws(const double* tensor, int mem, const int64_t dims[4], int64_t m,
+                               const char* compression, const char* sampling_method, int verbose,
+                               const int32_t* draws, int64_t n_draws, int64_t* n_consumed, fricc_st_t* out);
+/* build directly from m (flat index, value) pairs (host or device) -- used by the multi-GPU path after the gather  */
+int fricc_st_create_from_coo(const int64_t* flat_idx, const double* vals, int mem, const int64_t dims[4], int64_t m,
+                             fricc_st_t* out);
+int fricc_st_destroy(fricc_st_t t);
+int fricc_st_size(fricc_st_t t, int64_t* nnz);                                  /* size()       :87              */
+int fricc_st_dims(fricc_st_t t, int64_t dims[4]);                               /* dimensions() :86              */
+int fricc_st_get_element(fricc_st_t t, int64_t mi, int64_t idx[4], double* value); /* get_element  :138-143        */
+int fricc_st_set_element(fricc_st_t t, int64_t mi, int64_t flat_idx, double value); /* set_element  :127-136        */
+/* all entries in storage order: flat indices and values (host or device destination)                              */
+int fricc_st_export(fricc_st_t t, int64_t* flat_idx, double* vals, int mem);
+
+/* ---- contractions (reference: contract_SparseTensor4d_wrapper, src/sparse_tensor.cpp:349-382) -----------------
+ * out[...] += scale * sum_K T[R,K] * W[...]   for term in
+ *   "0101" "2323" "1302" "1202" "1303" "1203" "1323" "0112" "0313" "0113" "0312"   (table in SURVEY.md 8a-3)
+ * plus the experimental 2323 variants "taskloop" / "atomic" (sparse_tensor.cpp:445-459), which compute the same sum.
+ * W and out are 4-D binary64 arrays with arbitrary element strides (numpy semantics); out is accumulated in place. */
+int fricc_contract(const double* W, int w_mem, const int64_t w_shape[4], const int64_t w_strides[4], fricc_st_t T,
+                   double* out, int out_mem, const int64_t out_shape[4], const int64_t out_strides[4],
+                   const char* term);
+/* Pre-permuted operand: Wp is already the [K][L_local] row-major panel the kernel streams, holding the L-columns
+ * [l_begin, l_begin+l_count) of the term's free pair (the multi-GPU column shard).  out_panel is [R][l_count].   */
+int fricc_contract_panel(const double* Wp_dev, int64_t l_begin, int64_t l_count, fricc_st_t T, double* out_panel_dev,
+                         const char* term);
+/* permute a 4-D W into the [K][L] panel layout of `term` on the device (columns [l_begin, l_begin+l_count))        */
+int fricc_permute_w(const double* W, int w_mem, const int64_t w_shape[4], const int64_t w_strides[4],
+                    const char* term, int64_t l_begin, int64_t l_count, double* Wp_dev);
+
+/* ---- stage-wise FRI utilities (reference: include/fri_utils.hpp:8-32) ------------------------------------------ */
+/* one_norm (fri_utils.cpp:164-171): sum |x_i| accumulated in index order (bit-identical to the 1-thread reference) */
+int fricc_one_norm(const double* x, int mem, int64_t n, double* norm);
+/* argsort (fri_utils.cpp:11-36): indices of the m largest |x| in descending |x| (ties: ascending index)            */
+int fricc_argsort(const double* x, int mem, int64_t n, int64_t m, int64_t* idx_out_host);
+/* get_d_largest (fri_utils.cpp:400-437) */
+int fricc_get_d_largest(const double* x, int mem, int64_t n, int64_t n_sample, int64_t* D_out_host, int64_t* n_D,
+                        double* remaining_norm);
+/* make_probability_vector (fri_utils.cpp:367-398) */
+int fricc_make_probability_vector(const double* x, int mem, int64_t n, int64_t n_sample, const int64_t* D_host,
+                                  int64_t n_D, double remaining_norm, double* p_out, int p_mem);
+/* sample_pivotal (fri_utils.cpp:63-127) / sample_systematic (:129-159) on an explicit probability vector          */
+int fricc_sample_pivotal(int64_t n_sample, const double* probs, int mem, int64_t n, const int32_t* draws,
+                         int64_t n_draws, int64_t* n_consumed, int64_t* S_out_host);
+int fricc_sample_systematic(int64_t n_sample, const double* probs, int mem, int64_t n, const int32_t* draws,
+                            int64_t n_draws, int64_t* n_consumed, int64_t* S_out_host);
+/* fri_compression (fri_utils.cpp:439-522): returns m flat indices and m values, [D..., S...] order               */
+int fricc_fri_compression(const double* x, int mem, int64_t n, int64_t n_sample, const char* sampling_method,
+                          int verbose, const int32_t* draws, int64_t n_draws, int64_t* n_consumed,
+                          int64_t* idx_out_host, double* vals_out_host);
+
+/* ---- distributed compression building blocks (multi-GPU: x sharded by contiguous flat-index range) ------------- */
+/* 4096-bin histogram (count) of the 12-bit digit at `shift` of key(x)=bits(|x|), over elements whose higher bits
+ * equal `prefix` (prefix_bits of them); device output, to be all-reduced by the caller.                           */
+int fricc_key_histogram(const double* x_dev, int64_t n, int shift, uint64_t prefix, int prefix_bits,
+                        unsigned long long* hist_dev /*[4096]*/);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FRICC_B200_H */
