@@ -1,0 +1,70 @@
+"""The C-ABI library loads and exports every symbol include/fricc_b200.h declares (no compute calls: CPU-only)."""
+import ctypes
+import os
+import re
+
+import pytest
+
+from fricc_b200 import _lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    text = open(os.path.join(ROOT, "include", "fricc_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(fricc_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_is_built_in_tree():
+    assert os.path.exists(_lib.LIB_PATH), "run __graft_entry__.build() first"
+
+
+def test_every_declared_symbol_is_exported():
+    L = ctypes.CDLL(_lib.LIB_PATH)
+    names = declared_symbols()
+    assert len(names) >= 30
+    for n in names:
+        assert hasattr(L, n), f"{n} declared in include/fricc_b200.h but not exported"
+
+
+def test_binding_table_covers_header():
+    assert sorted(_lib.SIGNATURES) == declared_symbols()
+
+
+def test_version_and_error_string():
+    L = _lib.lib()
+    assert b"sm_100a" in L.fricc_version()
+    assert isinstance(L.fricc_last_error(), bytes)
+
+
+def test_no_cpu_fallback_without_device():
+    """Without a CUDA device a compute entry point must fail loudly, not fall back."""
+    import numpy as np
+
+    n = ctypes.c_int(0)
+    _lib.check(_lib.lib().fricc_device_count(ctypes.byref(n)))
+    if n.value > 0:
+        pytest.skip("a CUDA device is present")
+    from fricc_b200 import py_rccsd
+
+    x = np.arange(16, dtype=np.float64).reshape(1, 1, 4, 4)
+    with pytest.raises(RuntimeError):
+        py_rccsd.SparseTensor4d(x, x.shape, 3, "largest")
+
+
+def test_glibc_rand_stream_matches_libc():
+    """The library's rand() stream is glibc's (the reference draws with libc rand(), fri_utils.cpp:47,74)."""
+    import numpy as np
+
+    libc = ctypes.CDLL(None)
+    L = _lib.lib()
+    for seed in (1, 7, 20, 123456):
+        libc.srand(seed)
+        want = np.array([libc.rand() for _ in range(2000)], dtype=np.int32)
+        _lib.check(L.fricc_srand(seed))
+        got = np.empty(2000, dtype=np.int32)
+        _lib.check(L.fricc_rand_fill(got.ctypes.data_as(ctypes.POINTER(ctypes.c_int32)), 1200))
+        _lib.check(L.fricc_rand_fill(got[1200:].ctypes.data_as(ctypes.POINTER(ctypes.c_int32)), 800))
+        assert (got == want).all()
+        assert L.fricc_rand_consumed() == 2000

@@ -1,0 +1,118 @@
+"""GPU parity of the compression stages (P1-P5 of SURVEY.md 8c): bit-exact against the oracle and against the golden
+vectors recorded from the compiled reference, with the same injected uniform draws."""
+import numpy as np
+import pytest
+from conftest import synth_t2
+
+pytestmark = pytest.mark.gpu
+
+
+def test_golden_stages(rccsd, golden_compression):
+    g = golden_compression
+    for name in g["names"]:
+        x, m, draws = g[f"{name}/x"], int(g[f"{name}/m"]), g[f"{name}/draws"]
+        assert rccsd.one_norm(x) == float(g[f"{name}/one_norm"]), name                      # P2 (norm)
+        got = rccsd.argsort(x, m)
+        want = g[f"{name}/argsort"]
+        assert np.array_equal(np.abs(x[got]), np.abs(x[want])), name                         # P1
+        if len(np.unique(np.abs(x))) == len(x):
+            assert (got == want).all(), name
+        D, r = rccsd.get_d_largest(x, m)
+        assert (D == g[f"{name}/D"]).all() and r == float(g[f"{name}/remaining_norm"]), name  # P2
+        p = rccsd.make_probability_vector(x, m - len(D), D, r)
+        assert np.array_equal(p, g[f"{name}/p"]), name                                       # P3
+        for method in ("pivotal", "systematic"):
+            S = getattr(rccsd, f"sample_{method}")(m - len(D), p, draws=draws)
+            assert (np.array(S, dtype=np.int64) == g[f"{name}/{method}/S"]).all(), (name, method)   # P4
+            idx, vals = rccsd.fri_compression(x, m, method, draws=draws)
+            assert (idx == g[f"{name}/{method}/idx"]).all(), (name, method)
+            assert np.array_equal(vals, g[f"{name}/{method}/vals"]), (name, method)          # P5
+
+
+@pytest.mark.parametrize("kind", ["heavy", "heavier", "uniform", "diff"])
+@pytest.mark.parametrize("n,m", [(1, 1), (2, 1), (33, 33), (5000, 1), (20000, 3000), (300000, 40000)])
+def test_fri_vs_oracle(rccsd, port, kind, n, m):
+    rng = np.random.default_rng(n * 7 + m)
+    x = synth_t2(rng, n, kind)
+    draws = rng.integers(0, 2**31 - 1, size=n + 4).astype(np.int32)
+    for method in ("systematic", "pivotal"):
+        try:
+            want = port.fri_compression(x, m, method, draws)
+        except Exception as e:  # the reference would exit here; the GPU path must raise the matching error
+            with pytest.raises(Exception):
+                rccsd.fri_compression(x, m, method, draws=draws)
+            continue
+        idx, vals = rccsd.fri_compression(x, m, method, draws=draws)
+        assert (idx == want["idx"]).all(), method
+        assert np.array_equal(vals, want["vals"]), method
+
+
+def test_sparse_tensor_fri_ctor_and_consumed_draws(rccsd, port):
+    rng = np.random.default_rng(11)
+    no, nv = 6, 14
+    t2 = synth_t2(rng, no * no * nv * nv, "heavier").reshape(no, no, nv, nv)
+    m = 700
+    draws = rng.integers(0, 2**31 - 1, size=t2.size).astype(np.int32)
+    for method in ("systematic", "pivotal"):
+        T = rccsd.SparseTensor4d(t2, t2.shape, m, "fri", method, False, draws=draws)
+        want = port.fri_compression(t2, m, method, draws)
+        flat, vals = T.export()
+        assert (flat == want["idx"]).all() and np.array_equal(vals, want["vals"])
+        assert T.consumed_draws == want["consumed"]
+        idx, v = T.get_element(m - 1)
+        assert np.ravel_multi_index(tuple(idx), t2.shape) == want["idx"][-1] and v == want["vals"][-1]
+
+
+def test_library_rand_stream_is_glibc(rccsd, port):
+    """Without injected draws the module consumes glibc's rand() stream exactly like a stock reference build:
+    srand(seed), then one draw per systematic compression / one per visited element for pivotal."""
+    rng = np.random.default_rng(5)
+    x = synth_t2(rng, 4000, "heavy")
+    stream = port.glibc_rand(20, 3 * x.size)
+    rccsd.srand(20)
+    pos = 0
+    for method in ("systematic", "pivotal", "systematic", "pivotal"):
+        want = port.fri_compression(x, 300, method, stream[pos:])
+        idx, vals = rccsd.fri_compression(x, 300, method)
+        assert (idx == want["idx"]).all() and np.array_equal(vals, want["vals"])
+        pos += want["consumed"]
+        assert rccsd.rand_consumed() == pos
+
+
+def test_largest_with_ties_and_zeros(rccsd, port):
+    """The reference's contraction tests feed mostly-zero tensors with m larger than the number of distinct nonzeros,
+    so the cut lands inside a huge group of exact ties (zeros); pair-symmetric amplitudes tie in pairs."""
+    rng = np.random.default_rng(2)
+    x = np.zeros(50000)
+    nz = rng.choice(x.size, 400, replace=False)
+    x[nz] = rng.random(400)
+    x[rng.choice(nz, 50)] = 0.5  # exact ties among the kept values
+    for m in (100, 400, 450, 5000):
+        got = rccsd.argsort(x, m)
+        want = port.argsort(x, m)
+        assert (got == want).all()  # canonical order: |x| descending, index ascending
+    # big tie group straddling the cut (more ties than the small-bin threshold is not needed to hit the path)
+    y = np.full(3_000_000, 0.25)
+    y[::1000] = 1.0
+    got = rccsd.argsort(y, 3000 + 1234)
+    assert (got[:3000] == np.arange(0, 3_000_000, 1000)).all()
+    rest = got[3000:]
+    assert (rest == np.array([i for i in range(2000) if i % 1000][:1234])).all()
+
+
+def test_error_conditions(rccsd):
+    """Conditions on which the reference prints to stderr and exits become exceptions."""
+    from fricc_b200._lib import FriccError
+
+    with pytest.raises(FriccError):  # p > 1: fri_utils.cpp:383-395
+        rccsd.make_probability_vector(np.array([1.0, 1.0, 5.0]), 2, np.array([], dtype=np.int64), 3.0)
+    with pytest.raises(FriccError):  # wrong number of samples: fri_utils.cpp:110-124
+        rccsd.sample_pivotal(3, np.array([0.2, 0.2, 0.2, 0.2]), draws=np.arange(10, dtype=np.int32))
+    with pytest.raises(ValueError):  # m > N: the Python driver's own check (fricc/friccsd.py:69-72)
+        rccsd.SparseTensor4d(np.zeros((1, 1, 2, 2)), (1, 1, 2, 2), 5, "largest")
+    with pytest.raises(ValueError):
+        rccsd.SparseTensor4d(np.zeros((1, 1, 2, 2)), (1, 1, 2, 2), 2, "bogus")
+    with pytest.raises(TypeError):  # F-ordered tensor_arr is rejected (array_t<double, c_style>, noconvert)
+        rccsd.SparseTensor4d(np.asfortranarray(np.zeros((2, 2, 3, 3))), (2, 2, 3, 3), 2, "largest")
+    t = rccsd.SparseTensor4d([2, 2, 2, 2], 3)
+    assert t.get_element(0) == ([0, 0, 0, 0], 0.0)
