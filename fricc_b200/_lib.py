@@ -48,6 +48,7 @@ SIGNATURES = {
     "fricc_set_device": (c_int, [c_int]),
     "fricc_set_stream": (c_int, [c_void_p]),
     "fricc_stream_synchronize": (c_int, []),
+    "fricc_set_option": (c_int, [c_char_p, c_int]),
     "fricc_kernel_launches": (c_int64, []),
     "fricc_srand": (c_int, [c_uint32]),
     "fricc_rand_fill": (c_int, [POINTER(c_int32), c_int64]),
@@ -64,7 +65,8 @@ SIGNATURES = {
     "fricc_st_set_element": (c_int, [c_void_p, c_int64, c_int64, c_double]),
     "fricc_st_export": (c_int, [c_void_p, c_void_p, c_void_p, c_int]),
     "fricc_contract": (c_int, [c_void_p, c_int, _i64p, _i64p, c_void_p, c_void_p, c_int, _i64p, _i64p, c_char_p]),
-    "fricc_contract_panel": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_char_p]),
+    "fricc_contract_panel": (c_int, [c_void_p, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_int64, c_char_p]),
+    "fricc_accumulate_panels": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_char_p, c_void_p, _i64p, _i64p]),
     "fricc_permute_w": (c_int, [c_void_p, c_int, _i64p, _i64p, c_char_p, c_int64, c_int64, c_void_p]),
     "fricc_one_norm": (c_int, [c_void_p, c_int, c_int64, _f64p]),
     "fricc_argsort": (c_int, [c_void_p, c_int, c_int64, c_int64, c_void_p]),

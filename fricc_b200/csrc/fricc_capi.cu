@@ -125,6 +125,13 @@ int fricc_stream_synchronize(void) {
 }
 int64_t fricc_kernel_launches(void) { return fricc::launches(); }
 
+int fricc_set_option(const char* key, int value) {
+  FRICC_API_BEGIN
+  if (key && strcmp(key, "escan") == 0) set_parallel_scan(value);
+  else fail(FRICC_EINVAL, "unknown option '%s'", key ? key : "(null)");
+  FRICC_API_END
+}
+
 int fricc_srand(uint32_t seed) {
   rand_seed(seed);
   return FRICC_OK;
@@ -324,25 +331,48 @@ int fricc_permute_w(const double* W, int w_mem, const int64_t w_shape[4], const 
   FRICC_API_END
 }
 
-int fricc_contract_panel(const double* Wp_dev, int64_t l_begin, int64_t l_count, fricc_st_t T, double* out_panel_dev,
-                         const char* term) {
+int fricc_contract_panel(const double* Wp_dev, int64_t ldw, int64_t l_begin, int64_t l_count, fricc_st_t T,
+                         double* out_panel_dev, int64_t ld_out, const char* term) {
   FRICC_API_BEGIN
   check_handle(T);
   const TermSpec* ts = find_term(term);
   if (!ts) fail(FRICC_EINVAL, "CASE NOT IMPLEMENTED: unknown contraction term '%s'", term ? term : "(null)");
-  if (!Wp_dev || !out_panel_dev || l_count < 0) fail(FRICC_EINVAL, "bad arguments");
+  if (!Wp_dev || !out_panel_dev || l_count < 0 || ldw < l_count || ld_out < l_count) fail(FRICC_EINVAL, "bad arguments");
   if (T->nnz == 0 || l_count == 0) return FRICC_OK;
   Layout& lay = get_layout(T, *ts);
-  // out panel is [R][l_count] row-major: address = R*l_count + (l - l_begin)
+  // out panel is [R][ld_out] row-major: address = R*ld_out + (l - l_begin)
   OutMap om;
   om.nR2 = 1;
   om.nL2 = 1;
-  om.sR1 = l_count;
+  om.sR1 = ld_out;
   om.sR2 = 0;
   om.sL1 = 1;
   om.sL2 = 0;
-  // l = l_begin + col is mapped through sL1; shift the base so that column l_begin lands at offset 0
-  spmm(lay, Wp_dev, l_count, l_begin, l_count, out_panel_dev - l_begin, om, ts->scale);
+  // the kernel maps column l = l_begin + col through sL1; shift the base so that column l_begin lands at offset 0
+  spmm(lay, Wp_dev, ldw, l_begin, l_count, out_panel_dev - l_begin, om, ts->scale);
+  FRICC_API_END
+}
+
+int fricc_accumulate_panels(const double* panels_dev, int64_t n_panels, int64_t ld, fricc_st_t T, const char* term,
+                            double* out_dev, const int64_t out_shape[4], const int64_t out_strides[4]) {
+  FRICC_API_BEGIN
+  check_handle(T);
+  const TermSpec* ts = find_term(term);
+  if (!ts) fail(FRICC_EINVAL, "CASE NOT IMPLEMENTED: unknown contraction term '%s'", term ? term : "(null)");
+  if (!panels_dev || !out_dev || n_panels <= 0 || ld <= 0) fail(FRICC_EINVAL, "bad arguments");
+  const int64_t* d = T->dims;
+  for (int q = 0; q < 2; q++)
+    if (out_shape[ts->oR[q]] != d[ts->tR[q]]) fail(FRICC_EINVAL, "term %s: out does not match T on the owner pair", ts->name);
+  OutMap om;
+  om.nR2 = d[ts->tR[1]];
+  om.nL2 = out_shape[ts->oL[1]];
+  om.sR1 = out_strides[ts->oR[0]];
+  om.sR2 = out_strides[ts->oR[1]];
+  om.sL1 = out_strides[ts->oL[0]];
+  om.sL2 = out_strides[ts->oL[1]];
+  const int64_t nR = d[ts->tR[0]] * d[ts->tR[1]];
+  const int64_t nL = out_shape[ts->oL[0]] * out_shape[ts->oL[1]];
+  accumulate_panels(panels_dev, n_panels, ld, nR, nL, out_dev, om);
   FRICC_API_END
 }
 

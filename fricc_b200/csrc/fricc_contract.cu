@@ -271,4 +271,27 @@ void spmm(const Layout& lay, const double* Wp, int64_t ldw, int64_t l_begin, int
                  out, om, scale);
 }
 
+
+// gathered column-shard panels [g][R][ld] -> strided 4-D output (one read-modify-write per element, no atomics)
+__global__ void accumulate_panels_kernel(const double* __restrict__ panels, int64_t total, int64_t ld, int64_t nR,
+                                         int64_t nL, double* __restrict__ out, OutMap om) {
+  int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  int64_t c = idx % ld;
+  int64_t t = idx / ld;
+  int64_t R = t % nR, g = t / nR;
+  int64_t l = g * ld + c;
+  if (l >= nL) return;
+  int64_t r1 = R / om.nR2, r2 = R - r1 * om.nR2;
+  int64_t l1 = l / om.nL2, l2 = l - l1 * om.nL2;
+  out[r1 * om.sR1 + r2 * om.sR2 + l1 * om.sL1 + l2 * om.sL2] += panels[idx];
+}
+
+void accumulate_panels(const double* panels, int64_t n_panels, int64_t ld, int64_t nR, int64_t nL, double* out,
+                       const OutMap& om) {
+  int64_t total = n_panels * nR * ld;
+  if (total <= 0) return;
+  FRICC_LAUNCH(accumulate_panels_kernel, (unsigned)ceil_div(total, 256), 256, 0, panels, total, ld, nR, nL, out, om);
+}
+
 }  // namespace fricc

@@ -37,4 +37,7 @@ struct OutMap {
 void spmm(const Layout& lay, const double* Wp_dev, int64_t ldw, int64_t l_begin, int64_t l_count, double* out_dev,
           const OutMap& om, double scale);
 
+void accumulate_panels(const double* panels_dev, int64_t n_panels, int64_t ld, int64_t nR, int64_t nL, double* out_dev,
+                       const OutMap& om);
+
 }  // namespace fricc

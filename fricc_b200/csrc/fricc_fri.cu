@@ -11,39 +11,12 @@
 //   sample_pivotal      fri_utils.cpp:63-127    pivotal_chain_kernel    (exact mod-1 running sum + scan-form decisions)
 //   fri_compression     fri_utils.cpp:439-522   compress_fri
 #include "fricc_fri.cuh"
+#include "fricc_psrc.cuh"
 
 #include <chrono>
 #include <cmath>
 
 namespace fricc {
-
-// error flag bits raised by kernels
-constexpr int ERRF_PROB = 1;     // some p > 1               (fri_utils.cpp:383-395)
-constexpr int ERRF_ACCEPT = 2;   // acceptance prob. not in [0,1] (fri_utils.cpp:84-94)
-constexpr int ERRF_DRAWS = 4;    // draw buffer too short
-
-// ---------------------------------------------------------------------------------------------------------------
-// probability source: explicit vector, or computed on the fly from x exactly as make_probability_vector does
-// ---------------------------------------------------------------------------------------------------------------
-struct PSrc {
-  const double* probs;  // explicit probabilities (stage-wise API) or nullptr
-  const double* x;      // dense tensor
-  double r;             // remaining norm
-  double nprime;        // (double)(m - |D|)
-  uint64_t key_cut;     // D = { key > key_cut } U { key == key_cut and idx <= idx_cut };  no D: key_cut = ~0
-  uint64_t idx_cut;
-  int absval;           // 1: return |x| (one_norm)
-  __device__ __forceinline__ double operator()(int64_t j) const {
-    if (probs) return probs[j];
-    double xv = x[j];
-    if (absval) return fabs(xv);
-    uint64_t key = abs_key(xv);
-    bool inD = key > key_cut || (key == key_cut && (uint64_t)j <= idx_cut);
-    if (inD) return 0.0;
-    // abs(x[i]) / remaining_norm * n_sample   (fri_utils.cpp:375), left to right, no contraction
-    return __dmul_rn(__ddiv_rn(fabs(xv), r), nprime);
-  }
-};
 
 // ---------------------------------------------------------------------------------------------------------------
 // exact sequential running sums: one CTA; all threads stage a tile of terms in shared memory, thread 0 performs the
@@ -69,18 +42,6 @@ norm_chain_kernel(PSrc ps, int64_t n, double* __restrict__ out) {
     __syncthreads();
   }
   if (threadIdx.x == 0) *out = carry;
-}
-
-// smallest i in [0, nsamp] with fl((double)i + rn) >= X   (uk_i = i*1.0 + rn, fri_utils.cpp:45-58)
-__device__ __forceinline__ int64_t first_sample_at_or_above(double X, double rn, int64_t nsamp) {
-  double g = __dsub_rn(X, rn);
-  int64_t i;
-  if (!(g > 0.0)) i = 0;
-  else if (g >= (double)nsamp) i = nsamp;
-  else i = (int64_t)ceil(g);
-  while (i > 0 && __dadd_rn((double)(i - 1), rn) >= X) i--;
-  while (i < nsamp && __dadd_rn((double)i, rn) < X) i++;
-  return i;
 }
 
 __global__ void __launch_bounds__(CH_THREADS)
@@ -364,9 +325,22 @@ static inline unsigned blocks_for(int64_t n, int threads) { return (unsigned)std
 // ---------------------------------------------------------------------------------------------------------------
 // host orchestration
 // ---------------------------------------------------------------------------------------------------------------
+// FRICC_ESCAN=0 selects the single-thread chain kernels (reference implementation of the exact sums, kept for A/B
+// testing); the default is the parallel binade-segmented scan of fricc_escan.cu.  Both are bit-identical.
+static int g_escan = -1;
+void set_parallel_scan(int on) { g_escan = on ? 1 : 0; }
+static bool use_parallel_scan() {
+  if (g_escan < 0) {
+    const char* e = getenv("FRICC_ESCAN");
+    g_escan = (e && e[0] == '0') ? 0 : 1;
+  }
+  return g_escan == 1;
+}
+
 double one_norm_sequential(const double* x, int64_t n) {
   if (n <= 0) return 0.0;
   PSrc ps{nullptr, x, 0, 0, 0, 0, 1};
+  if (use_parallel_scan()) return exact_sum_parallel(ps, n, nullptr);
   DevBuf<double> out(1);
   FRICC_LAUNCH(norm_chain_kernel, 1, CH_THREADS, 0, ps, n, out.p);
   double h = 0;
@@ -428,11 +402,15 @@ static void run_systematic(const PSrc& ps, int64_t n, int64_t nsamp, const DrawS
   if (nsamp <= 0) return;
   FRICC_CUDA(cudaMemsetAsync(S_dev, 0, (size_t)nsamp * sizeof(int64_t), stream()));  // std::vector<size_t> S(n_sample)
   if (n <= 0) return;
-  DevBuf<int> err(1);
-  err.zero();
-  FRICC_LAUNCH(systematic_chain_kernel, 1, CH_THREADS, 0, ps, n, nsamp, rn, S_dev, err.p);
   int h = 0;
-  err.to_host(&h, 1);
+  if (use_parallel_scan()) {
+    systematic_parallel(ps, n, nsamp, rn, S_dev, &h);
+  } else {
+    DevBuf<int> err(1);
+    err.zero();
+    FRICC_LAUNCH(systematic_chain_kernel, 1, CH_THREADS, 0, ps, n, nsamp, rn, S_dev, err.p);
+    err.to_host(&h, 1);
+  }
   raise_flags(h);
 }
 

@@ -23,6 +23,9 @@ struct Compressed {
   DevBuf<double> vals;       // [m]
 };
 
+// select the implementation of the exact sums: 1 = parallel binade-segmented scan (default), 0 = one-thread chain
+void set_parallel_scan(int on);
+
 // exact sequential-order sums (bit-identical to a left-to-right fp64 accumulation)
 double one_norm_sequential(const double* x_dev, int64_t n);
 

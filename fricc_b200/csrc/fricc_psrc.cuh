@@ -1,0 +1,51 @@
+// fricc_psrc.cuh -- the probability source shared by the sampler kernels, and the kernel error flags.
+#pragma once
+#include "fricc_common.cuh"
+
+namespace fricc {
+
+// error flag bits raised by kernels
+constexpr int ERRF_PROB = 1;     // some p > 1                       (fri_utils.cpp:383-395)
+constexpr int ERRF_ACCEPT = 2;   // acceptance prob. not in [0,1]    (fri_utils.cpp:84-94)
+constexpr int ERRF_DRAWS = 4;    // draw buffer too short
+
+// probability source: an explicit vector, or computed on the fly from x exactly as make_probability_vector does
+// (/root/reference/src/fri_utils.cpp:367-398) -- the compression path never materialises p.
+// Requires -fmad=false in the including translation unit (no contraction of the divide/multiply).
+struct PSrc {
+  const double* probs;  // explicit probabilities (stage-wise API) or nullptr
+  const double* x;      // dense tensor
+  double r;             // remaining norm
+  double nprime;        // (double)(m - |D|)
+  uint64_t key_cut;     // D = { key > key_cut } U { key == key_cut and idx <= idx_cut };  no D: key_cut = ~0
+  uint64_t idx_cut;
+  int absval;           // 1: return |x| (one_norm)
+  __device__ __forceinline__ double operator()(int64_t j) const {
+    if (probs) return probs[j];
+    double xv = x[j];
+    if (absval) return fabs(xv);
+    uint64_t key = abs_key(xv);
+    bool inD = key > key_cut || (key == key_cut && (uint64_t)j <= idx_cut);
+    if (inD) return 0.0;
+    // abs(x[i]) / remaining_norm * n_sample   (fri_utils.cpp:375), left to right, no contraction
+    return __dmul_rn(__ddiv_rn(fabs(xv), r), nprime);
+  }
+};
+
+// smallest i in [0, nsamp] with fl((double)i + rn) >= X   (uk_i = i*1.0 + rn, fri_utils.cpp:45-58)
+__device__ __forceinline__ int64_t first_sample_at_or_above(double X, double rn, int64_t nsamp) {
+  double g = __dsub_rn(X, rn);
+  int64_t i;
+  if (!(g > 0.0)) i = 0;
+  else if (g >= (double)nsamp) i = nsamp;
+  else i = (int64_t)ceil(g);
+  while (i > 0 && __dadd_rn((double)(i - 1), rn) >= X) i--;
+  while (i < nsamp && __dadd_rn((double)i, rn) < X) i++;
+  return i;
+}
+
+// exact (left-to-right order) sums computed by the parallel binade-segmented scan  (fricc_escan.cu)
+double exact_sum_parallel(const PSrc& ps, int64_t n, int* err_flags_out);
+void systematic_parallel(const PSrc& ps, int64_t n, int64_t nsamp, double rn, int64_t* S_dev, int* err_flags_out);
+
+}  // namespace fricc

@@ -111,6 +111,7 @@ static void exclusive_scan_impl(T* d, int64_t n) {
 
 void exclusive_scan_u32(uint32_t* d, int64_t n) { exclusive_scan_impl<uint32_t>(d, n); }
 void exclusive_scan_i64(int64_t* d, int64_t n) { exclusive_scan_impl<int64_t>(d, n); }
+void exclusive_scan_f64(double* d, int64_t n) { exclusive_scan_impl<double>(d, n); }
 
 // ---------------------------------------------------------------------------------------------------------------
 // radix sort

@@ -20,5 +20,7 @@ int radix_sort_pairs(uint64_t* k[2], uint64_t* v[2], int64_t n, const std::vecto
 void exclusive_scan_u32(uint32_t* d, int64_t n);
 // exclusive prefix sum of n int64 values, in place
 void exclusive_scan_i64(int64_t* d, int64_t n);
+// exclusive prefix sum of n doubles, in place (tree order: an APPROXIMATION of the left-to-right sum)
+void exclusive_scan_f64(double* d, int64_t n);
 
 }  // namespace fricc

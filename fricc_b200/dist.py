@@ -1,0 +1,144 @@
+"""One-process-per-GPU orchestration of the FRI-CCSD inner loop.
+
+Sharding: every contraction  out[R, L] += scale * sum_K T[R, K] * W[K, L]  is split along its FREE pair L (the
+non-contracted pair of W): rank g owns the contiguous L-columns [g*lc, (g+1)*lc) of the [K][L] panel of W and produces
+the same columns of out.  The compressed tensor T (<= 16*m bytes) is replicated.  There is no data-path collective
+inside a contraction; the one exchange step is an all-gather of the column slices of each output (NCCL over
+NVLink), after which every rank holds the full output -- which is what the next compression needs.
+
+torch is used for device buffers, streams and torch.distributed only; all arithmetic is in libfricc_b200.so.
+"""
+import ctypes
+
+import torch
+
+from . import _lib
+from ._lib import check, i64x4
+from .py_rccsd import SparseTensor4d
+
+# term -> (W axes, out axes) in o/v extents, and which W axes form (K, L) / which out axes form (R, L)
+# (mirror of the C++ term table, fricc_contract.cu; used for sizes only)
+TERM_AXES = {
+    "2323": dict(w="vvvv", out="oovv", wK=(2, 3), wL=(0, 1), oR=(0, 1), oL=(2, 3)),
+    "0101": dict(w="oooo", out="oovv", wK=(0, 1), wL=(2, 3), oR=(2, 3), oL=(0, 1)),
+    "1323": dict(w="ovov", out="oooo", wK=(1, 3), wL=(0, 2), oR=(2, 3), oL=(0, 1)),
+    "1302": dict(w="voov", out="oovv", wK=(1, 3), wL=(0, 2), oR=(3, 1), oL=(2, 0)),
+    "1202": dict(w="vovo", out="oovv", wK=(1, 2), wL=(0, 3), oR=(3, 1), oL=(2, 0)),
+    "1303": dict(w="voov", out="oovv", wK=(1, 3), wL=(0, 2), oR=(3, 1), oL=(2, 0)),
+    "1203": dict(w="vovo", out="oovv", wK=(1, 2), wL=(0, 3), oR=(2, 1), oL=(3, 0)),
+    "0112": dict(w="ovov", out="voov", wK=(0, 1), wL=(2, 3), oR=(0, 2), oL=(1, 3)),
+    "0313": dict(w="ovov", out="voov", wK=(0, 3), wL=(2, 1), oR=(0, 2), oL=(1, 3)),
+    "0113": dict(w="ovov", out="voov", wK=(0, 1), wL=(2, 3), oR=(0, 2), oL=(1, 3)),
+    "0312": dict(w="ovov", out="vovo", wK=(0, 3), wL=(2, 1), oR=(0, 3), oL=(1, 2)),
+}
+
+
+def _ptr(t):
+    return ctypes.c_void_p(int(t.data_ptr()))
+
+
+def column_range(nL, rank, world):
+    """Columns of the free pair owned by `rank`: uniform width lc = ceil(nL/world) (the last shard may be short)."""
+    lc = -(-nL // world)
+    l0 = min(rank * lc, nL)
+    return l0, min(lc, nL - l0), lc
+
+
+class Comm:
+    """Thin wrapper: torch.distributed when world > 1, no-ops otherwise."""
+
+    def __init__(self, rank=0, world=1, group=None):
+        self.rank, self.world, self.group = rank, world, group
+
+    def all_gather(self, out, inp):
+        if self.world == 1:
+            if out.data_ptr() != inp.data_ptr():
+                out.view(-1)[: inp.numel()].copy_(inp.view(-1))
+            return
+        import torch.distributed as dist
+
+        dist.all_gather_into_tensor(out, inp, group=self.group)
+
+    def barrier(self):
+        if self.world > 1:
+            import torch.distributed as dist
+
+            dist.barrier(group=self.group)
+
+
+class ShardedTerm:
+    """One contraction term sharded by L-columns.  The W panel shard is either handed over already permuted
+    (`set_panel`, for operands that do not change between iterations) or permuted from a 4-D W on every call."""
+
+    def __init__(self, term, o, v, comm, device):
+        self.term, self.comm, self.device = term, comm, device
+        ax = TERM_AXES[term]
+        ext = {"o": o, "v": v}
+        self.w_shape = tuple(ext[c] for c in ax["w"])
+        self.out_shape = tuple(ext[c] for c in ax["out"])
+        self.nK = self.w_shape[ax["wK"][0]] * self.w_shape[ax["wK"][1]]
+        self.nL = self.w_shape[ax["wL"][0]] * self.w_shape[ax["wL"][1]]
+        self.nR = self.out_shape[ax["oR"][0]] * self.out_shape[ax["oR"][1]]
+        self.l0, self.lcnt, self.lc = column_range(self.nL, comm.rank, comm.world)
+        self.panel = None        # [nK][lcnt] W panel shard
+        self.out_panel = None    # [nR][lc]
+        self.gathered = None     # [world][nR][lc]
+        self.L = _lib.lib()
+
+    # -- operands ---------------------------------------------------------------------------------------------
+    def panel_bytes(self):
+        return self.nK * max(self.lcnt, 1) * 8
+
+    def set_panel(self, panel):
+        assert panel.dtype == torch.float64 and panel.numel() >= self.nK * self.lcnt
+        self.panel = panel
+
+    def permute_from(self, W):
+        """W: 4-D float64 CUDA tensor (any strides) -> this rank's [nK][lcnt] panel (hand-written transpose kernel)."""
+        if self.panel is None:
+            self.panel = torch.empty(self.nK * max(self.lcnt, 1), dtype=torch.float64, device=self.device)
+        if self.lcnt > 0:
+            check(self.L.fricc_permute_w(_ptr(W), _lib.FRICC_DEVICE, i64x4(W.shape), i64x4(W.stride()),
+                                         self.term.encode(), self.l0, self.lcnt, _ptr(self.panel)))
+
+    # -- compute ----------------------------------------------------------------------------------------------
+    def local(self, T):
+        """This rank's column slice of the output: out_panel[R][c] = scale * sum_K T[R,K] * Wp[K][c]."""
+        if self.out_panel is None:
+            self.out_panel = torch.empty(self.nR * self.lc, dtype=torch.float64, device=self.device)
+        self.out_panel.zero_()
+        if self.lcnt > 0:
+            check(self.L.fricc_contract_panel(_ptr(self.panel), self.lcnt, self.l0, self.lcnt, T._h,
+                                              _ptr(self.out_panel), self.lc, self.term.encode()))
+        return self.out_panel
+
+    def exchange_and_accumulate(self, T, out):
+        """all-gather the column slices and add them into the full 4-D output on every rank."""
+        w = self.comm.world
+        if w == 1:
+            g = self.out_panel
+        else:
+            if self.gathered is None:
+                self.gathered = torch.empty(w * self.nR * self.lc, dtype=torch.float64, device=self.device)
+            self.comm.all_gather(self.gathered, self.out_panel)
+            g = self.gathered
+        check(self.L.fricc_accumulate_panels(_ptr(g), w, self.lc, T._h, self.term.encode(), _ptr(out),
+                                             i64x4(out.shape), i64x4(out.stride())))
+
+    def __call__(self, T, out, W=None):
+        if W is not None:
+            self.permute_from(W)
+        self.local(T)
+        self.exchange_and_accumulate(T, out)
+
+
+def use_torch_stream():
+    """Issue the library's work on torch's current stream (so torch.cuda.Event timing and NCCL ordering see it)."""
+    s = torch.cuda.current_stream().cuda_stream
+    check(_lib.lib().fricc_set_stream(ctypes.c_void_p(s)))
+
+
+def compress(t2, m, compression="fri", sampling_method="systematic", draws=None):
+    """Replicated compression of the (replicated) dense T2: every rank runs the same deterministic kernels on the
+    same data with the same draws, so the sparse tensors are identical without any exchange."""
+    return SparseTensor4d(t2, tuple(t2.shape), int(m), compression, sampling_method, False, draws=draws)

@@ -118,6 +118,11 @@ def srand(seed):
     check(_lib.lib().fricc_srand(int(seed) & 0xFFFFFFFF))
 
 
+def set_option(key, value):
+    """Library switches (include/fricc_b200.h: fricc_set_option), e.g. ``set_option("escan", 0)``."""
+    check(_lib.lib().fricc_set_option(str(key).encode(), int(value)))
+
+
 def rand_consumed():
     return int(_lib.lib().fricc_rand_consumed())
 

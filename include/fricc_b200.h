@@ -48,6 +48,9 @@ int fricc_device_count(int* count);
 int fricc_set_device(int device);
 int fricc_set_stream(void* cuda_stream);      /* cudaStream_t of the caller (e.g. torch's current stream); NULL = default */
 int fricc_stream_synchronize(void);
+/* tuning / A-B switches.  "escan": 1 (default) = exact running sums by the parallel binade-segmented scan,
+ * 0 = by the one-thread chain kernels (bit-identical results, kept as the in-library cross-check).               */
+int fricc_set_option(const char* key, int value);
 /* number of kernels this library has launched since load (bench.py's "gpu_launches" evidence) */
 int64_t fricc_kernel_launches(void);
 
@@ -91,10 +94,15 @@ int fricc_st_export(fricc_st_t t, int64_t* flat_idx, double* vals, int mem);
 int fricc_contract(const double* W, int w_mem, const int64_t w_shape[4], const int64_t w_strides[4], fricc_st_t T,
                    double* out, int out_mem, const int64_t out_shape[4], const int64_t out_strides[4],
                    const char* term);
-/* Pre-permuted operand: Wp is already the [K][L_local] row-major panel the kernel streams, holding the L-columns
- * [l_begin, l_begin+l_count) of the term's free pair (the multi-GPU column shard).  out_panel is [R][l_count].   */
-int fricc_contract_panel(const double* Wp_dev, int64_t l_begin, int64_t l_count, fricc_st_t T, double* out_panel_dev,
-                         const char* term);
+/* Pre-permuted operand (the multi-GPU column shard): Wp is already the [K][ldw] row-major panel the kernel streams and
+ * holds the L-columns [l_begin, l_begin+l_count) of the term's free pair in its first l_count columns.
+ * out_panel is [R][ld_out] row-major and receives  out_panel[R][l - l_begin] += scale * sum_K T[R,K] * Wp[K][l - l_begin]. */
+int fricc_contract_panel(const double* Wp_dev, int64_t ldw, int64_t l_begin, int64_t l_count, fricc_st_t T,
+                         double* out_panel_dev, int64_t ld_out, const char* term);
+/* out[...] += panels[g][R][c] for the n_panels gathered column shards of `term` (panel g holds the L-columns
+ * [g*ld, min((g+1)*ld, nL)); panels is [n_panels][nR][ld] row-major on the device, out a 4-D strided device array).   */
+int fricc_accumulate_panels(const double* panels_dev, int64_t n_panels, int64_t ld, fricc_st_t T, const char* term,
+                            double* out_dev, const int64_t out_shape[4], const int64_t out_strides[4]);
 /* permute a 4-D W into the [K][L] panel layout of `term` on the device (columns [l_begin, l_begin+l_count))        */
 int fricc_permute_w(const double* W, int w_mem, const int64_t w_shape[4], const int64_t w_strides[4],
                     const char* term, int64_t l_begin, int64_t l_count, double* Wp_dev);

@@ -116,3 +116,40 @@ def test_error_conditions(rccsd):
         rccsd.SparseTensor4d(np.asfortranarray(np.zeros((2, 2, 3, 3))), (2, 2, 3, 3), 2, "largest")
     t = rccsd.SparseTensor4d([2, 2, 2, 2], 3)
     assert t.get_element(0) == ([0, 0, 0, 0], 0.0)
+
+
+@pytest.mark.parametrize("kind", ["heavy", "heavier", "uniform"])
+def test_parallel_exact_scan_equals_chain(rccsd, kind):
+    """The parallel binade-segmented scan (fricc_escan.cu) and the one-thread chain kernels are bit-identical at a size
+    where a tree-ordered sum is known to differ from the sequential one."""
+    rng = np.random.default_rng(77)
+    n, m = 6_000_000, 400_000
+    x = synth_t2(rng, n, kind)
+    x[: 5000] = 0.0                      # leading zeros: the zero-state path
+    draws = np.array([123456789], dtype=np.int32)
+    try:
+        rccsd.set_option("escan", 0)
+        norm0 = rccsd.one_norm(x)
+        idx0, val0 = rccsd.fri_compression(x, m, "systematic", draws=draws)
+    finally:
+        rccsd.set_option("escan", 1)
+    norm1 = rccsd.one_norm(x)
+    idx1, val1 = rccsd.fri_compression(x, m, "systematic", draws=draws)
+    assert norm0 == norm1
+    assert norm1 == float(np.cumsum(np.abs(x))[-1])   # numpy cumsum is the left-to-right recurrence
+    assert (idx0 == idx1).all() and np.array_equal(val0, val1)
+
+
+def test_exact_norm_adversarial(rccsd):
+    """Ties (addends that are odd multiples of half an ulp of the running sum), wide dynamic range, subnormals."""
+    rng = np.random.default_rng(3)
+    cases = [
+        np.concatenate([[1.0], rng.integers(0, 8, 300000) * 2.0 ** -53]),
+        np.concatenate([[0.75], rng.integers(1, 64, 300000) * 2.0 ** -54]),
+        rng.random(500000) * 10.0 ** rng.uniform(-20, 0, 500000),
+        np.concatenate([np.full(50, 5e-324), rng.random(5000) * 1e-310, rng.random(100000)]),
+        np.zeros(10000),
+        2.0 ** rng.integers(-60, 3, 200000).astype(np.float64),
+    ]
+    for x in cases:
+        assert rccsd.one_norm(x) == float(np.cumsum(np.abs(x))[-1])
