@@ -50,7 +50,7 @@ def parse_args():
     p.add_argument("--v", type=int, default=400)
     p.add_argument("--m", type=float, default=1e7)
     p.add_argument("--sampling", default="systematic", choices=["systematic", "pivotal"])
-    p.add_argument("--max-panel-gb", type=float, default=32.0, help="largest resident ladder W slice per sub-shard")
+    p.add_argument("--max-panel-gb", type=float, default=26.0, help="largest resident ladder W slice per sub-shard")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--only-ladder", action="store_true", help="debug: time only the ladder launches")
@@ -256,30 +256,60 @@ class Iteration:
             self.ladder_events.append((e0, e1, w))
         lad.exchange_and_accumulate(T, self.t2new)
 
+    def mark(self, name):
+        e = self.torch.cuda.Event(enable_timing=True)
+        e.record()
+        self.stage_events.append((name, e))
+
     def step(self, t2, timer=None):
+        self.mark("begin")
         T = self.compress(t2)
         T_alt = self.compress(t2)
+        self.mark("compress_x2")
         tm = self.terms
         if not self.args.only_ladder:
             self.Wklij.zero_(); self.Wakic.zero_(); self.Wakci.zero_()
             self.t2new.zero_()
             for t in self.tmp:
                 t.zero_()
+            self.mark("zero_outputs")
             tm["1323"](T_alt, self.Wklij)
+            self.mark("1323")
             tm["0112"](T_alt, self.Wakic)
+            self.mark("0112")
             tm["0313"](T_alt, self.Wakic)
+            self.mark("0313")
             tm["0113"](T_alt, self.Wakic)
+            self.mark("0113")
             tm["0312"](T_alt, self.Wakci)
+            self.mark("0312")
             tm["0101"](T, self.t2new, W=self.Wklij)
+            self.mark("0101")
         self.ladder(T, timer)
+        self.mark("2323_incl_regen" if not self.resident else "2323")
         if not self.args.only_ladder:
             tm["1302"](T, self.tmp[0], W=self.Wakic)
+            self.mark("1302")
             tm["1202"](T, self.tmp[0], W=self.Wakci)
+            self.mark("1202")
             tm["1303"].set_panel(tm["1302"].panel)   # same Wvoov panel (K=(k,c), L=(a,i))
             tm["1203"].set_panel(tm["1202"].panel)   # same Wvovo panel
             tm["1303"](T, self.tmp[1])
+            self.mark("1303")
             tm["1203"](T, self.tmp[2])
+            self.mark("1203")
         return T
+
+    def stage_breakdown(self, steps):
+        """ms per step spent between consecutive marks (rank-local; includes any exchange inside the stage)."""
+        self.torch.cuda.synchronize()
+        out = {}
+        for (n0, e0), (n1, e1) in zip(self.stage_events, self.stage_events[1:]):
+            if n1 == "begin":
+                continue
+            out[n1] = out.get(n1, 0.0) + e0.elapsed_time(e1)
+        self.stage_events.clear()
+        return {k: round(x / steps, 3) for k, x in out.items()}
 
 
 def ctypes_ptr(t, elem_offset=0):
@@ -393,6 +423,7 @@ def run_b200_arm(args):
         it.step(it.t2)
     sync_all()
     it.ladder_events.clear()
+    it.stage_events.clear()
 
     # ---- timed: device-resident inputs
     proc, cpath = start_clock_sampler(local_rank) if rank == 0 else (None, "")
@@ -407,6 +438,7 @@ def run_b200_arm(args):
     ms = timer.total_ms()
     launches = L.fricc_kernel_launches() - launches0
     clocks = stop_clock_sampler(proc, cpath) if rank == 0 else None
+    stage_ms = it.stage_breakdown(args.steps)
     lad_ms = [a.elapsed_time(b) for a, b, _ in it.ladder_events]
     lad_cols = [w for _, _, w in it.ladder_events]
     it.ladder_events.clear()
@@ -430,6 +462,7 @@ def run_b200_arm(args):
         sync_all()
         e2e_ms = t2timer.total_ms()
         it.ladder_events.clear()
+        it.stage_events.clear()
     # ---- reduce over ranks (max of times, sum of launches)
     stats = torch.tensor([ms, e2e_ms if not args.no_e2e else 0.0, float(launches)], dtype=torch.float64, device=device)
     if world > 1:
@@ -462,7 +495,7 @@ def run_b200_arm(args):
                          "launches_timed": len(lad_ms), "avg_launch_ms": (sum(lad_ms) / len(lad_ms)) if lad_ms else None,
                          "algorithmic_bytes_per_launch": (sum(alg) / len(alg)) if alg else None},
             "clocks": clocks, "gpu_launches": int(launches),
-            "ladder_ms_per_step": sum(lad_ms) / args.steps,
+            "ladder_ms_per_step": sum(lad_ms) / args.steps, "stage_ms_per_step": stage_ms,
             "timed_segments": "whole steps" if it.resident else
                               f"sum of segments; ladder W regenerated in HBM between {len(it.sub)} column sub-shards",
         }

@@ -128,6 +128,7 @@ int64_t fricc_kernel_launches(void) { return fricc::launches(); }
 int fricc_set_option(const char* key, int value) {
   FRICC_API_BEGIN
   if (key && strcmp(key, "escan") == 0) set_parallel_scan(value);
+  else if (key && strncmp(key, "spmm_", 5) == 0) set_spmm_option(key, value);
   else fail(FRICC_EINVAL, "unknown option '%s'", key ? key : "(null)");
   FRICC_API_END
 }

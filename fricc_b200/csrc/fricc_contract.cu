@@ -252,14 +252,111 @@ spmm_rows_kernel(const int64_t* __restrict__ rowptr, const uint32_t* __restrict_
   }
 }
 
+// Wide-tile variant: each thread owns NV2 double2 column pairs, interleaved so that every 128-bit load of a warp covers
+// 512 contiguous bytes; the bucket's (K, value) pairs are staged as ONE 16-byte shared-memory entry per nonzero, so a
+// nonzero costs one broadcast LDS.128 + NV2 LDG.128 + 2*NV2 DFMA per thread.  (The operand path -- one 8-byte W element
+// per FMA through L1 -- is the bound; the wider tile amortises the staged-entry reads and the address arithmetic.)
+struct __align__(16) StagedEntry {
+  unsigned long long koff;  // K * ldw (element offset of the panel row)
+  double val;
+};
+
+template <int NV2>
+__global__ void __launch_bounds__(256)
+spmm_rows_wide_kernel(const int64_t* __restrict__ rowptr, const uint32_t* __restrict__ kidx,
+                      const double* __restrict__ vals, const double* __restrict__ Wp, int64_t ldw, int64_t l_begin,
+                      int64_t l_count, double* __restrict__ out, OutMap om, double scale) {
+  __shared__ StagedEntry se[SPMM_CHUNK];
+  const int64_t R = blockIdx.x;
+  const int64_t e0 = rowptr[R], e1 = rowptr[R + 1];
+  if (e0 == e1) return;
+  const int stride = blockDim.x * 2;  // columns between a thread's consecutive double2
+  const int64_t col0 = (int64_t)blockIdx.y * (stride * NV2) + threadIdx.x * 2;
+  bool act[NV2];
+  double acc[2 * NV2];
+#pragma unroll
+  for (int j = 0; j < NV2; j++) {
+    act[j] = col0 + (int64_t)j * stride < l_count;
+    acc[2 * j] = 0.0;
+    acc[2 * j + 1] = 0.0;
+  }
+  const double* wcol = Wp + col0;
+
+  for (int64_t c = e0; c < e1; c += SPMM_CHUNK) {
+    const int cnt = (int)min((int64_t)SPMM_CHUNK, e1 - c);
+    __syncthreads();
+    for (int t = threadIdx.x; t < cnt; t += blockDim.x) {
+      StagedEntry e;
+      e.koff = (unsigned long long)kidx[c + t] * (unsigned long long)ldw;
+      e.val = vals[c + t];
+      se[t] = e;
+    }
+    __syncthreads();
+#pragma unroll 4
+    for (int t = 0; t < cnt; t++) {
+      const StagedEntry e = se[t];
+      const double* wp = wcol + e.koff;
+#pragma unroll
+      for (int j = 0; j < NV2; j++) {
+        if (act[j]) {
+          double2 w = __ldg(reinterpret_cast<const double2*>(wp + j * stride));
+          acc[2 * j] = fma(e.val, w.x, acc[2 * j]);
+          acc[2 * j + 1] = fma(e.val, w.y, acc[2 * j + 1]);
+        }
+      }
+    }
+  }
+  const int64_t r1 = R / om.nR2, r2 = R - r1 * om.nR2;
+  const int64_t rbase = r1 * om.sR1 + r2 * om.sR2;
+#pragma unroll
+  for (int j = 0; j < NV2; j++) {
+    if (act[j]) {
+#pragma unroll
+      for (int v = 0; v < 2; v++) {
+        int64_t l = l_begin + col0 + (int64_t)j * stride + v;
+        int64_t l1 = l / om.nL2, l2 = l - l1 * om.nL2;
+        int64_t o = rbase + l1 * om.sL1 + l2 * om.sL2;
+        out[o] += scale * acc[2 * j + v];
+      }
+    }
+  }
+}
+
+static int g_spmm_nv2 = 2;      // double2 per thread in the wide kernel (1, 2 or 4); 0 = narrow kernel
+static int g_spmm_threads = 64;  // measured best on B200 at the headline shape: 64 threads x 2 double2 (256-column tiles)
+void set_spmm_option(const char* key, int value) {
+  if (strcmp(key, "spmm_nv2") == 0) g_spmm_nv2 = value;
+  else if (strcmp(key, "spmm_threads") == 0) g_spmm_threads = value;
+}
+
 void spmm(const Layout& lay, const double* Wp, int64_t ldw, int64_t l_begin, int64_t l_count, double* out,
           const OutMap& om, double scale) {
   if (lay.nR == 0 || l_count == 0) return;
   bool vec2 = (ldw % 2 == 0) && (l_count % 2 == 0) && ((reinterpret_cast<uintptr_t>(Wp) & 15) == 0);
+  if (vec2 && g_spmm_nv2 > 0) {
+    int64_t pairs = l_count / 2;
+    int threads = 32;
+    while (threads < g_spmm_threads && threads < pairs) threads <<= 1;
+    int nv2 = g_spmm_nv2;
+    while (nv2 > 1 && (int64_t)threads * (nv2 / 2) >= pairs) nv2 >>= 1;  // do not over-provision small free pairs
+    int64_t tiles = ceil_div(pairs, (int64_t)threads * nv2);
+    if (tiles > 65535) fail(FRICC_EINVAL, "spmm: free pair too large (%lld columns)", (long long)l_count);
+    dim3 grid((unsigned)lay.nR, (unsigned)tiles);
+    if (nv2 >= 4)
+      FRICC_LAUNCH(spmm_rows_wide_kernel<4>, grid, threads, 0, lay.rowptr.p, lay.kidx.p, lay.vals.p, Wp, ldw, l_begin,
+                   l_count, out, om, scale);
+    else if (nv2 == 2)
+      FRICC_LAUNCH(spmm_rows_wide_kernel<2>, grid, threads, 0, lay.rowptr.p, lay.kidx.p, lay.vals.p, Wp, ldw, l_begin,
+                   l_count, out, om, scale);
+    else
+      FRICC_LAUNCH(spmm_rows_wide_kernel<1>, grid, threads, 0, lay.rowptr.p, lay.kidx.p, lay.vals.p, Wp, ldw, l_begin,
+                   l_count, out, om, scale);
+    return;
+  }
   int vec = vec2 ? 2 : 1;
   int64_t threads_needed = ceil_div(l_count, vec);
   int threads = 32;
-  while (threads < 256 && threads < threads_needed) threads <<= 1;
+  while (threads < 256 && threads < g_spmm_threads * 4 && threads < threads_needed) threads <<= 1;
   int64_t tiles = ceil_div(threads_needed, threads);
   if (tiles > 65535) fail(FRICC_EINVAL, "spmm: free pair too large (%lld columns)", (long long)l_count);
   dim3 grid((unsigned)lay.nR, (unsigned)tiles);
@@ -270,7 +367,6 @@ void spmm(const Layout& lay, const double* Wp, int64_t ldw, int64_t l_begin, int
     FRICC_LAUNCH(spmm_rows_kernel<1>, grid, threads, 0, lay.rowptr.p, lay.kidx.p, lay.vals.p, Wp, ldw, l_begin, l_count,
                  out, om, scale);
 }
-
 
 // gathered column-shard panels [g][R][ld] -> strided 4-D output (one read-modify-write per element, no atomics)
 __global__ void accumulate_panels_kernel(const double* __restrict__ panels, int64_t total, int64_t ld, int64_t nR,

@@ -37,6 +37,9 @@ struct OutMap {
 void spmm(const Layout& lay, const double* Wp_dev, int64_t ldw, int64_t l_begin, int64_t l_count, double* out_dev,
           const OutMap& om, double scale);
 
+// tuning switches of the SpMM launch ("spmm_nv2": double2 per thread 0/1/2/4, "spmm_threads")
+void set_spmm_option(const char* key, int value);
+
 void accumulate_panels(const double* panels_dev, int64_t n_panels, int64_t ld, int64_t nR, int64_t nL, double* out_dev,
                        const OutMap& om);
 

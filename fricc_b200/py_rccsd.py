@@ -218,7 +218,7 @@ class SparseTensor4d:
                 self._L.fricc_st_destroy(h)
             except Exception:
                 pass
-            self._h = c_void_p(None)
+            self._h = None  # (at interpreter shutdown module globals such as c_void_p may already be gone)
 
     # -- accessors -------------------------------------------------------------------------------------------
     def size(self):
