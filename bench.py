@@ -238,9 +238,11 @@ class Iteration:
         torch = self.torch
         lad = self.terms["2323"]
         L = lad.L
-        if lad.out_panel is None:
-            lad.out_panel = torch.empty(lad.nR * lad.lc, dtype=torch.float64, device=self.device)
-        lad.out_panel.zero_()
+        single = self.comm.world == 1   # one rank: accumulate straight into t2new (no panel, no gather)
+        if not single:
+            if lad.out_panel is None:
+                lad.out_panel = torch.empty(lad.nR * lad.lc, dtype=torch.float64, device=self.device)
+            lad.out_panel.zero_()
         for s, (c, w) in enumerate(self.sub):
             if not self.resident:
                 if timer:
@@ -250,11 +252,15 @@ class Iteration:
                     timer.resume()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
-            self.fd.check(L.fricc_contract_panel(self.fd._ptr(self.lad_panel), w, lad.l0 + c, w, T._h,
-                                                 ctypes_ptr(lad.out_panel, c), lad.lc, b"2323"))
+            if single:
+                lad.local_into(T, self.t2new, panel=self.lad_panel, l0=lad.l0 + c, lcnt=w)
+            else:
+                self.fd.check(L.fricc_contract_panel(self.fd._ptr(self.lad_panel), w, lad.l0 + c, w, T._h,
+                                                     ctypes_ptr(lad.out_panel, c), lad.lc, b"2323"))
             e1.record()
             self.ladder_events.append((e0, e1, w))
-        lad.exchange_and_accumulate(T, self.t2new)
+        if not single:
+            lad.exchange_and_accumulate(T, self.t2new)
 
     def mark(self, name):
         e = self.torch.cuda.Event(enable_timing=True)
@@ -310,6 +316,26 @@ class Iteration:
             out[n1] = out.get(n1, 0.0) + e0.elapsed_time(e1)
         self.stage_events.clear()
         return {k: round(x / steps, 3) for k, x in out.items()}
+
+
+def ncu_traffic_per_launch():
+    """dram__bytes_read.sum + dram__bytes_write.sum of ONE ladder launch (1600 x 20000-column slice, m=1e7), from the
+    committed `ncu --set full` capture (profiles/ncu_full_*_spmm_ladder.csv, newest round); None if absent."""
+    import csv
+    import glob
+
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "ncu_full_r*_spmm_ladder.csv")))
+    if not files:
+        return None
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
+    tot = 0.0
+    try:
+        for row in csv.DictReader(open(files[-1])):
+            if row["metric"] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                tot += float(row["value"]) * scale[row["unit"]]
+    except Exception:
+        return None
+    return tot or None
 
 
 def ctypes_ptr(t, elem_offset=0):
@@ -491,7 +517,8 @@ def run_b200_arm(args):
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": False, "scaling": "strong",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": workload_config(args, world),
             "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                         "traffic": None, "kernel": "spmm_rows_kernel<2> (ladder 2323)", "peak_source": peak_kind,
+                         "traffic": ncu_traffic_per_launch(), "kernel": "spmm_rows_wide_kernel<2> (ladder 2323)",
+                         "peak_source": peak_kind,
                          "launches_timed": len(lad_ms), "avg_launch_ms": (sum(lad_ms) / len(lad_ms)) if lad_ms else None,
                          "algorithmic_bytes_per_launch": (sum(alg) / len(alg)) if alg else None},
             "clocks": clocks, "gpu_launches": int(launches),

@@ -66,6 +66,8 @@ SIGNATURES = {
     "fricc_st_export": (c_int, [c_void_p, c_void_p, c_void_p, c_int]),
     "fricc_contract": (c_int, [c_void_p, c_int, _i64p, _i64p, c_void_p, c_void_p, c_int, _i64p, _i64p, c_char_p]),
     "fricc_contract_panel": (c_int, [c_void_p, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_int64, c_char_p]),
+    "fricc_contract_panel_into": (c_int, [c_void_p, c_int64, c_int64, c_int64, c_void_p, c_void_p, _i64p, _i64p,
+                                          c_char_p]),
     "fricc_accumulate_panels": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_char_p, c_void_p, _i64p, _i64p]),
     "fricc_permute_w": (c_int, [c_void_p, c_int, _i64p, _i64p, c_char_p, c_int64, c_int64, c_void_p]),
     "fricc_one_norm": (c_int, [c_void_p, c_int, c_int64, _f64p]),

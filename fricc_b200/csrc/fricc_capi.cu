@@ -128,6 +128,7 @@ int64_t fricc_kernel_launches(void) { return fricc::launches(); }
 int fricc_set_option(const char* key, int value) {
   FRICC_API_BEGIN
   if (key && strcmp(key, "escan") == 0) set_parallel_scan(value);
+  else if (key && strcmp(key, "d_candidates") == 0) set_first_candidates(value);
   else if (key && strncmp(key, "spmm_", 5) == 0) set_spmm_option(key, value);
   else fail(FRICC_EINVAL, "unknown option '%s'", key ? key : "(null)");
   FRICC_API_END
@@ -354,6 +355,33 @@ int fricc_contract_panel(const double* Wp_dev, int64_t ldw, int64_t l_begin, int
   FRICC_API_END
 }
 
+int fricc_contract_panel_into(const double* Wp_dev, int64_t ldw, int64_t l_begin, int64_t l_count, fricc_st_t T,
+                              double* out_dev, const int64_t out_shape[4], const int64_t out_strides[4],
+                              const char* term) {
+  FRICC_API_BEGIN
+  check_handle(T);
+  const TermSpec* ts = find_term(term);
+  if (!ts) fail(FRICC_EINVAL, "CASE NOT IMPLEMENTED: unknown contraction term '%s'", term ? term : "(null)");
+  if (!Wp_dev || !out_dev || !out_shape || !out_strides || l_begin < 0 || l_count < 0 || ldw < l_count)
+    fail(FRICC_EINVAL, "bad arguments");
+  const int64_t* d = T->dims;
+  for (int q = 0; q < 2; q++)
+    if (out_shape[ts->oR[q]] != d[ts->tR[q]]) fail(FRICC_EINVAL, "term %s: out does not match T on the owner pair", ts->name);
+  const int64_t nL = out_shape[ts->oL[0]] * out_shape[ts->oL[1]];
+  if (l_begin + l_count > nL) fail(FRICC_EINVAL, "column range out of bounds");
+  if (T->nnz == 0 || l_count == 0) return FRICC_OK;
+  Layout& lay = get_layout(T, *ts);
+  OutMap om;
+  om.nR2 = d[ts->tR[1]];
+  om.nL2 = out_shape[ts->oL[1]];
+  om.sR1 = out_strides[ts->oR[0]];
+  om.sR2 = out_strides[ts->oR[1]];
+  om.sL1 = out_strides[ts->oL[0]];
+  om.sL2 = out_strides[ts->oL[1]];
+  spmm(lay, Wp_dev, ldw, l_begin, l_count, out_dev, om, ts->scale);
+  FRICC_API_END
+}
+
 int fricc_accumulate_panels(const double* panels_dev, int64_t n_panels, int64_t ld, fricc_st_t T, const char* term,
                             double* out_dev, const int64_t out_shape[4], const int64_t out_strides[4]) {
   FRICC_API_BEGIN
@@ -407,7 +435,7 @@ int fricc_get_d_largest(const double* x, int mem, int64_t n, int64_t n_sample, i
   select_top_m(xd.p, n, n_sample, top);
   int64_t nD = 0;
   double r = norm;
-  if (n_sample > 0) d_greedy(top, norm, &nD, &r);
+  if (n_sample > 0) d_greedy(top, n_sample, norm, &nD, &r);
   if (nD > 0 && D_out) top.idx.to_host(reinterpret_cast<uint64_t*>(D_out), (size_t)nD);
   FRICC_CUDA(cudaStreamSynchronize(stream()));
   *n_D = nD;

@@ -383,10 +383,72 @@ __global__ void accumulate_panels_kernel(const double* __restrict__ panels, int6
   out[r1 * om.sR1 + r2 * om.sR2 + l1 * om.sL1 + l2 * om.sL2] += panels[idx];
 }
 
+// Tiled variant for outputs whose unit-stride axis is NOT the L-minor one (the panel's unit-stride axis): a 32x32
+// shared-memory transpose between the out-contiguous index X (R major, R minor or L major) and the panel-contiguous
+// index l2, with the two remaining indices fixed per CTA.  Reads are 256-byte runs of the panel, writes 256-byte runs
+// of out; one read-modify-write per output element, no atomics.
+//   XMODE 0: X = r1 (fixed: r2, l1)    XMODE 1: X = r2 (fixed: r1, l1)    XMODE 2: X = l1 (fixed: r1, r2)
+template <int XMODE>
+__global__ void __launch_bounds__(256)
+accumulate_panels_tiled_kernel(const double* __restrict__ panels, int64_t ld, int64_t nR, int64_t nL, int64_t nR1,
+                               int64_t nL1, double* __restrict__ out, OutMap om) {
+  __shared__ double tile[32][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int64_t fixed = blockIdx.x;
+  const int64_t x0 = (int64_t)blockIdx.y * 32, q0 = (int64_t)blockIdx.z * 32;  // q = l2
+  int64_t r1 = 0, r2 = 0, l1 = 0, nX;
+  if (XMODE == 0) { r2 = fixed % om.nR2; l1 = fixed / om.nR2; nX = nR1; }
+  else if (XMODE == 1) { r1 = fixed % nR1; l1 = fixed / nR1; nX = om.nR2; }
+  else { r2 = fixed % om.nR2; r1 = fixed / om.nR2; nX = nL1; }
+  // load: rows of the tile = X, columns = l2 (contiguous in the panel)
+  for (int r = ty; r < 32; r += 8) {
+    const int64_t x = x0 + r, q = q0 + tx;
+    if (x < nX && q < om.nL2) {
+      int64_t R, l;
+      if (XMODE == 0) { R = x * om.nR2 + r2; l = l1 * om.nL2 + q; }
+      else if (XMODE == 1) { R = r1 * om.nR2 + x; l = l1 * om.nL2 + q; }
+      else { R = r1 * om.nR2 + r2; l = x * om.nL2 + q; }
+      const int64_t g = l / ld, c = l - g * ld;
+      tile[r][tx] = panels[(g * nR + R) * ld + c];
+    }
+  }
+  __syncthreads();
+  // store: rows = l2, columns = X (contiguous in out)
+  for (int r = ty; r < 32; r += 8) {
+    const int64_t q = q0 + r, x = x0 + tx;
+    if (x < nX && q < om.nL2) {
+      int64_t o;
+      if (XMODE == 0) o = x * om.sR1 + r2 * om.sR2 + l1 * om.sL1 + q * om.sL2;
+      else if (XMODE == 1) o = r1 * om.sR1 + x * om.sR2 + l1 * om.sL1 + q * om.sL2;
+      else o = r1 * om.sR1 + r2 * om.sR2 + x * om.sL1 + q * om.sL2;
+      out[o] += tile[tx][r];
+    }
+  }
+}
+
 void accumulate_panels(const double* panels, int64_t n_panels, int64_t ld, int64_t nR, int64_t nL, double* out,
                        const OutMap& om) {
   int64_t total = n_panels * nR * ld;
   if (total <= 0) return;
+  const int64_t nR1 = nR / om.nR2, nL1 = nL / om.nL2;
+  // pick the transposing kernel when out's unit-stride axis is r1, r2 or l1 (and the grid fits)
+  int xmode = -1;
+  int64_t fixed = 0, nX = 0;
+  if (om.sL2 != 1 && n_panels * ld >= nL) {
+    if (om.sR1 == 1) { xmode = 0; fixed = om.nR2 * nL1; nX = nR1; }
+    else if (om.sR2 == 1) { xmode = 1; fixed = nR1 * nL1; nX = om.nR2; }
+    else if (om.sL1 == 1) { xmode = 2; fixed = nR1 * om.nR2; nX = nL1; }
+  }
+  if (xmode >= 0 && fixed > 0 && fixed < ((int64_t)1 << 31) && ceil_div(nX, 32) <= 65535 && ceil_div(om.nL2, 32) <= 65535) {
+    dim3 grid((unsigned)fixed, (unsigned)ceil_div(nX, 32), (unsigned)ceil_div(om.nL2, 32));
+    if (xmode == 0)
+      FRICC_LAUNCH(accumulate_panels_tiled_kernel<0>, grid, 256, 0, panels, ld, nR, nL, nR1, nL1, out, om);
+    else if (xmode == 1)
+      FRICC_LAUNCH(accumulate_panels_tiled_kernel<1>, grid, 256, 0, panels, ld, nR, nL, nR1, nL1, out, om);
+    else
+      FRICC_LAUNCH(accumulate_panels_tiled_kernel<2>, grid, 256, 0, panels, ld, nR, nL, nR1, nL1, out, om);
+    return;
+  }
   FRICC_LAUNCH(accumulate_panels_kernel, (unsigned)ceil_div(total, 256), 256, 0, panels, total, ld, nR, nL, out, om);
 }
 

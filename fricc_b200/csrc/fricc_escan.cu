@@ -50,7 +50,7 @@ __device__ __forceinline__ EMap warp_incl_scan_emap(EMap m) {
   return m;
 }
 
-// ordered exclusive scan over the CTA (one map per thread); smem: ES_WARPS entries; all threads must call
+// ordered exclusive scan over the CTA (one map per thread); smem: one entry per warp; all threads must call
 __device__ __forceinline__ EMap block_excl_scan_emap(EMap mine, EMap* smem) {
   const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   EMap inc = warp_incl_scan_emap(mine);
@@ -123,9 +123,10 @@ escan_map_kernel(PSrc ps, int64_t n, const double* __restrict__ approx_excl, Chu
 // ---- exact scan of one chunk by the whole CTA ----------------------------------------------------------------------
 // p[0..cnt) are the chunk's addends (shared memory), c_in the exact running sum before the chunk.  On return
 // cs[j] = exact running sum after element j, and the function returns the exact running sum after the chunk.
+constexpr int ES_MAX_WARPS = 32;  // the resolve kernel runs the same chunk scan with a 1024-thread CTA
 struct ChunkScratch {
-  EMap warp_maps[ES_WARPS];
-  int first_cross[ES_WARPS];
+  EMap warp_maps[ES_MAX_WARPS];
+  int first_cross[ES_MAX_WARPS];
   double c;
   int start;
 };
@@ -182,7 +183,7 @@ __device__ double chunk_exact_scan(const double* __restrict__ p, int cnt, double
     if (lane == 0) sc->first_cross[warp] = wf;
     __syncthreads();
     int jx = ES_CHUNK;
-    for (int w = 0; w < ES_WARPS; w++) jx = min(jx, sc->first_cross[w]);
+    for (int w = 0; w < (int)(blockDim.x >> 5); w++) jx = min(jx, sc->first_cross[w]);
     const int valid_end = min(jx, cnt);
 #pragma unroll
     for (int q = 0; q < ES_E; q++) {
@@ -211,14 +212,21 @@ __device__ double chunk_exact_scan(const double* __restrict__ p, int cnt, double
 }
 
 // ---- E3 ----------------------------------------------------------------------------------------------------------
-// One CTA.  Warp 0 consumes the chunk maps 32 at a time; every other warp idles except when a chunk has to be redone
-// cooperatively.  exact_in[i] = exact running sum before chunk i; *total = exact sum of everything.
-__global__ void __launch_bounds__(ES_THREADS)
+// One CTA of RS_THREADS threads walks the chunk maps RS_THREADS at a time (CTA-wide ordered scan of maps), carrying the
+// EXACT sum; the first chunk of a batch whose map is not applicable (binade crossing inside it, or the prediction was
+// off) is redone cooperatively with real additions at the crossings, and the walk resumes behind it.
+// exact_in[i] = exact running sum before chunk i; *total = exact sum of everything.
+constexpr int RS_THREADS = 1024;
+constexpr int RS_WARPS = RS_THREADS / 32;
+
+__global__ void __launch_bounds__(RS_THREADS)
 escan_resolve_kernel(PSrc ps, int64_t n, const ChunkMap* __restrict__ maps, int64_t nchunks,
                      double* __restrict__ exact_in, double* __restrict__ total, int* __restrict__ stats) {
   __shared__ double pbuf[ES_CHUNK];
   __shared__ double cs[ES_CHUNK];
   __shared__ ChunkScratch sc;
+  __shared__ EMap s_wmap[RS_WARPS];
+  __shared__ int s_wgood[RS_WARPS];
   __shared__ double s_c;
   __shared__ long long s_next;
   __shared__ int s_dirty;
@@ -233,9 +241,9 @@ escan_resolve_kernel(PSrc ps, int64_t n, const ChunkMap* __restrict__ maps, int6
     const int64_t i0 = s_next;
     if (i0 >= nchunks) break;
     __syncthreads();
-    if (warp == 0) {
+    {
       const double c = s_c;
-      const int64_t i = i0 + lane;
+      const int64_t i = i0 + threadIdx.x;
       ChunkMap cm;
       cm.A = 0; cm.B = 0; cm.even = 0; cm.k = ES_K_NONE;
       if (i < nchunks) cm = maps[i];
@@ -244,30 +252,39 @@ escan_resolve_kernel(PSrc ps, int64_t n, const ChunkMap* __restrict__ maps, int6
       const int64_t C0 = cnormal ? fx_to_state(c) : 0;
       EMap m{cm.A, cm.B, cm.even};
       EMap inc = warp_incl_scan_emap(m);
-      int64_t S_after = emap_apply(inc, C0);
-      // a lane is fine if its chunk's prediction matches the current binade and the sum stays inside the binade
-      bool ok = (i < nchunks) && cnormal && cm.k == kc && S_after < FX_TWO53;
-      unsigned okmask = __ballot_sync(0xffffffffu, ok);
-      int ngood = __ffs(~okmask) - 1;  // number of leading fine lanes (0..32); ~okmask == 0 -> ffs = 0 -> -1
-      if (okmask == 0xffffffffu) ngood = 32;
-      // exact sum BEFORE chunk i0+lane = state after lane-1
+      if (lane == 31) s_wmap[warp] = inc;
+      __syncthreads();
+      // composed map of all preceding warps: lanes load the warp totals below `warp`, ordered warp scan, take the last
+      EMap wm = (lane < warp) ? s_wmap[lane] : emap_identity();
+      wm = warp_incl_scan_emap(wm);
+      EMap pre;
+      pre.A = __shfl_sync(0xffffffffu, wm.A, 31);
+      pre.B = __shfl_sync(0xffffffffu, wm.B, 31);
+      pre.even = __shfl_sync(0xffffffffu, wm.even, 31);
+      const int64_t S_after = emap_apply(emap_compose(pre, inc), C0);
+      // a chunk is fine if its prediction matches the current binade and the sum stays inside the binade behind it
+      const bool ok = (i < nchunks) && cnormal && cm.k == kc && S_after < FX_TWO53;
+      const unsigned okmask = __ballot_sync(0xffffffffu, ok);
+      if (lane == 0) s_wgood[warp] = (okmask == 0xffffffffu) ? 32 : (__ffs(~okmask) - 1);
+      // exact state BEFORE chunk i = state after chunk i-1
       int64_t S_before = __shfl_up_sync(0xffffffffu, S_after, 1);
-      if (lane == 0) S_before = C0;
-      if ((int)lane < ngood || ((int)lane == ngood && i < nchunks && ngood > 0)) {
-        exact_in[i] = fx_from_state(S_before, kc);
-      } else if ((int)lane == ngood && i < nchunks) {
-        exact_in[i] = c;  // ngood == 0: the first chunk of the batch starts from the carried sum itself
+      if (lane == 0) S_before = emap_apply(pre, C0);
+      __syncthreads();
+      int ngood = 0;  // number of leading fine chunks of the batch (0..RS_THREADS)
+      for (int w = 0; w < RS_WARPS; w++) {
+        const int g = s_wgood[w];
+        ngood += g;
+        if (g < 32) break;
       }
-      if (lane == 0) {
-        // advance over the fine lanes
-        s_dirty = 0;
+      const int t = (int)threadIdx.x;
+      if (i < nchunks) {
+        if (t < ngood || (t == ngood && ngood > 0)) exact_in[i] = fx_from_state(S_before, kc);
+        else if (t == ngood) exact_in[i] = c;  // ngood == 0: the batch's first chunk starts from the carried sum
       }
-      __syncwarp();
-      if (ngood > 0 && (int)lane == ngood - 1) s_c = fx_from_state(S_after, kc);
-      __syncwarp();
-      if (lane == 0) {
+      if (ngood > 0 && t == ngood - 1) s_c = fx_from_state(S_after, kc);
+      if (t == 0) {
         s_next = i0 + ngood;
-        if (ngood < 32 && i0 + ngood < nchunks) s_dirty = 1;  // chunk i0+ngood must be redone cooperatively
+        s_dirty = (ngood < RS_THREADS && i0 + ngood < nchunks) ? 1 : 0;  // chunk i0+ngood is redone cooperatively
       }
     }
     __syncthreads();
@@ -275,7 +292,7 @@ escan_resolve_kernel(PSrc ps, int64_t n, const ChunkMap* __restrict__ maps, int6
       const int64_t ic = s_next;
       const int64_t base = ic * ES_CHUNK;
       const int cnt = (int)min((int64_t)ES_CHUNK, n - base);
-      for (int k = threadIdx.x; k < cnt; k += ES_THREADS) pbuf[k] = ps(base + k);
+      for (int k = threadIdx.x; k < cnt; k += RS_THREADS) pbuf[k] = ps(base + k);
       __syncthreads();
       double c_out = chunk_exact_scan(pbuf, cnt, s_c, cs, &sc);
       if (threadIdx.x == 0) {
@@ -340,7 +357,7 @@ static void escan_prepare(const PSrc& ps, int64_t n, EscanPlan& pl) {
   FRICC_LAUNCH(escan_approx_kernel, (unsigned)pl.nchunks, ES_THREADS, 0, ps, n, pl.approx.p, pl.err.p);
   exclusive_scan_f64(pl.approx.p, pl.nchunks);
   FRICC_LAUNCH(escan_map_kernel, (unsigned)pl.nchunks, ES_THREADS, 0, ps, n, pl.approx.p, pl.maps.p);
-  FRICC_LAUNCH(escan_resolve_kernel, 1, ES_THREADS, 0, ps, n, pl.maps.p, pl.nchunks, pl.exact_in.p, pl.total.p,
+  FRICC_LAUNCH(escan_resolve_kernel, 1, RS_THREADS, 0, ps, n, pl.maps.p, pl.nchunks, pl.exact_in.p, pl.total.p,
                pl.stats.p);
 }
 

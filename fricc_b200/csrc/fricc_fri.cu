@@ -251,20 +251,21 @@ pivotal_chain_kernel(PSrc ps, int64_t n, int64_t nsamp, const int32_t* __restric
 // ---------------------------------------------------------------------------------------------------------------
 // D-selection (greedy over the descending candidate list) -- one warp, lanes prefetch, the test itself is sequential
 // ---------------------------------------------------------------------------------------------------------------
-__global__ void d_greedy_kernel(const uint64_t* __restrict__ keys, int64_t m, double norm, long long* __restrict__ nD,
-                                double* __restrict__ rout) {
+// keys[0..ncand) = the ncand largest magnitudes in descending order; n_sample = the reference's n (m_keep).
+__global__ void d_greedy_kernel(const uint64_t* __restrict__ keys, int64_t ncand, int64_t n_sample, double norm,
+                                long long* __restrict__ nD, double* __restrict__ rout) {
   const unsigned lane = threadIdx.x & 31;
   double r = norm;
   long long d = 0;
   bool stop = false;
-  for (int64_t base = 0; base < m && !stop; base += 32) {
-    uint64_t key = (base + lane < m) ? keys[base + lane] : 0;
+  for (int64_t base = 0; base < ncand && !stop; base += 32) {
+    uint64_t key = (base + lane < ncand) ? keys[base + lane] : 0;
     double mine = key_to_double(key);
-    int lim = (int)min((int64_t)32, m - base);
+    int lim = (int)min((int64_t)32, ncand - base);
     for (int t = 0; t < lim; t++) {
       double xi = __shfl_sync(0xffffffffu, mine, t);
       // if ((n_sample - d) * xi >= remaining_norm - xi && remaining_norm > 1e-14)   (fri_utils.cpp:415)
-      if (__dmul_rn((double)(m - d), xi) >= __dsub_rn(r, xi) && r > 1e-14) {
+      if (__dmul_rn((double)(n_sample - d), xi) >= __dsub_rn(r, xi) && r > 1e-14) {
         d++;
         r = __dsub_rn(r, xi);
       } else {
@@ -327,6 +328,8 @@ static inline unsigned blocks_for(int64_t n, int threads) { return (unsigned)std
 // ---------------------------------------------------------------------------------------------------------------
 // FRICC_ESCAN=0 selects the single-thread chain kernels (reference implementation of the exact sums, kept for A/B
 // testing); the default is the parallel binade-segmented scan of fricc_escan.cu.  Both are bit-identical.
+static int64_t g_first_candidates = 1 << 16;  // first size of the D candidate list ("d_candidates" option)
+void set_first_candidates(int64_t c) { g_first_candidates = c > 0 ? c : 1; }
 static int g_escan = -1;
 void set_parallel_scan(int on) { g_escan = on ? 1 : 0; }
 static bool use_parallel_scan() {
@@ -348,10 +351,10 @@ double one_norm_sequential(const double* x, int64_t n) {
   return h;
 }
 
-void d_greedy(const TopM& top, double norm, int64_t* nD, double* remaining_norm) {
+void d_greedy(const TopM& top, int64_t n_sample, double norm, int64_t* nD, double* remaining_norm) {
   DevBuf<long long> d(1);
   DevBuf<double> r(1);
-  FRICC_LAUNCH(d_greedy_kernel, 1, 32, 0, top.keys.p, top.m, norm, d.p, r.p);
+  FRICC_LAUNCH(d_greedy_kernel, 1, 32, 0, top.keys.p, top.m, n_sample, norm, d.p, r.p);
   long long hd = 0;
   d.to_host(&hd, 1);
   r.to_host(remaining_norm, 1);
@@ -487,11 +490,18 @@ void compress_fri(const double* x, int64_t n, int64_t m, Sampling method, const 
   double t0 = verbose ? now_s() : 0;
   // ---- get_d_largest: norm, candidates, greedy
   double norm = one_norm_sequential(x, n);
+  // D is a PREFIX of the descending-|x| order (the greedy test stops at its first failure, fri_utils.cpp:415-431) and
+  // nothing behind that prefix is ever used, so only the top `cand` magnitudes are selected and ordered; cand grows
+  // geometrically until the greedy test fails inside the candidate list (or the list is all m entries).
   TopM top;
-  select_top_m(x, n, m, top);
   int64_t nD = 0;
   double r = norm;
-  if (m > 0) d_greedy(top, norm, &nD, &r);
+  for (int64_t cand = std::min<int64_t>(m, g_first_candidates); m > 0;
+       cand = (cand > m / 16) ? m : cand * 16) {
+    select_top_m(x, n, cand, top);
+    d_greedy(top, m, norm, &nD, &r);
+    if (nD < cand || cand == m) break;
+  }
   double t1 = verbose ? now_s() : 0;
 
   // ---- probability source

@@ -30,7 +30,10 @@ void set_parallel_scan(int on);
 double one_norm_sequential(const double* x_dev, int64_t n);
 
 // get_d_largest on a sorted candidate list
-void d_greedy(const TopM& top, double norm, int64_t* nD, double* remaining_norm);
+// (top holds the top.m largest magnitudes; n_sample is the reference's n = m_keep, which may exceed top.m)
+void d_greedy(const TopM& top, int64_t n_sample, double norm, int64_t* nD, double* remaining_norm);
+// first size of the candidate list compress_fri orders when it looks for D (grows x16 until the greedy test stops)
+void set_first_candidates(int64_t c);
 
 // make_probability_vector (materialised; stage-wise API only -- the compression itself never stores p)
 void make_probability_vector(const double* x_dev, int64_t n, int64_t n_sample, const int64_t* D_dev, int64_t nD,

@@ -125,9 +125,21 @@ class ShardedTerm:
         check(self.L.fricc_accumulate_panels(_ptr(g), w, self.lc, T._h, self.term.encode(), _ptr(out),
                                              i64x4(out.shape), i64x4(out.stride())))
 
+    def local_into(self, T, out, panel=None, l0=None, lcnt=None):
+        """Single-rank form: accumulate this panel's columns straight into the 4-D output (no intermediate panel)."""
+        panel = self.panel if panel is None else panel
+        l0 = self.l0 if l0 is None else l0
+        lcnt = self.lcnt if lcnt is None else lcnt
+        if lcnt > 0:
+            check(self.L.fricc_contract_panel_into(_ptr(panel), lcnt, l0, lcnt, T._h, _ptr(out), i64x4(out.shape),
+                                                   i64x4(out.stride()), self.term.encode()))
+
     def __call__(self, T, out, W=None):
         if W is not None:
             self.permute_from(W)
+        if self.comm.world == 1:
+            self.local_into(T, out)
+            return
         self.local(T)
         self.exchange_and_accumulate(T, out)
 

@@ -48,7 +48,9 @@ int fricc_device_count(int* count);
 int fricc_set_device(int device);
 int fricc_set_stream(void* cuda_stream);      /* cudaStream_t of the caller (e.g. torch's current stream); NULL = default */
 int fricc_stream_synchronize(void);
-/* tuning / A-B switches.  "escan": 1 (default) = exact running sums by the parallel binade-segmented scan,
+/* tuning / A-B switches.  "d_candidates": first size of the candidate list ordered when looking for D (default 65536;
+ * it grows x16 until the greedy test stops inside the list -- any value gives identical results).
+ * "escan": 1 (default) = exact running sums by the parallel binade-segmented scan,
  * 0 = by the one-thread chain kernels (bit-identical results, kept as the in-library cross-check).               */
 int fricc_set_option(const char* key, int value);
 /* number of kernels this library has launched since load (bench.py's "gpu_launches" evidence) */
@@ -99,6 +101,12 @@ int fricc_contract(const double* W, int w_mem, const int64_t w_shape[4], const i
  * out_panel is [R][ld_out] row-major and receives  out_panel[R][l - l_begin] += scale * sum_K T[R,K] * Wp[K][l - l_begin]. */
 int fricc_contract_panel(const double* Wp_dev, int64_t ldw, int64_t l_begin, int64_t l_count, fricc_st_t T,
                          double* out_panel_dev, int64_t ld_out, const char* term);
+/* Same operand, but accumulated straight into the 4-D strided device output (the single-GPU form of the sharded step:
+ * no intermediate panel, no gather):  out[..R.., ..l..] += scale * sum_K T[R,K] * Wp[K][l - l_begin]  for the
+ * L-columns l in [l_begin, l_begin + l_count).  (reference: the same terms of src/sparse_tensor.cpp:349-382)          */
+int fricc_contract_panel_into(const double* Wp_dev, int64_t ldw, int64_t l_begin, int64_t l_count, fricc_st_t T,
+                              double* out_dev, const int64_t out_shape[4], const int64_t out_strides[4],
+                              const char* term);
 /* out[...] += panels[g][R][c] for the n_panels gathered column shards of `term` (panel g holds the L-columns
  * [g*ld, min((g+1)*ld, nL)); panels is [n_panels][nR][ld] row-major on the device, out a 4-D strided device array).   */
 int fricc_accumulate_panels(const double* panels_dev, int64_t n_panels, int64_t ld, fricc_st_t T, const char* term,
