@@ -50,9 +50,12 @@ SIGNATURES = {
     "fricc_stream_synchronize": (c_int, []),
     "fricc_set_option": (c_int, [c_char_p, c_int]),
     "fricc_kernel_launches": (c_int64, []),
+    "fricc_get_stat": (c_int, [c_char_p, _i64p]),
     "fricc_srand": (c_int, [c_uint32]),
     "fricc_rand_fill": (c_int, [POINTER(c_int32), c_int64]),
     "fricc_rand_consumed": (c_int64, []),
+    "fricc_rand_skip": (c_int, [c_int64]),
+    "fricc_rand_fill_device": (c_int, [c_void_p, c_int64]),
     "fricc_st_create_empty": (c_int, [_i64p, c_int64, POINTER(c_void_p)]),
     "fricc_st_create": (c_int, [c_void_p, c_int, _i64p, c_int64, c_char_p, c_char_p, c_int, POINTER(c_void_p)]),
     "fricc_st_create_with_draws": (c_int, [c_void_p, c_int, _i64p, c_int64, c_char_p, c_char_p, c_int, c_void_p,

@@ -129,8 +129,19 @@ int fricc_set_option(const char* key, int value) {
   FRICC_API_BEGIN
   if (key && strcmp(key, "escan") == 0) set_parallel_scan(value);
   else if (key && strcmp(key, "d_candidates") == 0) set_first_candidates(value);
+  else if (key && strcmp(key, "d_estimate") == 0) set_d_estimate(value);
+  else if (key && strcmp(key, "pivotal_parallel") == 0) set_pivotal_parallel(value);
+  else if (key && strcmp(key, "d_parallel") == 0) set_d_parallel(value);
   else if (key && strncmp(key, "spmm_", 5) == 0) set_spmm_option(key, value);
   else fail(FRICC_EINVAL, "unknown option '%s'", key ? key : "(null)");
+  FRICC_API_END
+}
+
+int fricc_get_stat(const char* key, int64_t* value) {
+  FRICC_API_BEGIN
+  if (!key || !value) fail(FRICC_EINVAL, "null argument");
+  if (strcmp(key, "pivotal_restarts") == 0) *value = pivotal_restarts_last();
+  else fail(FRICC_EINVAL, "unknown stat '%s'", key);
   FRICC_API_END
 }
 
@@ -145,6 +156,19 @@ int fricc_rand_fill(int32_t* out, int64_t n) {
   FRICC_API_END
 }
 int64_t fricc_rand_consumed(void) { return rand_consumed(); }
+int fricc_rand_skip(int64_t n) {
+  FRICC_API_BEGIN
+  if (n < 0) fail(FRICC_EINVAL, "bad arguments");
+  rand_skip(n);
+  FRICC_API_END
+}
+int fricc_rand_fill_device(int32_t* out_dev, int64_t n) {
+  FRICC_API_BEGIN
+  if (n < 0 || (!out_dev && n > 0)) fail(FRICC_EINVAL, "bad arguments");
+  rand_fill_device(out_dev, n);
+  FRICC_CUDA(cudaStreamSynchronize(stream()));
+  FRICC_API_END
+}
 
 // ---- SparseTensor4d ------------------------------------------------------------------------------------------
 int fricc_st_create_empty(const int64_t dims[4], int64_t nnz, fricc_st_t* out) {

@@ -99,6 +99,10 @@ struct DevBuf {
     FRICC_CUDA(cudaMemcpyAsync(dst, p, count * sizeof(T), cudaMemcpyDeviceToHost, stream()));
     FRICC_CUDA(cudaStreamSynchronize(stream()));
   }
+  void to_host_at(T* dst, size_t index) const {  // one element
+    FRICC_CUDA(cudaMemcpyAsync(dst, p + index, sizeof(T), cudaMemcpyDeviceToHost, stream()));
+    FRICC_CUDA(cudaStreamSynchronize(stream()));
+  }
   void from_host(const T* src, size_t count) {
     FRICC_CUDA(cudaMemcpyAsync(p, src, count * sizeof(T), cudaMemcpyHostToDevice, stream()));
   }

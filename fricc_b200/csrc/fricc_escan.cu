@@ -14,6 +14,8 @@
 //
 // Compiled with -fmad=false (the probabilities are computed exactly as the reference does).
 #include "fricc_exact.cuh"
+#include "fricc_fri.cuh"
+#include "fricc_mscan.cuh"
 #include "fricc_psrc.cuh"
 #include "fricc_sort.cuh"
 
@@ -380,6 +382,130 @@ void systematic_parallel(const PSrc& ps, int64_t n, int64_t nsamp, double rn, in
   FRICC_LAUNCH(escan_emit_kernel, (unsigned)pl.nchunks, ES_THREADS, 0, ps, n, pl.exact_in.p, nsamp, rn, S_dev);
   if (err_flags_out) pl.err.to_host(err_flags_out, 1);
   else FRICC_CUDA(cudaStreamSynchronize(stream()));
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Parallel D-selection.  get_d_largest (fri_utils.cpp:400-437) walks the descending candidates with
+//     if ((n - d) * x_d >= r - x_d && r > 1e-14) { D.push(d); r -= x_d; } else break;
+// i.e. a left-to-right fp64 running SUBTRACTION whose value decides every test.  While r stays in one binade it is
+// C * ulp with C in [2^52, 2^53); in the mirrored state M = 2^54 - C a subtraction of x is the round-half-even integer
+// ADDITION  M' = RN_even(M + x/ulp)  (2^54 is even, so the parities of C' and M' agree) -- the same maps as the running
+// sums above.  One pass = chunk maps -> ordered scan -> every candidate's exact r before it, its test, and whether r
+// leaves the binade behind it.  The first event ends the pass: a failed test is the answer; a binade crossing is redone
+// with one real subtraction on the host and the pass restarts behind it (at most a few times: r only shrinks).
+// ---------------------------------------------------------------------------------------------------------------------
+struct EMapOp {
+  typedef EMap T;
+  __device__ __forceinline__ static EMap identity() { return emap_identity(); }
+  __device__ __forceinline__ static EMap op(const EMap& f, const EMap& g) { return emap_compose(f, g); }
+  __device__ __forceinline__ static EMap shfl_up(const EMap& m, int o) { return shfl_up_emap(m, o); }
+};
+
+constexpr int64_t DG_MIRROR = (int64_t)1 << 54;
+constexpr int64_t DG_LEFT = 3 * FX_TWO52;  // M >= DG_LEFT  <=>  C <= 2^52: r is at or below the binade's lower edge
+constexpr int DG_THREADS = 256;
+constexpr int DG_E = 8;
+constexpr int DG_CHUNK = DG_THREADS * DG_E;
+constexpr unsigned long long DG_NONE = ~0ULL;
+
+__global__ void __launch_bounds__(DG_THREADS)
+dg_chunk_maps_kernel(const uint64_t* __restrict__ keys, int64_t lo, int64_t hi, int k, EMap* __restrict__ maps) {
+  __shared__ EMap sm[32];
+  const int64_t base = lo + (int64_t)blockIdx.x * DG_CHUNK + (int64_t)threadIdx.x * DG_E;
+  EMap m = emap_identity();
+#pragma unroll
+  for (int q = 0; q < DG_E; q++)
+    if (base + q < hi) m = emap_compose(m, emap_of(key_to_double(keys[base + q]), k));
+  EMap ex, tot;
+  ms_block_scan<EMapOp>(m, sm, &ex, &tot);
+  if (threadIdx.x == 0) maps[blockIdx.x] = tot;
+}
+
+// rbefore[d] = exact r before candidate d (d in [lo, hi)), rbefore[hi] = r after all of them (valid up to the first event)
+// event = min over candidates of  2*d (test fails at d)  /  2*d+1 (test holds, r leaves the binade behind d)
+__global__ void __launch_bounds__(DG_THREADS)
+dg_apply_kernel(const uint64_t* __restrict__ keys, int64_t lo, int64_t hi, int k, int64_t M0,
+                const EMap* __restrict__ chunk_excl, int64_t n_sample, double* __restrict__ rbefore,
+                unsigned long long* __restrict__ event) {
+  __shared__ EMap sm[32];
+  const int64_t base = lo + (int64_t)blockIdx.x * DG_CHUNK + (int64_t)threadIdx.x * DG_E;
+  EMap mine = emap_identity();
+  uint64_t key[DG_E];
+#pragma unroll
+  for (int q = 0; q < DG_E; q++) {
+    key[q] = (base + q < hi) ? keys[base + q] : 0ULL;
+    if (base + q < hi) mine = emap_compose(mine, emap_of(key_to_double(key[q]), k));
+  }
+  EMap ex, tot;
+  ms_block_scan<EMapOp>(mine, sm, &ex, &tot);
+  int64_t M = emap_apply(ex, emap_apply(chunk_excl[blockIdx.x], M0));
+#pragma unroll
+  for (int q = 0; q < DG_E; q++) {
+    const int64_t d = base + q;
+    if (d >= hi) break;
+    if (M > DG_LEFT) break;  // r left the binade before this candidate: an earlier candidate has reported it
+    const double r = fx_from_state(DG_MIRROR - M, k);
+    const double xi = key_to_double(key[q]);
+    rbefore[d] = r;
+    // if ((n_sample - d) * xi >= remaining_norm - xi && remaining_norm > 1e-14)   (fri_utils.cpp:415)
+    const bool pass = __dmul_rn((double)(n_sample - d), xi) >= __dsub_rn(r, xi) && r > 1e-14;
+    if (!pass) {
+      atomicMin(event, (unsigned long long)d * 2ULL);
+      break;
+    }
+    M = emap_apply(emap_of(xi, k), M);
+    if (M >= DG_LEFT) {  // C' <= 2^52: r - x_d is below the binade, or lands on its lower edge (possibly from below)
+      atomicMin(event, (unsigned long long)d * 2ULL + 1ULL);
+      break;
+    }
+    if (d == hi - 1) rbefore[hi] = fx_from_state(DG_MIRROR - M, k);
+  }
+}
+
+void d_greedy_parallel(const uint64_t* keys, int64_t cand, int64_t n_sample, double norm, int64_t* nD, double* r_out) {
+  DevBuf<double> rbefore((size_t)cand + 1);
+  DevBuf<unsigned long long> event(1);
+  int64_t lo = 0;
+  double r = norm;
+  while (lo < cand) {
+    if (!fx_is_normal_positive(r)) {  // zero / subnormal / non-finite remaining norm: the plain walk from here
+      d_greedy_serial(keys, lo, cand, n_sample, r, nD, r_out);
+      return;
+    }
+    const int k = fx_binade(r);
+    const int64_t M0 = DG_MIRROR - fx_to_state(r);
+    const int64_t nchunks = ceil_div(cand - lo, DG_CHUNK);
+    DevBuf<EMap> maps((size_t)nchunks), excl((size_t)nchunks);
+    FRICC_LAUNCH(dg_chunk_maps_kernel, (unsigned)nchunks, DG_THREADS, 0, keys, lo, cand, k, maps.p);
+    ms_exclusive_scan<EMapOp>(maps.p, nchunks, excl.p);
+    FRICC_CUDA(cudaMemsetAsync(event.p, 0xff, sizeof(unsigned long long), stream()));
+    FRICC_LAUNCH(dg_apply_kernel, (unsigned)nchunks, DG_THREADS, 0, keys, lo, cand, k, M0, excl.p, n_sample, rbefore.p,
+                 event.p);
+    unsigned long long ev = 0;
+    event.to_host(&ev, 1);
+    if (ev == DG_NONE) {
+      rbefore.to_host_at(r_out, (size_t)cand);
+      *nD = cand;
+      return;
+    }
+    const int64_t e = (int64_t)(ev >> 1);
+    double re = 0;
+    rbefore.to_host_at(&re, (size_t)e);
+    if ((ev & 1ULL) == 0) {  // the test fails at e
+      *nD = e;
+      *r_out = re;
+      return;
+    }
+    // the test holds at e and r - x_e drops into a lower binade: one real subtraction, continue behind it
+    uint64_t ke = 0;
+    FRICC_CUDA(cudaMemcpyAsync(&ke, keys + e, 8, cudaMemcpyDeviceToHost, stream()));
+    FRICC_CUDA(cudaStreamSynchronize(stream()));
+    volatile double diff = re - key_to_double(ke);  // IEEE binary64 subtraction (x86-64 SSE2), as the reference does
+    r = diff;
+    lo = e + 1;
+  }
+  *nD = cand;
+  *r_out = r;
 }
 
 }  // namespace fricc

@@ -91,12 +91,6 @@ constexpr int PV_THREADS = 512;
 constexpr int PV_IPT = 4;
 constexpr int PV_TILE = PV_THREADS * PV_IPT;
 
-struct PivotalState {
-  double a;           // running sum after the last visited element
-  long long isel;     // current candidate i
-  long long count;    // samples written
-  long long visited;  // number of loop iterations the reference would have executed (= draws consumed)
-};
 
 __global__ void __launch_bounds__(PV_THREADS)
 pivotal_chain_kernel(PSrc ps, int64_t n, int64_t nsamp, const int32_t* __restrict__ draws, int64_t ndraws,
@@ -251,14 +245,15 @@ pivotal_chain_kernel(PSrc ps, int64_t n, int64_t nsamp, const int32_t* __restric
 // ---------------------------------------------------------------------------------------------------------------
 // D-selection (greedy over the descending candidate list) -- one warp, lanes prefetch, the test itself is sequential
 // ---------------------------------------------------------------------------------------------------------------
-// keys[0..ncand) = the ncand largest magnitudes in descending order; n_sample = the reference's n (m_keep).
-__global__ void d_greedy_kernel(const uint64_t* __restrict__ keys, int64_t ncand, int64_t n_sample, double norm,
-                                long long* __restrict__ nD, double* __restrict__ rout) {
+// keys[0..ncand) = the ncand largest magnitudes in descending order; n_sample = the reference's n (m_keep); the walk
+// starts at candidate `lo` with remaining norm r_start.
+__global__ void d_greedy_kernel(const uint64_t* __restrict__ keys, int64_t lo, int64_t ncand, int64_t n_sample,
+                                double r_start, long long* __restrict__ nD, double* __restrict__ rout) {
   const unsigned lane = threadIdx.x & 31;
-  double r = norm;
-  long long d = 0;
+  double r = r_start;
+  long long d = lo;
   bool stop = false;
-  for (int64_t base = 0; base < ncand && !stop; base += 32) {
+  for (int64_t base = lo; base < ncand && !stop; base += 32) {
     uint64_t key = (base + lane < ncand) ? keys[base + lane] : 0;
     double mine = key_to_double(key);
     int lim = (int)min((int64_t)32, ncand - base);
@@ -329,7 +324,15 @@ static inline unsigned blocks_for(int64_t n, int threads) { return (unsigned)std
 // FRICC_ESCAN=0 selects the single-thread chain kernels (reference implementation of the exact sums, kept for A/B
 // testing); the default is the parallel binade-segmented scan of fricc_escan.cu.  Both are bit-identical.
 static int64_t g_first_candidates = 1 << 16;  // first size of the D candidate list ("d_candidates" option)
+static int g_d_parallel = -1;                 // "d_parallel" option: -1 auto (lists >= 32768), 0 serial, 1 parallel
+void set_d_parallel(int mode) { g_d_parallel = mode; }
+static int g_d_estimate = 1;                  // size the list from the histogram estimate ("d_estimate" option)
 void set_first_candidates(int64_t c) { g_first_candidates = c > 0 ? c : 1; }
+void set_d_estimate(int on) { g_d_estimate = on ? 1 : 0; }
+static int g_pivotal_parallel = -1;  // "pivotal_parallel" option: -1 auto, 0 chain kernel, 1 always parallel
+static int g_pivotal_restarts = 0;
+void set_pivotal_parallel(int mode) { g_pivotal_parallel = mode; }
+int pivotal_restarts_last() { return g_pivotal_restarts; }
 static int g_escan = -1;
 void set_parallel_scan(int on) { g_escan = on ? 1 : 0; }
 static bool use_parallel_scan() {
@@ -351,14 +354,23 @@ double one_norm_sequential(const double* x, int64_t n) {
   return h;
 }
 
-void d_greedy(const TopM& top, int64_t n_sample, double norm, int64_t* nD, double* remaining_norm) {
+void d_greedy_serial(const uint64_t* keys, int64_t lo, int64_t cand, int64_t n_sample, double r_start, int64_t* nD,
+                     double* remaining_norm) {
   DevBuf<long long> d(1);
   DevBuf<double> r(1);
-  FRICC_LAUNCH(d_greedy_kernel, 1, 32, 0, top.keys.p, top.m, n_sample, norm, d.p, r.p);
+  FRICC_LAUNCH(d_greedy_kernel, 1, 32, 0, keys, lo, cand, n_sample, r_start, d.p, r.p);
   long long hd = 0;
   d.to_host(&hd, 1);
   r.to_host(remaining_norm, 1);
   *nD = hd;
+}
+
+void d_greedy(const TopM& top, int64_t n_sample, double norm, int64_t* nD, double* remaining_norm) {
+  // short lists: the one-warp walk; long ones: the parallel rounding-map scan (bit-identical, "d_parallel" option)
+  if (g_d_parallel == 1 || (g_d_parallel < 0 && top.m >= (1 << 15)))
+    d_greedy_parallel(top.keys.p, top.m, n_sample, norm, nD, remaining_norm);
+  else
+    d_greedy_serial(top.keys.p, 0, top.m, n_sample, norm, nD, remaining_norm);
 }
 
 static void raise_flags(int flags) {
@@ -420,12 +432,19 @@ static void run_systematic(const PSrc& ps, int64_t n, int64_t nsamp, const DrawS
 static void run_pivotal(const PSrc& ps, int64_t n, int64_t nsamp, const DrawSource& draws, int64_t* consumed,
                         int64_t* S_dev) {
   if (n < 1) fail(FRICC_EINVAL, "pivotal sampling needs a non-empty probability vector");
-  RandSnapshot snap{};
-  if (draws.from_stream) snap = rand_snapshot();
-  std::vector<int32_t> d;
-  fetch_draws(draws, n - 1, d);
-  DevBuf<int32_t> dd(d.size());
-  if (!d.empty()) dd.from_host(d.data(), d.size());
+  // one draw per visited element (fri_utils.cpp:74).  Library stream: the next n-1 values of rand() are generated on
+  // the device (jump-ahead, fricc_rand.cu) and the host stream is advanced afterwards by exactly the number consumed.
+  DevBuf<int32_t> dd;
+  int64_t ndraws = 0;
+  if (draws.from_stream) {
+    ndraws = n - 1;
+    dd.alloc((size_t)std::max<int64_t>(ndraws, 1));
+    rand_fill_device(dd.p, ndraws);
+  } else {
+    ndraws = std::min<int64_t>(draws.n, n - 1);
+    dd.alloc((size_t)std::max<int64_t>(ndraws, 1));
+    if (ndraws > 0) dd.from_host(draws.host, (size_t)ndraws);
+  }
   DevBuf<int> err(1);
   err.zero();
   DevBuf<PivotalState> st(1);
@@ -435,21 +454,22 @@ static void run_pivotal(const PSrc& ps, int64_t n, int64_t nsamp, const DrawSour
     dummy.alloc(1);
     Sp = dummy.p;
   }
-  FRICC_LAUNCH(pivotal_chain_kernel, 1, PV_THREADS, 0, ps, n, nsamp, dd.p, (int64_t)d.size(), Sp, st.p, err.p);
+  bool done = false;
+  g_pivotal_restarts = 0;
+  if (g_pivotal_parallel == 1 || (g_pivotal_parallel < 0 && n >= (1 << 16))) {
+    done = pivotal_parallel(ps, n, nsamp, dd.p, ndraws, Sp, st.p, err.p, &g_pivotal_restarts);
+    if (!done) err.zero();  // (flags raised by the abandoned attempt are raised again by the chain kernel)
+  }
+  if (!done)
+    FRICC_LAUNCH(pivotal_chain_kernel, 1, PV_THREADS, 0, ps, n, nsamp, dd.p, ndraws, Sp, st.p, err.p);
   int h = 0;
   err.to_host(&h, 1);
   PivotalState hs{};
   st.to_host(&hs, 1);
   *consumed = hs.visited;
-  if (draws.from_stream) {  // leave the stream exactly where the reference's rand() state would be
-    rand_restore(snap);
-    if (hs.visited > 0) {
-      std::vector<int32_t> skip((size_t)hs.visited);
-      rand_fill(skip.data(), hs.visited);
-    }
-  }
+  if (draws.from_stream && hs.visited > 0) rand_skip(hs.visited);  // leave the stream where the reference's rand() would be
   // a short caller buffer only matters if the sampler actually walked past its end
-  if ((h & ERRF_DRAWS) && hs.visited <= (long long)d.size()) h &= ~ERRF_DRAWS;
+  if ((h & ERRF_DRAWS) && hs.visited <= (long long)ndraws) h &= ~ERRF_DRAWS;
   raise_flags(h);
   if (hs.count != nsamp)
     fail(FRICC_ECOUNT,
@@ -496,11 +516,20 @@ void compress_fri(const double* x, int64_t n, int64_t m, Sampling method, const 
   TopM top;
   int64_t nD = 0;
   double r = norm;
-  for (int64_t cand = std::min<int64_t>(m, g_first_candidates); m > 0;
-       cand = (cand > m / 16) ? m : cand * 16) {
+  bool estimated = false;
+  for (int64_t cand = std::min<int64_t>(m, g_first_candidates); m > 0;) {
     select_top_m(x, n, cand, top);
     d_greedy(top, m, norm, &nD, &r);
     if (nD < cand || cand == m) break;
+    // the list was exhausted: size the next one from a count+sum histogram estimate of where the greedy test stops
+    // (plus slack), at least x16
+    int64_t next = (cand > m / 16) ? m : cand * 16;
+    if (g_d_estimate && !estimated) {
+      int64_t est = estimate_d_candidates(x, n, m, norm);
+      next = std::max<int64_t>(next, est + est / 8 + 1024);
+      estimated = true;
+    }
+    cand = std::min<int64_t>(m, next);
   }
   double t1 = verbose ? now_s() : 0;
 

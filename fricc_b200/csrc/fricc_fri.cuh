@@ -32,8 +32,15 @@ double one_norm_sequential(const double* x_dev, int64_t n);
 // get_d_largest on a sorted candidate list
 // (top holds the top.m largest magnitudes; n_sample is the reference's n = m_keep, which may exceed top.m)
 void d_greedy(const TopM& top, int64_t n_sample, double norm, int64_t* nD, double* remaining_norm);
+// the plain one-warp walk from candidate `lo` with remaining norm r_start, and the parallel form (fricc_escan.cu)
+void d_greedy_serial(const uint64_t* keys_dev, int64_t lo, int64_t cand, int64_t n_sample, double r_start, int64_t* nD,
+                     double* remaining_norm);
+void d_greedy_parallel(const uint64_t* keys_dev, int64_t cand, int64_t n_sample, double norm, int64_t* nD,
+                       double* remaining_norm);
 // first size of the candidate list compress_fri orders when it looks for D (grows x16 until the greedy test stops)
 void set_first_candidates(int64_t c);
+void set_d_estimate(int on);
+void set_d_parallel(int mode);
 
 // make_probability_vector (materialised; stage-wise API only -- the compression itself never stores p)
 void make_probability_vector(const double* x_dev, int64_t n, int64_t n_sample, const int64_t* D_dev, int64_t nD,
@@ -45,6 +52,21 @@ void sample_systematic_probs(int64_t n_sample, const double* p_dev, int64_t n, c
 void sample_pivotal_probs(int64_t n_sample, const double* p_dev, int64_t n, const DrawSource& draws, int64_t* consumed,
                           int64_t* S_dev);
 
+// final state of a pivotal walk (device struct shared by the chain kernel and the parallel sampler)
+struct PivotalState {
+  double a;           // running sum after the last visited element
+  long long isel;     // current candidate i
+  long long count;    // samples written
+  long long visited;  // number of loop iterations the reference would have executed (= draws consumed)
+};
+struct PSrc;
+// parallel exact pivotal sampling (fricc_pivotal.cu); false = could not finish (caller falls back to the chain kernel)
+bool pivotal_parallel(const PSrc& ps, int64_t n, int64_t nsamp, const int32_t* draws_dev, int64_t ndraws,
+                      int64_t* S_dev, PivotalState* st_dev, int* err_dev, int* restarts_out);
+// "pivotal_parallel" option: -1 auto (parallel for n >= 65536), 0 one-thread chain, 1 always parallel
+void set_pivotal_parallel(int mode);
+int pivotal_restarts_last();
+
 // the two compressions behind SparseTensor4d's constructor
 void compress_largest(const double* x_dev, int64_t n, int64_t m, Compressed& out);
 void compress_fri(const double* x_dev, int64_t n, int64_t m, Sampling method, const DrawSource& draws, bool verbose,
@@ -53,6 +75,8 @@ void compress_fri(const double* x_dev, int64_t n, int64_t m, Sampling method, co
 // glibc-compatible rand() stream (host side)
 void rand_seed(uint32_t seed);
 void rand_fill(int32_t* out, int64_t n);  // advances
+void rand_fill_device(int32_t* out_dev, int64_t n);  // next n draws into device memory; does NOT advance the stream
+void rand_skip(int64_t count);                        // advance the stream by count draws (jump-ahead)
 int64_t rand_consumed();
 struct RandSnapshot {
   uint32_t ring[31];

@@ -37,6 +37,36 @@ key_hist_kernel(const double* __restrict__ x, int64_t n, int shift, unsigned mas
     if (sh[i]) atomicAdd(&hist[i], (unsigned long long)sh[i]);
 }
 
+// counts AND magnitude sums per 12-bit digit (same filter as key_hist_kernel); used only to ESTIMATE where the greedy
+// D test stops (the estimate sizes the candidate list, it never decides anything -- see estimate_d_candidates).
+__global__ void __launch_bounds__(SEL_THREADS)
+key_hist_sum_kernel(const double* __restrict__ x, int64_t n, int shift, uint64_t prefix, int prefix_shift, int use_prefix,
+                    unsigned long long* __restrict__ hist, double* __restrict__ sums) {
+  __shared__ unsigned sh[SEL_BINS];
+  __shared__ double ss[SEL_BINS];
+  for (int i = threadIdx.x; i < SEL_BINS; i += SEL_THREADS) {
+    sh[i] = 0;
+    ss[i] = 0.0;
+  }
+  __syncthreads();
+  const int64_t stride = (int64_t)gridDim.x * SEL_THREADS;
+  for (int64_t i = (int64_t)blockIdx.x * SEL_THREADS + threadIdx.x; i < n; i += stride) {
+    uint64_t key = abs_key(x[i]);
+    bool ok = !use_prefix || ((key >> prefix_shift) == prefix);
+    if (ok) {
+      unsigned b = (unsigned)(key >> shift) & (SEL_BINS - 1);
+      atomicAdd(&sh[b], 1u);
+      atomicAdd(&ss[b], key_to_double(key));
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < SEL_BINS; i += SEL_THREADS)
+    if (sh[i]) {
+      atomicAdd(&hist[i], (unsigned long long)sh[i]);
+      atomicAdd(&sums[i], ss[i]);
+    }
+}
+
 // Appends (key, index) of every element with (key >> cshift) > cut to `above`, and of every element with
 // (key >> cshift) == cut to `amb` (skipped when amb_k == nullptr).  One CTA handles tiles of SEL_THREADS*CP_ITEMS
 // elements: classify in registers, CTA-wide exclusive scan of the two class counts, ONE atomicAdd pair per tile
@@ -262,6 +292,66 @@ void select_top_m(const double* x, int64_t n, int64_t m, TopM& out) {
     FRICC_CUDA(cudaMemcpyAsync(out.keys.p, k1.p, (size_t)m * 8, cudaMemcpyDeviceToDevice, stream()));
     FRICC_CUDA(cudaMemcpyAsync(out.idx.p, i1.p, (size_t)m * 8, cudaMemcpyDeviceToDevice, stream()));
   }
+}
+
+// Upper estimate of |D|+1 for get_d_largest (fri_utils.cpp:400-437): the greedy test at rank d is
+//   (n_sample - d) * x_d >= r_d - x_d   with  r_d = norm - sum_{i<d} x_i .
+// It is evaluated at the lower edges of the magnitude bins (counts and sums above the edge from one or two histogram
+// passes); the first edge where it fails bounds the prefix from above when the test is monotone, and compress_fri grows
+// the list if the bound turns out too small, so this only ever sizes buffers -- the exact greedy test decides D.
+int64_t estimate_d_candidates(const double* x, int64_t n, int64_t n_sample, double norm) {
+  if (n_sample <= 0 || n <= 0) return 0;
+  DevBuf<unsigned long long> hist(SEL_BINS);
+  DevBuf<double> sums(SEL_BINS);
+  std::vector<unsigned long long> h(SEL_BINS);
+  std::vector<double> hs(SEL_BINS);
+  uint64_t prefix = 0;
+  int prefix_bits = 0;
+  int64_t c_above = 0;     // elements strictly above the bin under refinement
+  double s_above = 0.0;
+  const int64_t budget = std::max<int64_t>(1 << 16, n_sample / 64);
+  int64_t est = n_sample;
+  for (int pass = 0; pass < 3; pass++) {
+    const int shift = kShifts[pass];
+    hist.zero();
+    sums.zero();
+    FRICC_LAUNCH(key_hist_sum_kernel, hist_grid(n), SEL_THREADS, 0, x, n, shift, prefix, shift + SEL_BITS, prefix_bits > 0 ? 1 : 0,
+                 hist.p, sums.p);
+    hist.to_host(h.data(), SEL_BINS);
+    sums.to_host(hs.data(), SEL_BINS);
+    int64_t c = c_above;
+    double sm = s_above;
+    int b = SEL_BINS - 1;
+    int64_t c_before = c;
+    double s_before = sm;
+    bool failed = false;
+    for (; b >= 0; b--) {
+      c_before = c;
+      s_before = sm;
+      c += (int64_t)h[b];
+      sm += hs[b];
+      if (h[b] == 0) continue;
+      // lower edge of bin b: every element of the bin is >= t
+      const double t = key_to_double(((prefix << SEL_BITS) | (uint64_t)b) << shift);
+      const bool holds = c < n_sample && (double)(n_sample - c) * t >= (norm - sm) - t && (norm - sm) > 1e-14;
+      if (!holds) {
+        failed = true;
+        break;
+      }
+    }
+    if (!failed) {  // the test holds down to the smallest magnitude seen: D may be everything
+      est = n_sample;
+      break;
+    }
+    est = std::min<int64_t>(n_sample, c + 1);
+    if ((int64_t)h[b] <= budget || shift == 0) break;
+    // the failing bin is fat: look inside it
+    prefix = (prefix << SEL_BITS) | (uint64_t)b;
+    prefix_bits += SEL_BITS;
+    c_above = c_before;
+    s_above = s_before;
+  }
+  return std::max<int64_t>(1, std::min<int64_t>(est, n_sample));
 }
 
 // LSD digit order for (key descending, index ascending): index digits first (least significant), then key digits

@@ -20,4 +20,7 @@ void key_histogram(const double* x_dev, int64_t n, int shift, unsigned mask, uin
 
 std::vector<Digit> candidate_digits(int64_t n);
 
+// upper estimate of how many of the largest magnitudes the greedy D test can accept (sizes compress_fri's candidate list)
+int64_t estimate_d_candidates(const double* x_dev, int64_t n, int64_t n_sample, double norm);
+
 }  // namespace fricc

@@ -123,6 +123,13 @@ def set_option(key, value):
     check(_lib.lib().fricc_set_option(str(key).encode(), int(value)))
 
 
+def get_stat(key):
+    """Counters of the last library call (include/fricc_b200.h: fricc_get_stat), e.g. ``get_stat("pivotal_restarts")``."""
+    v = c_int64(0)
+    check(_lib.lib().fricc_get_stat(str(key).encode(), byref(v)))
+    return v.value
+
+
 def rand_consumed():
     return int(_lib.lib().fricc_rand_consumed())
 

@@ -49,10 +49,18 @@ int fricc_set_device(int device);
 int fricc_set_stream(void* cuda_stream);      /* cudaStream_t of the caller (e.g. torch's current stream); NULL = default */
 int fricc_stream_synchronize(void);
 /* tuning / A-B switches.  "d_candidates": first size of the candidate list ordered when looking for D (default 65536;
- * it grows x16 until the greedy test stops inside the list -- any value gives identical results).
+ * it grows x16 until the greedy test stops inside the list -- any value gives identical results); "d_estimate": 1
+ * (default) sizes that list from a count+sum histogram estimate of where the greedy test stops, 0 = geometric growth only.
  * "escan": 1 (default) = exact running sums by the parallel binade-segmented scan,
  * 0 = by the one-thread chain kernels (bit-identical results, kept as the in-library cross-check).               */
 int fricc_set_option(const char* key, int value);
+/* "d_parallel": -1 (default) = the parallel D-selection for candidate lists >= 32768 and the one-warp walk below,
+ * 0 / 1 = always serial / always parallel (bit-identical).
+ * "pivotal_parallel": -1 (default) = the parallel exact pivotal sampler for N >= 65536 and the one-thread chain kernel
+ * below, 0 = always the chain kernel, 1 = always the parallel sampler (bit-identical results).
+ * fricc_get_stat: counters of the last call -- "pivotal_restarts" (how many times the parallel sampler had to restart
+ * behind a run whose predicted start did not match the chain; 0 in the common case).                              */
+int fricc_get_stat(const char* key, int64_t* value);
 /* number of kernels this library has launched since load (bench.py's "gpu_launches" evidence) */
 int64_t fricc_kernel_launches(void);
 
@@ -63,6 +71,10 @@ int64_t fricc_kernel_launches(void);
 int fricc_srand(uint32_t seed);                                  /* == libc srand(seed)                           */
 int fricc_rand_fill(int32_t* out_host, int64_t n);               /* next n values of rand(); advances the stream  */
 int64_t fricc_rand_consumed(void);                               /* draws consumed since the last fricc_srand     */
+int fricc_rand_skip(int64_t n);                                  /* advance the stream by n draws (O(log n) jump)  */
+/* the next n values of rand() generated ON THE DEVICE into out_dev (per-thread jump-ahead over the linear recurrence);
+ * does not advance the stream -- pair it with fricc_rand_skip(consumed)                                          */
+int fricc_rand_fill_device(int32_t* out_dev, int64_t n);
 
 /* ---- SparseTensor4d (reference: include/sparse_tensor.hpp:13-100, src/py_rccsd.cpp:32-47) -------------------- */
 /* ctor #1 (sparse_tensor.hpp:27-31): nnz zero entries */

@@ -68,3 +68,23 @@ def test_glibc_rand_stream_matches_libc():
         _lib.check(L.fricc_rand_fill(got[1200:].ctypes.data_as(ctypes.POINTER(ctypes.c_int32)), 800))
         assert (got == want).all()
         assert L.fricc_rand_consumed() == 2000
+
+
+def test_rand_skip_is_a_jump_ahead_of_the_same_stream():
+    """fricc_rand_skip(n) (O(log n) polynomial jump over the linear recurrence) == drawing n values and dropping them."""
+    import numpy as np
+
+    libc = ctypes.CDLL(None)
+    L = _lib.lib()
+    p32 = ctypes.POINTER(ctypes.c_int32)
+    for seed, skip in ((1, 1), (3, 30), (3, 31), (9, 992), (20, 12345), (5, 1_000_003)):
+        libc.srand(seed)
+        for _ in range(skip):
+            libc.rand()
+        want = np.array([libc.rand() for _ in range(200)], dtype=np.int32)
+        _lib.check(L.fricc_srand(seed))
+        _lib.check(L.fricc_rand_skip(skip))
+        got = np.empty(200, dtype=np.int32)
+        _lib.check(L.fricc_rand_fill(got.ctypes.data_as(p32), 200))
+        assert (got == want).all(), (seed, skip)
+        assert L.fricc_rand_consumed() == skip + 200

@@ -153,3 +153,149 @@ def test_exact_norm_adversarial(rccsd):
     ]
     for x in cases:
         assert rccsd.one_norm(x) == float(np.cumsum(np.abs(x))[-1])
+
+
+@pytest.mark.parametrize("kind,n,m", [("heavier", 400000, 300000), ("uniform", 200000, 150000), ("heavy", 300000, 1000)])
+def test_adaptive_d_candidate_list(rccsd, port, kind, n, m):
+    """compress_fri orders only a candidate prefix when it looks for D (sized by a histogram estimate, grown x16 when the
+    greedy test does not stop inside it).  Every sizing policy must give the oracle's result, including large |D|."""
+    rng = np.random.default_rng(n + m)
+    x = synth_t2(rng, n, kind)
+    draws = np.array([987654321], dtype=np.int32)
+    want = port.fri_compression(x, m, "systematic", draws)
+    try:
+        for cand, est in ((4, 0), (4, 1), (1 << 16, 1), (1 << 30, 0)):
+            rccsd.set_option("d_candidates", cand)
+            rccsd.set_option("d_estimate", est)
+            idx, vals = rccsd.fri_compression(x, m, "systematic", draws=draws)
+            assert (idx == want["idx"]).all(), (cand, est)
+            assert np.array_equal(vals, want["vals"]), (cand, est)
+    finally:
+        rccsd.set_option("d_candidates", 1 << 16)
+        rccsd.set_option("d_estimate", 1)
+
+
+@pytest.mark.parametrize("kind", ["heavy", "heavier", "uniform", "diff"])
+@pytest.mark.parametrize("n,m", [(1, 1), (2, 1), (33, 33), (5000, 1), (20000, 3000), (300000, 40000), (2_000_000, 150_000)])
+def test_parallel_pivotal_equals_oracle(rccsd, port, kind, n, m):
+    """The parallel exact pivotal sampler (fricc_pivotal.cu) forced on at every size: bit-identical sample lists, values
+    and consumed-draw counts to the sequential walk of the oracle (and to the one-thread chain kernel)."""
+    rng = np.random.default_rng(n * 13 + m)
+    x = synth_t2(rng, n, kind)
+    draws = rng.integers(0, 2**31 - 1, size=n + 4).astype(np.int32)
+    try:
+        want = port.fri_compression(x, m, "pivotal", draws)
+    except Exception:
+        want = None
+    try:
+        rccsd.set_option("pivotal_parallel", 1)
+        if want is None:
+            with pytest.raises(Exception):
+                rccsd.fri_compression(x, m, "pivotal", draws=draws)
+            return
+        idx, vals = rccsd.fri_compression(x, m, "pivotal", draws=draws)
+        restarts = rccsd.get_stat("pivotal_restarts")
+    finally:
+        rccsd.set_option("pivotal_parallel", -1)
+    assert (idx == want["idx"]).all()
+    assert np.array_equal(vals, want["vals"])
+    assert restarts <= 2, restarts   # a restart costs time, never correctness; more than a couple means the model is off
+
+
+def test_parallel_pivotal_probability_vectors(rccsd, port):
+    """Stage-wise sampler on explicit probability vectors with adversarial structure: exact ties at the wrap step (all
+    probabilities multiples of 2^-k), long zero stretches, probabilities equal to 1, tiny probabilities."""
+    rng = np.random.default_rng(5)
+    cases = []
+    p = rng.integers(0, 2**20, 200000) / 2.0**22            # dyadic: many exact ties
+    cases.append(p)
+    p = rng.random(300000) * (rng.random(300000) < 0.05)    # 95 % zeros
+    cases.append(p)
+    p = rng.random(100000) ** 8
+    p[::1000] = 1.0                                         # probabilities of exactly one
+    cases.append(p)
+    p = np.concatenate([np.full(70000, 2.0**-30), rng.random(70000), np.full(70000, 1e-300)])
+    cases.append(p)
+    p = rng.integers(1, 4, 150000) * 2.0**-53 + 0.25        # half-ulp offsets around a coarse value
+    cases.append(p)
+    try:
+        rccsd.set_option("pivotal_parallel", 1)
+        for k, p in enumerate(cases):
+            ns = int(np.floor(p.sum()))
+            p = p * (ns / p.sum())                          # sum ~ ns so that the walk ends with a ~ 1 or fills S
+            p = np.minimum(p, 1.0)
+            draws = rng.integers(0, 2**31 - 1, size=p.size).astype(np.int32)
+            try:
+                want, _ = port.sample_pivotal(ns, p, draws)
+            except Exception:
+                with pytest.raises(Exception):
+                    rccsd.sample_pivotal(ns, p, draws=draws)
+                continue
+            got = rccsd.sample_pivotal(ns, p, draws=draws)
+            assert (np.array(got, dtype=np.int64) == np.array(want, dtype=np.int64)).all(), k
+    finally:
+        rccsd.set_option("pivotal_parallel", -1)
+
+
+def test_parallel_d_selection(rccsd, port):
+    """get_d_largest by the parallel rounding-map scan (fricc_escan.cu: d_greedy_parallel) vs the one-warp walk vs the
+    oracle: identical D and bit-identical remaining norm, including lists where r drops through several binades, exact
+    ties (dyadic magnitudes), zeros, and D == everything."""
+    rng = np.random.default_rng(17)
+    cases = []
+    x = synth_t2(rng, 400000, "heavier"); cases.append((x, 300000))
+    x = synth_t2(rng, 200000, "uniform"); cases.append((x, 150000))
+    x = np.concatenate([rng.random(50) * 1e6, rng.random(300000) * 1e-3]); cases.append((x, 200000))     # r falls ~30 binades
+    x = rng.integers(1, 2**12, 300000) * 2.0**-20; cases.append((x, 250000))                             # dyadic: ties
+    x = np.concatenate([2.0 ** rng.integers(-40, 10, 100000).astype(np.float64), np.zeros(1000)]); cases.append((x, 100500))
+    x = np.full(70000, 0.125); cases.append((x, 70000))                                                  # D == everything
+    x = np.concatenate([[1.0], rng.integers(0, 8, 100000) * 2.0**-53]); cases.append((x, 60000))
+    for k, (x, m) in enumerate(cases):
+        x = x * np.where(rng.random(x.size) < 0.5, -1.0, 1.0)
+        wantD, wantr = port.get_d_largest(x, m)
+        try:
+            res = {}
+            for mode in (0, 1):
+                rccsd.set_option("d_parallel", mode)
+                res[mode] = rccsd.get_d_largest(x, m)
+        finally:
+            rccsd.set_option("d_parallel", -1)
+        for mode in (0, 1):
+            D, r = res[mode]
+            assert len(D) == len(wantD), (k, mode, len(D), len(wantD))
+            assert r == wantr, (k, mode)
+            assert np.array_equal(np.abs(x[D]), np.abs(x[wantD])), (k, mode)
+
+
+def test_device_rand_stream_equals_host_stream(rccsd):
+    """The device generator (per-thread jump-ahead, fricc_rand.cu) produces exactly the host/libc stream, and a pivotal
+    compression that draws from the library stream consumes it exactly like one fed the same draws explicitly."""
+    import ctypes
+
+    import torch
+    from fricc_b200 import _lib
+
+    L = _lib.lib()
+    for seed, n in ((1, 5), (4, 992), (4, 993), (11, 3_000_001)):
+        _lib.check(L.fricc_srand(seed))
+        d = torch.empty(n, dtype=torch.int32, device="cuda")
+        _lib.check(L.fricc_rand_fill_device(ctypes.c_void_p(d.data_ptr()), n))
+        assert L.fricc_rand_consumed() == 0
+        want = np.empty(n, dtype=np.int32)
+        _lib.check(L.fricc_rand_fill(want.ctypes.data_as(ctypes.POINTER(ctypes.c_int32)), n))
+        assert (d.cpu().numpy() == want).all(), (seed, n)
+    rng = np.random.default_rng(2)
+    x = synth_t2(rng, 500000, "heavier")
+    m = 30000
+    _lib.check(L.fricc_srand(77))
+    draws = np.empty(x.size, dtype=np.int32)
+    _lib.check(L.fricc_rand_fill(draws.ctypes.data_as(ctypes.POINTER(ctypes.c_int32)), x.size))
+    idx0, val0 = rccsd.fri_compression(x, m, "pivotal", draws=draws)
+    _lib.check(L.fricc_srand(77))
+    idx1, val1 = rccsd.fri_compression(x, m, "pivotal")
+    used = L.fricc_rand_consumed()
+    assert (idx0 == idx1).all() and np.array_equal(val0, val1)
+    # the stream stands where the reference's rand() would: the next value is draws[used]
+    nxt = np.empty(1, dtype=np.int32)
+    _lib.check(L.fricc_rand_fill(nxt.ctypes.data_as(ctypes.POINTER(ctypes.c_int32)), 1))
+    assert 0 < used <= x.size - 1 and nxt[0] == draws[used]
