@@ -46,14 +46,15 @@ def parse_args():
     p.add_argument("--steps", type=int, default=3)
     p.add_argument("--warmup", type=int, default=3)
     p.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    p.add_argument("--o", type=int, default=40)
-    p.add_argument("--v", type=int, default=400)
-    p.add_argument("--m", type=float, default=1e7)
+    p.add_argument("--o", "--nocc", dest="o", type=int, default=40)
+    p.add_argument("--v", "--nvir", dest="v", type=int, default=400)
+    p.add_argument("--m", "--nkeep", dest="m", type=float, default=1e7)
     p.add_argument("--sampling", default="systematic", choices=["systematic", "pivotal"])
     p.add_argument("--max-panel-gb", type=float, default=26.0, help="largest resident ladder W slice per sub-shard")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--only-ladder", action="store_true", help="debug: time only the ladder launches")
+    p.add_argument("--no-overlap", action="store_true", help="N>1: one blocking exchange per term (A/B of the pipelined step)")
     return p.parse_args()
 
 
@@ -233,8 +234,8 @@ class Iteration:
         self.draw_pos += 1
         return self.fd.compress(t2, self.m, "fri", self.args.sampling, draws=d if self.args.sampling == "systematic" else None)
 
-    def ladder(self, T, timer=None):
-        """Particle-particle ladder on this rank's column slice; returns the list of timed segments (events)."""
+    def ladder_local(self, T, timer=None):
+        """Particle-particle ladder on this rank's column slice (into t2new directly when there is one rank)."""
         torch = self.torch
         lad = self.terms["2323"]
         L = lad.L
@@ -259,8 +260,11 @@ class Iteration:
                                                      ctypes_ptr(lad.out_panel, c), lad.lc, b"2323"))
             e1.record()
             self.ladder_events.append((e0, e1, w))
-        if not single:
-            lad.exchange_and_accumulate(T, self.t2new)
+
+    def ladder(self, T, timer=None):
+        self.ladder_local(T, timer)
+        if self.comm.world > 1:
+            self.terms["2323"].exchange_and_accumulate(T, self.t2new)
 
     def mark(self, name):
         e = self.torch.cuda.Event(enable_timing=True)
@@ -272,6 +276,8 @@ class Iteration:
         T = self.compress(t2)
         T_alt = self.compress(t2)
         self.mark("compress_x2")
+        if self.comm.world > 1 and not self.args.only_ladder and not self.args.no_overlap:
+            return self.step_pipelined(T, T_alt, timer)
         tm = self.terms
         if not self.args.only_ladder:
             self.Wklij.zero_(); self.Wakic.zero_(); self.Wakci.zero_()
@@ -304,6 +310,45 @@ class Iteration:
             self.mark("1303")
             tm["1203"](T, self.tmp[2])
             self.mark("1203")
+        return T
+
+    def step_pipelined(self, T, T_alt, timer=None):
+        """N > 1: the same 11 contractions, ordered so that every all-gather (NCCL, its own stream) runs under the next
+        term's SpMM, and terms that feed the same output through the same (R, L) map share one panel and one exchange
+        (0112+0313+0113 -> Wvoov, 1302+1202 -> tmp).  Data dependences: 0101 reads Woooo (1323), 1302/1303 read Wvoov,
+        1202/1203 read Wvovo (0312)."""
+        tm = self.terms
+        self.Wklij.zero_(); self.Wakic.zero_(); self.Wakci.zero_()
+        self.t2new.zero_()
+        for t in self.tmp:
+            t.zero_()
+        self.mark("zero_outputs")
+        tm["1323"].local(T_alt); tm["1323"].start_exchange()
+        tm["0112"].local(T_alt)
+        tm["0313"].local(T_alt, into=tm["0112"])
+        tm["0113"].local(T_alt, into=tm["0112"])
+        tm["0112"].start_exchange()
+        tm["0312"].local(T_alt); tm["0312"].start_exchange()
+        self.mark("ovov_terms_local")
+        self.ladder_local(T, timer)                       # the long one: hides the three gathers above
+        tm["2323"].start_exchange()
+        self.mark("2323_local" if self.resident else "2323_local_incl_regen")
+        tm["1323"].finish(T_alt, self.Wklij)
+        tm["0112"].finish(T_alt, self.Wakic)
+        tm["0312"].finish(T_alt, self.Wakci)
+        tm["0101"].permute_from(self.Wklij); tm["0101"].local(T); tm["0101"].start_exchange()
+        tm["1302"].permute_from(self.Wakic); tm["1302"].local(T)
+        tm["1202"].permute_from(self.Wakci); tm["1202"].local(T, into=tm["1302"])
+        tm["1302"].start_exchange()
+        tm["2323"].finish(T, self.t2new)
+        self.mark("intermediates_0101_1302_1202")
+        tm["1303"].set_panel(tm["1302"].panel); tm["1303"].local(T); tm["1303"].start_exchange()
+        tm["0101"].finish(T, self.t2new)
+        tm["1203"].set_panel(tm["1202"].panel); tm["1203"].local(T); tm["1203"].start_exchange()
+        tm["1302"].finish(T, self.tmp[0])
+        tm["1303"].finish(T, self.tmp[1])
+        tm["1203"].finish(T, self.tmp[2])
+        self.mark("1303_1203_and_drain")
         return T
 
     def stage_breakdown(self, steps):
@@ -465,6 +510,11 @@ def run_b200_arm(args):
     launches = L.fricc_kernel_launches() - launches0
     clocks = stop_clock_sampler(proc, cpath) if rank == 0 else None
     stage_ms = it.stage_breakdown(args.steps)
+    # checksums of the step's outputs (after the last timed step): identical between the pipelined and the blocking
+    # schedule, between ranks, and between GPU counts up to summation order
+    checks = {k: float(v.double().sum().item()) for k, v in
+              (("t2new", it.t2new), ("tmp0", it.tmp[0]), ("tmp1", it.tmp[1]), ("tmp2", it.tmp[2]),
+               ("Wvoov", it.Wakic), ("Wvovo", it.Wakci), ("Woooo", it.Wklij))}
     lad_ms = [a.elapsed_time(b) for a, b, _ in it.ladder_events]
     lad_cols = [w for _, _, w in it.ladder_events]
     it.ladder_events.clear()
@@ -473,17 +523,27 @@ def run_b200_arm(args):
     # ---- e2e: T2 from pinned host memory, residual back to pinned host memory, inside the timed region
     e2e = None
     if not args.no_e2e:
-        h_t2 = torch.empty(it.t2.shape, dtype=torch.float64, pin_memory=True)
-        h_t2.copy_(it.t2)
-        h_out = torch.empty(it.t2new.shape, dtype=torch.float64, pin_memory=True)
-        d_t2 = torch.empty_like(it.t2)
+        # every rank moves only ITS 1/world slice over PCIe; the full T2 is assembled over NVLink (NCCL all-gather) and
+        # each rank returns its slice of the residual -- h2d/d2h bytes below are the totals over all ranks
+        nel = it.t2.numel()
+        per = -(-nel // world)
+        lo, hi = min(rank * per, nel), min((rank + 1) * per, nel)
+        h_t2 = torch.empty(per, dtype=torch.float64, pin_memory=True)
+        h_t2[: hi - lo].copy_(it.t2.view(-1)[lo:hi])
+        h_out = torch.empty(per, dtype=torch.float64, pin_memory=True)
+        d_slice = torch.zeros(per, dtype=torch.float64, device=device)
+        d_full = torch.empty(per * world, dtype=torch.float64, device=device)
         sync_all()
         t2timer = SegmentTimer(torch)
         t2timer.resume()
         for _ in range(args.steps):
-            d_t2.copy_(h_t2, non_blocking=True)
-            it.step(d_t2, t2timer)
-            h_out.copy_(it.t2new, non_blocking=True)
+            d_slice.copy_(h_t2, non_blocking=True)
+            if world > 1:
+                dist.all_gather_into_tensor(d_full, d_slice)
+            else:
+                d_full = d_slice
+            it.step(d_full[:nel].view(it.t2.shape), t2timer)
+            h_out[: hi - lo].copy_(it.t2new.view(-1)[lo:hi], non_blocking=True)
         t2timer.pause()
         sync_all()
         e2e_ms = t2timer.total_ms()
@@ -522,7 +582,9 @@ def run_b200_arm(args):
                          "launches_timed": len(lad_ms), "avg_launch_ms": (sum(lad_ms) / len(lad_ms)) if lad_ms else None,
                          "algorithmic_bytes_per_launch": (sum(alg) / len(alg)) if alg else None},
             "clocks": clocks, "gpu_launches": int(launches),
-            "ladder_ms_per_step": sum(lad_ms) / args.steps, "stage_ms_per_step": stage_ms,
+            "ladder_ms_per_step": sum(lad_ms) / args.steps, "stage_ms_per_step": stage_ms, "output_checksums": checks,
+            "schedule": ("blocking exchange per term" if (world == 1 or args.no_overlap) else
+                         "pipelined: NCCL all-gathers overlap the next term's SpMM; 7 exchanges for 11 terms"),
             "timed_segments": "whole steps" if it.resident else
                               f"sum of segments; ladder W regenerated in HBM between {len(it.sub)} column sub-shards",
         }

@@ -50,14 +50,14 @@ class Comm:
     def __init__(self, rank=0, world=1, group=None):
         self.rank, self.world, self.group = rank, world, group
 
-    def all_gather(self, out, inp):
+    def all_gather(self, out, inp, async_op=False):
         if self.world == 1:
             if out.data_ptr() != inp.data_ptr():
                 out.view(-1)[: inp.numel()].copy_(inp.view(-1))
-            return
+            return None
         import torch.distributed as dist
 
-        dist.all_gather_into_tensor(out, inp, group=self.group)
+        return dist.all_gather_into_tensor(out, inp, group=self.group, async_op=async_op)
 
     def barrier(self):
         if self.world > 1:
@@ -102,28 +102,49 @@ class ShardedTerm:
                                          self.term.encode(), self.l0, self.lcnt, _ptr(self.panel)))
 
     # -- compute ----------------------------------------------------------------------------------------------
-    def local(self, T):
-        """This rank's column slice of the output: out_panel[R][c] = scale * sum_K T[R,K] * Wp[K][c]."""
-        if self.out_panel is None:
-            self.out_panel = torch.empty(self.nR * self.lc, dtype=torch.float64, device=self.device)
-        self.out_panel.zero_()
+    def local(self, T, into=None):
+        """This rank's column slice of the output: out_panel[R][c] (+)= scale * sum_K T[R,K] * Wp[K][c].
+        `into`: another ShardedTerm with the same (R, L) output mapping whose panel this term is ADDED to (terms that
+        feed the same output share one exchange, e.g. 0112/0313/0113 -> Wvoov)."""
+        if into is not None:
+            assert (into.nR, into.lc, into.l0) == (self.nR, self.lc, self.l0)
+            target = into.out_panel
+        else:
+            if self.out_panel is None:
+                self.out_panel = torch.empty(self.nR * self.lc, dtype=torch.float64, device=self.device)
+            self.out_panel.zero_()
+            target = self.out_panel
         if self.lcnt > 0:
             check(self.L.fricc_contract_panel(_ptr(self.panel), self.lcnt, self.l0, self.lcnt, T._h,
-                                              _ptr(self.out_panel), self.lc, self.term.encode()))
-        return self.out_panel
+                                              _ptr(target), self.lc, self.term.encode()))
+        return target
 
-    def exchange_and_accumulate(self, T, out):
-        """all-gather the column slices and add them into the full 4-D output on every rank."""
+    def start_exchange(self):
+        """Launch the all-gather of the column slices without waiting for it: NCCL runs on its own stream behind the work
+        already queued on the current one, so the next term's SpMM overlaps the transfer."""
+        self._work = None
+        if self.comm.world > 1:
+            if self.gathered is None:
+                self.gathered = torch.empty(self.comm.world * self.nR * self.lc, dtype=torch.float64, device=self.device)
+            self._work = self.comm.all_gather(self.gathered, self.out_panel, async_op=True)
+
+    def finish(self, T, out):
+        """Wait for the gather started by start_exchange and add the panels into the full 4-D output."""
         w = self.comm.world
         if w == 1:
             g = self.out_panel
         else:
-            if self.gathered is None:
-                self.gathered = torch.empty(w * self.nR * self.lc, dtype=torch.float64, device=self.device)
-            self.comm.all_gather(self.gathered, self.out_panel)
+            if self._work is not None:
+                self._work.wait()
+                self._work = None
             g = self.gathered
         check(self.L.fricc_accumulate_panels(_ptr(g), w, self.lc, T._h, self.term.encode(), _ptr(out),
                                              i64x4(out.shape), i64x4(out.stride())))
+
+    def exchange_and_accumulate(self, T, out):
+        """all-gather the column slices and add them into the full 4-D output on every rank."""
+        self.start_exchange()
+        self.finish(T, out)
 
     def local_into(self, T, out, panel=None, l0=None, lcnt=None):
         """Single-rank form: accumulate this panel's columns straight into the 4-D output (no intermediate panel)."""
