@@ -72,6 +72,15 @@ SIGNATURES = {
     "fricc_contract_panel_into": (c_int, [c_void_p, c_int64, c_int64, c_int64, c_void_p, c_void_p, _i64p, _i64p,
                                           c_char_p]),
     "fricc_accumulate_panels": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_char_p, c_void_p, _i64p, _i64p]),
+    "fricc_wslices_create": (c_int, [c_void_p, c_int64, c_int64, c_int64, c_int, POINTER(c_void_p)]),
+    "fricc_wslices_update": (c_int, [c_void_p, c_void_p, c_int64]),
+    "fricc_wslices_destroy": (c_int, [c_void_p]),
+    "fricc_wslices_bytes": (c_int, [c_void_p, _i64p]),
+    "fricc_wslices_reconstruct": (c_int, [c_void_p, c_void_p]),
+    "fricc_st_sign_fraction": (c_int, [c_void_p, c_char_p, _f64p]),
+    "fricc_contract_panel_tc": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_int64, c_char_p]),
+    "fricc_contract_panel_into_tc": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p, _i64p, _i64p,
+                                             c_char_p]),
     "fricc_permute_w": (c_int, [c_void_p, c_int, _i64p, _i64p, c_char_p, c_int64, c_int64, c_void_p]),
     "fricc_one_norm": (c_int, [c_void_p, c_int, c_int64, _f64p]),
     "fricc_argsort": (c_int, [c_void_p, c_int, c_int64, c_int64, c_void_p]),

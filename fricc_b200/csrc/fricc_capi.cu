@@ -3,7 +3,7 @@
 #include <numeric>
 
 #include "fricc_common.cuh"
-#include "fricc_contract.cuh"
+#include "fricc_dense.cuh"
 #include "fricc_fri.cuh"
 #include "fricc_select.cuh"
 
@@ -426,6 +426,109 @@ int fricc_accumulate_panels(const double* panels_dev, int64_t n_panels, int64_t 
   const int64_t nR = d[ts->tR[0]] * d[ts->tR[1]];
   const int64_t nL = out_shape[ts->oL[0]] * out_shape[ts->oL[1]];
   accumulate_panels(panels_dev, n_panels, ld, nR, nL, out_dev, om);
+  FRICC_API_END
+}
+
+// ---- tensor-core form of the contractions (fricc_dense.cu) ---------------------------------------------------
+struct fricc_wslices {
+  fricc::WSlices ws;
+};
+
+int fricc_wslices_create(const double* Wp_dev, int64_t ldw, int64_t nK, int64_t l_count, int n_planes,
+                         fricc_wslices_t* out) {
+  FRICC_API_BEGIN
+  if (!Wp_dev || !out) fail(FRICC_EINVAL, "null argument");
+
+  fricc_wslices* h = new fricc_wslices();
+  try {
+    wslices_build(h->ws, Wp_dev, ldw, nK, l_count, n_planes);
+  } catch (...) {
+    delete h;
+    throw;
+  }
+  *out = h;
+  FRICC_API_END
+}
+
+int fricc_wslices_update(fricc_wslices_t h, const double* Wp_dev, int64_t ldw) {
+  FRICC_API_BEGIN
+  if (!h || !Wp_dev) fail(FRICC_EINVAL, "null argument");
+  wslices_build(h->ws, Wp_dev, ldw, h->ws.nK, h->ws.l_count, h->ws.S);
+  FRICC_API_END
+}
+
+int fricc_wslices_destroy(fricc_wslices_t h) {
+  FRICC_API_BEGIN
+  delete h;
+  FRICC_API_END
+}
+
+int fricc_wslices_bytes(fricc_wslices_t h, int64_t* bytes) {
+  FRICC_API_BEGIN
+  if (!h || !bytes) fail(FRICC_EINVAL, "null argument");
+  *bytes = (int64_t)h->ws.q.n;
+  FRICC_API_END
+}
+
+int fricc_wslices_reconstruct(fricc_wslices_t h, double* Wrec_dev) {
+  FRICC_API_BEGIN
+  if (!h || !Wrec_dev) fail(FRICC_EINVAL, "null argument");
+  wslices_reconstruct(h->ws, Wrec_dev);
+  FRICC_CUDA(cudaStreamSynchronize(stream()));
+  FRICC_API_END
+}
+
+int fricc_st_sign_fraction(fricc_st_t T, const char* term, double* fraction) {
+  FRICC_API_BEGIN
+  check_handle(T);
+  const TermSpec* ts = find_term(term);
+  if (!ts || !fraction) fail(FRICC_EINVAL, "bad arguments");
+  *fraction = T->nnz > 0 ? dense_form(T, get_layout(T, *ts)) : 0.0;
+  FRICC_API_END
+}
+
+static void contract_tc_common(fricc_wslices_t h, const double* Wp_dev, int64_t ldw, int64_t l_begin, fricc_st_t T,
+                               double* out, const OutMap& om, const TermSpec* ts) {
+  if (T->nnz == 0 || h->ws.l_count == 0) return;
+  Layout& lay = get_layout(T, *ts);
+  contract_dense(T, lay, h->ws, Wp_dev, ldw, l_begin, out, om, ts->scale);
+}
+
+int fricc_contract_panel_tc(fricc_wslices_t h, const double* Wp_dev, int64_t ldw, int64_t l_begin, fricc_st_t T,
+                            double* out_panel_dev, int64_t ld_out, const char* term) {
+  FRICC_API_BEGIN
+  check_handle(T);
+  const TermSpec* ts = find_term(term);
+  if (!ts) fail(FRICC_EINVAL, "CASE NOT IMPLEMENTED: unknown contraction term '%s'", term ? term : "(null)");
+  if (!h || !Wp_dev || !out_panel_dev || ldw < h->ws.l_count || ld_out < h->ws.l_count) fail(FRICC_EINVAL, "bad arguments");
+  OutMap om;
+  om.nR2 = 1; om.nL2 = 1; om.sR1 = ld_out; om.sR2 = 0; om.sL1 = 1; om.sL2 = 0;
+  contract_tc_common(h, Wp_dev, ldw, l_begin, T, out_panel_dev - l_begin, om, ts);
+  FRICC_API_END
+}
+
+int fricc_contract_panel_into_tc(fricc_wslices_t h, const double* Wp_dev, int64_t ldw, int64_t l_begin, fricc_st_t T,
+                                 double* out_dev, const int64_t out_shape[4], const int64_t out_strides[4],
+                                 const char* term) {
+  FRICC_API_BEGIN
+  check_handle(T);
+  const TermSpec* ts = find_term(term);
+  if (!ts) fail(FRICC_EINVAL, "CASE NOT IMPLEMENTED: unknown contraction term '%s'", term ? term : "(null)");
+  if (!h || !Wp_dev || !out_dev || !out_shape || !out_strides || l_begin < 0 || ldw < h->ws.l_count)
+    fail(FRICC_EINVAL, "bad arguments");
+  const int64_t* d = T->dims;
+  for (int q = 0; q < 2; q++)
+    if (out_shape[ts->oR[q]] != d[ts->tR[q]]) fail(FRICC_EINVAL, "term %s: out does not match T on the owner pair", ts->name);
+  const int64_t nL = out_shape[ts->oL[0]] * out_shape[ts->oL[1]];
+  if (l_begin + h->ws.l_count > nL) fail(FRICC_EINVAL, "column range out of bounds");
+  OutMap om;
+  om.nR2 = d[ts->tR[1]];
+  om.nL2 = out_shape[ts->oL[1]];
+  om.sR1 = out_strides[ts->oR[0]];
+  om.sR2 = out_strides[ts->oR[1]];
+  om.sL1 = out_strides[ts->oL[0]];
+  om.sL2 = out_strides[ts->oL[1]];
+  contract_tc_common(h, Wp_dev, ldw, l_begin, T, out_dev, om, ts);
   FRICC_API_END
 }
 

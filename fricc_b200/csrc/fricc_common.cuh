@@ -161,6 +161,17 @@ struct Layout {
   DevBuf<uint32_t> kidx;   // [nnz]
   DevBuf<double> vals;     // [nnz]
   int64_t max_row = 0;     // longest bucket (entries)
+  // ---- tensor-core form (fricc_dense.cu), built lazily: the entries whose value is +-c (every sampled entry of an FRI
+  // compression carries the same magnitude c = r/n') as a dense int8 sign matrix A[Mpad][Kpad]; everything else (the
+  // exactly preserved set D, duplicates) stays a CSR remainder that goes through the fp64 SpMM.
+  bool dense_built = false;
+  int64_t Mpad = 0, Kpad = 0;
+  DevBuf<int8_t> dense;        // [Mpad][Kpad], K-major
+  DevBuf<double> cmag;         // [1]  c
+  int64_t n_rest = 0;          // entries in the CSR remainder
+  DevBuf<int64_t> rest_rowptr; // [nR+1]
+  DevBuf<uint32_t> rest_kidx;
+  DevBuf<double> rest_vals;
 };
 
 }  // namespace fricc

@@ -6,7 +6,7 @@
 // (sort by (R,K), CSR row pointers), W is brought into a [K][L] row-major panel so that the row a nonzero needs is
 // contiguous, and one kernel does   out[R, L] += scale * sum_{e in bucket R} val_e * Wp[K_e, L]
 // with the accumulators in registers and exactly one read-modify-write of each output element (no atomics).
-#include "fricc_contract.cuh"
+#include "fricc_dense.cuh"
 
 #include <algorithm>
 
@@ -329,9 +329,9 @@ void set_spmm_option(const char* key, int value) {
   else if (strcmp(key, "spmm_threads") == 0) g_spmm_threads = value;
 }
 
-void spmm(const Layout& lay, const double* Wp, int64_t ldw, int64_t l_begin, int64_t l_count, double* out,
-          const OutMap& om, double scale) {
-  if (lay.nR == 0 || l_count == 0) return;
+void spmm_csr(const int64_t* rowptr, const uint32_t* kidx, const double* vals, int64_t nR, const double* Wp, int64_t ldw,
+              int64_t l_begin, int64_t l_count, double* out, const OutMap& om, double scale) {
+  if (nR == 0 || l_count == 0) return;
   bool vec2 = (ldw % 2 == 0) && (l_count % 2 == 0) && ((reinterpret_cast<uintptr_t>(Wp) & 15) == 0);
   if (vec2 && g_spmm_nv2 > 0) {
     int64_t pairs = l_count / 2;
@@ -341,15 +341,15 @@ void spmm(const Layout& lay, const double* Wp, int64_t ldw, int64_t l_begin, int
     while (nv2 > 1 && (int64_t)threads * (nv2 / 2) >= pairs) nv2 >>= 1;  // do not over-provision small free pairs
     int64_t tiles = ceil_div(pairs, (int64_t)threads * nv2);
     if (tiles > 65535) fail(FRICC_EINVAL, "spmm: free pair too large (%lld columns)", (long long)l_count);
-    dim3 grid((unsigned)lay.nR, (unsigned)tiles);
+    dim3 grid((unsigned)nR, (unsigned)tiles);
     if (nv2 >= 4)
-      FRICC_LAUNCH(spmm_rows_wide_kernel<4>, grid, threads, 0, lay.rowptr.p, lay.kidx.p, lay.vals.p, Wp, ldw, l_begin,
+      FRICC_LAUNCH(spmm_rows_wide_kernel<4>, grid, threads, 0, rowptr, kidx, vals, Wp, ldw, l_begin,
                    l_count, out, om, scale);
     else if (nv2 == 2)
-      FRICC_LAUNCH(spmm_rows_wide_kernel<2>, grid, threads, 0, lay.rowptr.p, lay.kidx.p, lay.vals.p, Wp, ldw, l_begin,
+      FRICC_LAUNCH(spmm_rows_wide_kernel<2>, grid, threads, 0, rowptr, kidx, vals, Wp, ldw, l_begin,
                    l_count, out, om, scale);
     else
-      FRICC_LAUNCH(spmm_rows_wide_kernel<1>, grid, threads, 0, lay.rowptr.p, lay.kidx.p, lay.vals.p, Wp, ldw, l_begin,
+      FRICC_LAUNCH(spmm_rows_wide_kernel<1>, grid, threads, 0, rowptr, kidx, vals, Wp, ldw, l_begin,
                    l_count, out, om, scale);
     return;
   }
@@ -359,13 +359,18 @@ void spmm(const Layout& lay, const double* Wp, int64_t ldw, int64_t l_begin, int
   while (threads < 256 && threads < g_spmm_threads * 4 && threads < threads_needed) threads <<= 1;
   int64_t tiles = ceil_div(threads_needed, threads);
   if (tiles > 65535) fail(FRICC_EINVAL, "spmm: free pair too large (%lld columns)", (long long)l_count);
-  dim3 grid((unsigned)lay.nR, (unsigned)tiles);
+  dim3 grid((unsigned)nR, (unsigned)tiles);
   if (vec2)
-    FRICC_LAUNCH(spmm_rows_kernel<2>, grid, threads, 0, lay.rowptr.p, lay.kidx.p, lay.vals.p, Wp, ldw, l_begin, l_count,
+    FRICC_LAUNCH(spmm_rows_kernel<2>, grid, threads, 0, rowptr, kidx, vals, Wp, ldw, l_begin, l_count,
                  out, om, scale);
   else
-    FRICC_LAUNCH(spmm_rows_kernel<1>, grid, threads, 0, lay.rowptr.p, lay.kidx.p, lay.vals.p, Wp, ldw, l_begin, l_count,
+    FRICC_LAUNCH(spmm_rows_kernel<1>, grid, threads, 0, rowptr, kidx, vals, Wp, ldw, l_begin, l_count,
                  out, om, scale);
+}
+
+void spmm(const Layout& lay, const double* Wp, int64_t ldw, int64_t l_begin, int64_t l_count, double* out,
+          const OutMap& om, double scale) {
+  spmm_csr(lay.rowptr.p, lay.kidx.p, lay.vals.p, lay.nR, Wp, ldw, l_begin, l_count, out, om, scale);
 }
 
 // gathered column-shard panels [g][R][ld] -> strided 4-D output (one read-modify-write per element, no atomics)

@@ -1,0 +1,578 @@
+// fricc_dense.cu -- the contractions on the 5th-generation tensor cores (tcgen05 / TMEM / TMA), without giving up fp64.
+//
+// Why a dense form exists at all.  The sampled part S of an FRI compression stores x_i / p_i with p_i = |x_i|/r * n'
+// (/root/reference/src/fri_utils.cpp:375,502-504): every sampled entry has the SAME magnitude c = r/n' (up to the last
+// bits of the two roundings), only the sign varies; the exactly preserved set D is a small prefix.  So
+//     out[R, l] += scale * ( c * sum_K sgn[R,K] * W[K,l]  +  sum_{rest} val * W[K,l] )
+// and the first sum is a {-1,0,+1} matrix times a dense fp64 matrix.  W is expanded ERROR-FREE into S int8 digit
+// planes per column (radix 128, digits in [-64,64], one power-of-two scale per column l -- the contracted index K runs
+// inside a column, so every partial product of a plane is an exact small integer):
+//     W[K,l] = 2^(e_l-6) * sum_s d_s[K,l] * 128^-s   + remainder,  |remainder| <= 2^(e_l - 7*S)
+// `tcgen05.mma.kind::i8` accumulates sgn x d_s exactly in int32 (|sum| <= 64 * nnz_row < 2^31), and the epilogue
+// recombines the S integer planes in fp64.  The only error is the dropped remainder: with S = 7 it is 2^-49 of the
+// column's largest element per term, i.e. below the rounding noise of the reference's own fp64 accumulation.
+//
+// When it wins: the dense product costs M*K*N*S int8 MACs regardless of m, the sparse product m*N fp64 FMAs through the
+// L1 data pipe (9.5 FMA/clk/SM measured, fricc_contract.cu).  At the headline density (3.9 %) the int8 path is several
+// times faster; below ~1.5 % the bucketed SpMM wins and is used (decision in dist.py / contract_dense's caller).
+//
+// Kernel: one CTA = 128 rows (R) x 64 columns (l) x all S planes; warp 0 = TMA producer (128-byte-swizzled K-major
+// tiles, mbarrier ring), warp 1 = one thread issuing tcgen05.mma (A = sign tile 128 x 32 B, B = up to 4 planes x 64
+// columns per instruction), accumulators = S*64 TMEM columns, warps 2-5 = epilogue (tcgen05.ld -> fp64 Horner over
+// the planes -> one read-modify-write of out through the 4-D stride map).
+#include "fricc_dense.cuh"
+
+#include <cuda.h>  // CUtensorMap + enums only; the encoder is fetched with cudaGetDriverEntryPoint (no -lcuda)
+
+#include <algorithm>
+
+namespace fricc {
+
+constexpr int TC_BM = 128;       // rows of the sign matrix per CTA (= TMEM lanes)
+constexpr int TC_BN = 64;        // output columns per CTA
+constexpr int TC_BK = 128;       // contracted indices per pipeline stage = one 128-byte swizzle atom of int8
+constexpr int TC_UMMA_K = 32;    // K of one tcgen05.mma.kind::i8
+constexpr int TC_THREADS = 192;  // warp 0 TMA, warp 1 MMA + TMEM allocation, warps 2..5 epilogue
+constexpr uint32_t TC_A_BYTES = TC_BM * TC_BK;      // 16 KB
+constexpr uint32_t TC_B_PLANE_BYTES = TC_BN * TC_BK;  // 8 KB per plane
+constexpr uint32_t TC_TMEM_COLS = 512;
+
+// ---------------------------------------------------------------------------------------------------------------
+// PTX wrappers
+// ---------------------------------------------------------------------------------------------------------------
+namespace ptx {
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+// bounded wait: a protocol error becomes a trap (reported as a launch failure) instead of a hung GPU
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  if (mbar_try_wait(bar, parity)) return;
+  const long long t0 = clock64();
+  while (!mbar_try_wait(bar, parity)) {
+    if (clock64() - t0 > 20000000000LL) __trap();  // ~10 s
+  }
+}
+__device__ __forceinline__ void prefetch_tensormap(const void* tm) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(tm)) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const void* tm, uint64_t* bar, int32_t c0, int32_t c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(tm)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_alloc(uint32_t* slot, uint32_t cols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(slot)), "r"(cols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t cols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+// D[tmem] (+)= A[smem] * B[smem], int8 x int8 -> int32, issued by ONE thread for the whole CTA
+__device__ __forceinline__ void mma_i8(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// arrive on an mbarrier when every tcgen05.mma issued so far by this thread has completed
+__device__ __forceinline__ void mma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+// 32 lanes x 8 consecutive 32-bit columns -> 8 registers per thread (thread i of the warp <-> lane base+i)
+__device__ __forceinline__ void tmem_ld_x8(uint32_t taddr, int32_t (&r)[8]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+               : "r"(taddr)
+               : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+}  // namespace ptx
+
+// shared-memory matrix descriptor of a K-major tile with 128-byte rows, 128-byte swizzle (8-row groups 1024 B apart)
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr & 0x3FFFFu) >> 4);  // start address            bits [0,14)
+  d |= (uint64_t)1 << 16;                    // leading byte offset (unused for swizzled K-major)   bits [16,30)
+  d |= (uint64_t)(1024 >> 4) << 32;          // stride byte offset: 8 rows x 128 B                  bits [32,46)
+  d |= (uint64_t)1 << 46;                    // descriptor version 1 (sm_100)                       bits [46,48)
+  d |= (uint64_t)2 << 61;                    // SWIZZLE_128B                                        bits [61,64)
+  return d;
+}
+// instruction descriptor, kind::i8: D = S32, A = B = signed int8, both K-major, dense
+__host__ __device__ constexpr uint32_t umma_idesc_i8(int M, int N) {
+  return (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// W panel -> int8 digit planes
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void colmax_kernel(const double* __restrict__ Wp, int64_t ldw, int64_t nK, int64_t l_count, int64_t k_per_block,
+                              unsigned long long* __restrict__ colmax) {
+  const int64_t col = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (col >= l_count) return;
+  const int64_t k0 = (int64_t)blockIdx.y * k_per_block, k1 = min(nK, k0 + k_per_block);
+  unsigned long long mx = 0;
+  for (int64_t k = k0; k < k1; k++) {
+    unsigned long long key = abs_key(Wp[k * ldw + col]);
+    mx = key > mx ? key : mx;
+  }
+  atomicMax(&colmax[col], mx);
+}
+
+// e_l: the smallest exponent with max_K |W[K,l]| < 2^e_l; non-finite columns raise *bad
+__global__ void colexp_kernel(const unsigned long long* __restrict__ colmax, int64_t l_count, int64_t n_cols,
+                              int32_t* __restrict__ expo, double* __restrict__ colscale, int* __restrict__ bad) {
+  const int64_t col = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (col >= n_cols) return;
+  int e = 0;
+  if (col < l_count) {
+    const double mx = key_to_double(colmax[col]);
+    if (!(mx <= 1.7976931348623157e308)) *bad = 1;  // inf or nan
+    else if (mx > 0.0) frexp(mx, &e);               // mx = f * 2^e, f in [0.5, 1)
+  }
+  expo[col] = e;
+  colscale[col] = ldexp(1.0, e - 6);
+}
+
+// One CTA = one 64-column tile x 128 contracted indices.  Thread (col, kq) expands 4 consecutive K of its column per
+// step (coalesced 512-byte reads across the 64 columns) and packs the 4 digits of each plane into one 32-bit word;
+// the planes go through shared memory (pitch 33 words, conflict-free) so that every 128-byte K-major row is written
+// by one warp in one piece.
+__global__ void __launch_bounds__(256)
+slice_kernel(const double* __restrict__ Wp, int64_t ldw, int64_t nK, int64_t l_count, int64_t Kpad, int S,
+             const int32_t* __restrict__ expo, int8_t* __restrict__ q) {
+  extern __shared__ uint32_t sq[];  // [S][64][33]
+  const int64_t tile = blockIdx.x, kb = blockIdx.y;
+  const int col = threadIdx.x & 63, kq = threadIdx.x >> 6;
+  const int64_t l = tile * TC_BN + col;
+  const bool col_ok = l < l_count;
+  const int sh = 6 - (col_ok ? expo[l] : 0);
+  for (int it = 0; it < 8; it++) {
+    const int kw = it * 4 + kq;
+    uint32_t pack[TC_MAX_SLICES];
+#pragma unroll
+    for (int s = 0; s < TC_MAX_SLICES; s++) pack[s] = 0;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      const int64_t K = kb * TC_BK + kw * 4 + i;
+      double x = (col_ok && K < nK) ? Wp[K * ldw + l] : 0.0;
+      x = scalbn(x, sh);  // |x| < 64; exact (power-of-two scaling)
+#pragma unroll
+      for (int s = 0; s < TC_MAX_SLICES; s++) {
+        if (s < S) {
+          const double d = rint(x);   // |d| <= 64
+          x = (x - d) * 128.0;        // exact: |x - d| <= 1/2
+          pack[s] |= ((uint32_t)(uint8_t)(int8_t)(int)d) << (8 * i);
+        }
+      }
+    }
+#pragma unroll
+    for (int s = 0; s < TC_MAX_SLICES; s++)
+      if (s < S) sq[(s * TC_BN + col) * 33 + kw] = pack[s];
+  }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int row = warp; row < S * TC_BN; row += 8) {
+    const int s = row / TC_BN, c = row % TC_BN;
+    const int64_t orow = (tile * S + s) * TC_BN + c;
+    reinterpret_cast<uint32_t*>(q + orow * Kpad + kb * TC_BK)[lane] = sq[row * 33 + lane];
+  }
+}
+
+__global__ void reconstruct_kernel(const int8_t* __restrict__ q, const double* __restrict__ colscale, int64_t nK,
+                                   int64_t l_count, int64_t Kpad, int S, double* __restrict__ Wrec) {
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= nK * l_count) return;
+  const int64_t K = idx / l_count, l = idx - K * l_count;
+  const int64_t tile = l / TC_BN, c = l % TC_BN;
+  double v = 0.0;
+  for (int s = S - 1; s >= 0; s--) v = v * 0.0078125 + (double)q[((tile * S + s) * TC_BN + c) * Kpad + K];
+  Wrec[idx] = v * colscale[l];
+}
+
+void wslices_build(WSlices& ws, const double* Wp, int64_t ldw, int64_t nK, int64_t l_count, int S) {
+  if (S < 1 || S > TC_MAX_SLICES) fail(FRICC_EINVAL, "digit planes must be 1..%d", TC_MAX_SLICES);
+  if (nK <= 0 || l_count <= 0 || ldw < l_count) fail(FRICC_EINVAL, "bad panel shape");
+  const int64_t Kpad = ceil_div(nK, TC_BK) * TC_BK, n_tiles = ceil_div(l_count, TC_BN);
+  const size_t qbytes = (size_t)n_tiles * S * TC_BN * Kpad;
+  if (ws.q.n != qbytes) ws.q.alloc(qbytes);
+  if (ws.expo.n != (size_t)(n_tiles * TC_BN)) {
+    ws.expo.alloc((size_t)(n_tiles * TC_BN));
+    ws.colscale.alloc((size_t)(n_tiles * TC_BN));
+  }
+  ws.nK = nK; ws.Kpad = Kpad; ws.l_count = l_count; ws.n_tiles = n_tiles; ws.S = S;
+  DevBuf<unsigned long long> colmax((size_t)l_count);
+  colmax.zero();
+  DevBuf<int> bad(1);
+  bad.zero();
+  const int64_t kpb = std::max<int64_t>(256, ceil_div(nK, 64));
+  dim3 g1((unsigned)ceil_div(l_count, 128), (unsigned)ceil_div(nK, kpb));
+  FRICC_LAUNCH(colmax_kernel, g1, 128, 0, Wp, ldw, nK, l_count, kpb, colmax.p);
+  FRICC_LAUNCH(colexp_kernel, (unsigned)ceil_div(n_tiles * TC_BN, 256), 256, 0, colmax.p, l_count, n_tiles * TC_BN,
+               ws.expo.p, ws.colscale.p, bad.p);
+  const size_t smem = (size_t)S * TC_BN * 33 * 4;
+  static bool attr_set = false;
+  if (!attr_set) {
+    FRICC_CUDA(cudaFuncSetAttribute(slice_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_MAX_SLICES * TC_BN * 33 * 4));
+    attr_set = true;
+  }
+  if (Kpad / TC_BK > 65535) fail(FRICC_EINVAL, "contracted pair too large for the slicing grid");
+  dim3 g2((unsigned)n_tiles, (unsigned)(Kpad / TC_BK));
+  FRICC_LAUNCH(slice_kernel, g2, 256, smem, Wp, ldw, nK, l_count, Kpad, S, ws.expo.p, ws.q.p);
+  int hbad = 0;
+  bad.to_host(&hbad, 1);
+  if (hbad) fail(FRICC_EINVAL, "W contains non-finite values: no digit expansion");
+}
+
+void wslices_reconstruct(const WSlices& ws, double* Wrec) {
+  const int64_t total = ws.nK * ws.l_count;
+  FRICC_LAUNCH(reconstruct_kernel, (unsigned)ceil_div(total, 256), 256, 0, ws.q.p, ws.colscale.p, ws.nK, ws.l_count,
+               ws.Kpad, ws.S, Wrec);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// bucketed entries -> int8 sign matrix + CSR remainder
+// ---------------------------------------------------------------------------------------------------------------
+// An entry goes into the sign matrix when its magnitude is c within 2^-49 relative (the spread the reference's
+// x/p rounding leaves is <= 3 ulp) and no other entry of the same (R, K) exists; everything else is the remainder.
+__device__ __forceinline__ bool is_sign_entry(const uint32_t* __restrict__ kidx, const double* __restrict__ vals,
+                                              int64_t t, int64_t e0, int64_t e1, double c, double tol) {
+  const double v = vals[t];
+  if (!(fabs(fabs(v) - c) <= tol) || v == 0.0) return false;
+  const uint32_t k = kidx[t];
+  if (t > e0 && kidx[t - 1] == k) return false;
+  if (t + 1 < e1 && kidx[t + 1] == k) return false;
+  return true;
+}
+
+// c = |value of the LAST stored entry| (storage order is [D..., S...]: the last entry is a sampled one whenever S is
+// not empty)
+__global__ void cmag_kernel(const double* __restrict__ stored_vals, int64_t nnz, double* __restrict__ cmag) {
+  cmag[0] = nnz > 0 ? fabs(stored_vals[nnz - 1]) : 0.0;
+}
+
+// one warp per row R: count the remainder entries
+__global__ void rest_count_kernel(const int64_t* __restrict__ rowptr, const uint32_t* __restrict__ kidx,
+                                  const double* __restrict__ vals, int64_t nR, const double* __restrict__ cmag,
+                                  int64_t* __restrict__ counts) {
+  const int64_t R = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (R >= nR) return;
+  const double c = cmag[0], tol = c * 1.7763568394002505e-15;  // 2^-49
+  const int64_t e0 = rowptr[R], e1 = rowptr[R + 1];
+  int64_t n = 0;
+  for (int64_t t = e0 + lane; t < e1; t += 32) n += is_sign_entry(kidx, vals, t, e0, e1, c, tol) ? 0 : 1;
+  for (int o = 16; o > 0; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
+  if (lane == 0) counts[R] = n;
+}
+
+// exclusive scan of nR counts by one CTA (nR is at most a few 10^5)
+__global__ void __launch_bounds__(1024) scan_counts_kernel(const int64_t* __restrict__ counts, int64_t nR,
+                                                           int64_t* __restrict__ rowptr) {
+  __shared__ int64_t warp_tot[32];
+  __shared__ int64_t carry_s;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) carry_s = 0;
+  __syncthreads();
+  for (int64_t base = 0; base < nR; base += 1024) {
+    const int64_t i = base + threadIdx.x;
+    const int64_t v = i < nR ? counts[i] : 0;
+    int64_t x = v;
+    for (int o = 1; o < 32; o <<= 1) {
+      int64_t y = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= o) x += y;
+    }
+    if (lane == 31) warp_tot[warp] = x;
+    __syncthreads();
+    if (warp == 0) {
+      int64_t w = warp_tot[lane];
+      for (int o = 1; o < 32; o <<= 1) {
+        int64_t y = __shfl_up_sync(0xffffffffu, w, o);
+        if (lane >= o) w += y;
+      }
+      warp_tot[lane] = w;  // inclusive over warps
+    }
+    __syncthreads();
+    const int64_t carry = carry_s;
+    const int64_t excl = carry + (warp > 0 ? warp_tot[warp - 1] : 0) + x - v;
+    if (i < nR) rowptr[i] = excl;
+    __syncthreads();
+    if (threadIdx.x == 1023) carry_s = carry + warp_tot[31];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) rowptr[nR] = carry_s;
+}
+
+// one warp per row R: signs into A[R][K], the remainder compacted in order
+__global__ void dense_fill_kernel(const int64_t* __restrict__ rowptr, const uint32_t* __restrict__ kidx,
+                                  const double* __restrict__ vals, int64_t nR, const double* __restrict__ cmag,
+                                  int64_t Kpad, int8_t* __restrict__ A, const int64_t* __restrict__ rest_rowptr,
+                                  uint32_t* __restrict__ rest_kidx, double* __restrict__ rest_vals) {
+  const int64_t R = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (R >= nR) return;
+  const double c = cmag[0], tol = c * 1.7763568394002505e-15;
+  const int64_t e0 = rowptr[R], e1 = rowptr[R + 1];
+  int64_t pos = rest_rowptr[R];
+  for (int64_t b = e0; b < e1; b += 32) {
+    const int64_t t = b + lane;
+    bool rest = false;
+    if (t < e1) {
+      if (is_sign_entry(kidx, vals, t, e0, e1, c, tol)) A[R * Kpad + kidx[t]] = vals[t] > 0.0 ? (int8_t)1 : (int8_t)-1;
+      else rest = true;
+    }
+    const unsigned mask = __ballot_sync(0xffffffffu, rest);
+    if (rest) {
+      const int64_t o = pos + __popc(mask & ((1u << lane) - 1u));
+      rest_kidx[o] = kidx[t];
+      rest_vals[o] = vals[t];
+    }
+    pos += __popc(mask);
+  }
+}
+
+double dense_form(fricc_st* T, Layout& lay) {
+  const int64_t m = T->nnz;
+  if (!lay.dense_built) {
+    lay.Mpad = ceil_div(lay.nR, TC_BM) * TC_BM;
+    lay.Kpad = ceil_div(lay.nK, TC_BK) * TC_BK;
+    lay.dense.alloc((size_t)(lay.Mpad * lay.Kpad));
+    lay.dense.zero();
+    lay.cmag.alloc(1);
+    lay.rest_rowptr.alloc((size_t)lay.nR + 1);
+    FRICC_LAUNCH(cmag_kernel, 1, 1, 0, T->vals.p, m, lay.cmag.p);
+    DevBuf<int64_t> counts((size_t)lay.nR);
+    const unsigned g = (unsigned)ceil_div(lay.nR * 32, 256);
+    FRICC_LAUNCH(rest_count_kernel, g, 256, 0, lay.rowptr.p, lay.kidx.p, lay.vals.p, lay.nR, lay.cmag.p, counts.p);
+    FRICC_LAUNCH(scan_counts_kernel, 1, 1024, 0, counts.p, lay.nR, lay.rest_rowptr.p);
+    int64_t n_rest = 0;
+    lay.rest_rowptr.to_host_at(&n_rest, (size_t)lay.nR);
+    lay.n_rest = n_rest;
+    lay.rest_kidx.alloc((size_t)std::max<int64_t>(n_rest, 1));
+    lay.rest_vals.alloc((size_t)std::max<int64_t>(n_rest, 1));
+    FRICC_LAUNCH(dense_fill_kernel, g, 256, 0, lay.rowptr.p, lay.kidx.p, lay.vals.p, lay.nR, lay.cmag.p, lay.Kpad,
+                 lay.dense.p, lay.rest_rowptr.p, lay.rest_kidx.p, lay.rest_vals.p);
+    lay.dense_built = true;
+  }
+  return m > 0 ? 1.0 - (double)lay.n_rest / (double)m : 0.0;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// the tensor-core kernel
+// ---------------------------------------------------------------------------------------------------------------
+struct TcParams {
+  int64_t nR, l_begin, l_count;
+  int S, stages, nkb;
+  const double* colscale;  // [n_tiles*64]  2^(e_l - 6)
+  const double* cmag;      // [1]
+  double scale;
+  double* out;
+  OutMap om;
+};
+
+__global__ void __launch_bounds__(TC_THREADS, 1)
+tc_sign_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const TcParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const int S = p.S, stages = p.stages;
+  const uint32_t stage_bytes = TC_A_BYTES + (uint32_t)S * TC_B_PLANE_BYTES;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + (size_t)stages * stage_bytes);
+  uint64_t* empty = full + stages;
+  uint64_t* tmem_full = empty + stages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m_tile = blockIdx.x, n_tile = blockIdx.y;
+
+  if (threadIdx.x == 0) {
+    ptx::prefetch_tensormap(&tmA);
+    ptx::prefetch_tensormap(&tmB);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int s = 0; s < stages; s++) {
+        ptx::mbar_init(&full[s], 1);
+        ptx::mbar_init(&empty[s], 1);
+      }
+      ptx::mbar_init(tmem_full, 1);
+      ptx::fence_barrier_init();
+    }
+    __syncwarp();
+    ptx::tmem_alloc(tmem_slot, TC_TMEM_COLS);
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      for (int kb = 0; kb < p.nkb; kb++) {
+        const int st = kb % stages, it = kb / stages;
+        if (it > 0) ptx::mbar_wait(&empty[st], (uint32_t)((it - 1) & 1));
+        uint8_t* a_dst = smem + (size_t)st * stage_bytes;
+        uint8_t* b_dst = a_dst + TC_A_BYTES;
+        ptx::mbar_expect_tx(&full[st], stage_bytes);
+        ptx::tma_load_2d(a_dst, &tmA, &full[st], kb * TC_BK, m_tile * TC_BM);
+        for (int s = 0; s < S; s++)
+          ptx::tma_load_2d(b_dst + (size_t)s * TC_B_PLANE_BYTES, &tmB, &full[st], kb * TC_BK, (n_tile * S + s) * TC_BN);
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ===== MMA issuer (one thread) =====
+    if (lane == 0) {
+      const int n1 = min(S, 4) * TC_BN, n2 = (S - min(S, 4)) * TC_BN;  // planes 0..3 | planes 4..S-1
+      const uint32_t idesc1 = umma_idesc_i8(TC_BM, n1), idesc2 = umma_idesc_i8(TC_BM, n2 > 0 ? n2 : 16);
+      for (int kb = 0; kb < p.nkb; kb++) {
+        const int st = kb % stages, it = kb / stages;
+        ptx::mbar_wait(&full[st], (uint32_t)(it & 1));
+        ptx::tc_fence_after();
+        const uint32_t a_addr = ptx::smem_u32(smem + (size_t)st * stage_bytes);
+        const uint32_t b_addr = a_addr + TC_A_BYTES;
+#pragma unroll
+        for (int k = 0; k < TC_BK / TC_UMMA_K; k++) {
+          const uint32_t acc = (kb | k) != 0 ? 1u : 0u;
+          const uint64_t adesc = umma_desc_sw128(a_addr + k * TC_UMMA_K);
+          ptx::mma_i8(tmem_base, adesc, umma_desc_sw128(b_addr + k * TC_UMMA_K), idesc1, acc);
+          if (n2 > 0)
+            ptx::mma_i8(tmem_base + 256, adesc, umma_desc_sw128(b_addr + 4 * TC_B_PLANE_BYTES + k * TC_UMMA_K), idesc2, acc);
+        }
+        ptx::mma_commit(&empty[st]);  // the stage may be refilled once these MMAs have read it
+      }
+      ptx::mma_commit(tmem_full);
+    }
+    __syncwarp();
+  } else {
+    // ===== epilogue: TMEM -> fp64 recombination of the planes -> out =====
+    const int q = warp & 3;  // the TMEM lane quarter this warp may access
+    const int64_t R = (int64_t)m_tile * TC_BM + q * 32 + lane;
+    ptx::mbar_wait(tmem_full, 0);
+    ptx::tc_fence_after();
+    const double coef = p.scale * p.cmag[0];
+    const bool row_ok = R < p.nR;
+    int64_t rbase = 0;
+    if (row_ok) {
+      const int64_t r1 = R / p.om.nR2, r2 = R - r1 * p.om.nR2;
+      rbase = r1 * p.om.sR1 + r2 * p.om.sR2;
+    }
+    const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
+    for (int j = 0; j < TC_BN / 8; j++) {
+      int32_t r[TC_MAX_SLICES][8];
+#pragma unroll
+      for (int s = 0; s < TC_MAX_SLICES; s++)
+        if (s < S) ptx::tmem_ld_x8(lane_addr + (uint32_t)(s * TC_BN + j * 8), r[s]);
+      ptx::tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < 8; i++) {
+        double v = 0.0;
+#pragma unroll
+        for (int s = TC_MAX_SLICES - 1; s >= 0; s--)
+          if (s < S) v = v * 0.0078125 + (double)r[s][i];
+        const int64_t c = (int64_t)n_tile * TC_BN + j * 8 + i;
+        if (row_ok && c < p.l_count) {
+          const int64_t l = p.l_begin + c;
+          const int64_t l1 = l / p.om.nL2, l2 = l - l1 * p.om.nL2;
+          double* o = p.out + rbase + l1 * p.om.sL1 + l2 * p.om.sL2;
+          *o += coef * p.colscale[c] * v;
+        }
+      }
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, TC_TMEM_COLS);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_tiled() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    FRICC_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres));
+    if (qres != cudaDriverEntryPointSuccess || !p) fail(FRICC_ECUDA, "cuTensorMapEncodeTiled is not available in this driver");
+    fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// int8 matrix [rows][Kpad] (K contiguous) -> tiled map with a (128 B x box_rows) box, 128-byte swizzle
+static CUtensorMap make_map_i8(const int8_t* base, int64_t rows, int64_t Kpad, int box_rows) {
+  CUtensorMap tm;
+  cuuint64_t dims[2] = {(cuuint64_t)Kpad, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)Kpad};
+  cuuint32_t box[2] = {(cuuint32_t)TC_BK, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = encode_tiled()(&tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<int8_t*>(base), dims, strides, box, estr,
+                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) fail(FRICC_ECUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
+  return tm;
+}
+
+void contract_dense(fricc_st* T, Layout& lay, const WSlices& ws, const double* Wp, int64_t ldw, int64_t l_begin,
+                    double* out, const OutMap& om, double scale) {
+  if (ws.nK != lay.nK) fail(FRICC_EINVAL, "digit planes were built for %lld contracted indices, the term has %lld",
+                            (long long)ws.nK, (long long)lay.nK);
+  dense_form(T, lay);
+  if (lay.n_rest < T->nnz) {
+    const int S = ws.S;
+    const uint32_t stage_bytes = TC_A_BYTES + (uint32_t)S * TC_B_PLANE_BYTES;
+    int stages = (int)std::min<uint32_t>(6, (220u * 1024u) / stage_bytes);
+    if (stages < 2) fail(FRICC_EINVAL, "too many digit planes for the shared-memory pipeline");
+    const size_t smem = (size_t)stages * stage_bytes + 1024 + 256;
+    static size_t attr_smem = 0;
+    if (smem > attr_smem) {
+      FRICC_CUDA(cudaFuncSetAttribute(tc_sign_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
+      attr_smem = 227 * 1024;
+    }
+    const CUtensorMap tmA = make_map_i8(lay.dense.p, lay.Mpad, lay.Kpad, TC_BM);
+    const CUtensorMap tmB = make_map_i8(ws.q.p, ws.n_tiles * S * TC_BN, ws.Kpad, TC_BN);
+    TcParams p;
+    p.nR = lay.nR; p.l_begin = l_begin; p.l_count = ws.l_count;
+    p.S = S; p.stages = stages; p.nkb = (int)(lay.Kpad / TC_BK);
+    p.colscale = ws.colscale.p; p.cmag = lay.cmag.p; p.scale = scale; p.out = out; p.om = om;
+    if (ws.n_tiles > 65535) fail(FRICC_EINVAL, "free pair too large for the tensor-core grid");
+    dim3 grid((unsigned)(lay.Mpad / TC_BM), (unsigned)ws.n_tiles);
+    FRICC_LAUNCH(tc_sign_gemm_kernel, grid, TC_THREADS, smem, tmA, tmB, p);
+  }
+  if (lay.n_rest > 0)
+    spmm_csr(lay.rest_rowptr.p, lay.rest_kidx.p, lay.rest_vals.p, lay.nR, Wp, ldw, l_begin, ws.l_count, out, om, scale);
+}
+
+}  // namespace fricc

@@ -84,6 +84,9 @@ class ShardedTerm:
         self.out_panel = None    # [nR][lc]
         self.gathered = None     # [world][nR][lc]
         self.L = _lib.lib()
+        self.planes = None       # int8 digit planes of `panel` (tensor-core form, fricc_dense.cu); None = fp64 SpMM only
+        self.n_planes = 0
+        self.tc_min_fraction = 0.5   # use the tensor-core form when at least this share of T is in the sign matrix
 
     # -- operands ---------------------------------------------------------------------------------------------
     def panel_bytes(self):
@@ -101,6 +104,48 @@ class ShardedTerm:
             check(self.L.fricc_permute_w(_ptr(W), _lib.FRICC_DEVICE, i64x4(W.shape), i64x4(W.stride()),
                                          self.term.encode(), self.l0, self.lcnt, _ptr(self.panel)))
 
+    # -- tensor-core form ------------------------------------------------------------------------------------
+    def build_planes(self, n_planes=7, panel=None, lcnt=None):
+        """Expand this rank's W panel into int8 digit planes (error-free up to 2^(-7*n_planes) of each column's largest
+        element).  Call again (or `refresh_planes`) whenever the panel's values change."""
+        panel = self.panel if panel is None else panel
+        lcnt = self.lcnt if lcnt is None else lcnt
+        self.drop_planes()
+        if lcnt <= 0:
+            return
+        h = ctypes.c_void_p()
+        check(self.L.fricc_wslices_create(_ptr(panel), lcnt, self.nK, lcnt, int(n_planes), ctypes.byref(h)))
+        self.planes, self.n_planes, self._planes_lcnt = h, int(n_planes), lcnt
+
+    def refresh_planes(self, panel=None):
+        panel = self.panel if panel is None else panel
+        if self.planes is not None:
+            check(self.L.fricc_wslices_update(self.planes, _ptr(panel), self._planes_lcnt))
+
+    def share_planes(self, other):
+        """Terms that read the same panel share its planes (not owned: only `other` frees them)."""
+        self.planes, self.n_planes, self._planes_lcnt, self._planes_borrowed = other.planes, other.n_planes, other._planes_lcnt, True
+
+    def drop_planes(self):
+        if self.planes is not None and not getattr(self, "_planes_borrowed", False):
+            self.L.fricc_wslices_destroy(self.planes)
+        self.planes, self._planes_borrowed = None, False
+
+    def __del__(self):
+        try:
+            self.drop_planes()
+        except Exception:
+            pass
+
+    def use_tc(self, T):
+        """Tensor-core form for this (term, T)?  Needs planes and a T whose entries mostly share one magnitude (an FRI
+        compression); density gating is the caller's choice of whether to build planes at all."""
+        if self.planes is None:
+            return False
+        f = ctypes.c_double(0.0)
+        check(self.L.fricc_st_sign_fraction(T._h, self.term.encode(), ctypes.byref(f)))
+        return f.value >= self.tc_min_fraction
+
     # -- compute ----------------------------------------------------------------------------------------------
     def local(self, T, into=None):
         """This rank's column slice of the output: out_panel[R][c] (+)= scale * sum_K T[R,K] * Wp[K][c].
@@ -115,8 +160,12 @@ class ShardedTerm:
             self.out_panel.zero_()
             target = self.out_panel
         if self.lcnt > 0:
-            check(self.L.fricc_contract_panel(_ptr(self.panel), self.lcnt, self.l0, self.lcnt, T._h,
-                                              _ptr(target), self.lc, self.term.encode()))
+            if self.use_tc(T):
+                check(self.L.fricc_contract_panel_tc(self.planes, _ptr(self.panel), self.lcnt, self.l0, T._h,
+                                                     _ptr(target), self.lc, self.term.encode()))
+            else:
+                check(self.L.fricc_contract_panel(_ptr(self.panel), self.lcnt, self.l0, self.lcnt, T._h,
+                                                  _ptr(target), self.lc, self.term.encode()))
         return target
 
     def start_exchange(self):
@@ -152,8 +201,12 @@ class ShardedTerm:
         l0 = self.l0 if l0 is None else l0
         lcnt = self.lcnt if lcnt is None else lcnt
         if lcnt > 0:
-            check(self.L.fricc_contract_panel_into(_ptr(panel), lcnt, l0, lcnt, T._h, _ptr(out), i64x4(out.shape),
-                                                   i64x4(out.stride()), self.term.encode()))
+            if self.planes is not None and lcnt == self._planes_lcnt and self.use_tc(T):
+                check(self.L.fricc_contract_panel_into_tc(self.planes, _ptr(panel), lcnt, l0, T._h, _ptr(out),
+                                                          i64x4(out.shape), i64x4(out.stride()), self.term.encode()))
+            else:
+                check(self.L.fricc_contract_panel_into(_ptr(panel), lcnt, l0, lcnt, T._h, _ptr(out), i64x4(out.shape),
+                                                       i64x4(out.stride()), self.term.encode()))
 
     def __call__(self, T, out, W=None):
         if W is not None:

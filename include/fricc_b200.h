@@ -123,6 +123,32 @@ int fricc_contract_panel_into(const double* Wp_dev, int64_t ldw, int64_t l_begin
  * [g*ld, min((g+1)*ld, nL)); panels is [n_panels][nR][ld] row-major on the device, out a 4-D strided device array).   */
 int fricc_accumulate_panels(const double* panels_dev, int64_t n_panels, int64_t ld, fricc_st_t T, const char* term,
                             double* out_dev, const int64_t out_shape[4], const int64_t out_strides[4]);
+/* ---- tensor-core form of the contractions (fricc_b200/csrc/fricc_dense.cu) ------------------------------------
+ * Replaces the same reference kernels as fricc_contract_panel (src/sparse_tensor.cpp:12-346) when T comes out of an
+ * FRI compression: every sampled entry then has the same magnitude c (fri_utils.cpp:375,502-504), so
+ *   out += scale * ( c * SIGN[R,K] x W[K,l]  +  REST[R,K] x W[K,l] ).
+ * W is expanded error-free into `n_planes` int8 digit planes (radix 128, one power-of-two scale per column l);
+ * SIGN x planes runs on the int8 tensor cores (tcgen05.mma.kind::i8, exact int32 accumulation), the planes are
+ * recombined in fp64, REST (the exactly preserved set D, duplicates, any entry whose magnitude is not c) goes through
+ * the fp64 SpMM.  The only approximation is the dropped tail of the expansion: <= 2^(-7*n_planes) of the column's
+ * largest |W| per term (n_planes = 7: 2^-49).                                                                        */
+typedef struct fricc_wslices* fricc_wslices_t; /* digit planes of one W panel (device) */
+/* planes of the panel columns [0, l_count) of Wp_dev[nK][ldw] */
+int fricc_wslices_create(const double* Wp_dev, int64_t ldw, int64_t nK, int64_t l_count, int n_planes,
+                         fricc_wslices_t* out);
+int fricc_wslices_update(fricc_wslices_t h, const double* Wp_dev, int64_t ldw); /* re-expand (W changed), same shape */
+int fricc_wslices_destroy(fricc_wslices_t h);
+int fricc_wslices_bytes(fricc_wslices_t h, int64_t* bytes);
+/* Wrec_dev[nK][l_count] = the fp64 value the planes represent (for tests of the expansion) */
+int fricc_wslices_reconstruct(fricc_wslices_t h, double* Wrec_dev);
+/* fraction of T's entries that the layout of `term` holds in the sign matrix (0 for "largest" compressions) */
+int fricc_st_sign_fraction(fricc_st_t T, const char* term, double* fraction);
+/* same contract as fricc_contract_panel / fricc_contract_panel_into; l_count is the planes' l_count */
+int fricc_contract_panel_tc(fricc_wslices_t h, const double* Wp_dev, int64_t ldw, int64_t l_begin, fricc_st_t T,
+                            double* out_panel_dev, int64_t ld_out, const char* term);
+int fricc_contract_panel_into_tc(fricc_wslices_t h, const double* Wp_dev, int64_t ldw, int64_t l_begin, fricc_st_t T,
+                                 double* out_dev, const int64_t out_shape[4], const int64_t out_strides[4],
+                                 const char* term);
 /* permute a 4-D W into the [K][L] panel layout of `term` on the device (columns [l_begin, l_begin+l_count))        */
 int fricc_permute_w(const double* W, int w_mem, const int64_t w_shape[4], const int64_t w_strides[4],
                     const char* term, int64_t l_begin, int64_t l_count, double* Wp_dev);

@@ -1,0 +1,179 @@
+"""Tensor-core form of the contractions (fricc_b200/csrc/fricc_dense.cu), through the C-ABI:
+  * the int8 digit-plane expansion of W is error-free up to its stated tail (fricc_wslices_reconstruct),
+  * sign matrix x planes (tcgen05.mma.kind::i8) + fp64 remainder == the fp64 SpMM == the oracle, <= 1e-10 relative
+    (the P6 tolerance) for every term, on FRI-compressed tensors, at ragged shapes (rows % 128, columns % 64,
+    contracted pair % 128 all non-zero), onto non-zero outputs,
+  * "largest" compressions (no common magnitude) fall through to the fp64 SpMM.
+"""
+import ctypes
+
+import numpy as np
+import pytest
+
+from conftest import TERMS, synth_t2
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-10
+
+
+def _fri_tensor(rccsd, rng, no, nv, frac, method="systematic"):
+    n = no * no * nv * nv
+    t2 = synth_t2(rng, n, "heavier").reshape(no, no, nv, nv)
+    m = max(2, int(frac * n))
+    draws = rng.integers(0, 2**31 - 1, size=n).astype(np.int32)
+    T = rccsd.SparseTensor4d(t2, t2.shape, m, "fri", method, False, draws=draws)
+    flat, vals = T.export()
+    return T, flat, vals, (no, no, nv, nv)
+
+
+@pytest.mark.parametrize("n_planes", [1, 3, 7, 8])
+def test_digit_planes_are_error_free(rccsd, n_planes):
+    import torch
+
+    from fricc_b200 import _lib
+
+    L = _lib.lib()
+    rng = np.random.default_rng(n_planes)
+    nK, ld, lcnt = 300, 200, 150
+    W = rng.standard_normal((nK, ld)) * 10.0 ** rng.uniform(-8, 3, size=(1, ld))   # wide range of column scales
+    W[:, 5] = 0.0
+    W[7, :] = 0.0
+    Wd = torch.from_numpy(W).cuda()
+    h = ctypes.c_void_p()
+    _lib.check(L.fricc_wslices_create(ctypes.c_void_p(Wd.data_ptr()), ld, nK, lcnt, n_planes, ctypes.byref(h)))
+    rec = torch.empty(nK, lcnt, dtype=torch.float64, device="cuda")
+    _lib.check(L.fricc_wslices_reconstruct(h, ctypes.c_void_p(rec.data_ptr())))
+    _lib.check(L.fricc_wslices_destroy(h))
+    rec = rec.cpu().numpy()
+    colmax = np.abs(W[:, :lcnt]).max(axis=0)
+    e = np.where(colmax > 0, np.frexp(colmax)[1], 0)
+    bound = np.ldexp(1.0, e - 7 * n_planes)          # |remainder| <= 2^(e_l - 7 S)
+    err = np.abs(rec - W[:, :lcnt])
+    assert (err <= bound[None, :] * (1 + 1e-12) + 1e-300).all()
+    if n_planes == 8:
+        # 6 + 7*7 = 55 bits below the column's leading bit: elements within 2^-2 of the column maximum are exact
+        big = np.abs(W[:, :lcnt]) >= 0.25 * colmax[None, :]
+        assert np.array_equal(rec[big], W[:, :lcnt][big])
+
+
+@pytest.mark.parametrize("term", sorted(TERMS))
+@pytest.mark.parametrize("no,nv,frac", [(3, 7, 0.5), (6, 21, 0.2), (13, 17, 0.3)])
+def test_tc_equals_fp64_and_oracle(rccsd, port, term, no, nv, frac):
+    import torch
+
+    from fricc_b200 import dist as fd
+
+    rng = np.random.default_rng(1000 * no + nv)
+    T, flat, vals, dims = _fri_tensor(rccsd, rng, no, nv, frac)
+    ext = {"o": no, "v": nv}
+    waxes, oaxes, _, _ = TERMS[term]
+    W = rng.random([ext[c] for c in waxes]) - 0.3
+    out0 = rng.random([ext[c] for c in oaxes])
+    want = out0.copy()
+    port.contract(term, W, flat, vals, dims, want)
+
+    dev = torch.device("cuda", 0)
+    Wd = torch.from_numpy(W).to(dev)
+    world = 2
+    for n_planes in (7,):
+        outd = torch.from_numpy(out0).to(dev)
+        used = 0
+        for g in range(world):
+            st = fd.ShardedTerm(term, no, nv, fd.Comm(g, world), dev)
+            st.permute_from(Wd)
+            st.build_planes(n_planes)
+            st.tc_min_fraction = 0.0     # always take the tensor-core form (the sign matrix may be small here)
+            used += int(st.use_tc(T))
+            st.local_into(T, outd)
+            st.drop_planes()
+        assert used == world
+        got = outd.cpu().numpy()
+        assert np.abs(got - want).max() <= TOL * max(1.0, np.abs(want).max())
+
+
+def test_tc_panel_form_and_shared_panels(rccsd, port):
+    """out_panel form (multi-GPU layout) + accumulate; two terms adding into one panel."""
+    import torch
+
+    from fricc_b200 import dist as fd
+
+    rng = np.random.default_rng(3)
+    no, nv, world = 5, 19, 3
+    T, flat, vals, dims = _fri_tensor(rccsd, rng, no, nv, 0.3, "pivotal")
+    dev = torch.device("cuda", 0)
+    for term in ("2323", "1302", "0313"):
+        ext = {"o": no, "v": nv}
+        waxes, oaxes, _, _ = TERMS[term]
+        W = rng.random([ext[c] for c in waxes])
+        out0 = rng.random([ext[c] for c in oaxes])
+        want = out0.copy()
+        port.contract(term, W, flat, vals, dims, want)
+        Wd = torch.from_numpy(W).to(dev)
+        ranks = [fd.ShardedTerm(term, no, nv, fd.Comm(g, world), dev) for g in range(world)]
+        nR, lc = ranks[0].nR, ranks[0].lc
+        gathered = torch.zeros(world * nR * lc, dtype=torch.float64, device=dev)
+        for g, st in enumerate(ranks):
+            st.permute_from(Wd)
+            st.build_planes(7)
+            st.tc_min_fraction = 0.0
+            gathered[g * nR * lc:(g + 1) * nR * lc].copy_(st.local(T))
+        outd = torch.from_numpy(out0).to(dev)
+        fd.check(ranks[0].L.fricc_accumulate_panels(fd._ptr(gathered), world, lc, T._h, term.encode(), fd._ptr(outd),
+                                                    fd.i64x4(outd.shape), fd.i64x4(outd.stride())))
+        got = outd.cpu().numpy()
+        assert np.abs(got - want).max() <= TOL * max(1.0, np.abs(want).max()), term
+
+
+def test_largest_compression_has_no_sign_matrix(rccsd, port):
+    import torch
+
+    from fricc_b200 import _lib
+    from fricc_b200 import dist as fd
+
+    rng = np.random.default_rng(11)
+    no, nv = 4, 12
+    t2 = rng.standard_normal((no, no, nv, nv))
+    T = rccsd.SparseTensor4d(t2, t2.shape, 500, "largest")
+    f = ctypes.c_double(-1.0)
+    _lib.check(_lib.lib().fricc_st_sign_fraction(T._h, b"2323", ctypes.byref(f)))
+    assert f.value <= 2.0 / 500
+    flat, vals = T.export()
+    W = rng.random((nv, nv, nv, nv))
+    want = np.zeros((no, no, nv, nv))
+    port.contract("2323", W, flat, vals, t2.shape, want)
+    dev = torch.device("cuda", 0)
+    st = fd.ShardedTerm("2323", no, nv, fd.Comm(0, 1), dev)
+    st.permute_from(torch.from_numpy(W).to(dev))
+    st.build_planes(7)
+    assert not st.use_tc(T)
+    st.tc_min_fraction = 0.0      # forced: everything goes through the remainder, still correct
+    outd = torch.zeros(no, no, nv, nv, dtype=torch.float64, device=dev)
+    st.local_into(T, outd)
+    assert np.abs(outd.cpu().numpy() - want).max() <= TOL * np.abs(want).max()
+
+
+def test_tc_accuracy_follows_the_plane_count(rccsd, port):
+    """error ~ 2^(-7 S): each extra plane buys 7 bits; S = 7 is at fp64 rounding level."""
+    import torch
+
+    from fricc_b200 import dist as fd
+
+    rng = np.random.default_rng(5)
+    no, nv = 6, 24
+    T, flat, vals, dims = _fri_tensor(rccsd, rng, no, nv, 0.25)
+    W = rng.random((nv, nv, nv, nv))
+    want = np.zeros((no, no, nv, nv))
+    port.contract("2323", W, flat, vals, dims, want)
+    dev = torch.device("cuda", 0)
+    st = fd.ShardedTerm("2323", no, nv, fd.Comm(0, 1), dev)
+    st.permute_from(torch.from_numpy(W).to(dev))
+    st.tc_min_fraction = 0.0
+    errs = {}
+    for S in (2, 4, 6, 7):
+        st.build_planes(S)
+        outd = torch.zeros(no, no, nv, nv, dtype=torch.float64, device=dev)
+        st.local_into(T, outd)
+        errs[S] = np.abs(outd.cpu().numpy() - want).max() / np.abs(want).max()
+    assert errs[2] > errs[4] > errs[6] >= errs[7] * 0.5
+    assert errs[4] < 1e-6 and errs[6] <= TOL and errs[7] <= 1e-13
