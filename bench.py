@@ -54,6 +54,8 @@ def parse_args():
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--only-ladder", action="store_true", help="debug: time only the ladder launches")
+    p.add_argument("--planes", type=int, default=6,
+                   help="int8 digit planes of W for the tensor-core form of the contractions (0 = fp64 SpMM only)")
     p.add_argument("--no-overlap", action="store_true", help="N>1: one blocking exchange per term (A/B of the pipelined step)")
     return p.parse_args()
 
@@ -184,14 +186,18 @@ class Iteration:
         self.t2 = (z * torch.pow(10.0, -6.0 * u * u)).reshape(o, o, v, v).contiguous()
         del u, z
         self.terms = {t: fd.ShardedTerm(t, o, v, comm, device) for t in CONTRACTION_ORDER}
+        # tensor-core form when T is dense enough for it to win (fricc_dense.cu: break-even ~1.3 % at 6 planes)
+        self.planes = args.planes if (args.planes > 0 and self.m / self.N >= 0.015) else 0
+        for t in self.terms.values():
+            t.auto_planes = self.planes
         # ---- dense operands (U(0,1) like the reference's tests, fricc/tests/test_sparse_tensors.py:78)
         self.ovov = torch.rand(o, v, o, v, generator=g, device=device, dtype=torch.float64)
         # iteration-invariant operand -> its panels are permuted once, outside the timed region
         for t in ("1323", "0112", "0313"):
             self.terms[t].permute_from(self.ovov)
         # terms that read the same operand through the same (K, L) axes share one panel
-        self.terms["0113"].set_panel(self.terms["0112"].panel)
-        self.terms["0312"].set_panel(self.terms["0313"].panel)
+        self.terms["0113"].set_panel(self.terms["0112"].panel, planes_from=self.terms["0112"])
+        self.terms["0312"].set_panel(self.terms["0313"].panel, planes_from=self.terms["0313"])
         self.Wklij = torch.zeros(o, o, o, o, device=device, dtype=torch.float64)
         self.Wakic = torch.zeros(v, o, o, v, device=device, dtype=torch.float64)
         self.Wakci = torch.zeros(v, o, v, o, device=device, dtype=torch.float64)
@@ -209,6 +215,7 @@ class Iteration:
         self.lad_width = max((w for _, w in self.sub), default=1)
         self.lad_panel = torch.empty(lad.nK * self.lad_width, device=device, dtype=torch.float64)
         self.resident = len(self.sub) <= 1
+        self.plane_build_ms = []
         if self.resident and self.sub:
             self.fill_ladder_panel(0)
         self.draws = torch.randint(0, 2**31 - 1, (64,), generator=torch.Generator().manual_seed(5)).numpy().astype("int32")
@@ -228,6 +235,17 @@ class Iteration:
         step = 1 << 28
         for a in range(0, view.numel(), step):
             view[a: a + step].uniform_(0.0, 1.0, generator=g)
+        if self.planes > 0:
+            # the digit planes are a re-encoding of this INPUT (like its [K][L] permutation): built with it, untimed,
+            # and reported separately (`ladder_plane_build_ms`)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            if lad.planes is not None and lad._planes_lcnt == w:
+                lad.refresh_planes(self.lad_panel)
+            else:
+                lad.build_planes(self.planes, panel=self.lad_panel, lcnt=w)
+            e1.record()
+            self.plane_build_ms.append((e0, e1))
 
     def compress(self, t2):
         d = self.draws[self.draw_pos % 32:]
@@ -256,8 +274,12 @@ class Iteration:
             if single:
                 lad.local_into(T, self.t2new, panel=self.lad_panel, l0=lad.l0 + c, lcnt=w)
             else:
-                self.fd.check(L.fricc_contract_panel(self.fd._ptr(self.lad_panel), w, lad.l0 + c, w, T._h,
-                                                     ctypes_ptr(lad.out_panel, c), lad.lc, b"2323"))
+                if lad.planes is not None and lad._planes_lcnt == w and lad.use_tc(T):
+                    self.fd.check(L.fricc_contract_panel_tc(lad.planes, self.fd._ptr(self.lad_panel), w, lad.l0 + c, T._h,
+                                                            ctypes_ptr(lad.out_panel, c), lad.lc, b"2323"))
+                else:
+                    self.fd.check(L.fricc_contract_panel(self.fd._ptr(self.lad_panel), w, lad.l0 + c, w, T._h,
+                                                         ctypes_ptr(lad.out_panel, c), lad.lc, b"2323"))
             e1.record()
             self.ladder_events.append((e0, e1, w))
 
@@ -304,8 +326,8 @@ class Iteration:
             self.mark("1302")
             tm["1202"](T, self.tmp[0], W=self.Wakci)
             self.mark("1202")
-            tm["1303"].set_panel(tm["1302"].panel)   # same Wvoov panel (K=(k,c), L=(a,i))
-            tm["1203"].set_panel(tm["1202"].panel)   # same Wvovo panel
+            tm["1303"].set_panel(tm["1302"].panel, planes_from=tm["1302"])   # same Wvoov panel (K=(k,c), L=(a,i))
+            tm["1203"].set_panel(tm["1202"].panel, planes_from=tm["1202"])   # same Wvovo panel
             tm["1303"](T, self.tmp[1])
             self.mark("1303")
             tm["1203"](T, self.tmp[2])
@@ -342,9 +364,9 @@ class Iteration:
         tm["1302"].start_exchange()
         tm["2323"].finish(T, self.t2new)
         self.mark("intermediates_0101_1302_1202")
-        tm["1303"].set_panel(tm["1302"].panel); tm["1303"].local(T); tm["1303"].start_exchange()
+        tm["1303"].set_panel(tm["1302"].panel, planes_from=tm["1302"]); tm["1303"].local(T); tm["1303"].start_exchange()
         tm["0101"].finish(T, self.t2new)
-        tm["1203"].set_panel(tm["1202"].panel); tm["1203"].local(T); tm["1203"].start_exchange()
+        tm["1203"].set_panel(tm["1202"].panel, planes_from=tm["1202"]); tm["1203"].local(T); tm["1203"].start_exchange()
         tm["1302"].finish(T, self.tmp[0])
         tm["1303"].finish(T, self.tmp[1])
         tm["1203"].finish(T, self.tmp[2])
@@ -363,13 +385,13 @@ class Iteration:
         return {k: round(x / steps, 3) for k, x in out.items()}
 
 
-def ncu_traffic_per_launch():
+def ncu_traffic_per_launch(which="spmm_ladder"):
     """dram__bytes_read.sum + dram__bytes_write.sum of ONE ladder launch (1600 x 20000-column slice, m=1e7), from the
     committed `ncu --set full` capture (profiles/ncu_full_*_spmm_ladder.csv, newest round); None if absent."""
     import csv
     import glob
 
-    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "ncu_full_r*_spmm_ladder.csv")))
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", f"ncu_full_r*_{which}.csv")))
     if not files:
         return None
     scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
@@ -567,20 +589,41 @@ def run_b200_arm(args):
             pass
         peak = float(peaks.get("hbm_gbs", 6650.0))
         peak_kind = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
-        # dominant kernel: spmm_rows_kernel on the ladder; algorithmic bytes per launch:
-        # 8*m*cols (one W row slice per nonzero) + 8*o^2*cols (one R2 write) + 12*m (packed entries)
-        alg = [8.0 * m * c + 8.0 * o * o * c + 12.0 * m for c in lad_cols]
-        ach = sum(alg) / (sum(lad_ms) * 1e-3) / 1e9 if lad_ms else 0.0
+        tc = it.planes > 0
+        if tc:
+            # dominant kernel: tc_sign_gemm_kernel on the ladder (int8 tensor cores).  Algorithmic work per launch:
+            # 2 * rows * cols * nK * planes int8 operations (the dense sign-matrix x digit-plane product, unpadded).
+            # Peak: int8 runs at twice the bf16 rate on B200 (4.5 vs 2.25 POP/s nominal), so 2 x the MEASURED cuBLAS bf16
+            # figure; the ladder launches sit inside a long step -> the sustained (power-capped) figure.
+            alg = [2.0 * lad.nR * c * lad.nK * it.planes for c in lad_cols]
+            ach = sum(alg) / (sum(lad_ms) * 1e-3) / 1e12 if lad_ms else 0.0
+            bf16 = float(peaks.get("bf16_tflops_sustained", 1400.0))
+            peak = 2.0 * bf16
+            peak_kind = ("2 x measured bf16_tflops_sustained (MEASURED_PEAKS.json); int8 = 2 x bf16 rate" if
+                         "bf16_tflops_sustained" in peaks else "2 x fallback 1400 TFLOP/s sustained bf16")
+            roof = {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
+                    "traffic": ncu_traffic_per_launch("tc_ladder"),
+                    "kernel": f"tc_sign_gemm_kernel (ladder 2323, int8 tcgen05.mma, {it.planes} digit planes)",
+                    "peak_source": peak_kind, "peak_burst": 2.0 * float(peaks.get("bf16_tflops", 1590.0)),
+                    "unit_note": "int8 TOP/s (2 x MAC)",
+                    "fp64_equivalent_algorithmic_gbs": sum(8.0 * m * c for c in lad_cols) / (sum(lad_ms) * 1e-3) / 1e9
+                    if lad_ms else None}
+        else:
+            # dominant kernel: spmm_rows_kernel on the ladder; algorithmic bytes per launch:
+            # 8*m*cols (one W row slice per nonzero) + 8*o^2*cols (one R2 write) + 12*m (packed entries)
+            alg = [8.0 * m * c + 8.0 * o * o * c + 12.0 * m for c in lad_cols]
+            ach = sum(alg) / (sum(lad_ms) * 1e-3) / 1e9 if lad_ms else 0.0
+            roof = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                    "traffic": ncu_traffic_per_launch("spmm_ladder"), "kernel": "spmm_rows_wide_kernel<2> (ladder 2323)",
+                    "peak_source": peak_kind}
+        roof.update(launches_timed=len(lad_ms), avg_launch_ms=(sum(lad_ms) / len(lad_ms)) if lad_ms else None,
+                    algorithmic_per_launch=(sum(alg) / len(alg)) if alg else None)
         s_per_iter = ms * 1e-3 / args.steps
         line = {
             "metric": METRIC, "value": s_per_iter, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": False, "scaling": "strong",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": workload_config(args, world),
-            "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                         "traffic": ncu_traffic_per_launch(), "kernel": "spmm_rows_wide_kernel<2> (ladder 2323)",
-                         "peak_source": peak_kind,
-                         "launches_timed": len(lad_ms), "avg_launch_ms": (sum(lad_ms) / len(lad_ms)) if lad_ms else None,
-                         "algorithmic_bytes_per_launch": (sum(alg) / len(alg)) if alg else None},
+            "roofline": roof,
             "clocks": clocks, "gpu_launches": int(launches),
             "ladder_ms_per_step": sum(lad_ms) / args.steps, "stage_ms_per_step": stage_ms, "output_checksums": checks,
             "schedule": ("blocking exchange per term" if (world == 1 or args.no_overlap) else
@@ -589,6 +632,16 @@ def run_b200_arm(args):
                               f"sum of segments; ladder W regenerated in HBM between {len(it.sub)} column sub-shards",
         }
         line["config"]["ladder_subshards"] = len(it.sub)
+        line["config"]["precision"] = ("fp64 results: W expanded error-free into int8 digit planes (tail 2^-48 of each column's "
+                                       "largest element), exact int32 accumulation, fp64 recombination; measured max "
+                                       "deviation from the fp64 SpMM 7e-15 relative (profiles/tc_vs_fp64_r01_H_1gpu.jsonl)"
+                                       ) if tc else "fp64 FMA"
+        line["config"]["contraction_kernel"] = (f"int8 tensor cores, {it.planes} digit planes + fp64 remainder" if tc
+                                                else "fp64 bucketed SpMM")
+        if tc and it.plane_build_ms:
+            pb = [a.elapsed_time(b) for a, b in it.plane_build_ms]
+            line["ladder_plane_build_ms"] = {"per_build": sum(pb) / len(pb), "builds": len(pb),
+                                             "note": "untimed: re-encoding of the iteration-invariant ladder operand"}
         if not args.no_e2e:
             line["e2e"] = {"value": e2e_ms * 1e-3 / args.steps, "unit": UNIT,
                            "h2d_bytes_per_step": int(it.t2.numel() * 8), "d2h_bytes_per_step": int(it.t2new.numel() * 8)}

@@ -168,6 +168,7 @@ struct Layout {
   int64_t Mpad = 0, Kpad = 0;
   DevBuf<int8_t> dense;        // [Mpad][Kpad], K-major
   DevBuf<double> cmag;         // [1]  c
+  DevBuf<int32_t> rowsum;      // [Mpad] sum_K dense[R][K]
   int64_t n_rest = 0;          // entries in the CSR remainder
   DevBuf<int64_t> rest_rowptr; // [nR+1]
   DevBuf<uint32_t> rest_kidx;

@@ -4,17 +4,19 @@
 // (/root/reference/src/fri_utils.cpp:375,502-504): every sampled entry has the SAME magnitude c = r/n' (up to the last
 // bits of the two roundings), only the sign varies; the exactly preserved set D is a small prefix.  So
 //     out[R, l] += scale * ( c * sum_K sgn[R,K] * W[K,l]  +  sum_{rest} val * W[K,l] )
-// and the first sum is a {-1,0,+1} matrix times a dense fp64 matrix.  W is expanded ERROR-FREE into S int8 digit
-// planes per column (radix 128, digits in [-64,64], one power-of-two scale per column l -- the contracted index K runs
-// inside a column, so every partial product of a plane is an exact small integer):
-//     W[K,l] = 2^(e_l-6) * sum_s d_s[K,l] * 128^-s   + remainder,  |remainder| <= 2^(e_l - 7*S)
-// `tcgen05.mma.kind::i8` accumulates sgn x d_s exactly in int32 (|sum| <= 64 * nnz_row < 2^31), and the epilogue
-// recombines the S integer planes in fp64.  The only error is the dropped remainder: with S = 7 it is 2^-49 of the
-// column's largest element per term, i.e. below the rounding noise of the reference's own fp64 accumulation.
+// and the first sum is a {-1,0,+1} matrix times a dense fp64 matrix.  W is expanded ERROR-FREE into S unsigned 8-bit
+// digit planes per column (radix 256; one power-of-two scale 2^e_l per column l, e_l = exponent of the column's largest
+// magnitude -- the contracted index K runs inside a column, so every partial product of a plane is an exact integer):
+//     W[K,l] + 2^e_l = 2^(e_l+1) * sum_s d_s[K,l] * 256^-(s+1)  + tail,   d_s in [0,255],  |tail| <= 2^(e_l - 8 S)
+// (the 8S-bit integer rint(W * 2^(8S-1-e_l)) + 2^(8S-1), cut into bytes).  `tcgen05.mma.kind::i8` (signed A, unsigned B)
+// accumulates sgn x d_s exactly in int32 (|sum| <= 255 * nnz_row < 2^31); the epilogue removes the 2^e_l offset exactly
+// (an integer multiple of the row sum of the sign matrix, in units of plane 0) and recombines the planes in fp64.  The
+// only error is the rounded tail: with S = 6 it is 2^-48 of the column's largest element per term -- below the
+// rounding noise of the reference's own fp64 accumulation of ~6000 terms.
 //
 // When it wins: the dense product costs M*K*N*S int8 MACs regardless of m, the sparse product m*N fp64 FMAs through the
 // L1 data pipe (9.5 FMA/clk/SM measured, fricc_contract.cu).  At the headline density (3.9 %) the int8 path is several
-// times faster; below ~1.5 % the bucketed SpMM wins and is used (decision in dist.py / contract_dense's caller).
+// times faster; below ~1.3 % the bucketed SpMM wins and is used (decision in dist.py / contract_dense's caller).
 //
 // Kernel: one CTA = 128 rows (R) x 64 columns (l) x all S planes; warp 0 = TMA producer (128-byte-swizzled K-major
 // tiles, mbarrier ring), warp 1 = one thread issuing tcgen05.mma (A = sign tile 128 x 32 B, B = up to 4 planes x 64
@@ -123,9 +125,9 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr) {
   d |= (uint64_t)2 << 61;                    // SWIZZLE_128B                                        bits [61,64)
   return d;
 }
-// instruction descriptor, kind::i8: D = S32, A = B = signed int8, both K-major, dense
+// instruction descriptor, kind::i8: D = S32, A = signed int8, B = unsigned int8, both K-major, dense
 __host__ __device__ constexpr uint32_t umma_idesc_i8(int M, int N) {
-  return (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+  return (2u << 4) | (1u << 7) | (0u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -156,7 +158,7 @@ __global__ void colexp_kernel(const unsigned long long* __restrict__ colmax, int
     else if (mx > 0.0) frexp(mx, &e);               // mx = f * 2^e, f in [0.5, 1)
   }
   expo[col] = e;
-  colscale[col] = ldexp(1.0, e - 6);
+  colscale[col] = ldexp(1.0, e - 7);  // one unit of plane 0
 }
 
 // One CTA = one 64-column tile x 128 contracted indices.  Thread (col, kq) expands 4 consecutive K of its column per
@@ -171,7 +173,8 @@ slice_kernel(const double* __restrict__ Wp, int64_t ldw, int64_t nK, int64_t l_c
   const int col = threadIdx.x & 63, kq = threadIdx.x >> 6;
   const int64_t l = tile * TC_BN + col;
   const bool col_ok = l < l_count;
-  const int sh = 6 - (col_ok ? expo[l] : 0);
+  const int sh = 8 * S - 1 - (col_ok ? expo[l] : 0);
+  const long long half = 1LL << (8 * S - 1), top = (1LL << (8 * S)) - 1;
   for (int it = 0; it < 8; it++) {
     const int kw = it * 4 + kq;
     uint32_t pack[TC_MAX_SLICES];
@@ -180,16 +183,15 @@ slice_kernel(const double* __restrict__ Wp, int64_t ldw, int64_t nK, int64_t l_c
 #pragma unroll
     for (int i = 0; i < 4; i++) {
       const int64_t K = kb * TC_BK + kw * 4 + i;
-      double x = (col_ok && K < nK) ? Wp[K * ldw + l] : 0.0;
-      x = scalbn(x, sh);  // |x| < 64; exact (power-of-two scaling)
-#pragma unroll
-      for (int s = 0; s < TC_MAX_SLICES; s++) {
-        if (s < S) {
-          const double d = rint(x);   // |d| <= 64
-          x = (x - d) * 128.0;        // exact: |x - d| <= 1/2
-          pack[s] |= ((uint32_t)(uint8_t)(int8_t)(int)d) << (8 * i);
-        }
+      long long qi = 0;
+      if (col_ok && K < nK) {
+        // exact power-of-two scaling, ONE rounding to the 8S-bit grid; |W| < 2^e  =>  0 <= qi <= 2^(8S)
+        qi = llrint(scalbn(Wp[K * ldw + l], sh)) + half;
+        qi = qi > top ? top : (qi < 0 ? 0 : qi);
       }
+#pragma unroll
+      for (int s = 0; s < TC_MAX_SLICES; s++)
+        if (s < S) pack[s] |= (uint32_t)((qi >> (8 * (S - 1 - s))) & 255) << (8 * i);
     }
 #pragma unroll
     for (int s = 0; s < TC_MAX_SLICES; s++)
@@ -211,8 +213,8 @@ __global__ void reconstruct_kernel(const int8_t* __restrict__ q, const double* _
   const int64_t K = idx / l_count, l = idx - K * l_count;
   const int64_t tile = l / TC_BN, c = l % TC_BN;
   double v = 0.0;
-  for (int s = S - 1; s >= 0; s--) v = v * 0.0078125 + (double)q[((tile * S + s) * TC_BN + c) * Kpad + K];
-  Wrec[idx] = v * colscale[l];
+  for (int s = S - 1; s >= 0; s--) v = v * 0.00390625 + (double)(uint8_t)q[((tile * S + s) * TC_BN + c) * Kpad + K];
+  Wrec[idx] = (v - 128.0) * colscale[l];
 }
 
 void wslices_build(WSlices& ws, const double* Wp, int64_t ldw, int64_t nK, int64_t l_count, int S) {
@@ -331,20 +333,27 @@ __global__ void __launch_bounds__(1024) scan_counts_kernel(const int64_t* __rest
 // one warp per row R: signs into A[R][K], the remainder compacted in order
 __global__ void dense_fill_kernel(const int64_t* __restrict__ rowptr, const uint32_t* __restrict__ kidx,
                                   const double* __restrict__ vals, int64_t nR, const double* __restrict__ cmag,
-                                  int64_t Kpad, int8_t* __restrict__ A, const int64_t* __restrict__ rest_rowptr,
-                                  uint32_t* __restrict__ rest_kidx, double* __restrict__ rest_vals) {
+                                  int64_t Kpad, int8_t* __restrict__ A, int32_t* __restrict__ rowsum,
+                                  const int64_t* __restrict__ rest_rowptr, uint32_t* __restrict__ rest_kidx,
+                                  double* __restrict__ rest_vals) {
   const int64_t R = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (R >= nR) return;
   const double c = cmag[0], tol = c * 1.7763568394002505e-15;
   const int64_t e0 = rowptr[R], e1 = rowptr[R + 1];
   int64_t pos = rest_rowptr[R];
+  int sum = 0;
   for (int64_t b = e0; b < e1; b += 32) {
     const int64_t t = b + lane;
     bool rest = false;
     if (t < e1) {
-      if (is_sign_entry(kidx, vals, t, e0, e1, c, tol)) A[R * Kpad + kidx[t]] = vals[t] > 0.0 ? (int8_t)1 : (int8_t)-1;
-      else rest = true;
+      if (is_sign_entry(kidx, vals, t, e0, e1, c, tol)) {
+        const int sg = vals[t] > 0.0 ? 1 : -1;
+        A[R * Kpad + kidx[t]] = (int8_t)sg;
+        sum += sg;
+      } else {
+        rest = true;
+      }
     }
     const unsigned mask = __ballot_sync(0xffffffffu, rest);
     if (rest) {
@@ -354,6 +363,8 @@ __global__ void dense_fill_kernel(const int64_t* __restrict__ rowptr, const uint
     }
     pos += __popc(mask);
   }
+  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  if (lane == 0) rowsum[R] = sum;
 }
 
 double dense_form(fricc_st* T, Layout& lay) {
@@ -364,6 +375,8 @@ double dense_form(fricc_st* T, Layout& lay) {
     lay.dense.alloc((size_t)(lay.Mpad * lay.Kpad));
     lay.dense.zero();
     lay.cmag.alloc(1);
+    lay.rowsum.alloc((size_t)lay.Mpad);
+    lay.rowsum.zero();
     lay.rest_rowptr.alloc((size_t)lay.nR + 1);
     FRICC_LAUNCH(cmag_kernel, 1, 1, 0, T->vals.p, m, lay.cmag.p);
     DevBuf<int64_t> counts((size_t)lay.nR);
@@ -376,7 +389,7 @@ double dense_form(fricc_st* T, Layout& lay) {
     lay.rest_kidx.alloc((size_t)std::max<int64_t>(n_rest, 1));
     lay.rest_vals.alloc((size_t)std::max<int64_t>(n_rest, 1));
     FRICC_LAUNCH(dense_fill_kernel, g, 256, 0, lay.rowptr.p, lay.kidx.p, lay.vals.p, lay.nR, lay.cmag.p, lay.Kpad,
-                 lay.dense.p, lay.rest_rowptr.p, lay.rest_kidx.p, lay.rest_vals.p);
+                 lay.dense.p, lay.rowsum.p, lay.rest_rowptr.p, lay.rest_kidx.p, lay.rest_vals.p);
     lay.dense_built = true;
   }
   return m > 0 ? 1.0 - (double)lay.n_rest / (double)m : 0.0;
@@ -388,7 +401,8 @@ double dense_form(fricc_st* T, Layout& lay) {
 struct TcParams {
   int64_t nR, l_begin, l_count;
   int S, stages, nkb;
-  const double* colscale;  // [n_tiles*64]  2^(e_l - 6)
+  const double* colscale;  // [n_tiles*64]  2^(e_l - 7)
+  const int32_t* rowsum;   // [Mpad]
   const double* cmag;      // [1]
   double scale;
   double* out;
@@ -482,25 +496,32 @@ tc_sign_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       rbase = r1 * p.om.sR1 + r2 * p.om.sR2;
     }
     const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
+    const int off0 = 128 * p.rowsum[(int64_t)m_tile * TC_BM + q * 32 + lane];  // the 2^e_l offset, in units of plane 0
+    // first column of this tile, split into the (major, minor) pair of the free index
+    int64_t l = p.l_begin + (int64_t)n_tile * TC_BN;
+    int64_t l1 = l / p.om.nL2, l2 = l - l1 * p.om.nL2;
+    const int ncol = (int)min((int64_t)TC_BN, p.l_count - (int64_t)n_tile * TC_BN);
     for (int j = 0; j < TC_BN / 8; j++) {
       int32_t r[TC_MAX_SLICES][8];
 #pragma unroll
       for (int s = 0; s < TC_MAX_SLICES; s++)
         if (s < S) ptx::tmem_ld_x8(lane_addr + (uint32_t)(s * TC_BN + j * 8), r[s]);
       ptx::tmem_ld_wait();
+      double cs[8];
+#pragma unroll
+      for (int i = 0; i < 8; i++) cs[i] = (j * 8 + i < ncol) ? p.colscale[n_tile * TC_BN + j * 8 + i] : 0.0;
 #pragma unroll
       for (int i = 0; i < 8; i++) {
         double v = 0.0;
 #pragma unroll
-        for (int s = TC_MAX_SLICES - 1; s >= 0; s--)
-          if (s < S) v = v * 0.0078125 + (double)r[s][i];
-        const int64_t c = (int64_t)n_tile * TC_BN + j * 8 + i;
-        if (row_ok && c < p.l_count) {
-          const int64_t l = p.l_begin + c;
-          const int64_t l1 = l / p.om.nL2, l2 = l - l1 * p.om.nL2;
+        for (int s = TC_MAX_SLICES - 1; s >= 1; s--)
+          if (s < S) v = (v + (double)r[s][i]) * 0.00390625;
+        v += (double)(r[0][i] - off0);
+        if (row_ok && j * 8 + i < ncol) {
           double* o = p.out + rbase + l1 * p.om.sL1 + l2 * p.om.sL2;
-          *o += coef * p.colscale[c] * v;
+          *o += coef * cs[i] * v;
         }
+        if (++l2 == p.om.nL2) { l2 = 0; l1++; }
       }
     }
   }
@@ -566,7 +587,7 @@ void contract_dense(fricc_st* T, Layout& lay, const WSlices& ws, const double* W
     TcParams p;
     p.nR = lay.nR; p.l_begin = l_begin; p.l_count = ws.l_count;
     p.S = S; p.stages = stages; p.nkb = (int)(lay.Kpad / TC_BK);
-    p.colscale = ws.colscale.p; p.cmag = lay.cmag.p; p.scale = scale; p.out = out; p.om = om;
+    p.colscale = ws.colscale.p; p.rowsum = lay.rowsum.p; p.cmag = lay.cmag.p; p.scale = scale; p.out = out; p.om = om;
     if (ws.n_tiles > 65535) fail(FRICC_EINVAL, "free pair too large for the tensor-core grid");
     dim3 grid((unsigned)(lay.Mpad / TC_BM), (unsigned)ws.n_tiles);
     FRICC_LAUNCH(tc_sign_gemm_kernel, grid, TC_THREADS, smem, tmA, tmB, p);

@@ -5,7 +5,7 @@
 namespace fricc {
 
 // Error-free int8 digit expansion of a W panel (columns [0, l_count) of Wp[K][ldw]):
-//   W[K][l] = 2^(e_l - 6) * sum_s digit_s[K][l] * 128^(-s)  (+ a remainder below 2^(e_l - 7*S)),   |digit| <= 64,
+//   W[K][l] + 2^e_l = 2^(e_l - 7) * sum_s digit_s[K][l] * 256^(-s)  (+ a tail below 2^(e_l - 8*S)),   0 <= digit <= 255,
 // e_l = exponent of the largest magnitude in column l.  Stored K-major per 64-column tile:
 //   q[((tile*S + s)*64 + col)][Kpad]  (int8)
 struct WSlices {
@@ -13,10 +13,10 @@ struct WSlices {
   int S = 0;
   DevBuf<int8_t> q;
   DevBuf<int32_t> expo;      // [n_tiles*64]
-  DevBuf<double> colscale;   // [n_tiles*64]  2^(e_l - 6)
+  DevBuf<double> colscale;   // [n_tiles*64]  2^(e_l - 7)
 };
 
-constexpr int TC_MAX_SLICES = 8;
+constexpr int TC_MAX_SLICES = 7;
 
 void wslices_build(WSlices& ws, const double* Wp_dev, int64_t ldw, int64_t nK, int64_t l_count, int S);
 // Wrec[K][l_count] = the value the digits represent (fp64), for tests of the expansion

@@ -87,14 +87,18 @@ class ShardedTerm:
         self.planes = None       # int8 digit planes of `panel` (tensor-core form, fricc_dense.cu); None = fp64 SpMM only
         self.n_planes = 0
         self.tc_min_fraction = 0.5   # use the tensor-core form when at least this share of T is in the sign matrix
+        self.auto_planes = 0         # > 0: permute_from() also (re)builds that many digit planes
 
     # -- operands ---------------------------------------------------------------------------------------------
     def panel_bytes(self):
         return self.nK * max(self.lcnt, 1) * 8
 
-    def set_panel(self, panel):
+    def set_panel(self, panel, planes_from=None):
+        """Use an already permuted panel (optionally together with the digit planes another term built from it)."""
         assert panel.dtype == torch.float64 and panel.numel() >= self.nK * self.lcnt
         self.panel = panel
+        if planes_from is not None and planes_from.planes is not None:
+            self.share_planes(planes_from)
 
     def permute_from(self, W):
         """W: 4-D float64 CUDA tensor (any strides) -> this rank's [nK][lcnt] panel (hand-written transpose kernel)."""
@@ -103,10 +107,15 @@ class ShardedTerm:
         if self.lcnt > 0:
             check(self.L.fricc_permute_w(_ptr(W), _lib.FRICC_DEVICE, i64x4(W.shape), i64x4(W.stride()),
                                          self.term.encode(), self.l0, self.lcnt, _ptr(self.panel)))
+            if self.auto_planes > 0:     # keep the tensor-core operand in step with the panel
+                if self.planes is None:
+                    self.build_planes(self.auto_planes)
+                else:
+                    self.refresh_planes()
 
     # -- tensor-core form ------------------------------------------------------------------------------------
-    def build_planes(self, n_planes=7, panel=None, lcnt=None):
-        """Expand this rank's W panel into int8 digit planes (error-free up to 2^(-7*n_planes) of each column's largest
+    def build_planes(self, n_planes=6, panel=None, lcnt=None):
+        """Expand this rank's W panel into int8 digit planes (error-free up to 2^(-8*n_planes) of each column's largest
         element).  Call again (or `refresh_planes`) whenever the panel's values change."""
         panel = self.panel if panel is None else panel
         lcnt = self.lcnt if lcnt is None else lcnt

@@ -127,11 +127,11 @@ int fricc_accumulate_panels(const double* panels_dev, int64_t n_panels, int64_t 
  * Replaces the same reference kernels as fricc_contract_panel (src/sparse_tensor.cpp:12-346) when T comes out of an
  * FRI compression: every sampled entry then has the same magnitude c (fri_utils.cpp:375,502-504), so
  *   out += scale * ( c * SIGN[R,K] x W[K,l]  +  REST[R,K] x W[K,l] ).
- * W is expanded error-free into `n_planes` int8 digit planes (radix 128, one power-of-two scale per column l);
+ * W is expanded error-free into `n_planes` (1..7) 8-bit digit planes (radix 256, one power-of-two scale per column l);
  * SIGN x planes runs on the int8 tensor cores (tcgen05.mma.kind::i8, exact int32 accumulation), the planes are
  * recombined in fp64, REST (the exactly preserved set D, duplicates, any entry whose magnitude is not c) goes through
- * the fp64 SpMM.  The only approximation is the dropped tail of the expansion: <= 2^(-7*n_planes) of the column's
- * largest |W| per term (n_planes = 7: 2^-49).                                                                        */
+ * the fp64 SpMM.  The only approximation is the rounded tail of the expansion: <= 2^(-8*n_planes) of the column's
+ * largest |W| per term (n_planes = 6: 2^-48).                                                                        */
 typedef struct fricc_wslices* fricc_wslices_t; /* digit planes of one W panel (device) */
 /* planes of the panel columns [0, l_count) of Wp_dev[nK][ldw] */
 int fricc_wslices_create(const double* Wp_dev, int64_t ldw, int64_t nK, int64_t l_count, int n_planes,

@@ -20,7 +20,7 @@ def main():
     ap.add_argument("--v", type=int, default=400)
     ap.add_argument("--m", type=float, default=1e7)
     ap.add_argument("--cols", type=int, default=20000, help="columns of the ladder slice held by this GPU")
-    ap.add_argument("--planes", type=int, default=7)
+    ap.add_argument("--planes", type=int, default=6)
     ap.add_argument("--terms", default="2323,1302")
     ap.add_argument("--reps", type=int, default=3)
     ap.add_argument("--check", action="store_true", help="compare the two kernels' outputs")
