@@ -346,31 +346,38 @@ class Iteration:
             t.zero_()
         self.mark("zero_outputs")
         tm["1323"].local(T_alt); tm["1323"].start_exchange()
+        self.mark("1323_local")
         tm["0112"].local(T_alt)
         tm["0313"].local(T_alt, into=tm["0112"])
         tm["0113"].local(T_alt, into=tm["0112"])
         tm["0112"].start_exchange()
+        self.mark("0112_0313_0113_local")
         tm["0312"].local(T_alt); tm["0312"].start_exchange()
-        self.mark("ovov_terms_local")
+        self.mark("0312_local")
         self.ladder_local(T, timer)                       # the long one: hides the three gathers above
         tm["2323"].start_exchange()
         self.mark("2323_local" if self.resident else "2323_local_incl_regen")
         tm["1323"].finish(T_alt, self.Wklij)
         tm["0112"].finish(T_alt, self.Wakic)
         tm["0312"].finish(T_alt, self.Wakci)
+        self.mark("finish_Woooo_Wvoov_Wvovo")
         tm["0101"].permute_from(self.Wklij); tm["0101"].local(T); tm["0101"].start_exchange()
+        self.mark("0101_local")
         tm["1302"].permute_from(self.Wakic); tm["1302"].local(T)
         tm["1202"].permute_from(self.Wakci); tm["1202"].local(T, into=tm["1302"])
         tm["1302"].start_exchange()
+        self.mark("1302_1202_local")
         tm["2323"].finish(T, self.t2new)
-        self.mark("intermediates_0101_1302_1202")
+        self.mark("finish_2323")
         tm["1303"].set_panel(tm["1302"].panel, planes_from=tm["1302"]); tm["1303"].local(T); tm["1303"].start_exchange()
+        self.mark("1303_local")
         tm["0101"].finish(T, self.t2new)
         tm["1203"].set_panel(tm["1202"].panel, planes_from=tm["1202"]); tm["1203"].local(T); tm["1203"].start_exchange()
+        self.mark("finish_0101_1203_local")
         tm["1302"].finish(T, self.tmp[0])
         tm["1303"].finish(T, self.tmp[1])
         tm["1203"].finish(T, self.tmp[2])
-        self.mark("1303_1203_and_drain")
+        self.mark("finish_tmp0_tmp1_tmp2")
         return T
 
     def stage_breakdown(self, steps):

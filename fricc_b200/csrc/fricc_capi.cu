@@ -40,6 +40,7 @@ int64_t span_of(const int64_t shape[4], const int64_t strides[4]) {
 
 void build_from_compressed(fricc_st* t, Compressed& c) {
   t->nnz = c.m;
+  t->n_exact = c.nD;
   t->flat = std::move(c.flat);
   t->vals = std::move(c.vals);
   t->layouts.clear();
@@ -85,6 +86,7 @@ int create_impl(const double* tensor, int mem, const int64_t dims[4], int64_t m,
   fricc_st* t = new fricc_st();
   for (int i = 0; i < 4; i++) t->dims[i] = dims[i];
   build_from_compressed(t, c);
+  if (largest) t->n_exact = t->nnz;  // no common magnitude to expect
   FRICC_CUDA(cudaStreamSynchronize(stream()));  // staged input must outlive the kernels that read it
   *out = t;
   FRICC_API_END
@@ -265,6 +267,7 @@ int fricc_st_set_element(fricc_st_t t, int64_t mi, int64_t flat_idx, double valu
   FRICC_CUDA(cudaMemcpyAsync(t->vals.p + mi, &value, 8, cudaMemcpyHostToDevice, stream()));
   FRICC_CUDA(cudaStreamSynchronize(stream()));
   t->layouts.clear();
+  t->n_exact = -1;
   t->host_valid = false;
   FRICC_API_END
 }

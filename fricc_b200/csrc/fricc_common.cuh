@@ -169,7 +169,7 @@ struct Layout {
   DevBuf<int8_t> dense;        // [Mpad][Kpad], K-major
   DevBuf<double> cmag;         // [1]  c
   DevBuf<int32_t> rowsum;      // [Mpad] sum_K dense[R][K]
-  int64_t n_rest = 0;          // entries in the CSR remainder
+  int64_t n_rest = -1;         // entries in the CSR remainder (-1: only known on the device, rest_rowptr[nR])
   DevBuf<int64_t> rest_rowptr; // [nR+1]
   DevBuf<uint32_t> rest_kidx;
   DevBuf<double> rest_vals;
@@ -180,6 +180,7 @@ struct Layout {
 struct fricc_st {
   int64_t dims[4] = {0, 0, 0, 0};
   int64_t nnz = 0;
+  int64_t n_exact = -1;  // leading entries that are NOT sampled ones (|D| of an FRI compression; nnz for "largest"); -1 = unknown
   fricc::DevBuf<int64_t> flat;   // [nnz] flat row-major index, storage order = reference order [D..., S...]
   fricc::DevBuf<double> vals;    // [nnz]
   std::vector<fricc::Layout> layouts;  // built lazily per term family, invalidated by set_element

@@ -146,19 +146,21 @@ __global__ void colmax_kernel(const double* __restrict__ Wp, int64_t ldw, int64_
   atomicMax(&colmax[col], mx);
 }
 
-// e_l: the smallest exponent with max_K |W[K,l]| < 2^e_l; non-finite columns raise *bad
+// e_l: the smallest exponent with max_K |W[K,l]| < 2^e_l.  A column holding inf/nan gets a NaN scale: its outputs
+// are poisoned (as the reference's fp64 sum would be) instead of becoming finite garbage -- no host round trip.
 __global__ void colexp_kernel(const unsigned long long* __restrict__ colmax, int64_t l_count, int64_t n_cols,
-                              int32_t* __restrict__ expo, double* __restrict__ colscale, int* __restrict__ bad) {
+                              int32_t* __restrict__ expo, double* __restrict__ colscale) {
   const int64_t col = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (col >= n_cols) return;
   int e = 0;
+  bool finite = true;
   if (col < l_count) {
     const double mx = key_to_double(colmax[col]);
-    if (!(mx <= 1.7976931348623157e308)) *bad = 1;  // inf or nan
-    else if (mx > 0.0) frexp(mx, &e);               // mx = f * 2^e, f in [0.5, 1)
+    finite = mx <= 1.7976931348623157e308;
+    if (finite && mx > 0.0) frexp(mx, &e);  // mx = f * 2^e, f in [0.5, 1)
   }
   expo[col] = e;
-  colscale[col] = ldexp(1.0, e - 7);  // one unit of plane 0
+  colscale[col] = finite ? ldexp(1.0, e - 7) : __longlong_as_double(0x7ff8000000000000LL);  // one unit of plane 0
 }
 
 // One CTA = one 64-column tile x 128 contracted indices.  Thread (col, kq) expands 4 consecutive K of its column per
@@ -230,13 +232,11 @@ void wslices_build(WSlices& ws, const double* Wp, int64_t ldw, int64_t nK, int64
   ws.nK = nK; ws.Kpad = Kpad; ws.l_count = l_count; ws.n_tiles = n_tiles; ws.S = S;
   DevBuf<unsigned long long> colmax((size_t)l_count);
   colmax.zero();
-  DevBuf<int> bad(1);
-  bad.zero();
   const int64_t kpb = std::max<int64_t>(256, ceil_div(nK, 64));
   dim3 g1((unsigned)ceil_div(l_count, 128), (unsigned)ceil_div(nK, kpb));
   FRICC_LAUNCH(colmax_kernel, g1, 128, 0, Wp, ldw, nK, l_count, kpb, colmax.p);
   FRICC_LAUNCH(colexp_kernel, (unsigned)ceil_div(n_tiles * TC_BN, 256), 256, 0, colmax.p, l_count, n_tiles * TC_BN,
-               ws.expo.p, ws.colscale.p, bad.p);
+               ws.expo.p, ws.colscale.p);
   const size_t smem = (size_t)S * TC_BN * 33 * 4;
   static bool attr_set = false;
   if (!attr_set) {
@@ -246,9 +246,6 @@ void wslices_build(WSlices& ws, const double* Wp, int64_t ldw, int64_t nK, int64
   if (Kpad / TC_BK > 65535) fail(FRICC_EINVAL, "contracted pair too large for the slicing grid");
   dim3 g2((unsigned)n_tiles, (unsigned)(Kpad / TC_BK));
   FRICC_LAUNCH(slice_kernel, g2, 256, smem, Wp, ldw, nK, l_count, Kpad, S, ws.expo.p, ws.q.p);
-  int hbad = 0;
-  bad.to_host(&hbad, 1);
-  if (hbad) fail(FRICC_EINVAL, "W contains non-finite values: no digit expansion");
 }
 
 void wslices_reconstruct(const WSlices& ws, double* Wrec) {
@@ -383,16 +380,18 @@ double dense_form(fricc_st* T, Layout& lay) {
     const unsigned g = (unsigned)ceil_div(lay.nR * 32, 256);
     FRICC_LAUNCH(rest_count_kernel, g, 256, 0, lay.rowptr.p, lay.kidx.p, lay.vals.p, lay.nR, lay.cmag.p, counts.p);
     FRICC_LAUNCH(scan_counts_kernel, 1, 1024, 0, counts.p, lay.nR, lay.rest_rowptr.p);
-    int64_t n_rest = 0;
-    lay.rest_rowptr.to_host_at(&n_rest, (size_t)lay.nR);
-    lay.n_rest = n_rest;
-    lay.rest_kidx.alloc((size_t)std::max<int64_t>(n_rest, 1));
-    lay.rest_vals.alloc((size_t)std::max<int64_t>(n_rest, 1));
+    // no host round trip: the remainder is compacted into buffers sized for the worst case (every entry)
+    lay.n_rest = -1;
+    lay.rest_kidx.alloc((size_t)std::max<int64_t>(m, 1));
+    lay.rest_vals.alloc((size_t)std::max<int64_t>(m, 1));
     FRICC_LAUNCH(dense_fill_kernel, g, 256, 0, lay.rowptr.p, lay.kidx.p, lay.vals.p, lay.nR, lay.cmag.p, lay.Kpad,
                  lay.dense.p, lay.rowsum.p, lay.rest_rowptr.p, lay.rest_kidx.p, lay.rest_vals.p);
     lay.dense_built = true;
   }
-  return m > 0 ? 1.0 - (double)lay.n_rest / (double)m : 0.0;
+  if (m == 0) return 0.0;
+  if (T->n_exact >= 0) return 1.0 - (double)T->n_exact / (double)m;  // FRI compression: everything behind D is sampled
+  if (lay.n_rest < 0) lay.rest_rowptr.to_host_at(&lay.n_rest, (size_t)lay.nR);  // unknown provenance: count (one sync)
+  return 1.0 - (double)lay.n_rest / (double)m;
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -571,7 +570,7 @@ void contract_dense(fricc_st* T, Layout& lay, const WSlices& ws, const double* W
   if (ws.nK != lay.nK) fail(FRICC_EINVAL, "digit planes were built for %lld contracted indices, the term has %lld",
                             (long long)ws.nK, (long long)lay.nK);
   dense_form(T, lay);
-  if (lay.n_rest < T->nnz) {
+  if (lay.n_rest != T->nnz) {
     const int S = ws.S;
     const uint32_t stage_bytes = TC_A_BYTES + (uint32_t)S * TC_B_PLANE_BYTES;
     int stages = (int)std::min<uint32_t>(6, (220u * 1024u) / stage_bytes);
@@ -592,7 +591,7 @@ void contract_dense(fricc_st* T, Layout& lay, const WSlices& ws, const double* W
     dim3 grid((unsigned)(lay.Mpad / TC_BM), (unsigned)ws.n_tiles);
     FRICC_LAUNCH(tc_sign_gemm_kernel, grid, TC_THREADS, smem, tmA, tmB, p);
   }
-  if (lay.n_rest > 0)
+  if (lay.n_rest != 0)
     spmm_csr(lay.rest_rowptr.p, lay.rest_kidx.p, lay.rest_vals.p, lay.nR, Wp, ldw, l_begin, ws.l_count, out, om, scale);
 }
 
