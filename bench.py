@@ -295,8 +295,16 @@ class Iteration:
 
     def step(self, t2, timer=None):
         self.mark("begin")
-        T = self.compress(t2)
-        T_alt = self.compress(t2)
+        if self.comm.world > 1 and not self.args.no_overlap:
+            # task-parallel: even ranks compress with the first draws, odd ranks with the second, entries broadcast
+            d = None
+            if self.args.sampling == "systematic":
+                d = (self.draws[self.draw_pos % 32:], self.draws[(self.draw_pos + 1) % 32:])
+            self.draw_pos += 2
+            T, T_alt = self.fd.compress_pair(t2, self.m, self.comm, "fri", self.args.sampling, draws=d)
+        else:
+            T = self.compress(t2)
+            T_alt = self.compress(t2)
         self.mark("compress_x2")
         if self.comm.world > 1 and not self.args.only_ladder and not self.args.no_overlap:
             return self.step_pipelined(T, T_alt, timer)

@@ -61,6 +61,11 @@ SIGNATURES = {
     "fricc_st_create_with_draws": (c_int, [c_void_p, c_int, _i64p, c_int64, c_char_p, c_char_p, c_int, c_void_p,
                                            c_int64, _i64p, POINTER(c_void_p)]),
     "fricc_st_create_from_coo": (c_int, [c_void_p, c_void_p, c_int, _i64p, c_int64, POINTER(c_void_p)]),
+    "fricc_st_get_n_exact": (c_int, [c_void_p, _i64p]),
+    "fricc_st_set_n_exact": (c_int, [c_void_p, c_int64]),
+    "fricc_rand_state_size": (c_int, []),
+    "fricc_rand_get_state": (c_int, [c_void_p]),
+    "fricc_rand_set_state": (c_int, [c_void_p]),
     "fricc_st_destroy": (c_int, [c_void_p]),
     "fricc_st_size": (c_int, [c_void_p, _i64p]),
     "fricc_st_dims": (c_int, [c_void_p, _i64p]),

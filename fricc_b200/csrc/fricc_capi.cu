@@ -164,6 +164,22 @@ int fricc_rand_skip(int64_t n) {
   rand_skip(n);
   FRICC_API_END
 }
+int fricc_rand_state_size(void) { return (int)sizeof(RandSnapshot); }
+int fricc_rand_get_state(void* buf) {
+  FRICC_API_BEGIN
+  if (!buf) fail(FRICC_EINVAL, "null argument");
+  RandSnapshot s = rand_snapshot();
+  memcpy(buf, &s, sizeof(s));
+  FRICC_API_END
+}
+int fricc_rand_set_state(const void* buf) {
+  FRICC_API_BEGIN
+  if (!buf) fail(FRICC_EINVAL, "null argument");
+  RandSnapshot s;
+  memcpy(&s, buf, sizeof(s));
+  rand_restore(s);
+  FRICC_API_END
+}
 int fricc_rand_fill_device(int32_t* out_dev, int64_t n) {
   FRICC_API_BEGIN
   if (n < 0 || (!out_dev && n > 0)) fail(FRICC_EINVAL, "bad arguments");
@@ -220,6 +236,22 @@ int fricc_st_create_from_coo(const int64_t* flat_idx, const double* vals, int me
     FRICC_CUDA(cudaStreamSynchronize(stream()));
   }
   *out = t;
+  FRICC_API_END
+}
+
+int fricc_st_get_n_exact(fricc_st_t t, int64_t* n_exact) {
+  FRICC_API_BEGIN
+  check_handle(t);
+  if (!n_exact) fail(FRICC_EINVAL, "null argument");
+  *n_exact = t->n_exact;
+  FRICC_API_END
+}
+
+int fricc_st_set_n_exact(fricc_st_t t, int64_t n_exact) {
+  FRICC_API_BEGIN
+  check_handle(t);
+  if (n_exact < -1 || n_exact > t->nnz) fail(FRICC_EINVAL, "n_exact out of range");
+  t->n_exact = n_exact;
   FRICC_API_END
 }
 

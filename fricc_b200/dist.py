@@ -237,3 +237,72 @@ def compress(t2, m, compression="fri", sampling_method="systematic", draws=None)
     """Replicated compression of the (replicated) dense T2: every rank runs the same deterministic kernels on the
     same data with the same draws, so the sparse tensors are identical without any exchange."""
     return SparseTensor4d(t2, tuple(t2.shape), int(m), compression, sampling_method, False, draws=draws)
+
+
+def _assumed_consumption(n, sampling_method):
+    """rand() draws one compression of an n-element tensor takes from the global stream: systematic draws once
+    (fri_utils.cpp:47); pivotal draws once per visited element, n - 1 unless the walk stops early (fri_utils.cpp:74,103)."""
+    return 1 if sampling_method == "systematic" else max(n - 1, 0)
+
+
+def compress_pair(t2, m, comm, compression="fri", sampling_method="systematic", draws=None):
+    """The TWO compressions of one FRICCSD iteration (fricc/friccsd.py:100-136: the same t2 compressed twice with fresh
+    draws -> t2_sparse, t2_sparse_alt), computed task-parallel: even ranks compute the first, odd ranks the second, and
+    the entries (16*m bytes each) are broadcast over NVLink, so no rank pays for both.
+
+    draws: None -> both compressions draw from the library's single glibc-compatible stream, in the reference's order
+    (the second starts where the first stopped); (d_first, d_second) -> explicit draw buffers (parity tests, bench).
+    Results are identical to two consecutive `compress` calls on every rank."""
+    world = comm.world
+    L = _lib.lib()
+    if world == 1:
+        if draws is None:
+            return (compress(t2, m, compression, sampling_method), compress(t2, m, compression, sampling_method))
+        return (compress(t2, m, compression, sampling_method, draws=draws[0]),
+                compress(t2, m, compression, sampling_method, draws=draws[1]))
+    import torch.distributed as dist
+
+    n = t2.numel()
+    mine = comm.rank % 2
+    state = None
+    if draws is None:
+        state = ctypes.create_string_buffer(L.fricc_rand_state_size())
+        check(L.fricc_rand_get_state(state))
+        assumed = _assumed_consumption(n, sampling_method)
+        if mine == 1:
+            check(L.fricc_rand_skip(assumed))
+        T_mine = compress(t2, m, compression, sampling_method)
+    else:
+        T_mine = compress(t2, m, compression, sampling_method, draws=draws[mine])
+    nnz = T_mine.size()
+    # payload per compression: [flat (nnz) | n_exact | consumed draws] and the values
+    idx = [torch.empty(nnz + 2, dtype=torch.int64, device=t2.device) for _ in range(2)]
+    val = [torch.empty(max(nnz, 1), dtype=torch.float64, device=t2.device) for _ in range(2)]
+    ne = ctypes.c_int64(0)
+    check(L.fricc_st_get_n_exact(T_mine._h, ctypes.byref(ne)))
+    check(L.fricc_st_export(T_mine._h, _ptr(idx[mine]), _ptr(val[mine]), _lib.FRICC_DEVICE))
+    idx[mine][nnz:] = torch.tensor([ne.value, int(T_mine.consumed_draws)], dtype=torch.int64, device=t2.device)
+    works = []
+    for which in (0, 1):   # rank 0 holds the first compression, rank 1 the second
+        works.append(dist.broadcast(idx[which], src=which, group=comm.group, async_op=True))
+        works.append(dist.broadcast(val[which], src=which, group=comm.group, async_op=True))
+    for w in works:
+        w.wait()
+    tail = torch.stack([idx[0][nnz:], idx[1][nnz:]]).cpu().tolist()   # [[n_exact, consumed], [n_exact, consumed]]
+    other = 1 - mine
+    T_other = SparseTensor4d.from_coo(idx[other][:nnz], val[other][:nnz], tuple(t2.shape))
+    check(L.fricc_st_set_n_exact(T_other._h, int(tail[other][0])))
+    T_other.consumed_draws = int(tail[other][1])
+    pair = [None, None]
+    pair[mine], pair[other] = T_mine, T_other
+    if draws is None:
+        c1 = int(tail[0][1])
+        check(L.fricc_rand_set_state(state))
+        check(L.fricc_rand_skip(c1))
+        if c1 != assumed:
+            # the first walk stopped early: the second compression started from the wrong stream position on the odd
+            # ranks -- redo it everywhere from the right one (rare; keeps the result exact)
+            pair[1] = compress(t2, m, compression, sampling_method)
+        else:
+            check(L.fricc_rand_skip(int(tail[1][1])))
+    return pair[0], pair[1]

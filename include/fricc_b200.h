@@ -74,6 +74,11 @@ int64_t fricc_rand_consumed(void);                               /* draws consum
 int fricc_rand_skip(int64_t n);                                  /* advance the stream by n draws (O(log n) jump)  */
 /* the next n values of rand() generated ON THE DEVICE into out_dev (per-thread jump-ahead over the linear recurrence);
  * does not advance the stream -- pair it with fricc_rand_skip(consumed)                                          */
+/* snapshot / restore of the rand() stream (ring + position), fricc_rand_state_size() bytes: lets ranks that compute
+ * different compressions of one iteration keep the single global stream the reference draws from (dist.compress_pair) */
+int fricc_rand_state_size(void);
+int fricc_rand_get_state(void* buf);
+int fricc_rand_set_state(const void* buf);
 int fricc_rand_fill_device(int32_t* out_dev, int64_t n);
 
 /* ---- SparseTensor4d (reference: include/sparse_tensor.hpp:13-100, src/py_rccsd.cpp:32-47) -------------------- */
@@ -92,6 +97,12 @@ int fricc_st_create_with_draws(const double* tensor, int mem, const int64_t dims
 /* build directly from m (flat index, value) pairs (host or device) -- used by the multi-GPU path after the gather  */
 int fricc_st_create_from_coo(const int64_t* flat_idx, const double* vals, int mem, const int64_t dims[4], int64_t m,
                              fricc_st_t* out);
+/* Provenance hint for the tensor-core form: the first n_exact stored entries are the exactly preserved set D of an FRI
+ * compression (include/sparse_tensor.hpp:58-67 stores [D..., S...]); every entry behind them is a sampled one and
+ * carries the common magnitude r/n'.  -1 = unknown (from_coo / set_element); nnz for "largest".  A tensor rebuilt from
+ * exported entries on another rank carries the hint over with set_n_exact.                                           */
+int fricc_st_get_n_exact(fricc_st_t T, int64_t* n_exact);
+int fricc_st_set_n_exact(fricc_st_t T, int64_t n_exact);
 int fricc_st_destroy(fricc_st_t t);
 int fricc_st_size(fricc_st_t t, int64_t* nnz);                                  /* size()       :87              */
 int fricc_st_dims(fricc_st_t t, int64_t dims[4]);                               /* dimensions() :86              */
