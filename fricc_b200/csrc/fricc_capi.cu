@@ -518,15 +518,15 @@ int fricc_st_sign_fraction(fricc_st_t T, const char* term, double* fraction) {
   check_handle(T);
   const TermSpec* ts = find_term(term);
   if (!ts || !fraction) fail(FRICC_EINVAL, "bad arguments");
-  *fraction = T->nnz > 0 ? dense_form(T, get_layout(T, *ts)) : 0.0;
+  *fraction = T->nnz > 0 ? dense_form(T, *ts, get_layout(T, *ts, false)) : 0.0;
   FRICC_API_END
 }
 
 static void contract_tc_common(fricc_wslices_t h, const double* Wp_dev, int64_t ldw, int64_t l_begin, fricc_st_t T,
                                double* out, const OutMap& om, const TermSpec* ts) {
   if (T->nnz == 0 || h->ws.l_count == 0) return;
-  Layout& lay = get_layout(T, *ts);
-  contract_dense(T, lay, h->ws, Wp_dev, ldw, l_begin, out, om, ts->scale);
+  Layout& lay = get_layout(T, *ts, false);
+  contract_dense(T, *ts, lay, h->ws, Wp_dev, ldw, l_begin, out, om, ts->scale);
 }
 
 int fricc_contract_panel_tc(fricc_wslices_t h, const double* Wp_dev, int64_t ldw, int64_t l_begin, fricc_st_t T,

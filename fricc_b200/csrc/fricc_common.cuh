@@ -157,6 +157,7 @@ static inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
 struct Layout {
   int r0 = -1, r1 = -1;  // which T axes form R = (r0, r1)   (K is the remaining two axes in ascending order)
   int64_t nR = 0, nK = 0;
+  bool csr_built = false;
   DevBuf<int64_t> rowptr;  // [nR+1]
   DevBuf<uint32_t> kidx;   // [nnz]
   DevBuf<double> vals;     // [nnz]

@@ -101,39 +101,54 @@ __global__ void rowptr_kernel(const uint64_t* __restrict__ keys, int64_t m, int6
   rowptr[R] = lo;
 }
 
-Layout& get_layout(fricc_st* T, const TermSpec& ts) {
-  for (Layout& l : T->layouts)
-    if (l.r0 == ts.tR[0] && l.r1 == ts.tR[1]) return l;
-  T->layouts.emplace_back();
-  Layout& lay = T->layouts.back();
-  lay.r0 = ts.tR[0];
-  lay.r1 = ts.tR[1];
+// entries [first, first + count) of T, bucketed by the owner pair of `ts`: sort by (R, K), CSR row pointers
+void build_csr(fricc_st* T, const TermSpec& ts, int64_t first, int64_t count, int64_t nR, int64_t nK,
+               DevBuf<int64_t>& rowptr, DevBuf<uint32_t>& kidx, DevBuf<double>& vals) {
   const int64_t* d = T->dims;
-  lay.nR = d[ts.tR[0]] * d[ts.tR[1]];
-  lay.nK = d[ts.tK[0]] * d[ts.tK[1]];
-  if (lay.nK >= ((int64_t)1 << 32)) fail(FRICC_EINVAL, "contracted pair too large for 32-bit packing");
-  const int64_t m = T->nnz;
-  lay.rowptr.alloc((size_t)lay.nR + 1);
-  lay.kidx.alloc((size_t)std::max<int64_t>(m, 1));
-  lay.vals.alloc((size_t)std::max<int64_t>(m, 1));
-  if (m == 0) {
-    lay.rowptr.zero();
-    return lay;
+  rowptr.alloc((size_t)nR + 1);
+  kidx.alloc((size_t)std::max<int64_t>(count, 1));
+  vals.alloc((size_t)std::max<int64_t>(count, 1));
+  if (count == 0) {
+    rowptr.zero();
+    return;
   }
+  const int64_t m = count;
   DevBuf<uint64_t> ka((size_t)m), kb((size_t)m), pa((size_t)m), pb((size_t)m);
   Dims4 dm{{d[0], d[1], d[2], d[3]}};
   unsigned g = (unsigned)ceil_div(m, 256);
-  FRICC_LAUNCH(make_keys_kernel, g, 256, 0, T->flat.p, T->vals.p, m, dm, ts.tR[0], ts.tR[1], ts.tK[0], ts.tK[1], ka.p, pa.p);
+  FRICC_LAUNCH(make_keys_kernel, g, 256, 0, T->flat.p + first, T->vals.p + first, m, dm, ts.tR[0], ts.tR[1], ts.tK[0],
+               ts.tK[1], ka.p, pa.p);
   int bits = 1;
-  while (bits < 63 && ((int64_t)1 << bits) < lay.nR * lay.nK) bits++;
+  while (bits < 63 && ((int64_t)1 << bits) < nR * nK) bits++;
   std::vector<Digit> digits;
   for (int s = 0; s < bits; s += 8) digits.push_back(Digit{0, s, 0});
   uint64_t* kk[2] = {ka.p, kb.p};
   uint64_t* pp[2] = {pa.p, pb.p};
   int r = radix_sort_pairs(kk, pp, m, digits);  // stable: duplicates keep their storage order
-  FRICC_LAUNCH(split_keys_kernel, g, 256, 0, kk[r], pp[r], m, lay.nK, lay.kidx.p, lay.vals.p);
-  FRICC_LAUNCH(rowptr_kernel, (unsigned)ceil_div(lay.nR + 1, 256), 256, 0, kk[r], m, lay.nK, lay.nR, lay.rowptr.p);
-  return lay;
+  FRICC_LAUNCH(split_keys_kernel, g, 256, 0, kk[r], pp[r], m, nK, kidx.p, vals.p);
+  FRICC_LAUNCH(rowptr_kernel, (unsigned)ceil_div(nR + 1, 256), 256, 0, kk[r], m, nK, nR, rowptr.p);
+}
+
+Layout& get_layout(fricc_st* T, const TermSpec& ts, bool need_csr) {
+  Layout* found = nullptr;
+  for (Layout& l : T->layouts)
+    if (l.r0 == ts.tR[0] && l.r1 == ts.tR[1]) found = &l;
+  if (!found) {
+    T->layouts.emplace_back();
+    Layout& lay = T->layouts.back();
+    lay.r0 = ts.tR[0];
+    lay.r1 = ts.tR[1];
+    const int64_t* d = T->dims;
+    lay.nR = d[ts.tR[0]] * d[ts.tR[1]];
+    lay.nK = d[ts.tK[0]] * d[ts.tK[1]];
+    if (lay.nK >= ((int64_t)1 << 32)) fail(FRICC_EINVAL, "contracted pair too large for 32-bit packing");
+    found = &lay;
+  }
+  if (need_csr && !found->csr_built) {
+    build_csr(T, ts, 0, T->nnz, found->nR, found->nK, found->rowptr, found->kidx, found->vals);
+    found->csr_built = true;
+  }
+  return *found;
 }
 
 // ---------------------------------------------------------------------------------------------------------------

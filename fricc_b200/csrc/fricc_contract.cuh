@@ -22,8 +22,11 @@ struct TermSpec {
 
 const TermSpec* find_term(const char* name);
 
-// bucketed layout of T for owner pair (tR) / contracted pair (tK); cached in the handle
-Layout& get_layout(fricc_st* T, const TermSpec& ts);
+// bucketed layout of T for owner pair (tR) / contracted pair (tK); cached in the handle.  need_csr = false returns the
+// entry without sorting the entries (the tensor-core form of an FRI compression does not need the full CSR)
+Layout& get_layout(fricc_st* T, const TermSpec& ts, bool need_csr = true);
+void build_csr(fricc_st* T, const TermSpec& ts, int64_t first, int64_t count, int64_t nR, int64_t nK,
+               DevBuf<int64_t>& rowptr, DevBuf<uint32_t>& kidx, DevBuf<double>& vals);
 
 // W (4-D, element strides) -> panel Wp[K][l_count] for the L columns [l_begin, l_begin + l_count)
 void permute_w(const double* W_dev, const int64_t shape[4], const int64_t strides[4], const TermSpec& ts,

@@ -364,7 +364,76 @@ __global__ void dense_fill_kernel(const int64_t* __restrict__ rowptr, const uint
   if (lane == 0) rowsum[R] = sum;
 }
 
-double dense_form(fricc_st* T, Layout& lay) {
+// ---- fast path for FRI compressions (T->n_exact >= 0): the entries behind the first n_exact ARE the sign matrix, so
+// nothing has to be sorted: scatter the signs straight from storage order, reduce the rows, and bucket only D.
+struct TDims {
+  int64_t d[4];
+  int r0, r1, k0, k1;
+};
+
+__global__ void sign_scatter_kernel(const int64_t* __restrict__ flat, const double* __restrict__ vals, int64_t first,
+                                    int64_t m, TDims td, const double* __restrict__ cmag, int64_t Kpad,
+                                    int8_t* __restrict__ A, unsigned long long* __restrict__ stragglers) {
+  const int64_t e = first + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= m) return;
+  int64_t f = flat[e];
+  int64_t ix[4];
+  ix[3] = f % td.d[3]; f /= td.d[3];
+  ix[2] = f % td.d[2]; f /= td.d[2];
+  ix[1] = f % td.d[1]; f /= td.d[1];
+  ix[0] = f;
+  const int64_t R = ix[td.r0] * td.d[td.r1] + ix[td.r1];
+  const int64_t K = ix[td.k0] * td.d[td.k1] + ix[td.k1];
+  const double v = vals[e], c = cmag[0];
+  if (fabs(fabs(v) - c) <= c * 1.7763568394002505e-15 && v != 0.0) A[R * Kpad + K] = v > 0.0 ? (int8_t)1 : (int8_t)-1;
+  else atomicAdd(stragglers, 1ULL);
+}
+
+// one CTA per row: sum and non-zero count of the row's bytes
+__global__ void __launch_bounds__(256)
+rowsum_kernel(const int8_t* __restrict__ A, int64_t Kpad, int32_t* __restrict__ rowsum,
+              unsigned long long* __restrict__ nnzA) {
+  __shared__ int ssum[8], scnt[8];
+  const int4* row = reinterpret_cast<const int4*>(A + (int64_t)blockIdx.x * Kpad);
+  int sum = 0, cnt = 0;
+  for (int64_t i = threadIdx.x; i < Kpad / 16; i += blockDim.x) {
+    const int4 w = row[i];
+    const int ws[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+      if (ws[q] == 0) continue;
+#pragma unroll
+      for (int b = 0; b < 4; b++) {
+        const int v = (int)(int8_t)((unsigned)ws[q] >> (8 * b));
+        sum += v;
+        cnt += v != 0;
+      }
+    }
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+  }
+  if ((threadIdx.x & 31) == 0) { ssum[threadIdx.x >> 5] = sum; scnt[threadIdx.x >> 5] = cnt; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int s = 0, c = 0;
+    for (int w = 0; w < 8; w++) { s += ssum[w]; c += scnt[w]; }
+    rowsum[blockIdx.x] = s;
+    if (c) atomicAdd(nnzA, (unsigned long long)c);
+  }
+}
+
+// The provenance hint promised "every entry behind the first n_exact is +-c at a distinct position".  If that does not
+// hold (a straggler magnitude, or two entries on one position) the common magnitude is poisoned, so the contraction
+// returns NaN instead of a silently wrong number -- without a host round trip.
+__global__ void sign_check_kernel(const unsigned long long* __restrict__ stragglers,
+                                  const unsigned long long* __restrict__ nnzA, unsigned long long expected,
+                                  double* __restrict__ cmag) {
+  if (stragglers[0] != 0 || nnzA[0] != expected) cmag[0] = __longlong_as_double(0x7ff8000000000000LL);
+}
+
+double dense_form(fricc_st* T, const TermSpec& ts, Layout& lay) {
   const int64_t m = T->nnz;
   if (!lay.dense_built) {
     lay.Mpad = ceil_div(lay.nR, TC_BM) * TC_BM;
@@ -374,24 +443,37 @@ double dense_form(fricc_st* T, Layout& lay) {
     lay.cmag.alloc(1);
     lay.rowsum.alloc((size_t)lay.Mpad);
     lay.rowsum.zero();
-    lay.rest_rowptr.alloc((size_t)lay.nR + 1);
     FRICC_LAUNCH(cmag_kernel, 1, 1, 0, T->vals.p, m, lay.cmag.p);
-    DevBuf<int64_t> counts((size_t)lay.nR);
-    const unsigned g = (unsigned)ceil_div(lay.nR * 32, 256);
-    FRICC_LAUNCH(rest_count_kernel, g, 256, 0, lay.rowptr.p, lay.kidx.p, lay.vals.p, lay.nR, lay.cmag.p, counts.p);
-    FRICC_LAUNCH(scan_counts_kernel, 1, 1024, 0, counts.p, lay.nR, lay.rest_rowptr.p);
-    // no host round trip: the remainder is compacted into buffers sized for the worst case (every entry)
-    lay.n_rest = -1;
-    lay.rest_kidx.alloc((size_t)std::max<int64_t>(m, 1));
-    lay.rest_vals.alloc((size_t)std::max<int64_t>(m, 1));
-    FRICC_LAUNCH(dense_fill_kernel, g, 256, 0, lay.rowptr.p, lay.kidx.p, lay.vals.p, lay.nR, lay.cmag.p, lay.Kpad,
-                 lay.dense.p, lay.rowsum.p, lay.rest_rowptr.p, lay.rest_kidx.p, lay.rest_vals.p);
+    if (T->n_exact >= 0) {
+      const int64_t nS = m - T->n_exact;
+      DevBuf<unsigned long long> counters(2);
+      counters.zero();
+      if (nS > 0) {
+        TDims td{{T->dims[0], T->dims[1], T->dims[2], T->dims[3]}, ts.tR[0], ts.tR[1], ts.tK[0], ts.tK[1]};
+        FRICC_LAUNCH(sign_scatter_kernel, (unsigned)ceil_div(nS, 256), 256, 0, T->flat.p, T->vals.p, T->n_exact, m, td,
+                     lay.cmag.p, lay.Kpad, lay.dense.p, counters.p);
+        FRICC_LAUNCH(rowsum_kernel, (unsigned)lay.nR, 256, 0, lay.dense.p, lay.Kpad, lay.rowsum.p, counters.p + 1);
+        FRICC_LAUNCH(sign_check_kernel, 1, 1, 0, counters.p, counters.p + 1, (unsigned long long)nS, lay.cmag.p);
+      }
+      lay.n_rest = T->n_exact;
+      build_csr(T, ts, 0, T->n_exact, lay.nR, lay.nK, lay.rest_rowptr, lay.rest_kidx, lay.rest_vals);
+    } else {
+      // unknown provenance: classify every entry of the sorted layout (duplicates and other magnitudes -> remainder)
+      get_layout(T, ts, true);
+      lay.rest_rowptr.alloc((size_t)lay.nR + 1);
+      DevBuf<int64_t> counts((size_t)lay.nR);
+      const unsigned g = (unsigned)ceil_div(lay.nR * 32, 256);
+      FRICC_LAUNCH(rest_count_kernel, g, 256, 0, lay.rowptr.p, lay.kidx.p, lay.vals.p, lay.nR, lay.cmag.p, counts.p);
+      FRICC_LAUNCH(scan_counts_kernel, 1, 1024, 0, counts.p, lay.nR, lay.rest_rowptr.p);
+      lay.rest_rowptr.to_host_at(&lay.n_rest, (size_t)lay.nR);
+      lay.rest_kidx.alloc((size_t)std::max<int64_t>(lay.n_rest, 1));
+      lay.rest_vals.alloc((size_t)std::max<int64_t>(lay.n_rest, 1));
+      FRICC_LAUNCH(dense_fill_kernel, g, 256, 0, lay.rowptr.p, lay.kidx.p, lay.vals.p, lay.nR, lay.cmag.p, lay.Kpad,
+                   lay.dense.p, lay.rowsum.p, lay.rest_rowptr.p, lay.rest_kidx.p, lay.rest_vals.p);
+    }
     lay.dense_built = true;
   }
-  if (m == 0) return 0.0;
-  if (T->n_exact >= 0) return 1.0 - (double)T->n_exact / (double)m;  // FRI compression: everything behind D is sampled
-  if (lay.n_rest < 0) lay.rest_rowptr.to_host_at(&lay.n_rest, (size_t)lay.nR);  // unknown provenance: count (one sync)
-  return 1.0 - (double)lay.n_rest / (double)m;
+  return m > 0 ? 1.0 - (double)lay.n_rest / (double)m : 0.0;
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -565,11 +647,11 @@ static CUtensorMap make_map_i8(const int8_t* base, int64_t rows, int64_t Kpad, i
   return tm;
 }
 
-void contract_dense(fricc_st* T, Layout& lay, const WSlices& ws, const double* Wp, int64_t ldw, int64_t l_begin,
-                    double* out, const OutMap& om, double scale) {
+void contract_dense(fricc_st* T, const TermSpec& ts, Layout& lay, const WSlices& ws, const double* Wp, int64_t ldw,
+                    int64_t l_begin, double* out, const OutMap& om, double scale) {
   if (ws.nK != lay.nK) fail(FRICC_EINVAL, "digit planes were built for %lld contracted indices, the term has %lld",
                             (long long)ws.nK, (long long)lay.nK);
-  dense_form(T, lay);
+  dense_form(T, ts, lay);
   if (lay.n_rest != T->nnz) {
     const int S = ws.S;
     const uint32_t stage_bytes = TC_A_BYTES + (uint32_t)S * TC_B_PLANE_BYTES;

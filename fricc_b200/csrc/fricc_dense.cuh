@@ -23,13 +23,13 @@ void wslices_build(WSlices& ws, const double* Wp_dev, int64_t ldw, int64_t nK, i
 void wslices_reconstruct(const WSlices& ws, double* Wrec_dev);
 
 // Builds (once per layout) the int8 sign matrix + CSR remainder; returns the fraction of entries in the sign matrix.
-double dense_form(fricc_st* T, Layout& lay);
+double dense_form(fricc_st* T, const TermSpec& ts, Layout& lay);
 
 // out[R, l] += scale * sum_K T[R,K] * W[K,l]   for the panel columns of `ws` (panel-local column j <-> l = l_begin + j):
 // sign matrix x digit slices on the int8 tensor cores (tcgen05.mma.kind::i8, exact int32 accumulation), the remainder
 // through the fp64 SpMM on Wp_dev.
-void contract_dense(fricc_st* T, Layout& lay, const WSlices& ws, const double* Wp_dev, int64_t ldw, int64_t l_begin,
-                    double* out_dev, const OutMap& om, double scale);
+void contract_dense(fricc_st* T, const TermSpec& ts, Layout& lay, const WSlices& ws, const double* Wp_dev, int64_t ldw,
+                    int64_t l_begin, double* out_dev, const OutMap& om, double scale);
 
 // CSR SpMM on raw arrays (fricc_contract.cu)
 void spmm_csr(const int64_t* rowptr, const uint32_t* kidx, const double* vals, int64_t nR, const double* Wp_dev,

@@ -177,3 +177,42 @@ def test_tc_accuracy_follows_the_plane_count(rccsd, port):
         errs[S] = np.abs(outd.cpu().numpy() - want).max() / np.abs(want).max()
     assert errs[2] > errs[3] > errs[5] >= errs[6] * 0.5
     assert errs[3] < 1e-5 and errs[5] <= TOL and errs[6] <= 1e-13
+
+
+def test_false_provenance_hint_poisons_instead_of_lying(rccsd, port):
+    """fricc_st_set_n_exact promises "everything behind the first n_exact entries is +-c at distinct positions"; when
+    that is false the result must be NaN, not a plausible wrong number."""
+    import torch
+
+    from fricc_b200 import _lib
+    from fricc_b200 import dist as fd
+
+    rng = np.random.default_rng(2)
+    no, nv = 4, 10
+    n = no * no * nv * nv
+    flat = rng.choice(n, 300, replace=False).astype(np.int64)
+    vals = rng.standard_normal(300)                     # not a common magnitude
+    T = rccsd.SparseTensor4d.from_coo(flat, vals, (no, no, nv, nv))
+    dev = torch.device("cuda", 0)
+    st = fd.ShardedTerm("2323", no, nv, fd.Comm(0, 1), dev)
+    st.permute_from(torch.rand(nv, nv, nv, nv, dtype=torch.float64, device=dev))
+    st.build_planes(6)
+    st.tc_min_fraction = 0.0
+    # honest (unknown provenance): everything is classified, the result is right
+    outd = torch.zeros(no, no, nv, nv, dtype=torch.float64, device=dev)
+    st.local_into(T, outd)
+    assert torch.isfinite(outd).all()
+    # false hint on a fresh handle
+    T2 = rccsd.SparseTensor4d.from_coo(flat, vals, (no, no, nv, nv))
+    _lib.check(_lib.lib().fricc_st_set_n_exact(T2._h, 0))
+    outd2 = torch.zeros(no, no, nv, nv, dtype=torch.float64, device=dev)
+    st.local_into(T2, outd2)
+    assert torch.isnan(outd2).any()
+    # duplicates behind a true-magnitude hint are caught as well
+    fdup = np.concatenate([flat[:50], flat[:1]])
+    vdup = np.full(51, 0.25)
+    T3 = rccsd.SparseTensor4d.from_coo(fdup, vdup, (no, no, nv, nv))
+    _lib.check(_lib.lib().fricc_st_set_n_exact(T3._h, 0))
+    outd3 = torch.zeros(no, no, nv, nv, dtype=torch.float64, device=dev)
+    st.local_into(T3, outd3)
+    assert torch.isnan(outd3).any()
