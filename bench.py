@@ -56,6 +56,9 @@ def parse_args():
     p.add_argument("--only-ladder", action="store_true", help="debug: time only the ladder launches")
     p.add_argument("--planes", type=int, default=6,
                    help="int8 digit planes of W for the tensor-core form of the contractions (0 = fp64 SpMM only)")
+    p.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
+                   help="N>1: how column slices reach the other ranks: stores into peer memory over NVLink (default) or "
+                        "NCCL all-gather of panels + accumulate")
     p.add_argument("--no-overlap", action="store_true", help="N>1: one blocking exchange per term (A/B of the pipelined step)")
     return p.parse_args()
 
@@ -198,11 +201,21 @@ class Iteration:
         # terms that read the same operand through the same (K, L) axes share one panel
         self.terms["0113"].set_panel(self.terms["0112"].panel, planes_from=self.terms["0112"])
         self.terms["0312"].set_panel(self.terms["0313"].panel, planes_from=self.terms["0313"])
-        self.Wklij = torch.zeros(o, o, o, o, device=device, dtype=torch.float64)
-        self.Wakic = torch.zeros(v, o, o, v, device=device, dtype=torch.float64)
-        self.Wakci = torch.zeros(v, o, v, o, device=device, dtype=torch.float64)
-        self.t2new = torch.zeros(o, o, v, v, device=device, dtype=torch.float64)
-        self.tmp = [torch.zeros(o, o, v, v, device=device, dtype=torch.float64) for _ in range(3)]
+        self.peer = comm.world > 1 and args.exchange == "peer" and not args.no_overlap and not args.only_ladder
+        if self.peer:
+            # the outputs live in one symmetric allocation per rank: every rank stores its columns into all copies
+            nb = 8 * (o ** 4 + 2 * v * o * o * v + 4 * o * o * v * v) + 8 * 4096
+            self.arena = fd.SymmArena(nb, comm, device)
+            mk = lambda *shape: self.arena.tensor(shape).zero_()
+        else:
+            self.arena = None
+            mk = lambda *shape: torch.zeros(*shape, device=device, dtype=torch.float64)
+        self.Wklij = mk(o, o, o, o)
+        self.Wakic = mk(v, o, o, v)
+        self.Wakci = mk(v, o, v, o)
+        self.t2new = mk(o, o, v, v)
+        self.tmp = [mk(o, o, v, v) for _ in range(3)]
+        self.flag = torch.zeros(1, device=device, dtype=torch.float32)
         # ---- the ladder operand: this rank's (a,b)-column slice of Wp[(c,d)][(a,b)], possibly in sub-shards
         lad = self.terms["2323"]
         max_cols = max(1, int(args.max_panel_gb * 1e9 / (8 * lad.nK)))
@@ -276,7 +289,7 @@ class Iteration:
             else:
                 if lad.planes is not None and lad._planes_lcnt == w and lad.use_tc(T):
                     self.fd.check(L.fricc_contract_panel_tc(lad.planes, self.fd._ptr(self.lad_panel), w, lad.l0 + c, T._h,
-                                                            ctypes_ptr(lad.out_panel, c), lad.lc, b"2323"))
+                                                            ctypes_ptr(lad.out_panel, c), lad.lc, b"2323", 0))
                 else:
                     self.fd.check(L.fricc_contract_panel(self.fd._ptr(self.lad_panel), w, lad.l0 + c, w, T._h,
                                                          ctypes_ptr(lad.out_panel, c), lad.lc, b"2323"))
@@ -306,6 +319,8 @@ class Iteration:
             T = self.compress(t2)
             T_alt = self.compress(t2)
         self.mark("compress_x2")
+        if self.peer:
+            return self.step_peer(T, T_alt, timer)
         if self.comm.world > 1 and not self.args.only_ladder and not self.args.no_overlap:
             return self.step_pipelined(T, T_alt, timer)
         tm = self.terms
@@ -340,6 +355,66 @@ class Iteration:
             self.mark("1303")
             tm["1203"](T, self.tmp[2])
             self.mark("1203")
+        return T
+
+    def rank_barrier(self):
+        """Stream-ordered barrier (a 4-byte NCCL all-reduce): everything every rank queued before it -- including its
+        stores into this rank's memory -- has completed when the work queued behind it starts.  Does not block the host."""
+        import torch.distributed as dist
+
+        dist.all_reduce(self.flag, group=self.comm.group)
+
+    def step_peer(self, T, T_alt, timer=None):
+        """N > 1, exchange over peer memory: every term accumulates its L-columns straight into this rank's copy of the
+        4-D output and the finished columns are stored into every peer's copy over NVLink (fricc_peer.cu) -- no panels,
+        no all-gather, no re-accumulation pass.  Three barriers order consumers behind writers:
+          B0 after the outputs are zeroed (a peer must not zero what was already pushed to it),
+          B1 before Woooo / Wvoov / Wvovo are read as operands and before 0101 (column axis (i,j)) accumulates onto the
+             ladder's t2new (column axis (a,b)): an output must be complete everywhere before a term with a different
+             column axis adds to it,
+          B2 at the end of the step."""
+        tm, dims, push = self.terms, (self.o, self.o, self.v, self.v), self.fd.push_columns
+        self.Wklij.zero_(); self.Wakic.zero_(); self.Wakci.zero_()
+        self.t2new.zero_()
+        for t in self.tmp:
+            t.zero_()
+        self.rank_barrier()
+        self.mark("zero_outputs_B0")
+        A = self.arena
+        tm["1323"].accumulate(T_alt, self.Wklij, arena=A)
+        self.mark("1323")
+        tm["0112"].accumulate(T_alt, self.Wakic, also=(tm["0313"], tm["0113"]), arena=A)
+        self.mark("0112_0313_0113")
+        tm["0312"].accumulate(T_alt, self.Wakci, arena=A)
+        self.mark("0312")
+        lad = tm["2323"]
+        for s_, (c, w) in enumerate(self.sub):
+            if not self.resident:
+                if timer:
+                    timer.pause()
+                self.fill_ladder_panel(s_)
+                if timer:
+                    timer.resume()
+            e0, e1 = self.torch.cuda.Event(enable_timing=True), self.torch.cuda.Event(enable_timing=True)
+            e0.record()
+            lad.local_into(T, self.t2new, panel=self.lad_panel, l0=lad.l0 + c, lcnt=w)
+            e1.record()
+            self.ladder_events.append((e0, e1, w))
+        push(lad, dims, self.t2new, A)
+        self.mark("2323" if self.resident else "2323_incl_regen")
+        self.rank_barrier()
+        self.mark("B1")
+        tm["0101"].permute_from(self.Wklij); tm["0101"].accumulate(T, self.t2new, arena=A)
+        self.mark("0101")
+        tm["1302"].permute_from(self.Wakic); tm["1202"].permute_from(self.Wakci)
+        tm["1302"].accumulate(T, self.tmp[0], also=(tm["1202"],), arena=A)
+        self.mark("1302_1202")
+        tm["1303"].set_panel(tm["1302"].panel, planes_from=tm["1302"]); tm["1303"].accumulate(T, self.tmp[1], arena=A)
+        self.mark("1303")
+        tm["1203"].set_panel(tm["1202"].panel, planes_from=tm["1202"]); tm["1203"].accumulate(T, self.tmp[2], arena=A)
+        self.mark("1203")
+        self.rank_barrier()
+        self.mark("B2")
         return T
 
     def step_pipelined(self, T, T_alt, timer=None):
@@ -641,8 +716,10 @@ def run_b200_arm(args):
             "roofline": roof,
             "clocks": clocks, "gpu_launches": int(launches),
             "ladder_ms_per_step": sum(lad_ms) / args.steps, "stage_ms_per_step": stage_ms, "output_checksums": checks,
-            "schedule": ("blocking exchange per term" if (world == 1 or args.no_overlap) else
-                         "pipelined: NCCL all-gathers overlap the next term's SpMM; 7 exchanges for 11 terms"),
+            "schedule": ("single rank" if world == 1 else "blocking NCCL exchange per term" if args.no_overlap else
+                         "peer memory: each rank accumulates its columns in place and stores them into every peer's copy "
+                         "over NVLink; 3 stream-ordered barriers per step, no NCCL on the data path" if it.peer else
+                         "pipelined: NCCL all-gathers overlap the next term's kernel; 7 exchanges for 11 terms"),
             "timed_segments": "whole steps" if it.resident else
                               f"sum of segments; ladder W regenerated in HBM between {len(it.sub)} column sub-shards",
         }

@@ -83,9 +83,18 @@ SIGNATURES = {
     "fricc_wslices_bytes": (c_int, [c_void_p, _i64p]),
     "fricc_wslices_reconstruct": (c_int, [c_void_p, c_void_p]),
     "fricc_st_sign_fraction": (c_int, [c_void_p, c_char_p, _f64p]),
-    "fricc_contract_panel_tc": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_int64, c_char_p]),
+    "fricc_contract_panel_tc": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_int64, c_char_p,
+                                        c_int]),
     "fricc_contract_panel_into_tc": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p, _i64p, _i64p,
                                              c_char_p]),
+    "fricc_symm_alloc": (c_int, [c_int64, POINTER(c_void_p), c_void_p]),
+    "fricc_symm_open": (c_int, [c_void_p, POINTER(c_void_p)]),
+    "fricc_symm_close": (c_int, [c_void_p]),
+    "fricc_symm_free": (c_int, [c_void_p]),
+    "fricc_push_columns": (c_int, [c_void_p, POINTER(c_void_p), c_int, c_int, c_char_p, _i64p, _i64p, _i64p, c_int64,
+                                   c_int64]),
+    "fricc_scatter_panel": (c_int, [c_void_p, c_int64, c_int64, c_int64, c_char_p, _i64p, c_void_p, POINTER(c_void_p),
+                                    c_int, c_int, _i64p, _i64p]),
     "fricc_permute_w": (c_int, [c_void_p, c_int, _i64p, _i64p, c_char_p, c_int64, c_int64, c_void_p]),
     "fricc_one_norm": (c_int, [c_void_p, c_int, c_int64, _f64p]),
     "fricc_argsort": (c_int, [c_void_p, c_int, c_int64, c_int64, c_void_p]),

@@ -135,6 +135,7 @@ int fricc_set_option(const char* key, int value) {
   else if (key && strcmp(key, "pivotal_parallel") == 0) set_pivotal_parallel(value);
   else if (key && strcmp(key, "d_parallel") == 0) set_d_parallel(value);
   else if (key && strncmp(key, "spmm_", 5) == 0) set_spmm_option(key, value);
+  else if (key && strncmp(key, "tc_", 3) == 0) set_tc_option(key, value);
   else fail(FRICC_EINVAL, "unknown option '%s'", key ? key : "(null)");
   FRICC_API_END
 }
@@ -530,7 +531,7 @@ static void contract_tc_common(fricc_wslices_t h, const double* Wp_dev, int64_t 
 }
 
 int fricc_contract_panel_tc(fricc_wslices_t h, const double* Wp_dev, int64_t ldw, int64_t l_begin, fricc_st_t T,
-                            double* out_panel_dev, int64_t ld_out, const char* term) {
+                            double* out_panel_dev, int64_t ld_out, const char* term, int overwrite) {
   FRICC_API_BEGIN
   check_handle(T);
   const TermSpec* ts = find_term(term);
@@ -538,7 +539,26 @@ int fricc_contract_panel_tc(fricc_wslices_t h, const double* Wp_dev, int64_t ldw
   if (!h || !Wp_dev || !out_panel_dev || ldw < h->ws.l_count || ld_out < h->ws.l_count) fail(FRICC_EINVAL, "bad arguments");
   OutMap om;
   om.nR2 = 1; om.nL2 = 1; om.sR1 = ld_out; om.sR2 = 0; om.sL1 = 1; om.sL2 = 0;
-  contract_tc_common(h, Wp_dev, ldw, l_begin, T, out_panel_dev - l_begin, om, ts);
+  const int64_t nR = T->dims[ts->tR[0]] * T->dims[ts->tR[1]];
+  bool ow = overwrite != 0;
+  if (ow) {
+    // "out = result": the tensor-core kernel writes every element of the panel columns without reading them.  When it
+    // will not run (no entries, or nothing in the sign matrix) the columns are cleared here instead.
+    bool gemm_runs = false;
+    if (T->nnz > 0 && h->ws.l_count > 0) {
+      Layout& lay = get_layout(T, *ts, false);
+      dense_form(T, *ts, lay);
+      gemm_runs = lay.n_rest != T->nnz;
+    }
+    if (!gemm_runs) {
+      if (h->ws.l_count > 0 && nR > 0)
+        FRICC_CUDA(cudaMemset2DAsync(out_panel_dev, (size_t)ld_out * 8, 0, (size_t)h->ws.l_count * 8, (size_t)nR, stream()));
+      ow = false;
+    }
+  }
+  if (T->nnz == 0 || h->ws.l_count == 0) return FRICC_OK;
+  Layout& lay = get_layout(T, *ts, false);
+  contract_dense(T, *ts, lay, h->ws, Wp_dev, ldw, l_begin, out_panel_dev - l_begin, om, ts->scale, ow);
   FRICC_API_END
 }
 

@@ -34,7 +34,8 @@ constexpr int TC_BM = 128;       // rows of the sign matrix per CTA (= TMEM lane
 constexpr int TC_BN = 64;        // output columns per CTA
 constexpr int TC_BK = 128;       // contracted indices per pipeline stage = one 128-byte swizzle atom of int8
 constexpr int TC_UMMA_K = 32;    // K of one tcgen05.mma.kind::i8
-constexpr int TC_THREADS = 192;  // warp 0 TMA, warp 1 MMA + TMEM allocation, warps 2..5 epilogue
+constexpr int TC_EPI_WARPS = 8;
+constexpr int TC_THREADS = 64 + 32 * TC_EPI_WARPS;  // warp 0 TMA, warp 1 MMA + TMEM allocation, warps 2..9 epilogue
 constexpr uint32_t TC_A_BYTES = TC_BM * TC_BK;      // 16 KB
 constexpr uint32_t TC_B_PLANE_BYTES = TC_BN * TC_BK;  // 8 KB per plane
 constexpr uint32_t TC_TMEM_COLS = 512;
@@ -52,6 +53,9 @@ __device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarr
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
   uint32_t ok;
@@ -482,12 +486,14 @@ double dense_form(fricc_st* T, const TermSpec& ts, Layout& lay) {
 struct TcParams {
   int64_t nR, l_begin, l_count;
   int S, stages, nkb;
+  int m_tiles, n_tiles;
   const double* colscale;  // [n_tiles*64]  2^(e_l - 7)
   const int32_t* rowsum;   // [Mpad]
   const double* cmag;      // [1]
   double scale;
   double* out;
   OutMap om;
+  int beta;  // 1: out += result (read-modify-write); 0: out = result (the caller knows out holds nothing yet)
 };
 
 __global__ void __launch_bounds__(TC_THREADS, 1)
@@ -499,9 +505,12 @@ tc_sign_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + (size_t)stages * stage_bytes);
   uint64_t* empty = full + stages;
   uint64_t* tmem_full = empty + stages;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+  uint64_t* tmem_empty = tmem_full + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 1);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int m_tile = blockIdx.x, n_tile = blockIdx.y;
+  // persistent: CTA b works on tiles b, b + gridDim.x, ...; consecutive tile numbers share the column tile (n) and
+  // differ in the row tile (m), so the CTAs running at the same time read the same planes of W through L2
+  const int64_t total_tiles = (int64_t)p.m_tiles * p.n_tiles;
 
   if (threadIdx.x == 0) {
     ptx::prefetch_tensormap(&tmA);
@@ -514,6 +523,7 @@ tc_sign_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         ptx::mbar_init(&empty[s], 1);
       }
       ptx::mbar_init(tmem_full, 1);
+      ptx::mbar_init(tmem_empty, TC_EPI_WARPS);
       ptx::fence_barrier_init();
     }
     __syncwarp();
@@ -525,17 +535,22 @@ tc_sign_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    // ===== TMA producer =====
+    // ===== TMA producer: runs ahead into the next tile while the epilogue drains the current one =====
     if (lane == 0) {
-      for (int kb = 0; kb < p.nkb; kb++) {
-        const int st = kb % stages, it = kb / stages;
-        if (it > 0) ptx::mbar_wait(&empty[st], (uint32_t)((it - 1) & 1));
-        uint8_t* a_dst = smem + (size_t)st * stage_bytes;
-        uint8_t* b_dst = a_dst + TC_A_BYTES;
-        ptx::mbar_expect_tx(&full[st], stage_bytes);
-        ptx::tma_load_2d(a_dst, &tmA, &full[st], kb * TC_BK, m_tile * TC_BM);
-        for (int s = 0; s < S; s++)
-          ptx::tma_load_2d(b_dst + (size_t)s * TC_B_PLANE_BYTES, &tmB, &full[st], kb * TC_BK, (n_tile * S + s) * TC_BN);
+      int64_t gk = 0;
+      for (int64_t t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        const int m_tile = (int)(t % p.m_tiles), n_tile = (int)(t / p.m_tiles);
+        for (int kb = 0; kb < p.nkb; kb++, gk++) {
+          const int st = (int)(gk % stages);
+          const int64_t it = gk / stages;
+          if (it > 0) ptx::mbar_wait(&empty[st], (uint32_t)((it - 1) & 1));
+          uint8_t* a_dst = smem + (size_t)st * stage_bytes;
+          uint8_t* b_dst = a_dst + TC_A_BYTES;
+          ptx::mbar_expect_tx(&full[st], stage_bytes);
+          ptx::tma_load_2d(a_dst, &tmA, &full[st], kb * TC_BK, m_tile * TC_BM);
+          for (int s = 0; s < S; s++)
+            ptx::tma_load_2d(b_dst + (size_t)s * TC_B_PLANE_BYTES, &tmB, &full[st], kb * TC_BK, (n_tile * S + s) * TC_BN);
+        }
       }
     }
     __syncwarp();
@@ -544,65 +559,131 @@ tc_sign_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     if (lane == 0) {
       const int n1 = min(S, 4) * TC_BN, n2 = (S - min(S, 4)) * TC_BN;  // planes 0..3 | planes 4..S-1
       const uint32_t idesc1 = umma_idesc_i8(TC_BM, n1), idesc2 = umma_idesc_i8(TC_BM, n2 > 0 ? n2 : 16);
-      for (int kb = 0; kb < p.nkb; kb++) {
-        const int st = kb % stages, it = kb / stages;
-        ptx::mbar_wait(&full[st], (uint32_t)(it & 1));
-        ptx::tc_fence_after();
-        const uint32_t a_addr = ptx::smem_u32(smem + (size_t)st * stage_bytes);
-        const uint32_t b_addr = a_addr + TC_A_BYTES;
-#pragma unroll
-        for (int k = 0; k < TC_BK / TC_UMMA_K; k++) {
-          const uint32_t acc = (kb | k) != 0 ? 1u : 0u;
-          const uint64_t adesc = umma_desc_sw128(a_addr + k * TC_UMMA_K);
-          ptx::mma_i8(tmem_base, adesc, umma_desc_sw128(b_addr + k * TC_UMMA_K), idesc1, acc);
-          if (n2 > 0)
-            ptx::mma_i8(tmem_base + 256, adesc, umma_desc_sw128(b_addr + 4 * TC_B_PLANE_BYTES + k * TC_UMMA_K), idesc2, acc);
+      int64_t gk = 0;
+      uint32_t tl = 0;
+      for (int64_t t = blockIdx.x; t < total_tiles; t += gridDim.x, tl++) {
+        if (tl > 0) {  // the epilogue must have read the previous tile's accumulators out of TMEM
+          ptx::mbar_wait(tmem_empty, (tl - 1) & 1);
+          ptx::tc_fence_after();
         }
-        ptx::mma_commit(&empty[st]);  // the stage may be refilled once these MMAs have read it
+        for (int kb = 0; kb < p.nkb; kb++, gk++) {
+          const int st = (int)(gk % stages);
+          const int64_t it = gk / stages;
+          ptx::mbar_wait(&full[st], (uint32_t)(it & 1));
+          ptx::tc_fence_after();
+          const uint32_t a_addr = ptx::smem_u32(smem + (size_t)st * stage_bytes);
+          const uint32_t b_addr = a_addr + TC_A_BYTES;
+#pragma unroll
+          for (int k = 0; k < TC_BK / TC_UMMA_K; k++) {
+            const uint32_t acc = (kb | k) != 0 ? 1u : 0u;
+            const uint64_t adesc = umma_desc_sw128(a_addr + k * TC_UMMA_K);
+            ptx::mma_i8(tmem_base, adesc, umma_desc_sw128(b_addr + k * TC_UMMA_K), idesc1, acc);
+            if (n2 > 0)
+              ptx::mma_i8(tmem_base + 256, adesc, umma_desc_sw128(b_addr + 4 * TC_B_PLANE_BYTES + k * TC_UMMA_K), idesc2, acc);
+          }
+          ptx::mma_commit(&empty[st]);  // the stage may be refilled once these MMAs have read it
+        }
+        ptx::mma_commit(tmem_full);
       }
-      ptx::mma_commit(tmem_full);
     }
     __syncwarp();
   } else {
-    // ===== epilogue: TMEM -> fp64 recombination of the planes -> out =====
-    const int q = warp & 3;  // the TMEM lane quarter this warp may access
-    const int64_t R = (int64_t)m_tile * TC_BM + q * 32 + lane;
-    ptx::mbar_wait(tmem_full, 0);
-    ptx::tc_fence_after();
+    // ===== epilogue (8 warps): TMEM -> fp64 recombination of the planes -> out =====
+    const int q = warp & 3;                // the TMEM lane quarter this warp may access
+    const int half = (warp - 2) >> 2;      // two warps per quarter: column chunks 0..3 | 4..7
     const double coef = p.scale * p.cmag[0];
-    const bool row_ok = R < p.nR;
-    int64_t rbase = 0;
-    if (row_ok) {
-      const int64_t r1 = R / p.om.nR2, r2 = R - r1 * p.om.nR2;
-      rbase = r1 * p.om.sR1 + r2 * p.om.sR2;
-    }
     const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
-    const int off0 = 128 * p.rowsum[(int64_t)m_tile * TC_BM + q * 32 + lane];  // the 2^e_l offset, in units of plane 0
-    // first column of this tile, split into the (major, minor) pair of the free index
-    int64_t l = p.l_begin + (int64_t)n_tile * TC_BN;
-    int64_t l1 = l / p.om.nL2, l2 = l - l1 * p.om.nL2;
-    const int ncol = (int)min((int64_t)TC_BN, p.l_count - (int64_t)n_tile * TC_BN);
-    for (int j = 0; j < TC_BN / 8; j++) {
-      int32_t r[TC_MAX_SLICES][8];
-#pragma unroll
-      for (int s = 0; s < TC_MAX_SLICES; s++)
-        if (s < S) ptx::tmem_ld_x8(lane_addr + (uint32_t)(s * TC_BN + j * 8), r[s]);
-      ptx::tmem_ld_wait();
-      double cs[8];
-#pragma unroll
-      for (int i = 0; i < 8; i++) cs[i] = (j * 8 + i < ncol) ? p.colscale[n_tile * TC_BN + j * 8 + i] : 0.0;
-#pragma unroll
-      for (int i = 0; i < 8; i++) {
-        double v = 0.0;
-#pragma unroll
-        for (int s = TC_MAX_SLICES - 1; s >= 1; s--)
-          if (s < S) v = (v + (double)r[s][i]) * 0.00390625;
-        v += (double)(r[0][i] - off0);
-        if (row_ok && j * 8 + i < ncol) {
-          double* o = p.out + rbase + l1 * p.om.sL1 + l2 * p.om.sL2;
-          *o += coef * cs[i] * v;
+    uint32_t tl = 0;
+    for (int64_t t = blockIdx.x; t < total_tiles; t += gridDim.x, tl++) {
+      const int m_tile = (int)(t % p.m_tiles), n_tile = (int)(t / p.m_tiles);
+      const int64_t R = (int64_t)m_tile * TC_BM + q * 32 + lane;
+      const bool row_ok = R < p.nR;
+      int64_t rbase = 0;
+      if (row_ok) {
+        const int64_t r1 = R / p.om.nR2, r2 = R - r1 * p.om.nR2;
+        rbase = r1 * p.om.sR1 + r2 * p.om.sR2;
+      }
+      // first column of this warp's half of the tile, split into the (major, minor) pair of the free index
+      const int c_first = half * (TC_BN / 2);
+      const int64_t l_first = p.l_begin + (int64_t)n_tile * TC_BN + c_first;
+      int64_t l1 = l_first / p.om.nL2, l2 = l_first - l1 * p.om.nL2;
+      const int ncol = (int)min((int64_t)TC_BN, p.l_count - (int64_t)n_tile * TC_BN);
+      if (p.beta && row_ok) {
+        // read-modify-write: pull this thread's output elements towards L2 while the main loop runs
+        int64_t a1 = l1, a2 = l2;
+        for (int c = c_first; c < min(ncol, c_first + TC_BN / 2); c++) {
+          if (p.om.sL2 != 1 || (c & 3) == 0)
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(p.out + rbase + a1 * p.om.sL1 + a2 * p.om.sL2));
+          if (++a2 == p.om.nL2) { a2 = 0; a1++; }
         }
-        if (++l2 == p.om.nL2) { l2 = 0; l1++; }
+      }
+      const int off0 = 128 * p.rowsum[(int64_t)m_tile * TC_BM + q * 32 + lane];  // the 2^e_l offset, units of plane 0
+      ptx::mbar_wait(tmem_full, tl & 1);
+      ptx::tc_fence_after();
+      for (int j = half * 4; j < half * 4 + 4; j++) {
+        int32_t r[TC_MAX_SLICES][8];
+#pragma unroll
+        for (int s = 0; s < TC_MAX_SLICES; s++)
+          if (s < S) ptx::tmem_ld_x8(lane_addr + (uint32_t)(s * TC_BN + j * 8), r[s]);
+        ptx::tmem_ld_wait();
+        if (j == half * 4 + 3) {
+          // last read of this tile's accumulators by this warp: hand TMEM back to the MMA issuer
+          ptx::tc_fence_before();
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(tmem_empty);
+        }
+        double v[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+          double tt = 0.0;
+#pragma unroll
+          for (int s = TC_MAX_SLICES - 1; s >= 1; s--)
+            if (s < S) tt = (tt + (double)r[s][i]) * 0.00390625;
+          tt += (double)(r[0][i] - off0);
+          const double cs = (j * 8 + i < ncol) ? p.colscale[n_tile * TC_BN + j * 8 + i] : 0.0;
+          v[i] = coef * cs * tt;
+        }
+        double* o8 = p.out + rbase + l1 * p.om.sL1 + l2 * p.om.sL2;
+        const bool contiguous = p.om.sL2 == 1 && l2 + 8 <= p.om.nL2 && j * 8 + 8 <= ncol &&
+                                (reinterpret_cast<uintptr_t>(o8) & 15) == 0;
+        if (contiguous) {
+          if (row_ok) {
+            double2* o2 = reinterpret_cast<double2*>(o8);
+            if (p.beta) {
+              double2 old[4];
+#pragma unroll
+              for (int i = 0; i < 4; i++) old[i] = o2[i];
+#pragma unroll
+              for (int i = 0; i < 4; i++) o2[i] = make_double2(old[i].x + v[2 * i], old[i].y + v[2 * i + 1]);
+            } else {
+#pragma unroll
+              for (int i = 0; i < 4; i++) o2[i] = make_double2(v[2 * i], v[2 * i + 1]);
+            }
+          }
+          l2 += 8;
+          if (l2 == p.om.nL2) { l2 = 0; l1++; }
+        } else {
+          double* oe[8];
+#pragma unroll
+          for (int i = 0; i < 8; i++) {
+            oe[i] = p.out + rbase + l1 * p.om.sL1 + l2 * p.om.sL2;
+            if (++l2 == p.om.nL2) { l2 = 0; l1++; }
+          }
+          if (row_ok) {
+            if (p.beta) {
+              double old[8];
+#pragma unroll
+              for (int i = 0; i < 8; i++) old[i] = (j * 8 + i < ncol) ? *oe[i] : 0.0;
+#pragma unroll
+              for (int i = 0; i < 8; i++)
+                if (j * 8 + i < ncol) *oe[i] = old[i] + v[i];
+            } else {
+#pragma unroll
+              for (int i = 0; i < 8; i++)
+                if (j * 8 + i < ncol) *oe[i] = v[i];
+            }
+          }
+        }
       }
     }
   }
@@ -647,8 +728,13 @@ static CUtensorMap make_map_i8(const int8_t* base, int64_t rows, int64_t Kpad, i
   return tm;
 }
 
+static int g_tc_persistent = 1;  // "tc_persistent" option: 1 = one CTA per SM looping over tiles, 0 = one CTA per tile
+void set_tc_option(const char* key, int value) {
+  if (strcmp(key, "tc_persistent") == 0) g_tc_persistent = value;
+}
+
 void contract_dense(fricc_st* T, const TermSpec& ts, Layout& lay, const WSlices& ws, const double* Wp, int64_t ldw,
-                    int64_t l_begin, double* out, const OutMap& om, double scale) {
+                    int64_t l_begin, double* out, const OutMap& om, double scale, bool overwrite) {
   if (ws.nK != lay.nK) fail(FRICC_EINVAL, "digit planes were built for %lld contracted indices, the term has %lld",
                             (long long)ws.nK, (long long)lay.nK);
   dense_form(T, ts, lay);
@@ -657,7 +743,7 @@ void contract_dense(fricc_st* T, const TermSpec& ts, Layout& lay, const WSlices&
     const uint32_t stage_bytes = TC_A_BYTES + (uint32_t)S * TC_B_PLANE_BYTES;
     int stages = (int)std::min<uint32_t>(6, (220u * 1024u) / stage_bytes);
     if (stages < 2) fail(FRICC_EINVAL, "too many digit planes for the shared-memory pipeline");
-    const size_t smem = (size_t)stages * stage_bytes + 1024 + 256;
+    const size_t smem = (size_t)stages * stage_bytes + 1024 + 256;  // tiles + alignment slack + barriers
     static size_t attr_smem = 0;
     if (smem > attr_smem) {
       FRICC_CUDA(cudaFuncSetAttribute(tc_sign_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
@@ -668,9 +754,11 @@ void contract_dense(fricc_st* T, const TermSpec& ts, Layout& lay, const WSlices&
     TcParams p;
     p.nR = lay.nR; p.l_begin = l_begin; p.l_count = ws.l_count;
     p.S = S; p.stages = stages; p.nkb = (int)(lay.Kpad / TC_BK);
-    p.colscale = ws.colscale.p; p.rowsum = lay.rowsum.p; p.cmag = lay.cmag.p; p.scale = scale; p.out = out; p.om = om;
-    if (ws.n_tiles > 65535) fail(FRICC_EINVAL, "free pair too large for the tensor-core grid");
-    dim3 grid((unsigned)(lay.Mpad / TC_BM), (unsigned)ws.n_tiles);
+    p.colscale = ws.colscale.p; p.rowsum = lay.rowsum.p; p.cmag = lay.cmag.p; p.scale = scale; p.out = out; p.om = om; p.beta = overwrite ? 0 : 1;
+    p.m_tiles = (int)(lay.Mpad / TC_BM);
+    p.n_tiles = (int)ws.n_tiles;
+    const int64_t total = (int64_t)p.m_tiles * p.n_tiles;
+    const unsigned grid = (unsigned)(g_tc_persistent ? std::min<int64_t>(total, num_sms()) : total);
     FRICC_LAUNCH(tc_sign_gemm_kernel, grid, TC_THREADS, smem, tmA, tmB, p);
   }
   if (lay.n_rest != 0)

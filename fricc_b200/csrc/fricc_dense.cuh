@@ -29,7 +29,9 @@ double dense_form(fricc_st* T, const TermSpec& ts, Layout& lay);
 // sign matrix x digit slices on the int8 tensor cores (tcgen05.mma.kind::i8, exact int32 accumulation), the remainder
 // through the fp64 SpMM on Wp_dev.
 void contract_dense(fricc_st* T, const TermSpec& ts, Layout& lay, const WSlices& ws, const double* Wp_dev, int64_t ldw,
-                    int64_t l_begin, double* out_dev, const OutMap& om, double scale);
+                    int64_t l_begin, double* out_dev, const OutMap& om, double scale, bool overwrite = false);
+
+void set_tc_option(const char* key, int value);
 
 // CSR SpMM on raw arrays (fricc_contract.cu)
 void spmm_csr(const int64_t* rowptr, const uint32_t* kidx, const double* vals, int64_t nR, const double* Wp_dev,

@@ -1,0 +1,275 @@
+// fricc_peer.cu -- the exchange step of the sharded contractions over NVLink peer memory (no NCCL on the data path).
+//
+// Every rank owns the L-columns [l_begin, l_begin + l_count) of each contraction output and every rank needs the full
+// output afterwards (the next contraction reads it as W, the next compression reads all of t2new).  Instead of
+// all-gathering column panels and re-adding them into the 4-D array (one NCCL launch + a 6 GB read-modify-write pass per
+// output), each rank accumulates its columns straight into ITS copy of the 4-D output and then pushes exactly those
+// elements into the same addresses of every peer's copy with plain stores over NVLink / NVSwitch: the copies live in
+// one symmetric allocation per rank (cudaMalloc + CUDA IPC), so "the same element on peer p" is base_p + offset.
+// A column is written by its owner only, so no two ranks ever store to the same address; consumers are ordered behind
+// the writers by a stream-ordered barrier (fricc_b200/dist.py).
+#include "fricc_contract.cuh"
+
+namespace fricc {
+
+constexpr int MAX_PEERS = 16;
+
+struct PeerPtrs {
+  double* p[MAX_PEERS];
+};
+
+// thread <-> one element of this rank's column slice; FAST = which index runs along threadIdx.x:
+//   0: l (the free pair; contiguous when out's unit-stride axis is the L-minor one)      1: R (owner pair)
+template <int FAST>
+__global__ void __launch_bounds__(256)
+push_columns_kernel(const double* __restrict__ src, PeerPtrs peers, int n_peers, int self, OutMap om, int64_t nR,
+                    int64_t l_begin, int64_t l_count) {
+  int64_t R, c;
+  if (FAST == 0) {
+    c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    R = blockIdx.y;
+  } else {
+    R = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    c = blockIdx.y;
+  }
+  if (R >= nR || c >= l_count) return;
+  const int64_t l = l_begin + c;
+  const int64_t r1 = R / om.nR2, r2 = R - r1 * om.nR2;
+  const int64_t l1 = l / om.nL2, l2 = l - l1 * om.nL2;
+  const int64_t o = r1 * om.sR1 + r2 * om.sR2 + l1 * om.sL1 + l2 * om.sL2;
+  const double v = src[o];
+  for (int d = 1; d < n_peers; d++) {
+    int q = self + d;
+    if (q >= n_peers) q -= n_peers;
+    peers.p[q][o] = v;
+  }
+}
+
+void push_columns(const double* out_local, double* const* peer_out, int n_peers, int self, const OutMap& om, int64_t nR,
+                  int64_t l_begin, int64_t l_count) {
+  if (n_peers <= 1 || nR == 0 || l_count == 0) return;
+  if (n_peers > MAX_PEERS) fail(FRICC_EINVAL, "at most %d peers", MAX_PEERS);
+  PeerPtrs pp;
+  for (int q = 0; q < MAX_PEERS; q++) pp.p[q] = q < n_peers ? peer_out[q] : nullptr;
+  const bool r_fast = om.sL2 != 1 && (om.sR2 == 1 || (om.nR2 == 1 && om.sR1 == 1));
+  if (!r_fast) {
+    if (nR > 65535) {
+      // many rows, few columns per row would waste the grid's y limit: fall through to the R-fast shape
+      dim3 grid((unsigned)ceil_div(nR, 256), (unsigned)l_count);
+      if (l_count > 65535) fail(FRICC_EINVAL, "push_columns: shape too large");
+      FRICC_LAUNCH(push_columns_kernel<1>, grid, 256, 0, out_local, pp, n_peers, self, om, nR, l_begin, l_count);
+      return;
+    }
+    dim3 grid((unsigned)ceil_div(l_count, 256), (unsigned)nR);
+    FRICC_LAUNCH(push_columns_kernel<0>, grid, 256, 0, out_local, pp, n_peers, self, om, nR, l_begin, l_count);
+  } else {
+    if (l_count > 65535) fail(FRICC_EINVAL, "push_columns: shape too large");
+    dim3 grid((unsigned)ceil_div(nR, 256), (unsigned)l_count);
+    FRICC_LAUNCH(push_columns_kernel<1>, grid, 256, 0, out_local, pp, n_peers, self, om, nR, l_begin, l_count);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// panel -> 4-D output (+ peers), transposing.  For terms whose output's unit-stride axis is neither the L-minor nor
+// the R-minor index (out(i,j,a,b) with R = (b,j), L = (a,i): 1302 / 1202 / 1303, and 1203) a direct epilogue write is
+// one 32-byte sector per element.  There the kernels write a coalesced [R][ld] panel and this kernel moves it through a
+// 32x32 shared-memory tile: reads follow the panel's contiguous index l2, writes follow out's contiguous index X
+// (r1 or l1).  new = out_local + panel is stored locally AND into every peer's copy (plain stores over NVLink), so
+// the accumulate pass and the exchange are one pass.   XMODE 0: X = r1 (fixed r2, l1)   XMODE 2: X = l1 (fixed r1, r2)
+// ---------------------------------------------------------------------------------------------------------------
+template <int XMODE>
+__global__ void __launch_bounds__(256)
+scatter_panel_tiled_kernel(const double* __restrict__ panel, int64_t ld, int64_t l_begin, int64_t l_count, int64_t nR1,
+                           int64_t l1_first, int64_t n_l1, double* __restrict__ out, PeerPtrs peers, int n_peers,
+                           int self, OutMap om) {
+  __shared__ double tile[32][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int64_t fixed = blockIdx.x;
+  const int64_t x0 = (int64_t)blockIdx.y * 32, q0 = (int64_t)blockIdx.z * 32;  // q = l2
+  int64_t r1 = 0, r2 = 0, l1 = 0, nX;
+  if (XMODE == 0) { r2 = fixed % om.nR2; l1 = l1_first + fixed / om.nR2; nX = nR1; }
+  else { r2 = fixed % om.nR2; r1 = fixed / om.nR2; nX = n_l1; }
+  const int64_t l_end = l_begin + l_count;
+  for (int r = ty; r < 32; r += 8) {
+    const int64_t x = x0 + r, q = q0 + tx;
+    if (x < nX && q < om.nL2) {
+      int64_t R, l;
+      if (XMODE == 0) { R = x * om.nR2 + r2; l = l1 * om.nL2 + q; }
+      else { R = r1 * om.nR2 + r2; l = (l1_first + x) * om.nL2 + q; }
+      if (l >= l_begin && l < l_end) tile[r][tx] = panel[R * ld + (l - l_begin)];
+    }
+  }
+  __syncthreads();
+  for (int r = ty; r < 32; r += 8) {
+    const int64_t q = q0 + r, x = x0 + tx;
+    if (x < nX && q < om.nL2) {
+      int64_t l, o;
+      if (XMODE == 0) { l = l1 * om.nL2 + q; o = x * om.sR1 + r2 * om.sR2 + l1 * om.sL1 + q * om.sL2; }
+      else { l = (l1_first + x) * om.nL2 + q; o = r1 * om.sR1 + r2 * om.sR2 + (l1_first + x) * om.sL1 + q * om.sL2; }
+      if (l >= l_begin && l < l_end) {
+        const double v = out[o] + tile[tx][r];
+        out[o] = v;
+        for (int d = 1; d < n_peers; d++) {
+          int p = self + d;
+          if (p >= n_peers) p -= n_peers;
+          peers.p[p][o] = v;
+        }
+      }
+    }
+  }
+}
+
+__global__ void scatter_panel_kernel(const double* __restrict__ panel, int64_t ld, int64_t l_begin, int64_t l_count,
+                                     int64_t nR, double* __restrict__ out, PeerPtrs peers, int n_peers, int self,
+                                     OutMap om) {
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= nR * l_count) return;
+  const int64_t R = idx / l_count, c = idx - R * l_count;
+  const int64_t l = l_begin + c;
+  const int64_t r1 = R / om.nR2, r2 = R - r1 * om.nR2;
+  const int64_t l1 = l / om.nL2, l2 = l - l1 * om.nL2;
+  const int64_t o = r1 * om.sR1 + r2 * om.sR2 + l1 * om.sL1 + l2 * om.sL2;
+  const double v = out[o] + panel[R * ld + c];
+  out[o] = v;
+  for (int d = 1; d < n_peers; d++) {
+    int p = self + d;
+    if (p >= n_peers) p -= n_peers;
+    peers.p[p][o] = v;
+  }
+}
+
+void scatter_panel(const double* panel, int64_t ld, int64_t l_begin, int64_t l_count, int64_t nR, double* out,
+                   double* const* peer_out, int n_peers, int self, const OutMap& om) {
+  if (nR == 0 || l_count == 0) return;
+  if (n_peers > MAX_PEERS) fail(FRICC_EINVAL, "at most %d peers", MAX_PEERS);
+  PeerPtrs pp;
+  for (int q = 0; q < MAX_PEERS; q++) pp.p[q] = (peer_out && q < n_peers) ? peer_out[q] : nullptr;
+  if (!peer_out) { n_peers = 1; self = 0; }
+  const int64_t nR1 = nR / om.nR2;
+  const int64_t l1_first = l_begin / om.nL2, l1_last = (l_begin + l_count - 1) / om.nL2;
+  const int64_t n_l1 = l1_last - l1_first + 1;
+  int xmode = -1;
+  int64_t fixed = 0, nX = 0;
+  if (om.sL2 != 1) {
+    if (om.sR1 == 1) { xmode = 0; fixed = om.nR2 * n_l1; nX = nR1; }
+    else if (om.sL1 == 1) { xmode = 2; fixed = nR1 * om.nR2; nX = n_l1; }
+  }
+  if (xmode >= 0 && fixed > 0 && fixed < ((int64_t)1 << 31) && ceil_div(nX, 32) <= 65535 && ceil_div(om.nL2, 32) <= 65535) {
+    dim3 grid((unsigned)fixed, (unsigned)ceil_div(nX, 32), (unsigned)ceil_div(om.nL2, 32));
+    if (xmode == 0)
+      FRICC_LAUNCH(scatter_panel_tiled_kernel<0>, grid, 256, 0, panel, ld, l_begin, l_count, nR1, l1_first, n_l1, out, pp,
+                   n_peers, self, om);
+    else
+      FRICC_LAUNCH(scatter_panel_tiled_kernel<2>, grid, 256, 0, panel, ld, l_begin, l_count, nR1, l1_first, n_l1, out, pp,
+                   n_peers, self, om);
+    return;
+  }
+  FRICC_LAUNCH(scatter_panel_kernel, (unsigned)ceil_div(nR * l_count, 256), 256, 0, panel, ld, l_begin, l_count, nR, out,
+               pp, n_peers, self, om);
+}
+
+}  // namespace fricc
+
+using namespace fricc;
+
+extern "C" {
+
+int fricc_symm_alloc(int64_t bytes, void** ptr, void* handle64) {
+  FRICC_API_BEGIN
+  if (bytes <= 0 || !ptr || !handle64) fail(FRICC_EINVAL, "bad arguments");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  void* p = nullptr;
+  FRICC_CUDA(cudaMalloc(&p, (size_t)bytes));
+  cudaIpcMemHandle_t h;
+  cudaError_t e = cudaIpcGetMemHandle(&h, p);
+  if (e != cudaSuccess) {
+    cudaFree(p);
+    fail(FRICC_ECUDA, "cudaIpcGetMemHandle failed: %s", cudaGetErrorString(e));
+  }
+  memcpy(handle64, &h, 64);
+  *ptr = p;
+  FRICC_API_END
+}
+
+int fricc_symm_open(const void* handle64, void** ptr) {
+  FRICC_API_BEGIN
+  if (!handle64 || !ptr) fail(FRICC_EINVAL, "bad arguments");
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, 64);
+  void* p = nullptr;
+  FRICC_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+  *ptr = p;
+  FRICC_API_END
+}
+
+int fricc_symm_close(void* ptr) {
+  FRICC_API_BEGIN
+  if (ptr) FRICC_CUDA(cudaIpcCloseMemHandle(ptr));
+  FRICC_API_END
+}
+
+int fricc_symm_free(void* ptr) {
+  FRICC_API_BEGIN
+  if (ptr) FRICC_CUDA(cudaFree(ptr));
+  FRICC_API_END
+}
+
+int fricc_push_columns(const double* out_local_dev, void* const* peer_out_dev, int n_peers, int self, const char* term,
+                       const int64_t t_dims[4], const int64_t out_shape[4], const int64_t out_strides[4],
+                       int64_t l_begin, int64_t l_count) {
+  FRICC_API_BEGIN
+  const TermSpec* ts = find_term(term);
+  if (!ts) fail(FRICC_EINVAL, "CASE NOT IMPLEMENTED: unknown contraction term '%s'", term ? term : "(null)");
+  if (!out_local_dev || !peer_out_dev || !t_dims || !out_shape || !out_strides || n_peers < 1 || self < 0 ||
+      self >= n_peers || l_begin < 0 || l_count < 0)
+    fail(FRICC_EINVAL, "bad arguments");
+  for (int q = 0; q < 2; q++)
+    if (out_shape[ts->oR[q]] != t_dims[ts->tR[q]]) fail(FRICC_EINVAL, "term %s: out does not match T on the owner pair", ts->name);
+  const int64_t nL = out_shape[ts->oL[0]] * out_shape[ts->oL[1]];
+  if (l_begin + l_count > nL) fail(FRICC_EINVAL, "column range out of bounds");
+  OutMap om;
+  om.nR2 = t_dims[ts->tR[1]];
+  om.nL2 = out_shape[ts->oL[1]];
+  om.sR1 = out_strides[ts->oR[0]];
+  om.sR2 = out_strides[ts->oR[1]];
+  om.sL1 = out_strides[ts->oL[0]];
+  om.sL2 = out_strides[ts->oL[1]];
+  const int64_t nR = t_dims[ts->tR[0]] * t_dims[ts->tR[1]];
+  double* peers[MAX_PEERS];
+  if (n_peers > MAX_PEERS) fail(FRICC_EINVAL, "at most %d peers", MAX_PEERS);
+  for (int q = 0; q < n_peers; q++) peers[q] = static_cast<double*>(peer_out_dev[q]);
+  push_columns(out_local_dev, peers, n_peers, self, om, nR, l_begin, l_count);
+  FRICC_API_END
+}
+
+int fricc_scatter_panel(const double* panel_dev, int64_t ld, int64_t l_begin, int64_t l_count, const char* term,
+                        const int64_t t_dims[4], double* out_local_dev, void* const* peer_out_dev, int n_peers, int self,
+                        const int64_t out_shape[4], const int64_t out_strides[4]) {
+  FRICC_API_BEGIN
+  const TermSpec* ts = find_term(term);
+  if (!ts) fail(FRICC_EINVAL, "CASE NOT IMPLEMENTED: unknown contraction term '%s'", term ? term : "(null)");
+  if (!panel_dev || !out_local_dev || !t_dims || !out_shape || !out_strides || ld < l_count || l_begin < 0 || l_count < 0 ||
+      (peer_out_dev && (n_peers < 1 || self < 0 || self >= n_peers)))
+    fail(FRICC_EINVAL, "bad arguments");
+  for (int q = 0; q < 2; q++)
+    if (out_shape[ts->oR[q]] != t_dims[ts->tR[q]]) fail(FRICC_EINVAL, "term %s: out does not match T on the owner pair", ts->name);
+  const int64_t nL = out_shape[ts->oL[0]] * out_shape[ts->oL[1]];
+  if (l_begin + l_count > nL) fail(FRICC_EINVAL, "column range out of bounds");
+  OutMap om;
+  om.nR2 = t_dims[ts->tR[1]];
+  om.nL2 = out_shape[ts->oL[1]];
+  om.sR1 = out_strides[ts->oR[0]];
+  om.sR2 = out_strides[ts->oR[1]];
+  om.sL1 = out_strides[ts->oL[0]];
+  om.sL2 = out_strides[ts->oL[1]];
+  const int64_t nR = t_dims[ts->tR[0]] * t_dims[ts->tR[1]];
+  double* peers[MAX_PEERS];
+  if (peer_out_dev) {
+    if (n_peers > MAX_PEERS) fail(FRICC_EINVAL, "at most %d peers", MAX_PEERS);
+    for (int q = 0; q < n_peers; q++) peers[q] = static_cast<double*>(peer_out_dev[q]);
+  }
+  scatter_panel(panel_dev, ld, l_begin, l_count, nR, out_local_dev, peer_out_dev ? peers : nullptr, n_peers, self, om);
+  FRICC_API_END
+}
+
+}  // extern "C"

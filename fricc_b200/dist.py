@@ -79,6 +79,7 @@ class ShardedTerm:
         self.nK = self.w_shape[ax["wK"][0]] * self.w_shape[ax["wK"][1]]
         self.nL = self.w_shape[ax["wL"][0]] * self.w_shape[ax["wL"][1]]
         self.nR = self.out_shape[ax["oR"][0]] * self.out_shape[ax["oR"][1]]
+        self.t_dims = (o, o, v, v)
         self.l0, self.lcnt, self.lc = column_range(self.nL, comm.rank, comm.world)
         self.panel = None        # [nK][lcnt] W panel shard
         self.out_panel = None    # [nR][lc]
@@ -160,18 +161,21 @@ class ShardedTerm:
         """This rank's column slice of the output: out_panel[R][c] (+)= scale * sum_K T[R,K] * Wp[K][c].
         `into`: another ShardedTerm with the same (R, L) output mapping whose panel this term is ADDED to (terms that
         feed the same output share one exchange, e.g. 0112/0313/0113 -> Wvoov)."""
+        fresh = into is None
         if into is not None:
             assert (into.nR, into.lc, into.l0) == (self.nR, self.lc, self.l0)
             target = into.out_panel
         else:
             if self.out_panel is None:
                 self.out_panel = torch.empty(self.nR * self.lc, dtype=torch.float64, device=self.device)
-            self.out_panel.zero_()
             target = self.out_panel
+        tc = self.lcnt > 0 and self.use_tc(T)
+        if fresh and not (tc and self.lcnt == self.lc):
+            target.zero_()       # the tensor-core kernel overwrites its columns; everything else accumulates
         if self.lcnt > 0:
-            if self.use_tc(T):
+            if tc:
                 check(self.L.fricc_contract_panel_tc(self.planes, _ptr(self.panel), self.lcnt, self.l0, T._h,
-                                                     _ptr(target), self.lc, self.term.encode()))
+                                                     _ptr(target), self.lc, self.term.encode(), 1 if fresh else 0))
             else:
                 check(self.L.fricc_contract_panel(_ptr(self.panel), self.lcnt, self.l0, self.lcnt, T._h,
                                                   _ptr(target), self.lc, self.term.encode()))
@@ -217,11 +221,44 @@ class ShardedTerm:
                 check(self.L.fricc_contract_panel_into(_ptr(panel), lcnt, l0, lcnt, T._h, _ptr(out), i64x4(out.shape),
                                                        i64x4(out.stride()), self.term.encode()))
 
+    def direct_ok(self, out):
+        """Is a kernel epilogue writing straight into `out` coalesced?  (threads run over R-minor, each thread over 8
+        consecutive L-minor indices: one of the two must be out's unit-stride axis)"""
+        ax = TERM_AXES[self.term]
+        st = out.stride()
+        return st[ax["oL"][1]] == 1 or st[ax["oR"][1]] == 1
+
+    def accumulate(self, T, out, also=(), arena=None):
+        """out[.., this rank's L-columns, ..] += this term (+ the terms in `also`, which must map (R, L) onto `out` the
+        same way and use the same T).  With an arena (SymmArena holding `out` on every rank) the finished columns are
+        also stored into every peer's copy -- the exchange step.  Terms whose output's unit-stride axis is R-major /
+        L-major (1302, 1202, 1303, 1203 on a C-contiguous t2new) go through a coalesced [R][lc] panel and one
+        transposing scatter pass; the others write straight from the kernel's epilogue."""
+        terms = (self,) + tuple(also)
+        for t in terms:
+            assert (t.nR, t.lc, t.l0) == (self.nR, self.lc, self.l0)
+        peers = arena.peers_of(out) if (arena is not None and self.comm.world > 1) else None
+        if self.direct_ok(out):
+            for t in terms:
+                t.local_into(T, out)
+            if peers is not None and self.lcnt > 0:
+                check(self.L.fricc_push_columns(_ptr(out), peers, self.comm.world, self.comm.rank, self.term.encode(),
+                                                i64x4(self.t_dims), i64x4(out.shape), i64x4(out.stride()), self.l0,
+                                                self.lcnt))
+            return
+        self.local(T)
+        for t in also:
+            t.local(T, into=self)
+        if self.lcnt > 0:
+            check(self.L.fricc_scatter_panel(_ptr(self.out_panel), self.lc, self.l0, self.lcnt, self.term.encode(),
+                                             i64x4(self.t_dims), _ptr(out), peers, self.comm.world if peers else 1,
+                                             self.comm.rank if peers else 0, i64x4(out.shape), i64x4(out.stride())))
+
     def __call__(self, T, out, W=None):
         if W is not None:
             self.permute_from(W)
         if self.comm.world == 1:
-            self.local_into(T, out)
+            self.accumulate(T, out)
             return
         self.local(T)
         self.exchange_and_accumulate(T, out)
@@ -306,3 +343,76 @@ def compress_pair(t2, m, comm, compression="fri", sampling_method="systematic", 
         else:
             check(L.fricc_rand_skip(int(tail[1][1])))
     return pair[0], pair[1]
+
+
+class _CudaArray:
+    """Zero-copy view of a raw device pointer for torch.as_tensor (the __cuda_array_interface__ protocol)."""
+
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (int(ptr), False), "version": 2}
+
+
+class SymmArena:
+    """One symmetric device allocation per rank for the contraction outputs (fricc_peer.cu): `tensor(shape)` carves the
+    same region out of every rank's allocation (every rank must request the same shapes in the same order), and
+    `peers_of(t)` gives the addresses of that region in all ranks' copies, so a rank can store its L-columns of an output
+    straight into its peers' HBM over NVLink.  world == 1: a plain allocation, no handles."""
+
+    def __init__(self, nbytes, comm, device):
+        self.comm, self.device, self.L = comm, device, _lib.lib()
+        self.nbytes = int(nbytes)
+        self.base = ctypes.c_void_p()
+        handle = ctypes.create_string_buffer(64)
+        check(self.L.fricc_symm_alloc(self.nbytes, ctypes.byref(self.base), handle))
+        self.peer_base = [None] * comm.world
+        self.peer_base[comm.rank] = self.base.value
+        self._opened = []
+        if comm.world > 1:
+            import torch.distributed as dist
+
+            handles = [None] * comm.world
+            dist.all_gather_object(handles, bytes(handle.raw), group=comm.group)
+            for q, h in enumerate(handles):
+                if q == comm.rank:
+                    continue
+                p = ctypes.c_void_p()
+                check(self.L.fricc_symm_open(ctypes.create_string_buffer(h, 64), ctypes.byref(p)))
+                self.peer_base[q] = p.value
+                self._opened.append(p)
+        self._bytes = torch.as_tensor(_CudaArray(self.base.value, self.nbytes), device=device)
+        self._used = 0
+
+    def tensor(self, shape, dtype=torch.float64):
+        n = 1
+        for s in shape:
+            n *= int(s)
+        nbytes = n * torch.empty((), dtype=dtype).element_size()
+        off = (self._used + 255) // 256 * 256
+        if off + nbytes > self.nbytes:
+            raise MemoryError("SymmArena exhausted")
+        self._used = off + nbytes
+        return self._bytes[off: off + nbytes].view(dtype).view(*shape)
+
+    def peers_of(self, t):
+        """Array of the world's addresses of `t` (a tensor carved from this arena)."""
+        off = int(t.data_ptr()) - self.base.value
+        assert 0 <= off < self.nbytes
+        return (ctypes.c_void_p * self.comm.world)(*[b + off for b in self.peer_base])
+
+    def close(self):
+        self._bytes = None
+        for p in self._opened:
+            self.L.fricc_symm_close(p)
+        self._opened = []
+        if self.base.value:
+            self.L.fricc_symm_free(self.base)
+            self.base = ctypes.c_void_p()
+
+
+def push_columns(term_obj, t_dims, out, arena):
+    """Store this rank's L-columns of `out` (already accumulated locally) into every peer's copy."""
+    if term_obj.comm.world == 1 or term_obj.lcnt <= 0:
+        return
+    check(term_obj.L.fricc_push_columns(_ptr(out), arena.peers_of(out), term_obj.comm.world, term_obj.comm.rank,
+                                        term_obj.term.encode(), i64x4(t_dims), i64x4(out.shape), i64x4(out.stride()),
+                                        term_obj.l0, term_obj.lcnt))

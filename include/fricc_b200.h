@@ -134,6 +134,27 @@ int fricc_contract_panel_into(const double* Wp_dev, int64_t ldw, int64_t l_begin
  * [g*ld, min((g+1)*ld, nL)); panels is [n_panels][nR][ld] row-major on the device, out a 4-D strided device array).   */
 int fricc_accumulate_panels(const double* panels_dev, int64_t n_panels, int64_t ld, fricc_st_t T, const char* term,
                             double* out_dev, const int64_t out_shape[4], const int64_t out_strides[4]);
+/* ---- exchange over NVLink peer memory (fricc_b200/csrc/fricc_peer.cu) -----------------------------------------
+ * The sharded step's one exchange per output, without NCCL on the data path: each rank accumulates its L-columns into
+ * its own copy of the 4-D output (fricc_contract_panel_into[_tc]) and then stores exactly those elements into the same
+ * addresses of every peer's copy.  The copies live in one symmetric allocation per rank: fricc_symm_alloc returns the
+ * device pointer and a 64-byte CUDA IPC handle; peers map it with fricc_symm_open.  (The reference has no counterpart:
+ * it is a single-process OpenMP code; the outputs are the `ouput` arrays of contract_DTSpT, src/py_rccsd.cpp:47-50.)   */
+int fricc_symm_alloc(int64_t bytes, void** ptr, void* handle64);
+int fricc_symm_open(const void* handle64, void** ptr);
+int fricc_symm_close(void* ptr);
+int fricc_symm_free(void* ptr);
+/* peer_out_dev[q] = address of the SAME 4-D output in rank q's copy (q = self: this rank's own, not written);
+ * pushes out_local[.., columns l_begin .. l_begin+l_count of the free pair of `term`, ..] to every peer.            */
+int fricc_push_columns(const double* out_local_dev, void* const* peer_out_dev, int n_peers, int self, const char* term,
+                       const int64_t t_dims[4], const int64_t out_shape[4], const int64_t out_strides[4],
+                       int64_t l_begin, int64_t l_count);
+/* out_local[.., l, ..] += panel[R][l - l_begin] for this rank's columns (a [nR][ld] panel written by
+ * fricc_contract_panel[_tc]); the sums are also stored into every peer's copy when peer_out_dev != NULL.  Transposes
+ * through shared memory when out's unit-stride axis is the R-major or L-major index (terms 1302/1202/1303/1203).       */
+int fricc_scatter_panel(const double* panel_dev, int64_t ld, int64_t l_begin, int64_t l_count, const char* term,
+                        const int64_t t_dims[4], double* out_local_dev, void* const* peer_out_dev, int n_peers, int self,
+                        const int64_t out_shape[4], const int64_t out_strides[4]);
 /* ---- tensor-core form of the contractions (fricc_b200/csrc/fricc_dense.cu) ------------------------------------
  * Replaces the same reference kernels as fricc_contract_panel (src/sparse_tensor.cpp:12-346) when T comes out of an
  * FRI compression: every sampled entry then has the same magnitude c (fri_utils.cpp:375,502-504), so
@@ -154,9 +175,10 @@ int fricc_wslices_bytes(fricc_wslices_t h, int64_t* bytes);
 int fricc_wslices_reconstruct(fricc_wslices_t h, double* Wrec_dev);
 /* fraction of T's entries that the layout of `term` holds in the sign matrix (0 for "largest" compressions) */
 int fricc_st_sign_fraction(fricc_st_t T, const char* term, double* fraction);
-/* same contract as fricc_contract_panel / fricc_contract_panel_into; l_count is the planes' l_count */
+/* same contract as fricc_contract_panel / fricc_contract_panel_into; l_count is the planes' l_count.
+ * overwrite != 0: out_panel[R][0 .. l_count) = result instead of += (a fresh panel needs neither clearing nor reading) */
 int fricc_contract_panel_tc(fricc_wslices_t h, const double* Wp_dev, int64_t ldw, int64_t l_begin, fricc_st_t T,
-                            double* out_panel_dev, int64_t ld_out, const char* term);
+                            double* out_panel_dev, int64_t ld_out, const char* term, int overwrite);
 int fricc_contract_panel_into_tc(fricc_wslices_t h, const double* Wp_dev, int64_t ldw, int64_t l_begin, fricc_st_t T,
                                  double* out_dev, const int64_t out_shape[4], const int64_t out_strides[4],
                                  const char* term);

@@ -95,3 +95,46 @@ def test_accumulate_into_strided_output(rccsd, port):
         mask = np.ones_like(big, dtype=bool)
         mask[::2, ::2, ::2, ::2] = False
         assert np.array_equal(bigd.cpu().numpy()[mask], big[mask])
+
+
+@pytest.mark.parametrize("term", sorted(TERMS))
+@pytest.mark.parametrize("no,nv,world", [(3, 5, 2), (6, 21, 3), (5, 40, 4)])
+def test_peer_push_exchange(rccsd, port, term, no, nv, world):
+    """The exchange over peer memory (fricc_peer.cu), ranks emulated one after another on one GPU: rank g accumulates
+    its L-columns into ITS copy of the output and stores them into every other copy; afterwards all copies hold the
+    full result.  The "peer" copies are ordinary buffers of this process (same kernel, same addressing)."""
+    import ctypes
+
+    from fricc_b200 import dist as fd
+
+    rng = np.random.default_rng(7 * no + nv + world)
+    torch, dims, flat, vals, T = _setup(rccsd, rng, no, nv, 0.3)
+    ext = {"o": no, "v": nv}
+    waxes, oaxes, _, _ = TERMS[term]
+    W = rng.random([ext[c] for c in waxes])
+    out0 = rng.random([ext[c] for c in oaxes])   # replicated, non-zero initial content
+    want = out0.copy()
+    port.contract(term, W, flat, vals, dims, want)
+    dev = torch.device("cuda", 0)
+    Wd = torch.from_numpy(W).to(dev)
+    copies = [torch.from_numpy(out0).to(dev) for _ in range(world)]
+    peers = (ctypes.c_void_p * world)(*[int(c.data_ptr()) for c in copies])
+
+    class FakeArena:   # the copies are ordinary buffers of this process; same kernels, same addressing
+        def peers_of(self, t):
+            return peers
+
+    for g in range(world):
+        st = fd.ShardedTerm(term, no, nv, fd.Comm(g, world), dev)
+        st.permute_from(Wd)
+        # direct epilogue write + column push, or coalesced panel + transposing scatter (1302/1202/1303/1203)
+        st.accumulate(T, copies[g], arena=FakeArena())
+    for c in copies:
+        got = c.cpu().numpy()
+        assert np.abs(got - want).max() <= TOL * max(1.0, np.abs(want).max())
+    # single rank, no peers: the same entry point is the 1-GPU path
+    one = torch.from_numpy(out0).to(dev)
+    st = fd.ShardedTerm(term, no, nv, fd.Comm(0, 1), dev)
+    st.permute_from(Wd)
+    st.accumulate(T, one)
+    assert np.abs(one.cpu().numpy() - want).max() <= TOL * max(1.0, np.abs(want).max())

@@ -53,9 +53,10 @@ def main():
             st.panel[s:s + step].uniform_(0.0, 1.0, generator=g)
         out = torch.zeros(st.nR * st.lc, dtype=torch.float64, device=dev)
         res = {}
-        for kind in ("fp64_spmm", "tensor_core"):
+        for kind in ("fp64_spmm", "tensor_core", "tensor_core_one_cta_per_tile"):
             ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
-            if kind == "tensor_core":
+            _lib.check(_lib.lib().fricc_set_option(b"tc_persistent", 0 if kind.endswith("per_tile") else 1))
+            if kind.startswith("tensor_core"):
                 ev[0].record()
                 st.build_planes(a.planes)
                 ev[1].record()
@@ -77,7 +78,7 @@ def main():
             ms = ev[2].elapsed_time(ev[3]) / a.reps
             line = {"term": term, "kernel": kind, "o": o, "v": v, "m": m, "rows": st.nR, "cols": st.lcnt, "nK": st.nK,
                     "ms": ms, "fma_per_s": m * st.lcnt / (ms * 1e-3)}
-            if kind == "tensor_core":
+            if kind.startswith("tensor_core"):
                 macs = (-(-st.nR // 128) * 128) * (-(-st.lcnt // 64) * 64) * (-(-st.nK // 128) * 128) * a.planes
                 b = ctypes.c_int64(0)
                 _lib.check(_lib.lib().fricc_wslices_bytes(st.planes, ctypes.byref(b)))
@@ -87,6 +88,7 @@ def main():
                 res[kind] = out.clone()
             print(json.dumps(line), flush=True)
         if a.check:
+            _lib.check(_lib.lib().fricc_set_option(b"tc_persistent", 1))
             d = (res["fp64_spmm"] - res["tensor_core"]).abs().max().item()
             print(json.dumps({"term": term, "max_abs_diff": d, "max_abs": res["fp64_spmm"].abs().max().item()}), flush=True)
         st.drop_planes()
@@ -99,7 +101,7 @@ def st_local(st, T, out):
 
     if st.planes is not None:
         check(st.L.fricc_contract_panel_tc(st.planes, _ptr(st.panel), st.lcnt, st.l0, T._h, _ptr(out), st.lc,
-                                           st.term.encode()))
+                                           st.term.encode(), 0))
     else:
         check(st.L.fricc_contract_panel(_ptr(st.panel), st.lcnt, st.l0, st.lcnt, T._h, _ptr(out), st.lc, st.term.encode()))
 
