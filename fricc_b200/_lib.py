@@ -106,6 +106,19 @@ SIGNATURES = {
     "fricc_fri_compression": (c_int, [c_void_p, c_int, c_int64, c_int64, c_char_p, c_int, c_void_p, c_int64, _i64p,
                                       c_void_p, c_void_p]),
     "fricc_key_histogram": (c_int, [c_void_p, c_int64, c_int, c_uint64, c_int, c_void_p]),
+    "fricc_shard_create": (c_int, [c_void_p, c_int64, c_int64, c_int64, POINTER(c_void_p)]),
+    "fricc_shard_destroy": (c_int, [c_void_p]),
+    "fricc_shard_use_abs": (c_int, [c_void_p]),
+    "fricc_shard_use_probabilities": (c_int, [c_void_p, c_double, c_int64, c_uint64, c_uint64]),
+    "fricc_shard_scan_local": (c_int, [c_void_p, c_void_p]),
+    "fricc_shard_scan_maps": (c_int, [c_void_p, c_void_p]),
+    "fricc_shard_scan_resolve": (c_int, [c_void_p, c_void_p, c_void_p]),
+    "fricc_shard_emit_systematic": (c_int, [c_void_p, c_int64, c_int32, c_void_p]),
+    "fricc_shard_check": (c_int, [c_void_p]),
+    "fricc_shard_candidates": (c_int, [c_void_p, c_uint64, c_void_p, c_void_p, c_int64, c_void_p]),
+    "fricc_sort_candidates": (c_int, [c_void_p, c_void_p, c_int64, c_int64]),
+    "fricc_d_greedy": (c_int, [c_void_p, c_int64, c_int64, c_double, _i64p, _f64p]),
+    "fricc_shard_values": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_void_p]),
 }
 
 

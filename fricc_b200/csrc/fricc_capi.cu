@@ -5,6 +5,7 @@
 #include "fricc_common.cuh"
 #include "fricc_dense.cuh"
 #include "fricc_fri.cuh"
+#include "fricc_psrc.cuh"  // host-side construction only (no kernels in this TU)
 #include "fricc_select.cuh"
 
 namespace fricc {
@@ -701,6 +702,132 @@ int fricc_key_histogram(const double* x_dev, int64_t n, int shift, uint64_t pref
   if (shift != 0 && shift != 3 && shift != 15 && shift != 27 && shift != 39 && shift != 51)
     fail(FRICC_EINVAL, "shift must be one of 51,39,27,15,3,0");
   key_histogram(x_dev, n, shift, shift == 0 ? 7u : 4095u, prefix, prefix_bits, hist_dev);
+  FRICC_API_END
+}
+
+// ---- range-sharded compression -------------------------------------------------------------------------------------
+struct fricc_shard {
+  const double* x = nullptr;
+  int64_t n = 0, j0 = 0, n_total = 0;
+  PSrc ps{};
+  ShardScan* scan = nullptr;
+};
+
+int fricc_shard_create(const double* x_dev, int64_t n, int64_t j0, int64_t n_total, fricc_shard_t* out) {
+  FRICC_API_BEGIN
+  if (!out) fail(FRICC_EINVAL, "null output handle");
+  if (n < 0 || j0 < 0 || j0 + n > n_total) fail(FRICC_EINVAL, "shard [j0, j0+n) must lie inside [0, n_total)");
+  if (n > 0 && !x_dev) fail(FRICC_EINVAL, "null shard pointer");
+  (void)num_sms();  // no device -> FRICC_ECUDA (there is no CPU path)
+  fricc_shard* s = new fricc_shard();
+  s->x = x_dev; s->n = n; s->j0 = j0; s->n_total = n_total;
+  s->ps = PSrc{nullptr, x_dev, 1.0, 0.0, ~0ULL, 0, 1, j0};
+  s->scan = shard_scan_create();
+  *out = s;
+  FRICC_API_END
+}
+
+int fricc_shard_destroy(fricc_shard_t s) {
+  FRICC_API_BEGIN
+  if (s) {
+    shard_scan_destroy(s->scan);
+    delete s;
+  }
+  FRICC_API_END
+}
+
+static void check_shard(fricc_shard_t s) {
+  if (!s) fail(FRICC_EINVAL, "null shard handle");
+}
+
+int fricc_shard_use_abs(fricc_shard_t s) {
+  FRICC_API_BEGIN
+  check_shard(s);
+  s->ps = PSrc{nullptr, s->x, 1.0, 0.0, ~0ULL, 0, 1, s->j0};
+  FRICC_API_END
+}
+
+int fricc_shard_use_probabilities(fricc_shard_t s, double remaining_norm, int64_t n_sample, uint64_t key_cut,
+                                  uint64_t idx_cut) {
+  FRICC_API_BEGIN
+  check_shard(s);
+  s->ps = PSrc{nullptr, s->x, remaining_norm, (double)n_sample, key_cut, idx_cut, 0, s->j0};
+  FRICC_API_END
+}
+
+int fricc_shard_scan_local(fricc_shard_t s, double* approx_total_dev) {
+  FRICC_API_BEGIN
+  check_shard(s);
+  shard_scan_local(s->scan, s->ps, s->n, approx_total_dev);
+  FRICC_API_END
+}
+
+int fricc_shard_scan_maps(fricc_shard_t s, const double* approx_carry_dev) {
+  FRICC_API_BEGIN
+  check_shard(s);
+  shard_scan_maps(s->scan, approx_carry_dev);
+  FRICC_API_END
+}
+
+int fricc_shard_scan_resolve(fricc_shard_t s, const double* carry_in_dev, double* carry_out_dev) {
+  FRICC_API_BEGIN
+  check_shard(s);
+  if (!carry_in_dev || !carry_out_dev) fail(FRICC_EINVAL, "null carry pointer");
+  shard_scan_resolve(s->scan, carry_in_dev, carry_out_dev);
+  FRICC_API_END
+}
+
+int fricc_shard_emit_systematic(fricc_shard_t s, int64_t n_sample, int32_t draw, int64_t* S_dev) {
+  FRICC_API_BEGIN
+  check_shard(s);
+  if (s->ps.absval) fail(FRICC_EINVAL, "fricc_shard_use_probabilities first");
+  const double rn = (double)draw / 2147483647.0;  // (double)rand() / RAND_MAX   (fri_utils.cpp:47)
+  shard_scan_emit(s->scan, n_sample, rn, S_dev);
+  FRICC_API_END
+}
+
+int fricc_shard_check(fricc_shard_t s) {
+  FRICC_API_BEGIN
+  check_shard(s);
+  raise_error_flags(shard_scan_errors(s->scan));
+  FRICC_API_END
+}
+
+int fricc_shard_candidates(fricc_shard_t s, uint64_t key_min, uint64_t* keys_out_dev, uint64_t* idx_out_dev, int64_t cap,
+                           unsigned long long* count_dev) {
+  FRICC_API_BEGIN
+  check_shard(s);
+  if (cap < 0 || !count_dev) fail(FRICC_EINVAL, "bad candidate buffer");
+  shard_candidates(s->x, s->n, s->j0, key_min, keys_out_dev, idx_out_dev, cap, count_dev);
+  FRICC_API_END
+}
+
+int fricc_sort_candidates(uint64_t* keys_dev, uint64_t* idx_dev, int64_t count, int64_t n_total) {
+  FRICC_API_BEGIN
+  (void)num_sms();  // no device -> FRICC_ECUDA (there is no CPU path)
+  sort_candidates(keys_dev, idx_dev, count, n_total);
+  FRICC_API_END
+}
+
+int fricc_d_greedy(const uint64_t* keys_sorted_dev, int64_t n_candidates, int64_t n_sample, double norm, int64_t* n_D,
+                   double* remaining_norm) {
+  FRICC_API_BEGIN
+  (void)num_sms();  // no device -> FRICC_ECUDA (there is no CPU path)
+  if (!n_D || !remaining_norm) fail(FRICC_EINVAL, "null output");
+  *n_D = 0;
+  *remaining_norm = norm;
+  if (n_candidates > 0) {
+    if (n_candidates >= (1 << 15)) d_greedy_parallel(keys_sorted_dev, n_candidates, n_sample, norm, n_D, remaining_norm);
+    else d_greedy_serial(keys_sorted_dev, 0, n_candidates, n_sample, norm, n_D, remaining_norm);
+  }
+  FRICC_API_END
+}
+
+int fricc_shard_values(fricc_shard_t s, const int64_t* flat_dev, int64_t m, int64_t n_D, double* vals_dev) {
+  FRICC_API_BEGIN
+  check_shard(s);
+  if (s->ps.absval) fail(FRICC_EINVAL, "fricc_shard_use_probabilities first");
+  shard_values(s->ps, s->n, flat_dev, m, n_D, vals_dev);
   FRICC_API_END
 }
 

@@ -95,10 +95,11 @@ escan_approx_kernel(PSrc ps, int64_t n, double* __restrict__ approx, int* __rest
 
 // ---- E2 ----------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(ES_THREADS)
-escan_map_kernel(PSrc ps, int64_t n, const double* __restrict__ approx_excl, ChunkMap* __restrict__ maps) {
+escan_map_kernel(PSrc ps, int64_t n, const double* __restrict__ approx_excl, const double* __restrict__ carry,
+                 ChunkMap* __restrict__ maps) {
   __shared__ EMap sm[ES_WARPS];
   const int64_t base = (int64_t)blockIdx.x * ES_CHUNK + (int64_t)threadIdx.x * ES_E;
-  const double c0 = approx_excl[blockIdx.x];
+  const double c0 = approx_excl[blockIdx.x] + (carry ? *carry : 0.0);  // carry: approximate sum before this shard
   const bool usable = fx_is_normal_positive(c0);
   const int k = usable ? fx_binade(c0) : 0;
   EMap m = emap_identity();
@@ -223,7 +224,7 @@ constexpr int RS_WARPS = RS_THREADS / 32;
 
 __global__ void __launch_bounds__(RS_THREADS)
 escan_resolve_kernel(PSrc ps, int64_t n, const ChunkMap* __restrict__ maps, int64_t nchunks,
-                     double* __restrict__ exact_in, double* __restrict__ total, int* __restrict__ stats) {
+                     double* __restrict__ exact_in, const double* carry_in, double* total, int* __restrict__ stats) {
   __shared__ double pbuf[ES_CHUNK];
   __shared__ double cs[ES_CHUNK];
   __shared__ ChunkScratch sc;
@@ -234,7 +235,7 @@ escan_resolve_kernel(PSrc ps, int64_t n, const ChunkMap* __restrict__ maps, int6
   __shared__ int s_dirty;
   const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (threadIdx.x == 0) {
-    s_c = 0.0;
+    s_c = carry_in ? *carry_in : 0.0;  // exact sum of everything before this shard (may alias `total`)
     s_next = 0;
   }
   __syncthreads();
@@ -331,7 +332,7 @@ escan_emit_kernel(PSrc ps, int64_t n, const double* __restrict__ exact_in, int64
     if (incl > excl) {
       int64_t lo = first_sample_at_or_above(excl, rn, nsamp);
       int64_t hi = first_sample_at_or_above(incl, rn, nsamp);
-      for (int64_t i = lo; i < hi; i++) S[i] = base + k;
+      for (int64_t i = lo; i < hi; i++) S[i] = ps.j0 + base + k;
     }
   }
 }
@@ -347,20 +348,78 @@ struct EscanPlan {
   DevBuf<int> stats;
 };
 
-static void escan_prepare(const PSrc& ps, int64_t n, EscanPlan& pl) {
+static void escan_stage_approx(const PSrc& ps, int64_t n, EscanPlan& pl) {
   pl.nchunks = ceil_div(n, ES_CHUNK);
-  pl.approx.alloc((size_t)pl.nchunks);
+  pl.approx.alloc((size_t)pl.nchunks + 1);  // one extra zero addend: the exclusive scan leaves the total behind it
   pl.maps.alloc((size_t)pl.nchunks);
   pl.exact_in.alloc((size_t)pl.nchunks);
   pl.total.alloc(1);
   pl.err.alloc(1);
   pl.stats.alloc(1);
   pl.err.zero();
+  FRICC_CUDA(cudaMemsetAsync(pl.approx.p + pl.nchunks, 0, sizeof(double), stream()));
   FRICC_LAUNCH(escan_approx_kernel, (unsigned)pl.nchunks, ES_THREADS, 0, ps, n, pl.approx.p, pl.err.p);
-  exclusive_scan_f64(pl.approx.p, pl.nchunks);
-  FRICC_LAUNCH(escan_map_kernel, (unsigned)pl.nchunks, ES_THREADS, 0, ps, n, pl.approx.p, pl.maps.p);
-  FRICC_LAUNCH(escan_resolve_kernel, 1, RS_THREADS, 0, ps, n, pl.maps.p, pl.nchunks, pl.exact_in.p, pl.total.p,
-               pl.stats.p);
+  exclusive_scan_f64(pl.approx.p, pl.nchunks + 1);
+}
+
+static void escan_prepare(const PSrc& ps, int64_t n, EscanPlan& pl) {
+  escan_stage_approx(ps, n, pl);
+  FRICC_LAUNCH(escan_map_kernel, (unsigned)pl.nchunks, ES_THREADS, 0, ps, n, pl.approx.p, (const double*)nullptr,
+               pl.maps.p);
+  FRICC_LAUNCH(escan_resolve_kernel, 1, RS_THREADS, 0, ps, n, pl.maps.p, pl.nchunks, pl.exact_in.p,
+               (const double*)nullptr, pl.total.p, pl.stats.p);
+}
+
+// ---- the scan in stages (range-sharded tensors; see fricc_psrc.cuh) -------------------------------------------------
+struct ShardScan {
+  EscanPlan pl;
+  PSrc ps{};
+  int64_t n = 0;
+};
+ShardScan* shard_scan_create() { return new ShardScan(); }
+void shard_scan_destroy(ShardScan* s) { delete s; }
+
+void shard_scan_local(ShardScan* s, const PSrc& ps, int64_t n, double* approx_total_dev) {
+  s->ps = ps;
+  s->n = n;
+  if (n <= 0) {
+    s->pl.nchunks = 0;
+    s->pl.err.alloc(1);
+    s->pl.err.zero();
+    FRICC_CUDA(cudaMemsetAsync(approx_total_dev, 0, sizeof(double), stream()));
+    return;
+  }
+  escan_stage_approx(ps, n, s->pl);
+  FRICC_CUDA(cudaMemcpyAsync(approx_total_dev, s->pl.approx.p + s->pl.nchunks, sizeof(double), cudaMemcpyDeviceToDevice,
+                             stream()));
+}
+
+void shard_scan_maps(ShardScan* s, const double* approx_carry_dev) {
+  if (s->n <= 0) return;
+  FRICC_LAUNCH(escan_map_kernel, (unsigned)s->pl.nchunks, ES_THREADS, 0, s->ps, s->n, s->pl.approx.p, approx_carry_dev,
+               s->pl.maps.p);
+}
+
+void shard_scan_resolve(ShardScan* s, const double* carry_in_dev, double* carry_out_dev) {
+  if (s->n <= 0) {
+    if (carry_out_dev != carry_in_dev)
+      FRICC_CUDA(cudaMemcpyAsync(carry_out_dev, carry_in_dev, sizeof(double), cudaMemcpyDeviceToDevice, stream()));
+    return;
+  }
+  FRICC_LAUNCH(escan_resolve_kernel, 1, RS_THREADS, 0, s->ps, s->n, s->pl.maps.p, s->pl.nchunks, s->pl.exact_in.p,
+               carry_in_dev, carry_out_dev, s->pl.stats.p);
+}
+
+void shard_scan_emit(ShardScan* s, int64_t nsamp, double rn, int64_t* S_dev) {
+  if (s->n <= 0 || nsamp <= 0) return;
+  FRICC_LAUNCH(escan_emit_kernel, (unsigned)s->pl.nchunks, ES_THREADS, 0, s->ps, s->n, s->pl.exact_in.p, nsamp, rn,
+               S_dev);
+}
+
+int shard_scan_errors(ShardScan* s) {
+  int e = 0;
+  s->pl.err.to_host(&e, 1);
+  return e;
 }
 
 double exact_sum_parallel(const PSrc& ps, int64_t n, int* err_flags_out) {

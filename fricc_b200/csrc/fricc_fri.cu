@@ -381,6 +381,8 @@ static void raise_flags(int flags) {
     fail(FRICC_EPIVOTAL, "ERROR IN PIVOTAL SAMPLING: acceptance probability outside [0,1] (reference: fri_utils.cpp:84-94)");
 }
 
+void raise_error_flags(int flags) { raise_flags(flags); }
+
 void make_probability_vector(const double* x, int64_t n, int64_t n_sample, const int64_t* D, int64_t nD,
                              double remaining_norm, double* p) {
   if (n <= 0) return;

@@ -72,6 +72,13 @@ void compress_largest(const double* x_dev, int64_t n, int64_t m, Compressed& out
 void compress_fri(const double* x_dev, int64_t n, int64_t m, Sampling method, const DrawSource& draws, bool verbose,
                   Compressed& out);
 
+// per-shard stages of the range-sharded compression (fricc_shard.cu)
+void shard_candidates(const double* x_dev, int64_t n, int64_t j0, uint64_t key_min, uint64_t* keys_out_dev,
+                      uint64_t* idx_out_dev, int64_t cap, unsigned long long* count_dev);
+void sort_candidates(uint64_t* keys_dev, uint64_t* idx_dev, int64_t count, int64_t n_total);
+void shard_values(const PSrc& ps, int64_t n, const int64_t* flat_dev, int64_t m, int64_t nD, double* vals_dev);
+void raise_error_flags(int flags);  // ERRF_* -> the reference's error (fail)
+
 // glibc-compatible rand() stream (host side)
 void rand_seed(uint32_t seed);
 void rand_fill(int32_t* out, int64_t n);  // advances

@@ -20,12 +20,13 @@ struct PSrc {
   uint64_t key_cut;     // D = { key > key_cut } U { key == key_cut and idx <= idx_cut };  no D: key_cut = ~0
   uint64_t idx_cut;
   int absval;           // 1: return |x| (one_norm)
+  int64_t j0 = 0;       // flat index of x[0] (range-sharded compression: x is the shard [j0, j0+n) of the tensor)
   __device__ __forceinline__ double operator()(int64_t j) const {
     if (probs) return probs[j];
     double xv = x[j];
     if (absval) return fabs(xv);
     uint64_t key = abs_key(xv);
-    bool inD = key > key_cut || (key == key_cut && (uint64_t)j <= idx_cut);
+    bool inD = key > key_cut || (key == key_cut && (uint64_t)(j + j0) <= idx_cut);
     if (inD) return 0.0;
     // abs(x[i]) / remaining_norm * n_sample   (fri_utils.cpp:375), left to right, no contraction
     return __dmul_rn(__ddiv_rn(fabs(xv), r), nprime);
@@ -47,5 +48,22 @@ __device__ __forceinline__ int64_t first_sample_at_or_above(double X, double rn,
 // exact (left-to-right order) sums computed by the parallel binade-segmented scan  (fricc_escan.cu)
 double exact_sum_parallel(const PSrc& ps, int64_t n, int* err_flags_out);
 void systematic_parallel(const PSrc& ps, int64_t n, int64_t nsamp, double rn, int64_t* S_dev, int* err_flags_out);
+
+// The same scan cut into its stages for a tensor sharded by contiguous flat-index ranges over several ranks
+// (fricc_shard.cu): the stages between which the caller exchanges one double per rank.  All scalars stay on the device,
+// so a rank-to-rank chain of carries is ordered by the stream alone.
+struct ShardScan;
+ShardScan* shard_scan_create();
+void shard_scan_destroy(ShardScan* s);
+// E1: approximate chunk sums of the shard; *approx_total_dev = approximate sum of the whole shard
+void shard_scan_local(ShardScan* s, const PSrc& ps, int64_t n, double* approx_total_dev);
+// E2: chunk maps in the binades predicted by (*approx_carry_dev + approximate running sum inside the shard)
+void shard_scan_maps(ShardScan* s, const double* approx_carry_dev);
+// E3: exact running sums at chunk starts from the exact sum *carry_in_dev of everything before the shard;
+// *carry_out_dev = exact sum behind the shard (may alias carry_in_dev)
+void shard_scan_resolve(ShardScan* s, const double* carry_in_dev, double* carry_out_dev);
+// E4: systematic samples owned by the shard's elements, written as GLOBAL flat indices into S_dev[nsamp]
+void shard_scan_emit(ShardScan* s, int64_t nsamp, double rn, int64_t* S_dev);
+int shard_scan_errors(ShardScan* s);  // ERRF_* raised so far (synchronises)
 
 }  // namespace fricc

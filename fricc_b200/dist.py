@@ -416,3 +416,7 @@ def push_columns(term_obj, t_dims, out, arena):
     check(term_obj.L.fricc_push_columns(_ptr(out), arena.peers_of(out), term_obj.comm.world, term_obj.comm.rank,
                                         term_obj.term.encode(), i64x4(t_dims), i64x4(out.shape), i64x4(out.stride()),
                                         term_obj.l0, term_obj.lcnt))
+
+
+# range-sharded compression (x split by contiguous flat-index ranges; all-reduced key histograms): fricc_b200/ranges.py
+from .ranges import compress_ranges, index_range  # noqa: E402,F401

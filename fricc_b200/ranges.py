@@ -1,0 +1,278 @@
+"""FRI compression of a tensor sharded by contiguous flat-index ranges over the ranks ("distributed
+top-m uses an all-reduced histogram"; BASELINE config 5, the compression-only sweep at 1/2/4/8 GPUs).
+
+Rank g holds x[j0_g : j0_g + n_g] of the flattened (o,o,v,v) tensor, rank order = index order.  The result is the SAME
+SparseTensor4d, bit for bit, that the single-process compression produces (reference: fri_compression,
+/root/reference/src/fri_utils.cpp:439-522, behind SparseTensor4d's constructor, include/sparse_tensor.hpp:58-67), and
+every rank ends up holding it (the contractions replicate T).
+
+What crosses NVLink per compression (m entries kept, G ranks):
+  * 2 x (G doubles all-gather + G one-double broadcasts): the exact left-to-right sums (norm; running sum of p)
+  * <= 6 all-reduces of a 4096-bin key histogram per candidate round (the top-|D| select)
+  * an all-gather of the candidates at or above the cut (~65 536 (key, index) pairs in the common case)
+  * all-reduce(SUM) of the m-entry index list and of the m-entry value list (each entry is written by exactly one rank)
+All arithmetic is in libfricc_b200.so (fricc_shard.cu, fricc_escan.cu); torch moves bytes.
+"""
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import check
+from .py_rccsd import SparseTensor4d
+
+KEY_SHIFTS = (51, 39, 27, 15, 3, 0)       # digit schedule over the 63 magnitude bits (fricc_select.cu)
+KEY_DIGIT_BITS = (12, 12, 12, 12, 12, 3)
+FIRST_CANDIDATES = 65536                  # same first candidate-list size as the single-GPU compress_fri
+SMALL_BIN = 1 << 16
+
+
+def _ptr(t):
+    return ctypes.c_void_p(int(t.data_ptr()))
+
+
+def index_range(n_total, rank, world):
+    """Contiguous flat-index range [j0, j0 + n) owned by `rank` (equal split, the last ranks may be one short)."""
+    base, extra = divmod(int(n_total), int(world))
+    j0 = rank * base + min(rank, extra)
+    return j0, base + (1 if rank < extra else 0)
+
+
+def locate_threshold(hist_fn, want, small_bin=SMALL_BIN):
+    """Walk the key digits from the top using GLOBAL (already all-reduced) histograms until the bin that straddles the
+    `want`-th largest key holds at most `small_bin` elements (or the bits are exhausted).
+
+    hist_fn(shift, prefix, prefix_bits) -> sequence of counts of the digit at `shift` among keys whose higher bits equal
+    `prefix`.  Returns (key_min, count): `count` >= min(want, N) elements have key >= key_min, and key_min is the
+    largest threshold of that digit depth with this property.  Pure host logic (tested on CPU with gloo)."""
+    prefix, prefix_bits, above, rem = 0, 0, 0, int(want)
+    if rem <= 0:
+        return (1 << 63), 0          # above every key: nothing selected
+    shift = 63
+    bin_count = 0
+    for shift, nbits in zip(KEY_SHIFTS, KEY_DIGIT_BITS):
+        h = hist_fn(shift, prefix, prefix_bits)
+        nb = 1 << nbits
+        acc, b = 0, nb - 1
+        while b >= 0:
+            c = int(h[b])
+            if acc + c >= rem:
+                break
+            acc += c
+            b -= 1
+        if b < 0:                    # fewer than `want` elements exist below this prefix: take them all
+            return prefix << (shift + nbits), above + acc
+        above += acc
+        rem -= acc
+        bin_count = int(h[b])
+        prefix = (prefix << nbits) | b
+        prefix_bits += nbits
+        if bin_count == rem or bin_count <= small_bin:
+            break
+    return prefix << shift, above + bin_count
+
+
+class _Shard:
+    """RAII wrapper of fricc_shard_t."""
+
+    def __init__(self, x_local, j0, n_total):
+        self.L = _lib.lib()
+        self.h = ctypes.c_void_p(None)
+        self.x = x_local
+        self.n = int(x_local.numel())
+        self.j0, self.n_total = int(j0), int(n_total)
+        check(self.L.fricc_shard_create(_ptr(x_local), self.n, self.j0, self.n_total, ctypes.byref(self.h)))
+
+    def close(self):
+        if self.h is not None and self.h.value:
+            self.L.fricc_shard_destroy(self.h)
+            self.h = ctypes.c_void_p(None)
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def _src(comm, g):
+    if comm.group is None:
+        return g
+    import torch.distributed as dist
+
+    return dist.get_global_rank(comm.group, g)
+
+
+def _all_reduce(comm, t, op="sum"):
+    if comm.world > 1:
+        import torch.distributed as dist
+
+        dist.all_reduce(t, op=dist.ReduceOp.SUM if op == "sum" else dist.ReduceOp.MAX, group=comm.group)
+    return t
+
+
+def exact_sum(shard, comm):
+    """Exact left-to-right sum of the current addends (|x| or p) over ALL shards in index order; the per-chunk exact
+    running sums stay in the shard for fricc_shard_emit_systematic.  Returns a 1-element device tensor (same on all
+    ranks).  Stages: approximate shard sums (all-gather) -> chunk maps (parallel on every rank) -> one small resolve
+    kernel per rank, the exact carry handed from rank to rank by a one-double broadcast (stream-ordered, no host sync)."""
+    L, dev = shard.L, shard.x.device
+    approx = torch.zeros(1, dtype=torch.float64, device=dev)
+    check(L.fricc_shard_scan_local(shard.h, _ptr(approx)))
+    if comm.world > 1:
+        allg = torch.empty(comm.world, dtype=torch.float64, device=dev)
+        comm.all_gather(allg, approx)
+        carry_approx = allg[: comm.rank].sum().reshape(1) if comm.rank > 0 else torch.zeros_like(approx)
+    else:
+        carry_approx = torch.zeros_like(approx)
+    check(L.fricc_shard_scan_maps(shard.h, _ptr(carry_approx)))
+    carry = torch.zeros(1, dtype=torch.float64, device=dev)
+    for g in range(comm.world):
+        if g == comm.rank:
+            check(L.fricc_shard_scan_resolve(shard.h, _ptr(carry), _ptr(carry)))
+        if comm.world > 1:
+            import torch.distributed as dist
+
+            dist.broadcast(carry, src=_src(comm, g), group=comm.group)
+    return carry
+
+
+def global_candidates(shard, comm, want):
+    """(keys, idx) of the `want` largest |x| over all shards, ordered by (|x| descending, flat index ascending), as
+    device tensors (identical on every rank).  The cut is located with all-reduced key histograms; only the elements at
+    or above it are gathered and sorted."""
+    L, dev = shard.L, shard.x.device
+    want = min(int(want), shard.n_total)
+    hist = torch.zeros(4096, dtype=torch.int64, device=dev)
+
+    def hist_fn(shift, prefix, prefix_bits):
+        hist.zero_()
+        check(L.fricc_key_histogram(_ptr(shard.x), shard.n, shift, ctypes.c_uint64(prefix), prefix_bits, _ptr(hist)))
+        _all_reduce(comm, hist)
+        return hist.cpu().numpy()
+
+    key_min, total = locate_threshold(hist_fn, want)
+    cap = max(min(total, shard.n), 1)
+    keys = torch.empty(cap, dtype=torch.int64, device=dev)      # uint64 bit patterns of |x| (sign bit clear)
+    idx = torch.empty(cap, dtype=torch.int64, device=dev)
+    cnt = torch.zeros(1, dtype=torch.int64, device=dev)
+    check(L.fricc_shard_candidates(shard.h, ctypes.c_uint64(key_min), _ptr(keys), _ptr(idx), cap, _ptr(cnt)))
+    if comm.world > 1:
+        counts = torch.empty(comm.world, dtype=torch.int64, device=dev)
+        comm.all_gather(counts, cnt)
+        counts = counts.cpu().tolist()
+        if sum(counts) != total or counts[comm.rank] > cap:
+            raise RuntimeError("distributed select: candidate counts disagree with the all-reduced histograms")
+        width = max(max(counts), 1)
+        pad_k = torch.zeros(width, dtype=torch.int64, device=dev)
+        pad_i = torch.zeros(width, dtype=torch.int64, device=dev)
+        pad_k[: counts[comm.rank]] = keys[: counts[comm.rank]]
+        pad_i[: counts[comm.rank]] = idx[: counts[comm.rank]]
+        all_k = torch.empty(comm.world * width, dtype=torch.int64, device=dev)
+        all_i = torch.empty(comm.world * width, dtype=torch.int64, device=dev)
+        comm.all_gather(all_k, pad_k)
+        comm.all_gather(all_i, pad_i)
+        keys = torch.cat([all_k[g * width: g * width + c] for g, c in enumerate(counts)])
+        idx = torch.cat([all_i[g * width: g * width + c] for g, c in enumerate(counts)])
+    else:
+        c = int(cnt.item())
+        if c != total:
+            raise RuntimeError("select: candidate count disagrees with the histograms")
+        keys, idx = keys[:c].clone(), idx[:c].clone()
+    if total > 0:
+        check(L.fricc_sort_candidates(_ptr(keys), _ptr(idx), total, shard.n_total))
+    return keys[:want], idx[:want]
+
+
+def compress_ranges(x_local, j0, dims, m, comm, compression="fri", sampling_method="systematic", draws=None):
+    """SparseTensor4d(tensor, dims, m, compression, sampling_method) for a tensor whose flattened elements
+    [j0, j0 + x_local.numel()) live on this rank (CUDA, float64, contiguous).  Every rank returns the full, identical
+    sparse tensor -- bit-identical to the single-process constructor on the concatenated tensor with the same draws.
+
+    draws: None -> the library's glibc-compatible rand() stream (every rank advances its copy by the one draw the
+    reference's systematic sampler consumes); or an int32 array whose first element is that draw.
+    sampling_method "pivotal" is not range-sharded (its walk carries four state words and one draw per element; use
+    dist.compress_pair, which runs whole compressions task-parallel) and raises NotImplementedError."""
+    from .dist import use_torch_stream
+
+    dims = tuple(int(d) for d in dims)
+    n_total = dims[0] * dims[1] * dims[2] * dims[3]
+    m = int(m)
+    if not (0 <= m <= n_total):
+        raise ValueError(f"need 0 <= m <= N (m={m}, N={n_total})")   # the reference's driver check, friccsd.py:69-72
+    if compression not in ("fri", "largest"):
+        raise ValueError(f"unknown compression '{compression}'")
+    if compression == "fri" and sampling_method != "systematic":
+        raise NotImplementedError("range-sharded compression implements the systematic sampler; use dist.compress_pair "
+                                  "for pivotal")
+    if x_local.dtype != torch.float64 or not x_local.is_cuda or not x_local.is_contiguous():
+        raise TypeError("x_local must be a contiguous CUDA float64 tensor")
+    use_torch_stream()
+    L, dev = _lib.lib(), x_local.device
+    shard = _Shard(x_local.view(-1), j0, n_total)
+    try:
+        consumed = 0
+        if compression == "largest":
+            keys, idx = global_candidates(shard, comm, m)
+            flat, n_exact = idx.clone(), m
+            check(L.fricc_shard_use_probabilities(shard.h, 1.0, 0, ctypes.c_uint64(2**64 - 1), ctypes.c_uint64(0)))
+        else:
+            # ---- get_d_largest (fri_utils.cpp:400-437): norm, ordered candidates, greedy test
+            check(L.fricc_shard_use_abs(shard.h))
+            norm = float(exact_sum(shard, comm).item())
+            nD, r = ctypes.c_int64(0), ctypes.c_double(norm)
+            cand = min(m, FIRST_CANDIDATES)
+            keys = idx = None
+            while m > 0:
+                keys, idx = global_candidates(shard, comm, cand)
+                check(L.fricc_d_greedy(_ptr(keys), cand, m, norm, ctypes.byref(nD), ctypes.byref(r)))
+                if nD.value < cand or cand == m:
+                    break
+                cand = m if cand > m // 16 else cand * 16
+            nD, r = nD.value, r.value
+            key_cut, idx_cut = 2**64 - 1, 0
+            if nD > 0:
+                key_cut, idx_cut = (int(v) for v in torch.stack([keys[nD - 1], idx[nD - 1]]).cpu().tolist())
+            nsamp = m - nD
+            # ---- sample_systematic (fri_utils.cpp:129-159) over p = |x| / r * n', p[D] = 0 (never materialised)
+            if draws is None:
+                d = (ctypes.c_int32 * 1)()
+                check(L.fricc_rand_fill(d, 1))
+                draw = int(d[0])
+            else:
+                d = np.asarray(draws).reshape(-1)
+                if d.size < 1:
+                    raise _lib.FriccError(_lib.EDRAWS, "systematic sampling needs one draw")
+                draw = int(d[0])
+            consumed = 1
+            check(L.fricc_shard_use_probabilities(shard.h, r, nsamp, ctypes.c_uint64(key_cut), ctypes.c_uint64(idx_cut)))
+            flat = torch.zeros(max(m, 1), dtype=torch.int64, device=dev)[:m]
+            if nD > 0:
+                flat[:nD] = idx[:nD] if comm.rank == 0 else 0    # summed over ranks below: rank 0 contributes D
+            if nsamp > 0:
+                exact_sum(shard, comm)
+                check(L.fricc_shard_emit_systematic(shard.h, nsamp, draw, _ptr(flat[nD:])))
+            _all_reduce(comm, flat)
+            n_exact = nD
+        vals = torch.zeros(max(m, 1), dtype=torch.float64, device=dev)[:m]
+        check(L.fricc_shard_values(shard.h, _ptr(flat), m, n_exact, _ptr(vals)))
+        _all_reduce(comm, vals)
+        # a kernel error on any rank (some p > 1: fri_utils.cpp:383-395) is raised on every rank
+        err = torch.zeros(1, dtype=torch.int64, device=dev)
+        msg = None
+        if compression == "fri":
+            try:
+                check(L.fricc_shard_check(shard.h))
+            except _lib.FriccError as e:
+                err += 1
+                msg = e
+        _all_reduce(comm, err, "max")
+        if int(err.item()):
+            raise msg if msg is not None else _lib.FriccError(_lib.EPROB, "ERROR MAKING PROBABILITY VECTOR on another rank")
+        T = SparseTensor4d.from_coo(flat, vals, dims)
+        check(L.fricc_st_set_n_exact(T._h, int(n_exact)))
+        T.consumed_draws = consumed
+        return T
+    finally:
+        shard.close()

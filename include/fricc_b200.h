@@ -207,11 +207,49 @@ int fricc_fri_compression(const double* x, int mem, int64_t n, int64_t n_sample,
                           int verbose, const int32_t* draws, int64_t n_draws, int64_t* n_consumed,
                           int64_t* idx_out_host, double* vals_out_host);
 
-/* ---- distributed compression building blocks (multi-GPU: x sharded by contiguous flat-index range) ------------- */
-/* 4096-bin histogram (count) of the 12-bit digit at `shift` of key(x)=bits(|x|), over elements whose higher bits
- * equal `prefix` (prefix_bits of them); device output, to be all-reduced by the caller.                           */
+/* ---- range-sharded compression (multi-GPU: x sharded by contiguous flat-index range; fricc_b200/csrc/fricc_shard.cu) --
+ * Rank g holds x[j0, j0+n) of an n_total-element tensor; rank order = index order.  These are the per-shard stages of
+ * fri_compression (fri_utils.cpp:439-522) between which the host exchanges a few bytes (fricc_b200/dist.py:
+ * compress_ranges); the assembled result is bit-identical to the single-process compression.  All *_dev scalars live on
+ * the device, so a chain of carries from rank to rank is ordered by the stream alone.                               */
+/* 4096-bin histogram (count) of the 12-bit digit at `shift` (51,39,27,15,3; shift 0 = the last 3 bits) of
+ * key(x)=bits(|x|), over elements whose higher bits equal `prefix` (prefix_bits > 0 enables the filter); ADDS into the
+ * device array, which the caller all-reduces (argsort, fri_utils.cpp:11-36, without the sort).                      */
 int fricc_key_histogram(const double* x_dev, int64_t n, int shift, uint64_t prefix, int prefix_bits,
                         unsigned long long* hist_dev /*[4096]*/);
+typedef struct fricc_shard* fricc_shard_t;
+int fricc_shard_create(const double* x_dev, int64_t n, int64_t j0, int64_t n_total, fricc_shard_t* out);
+int fricc_shard_destroy(fricc_shard_t s);
+/* what the exact running sum adds up: |x_j| (one_norm, fri_utils.cpp:164-171) ...                                    */
+int fricc_shard_use_abs(fricc_shard_t s);
+/* ... or p_j = |x_j| / remaining_norm * n_sample with p = 0 on D (make_probability_vector, fri_utils.cpp:367-398);
+ * D = { key > key_cut } U { key == key_cut and flat index <= idx_cut }; no D: key_cut = ~0                           */
+int fricc_shard_use_probabilities(fricc_shard_t s, double remaining_norm, int64_t n_sample, uint64_t key_cut,
+                                  uint64_t idx_cut);
+/* exact LEFT-TO-RIGHT sum across shards in three stages (std::partial_sum / one_norm order):
+ * (1) approximate sum of this shard -> *approx_total_dev; (2) chunk maps, given the approximate sum of all lower shards;
+ * (3) exact: *carry_out_dev = exact sum through this shard, given the exact sum *carry_in_dev through the lower ones. */
+int fricc_shard_scan_local(fricc_shard_t s, double* approx_total_dev);
+int fricc_shard_scan_maps(fricc_shard_t s, const double* approx_carry_dev);
+int fricc_shard_scan_resolve(fricc_shard_t s, const double* carry_in_dev, double* carry_out_dev);
+/* sample_systematic (fri_utils.cpp:129-159) after stage (3) over the probabilities: the samples owned by this shard's
+ * elements, as GLOBAL flat indices, into S_dev[n_sample] (zero-initialised by the caller; summed over ranks).
+ * draw = the rand() value of lin_space_add_const (fri_utils.cpp:47).                                                */
+int fricc_shard_emit_systematic(fricc_shard_t s, int64_t n_sample, int32_t draw, int64_t* S_dev);
+/* raises the reference's error if a kernel of this shard flagged one (some p > 1: fri_utils.cpp:383-395)            */
+int fricc_shard_check(fricc_shard_t s);
+/* (key, global flat index) of every element with key >= key_min, appended in arbitrary order; *count_dev = how many
+ * (may exceed cap: then only cap were stored)                                                                       */
+int fricc_shard_candidates(fricc_shard_t s, uint64_t key_min, uint64_t* keys_out_dev, uint64_t* idx_out_dev, int64_t cap,
+                           unsigned long long* count_dev);
+/* order gathered candidates by (key descending, index ascending), in place                                          */
+int fricc_sort_candidates(uint64_t* keys_dev, uint64_t* idx_dev, int64_t count, int64_t n_total);
+/* get_d_largest's greedy test (fri_utils.cpp:415-431) on an ordered candidate list                                   */
+int fricc_d_greedy(const uint64_t* keys_sorted_dev, int64_t n_candidates, int64_t n_sample, double norm, int64_t* n_D,
+                   double* remaining_norm);
+/* values (fri_utils.cpp:498-504) of the entries whose flat index this shard owns: x for the first n_D entries, x/p for
+ * the samples; 0.0 for entries owned by another shard (sum over ranks assembles the list)                           */
+int fricc_shard_values(fricc_shard_t s, const int64_t* flat_dev, int64_t m, int64_t n_D, double* vals_dev);
 
 #ifdef __cplusplus
 }
