@@ -59,6 +59,11 @@ def parse_args():
     p.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
                    help="N>1: how column slices reach the other ranks: stores into peer memory over NVLink (default) or "
                         "NCCL all-gather of panels + accumulate")
+    p.add_argument("--compress", default="auto", choices=["auto", "ranges", "pair", "replicated"],
+                   help="how the two compressions of a step are computed: 'ranges' = every rank scans its contiguous 1/N "
+                        "of T2, all-reduced key histograms, norm / D / running sums shared by both draws (systematic "
+                        "sampler; default for it); 'pair' = whole compressions task-parallel on even/odd ranks; "
+                        "'replicated' = both on every rank")
     p.add_argument("--no-overlap", action="store_true", help="N>1: one blocking exchange per term (A/B of the pipelined step)")
     return p.parse_args()
 
@@ -306,9 +311,27 @@ class Iteration:
         e.record()
         self.stage_events.append((name, e))
 
+    def compress_mode(self):
+        c = self.args.compress
+        if c == "auto":
+            if self.args.sampling == "systematic":
+                return "ranges"
+            return "pair" if (self.comm.world > 1 and not self.args.no_overlap) else "replicated"
+        return c
+
     def step(self, t2, timer=None):
         self.mark("begin")
-        if self.comm.world > 1 and not self.args.no_overlap:
+        mode = self.compress_mode()
+        if mode == "ranges":
+            # every rank scans only its contiguous 1/N of T2 (a view: T2 is replicated); the two compressions differ
+            # only in the draw, so norm, D and the running sums of p are computed once (fricc_b200/ranges.py)
+            d = (self.draws[self.draw_pos % 32:], self.draws[(self.draw_pos + 1) % 32:])
+            self.draw_pos += 2
+            flat = t2.view(-1)
+            j0, cnt = self.fd.index_range(flat.numel(), self.comm.rank, self.comm.world)
+            T, T_alt = self.fd.compress_ranges_pair(flat[j0:j0 + cnt], j0, tuple(t2.shape), self.m, self.comm, "fri",
+                                                    "systematic", draws=d)
+        elif mode == "pair" and self.comm.world > 1:
             # task-parallel: even ranks compress with the first draws, odd ranks with the second, entries broadcast
             d = None
             if self.args.sampling == "systematic":
@@ -724,6 +747,11 @@ def run_b200_arm(args):
                               f"sum of segments; ladder W regenerated in HBM between {len(it.sub)} column sub-shards",
         }
         line["config"]["ladder_subshards"] = len(it.sub)
+        line["config"]["compression"] = {
+            "ranges": "range-sharded: each rank scans its contiguous 1/N of T2, all-reduced key histograms, exact sums "
+                      "carried rank to rank; norm, D and running sums shared by the step's two draws",
+            "pair": "task-parallel: even ranks compute the first compression, odd ranks the second, entries broadcast",
+            "replicated": "both compressions on every rank"}[it.compress_mode()]
         line["config"]["precision"] = ("fp64 results: W expanded error-free into int8 digit planes (tail 2^-48 of each column's "
                                        "largest element), exact int32 accumulation, fp64 recombination; measured max "
                                        "deviation from the fp64 SpMM 7e-15 relative (profiles/tc_vs_fp64_r01_H_1gpu.jsonl)"

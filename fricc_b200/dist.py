@@ -419,4 +419,4 @@ def push_columns(term_obj, t_dims, out, arena):
 
 
 # range-sharded compression (x split by contiguous flat-index ranges; all-reduced key histograms): fricc_b200/ranges.py
-from .ranges import compress_ranges, index_range  # noqa: E402,F401
+from .ranges import compress_ranges, compress_ranges_pair, index_range  # noqa: E402,F401

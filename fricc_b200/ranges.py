@@ -194,11 +194,28 @@ def compress_ranges(x_local, j0, dims, m, comm, compression="fri", sampling_meth
     reference's systematic sampler consumes); or an int32 array whose first element is that draw.
     sampling_method "pivotal" is not range-sharded (its walk carries four state words and one draw per element; use
     dist.compress_pair, which runs whole compressions task-parallel) and raises NotImplementedError."""
+    return compress_ranges_multi(x_local, j0, dims, m, comm, compression, sampling_method,
+                                 draws=None if draws is None else [draws], count=1)[0]
+
+
+def compress_ranges_pair(x_local, j0, dims, m, comm, compression="fri", sampling_method="systematic", draws=None):
+    """The TWO compressions of one FRICCSD iteration (fricc/friccsd.py:100-136: the same t2 compressed twice, the
+    second with the next draw -> t2_sparse, t2_sparse_alt).  With the systematic sampler the two differ ONLY in the one
+    uniform draw: the norm, the exactly preserved set D, the remaining norm and the running sums of p are the same, so
+    they are computed once and only the sample emission and the values are done per draw.  Results are bit-identical to
+    two consecutive constructor calls.  draws: None (library stream, two draws consumed) or (d_first, d_second)."""
+    T = compress_ranges_multi(x_local, j0, dims, m, comm, compression, sampling_method, draws=draws, count=2)
+    return T[0], T[1]
+
+
+def compress_ranges_multi(x_local, j0, dims, m, comm, compression="fri", sampling_method="systematic", draws=None,
+                          count=1):
+    """`count` consecutive compressions of the same tensor (the k-th uses the k-th draw); see compress_ranges[_pair]."""
     from .dist import use_torch_stream
 
     dims = tuple(int(d) for d in dims)
     n_total = dims[0] * dims[1] * dims[2] * dims[3]
-    m = int(m)
+    m, count = int(m), int(count)
     if not (0 <= m <= n_total):
         raise ValueError(f"need 0 <= m <= N (m={m}, N={n_total})")   # the reference's driver check, friccsd.py:69-72
     if compression not in ("fri", "largest"):
@@ -208,14 +225,22 @@ def compress_ranges(x_local, j0, dims, m, comm, compression="fri", sampling_meth
                                   "for pivotal")
     if x_local.dtype != torch.float64 or not x_local.is_cuda or not x_local.is_contiguous():
         raise TypeError("x_local must be a contiguous CUDA float64 tensor")
+    if draws is not None and len(draws) < count:
+        raise _lib.FriccError(_lib.EDRAWS, "one draw buffer per compression is needed")
     use_torch_stream()
     L, dev = _lib.lib(), x_local.device
     shard = _Shard(x_local.view(-1), j0, n_total)
+    mm = max(m, 1)
     try:
         consumed = 0
+        # the `count` index / value lists side by side: ONE all-reduce each
+        flat = torch.zeros(count * mm, dtype=torch.int64, device=dev)
+        vals = torch.zeros(count * mm, dtype=torch.float64, device=dev)
         if compression == "largest":
             keys, idx = global_candidates(shard, comm, m)
-            flat, n_exact = idx.clone(), m
+            for k in range(count):
+                flat[k * mm: k * mm + m] = idx
+            n_exact = m
             check(L.fricc_shard_use_probabilities(shard.h, 1.0, 0, ctypes.c_uint64(2**64 - 1), ctypes.c_uint64(0)))
         else:
             # ---- get_d_largest (fri_utils.cpp:400-437): norm, ordered candidates, greedy test
@@ -236,27 +261,30 @@ def compress_ranges(x_local, j0, dims, m, comm, compression="fri", sampling_meth
                 key_cut, idx_cut = (int(v) for v in torch.stack([keys[nD - 1], idx[nD - 1]]).cpu().tolist())
             nsamp = m - nD
             # ---- sample_systematic (fri_utils.cpp:129-159) over p = |x| / r * n', p[D] = 0 (never materialised)
-            if draws is None:
-                d = (ctypes.c_int32 * 1)()
-                check(L.fricc_rand_fill(d, 1))
-                draw = int(d[0])
-            else:
-                d = np.asarray(draws).reshape(-1)
-                if d.size < 1:
-                    raise _lib.FriccError(_lib.EDRAWS, "systematic sampling needs one draw")
-                draw = int(d[0])
+            the_draws = []
+            for k in range(count):
+                if draws is None:
+                    d = (ctypes.c_int32 * 1)()
+                    check(L.fricc_rand_fill(d, 1))
+                    the_draws.append(int(d[0]))
+                else:
+                    d = np.asarray(draws[k]).reshape(-1)
+                    if d.size < 1:
+                        raise _lib.FriccError(_lib.EDRAWS, "systematic sampling needs one draw")
+                    the_draws.append(int(d[0]))
             consumed = 1
             check(L.fricc_shard_use_probabilities(shard.h, r, nsamp, ctypes.c_uint64(key_cut), ctypes.c_uint64(idx_cut)))
-            flat = torch.zeros(max(m, 1), dtype=torch.int64, device=dev)[:m]
-            if nD > 0:
-                flat[:nD] = idx[:nD] if comm.rank == 0 else 0    # summed over ranks below: rank 0 contributes D
             if nsamp > 0:
-                exact_sum(shard, comm)
-                check(L.fricc_shard_emit_systematic(shard.h, nsamp, draw, _ptr(flat[nD:])))
+                exact_sum(shard, comm)          # exact running sums of p at the chunk starts: shared by all draws
+            for k in range(count):
+                if nD > 0 and comm.rank == 0:   # summed over ranks below: rank 0 contributes D
+                    flat[k * mm: k * mm + nD] = idx[:nD]
+                if nsamp > 0:
+                    check(L.fricc_shard_emit_systematic(shard.h, nsamp, the_draws[k], _ptr(flat[k * mm + nD:])))
             _all_reduce(comm, flat)
             n_exact = nD
-        vals = torch.zeros(max(m, 1), dtype=torch.float64, device=dev)[:m]
-        check(L.fricc_shard_values(shard.h, _ptr(flat), m, n_exact, _ptr(vals)))
+        for k in range(count):
+            check(L.fricc_shard_values(shard.h, _ptr(flat[k * mm:]), m, n_exact, _ptr(vals[k * mm:])))
         _all_reduce(comm, vals)
         # a kernel error on any rank (some p > 1: fri_utils.cpp:383-395) is raised on every rank
         err = torch.zeros(1, dtype=torch.int64, device=dev)
@@ -270,9 +298,12 @@ def compress_ranges(x_local, j0, dims, m, comm, compression="fri", sampling_meth
         _all_reduce(comm, err, "max")
         if int(err.item()):
             raise msg if msg is not None else _lib.FriccError(_lib.EPROB, "ERROR MAKING PROBABILITY VECTOR on another rank")
-        T = SparseTensor4d.from_coo(flat, vals, dims)
-        check(L.fricc_st_set_n_exact(T._h, int(n_exact)))
-        T.consumed_draws = consumed
-        return T
+        out = []
+        for k in range(count):
+            T = SparseTensor4d.from_coo(flat[k * mm: k * mm + m], vals[k * mm: k * mm + m], dims)
+            check(L.fricc_st_set_n_exact(T._h, int(n_exact)))
+            T.consumed_draws = consumed
+            out.append(T)
+        return out
     finally:
         shard.close()

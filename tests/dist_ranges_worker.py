@@ -61,6 +61,17 @@ def main():
             if not good:
                 print(f"rank {rank}: MISMATCH dims={dims} kind={kind} {compression}", flush=True)
             ok &= good
+        # the two compressions of one iteration, sharing norm / D / running sums: equal to two constructor calls
+        draw2 = rng.integers(0, 2**31 - 1, size=1).astype(np.int32)
+        A, B = ranges.compress_ranges_pair(mine, j0, dims, m, comm, "fri", "systematic", draws=(draw, draw2))
+        ok &= same(A, py_rccsd.SparseTensor4d(full, dims, m, "fri", "systematic", False, draws=draw))
+        ok &= same(B, py_rccsd.SparseTensor4d(full, dims, m, "fri", "systematic", False, draws=draw2))
+        py_rccsd.srand(9)
+        A, B = ranges.compress_ranges_pair(mine, j0, dims, m, comm, "fri", "systematic")
+        pos2 = py_rccsd.rand_consumed()
+        py_rccsd.srand(9)
+        ok &= same(A, py_rccsd.SparseTensor4d(full, dims, m, "fri", "systematic"))
+        ok &= same(B, py_rccsd.SparseTensor4d(full, dims, m, "fri", "systematic")) and pos2 == 2
         # the library's own rand() stream: one draw consumed, as the reference's lin_space_add_const does
         py_rccsd.srand(5)
         T = ranges.compress_ranges(mine, j0, dims, m, comm, "fri", "systematic")
