@@ -64,6 +64,10 @@ def parse_args():
                         "of T2, all-reduced key histograms, norm / D / running sums shared by both draws (systematic "
                         "sampler; default for it); 'pair' = whole compressions task-parallel on even/odd ranks; "
                         "'replicated' = both on every rank")
+    p.add_argument("--push-inline", action="store_true",
+                   help="N>1, peer exchange: issue the stores into the peers on the compute stream (A/B of the side-stream "
+                        "push that runs them under the next term's kernel)")
+    p.add_argument("--push-ctas", type=int, default=0, help="peer-store kernels: CTAs per SM (0 = library default)")
     p.add_argument("--no-overlap", action="store_true", help="N>1: one blocking exchange per term (A/B of the pipelined step)")
     return p.parse_args()
 
@@ -207,6 +211,7 @@ class Iteration:
         self.terms["0113"].set_panel(self.terms["0112"].panel, planes_from=self.terms["0112"])
         self.terms["0312"].set_panel(self.terms["0313"].panel, planes_from=self.terms["0313"])
         self.peer = comm.world > 1 and args.exchange == "peer" and not args.no_overlap and not args.only_ladder
+        self.side = None
         if self.peer:
             # the outputs live in one symmetric allocation per rank: every rank stores its columns into all copies
             nb = 8 * (o ** 4 + 2 * v * o * o * v + 4 * o * o * v * v) + 8 * 4096
@@ -397,6 +402,9 @@ class Iteration:
              column axis adds to it,
           B2 at the end of the step."""
         tm, dims, push = self.terms, (self.o, self.o, self.v, self.v), self.fd.push_columns
+        if self.side is None and not self.args.push_inline:
+            self.side = self.fd.SideStream(self.device)
+        S = None if self.args.push_inline else self.side   # peer stores run on it, under the next term's kernel
         self.Wklij.zero_(); self.Wakic.zero_(); self.Wakci.zero_()
         self.t2new.zero_()
         for t in self.tmp:
@@ -404,12 +412,8 @@ class Iteration:
         self.rank_barrier()
         self.mark("zero_outputs_B0")
         A = self.arena
-        tm["1323"].accumulate(T_alt, self.Wklij, arena=A)
-        self.mark("1323")
-        tm["0112"].accumulate(T_alt, self.Wakic, also=(tm["0313"], tm["0113"]), arena=A)
-        self.mark("0112_0313_0113")
-        tm["0312"].accumulate(T_alt, self.Wakci, arena=A)
-        self.mark("0312")
+        # the ladder first: its 2 GB push then hides under the ovov terms; the o^4-sized output goes last, so that
+        # only its (tiny) push is exposed in front of the barrier
         lad = tm["2323"]
         for s_, (c, w) in enumerate(self.sub):
             if not self.resident:
@@ -423,19 +427,29 @@ class Iteration:
             lad.local_into(T, self.t2new, panel=self.lad_panel, l0=lad.l0 + c, lcnt=w)
             e1.record()
             self.ladder_events.append((e0, e1, w))
-        push(lad, dims, self.t2new, A)
+        push(lad, dims, self.t2new, A, side=S)
         self.mark("2323" if self.resident else "2323_incl_regen")
+        tm["0112"].accumulate(T_alt, self.Wakic, also=(tm["0313"], tm["0113"]), arena=A, side=S)
+        self.mark("0112_0313_0113")
+        tm["0312"].accumulate(T_alt, self.Wakci, arena=A, side=S)
+        self.mark("0312")
+        tm["1323"].accumulate(T_alt, self.Wklij, arena=A, side=S)
+        self.mark("1323")
+        if S is not None:
+            S.join()
         self.rank_barrier()
         self.mark("B1")
-        tm["0101"].permute_from(self.Wklij); tm["0101"].accumulate(T, self.t2new, arena=A)
-        self.mark("0101")
         tm["1302"].permute_from(self.Wakic); tm["1202"].permute_from(self.Wakci)
-        tm["1302"].accumulate(T, self.tmp[0], also=(tm["1202"],), arena=A)
+        tm["1302"].accumulate(T, self.tmp[0], also=(tm["1202"],), arena=A, side=S)
         self.mark("1302_1202")
-        tm["1303"].set_panel(tm["1302"].panel, planes_from=tm["1302"]); tm["1303"].accumulate(T, self.tmp[1], arena=A)
+        tm["1303"].set_panel(tm["1302"].panel, planes_from=tm["1302"]); tm["1303"].accumulate(T, self.tmp[1], arena=A, side=S)
         self.mark("1303")
-        tm["1203"].set_panel(tm["1202"].panel, planes_from=tm["1202"]); tm["1203"].accumulate(T, self.tmp[2], arena=A)
+        tm["1203"].set_panel(tm["1202"].panel, planes_from=tm["1202"]); tm["1203"].accumulate(T, self.tmp[2], arena=A, side=S)
         self.mark("1203")
+        tm["0101"].permute_from(self.Wklij); tm["0101"].accumulate(T, self.t2new, arena=A, side=S)
+        self.mark("0101")
+        if S is not None:
+            S.join()
         self.rank_barrier()
         self.mark("B2")
         return T
@@ -615,6 +629,8 @@ def run_b200_arm(args):
     fd.use_torch_stream()
     L = _lib.lib()
 
+    if args.push_ctas > 0:
+        _lib.check(L.fricc_set_option(b"push_ctas_per_sm", args.push_ctas))
     it = Iteration(args, comm, device)
     o, v, m = it.o, it.v, it.m
     lad = it.terms["2323"]
@@ -741,7 +757,8 @@ def run_b200_arm(args):
             "ladder_ms_per_step": sum(lad_ms) / args.steps, "stage_ms_per_step": stage_ms, "output_checksums": checks,
             "schedule": ("single rank" if world == 1 else "blocking NCCL exchange per term" if args.no_overlap else
                          "peer memory: each rank accumulates its columns in place and stores them into every peer's copy "
-                         "over NVLink; 3 stream-ordered barriers per step, no NCCL on the data path" if it.peer else
+                         "over NVLink" + (" on the compute stream" if args.push_inline else " on a side stream under the next term's kernel") +
+                         "; 3 stream-ordered barriers per step, no NCCL on the data path" if it.peer else
                          "pipelined: NCCL all-gathers overlap the next term's kernel; 7 exchanges for 11 terms"),
             "timed_segments": "whole steps" if it.resident else
                               f"sum of segments; ladder W regenerated in HBM between {len(it.sub)} column sub-shards",

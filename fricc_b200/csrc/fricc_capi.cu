@@ -13,6 +13,8 @@ const std::string& last_error();
 void set_stream(cudaStream_t s);
 int64_t launches();
 void reset_device_cache();
+void set_push_ctas_per_sm(int n);  // fricc_peer.cu: grid cap of the peer-store kernels (CTAs per SM)
+void set_push_carveout(int pct);   // fricc_peer.cu: L1/shared split the peer-store kernels ask for (-1: default)
 }  // namespace fricc
 
 using namespace fricc;
@@ -135,6 +137,8 @@ int fricc_set_option(const char* key, int value) {
   else if (key && strcmp(key, "d_estimate") == 0) set_d_estimate(value);
   else if (key && strcmp(key, "pivotal_parallel") == 0) set_pivotal_parallel(value);
   else if (key && strcmp(key, "d_parallel") == 0) set_d_parallel(value);
+  else if (key && strcmp(key, "push_ctas_per_sm") == 0) set_push_ctas_per_sm(value);
+  else if (key && strcmp(key, "push_carveout") == 0) set_push_carveout(value);
   else if (key && strncmp(key, "spmm_", 5) == 0) set_spmm_option(key, value);
   else if (key && strncmp(key, "tc_", 3) == 0) set_tc_option(key, value);
   else fail(FRICC_EINVAL, "unknown option '%s'", key ? key : "(null)");

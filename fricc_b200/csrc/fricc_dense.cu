@@ -496,7 +496,7 @@ struct TcParams {
   int beta;  // 1: out += result (read-modify-write); 0: out = result (the caller knows out holds nothing yet)
 };
 
-__global__ void __launch_bounds__(TC_THREADS, 1)
+__global__ void __maxnreg__(128)  // 320 threads x 128 = 40 960 registers: leaves 24 576 for three 256-thread peer-store CTAs (fricc_peer.cu)
 tc_sign_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const TcParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);

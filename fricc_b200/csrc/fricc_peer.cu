@@ -20,29 +20,51 @@ struct PeerPtrs {
 
 // thread <-> one element of this rank's column slice; FAST = which index runs along threadIdx.x:
 //   0: l (the free pair; contiguous when out's unit-stride axis is the L-minor one)      1: R (owner pair)
+// The grid is CAPPED (push_grid below) and every CTA walks "virtual blocks": the stores are NVLink-bound, a couple of
+// CTAs per SM saturate the links, and the kernel then leaves thread slots, registers and shared memory free for the
+// tensor-core kernel of the NEXT term, which runs concurrently on the compute stream (dist.SideStream).
 template <int FAST>
 __global__ void __launch_bounds__(256)
 push_columns_kernel(const double* __restrict__ src, PeerPtrs peers, int n_peers, int self, OutMap om, int64_t nR,
-                    int64_t l_begin, int64_t l_count) {
-  int64_t R, c;
-  if (FAST == 0) {
-    c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    R = blockIdx.y;
-  } else {
-    R = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    c = blockIdx.y;
+                    int64_t l_begin, int64_t l_count, int64_t nbx, int64_t nvb) {
+  for (int64_t vb = blockIdx.x; vb < nvb; vb += gridDim.x) {
+    const int64_t by = vb / nbx, bx = vb - by * nbx;
+    int64_t R, c;
+    if (FAST == 0) {
+      c = bx * 256 + threadIdx.x;
+      R = by;
+    } else {
+      R = bx * 256 + threadIdx.x;
+      c = by;
+    }
+    if (R >= nR || c >= l_count) continue;
+    const int64_t l = l_begin + c;
+    const int64_t r1 = R / om.nR2, r2 = R - r1 * om.nR2;
+    const int64_t l1 = l / om.nL2, l2 = l - l1 * om.nL2;
+    const int64_t o = r1 * om.sR1 + r2 * om.sR2 + l1 * om.sL1 + l2 * om.sL2;
+    const double v = src[o];
+    for (int d = 1; d < n_peers; d++) {
+      int q = self + d;
+      if (q >= n_peers) q -= n_peers;
+      peers.p[q][o] = v;
+    }
   }
-  if (R >= nR || c >= l_count) return;
-  const int64_t l = l_begin + c;
-  const int64_t r1 = R / om.nR2, r2 = R - r1 * om.nR2;
-  const int64_t l1 = l / om.nL2, l2 = l - l1 * om.nL2;
-  const int64_t o = r1 * om.sR1 + r2 * om.sR2 + l1 * om.sL1 + l2 * om.sL2;
-  const double v = src[o];
-  for (int d = 1; d < n_peers; d++) {
-    int q = self + d;
-    if (q >= n_peers) q -= n_peers;
-    peers.p[q][o] = v;
-  }
+}
+
+static int g_push_ctas_per_sm = 2;  // 2 x 256 threads x 32 registers fit beside the tensor-core CTA (320 x 128); 3 do not
+static int g_push_carveout = 100;  // percent of the L1/shared array configured as shared memory; -1 = leave the default
+void set_push_ctas_per_sm(int n) { g_push_ctas_per_sm = n < 1 ? 1 : n; }
+void set_push_carveout(int pct) { g_push_carveout = pct; }
+// An SM runs CTAs of two kernels side by side only under ONE L1/shared split.  The tensor-core kernel needs ~198 KB of
+// shared memory, i.e. the maximum-shared split; these kernels ask for the same split so that they can share the SMs
+// with it instead of waiting for them to drain.
+template <typename K>
+static void prefer_split(K kernel) {
+  if (g_push_carveout >= 0)
+    FRICC_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, g_push_carveout));
+}
+static unsigned push_grid(int64_t nvb) {
+  return (unsigned)std::max<int64_t>(1, std::min<int64_t>(nvb, (int64_t)num_sms() * g_push_ctas_per_sm));
 }
 
 void push_columns(const double* out_local, double* const* peer_out, int n_peers, int self, const OutMap& om, int64_t nR,
@@ -53,19 +75,15 @@ void push_columns(const double* out_local, double* const* peer_out, int n_peers,
   for (int q = 0; q < MAX_PEERS; q++) pp.p[q] = q < n_peers ? peer_out[q] : nullptr;
   const bool r_fast = om.sL2 != 1 && (om.sR2 == 1 || (om.nR2 == 1 && om.sR1 == 1));
   if (!r_fast) {
-    if (nR > 65535) {
-      // many rows, few columns per row would waste the grid's y limit: fall through to the R-fast shape
-      dim3 grid((unsigned)ceil_div(nR, 256), (unsigned)l_count);
-      if (l_count > 65535) fail(FRICC_EINVAL, "push_columns: shape too large");
-      FRICC_LAUNCH(push_columns_kernel<1>, grid, 256, 0, out_local, pp, n_peers, self, om, nR, l_begin, l_count);
-      return;
-    }
-    dim3 grid((unsigned)ceil_div(l_count, 256), (unsigned)nR);
-    FRICC_LAUNCH(push_columns_kernel<0>, grid, 256, 0, out_local, pp, n_peers, self, om, nR, l_begin, l_count);
+    const int64_t nbx = ceil_div(l_count, 256), nvb = nbx * nR;
+    prefer_split(push_columns_kernel<0>);
+    FRICC_LAUNCH(push_columns_kernel<0>, push_grid(nvb), 256, 0, out_local, pp, n_peers, self, om, nR, l_begin, l_count,
+                 nbx, nvb);
   } else {
-    if (l_count > 65535) fail(FRICC_EINVAL, "push_columns: shape too large");
-    dim3 grid((unsigned)ceil_div(nR, 256), (unsigned)l_count);
-    FRICC_LAUNCH(push_columns_kernel<1>, grid, 256, 0, out_local, pp, n_peers, self, om, nR, l_begin, l_count);
+    const int64_t nbx = ceil_div(nR, 256), nvb = nbx * l_count;
+    prefer_split(push_columns_kernel<1>);
+    FRICC_LAUNCH(push_columns_kernel<1>, push_grid(nvb), 256, 0, out_local, pp, n_peers, self, om, nR, l_begin, l_count,
+                 nbx, nvb);
   }
 }
 
@@ -81,11 +99,13 @@ template <int XMODE>
 __global__ void __launch_bounds__(256)
 scatter_panel_tiled_kernel(const double* __restrict__ panel, int64_t ld, int64_t l_begin, int64_t l_count, int64_t nR1,
                            int64_t l1_first, int64_t n_l1, double* __restrict__ out, PeerPtrs peers, int n_peers,
-                           int self, OutMap om) {
+                           int self, OutMap om, int64_t n_fixed, int64_t n_xb, int64_t nvb) {
   __shared__ double tile[32][33];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  const int64_t fixed = blockIdx.x;
-  const int64_t x0 = (int64_t)blockIdx.y * 32, q0 = (int64_t)blockIdx.z * 32;  // q = l2
+  for (int64_t vb = blockIdx.x; vb < nvb; vb += gridDim.x) {  // capped grid, see push_columns_kernel
+  const int64_t fixed = vb % n_fixed;
+  const int64_t vb2 = vb / n_fixed;
+  const int64_t x0 = (vb2 % n_xb) * 32, q0 = (vb2 / n_xb) * 32;  // q = l2
   int64_t r1 = 0, r2 = 0, l1 = 0, nX;
   if (XMODE == 0) { r2 = fixed % om.nR2; l1 = l1_first + fixed / om.nR2; nX = nR1; }
   else { r2 = fixed % om.nR2; r1 = fixed / om.nR2; nX = n_l1; }
@@ -116,6 +136,8 @@ scatter_panel_tiled_kernel(const double* __restrict__ panel, int64_t ld, int64_t
         }
       }
     }
+  }
+  __syncthreads();  // the tile is reused by the next virtual block
   }
 }
 
@@ -155,13 +177,19 @@ void scatter_panel(const double* panel, int64_t ld, int64_t l_begin, int64_t l_c
     else if (om.sL1 == 1) { xmode = 2; fixed = nR1 * om.nR2; nX = n_l1; }
   }
   if (xmode >= 0 && fixed > 0 && fixed < ((int64_t)1 << 31) && ceil_div(nX, 32) <= 65535 && ceil_div(om.nL2, 32) <= 65535) {
-    dim3 grid((unsigned)fixed, (unsigned)ceil_div(nX, 32), (unsigned)ceil_div(om.nL2, 32));
+    const int64_t n_xb = ceil_div(nX, 32), nvb = fixed * n_xb * ceil_div(om.nL2, 32);
+    // without peers this is a local HBM-bound pass: let it fill the GPU
+    const unsigned grid = peer_out ? push_grid(nvb) : (unsigned)std::min<int64_t>(nvb, (int64_t)num_sms() * 8);
+    if (peer_out) {
+      prefer_split(scatter_panel_tiled_kernel<0>);
+      prefer_split(scatter_panel_tiled_kernel<2>);
+    }
     if (xmode == 0)
       FRICC_LAUNCH(scatter_panel_tiled_kernel<0>, grid, 256, 0, panel, ld, l_begin, l_count, nR1, l1_first, n_l1, out, pp,
-                   n_peers, self, om);
+                   n_peers, self, om, fixed, n_xb, nvb);
     else
       FRICC_LAUNCH(scatter_panel_tiled_kernel<2>, grid, 256, 0, panel, ld, l_begin, l_count, nR1, l1_first, n_l1, out, pp,
-                   n_peers, self, om);
+                   n_peers, self, om, fixed, n_xb, nvb);
     return;
   }
   FRICC_LAUNCH(scatter_panel_kernel, (unsigned)ceil_div(nR * l_count, 256), 256, 0, panel, ld, l_begin, l_count, nR, out,

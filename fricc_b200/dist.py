@@ -228,31 +228,40 @@ class ShardedTerm:
         st = out.stride()
         return st[ax["oL"][1]] == 1 or st[ax["oR"][1]] == 1
 
-    def accumulate(self, T, out, also=(), arena=None):
+    def accumulate(self, T, out, also=(), arena=None, side=None):
         """out[.., this rank's L-columns, ..] += this term (+ the terms in `also`, which must map (R, L) onto `out` the
         same way and use the same T).  With an arena (SymmArena holding `out` on every rank) the finished columns are
         also stored into every peer's copy -- the exchange step.  Terms whose output's unit-stride axis is R-major /
         L-major (1302, 1202, 1303, 1203 on a C-contiguous t2new) go through a coalesced [R][lc] panel and one
-        transposing scatter pass; the others write straight from the kernel's epilogue."""
+        transposing scatter pass; the others write straight from the kernel's epilogue.
+        side: a SideStream -- the stores into the peers (NVLink-bound, a few SMs' worth of work) are issued on it behind
+        the compute, so they run under the NEXT term's kernel; the caller joins it before the next barrier."""
         terms = (self,) + tuple(also)
         for t in terms:
             assert (t.nR, t.lc, t.l0) == (self.nR, self.lc, self.l0)
         peers = arena.peers_of(out) if (arena is not None and self.comm.world > 1) else None
+        if peers is None:
+            side = None
         if self.direct_ok(out):
             for t in terms:
                 t.local_into(T, out)
             if peers is not None and self.lcnt > 0:
-                check(self.L.fricc_push_columns(_ptr(out), peers, self.comm.world, self.comm.rank, self.term.encode(),
-                                                i64x4(self.t_dims), i64x4(out.shape), i64x4(out.stride()), self.l0,
-                                                self.lcnt))
+                def push():
+                    check(self.L.fricc_push_columns(_ptr(out), peers, self.comm.world, self.comm.rank,
+                                                    self.term.encode(), i64x4(self.t_dims), i64x4(out.shape),
+                                                    i64x4(out.stride()), self.l0, self.lcnt))
+                side.run(push) if side is not None else push()
             return
         self.local(T)
         for t in also:
             t.local(T, into=self)
         if self.lcnt > 0:
-            check(self.L.fricc_scatter_panel(_ptr(self.out_panel), self.lc, self.l0, self.lcnt, self.term.encode(),
-                                             i64x4(self.t_dims), _ptr(out), peers, self.comm.world if peers else 1,
-                                             self.comm.rank if peers else 0, i64x4(out.shape), i64x4(out.stride())))
+            def scatter():
+                check(self.L.fricc_scatter_panel(_ptr(self.out_panel), self.lc, self.l0, self.lcnt, self.term.encode(),
+                                                 i64x4(self.t_dims), _ptr(out), peers, self.comm.world if peers else 1,
+                                                 self.comm.rank if peers else 0, i64x4(out.shape),
+                                                 i64x4(out.stride())))
+            side.run(scatter) if side is not None else scatter()
 
     def __call__(self, T, out, W=None):
         if W is not None:
@@ -409,13 +418,38 @@ class SymmArena:
             self.base = ctypes.c_void_p()
 
 
-def push_columns(term_obj, t_dims, out, arena):
+def push_columns(term_obj, t_dims, out, arena, side=None):
     """Store this rank's L-columns of `out` (already accumulated locally) into every peer's copy."""
     if term_obj.comm.world == 1 or term_obj.lcnt <= 0:
         return
-    check(term_obj.L.fricc_push_columns(_ptr(out), arena.peers_of(out), term_obj.comm.world, term_obj.comm.rank,
-                                        term_obj.term.encode(), i64x4(t_dims), i64x4(out.shape), i64x4(out.stride()),
-                                        term_obj.l0, term_obj.lcnt))
+
+    def push():
+        check(term_obj.L.fricc_push_columns(_ptr(out), arena.peers_of(out), term_obj.comm.world, term_obj.comm.rank,
+                                            term_obj.term.encode(), i64x4(t_dims), i64x4(out.shape),
+                                            i64x4(out.stride()), term_obj.l0, term_obj.lcnt))
+    side.run(push) if side is not None else push()
+
+
+class SideStream:
+    """A second CUDA stream for the peer stores of the exchange step.  run(fn): fn's library calls are issued on the
+    side stream, ordered behind everything queued on the current stream so far; join(): the current stream waits for
+    everything issued on the side stream (call it before a barrier, or before the pushed output is written again)."""
+
+    def __init__(self, device):
+        self.stream = torch.cuda.Stream(device=device)
+        self.L = _lib.lib()
+
+    def run(self, fn):
+        main = torch.cuda.current_stream()
+        self.stream.wait_stream(main)
+        check(self.L.fricc_set_stream(ctypes.c_void_p(self.stream.cuda_stream)))
+        try:
+            fn()
+        finally:
+            check(self.L.fricc_set_stream(ctypes.c_void_p(main.cuda_stream)))
+
+    def join(self):
+        torch.cuda.current_stream().wait_stream(self.stream)
 
 
 # range-sharded compression (x split by contiguous flat-index ranges; all-reduced key histograms): fricc_b200/ranges.py

@@ -52,7 +52,11 @@ int fricc_stream_synchronize(void);
  * it grows x16 until the greedy test stops inside the list -- any value gives identical results); "d_estimate": 1
  * (default) sizes that list from a count+sum histogram estimate of where the greedy test stops, 0 = geometric growth only.
  * "escan": 1 (default) = exact running sums by the parallel binade-segmented scan,
- * 0 = by the one-thread chain kernels (bit-identical results, kept as the in-library cross-check).               */
+ * 0 = by the one-thread chain kernels (bit-identical results, kept as the in-library cross-check).
+ * "push_ctas_per_sm": grid cap of the peer-store kernels (default 2 CTAs per SM: NVLink-bound, and it leaves thread
+ * slots and registers to the contraction kernel that runs concurrently on the compute stream); "push_carveout": the
+ * L1/shared split (percent shared) those kernels ask for, default 100 = the split the tensor-core kernel runs under,
+ * so that both can be resident on one SM; -1 = the device default.                                               */
 int fricc_set_option(const char* key, int value);
 /* "d_parallel": -1 (default) = the parallel D-selection for candidate lists >= 32768 and the one-warp walk below,
  * 0 / 1 = always serial / always parallel (bit-identical).

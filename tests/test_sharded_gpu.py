@@ -98,8 +98,8 @@ def test_accumulate_into_strided_output(rccsd, port):
 
 
 @pytest.mark.parametrize("term", sorted(TERMS))
-@pytest.mark.parametrize("no,nv,world", [(3, 5, 2), (6, 21, 3), (5, 40, 4)])
-def test_peer_push_exchange(rccsd, port, term, no, nv, world):
+@pytest.mark.parametrize("no,nv,world,side", [(3, 5, 2, False), (6, 21, 3, True), (5, 40, 4, False), (5, 40, 4, True)])
+def test_peer_push_exchange(rccsd, port, term, no, nv, world, side):
     """The exchange over peer memory (fricc_peer.cu), ranks emulated one after another on one GPU: rank g accumulates
     its L-columns into ITS copy of the output and stores them into every other copy; afterwards all copies hold the
     full result.  The "peer" copies are ordinary buffers of this process (same kernel, same addressing)."""
@@ -124,11 +124,15 @@ def test_peer_push_exchange(rccsd, port, term, no, nv, world):
         def peers_of(self, t):
             return peers
 
+    fd.use_torch_stream()
+    S = fd.SideStream(dev) if side else None   # peer stores issued on a second stream behind the compute
     for g in range(world):
         st = fd.ShardedTerm(term, no, nv, fd.Comm(g, world), dev)
         st.permute_from(Wd)
         # direct epilogue write + column push, or coalesced panel + transposing scatter (1302/1202/1303/1203)
-        st.accumulate(T, copies[g], arena=FakeArena())
+        st.accumulate(T, copies[g], arena=FakeArena(), side=S)
+        if S is not None:
+            S.join()
     for c in copies:
         got = c.cpu().numpy()
         assert np.abs(got - want).max() <= TOL * max(1.0, np.abs(want).max())

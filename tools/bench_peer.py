@@ -31,7 +31,14 @@ def main():
         bufs[shp] = arena.tensor(shp).zero_()
     flag = torch.zeros(1, device=dev)
     res = {}
-    for term, shp in shapes.items():
+    sweep = "--sweep" in sys.argv   # push throughput against the grid cap of the peer-store kernels
+    caps = (1, 2, 4, 8, 16) if sweep else (None,)
+    if sweep:
+        shapes = {k: shapes[k] for k in ("2323", "1302")}
+    for cap in caps:
+      if cap is not None:
+        _lib.check(_lib.lib().fricc_set_option(b"push_ctas_per_sm", cap))
+      for term, shp in shapes.items():
         out = bufs[shp]
         st = fd.ShardedTerm(term, o, v, comm, dev)
         st.out_panel = torch.rand(st.nR * st.lc, dtype=torch.float64, device=dev)
@@ -51,7 +58,7 @@ def main():
                 e1.record()
                 torch.cuda.synchronize()
                 ts.append(e0.elapsed_time(e1))
-            res[f"{term}_{mode}"] = round(min(ts), 3)
+            res[f"{term}_{mode}" + (f"_cap{cap}" if cap is not None else "")] = round(min(ts), 3)
     # NCCL all-gather of one output's worth of panels
     n = o * o * v * v
     src = torch.rand(n // world, dtype=torch.float64, device=dev)
