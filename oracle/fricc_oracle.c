@@ -167,6 +167,103 @@ int orc_sample_pivotal(int64_t n_sample, const double* probs, int64_t n, const i
   return ORC_OK;
 }
 
+/* ---- parallel_sample ("Alg. A.2"): fri_utils.cpp:176-362 -----------------------------------------------------------
+ * q is cut into n_chunks contiguous chunks (the reference uses omp_get_max_threads(); the last chunk takes the
+ * remainder, :183-184,199,216-219).  Per chunk: budget a_j = n_sample * |q_j|_1 / |q|_1, g_j = floor(a_j),
+ * t_j = a_j - g_j (:226-231); the c = n_sample - sum g_j left-over samples are given to chunks by a pivotal draw over t
+ * (:268-275); a chunk whose budget was rounded up / down has its leading probabilities raised / lowered until its mass
+ * is the integer g_j (:303-322); each chunk is then sampled with sample_pivotal (:345) and the indices are offset by
+ * j*step and concatenated in chunk order (:353-356).
+ * Draw order: the reference's threads call rand() concurrently, i.e. the order is a race for n_chunks > 1.  This
+ * restatement consumes the draws in chunk order (chunk j after chunk j-1) -- what the reference does whenever its
+ * threads happen to run one after another, and exactly what it does with one thread.  Pinned against oracle/_ref with
+ * one thread (random draws) and with several threads on a constant draw stream (where the race cannot matter).
+ * work: n doubles of scratch (the per-chunk copies qj, :196-198).                                                   */
+int orc_parallel_sample(int64_t n_sample, const double* q, int64_t n, int n_chunks, const int32_t* draws,
+                        int64_t n_draws, int64_t* S, int64_t* consumed, double* work) {
+  int64_t step, rem, c, used = 0, k, lb = 0;
+  double q_norm;
+  double *t, *a, *norms;
+  int64_t *g, *sp;
+  int j, rc = ORC_OK;
+  if (n_chunks < 1 || n < 0 || n_sample < 0) return ORC_EINVAL;
+  step = n / n_chunks;
+  rem = n % n_chunks;
+  t = (double*)malloc(sizeof(double) * (size_t)n_chunks * 3);
+  g = (int64_t*)malloc(sizeof(int64_t) * (size_t)n_chunks * 2 + sizeof(int64_t));
+  if (!t || !g) {
+    free(t);
+    free(g);
+    return ORC_EINVAL;
+  }
+  a = t + n_chunks;
+  norms = a + n_chunks;
+  sp = g + n_chunks;
+  *consumed = 0;
+  q_norm = orc_one_norm(q, n); /* :191 */
+  c = n_sample;
+  for (j = 0; j < n_chunks; j++) { /* :214-237 */
+    int64_t lo = (int64_t)j * step, len = step + ((j + 1 == n_chunks) ? rem : 0);
+    memcpy(work + lo, q + lo, sizeof(double) * (size_t)len);
+    norms[j] = orc_one_norm(work + lo, len);
+    a[j] = (double)n_sample * norms[j] / q_norm; /* size_t * double / double, left to right */
+    t[j] = a[j] - floor(a[j]);
+    g[j] = (int64_t)(int)floor(a[j]); /* std::vector<int> g */
+    c -= g[j];
+  }
+  /* :268  s_prime = sample_pivotal(c, t);  c is a size_t in the reference: a negative value cannot be sampled */
+  if (c < 0) {
+    rc = ORC_ECOUNT;
+    goto done;
+  }
+  {
+    int64_t u = 0;
+    rc = orc_sample_pivotal(c, t, n_chunks, draws, n_draws, sp, &u);
+    used += u;
+    if (rc != ORC_OK) goto done;
+    for (k = 0; k < c; k++) g[sp[k]] += 1; /* :269-275 */
+  }
+  for (j = 0; j < n_chunks; j++) { /* :297-357, chunk order */
+    int64_t lo = (int64_t)j * step, len = step + ((j + 1 == n_chunks) ? rem : 0), i, u = 0;
+    double* qj = work + lo;
+    double sj = norms[j];
+    const double gj = (double)g[j];
+    if (gj > a[j]) { /* :303-312 */
+      for (i = 0; i < len; i++) {
+        double yji = qj[i] / t[j];
+        if (!(yji < 1.)) yji = 1.; /* std::min(1., x): returns 1. unless x < 1. */
+        sj += yji - qj[i];
+        qj[i] = yji;
+        if (sj >= gj) {
+          qj[i] = yji + gj - sj;
+          break;
+        }
+      }
+    } else if (gj < a[j]) { /* :313-322 */
+      for (i = 0; i < len; i++) {
+        double yji = (qj[i] - t[j]) / (1. - t[j]);
+        if (!(0. < yji)) yji = 0.; /* std::max(0., x): returns 0. unless 0. < x */
+        sj += yji - qj[i];
+        qj[i] = yji;
+        if (sj <= gj) {
+          qj[i] = yji + gj - sj;
+          break;
+        }
+      }
+    }
+    rc = orc_sample_pivotal(g[j], qj, len, draws + used, n_draws - used, S + lb, &u); /* :345 */
+    used += u;
+    if (rc != ORC_OK) goto done;
+    for (i = 0; i < g[j]; i++) S[lb + i] += lo; /* :351-353  incr = j * step */
+    lb += g[j];
+  }
+done:
+  *consumed = used;
+  free(t);
+  free(g);
+  return rc;
+}
+
 /* ---- sample_systematic + lin_space_add_const: fri_utils.cpp:129-159, 45-58 --------------------------------------- */
 int orc_sample_systematic(int64_t n_sample, const double* probs, int64_t n, const int32_t* draws, int64_t n_draws,
                           int64_t* S, int64_t* consumed) {

@@ -75,6 +75,8 @@ class Port:
         L.orc_fri_compression.argtypes = [c_void_p, c_int64, c_int64, c_int, c_void_p, c_int64, c_void_p, c_void_p,
                                           POINTER(c_int64), POINTER(c_double), POINTER(c_int64)]
         L.orc_largest.argtypes = [c_void_p, c_int64, c_int64, c_void_p, c_void_p]
+        L.orc_parallel_sample.argtypes = [c_int64, c_void_p, c_int64, c_int, c_void_p, c_int64, c_void_p,
+                                          POINTER(c_int64), c_void_p]
         L.orc_contract.argtypes = [c_char_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p,
                                    c_void_p]
         self.L = L
@@ -126,6 +128,16 @@ class Port:
         S = np.zeros(max(int(n_sample), 1), dtype=np.int64)
         used = c_int64(0)
         self._chk(self.L.orc_sample_systematic(int(n_sample), _p(p), p.size, _p(d), d.size, _p(S), ctypes.byref(used)))
+        return S[: int(n_sample)].copy(), used.value
+
+    def parallel_sample(self, n_sample, probs, n_chunks, draws):
+        """fri_utils.cpp:176-362 with `n_chunks` chunks, draws consumed in chunk order -> (S, consumed)"""
+        p, d = _f64(probs).ravel(), _i32(draws)
+        S = np.zeros(max(int(n_sample), 1), dtype=np.int64)
+        work = np.empty(max(p.size, 1), dtype=np.float64)
+        used = c_int64(0)
+        self._chk(self.L.orc_parallel_sample(int(n_sample), _p(p), p.size, int(n_chunks), _p(d), d.size, _p(S),
+                                             ctypes.byref(used), _p(work)))
         return S[: int(n_sample)].copy(), used.value
 
     def fri_compression(self, x, n_sample, method, draws):
@@ -192,6 +204,9 @@ class Ref:
         L.ref_sample_pivotal.argtypes = [c_long, c_void_p, c_long, c_void_p]
         L.ref_sample_systematic.argtypes = [c_long, c_void_p, c_long, c_void_p]
         L.ref_fri_compression.argtypes = [c_void_p, c_long, c_long, c_char_p, c_int, c_void_p, c_void_p]
+        if hasattr(L, "ref_parallel_sample"):
+            L.ref_parallel_sample.restype = c_long
+            L.ref_parallel_sample.argtypes = [c_long, c_void_p, c_long, c_int, c_void_p]
         self.L = L
 
     def set_draws(self, draws):
@@ -244,6 +259,17 @@ class Ref:
         used = self.rand_calls()
         self.clear_draws()
         return S[: int(n_sample)].copy(), used
+
+    def parallel_sample(self, n_sample, probs, n_threads, draws):
+        """The reference's parallel_sample with omp_set_num_threads(n_threads).  Reproducible only for n_threads == 1
+        or a constant draw stream (its threads call rand() concurrently).  -> (S, rand() calls)"""
+        p = _f64(probs).ravel()
+        self.set_draws(draws)
+        S = np.zeros(max(int(n_sample), 1), dtype=np.int64)
+        n = self.L.ref_parallel_sample(int(n_sample), _p(p), p.size, int(n_threads), _p(S))
+        used = self.rand_calls()
+        self.clear_draws()
+        return S[: int(n)].copy(), used
 
     def fri_compression(self, x, n_sample, method, draws):
         x = _f64(x).ravel()

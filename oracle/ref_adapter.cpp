@@ -9,6 +9,8 @@
 // It also provides __wrap_rand (link flag -Wl,--wrap=rand): the reference draws its uniforms with
 // libc rand() (/root/reference/src/fri_utils.cpp:47,74); with the wrap in place the same integer
 // stream can be fed to the reference and to the CUDA implementation.
+#include <omp.h>
+
 #include <cstdlib>
 #include <cstring>
 #include <span>
@@ -87,6 +89,19 @@ void ref_sample_systematic(long n_sample, const double* p, long n, long* S) {
   std::vector<double> probs(p, p + n);
   auto s = sample_systematic((size_t)n_sample, probs);
   for (size_t i = 0; i < s.size(); i++) S[i] = (long)s[i];
+}
+
+// parallel_sample (fri_utils.cpp:176-362) cuts q into omp_get_max_threads() chunks and lets every thread call rand()
+// concurrently: with more than one thread the ORDER of the draws is a race, so only two cases are reproducible --
+// one thread (any draws), or any thread count with a constant draw stream.  n_threads is set for this call only.
+// Returns the number of samples written.
+long ref_parallel_sample(long n_sample, const double* q, long n, int n_threads, long* S) {
+  const int before = omp_get_max_threads();
+  omp_set_num_threads(n_threads);
+  auto s = parallel_sample((size_t)n_sample, std::span<const double>(q, (size_t)n));
+  omp_set_num_threads(before);
+  for (size_t i = 0; i < s.size(); i++) S[i] = (long)s[i];
+  return (long)s.size();
 }
 
 void ref_fri_compression(const double* x, long n, long n_sample, const char* method, int verbose, long* idx,

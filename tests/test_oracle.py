@@ -4,7 +4,9 @@ import ctypes
 
 import numpy as np
 import pytest
-from conftest import TERMS, create_sparse_ndarray, synth_t2
+import os
+
+from conftest import GOLDEN, TERMS, create_sparse_ndarray, synth_t2
 
 
 def test_glibc_rand_restatement(port):
@@ -95,3 +97,43 @@ def test_systematic_fallthrough_and_pivotal_tail(port, ref):
     S, used = port.sample_pivotal(2, p, draws)
     S2, used2 = ref.sample_pivotal(2, p, draws)
     assert (S == S2).all() and used == used2
+
+
+def _golden_parallel_cases():
+    g = np.load(os.path.join(GOLDEN, "parallel_sample.npz"))
+    for name in g["names"]:
+        name = str(name)
+        ns, T = (int(v) for v in g[name + "/meta"])
+        q = g[name + "/q"]
+        d = g[name + "/draws"]
+        draws = d if T == 1 else np.full(q.size + 8, int(d[0]), dtype=np.int32)
+        yield name, q, ns, T, draws, g[name + "/S"]
+
+
+def test_port_parallel_sample_matches_golden(port):
+    """parallel_sample (fri_utils.cpp:176-362): the restatement (draws consumed in chunk order) against outputs of the
+    compiled reference recorded by tests/golden/make_golden_parallel_sample.py -- one thread with random draws, and
+    2/3/8/16 threads on inputs where the reference's rand() race and reduction order cannot matter."""
+    n = 0
+    for name, q, ns, T, draws, want in _golden_parallel_cases():
+        S, used = port.parallel_sample(ns, q, T, draws)
+        assert np.array_equal(S, want), name
+        assert len(np.unique(S)) == ns and S.min() >= 0 and S.max() < q.size     # a sample without replacement
+        n += 1
+    assert n >= 50
+
+
+def test_port_parallel_sample_matches_compiled_reference(port, ref):
+    rng = np.random.default_rng(5)
+    for trial in range(12):          # one thread: any probabilities, random draws, draw count included
+        n = int(rng.integers(40, 5000))
+        ns = int(rng.integers(1, max(2, n // 6)))
+        x = np.abs(rng.standard_normal(n)) * np.exp(-3 * rng.random(n))
+        p = x / x.sum() * ns
+        while p.max() > 1:
+            p = np.minimum(p, 1.0)
+            p = p / p.sum() * ns
+        draws = rng.integers(0, 2**31 - 1, size=n + 8).astype(np.int32)
+        a, ua = port.parallel_sample(ns, p, 1, draws)
+        b, ub = ref.parallel_sample(ns, p, 1, draws)
+        assert np.array_equal(a, b) and ua == ub
