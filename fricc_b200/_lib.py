@@ -103,6 +103,7 @@ SIGNATURES = {
                                               c_void_p, c_int]),
     "fricc_sample_pivotal": (c_int, [c_int64, c_void_p, c_int, c_int64, c_void_p, c_int64, _i64p, c_void_p]),
     "fricc_sample_systematic": (c_int, [c_int64, c_void_p, c_int, c_int64, c_void_p, c_int64, _i64p, c_void_p]),
+    "fricc_parallel_sample": (c_int, [c_int64, c_void_p, c_int, c_int64, c_int, c_void_p, c_int64, _i64p, c_void_p]),
     "fricc_fri_compression": (c_int, [c_void_p, c_int, c_int64, c_int64, c_char_p, c_int, c_void_p, c_int64, _i64p,
                                       c_void_p, c_void_p]),
     "fricc_key_histogram": (c_int, [c_void_p, c_int64, c_int, c_uint64, c_int, c_void_p]),

@@ -679,6 +679,24 @@ int fricc_sample_systematic(int64_t n_sample, const double* probs, int mem, int6
   return sample_impl(false, n_sample, probs, mem, n, draws, n_draws, n_consumed, S_out);
 }
 
+int fricc_parallel_sample(int64_t n_sample, const double* probs, int mem, int64_t n, int n_chunks, const int32_t* draws,
+                          int64_t n_draws, int64_t* n_consumed, int64_t* S_out) {
+  FRICC_API_BEGIN
+  if (n < 0 || n_sample < 0 || (n > 0 && !probs) || (n_sample > 0 && !S_out)) fail(FRICC_EINVAL, "bad arguments");
+  DevIn<double> pd(probs, mem, (size_t)n);
+  DrawSource ds;
+  ds.from_stream = (draws == nullptr);
+  ds.host = draws;
+  ds.n = draws ? n_draws : 0;
+  DevBuf<int64_t> S((size_t)std::max<int64_t>(n_sample, 1));
+  int64_t consumed = 0;
+  parallel_sample(n_sample, pd.p, n, n_chunks, ds, &consumed, S.p);
+  if (n_sample > 0) S.to_host(S_out, (size_t)n_sample);
+  FRICC_CUDA(cudaStreamSynchronize(stream()));
+  if (n_consumed) *n_consumed = consumed;
+  FRICC_API_END
+}
+
 int fricc_fri_compression(const double* x, int mem, int64_t n, int64_t n_sample, const char* sampling_method,
                           int verbose, const int32_t* draws, int64_t n_draws, int64_t* n_consumed, int64_t* idx_out,
                           double* vals_out) {

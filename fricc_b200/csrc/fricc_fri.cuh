@@ -52,6 +52,10 @@ void sample_systematic_probs(int64_t n_sample, const double* p_dev, int64_t n, c
 void sample_pivotal_probs(int64_t n_sample, const double* p_dev, int64_t n, const DrawSource& draws, int64_t* consumed,
                           int64_t* S_dev);
 
+// parallel_sample (fri_utils.cpp:176-362) with n_chunks chunks, draws consumed in chunk order   (fricc_psample.cu)
+void parallel_sample(int64_t n_sample, const double* p_dev, int64_t n, int n_chunks, const DrawSource& draws,
+                     int64_t* consumed, int64_t* S_dev);
+
 // final state of a pivotal walk (device struct shared by the chain kernel and the parallel sampler)
 struct PivotalState {
   double a;           // running sum after the last visited element

@@ -19,6 +19,8 @@ There is no CPU implementation behind this module: without the built library and
 import ctypes
 from ctypes import byref, c_double, c_int64, c_void_p
 
+import os
+
 import numpy as np
 
 from . import _lib
@@ -364,10 +366,24 @@ def sample_systematic(n_sample, probs, draws=None):
     return S.tolist()
 
 
-def parallel_sample(n_sample, probs):
-    """The reference's thread-partitioned sampler (fri_utils.cpp:176-362) is not on the FRI-CCSD path and cannot be
-    called from Python at HEAD; it is listed as a later row of the scope table."""
-    raise NotImplementedError("parallel_sample is outside the hot path built so far (SURVEY.md section 8f-4)")
+def parallel_sample(n_sample, probs, n_chunks=None, draws=None):
+    """Thread-partitioned pivotal sampling, "Alg. A.2" (fri_utils.cpp:176-362) -> list[int].
+
+    The reference cuts `probs` into omp_get_max_threads() chunks; `n_chunks` is that number here (default: the value
+    omp_get_max_threads() would have in this process -- OMP_NUM_THREADS if set, else the CPU count).  The reference's
+    threads call rand() concurrently, so with more than one chunk the order of its draws is a race; this
+    implementation consumes them in chunk order (chunk j after chunk j-1), which is what the reference does when its
+    threads happen to run one after another and exactly what it does with one thread."""
+    if n_chunks is None:
+        env = os.environ.get("OMP_NUM_THREADS", "")
+        n_chunks = int(env.split(",")[0]) if env.split(",")[0].strip().isdigit() else (os.cpu_count() or 1)
+    p = _probs(probs)
+    S = np.empty(int(n_sample), dtype=np.int64)
+    dptr, dn, keep = _draws_arg(draws)
+    consumed = c_int64(0)
+    check(_lib.lib().fricc_parallel_sample(int(n_sample), p.ptr, p.mem, p.size, int(n_chunks), dptr, dn,
+                                           byref(consumed), S.ctypes.data))
+    return S.tolist()
 
 
 def fri_compression(x, n_sample, sampling_method="pivotal", verbose=False, draws=None):

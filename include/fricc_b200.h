@@ -206,6 +206,13 @@ int fricc_sample_pivotal(int64_t n_sample, const double* probs, int mem, int64_t
                          int64_t n_draws, int64_t* n_consumed, int64_t* S_out_host);
 int fricc_sample_systematic(int64_t n_sample, const double* probs, int mem, int64_t n, const int32_t* draws,
                             int64_t n_draws, int64_t* n_consumed, int64_t* S_out_host);
+/* parallel_sample (fri_utils.cpp:176-362, "Alg. A.2"): probs cut into n_chunks contiguous chunks (the reference uses
+ * omp_get_max_threads()), integer budgets by a pivotal draw over the fractional parts, leading probabilities of each
+ * chunk rescaled to its budget, chunks sampled independently with sample_pivotal.  The reference's threads call rand()
+ * concurrently (a race); here the draws are consumed in chunk order -- its behaviour when the threads run one after
+ * another, exactly its behaviour with one chunk.                                                                    */
+int fricc_parallel_sample(int64_t n_sample, const double* probs, int mem, int64_t n, int n_chunks, const int32_t* draws,
+                          int64_t n_draws, int64_t* n_consumed, int64_t* S_out_host);
 /* fri_compression (fri_utils.cpp:439-522): returns m flat indices and m values, [D..., S...] order               */
 int fricc_fri_compression(const double* x, int mem, int64_t n, int64_t n_sample, const char* sampling_method,
                           int verbose, const int32_t* draws, int64_t n_draws, int64_t* n_consumed,
