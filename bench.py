@@ -7,8 +7,12 @@ A "step" is one pass of the hot path exactly as fricc/friccsd.py:update_amps dri
 classes compressed: 2 FRI compressions of T2 (N = o^2 v^2 entries -> m) and the 11 sparse contractions
   1323 (ovov -> Woooo), 0112 0313 0113 (ovov -> Wvoov), 0312 (ovov -> Wvovo),
   0101 (Woooo), 2323 (Wvvvv: the particle-particle ladder), 1302 1303 (Wvoov), 1202 1203 (Wvovo)   -> t2new / tmp.
-Multi-GPU: every contraction is sharded along its free index pair (column slices of the [K][L] panel of W); the slices
-of each output are all-gathered over NCCL so every rank holds the full result; strong scaling (fixed problem).
+Multi-GPU: every contraction is sharded along its free index pair (column slices of the [K][L] panel of W); each rank
+accumulates its columns into its own copy of the 4-D output and stores them into every peer's copy over NVLink
+(symmetric allocation, stores issued on a side stream under the next term's kernel; `--exchange nccl` = all-gather of
+panels instead), so every rank holds the full result; strong scaling (fixed problem).  The step's two compressions come
+from one range-sharded pass (every rank scans its contiguous 1/N of T2; `--compress`).  For FRI-compressed tensors the
+contractions run in their tensor-core form (`--planes`, fricc_dense.cu; `--planes 0` = fp64 SpMM).
 
 Timing: W >= 3 untimed warm-up steps, then K steps; barrier + torch.cuda.synchronize on both sides; CUDA events on the
 launching stream; max over ranks.  Inputs are far larger than L2 (the ladder streams >= 25 GB of W per GPU per step).

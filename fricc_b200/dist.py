@@ -1,10 +1,17 @@
 """One-process-per-GPU orchestration of the FRI-CCSD inner loop.
 
 Sharding: every contraction  out[R, L] += scale * sum_K T[R, K] * W[K, L]  is split along its FREE pair L (the
-non-contracted pair of W): rank g owns the contiguous L-columns [g*lc, (g+1)*lc) of the [K][L] panel of W and produces
-the same columns of out.  The compressed tensor T (<= 16*m bytes) is replicated.  There is no data-path collective
-inside a contraction; the one exchange step is an all-gather of the column slices of each output (NCCL over
-NVLink), after which every rank holds the full output -- which is what the next compression needs.
+non-contracted pair of W): rank g owns the contiguous L-columns [g*lc, (g+1)*lc) of the [K][L] panel of W (and of its
+int8 digit planes, fricc_dense.cu) and produces the same columns of out.  The compressed tensor T (<= 16*m bytes) is
+replicated.  There is no data-path collective inside a contraction; the one exchange step per output is either
+  * stores into NVLink peer memory (SymmArena + ShardedTerm.accumulate(arena=...) / push_columns, fricc_peer.cu),
+    optionally issued on a SideStream so that they run under the next term's kernel -- the default of bench.py --, or
+  * an NCCL all-gather of column panels + fricc_accumulate_panels (ShardedTerm.local / start_exchange / finish),
+after which every rank holds the full output -- which is what the next compression needs.
+
+Compression: `compress` (replicated), `compress_pair` (the two compressions of an iteration task-parallel on even / odd
+ranks; any sampler), `compress_ranges[_pair]` (fricc_b200/ranges.py: every rank scans its contiguous 1/G of T2,
+all-reduced key histograms, exact sums carried rank to rank; systematic sampler).
 
 torch is used for device buffers, streams and torch.distributed only; all arithmetic is in libfricc_b200.so.
 """
