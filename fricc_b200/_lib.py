@@ -50,6 +50,7 @@ SIGNATURES = {
     "fricc_stream_synchronize": (c_int, []),
     "fricc_set_option": (c_int, [c_char_p, c_int]),
     "fricc_kernel_launches": (c_int64, []),
+    "fricc_plane_cache_clear": (c_int, []),
     "fricc_get_stat": (c_int, [c_char_p, _i64p]),
     "fricc_srand": (c_int, [c_uint32]),
     "fricc_rand_fill": (c_int, [POINTER(c_int32), c_int64]),

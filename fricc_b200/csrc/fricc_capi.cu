@@ -19,6 +19,8 @@ void set_push_carveout(int pct);   // fricc_peer.cu: L1/shared split the peer-st
 
 using namespace fricc;
 
+static int64_t g_tc_calls = 0, g_spmm_calls = 0;
+
 namespace {
 
 Sampling parse_sampling(const char* s) {
@@ -149,6 +151,8 @@ int fricc_get_stat(const char* key, int64_t* value) {
   FRICC_API_BEGIN
   if (!key || !value) fail(FRICC_EINVAL, "null argument");
   if (strcmp(key, "pivotal_restarts") == 0) *value = pivotal_restarts_last();
+  else if (strcmp(key, "tc_contract_calls") == 0) *value = g_tc_calls;      // fricc_contract calls that took the tensor-core form
+  else if (strcmp(key, "spmm_contract_calls") == 0) *value = g_spmm_calls;  // ... and the fp64 SpMM
   else fail(FRICC_EINVAL, "unknown stat '%s'", key);
   FRICC_API_END
 }
@@ -322,47 +326,163 @@ int fricc_st_export(fricc_st_t t, int64_t* flat_idx, double* vals, int mem) {
   FRICC_API_END
 }
 
+}  // extern "C"
+
 // ---- contractions --------------------------------------------------------------------------------------------
+namespace {
+
+OutMap out_map(const TermSpec& ts, const int64_t* t_dims, const int64_t out_shape[4], const int64_t out_strides[4]) {
+  OutMap om;
+  om.nR2 = t_dims[ts.tR[1]];
+  om.nL2 = out_shape[ts.oL[1]];
+  om.sR1 = out_strides[ts.oR[0]];
+  om.sR2 = out_strides[ts.oR[1]];
+  om.sL1 = out_strides[ts.oL[0]];
+  om.sL2 = out_strides[ts.oL[1]];
+  return om;
+}
+
+// The owner pair R and the free pair L of a term are unordered as far as the mathematics goes; the kernels walk the
+// MINOR index of R along the lanes of a warp and the minor index of L along a thread's consecutive columns.  Put
+// the index with the smaller output stride in the minor position, so that e.g. out(i,j,a,b) written by R = (b,j)
+// (terms 1302/1202/1303) is stored along b, its unit-stride axis, instead of one 32-byte sector per element.
+TermSpec oriented(const TermSpec& ts, const int64_t out_strides[4]) {
+  TermSpec e = ts;
+  if (out_strides[e.oR[0]] < out_strides[e.oR[1]]) {
+    std::swap(e.tR[0], e.tR[1]);
+    std::swap(e.oR[0], e.oR[1]);
+  }
+  if (out_strides[e.oL[0]] < out_strides[e.oL[1]]) {
+    std::swap(e.wL[0], e.wL[1]);
+    std::swap(e.oL[0], e.oL[1]);
+  }
+  return e;
+}
+
+// ---- digit planes kept across calls (option "tc_plane_cache", off by default) ---------------------------------
+// FRILCCSD hands the SAME operands to contract_DTSpT in every iteration (fricc/frilccsd.py:171-179); with the cache on,
+// their planes are built once.  An entry is keyed by (address, shape, strides, K/L axes, planes) and guarded by a
+// fingerprint of 4096 evenly spaced elements, re-read on every call -- a changed operand at an old address is rebuilt
+// unless every sampled element is unchanged, which is why the cache is opt-in: the caller states that operands at one
+// address are either rewritten wholesale or not at all.
+struct PlaneEntry {
+  const double* p = nullptr;
+  int64_t shape[4] = {0, 0, 0, 0}, strides[4] = {0, 0, 0, 0};
+  int axes[4] = {0, 0, 0, 0};
+  int S = 0;
+  uint64_t print = 0;
+  uint64_t stamp = 0;
+  fricc::WSlices ws;
+};
+std::vector<PlaneEntry*> g_plane_cache;
+uint64_t g_plane_stamp = 0;
+constexpr size_t kPlaneCacheEntries = 12;
+
+}  // namespace
+
+namespace fricc {
+uint64_t view_fingerprint(const WView& w, int64_t l_begin, int64_t l_count);  // fricc_dense.cu
+}
+
+namespace {
+
+void plane_cache_clear() {
+  for (PlaneEntry* e : g_plane_cache) delete e;
+  g_plane_cache.clear();
+}
+
+const WSlices& planes_for(const double* Wd, const int64_t shape[4], const int64_t strides[4], const TermSpec& ts,
+                          const WView& view, int64_t nL, WSlices& local) {
+  const int S = tc_planes();
+  if (!tc_plane_cache()) {
+    wslices_build_view(local, view, 0, nL, S);
+    return local;
+  }
+  const uint64_t fp = view_fingerprint(view, 0, nL);
+  const int axes[4] = {ts.wK[0], ts.wK[1], ts.wL[0], ts.wL[1]};
+  for (PlaneEntry* e : g_plane_cache) {
+    if (e->p == Wd && e->S == S && memcmp(e->shape, shape, sizeof(e->shape)) == 0 &&
+        memcmp(e->strides, strides, sizeof(e->strides)) == 0 && memcmp(e->axes, axes, sizeof(axes)) == 0) {
+      if (e->print != fp) {
+        wslices_build_view(e->ws, view, 0, nL, S);
+        e->print = fp;
+      }
+      e->stamp = ++g_plane_stamp;
+      return e->ws;
+    }
+  }
+  if (g_plane_cache.size() >= kPlaneCacheEntries) {  // evict the least recently used
+    size_t lru = 0;
+    for (size_t i = 1; i < g_plane_cache.size(); i++)
+      if (g_plane_cache[i]->stamp < g_plane_cache[lru]->stamp) lru = i;
+    delete g_plane_cache[lru];
+    g_plane_cache.erase(g_plane_cache.begin() + (long)lru);
+  }
+  PlaneEntry* e = new PlaneEntry();
+  e->p = Wd; e->S = S; e->print = fp; e->stamp = ++g_plane_stamp;
+  memcpy(e->shape, shape, sizeof(e->shape));
+  memcpy(e->strides, strides, sizeof(e->strides));
+  memcpy(e->axes, axes, sizeof(axes));
+  g_plane_cache.push_back(e);
+  wslices_build_view(e->ws, view, 0, nL, S);
+  return e->ws;
+}
+
+// fricc_contract's choice between the two forms of a contraction ("tc_mode": 0 never, 1 this cost model, 2 always).
+// Rates measured on B200 at the headline shape (profiles/): the bucketed fp64 SpMM sustains ~2.7e12 FMA/s (L1 data
+// pipe), the int8 form ~1.5e15 MAC/s over the PADDED dense product, plane building runs at HBM speed.
+bool use_tensor_cores(fricc_st* T, int64_t nR, int64_t nK, int64_t nL, bool panel_in_place) {
+  const int mode = tc_mode();
+  if (mode == 0 || spmm_exact_order() || T->nnz == 0) return false;
+  if (mode == 2) return true;
+  if (T->n_exact < 0) return false;                        // unknown provenance: would have to classify every entry
+  const double m = (double)T->nnz, nS = (double)(T->nnz - T->n_exact);
+  if (2.0 * nS < m || nK < 256 || nL < 64 || nR < 32) return false;
+  const double S = tc_planes();
+  const double Mpad = (double)(ceil_div(nR, 128) * 128), Kpad = (double)(ceil_div(nK, 128) * 128),
+               Lpad = (double)(ceil_div(nL, 64) * 64);
+  const double t_spmm = m * (double)nL / 2.7e12 + (panel_in_place ? 0.0 : 16.0 * (double)nK * (double)nL / 3.0e12);
+  const double t_tc = Mpad * Kpad * Lpad * S / 1.5e15 + (double)nK * (double)nL * (16.0 + S) / 3.0e12 +
+                      Mpad * Kpad / 1.0e12 + (m - nS) * (double)nL / 1.0e12 + 30e-6;
+  return t_tc < t_spmm;
+}
+
+}  // namespace
+
+extern "C" {
+
 int fricc_contract(const double* W, int w_mem, const int64_t w_shape[4], const int64_t w_strides[4], fricc_st_t T,
                    double* out, int out_mem, const int64_t out_shape[4], const int64_t out_strides[4],
                    const char* term) {
   FRICC_API_BEGIN
   check_handle(T);
   if (!W || !out || !w_shape || !w_strides || !out_shape || !out_strides) fail(FRICC_EINVAL, "null argument");
-  const TermSpec* ts = find_term(term);
-  if (!ts) fail(FRICC_EINVAL, "CASE NOT IMPLEMENTED: unknown contraction term '%s'", term ? term : "(null)");
+  const TermSpec* ts0 = find_term(term);
+  if (!ts0) fail(FRICC_EINVAL, "CASE NOT IMPLEMENTED: unknown contraction term '%s'", term ? term : "(null)");
   const int64_t* d = T->dims;
   // shape agreement (the reference indexes unchecked; here a mismatch is an error instead of a wild read)
   for (int q = 0; q < 2; q++) {
-    if (w_shape[ts->wK[q]] != d[ts->tK[q]])
-      fail(FRICC_EINVAL, "term %s (%s): W axis %d has extent %lld, T axis %d has %lld", ts->name, ts->einsum, ts->wK[q],
-           (long long)w_shape[ts->wK[q]], ts->tK[q], (long long)d[ts->tK[q]]);
-    if (out_shape[ts->oR[q]] != d[ts->tR[q]])
-      fail(FRICC_EINVAL, "term %s (%s): out axis %d has extent %lld, T axis %d has %lld", ts->name, ts->einsum,
-           ts->oR[q], (long long)out_shape[ts->oR[q]], ts->tR[q], (long long)d[ts->tR[q]]);
-    if (out_shape[ts->oL[q]] != w_shape[ts->wL[q]])
-      fail(FRICC_EINVAL, "term %s (%s): out axis %d has extent %lld, W axis %d has %lld", ts->name, ts->einsum,
-           ts->oL[q], (long long)out_shape[ts->oL[q]], ts->wL[q], (long long)w_shape[ts->wL[q]]);
+    if (w_shape[ts0->wK[q]] != d[ts0->tK[q]])
+      fail(FRICC_EINVAL, "term %s (%s): W axis %d has extent %lld, T axis %d has %lld", ts0->name, ts0->einsum,
+           ts0->wK[q], (long long)w_shape[ts0->wK[q]], ts0->tK[q], (long long)d[ts0->tK[q]]);
+    if (out_shape[ts0->oR[q]] != d[ts0->tR[q]])
+      fail(FRICC_EINVAL, "term %s (%s): out axis %d has extent %lld, T axis %d has %lld", ts0->name, ts0->einsum,
+           ts0->oR[q], (long long)out_shape[ts0->oR[q]], ts0->tR[q], (long long)d[ts0->tR[q]]);
+    if (out_shape[ts0->oL[q]] != w_shape[ts0->wL[q]])
+      fail(FRICC_EINVAL, "term %s (%s): out axis %d has extent %lld, W axis %d has %lld", ts0->name, ts0->einsum,
+           ts0->oL[q], (long long)out_shape[ts0->oL[q]], ts0->wL[q], (long long)w_shape[ts0->wL[q]]);
   }
+  const TermSpec tsv = oriented(*ts0, out_strides);
+  const TermSpec* ts = &tsv;
   const int64_t nK1 = w_shape[ts->wK[0]], nK2 = w_shape[ts->wK[1]];
   const int64_t nL1 = w_shape[ts->wL[0]], nL2 = w_shape[ts->wL[1]];
   const int64_t nK = nK1 * nK2, nL = nL1 * nL2;
+  const int64_t nR = d[ts->tR[0]] * d[ts->tR[1]];
   if (nK == 0 || nL == 0 || T->nnz == 0) return FRICC_OK;
 
   const int64_t w_span = span_of(w_shape, w_strides);
   const int64_t o_span = span_of(out_shape, out_strides);
   DevIn<double> Wd(W, w_mem, (size_t)w_span);
-
-  // is W already the [K1][K2][L1][L2] row-major panel?  then stream it in place
-  const bool in_place = w_strides[ts->wL[1]] == 1 && w_strides[ts->wL[0]] == nL2 && w_strides[ts->wK[1]] == nL &&
-                        w_strides[ts->wK[0]] == nK2 * nL;
-  DevBuf<double> panel;
-  const double* Wp = Wd.p;
-  if (!in_place) {
-    panel.alloc((size_t)(nK * nL));
-    permute_w(Wd.p, w_shape, w_strides, *ts, 0, nL, panel.p);
-    Wp = panel.p;
-  }
 
   DevBuf<double> out_stage;
   double* od = out;
@@ -371,17 +491,39 @@ int fricc_contract(const double* W, int w_mem, const int64_t w_shape[4], const i
     out_stage.from_host(out, (size_t)o_span);
     od = out_stage.p;
   }
-  Layout& lay = get_layout(T, *ts);
-  OutMap om;
-  om.nR2 = d[ts->tR[1]];
-  om.nL2 = nL2;
-  om.sR1 = out_strides[ts->oR[0]];
-  om.sR2 = out_strides[ts->oR[1]];
-  om.sL1 = out_strides[ts->oL[0]];
-  om.sL2 = out_strides[ts->oL[1]];
-  spmm(lay, Wp, nL, 0, nL, od, om, ts->scale);
+  const OutMap om = out_map(*ts, d, out_shape, out_strides);
+
+  // is W already the [K1][K2][L1][L2] row-major panel?  then the SpMM streams it in place
+  const bool in_place = w_strides[ts->wL[1]] == 1 && w_strides[ts->wL[0]] == nL2 && w_strides[ts->wK[1]] == nL &&
+                        w_strides[ts->wK[0]] == nK2 * nL;
+  if (use_tensor_cores(T, nR, nK, nL, in_place)) {
+    // tensor-core form, W read where it lies: digit planes straight from the 4-D operand, sign matrix x planes on
+    // tcgen05.mma.kind::i8, the exact part of T through the fp64 remainder kernel on the same view
+    g_tc_calls++;
+    const WView view = term_view(Wd.p, w_shape, w_strides, *ts);
+    WSlices local;
+    const WSlices& ws = planes_for(w_mem == FRICC_DEVICE ? W : nullptr, w_shape, w_strides, *ts, view, nL, local);
+    Layout& lay = get_layout(T, *ts, false);
+    contract_dense(T, *ts, lay, ws, view, 0, od, om, ts->scale, false);
+  } else {
+    g_spmm_calls++;
+    DevBuf<double> panel;
+    const double* Wp = Wd.p;
+    if (!in_place) {
+      panel.alloc((size_t)(nK * nL));
+      permute_w(Wd.p, w_shape, w_strides, *ts, 0, nL, panel.p);
+      Wp = panel.p;
+    }
+    spmm_term(T, *ts, Wp, nL, 0, nL, od, om);
+  }
   if (out_mem != FRICC_DEVICE) out_stage.to_host(out, (size_t)o_span);
-  else FRICC_CUDA(cudaStreamSynchronize(stream()));  // staged W / panel are released after this call
+  // (all-device calls return without synchronising: scratch buffers are stream-ordered allocations)
+  FRICC_API_END
+}
+
+int fricc_plane_cache_clear(void) {
+  FRICC_API_BEGIN
+  plane_cache_clear();
   FRICC_API_END
 }
 
@@ -406,7 +548,6 @@ int fricc_contract_panel(const double* Wp_dev, int64_t ldw, int64_t l_begin, int
   if (!ts) fail(FRICC_EINVAL, "CASE NOT IMPLEMENTED: unknown contraction term '%s'", term ? term : "(null)");
   if (!Wp_dev || !out_panel_dev || l_count < 0 || ldw < l_count || ld_out < l_count) fail(FRICC_EINVAL, "bad arguments");
   if (T->nnz == 0 || l_count == 0) return FRICC_OK;
-  Layout& lay = get_layout(T, *ts);
   // out panel is [R][ld_out] row-major: address = R*ld_out + (l - l_begin)
   OutMap om;
   om.nR2 = 1;
@@ -416,7 +557,7 @@ int fricc_contract_panel(const double* Wp_dev, int64_t ldw, int64_t l_begin, int
   om.sL1 = 1;
   om.sL2 = 0;
   // the kernel maps column l = l_begin + col through sL1; shift the base so that column l_begin lands at offset 0
-  spmm(lay, Wp_dev, ldw, l_begin, l_count, out_panel_dev - l_begin, om, ts->scale);
+  spmm_term(T, *ts, Wp_dev, ldw, l_begin, l_count, out_panel_dev - l_begin, om);
   FRICC_API_END
 }
 
@@ -435,15 +576,8 @@ int fricc_contract_panel_into(const double* Wp_dev, int64_t ldw, int64_t l_begin
   const int64_t nL = out_shape[ts->oL[0]] * out_shape[ts->oL[1]];
   if (l_begin + l_count > nL) fail(FRICC_EINVAL, "column range out of bounds");
   if (T->nnz == 0 || l_count == 0) return FRICC_OK;
-  Layout& lay = get_layout(T, *ts);
-  OutMap om;
-  om.nR2 = d[ts->tR[1]];
-  om.nL2 = out_shape[ts->oL[1]];
-  om.sR1 = out_strides[ts->oR[0]];
-  om.sR2 = out_strides[ts->oR[1]];
-  om.sL1 = out_strides[ts->oL[0]];
-  om.sL2 = out_strides[ts->oL[1]];
-  spmm(lay, Wp_dev, ldw, l_begin, l_count, out_dev, om, ts->scale);
+  const OutMap om = out_map(*ts, d, out_shape, out_strides);
+  spmm_term(T, *ts, Wp_dev, ldw, l_begin, l_count, out_dev, om);
   FRICC_API_END
 }
 
@@ -531,6 +665,10 @@ int fricc_st_sign_fraction(fricc_st_t T, const char* term, double* fraction) {
 static void contract_tc_common(fricc_wslices_t h, const double* Wp_dev, int64_t ldw, int64_t l_begin, fricc_st_t T,
                                double* out, const OutMap& om, const TermSpec* ts) {
   if (T->nnz == 0 || h->ws.l_count == 0) return;
+  if (spmm_exact_order()) {  // parity mode: the reference's own order and roundings on the fp64 panel
+    spmm_term(T, *ts, Wp_dev, ldw, l_begin, h->ws.l_count, out, om);
+    return;
+  }
   Layout& lay = get_layout(T, *ts, false);
   contract_dense(T, *ts, lay, h->ws, Wp_dev, ldw, l_begin, out, om, ts->scale);
 }
@@ -546,6 +684,13 @@ int fricc_contract_panel_tc(fricc_wslices_t h, const double* Wp_dev, int64_t ldw
   om.nR2 = 1; om.nL2 = 1; om.sR1 = ld_out; om.sR2 = 0; om.sL1 = 1; om.sL2 = 0;
   const int64_t nR = T->dims[ts->tR[0]] * T->dims[ts->tR[1]];
   bool ow = overwrite != 0;
+  if (spmm_exact_order()) {
+    if (ow && h->ws.l_count > 0 && nR > 0)
+      FRICC_CUDA(cudaMemset2DAsync(out_panel_dev, (size_t)ld_out * 8, 0, (size_t)h->ws.l_count * 8, (size_t)nR, stream()));
+    if (T->nnz > 0 && h->ws.l_count > 0)
+      spmm_term(T, *ts, Wp_dev, ldw, l_begin, h->ws.l_count, out_panel_dev - l_begin, om);
+    return FRICC_OK;
+  }
   if (ow) {
     // "out = result": the tensor-core kernel writes every element of the panel columns without reading them.  When it
     // will not run (no entries, or nothing in the sign matrix) the columns are cleared here instead.

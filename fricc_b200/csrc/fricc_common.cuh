@@ -162,6 +162,12 @@ struct Layout {
   DevBuf<uint32_t> kidx;   // [nnz]
   DevBuf<double> vals;     // [nnz]
   int64_t max_row = 0;     // longest bucket (entries)
+  // ---- "exact order" form (fricc_contract.cu: spmm_exact): buckets by R only, entries of a bucket in STORAGE order --
+  // the order in which the reference's loop nest adds them (sparse_tensor.cpp:66-73: `for s in 0..m`)
+  bool xo_built = false;
+  DevBuf<int64_t> xo_rowptr;  // [nR+1]
+  DevBuf<uint32_t> xo_kidx;   // [nnz]
+  DevBuf<double> xo_vals;     // [nnz]
   // ---- tensor-core form (fricc_dense.cu), built lazily: the entries whose value is +-c (every sampled entry of an FRI
   // compression carries the same magnitude c = r/n') as a dense int8 sign matrix A[Mpad][Kpad]; everything else (the
   // exactly preserved set D, duplicates) stays a CSR remainder that goes through the fp64 SpMM.

@@ -337,11 +337,14 @@ spmm_rows_wide_kernel(const int64_t* __restrict__ rowptr, const uint32_t* __rest
   }
 }
 
+static int g_spmm_exact = 0;    // "spmm_exact_order": 1 = the reference's summation order and roundings (bit-identical)
 static int g_spmm_nv2 = 2;      // double2 per thread in the wide kernel (1, 2 or 4); 0 = narrow kernel
 static int g_spmm_threads = 64;  // measured best on B200 at the headline shape: 64 threads x 2 double2 (256-column tiles)
 void set_spmm_option(const char* key, int value) {
   if (strcmp(key, "spmm_nv2") == 0) g_spmm_nv2 = value;
   else if (strcmp(key, "spmm_threads") == 0) g_spmm_threads = value;
+  else if (strcmp(key, "spmm_exact_order") == 0) g_spmm_exact = value;
+  else fail(FRICC_EINVAL, "unknown option '%s'", key);
 }
 
 void spmm_csr(const int64_t* rowptr, const uint32_t* kidx, const double* vals, int64_t nR, const double* Wp, int64_t ldw,
@@ -386,6 +389,138 @@ void spmm_csr(const int64_t* rowptr, const uint32_t* kidx, const double* vals, i
 void spmm(const Layout& lay, const double* Wp, int64_t ldw, int64_t l_begin, int64_t l_count, double* out,
           const OutMap& om, double scale) {
   spmm_csr(lay.rowptr.p, lay.kidx.p, lay.vals.p, lay.nR, Wp, ldw, l_begin, l_count, out, om, scale);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// "exact order" form: bit-identical to the reference's loop nest (option "spmm_exact_order")
+// ---------------------------------------------------------------------------------------------------------------
+// The reference adds the stored entries of an owner pair in STORAGE order s = 0..m-1, one rounded product and one
+// rounded sum per entry, straight onto the output element (sparse_tensor.cpp:66-73 and the ten kernels like it; a plain
+// x86-64 build: no FMA).  Every prefactor is a power of two, so (scale * W) * value has the one rounding of W * value.
+// The fast kernels above sum in (R, K) order with FMAs into a zero accumulator -- within 1e-10, not the same bits.  An
+// FRI-CCSD trajectory feeds every residual back into the next compression, and the pivotal sampler's decisions can sit
+// on an exact tie, so the energy parity of SURVEY.md 8c (P7) needs identical bits; this form provides them.
+__global__ void make_rkeys_kernel(const int64_t* __restrict__ flat, int64_t m, Dims4 dm, int r0, int r1,
+                                  uint64_t* __restrict__ keys, uint64_t* __restrict__ pay) {
+  int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= m) return;
+  int64_t f = flat[e];
+  int64_t ix[4];
+  ix[3] = f % dm.d[3]; f /= dm.d[3];
+  ix[2] = f % dm.d[2]; f /= dm.d[2];
+  ix[1] = f % dm.d[1]; f /= dm.d[1];
+  ix[0] = f;
+  keys[e] = (uint64_t)(ix[r0] * dm.d[r1] + ix[r1]);
+  pay[e] = (uint64_t)e;
+}
+
+__global__ void gather_storage_kernel(const uint64_t* __restrict__ pay, const int64_t* __restrict__ flat,
+                                      const double* __restrict__ vals, int64_t m, Dims4 dm, int k0, int k1,
+                                      uint32_t* __restrict__ kidx, double* __restrict__ ovals) {
+  int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= m) return;
+  const int64_t e = (int64_t)pay[t];
+  int64_t f = flat[e];
+  int64_t ix[4];
+  ix[3] = f % dm.d[3]; f /= dm.d[3];
+  ix[2] = f % dm.d[2]; f /= dm.d[2];
+  ix[1] = f % dm.d[1]; f /= dm.d[1];
+  ix[0] = f;
+  kidx[t] = (uint32_t)(ix[k0] * dm.d[k1] + ix[k1]);
+  ovals[t] = vals[e];
+}
+
+static void build_exact_order(fricc_st* T, const TermSpec& ts, Layout& lay) {
+  const int64_t m = T->nnz;
+  const int64_t* d = T->dims;
+  lay.xo_rowptr.alloc((size_t)lay.nR + 1);
+  lay.xo_kidx.alloc((size_t)std::max<int64_t>(m, 1));
+  lay.xo_vals.alloc((size_t)std::max<int64_t>(m, 1));
+  if (m == 0) {
+    lay.xo_rowptr.zero();
+    lay.xo_built = true;
+    return;
+  }
+  DevBuf<uint64_t> ka((size_t)m), kb((size_t)m), pa((size_t)m), pb((size_t)m);
+  Dims4 dm{{d[0], d[1], d[2], d[3]}};
+  const unsigned g = (unsigned)ceil_div(m, 256);
+  FRICC_LAUNCH(make_rkeys_kernel, g, 256, 0, T->flat.p, m, dm, ts.tR[0], ts.tR[1], ka.p, pa.p);
+  int bits = 1;
+  while (bits < 63 && ((int64_t)1 << bits) < lay.nR) bits++;
+  std::vector<Digit> digits;
+  for (int s = 0; s < bits; s += 8) digits.push_back(Digit{0, s, 0});
+  uint64_t* kk[2] = {ka.p, kb.p};
+  uint64_t* pp[2] = {pa.p, pb.p};
+  const int r = radix_sort_pairs(kk, pp, m, digits);  // stable: a bucket keeps its storage order
+  FRICC_LAUNCH(gather_storage_kernel, g, 256, 0, pp[r], T->flat.p, T->vals.p, m, dm, ts.tK[0], ts.tK[1], lay.xo_kidx.p,
+               lay.xo_vals.p);
+  FRICC_LAUNCH(rowptr_kernel, (unsigned)ceil_div(lay.nR + 1, 256), 256, 0, kk[r], m, (int64_t)1, lay.nR, lay.xo_rowptr.p);
+  lay.xo_built = true;
+}
+
+// one CTA = one bucket R x 128 columns; a thread owns one output element and walks the bucket in storage order
+__global__ void __launch_bounds__(128)
+spmm_rows_exact_kernel(const int64_t* __restrict__ rowptr, const uint32_t* __restrict__ kidx,
+                       const double* __restrict__ vals, const double* __restrict__ Wp, int64_t ldw, int64_t l_begin,
+                       int64_t l_count, double* __restrict__ out, OutMap om, double scale) {
+  __shared__ StagedEntry se[SPMM_CHUNK];
+  const int64_t R = blockIdx.x;
+  const int64_t e0 = rowptr[R], e1 = rowptr[R + 1];
+  if (e0 == e1) return;
+  const int64_t col = (int64_t)blockIdx.y * blockDim.x + threadIdx.x;
+  const bool active = col < l_count;
+  int64_t o = 0;
+  double acc = 0.0;
+  if (active) {
+    const int64_t r1 = R / om.nR2, r2 = R - r1 * om.nR2;
+    const int64_t l = l_begin + col;
+    const int64_t l1 = l / om.nL2, l2 = l - l1 * om.nL2;
+    o = r1 * om.sR1 + r2 * om.sR2 + l1 * om.sL1 + l2 * om.sL2;
+    acc = out[o];
+  }
+  for (int64_t c = e0; c < e1; c += SPMM_CHUNK) {
+    const int cnt = (int)min((int64_t)SPMM_CHUNK, e1 - c);
+    __syncthreads();
+    for (int t = threadIdx.x; t < cnt; t += blockDim.x) {
+      StagedEntry e;
+      e.koff = (unsigned long long)kidx[c + t] * (unsigned long long)ldw;
+      e.val = vals[c + t];
+      se[t] = e;
+    }
+    __syncthreads();
+    if (active) {
+#pragma unroll 4
+      for (int t = 0; t < cnt; t++) {
+        const StagedEntry e = se[t];
+        const double w = __ldg(Wp + e.koff + col);
+        acc = __dadd_rn(acc, __dmul_rn(__dmul_rn(scale, w), e.val));  // output += (scale * W) * value, two roundings
+      }
+    }
+  }
+  if (active) out[o] = acc;
+}
+
+bool spmm_exact_order() { return g_spmm_exact != 0; }
+
+void spmm_exact(fricc_st* T, const TermSpec& ts, const double* Wp, int64_t ldw, int64_t l_begin, int64_t l_count,
+                double* out, const OutMap& om) {
+  Layout& lay = get_layout(T, ts, false);
+  if (!lay.xo_built) build_exact_order(T, ts, lay);
+  if (lay.nR == 0 || l_count == 0 || T->nnz == 0) return;
+  const int64_t tiles = ceil_div(l_count, 128);
+  if (tiles > 65535) fail(FRICC_EINVAL, "spmm: free pair too large (%lld columns)", (long long)l_count);
+  dim3 grid((unsigned)lay.nR, (unsigned)tiles);
+  FRICC_LAUNCH(spmm_rows_exact_kernel, grid, 128, 0, lay.xo_rowptr.p, lay.xo_kidx.p, lay.xo_vals.p, Wp, ldw, l_begin,
+               l_count, out, om, ts.scale);
+}
+
+void spmm_term(fricc_st* T, const TermSpec& ts, const double* Wp, int64_t ldw, int64_t l_begin, int64_t l_count,
+               double* out, const OutMap& om) {
+  if (g_spmm_exact) {
+    spmm_exact(T, ts, Wp, ldw, l_begin, l_count, out, om);
+    return;
+  }
+  spmm(get_layout(T, ts), Wp, ldw, l_begin, l_count, out, om, ts.scale);
 }
 
 // gathered column-shard panels [g][R][ld] -> strided 4-D output (one read-modify-write per element, no atomics)

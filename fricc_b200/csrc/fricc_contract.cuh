@@ -40,6 +40,14 @@ struct OutMap {
 void spmm(const Layout& lay, const double* Wp_dev, int64_t ldw, int64_t l_begin, int64_t l_count, double* out_dev,
           const OutMap& om, double scale);
 
+// The contraction of one term on a [K][ldw] panel, in whichever form the "spmm_exact_order" option selects:
+//   0 (default): (R,K)-sorted buckets, FMA accumulation from zero, one read-modify-write per output element;
+//   1: the reference's own order and roundings -- entries of a bucket in storage order, out += (scale*W)*value with a
+//      rounded product and a rounded sum per entry (sparse_tensor.cpp:66-73) -- bit-identical to the compiled reference.
+void spmm_term(fricc_st* T, const TermSpec& ts, const double* Wp_dev, int64_t ldw, int64_t l_begin, int64_t l_count,
+               double* out_dev, const OutMap& om);
+bool spmm_exact_order();
+
 // tuning switches of the SpMM launch ("spmm_nv2": double2 per thread 0/1/2/4, "spmm_threads")
 void set_spmm_option(const char* key, int value);
 

@@ -135,19 +135,54 @@ __host__ __device__ constexpr uint32_t umma_idesc_i8(int M, int N) {
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// W panel -> int8 digit planes
+// W (any 4-D view) -> int8 digit planes
 // ---------------------------------------------------------------------------------------------------------------
-__global__ void colmax_kernel(const double* __restrict__ Wp, int64_t ldw, int64_t nK, int64_t l_count, int64_t k_per_block,
-                              unsigned long long* __restrict__ colmax) {
-  const int64_t col = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (col >= l_count) return;
+// The operand is read where it lies: element (K, l) of the term's [K][L] matrix is W[offK(K) + offL(l)] of the caller's
+// 4-D array (WView), so neither the [K][L] fp64 panel nor a permutation pass exists on this path.  Two thread maps,
+// picked by which index runs along the unit stride: LCONTIG (columns l contiguous: the panel layout, Wvovo) and
+// KCONTIG (the contracted minor index contiguous: the ladder's native W[a,b,c,d], ovov, Wvoov).
+__device__ __forceinline__ int64_t view_offK(const WView& w, int64_t K) {
+  const int64_t k1 = K / w.nK2;
+  return k1 * w.sK1 + (K - k1 * w.nK2) * w.sK2;
+}
+__device__ __forceinline__ int64_t view_offL(const WView& w, int64_t l) {
+  const int64_t l1 = l / w.nL2;
+  return l1 * w.sL1 + (l - l1 * w.nL2) * w.sL2;
+}
+
+// LCONTIG: thread = column, a CTA row of threads walks K; KCONTIG: warp = column, lanes walk K
+template <bool KCONTIG>
+__global__ void colmax_view_kernel(const WView w, int64_t nK, int64_t l_begin, int64_t l_count, int64_t k_per_block,
+                                   unsigned long long* __restrict__ colmax) {
   const int64_t k0 = (int64_t)blockIdx.y * k_per_block, k1 = min(nK, k0 + k_per_block);
-  unsigned long long mx = 0;
-  for (int64_t k = k0; k < k1; k++) {
-    unsigned long long key = abs_key(Wp[k * ldw + col]);
-    mx = key > mx ? key : mx;
+  if (KCONTIG) {
+    const int64_t col = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (col >= l_count) return;
+    const int lane = threadIdx.x & 31;
+    const double* base = w.p + view_offL(w, l_begin + col);
+    unsigned long long mx = 0;
+    for (int64_t k = k0 + lane; k < k1; k += 32) {
+      const unsigned long long key = abs_key(base[view_offK(w, k)]);
+      mx = key > mx ? key : mx;
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+      const unsigned long long y = __shfl_xor_sync(0xffffffffu, mx, o);
+      mx = y > mx ? y : mx;
+    }
+    if (lane == 0) atomicMax(&colmax[col], mx);
+  } else {
+    const int64_t col = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (col >= l_count) return;
+    const double* base = w.p + view_offL(w, l_begin + col);
+    unsigned long long mx = 0;
+    int64_t ka = k0 / w.nK2, kb = k0 - ka * w.nK2;
+    for (int64_t k = k0; k < k1; k++) {
+      const unsigned long long key = abs_key(base[ka * w.sK1 + kb * w.sK2]);
+      mx = key > mx ? key : mx;
+      if (++kb == w.nK2) { kb = 0; ka++; }
+    }
+    atomicMax(&colmax[col], mx);
   }
-  atomicMax(&colmax[col], mx);
 }
 
 // e_l: the smallest exponent with max_K |W[K,l]| < 2^e_l.  A column holding inf/nan gets a NaN scale: its outputs
@@ -167,34 +202,42 @@ __global__ void colexp_kernel(const unsigned long long* __restrict__ colmax, int
   colscale[col] = finite ? ldexp(1.0, e - 7) : __longlong_as_double(0x7ff8000000000000LL);  // one unit of plane 0
 }
 
-// One CTA = one 64-column tile x 128 contracted indices.  Thread (col, kq) expands 4 consecutive K of its column per
-// step (coalesced 512-byte reads across the 64 columns) and packs the 4 digits of each plane into one 32-bit word;
-// the planes go through shared memory (pitch 33 words, conflict-free) so that every 128-byte K-major row is written
-// by one warp in one piece.
+// the 8S-bit digit string of one element: exact power-of-two scaling, ONE rounding to the 8S-bit grid;
+// |W| < 2^e  =>  0 <= q <= 2^(8S)   (clamped to the top code)
+__device__ __forceinline__ long long digit_string(double w, int sh, long long half, long long top) {
+  long long q = llrint(scalbn(w, sh)) + half;
+  return q > top ? top : (q < 0 ? 0 : q);
+}
+
+// One CTA = one 64-column tile x 128 contracted indices.  Each thread expands 4 consecutive K of one column per step
+// and packs the 4 digits of each plane into one 32-bit word; the planes go through shared memory (pitch 33 words,
+// conflict-free) so that every 128-byte K-major row is written by one warp in one piece.
+//   LCONTIG: thread (col = t & 63, kq = t >> 6): a warp reads 32 consecutive columns (256 B) per K;
+//   KCONTIG: thread (kw = t & 31, cq = t >> 5): a warp reads 128 consecutive K (1 KB) of one column.
+template <bool KCONTIG>
 __global__ void __launch_bounds__(256)
-slice_kernel(const double* __restrict__ Wp, int64_t ldw, int64_t nK, int64_t l_count, int64_t Kpad, int S,
-             const int32_t* __restrict__ expo, int8_t* __restrict__ q) {
+slice_view_kernel(const WView w, int64_t nK, int64_t l_begin, int64_t l_count, int64_t Kpad, int S,
+                  const int32_t* __restrict__ expo, int8_t* __restrict__ q) {
   extern __shared__ uint32_t sq[];  // [S][64][33]
   const int64_t tile = blockIdx.x, kb = blockIdx.y;
-  const int col = threadIdx.x & 63, kq = threadIdx.x >> 6;
-  const int64_t l = tile * TC_BN + col;
-  const bool col_ok = l < l_count;
-  const int sh = 8 * S - 1 - (col_ok ? expo[l] : 0);
   const long long half = 1LL << (8 * S - 1), top = (1LL << (8 * S)) - 1;
   for (int it = 0; it < 8; it++) {
-    const int kw = it * 4 + kq;
+    const int col = KCONTIG ? (int)(threadIdx.x >> 5) + 8 * it : (int)(threadIdx.x & 63);
+    const int kw = KCONTIG ? (int)(threadIdx.x & 31) : it * 4 + (int)(threadIdx.x >> 6);
+    const int64_t l = tile * TC_BN + col;
+    const bool col_ok = l < l_count;
+    const int sh = 8 * S - 1 - (col_ok ? expo[l] : 0);
+    const double* base = w.p + (col_ok ? view_offL(w, l_begin + l) : 0);
     uint32_t pack[TC_MAX_SLICES];
 #pragma unroll
     for (int s = 0; s < TC_MAX_SLICES; s++) pack[s] = 0;
+    const int64_t K0 = kb * TC_BK + kw * 4;
+    int64_t ka = K0 / w.nK2, kr = K0 - ka * w.nK2;
 #pragma unroll
     for (int i = 0; i < 4; i++) {
-      const int64_t K = kb * TC_BK + kw * 4 + i;
       long long qi = 0;
-      if (col_ok && K < nK) {
-        // exact power-of-two scaling, ONE rounding to the 8S-bit grid; |W| < 2^e  =>  0 <= qi <= 2^(8S)
-        qi = llrint(scalbn(Wp[K * ldw + l], sh)) + half;
-        qi = qi > top ? top : (qi < 0 ? 0 : qi);
-      }
+      if (col_ok && K0 + i < nK) qi = digit_string(base[ka * w.sK1 + kr * w.sK2], sh, half, top);
+      if (++kr == w.nK2) { kr = 0; ka++; }
 #pragma unroll
       for (int s = 0; s < TC_MAX_SLICES; s++)
         if (s < S) pack[s] |= (uint32_t)((qi >> (8 * (S - 1 - s))) & 255) << (8 * i);
@@ -223,9 +266,289 @@ __global__ void reconstruct_kernel(const int8_t* __restrict__ q, const double* _
   Wrec[idx] = (v - 128.0) * colscale[l];
 }
 
-void wslices_build(WSlices& ws, const double* Wp, int64_t ldw, int64_t nK, int64_t l_count, int S) {
+// ---------------------------------------------------------------------------------------------------------------
+// single-read plane builder for operands whose K run is contiguous (the ladder's native W[a,b,c,d]: column (a,b) IS
+// the contiguous run of v^2 doubles W[a,b,:,:])
+// ---------------------------------------------------------------------------------------------------------------
+// A column needs two looks -- its largest magnitude, then its digits -- and at 1.28 MB per column (v = 400) neither
+// one CTA's shared memory nor, with 148 columns in flight, the L2 holds it between the two.  So a CLUSTER of C CTAs
+// holds one column in distributed shared memory: CTA r keeps K in [r*segK, (r+1)*segK) (<= 208 KB) in a ring of 16 KB
+// chunks filled by 1-D bulk copies (cp.async.bulk + mbarrier), the chunk maxima are combined through DSMEM stores and
+// one cluster barrier, and the digits are cut straight out of shared memory -- every element is read from HBM ONCE.
+// While the digits of column c are written, the freed chunks are already being refilled with column c + 1.
+// Traffic = 8 bytes read + S bytes written per element: the algorithmic minimum.
+constexpr int PF_THREADS = 256;
+constexpr int PF_CHUNK = 2048;      // doubles per chunk (16 KB)
+constexpr int PF_MAX_CHUNKS = 13;   // 208 KB of the 227 KB
+
+struct PfParams {
+  WView w;
+  int64_t nK, Kpad, l_begin, l_count;
+  int S, segK, n_chunks, C;
+  int8_t* q;
+  int32_t* expo;
+  double* colscale;
+};
+
+namespace ptx {
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
+// store a 64-bit value into the SAME shared-memory variable of CTA `rank` of this cluster
+__device__ __forceinline__ void st_cluster_u64(const void* local_smem, uint32_t rank, unsigned long long v) {
+  uint32_t remote;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(smem_u32(local_smem)), "r"(rank));
+  asm volatile("st.shared::cluster.u64 [%0], %1;" ::"r"(remote), "l"(v) : "memory");
+}
+// 1-D bulk copy global -> this CTA's shared memory, completion on an mbarrier (bytes: multiple of 16, 16-byte aligned)
+__device__ __forceinline__ void bulk_load_1d(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(gsrc)), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+}  // namespace ptx
+
+__global__ void __launch_bounds__(PF_THREADS, 1) planes_fused_kernel(const PfParams p) {
+  extern __shared__ __align__(128) uint8_t pf_smem[];
+  double* ring = reinterpret_cast<double*>(pf_smem);                                   // [n_chunks][PF_CHUNK]
+  uint64_t* full = reinterpret_cast<uint64_t*>(pf_smem + (size_t)p.n_chunks * PF_CHUNK * 8);  // [n_chunks]
+  unsigned long long* slots = reinterpret_cast<unsigned long long*>(full + PF_MAX_CHUNKS);   // [2][8] maxima of the cluster
+  unsigned long long* red = slots + 16;                                                // [8] warp maxima
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t rank = ptx::cluster_ctarank();
+  const int64_t cluster_id = blockIdx.x / p.C, n_clusters = gridDim.x / p.C;
+  const int64_t k_lo = (int64_t)rank * p.segK;
+  const int64_t my_n = max((int64_t)0, min(p.nK, k_lo + p.segK) - k_lo);  // K held by this CTA (even)
+  const int S = p.S;
+  const long long half = 1LL << (8 * S - 1), top = (1LL << (8 * S)) - 1;
+
+  if (tid == 0) {
+    for (int j = 0; j < p.n_chunks; j++) ptx::mbar_init(&full[j], 1);
+    ptx::fence_barrier_init();
+  }
+  __syncthreads();
+  // every CTA of the cluster must be running before anyone stores into its shared memory
+  ptx::cluster_arrive();
+  ptx::cluster_wait();
+
+  auto issue = [&](int64_t col, int j) {  // thread 0: refill chunk j with this CTA's part of column `col`
+    const int64_t off = (int64_t)j * PF_CHUNK;
+    const int64_t cnt = min((int64_t)PF_CHUNK, my_n - off);
+    if (cnt <= 0) return;
+    const double* src = p.w.p + view_offL(p.w, p.l_begin + col) + k_lo + off;
+    ptx::mbar_expect_tx(&full[j], (uint32_t)(cnt * 8));
+    ptx::bulk_load_1d(ring + off, src, (uint32_t)(cnt * 8), &full[j]);
+  };
+
+  int64_t col = cluster_id;
+  if (tid == 0 && col < p.l_count)
+    for (int j = 0; j < p.n_chunks; j++) issue(col, j);
+
+  for (uint32_t it = 0; col < p.l_count; col += n_clusters, it++) {
+    const uint32_t par = it & 1;
+    // ---- pass 1: largest magnitude of this CTA's part, chunk by chunk as the copies land
+    unsigned long long mx = 0;
+    for (int j = 0; j < p.n_chunks; j++) {
+      const int64_t off = (int64_t)j * PF_CHUNK;
+      const int cnt = (int)min((int64_t)PF_CHUNK, my_n - off);
+      if (cnt <= 0) break;
+      ptx::mbar_wait(&full[j], par);
+      const double2* c2 = reinterpret_cast<const double2*>(ring + off);
+      for (int i = tid; i < cnt / 2; i += PF_THREADS) {
+        const double2 v = c2[i];
+        const unsigned long long a = abs_key(v.x), b = abs_key(v.y);
+        mx = a > mx ? a : mx;
+        mx = b > mx ? b : mx;
+      }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+      const unsigned long long y = __shfl_xor_sync(0xffffffffu, mx, o);
+      mx = y > mx ? y : mx;
+    }
+    if (lane == 0) red[warp] = mx;
+    __syncthreads();
+    if (tid == 0) {
+      for (int w = 1; w < PF_THREADS / 32; w++) mx = red[w] > mx ? red[w] : mx;
+      for (int r = 0; r < p.C; r++) ptx::st_cluster_u64(&slots[par * 8 + rank], (uint32_t)r, mx);
+    }
+    ptx::cluster_arrive();
+    ptx::cluster_wait();
+    unsigned long long gmx = 0;
+    for (int r = 0; r < p.C; r++) gmx = slots[par * 8 + r] > gmx ? slots[par * 8 + r] : gmx;
+    // ---- the column's exponent / scale (same arithmetic as colexp_kernel)
+    int e = 0;
+    const double mxd = key_to_double(gmx);
+    const bool finite = mxd <= 1.7976931348623157e308;
+    if (finite && mxd > 0.0) frexp(mxd, &e);
+    if (rank == 0 && tid == 0) {
+      p.expo[col] = e;
+      p.colscale[col] = finite ? ldexp(1.0, e - 7) : __longlong_as_double(0x7ff8000000000000LL);
+    }
+    const int sh = 8 * S - 1 - e;
+    const bool fast_scale = sh > -1000 && sh < 1000;
+    const double mul = fast_scale ? ldexp(1.0, sh) : 0.0;  // exact power of two: w * mul == scalbn(w, sh)
+    // ---- pass 2: digits out of shared memory; chunk j is refilled with the next column as soon as it has been read
+    const int64_t tile = col / TC_BN, c_in = col - tile * TC_BN;
+    int8_t* qcol = p.q + ((tile * S) * TC_BN + c_in) * p.Kpad + k_lo;  // plane s: + s * TC_BN * Kpad
+    const int64_t next = col + n_clusters;
+    for (int j = 0; j < p.n_chunks; j++) {
+      const int64_t off = (int64_t)j * PF_CHUNK;
+      const int cnt = (int)min((int64_t)PF_CHUNK, my_n - off);
+      if (cnt <= 0) break;
+      for (int i4 = tid * 4; i4 < cnt; i4 += PF_THREADS * 4) {
+        const double2 v01 = *reinterpret_cast<const double2*>(ring + off + i4);
+        double2 v23 = make_double2(0.0, 0.0);
+        const bool two = i4 + 2 < cnt;   // cnt is even: a tail of two is possible
+        if (two) v23 = *reinterpret_cast<const double2*>(ring + off + i4 + 2);
+        const double wv[4] = {v01.x, v01.y, v23.x, v23.y};
+        uint32_t pack[TC_MAX_SLICES];
+#pragma unroll
+        for (int s = 0; s < TC_MAX_SLICES; s++) pack[s] = 0;
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+          long long qi = 0;
+          if (i < 2 || two) {
+            qi = (fast_scale ? llrint(wv[i] * mul) : llrint(scalbn(wv[i], sh))) + half;
+            qi = qi > top ? top : (qi < 0 ? 0 : qi);
+          }
+#pragma unroll
+          for (int s = 0; s < TC_MAX_SLICES; s++)
+            if (s < S) pack[s] |= (uint32_t)((qi >> (8 * (S - 1 - s))) & 255) << (8 * i);
+        }
+#pragma unroll
+        for (int s = 0; s < TC_MAX_SLICES; s++)
+          if (s < S) *reinterpret_cast<uint32_t*>(qcol + (int64_t)s * TC_BN * p.Kpad + off + i4) = pack[s];
+      }
+      __syncthreads();  // every thread has read chunk j
+      if (tid == 0 && next < p.l_count) {
+        ptx::fence_proxy_async();
+        issue(next, j);
+      }
+    }
+    // zero the K padding of this column's rows (the CTA that holds the end of the run)
+    if (k_lo + my_n == p.nK && my_n > 0) {
+      const int64_t pad0 = (p.nK + 3) & ~(int64_t)3;
+      for (int64_t k = pad0 + tid * 4; k < p.Kpad; k += PF_THREADS * 4)
+        for (int s = 0; s < S; s++) *reinterpret_cast<uint32_t*>(qcol - k_lo + (int64_t)s * TC_BN * p.Kpad + k) = 0u;
+    }
+  }
+  // nobody may exit while a peer can still store into its shared memory
+  ptx::cluster_arrive();
+  ptx::cluster_wait();
+}
+
+static bool planes_fused_applicable(const WView& w, int64_t nK) {
+  if (w.sK2 != 1 || !(w.nK1 == 1 || w.sK1 == w.nK2)) return false;       // one contiguous run of nK doubles per column
+  if (nK % 2 != 0 || nK < 4096 || nK > (int64_t)8 * PF_MAX_CHUNKS * PF_CHUNK) return false;
+  if ((reinterpret_cast<uintptr_t>(w.p) & 15) != 0) return false;         // bulk copies: 16-byte aligned
+  if (w.sL2 % 2 != 0 || (w.nL1 > 1 && w.sL1 % 2 != 0)) return false;
+  return true;
+}
+
+static void planes_fused_build(WSlices& ws, const WView& w, int64_t l_begin) {
+  PfParams p;
+  p.w = w; p.nK = ws.nK; p.Kpad = ws.Kpad; p.l_begin = l_begin; p.l_count = ws.l_count; p.S = ws.S;
+  int C = 1;
+  while (C < 8 && ceil_div(ws.nK, C) > (int64_t)PF_MAX_CHUNKS * PF_CHUNK) C <<= 1;
+  p.C = C;
+  p.segK = (int)(ceil_div(ceil_div(ws.nK, C), 16) * 16);
+  p.n_chunks = (int)ceil_div(p.segK, PF_CHUNK);
+  p.q = ws.q.p; p.expo = ws.expo.p; p.colscale = ws.colscale.p;
+  const size_t smem = (size_t)p.n_chunks * PF_CHUNK * 8 + PF_MAX_CHUNKS * 8 + 16 * 8 + 8 * 8;
+  static size_t attr_smem = 0;
+  if (smem > attr_smem) {
+    FRICC_CUDA(cudaFuncSetAttribute(planes_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
+    attr_smem = 227 * 1024;
+  }
+  // the tail tiles' unused column slots carry exponent 0 / scale 2^-7 like the two-pass builder leaves them
+  FRICC_LAUNCH(colexp_kernel, (unsigned)ceil_div(ws.n_tiles * TC_BN, 256), 256, 0, (const unsigned long long*)nullptr,
+               (int64_t)0, ws.n_tiles * TC_BN, ws.expo.p, ws.colscale.p);
+  cudaLaunchConfig_t cfg{};
+  cfg.blockDim = dim3(PF_THREADS);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream();
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = (unsigned)C;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  // persistent clusters: as many as can be co-resident (a cluster waiting for SMs would run its columns alone at the end)
+  cfg.gridDim = dim3((unsigned)(num_sms() / C * C));
+  int max_clusters = 0;
+  FRICC_CUDA(cudaOccupancyMaxActiveClusters(&max_clusters, planes_fused_kernel, &cfg));
+  if (max_clusters < 1) fail(FRICC_ECUDA, "planes_fused_kernel: no cluster of %d CTAs fits on this device", C);
+  const int64_t n_clusters = std::min<int64_t>(max_clusters, ws.l_count);
+  cfg.gridDim = dim3((unsigned)(n_clusters * C));
+  FRICC_CUDA(cudaLaunchKernelEx(&cfg, planes_fused_kernel, p));
+  check_launch("planes_fused_kernel");
+}
+
+// fingerprint of an operand for the plane cache: 4096 evenly spaced elements of the [K][L] view, XOR-folded with their
+// positions.  One tiny kernel + an 8-byte read-back.
+__global__ void fingerprint_kernel(const WView w, int64_t nK, int64_t l_begin, int64_t l_count,
+                                   unsigned long long* __restrict__ out) {
+  const int64_t total = nK * l_count;
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;  // 0..4095
+  const int64_t pos = total <= 4096 ? t : (int64_t)(((__int128)total * t) >> 12);
+  unsigned long long h = 0;
+  if (pos < total) {
+    const int64_t l = pos / nK, K = pos - l * nK;
+    const unsigned long long bits = (unsigned long long)__double_as_longlong(w.p[view_offK(w, K) + view_offL(w, l_begin + l)]);
+    h = (bits ^ (0x9E3779B97F4A7C15ULL * (unsigned long long)(pos + 1)));
+    h ^= h >> 29; h *= 0xBF58476D1CE4E5B9ULL; h ^= h >> 32;
+  }
+  for (int o = 16; o > 0; o >>= 1) h ^= __shfl_xor_sync(0xffffffffu, h, o);
+  if ((threadIdx.x & 31) == 0) atomicXor(out, h);
+}
+
+uint64_t view_fingerprint(const WView& w, int64_t l_begin, int64_t l_count) {
+  DevBuf<unsigned long long> acc(1);
+  acc.zero();
+  FRICC_LAUNCH(fingerprint_kernel, 16, 256, 0, w, w.nK1 * w.nK2, l_begin, l_count, acc.p);
+  unsigned long long h = 0;
+  acc.to_host(&h, 1);
+  return (uint64_t)h;
+}
+
+WView panel_view(const double* Wp, int64_t ldw, int64_t nK, int64_t l_begin, int64_t nL) {
+  // Wp[K][ldw] holds the columns [l_begin, ...) of the term's [K][L] matrix: element (K, l) = Wp[K*ldw + (l - l_begin)]
+  WView w;
+  w.p = Wp - l_begin;
+  w.sK1 = nK * ldw; w.sK2 = ldw; w.sL1 = nL; w.sL2 = 1;
+  w.nK1 = 1; w.nK2 = nK; w.nL1 = 1; w.nL2 = nL;
+  return w;
+}
+
+WView term_view(const double* W, const int64_t shape[4], const int64_t strides[4], const TermSpec& ts) {
+  WView w;
+  w.p = W;
+  w.sK1 = strides[ts.wK[0]]; w.sK2 = strides[ts.wK[1]];
+  w.sL1 = strides[ts.wL[0]]; w.sL2 = strides[ts.wL[1]];
+  w.nK1 = shape[ts.wK[0]]; w.nK2 = shape[ts.wK[1]];
+  w.nL1 = shape[ts.wL[0]]; w.nL2 = shape[ts.wL[1]];
+  return w;
+}
+
+bool view_is_panel(const WView& w) { return w.sL2 == 1 && (w.nL1 == 1 || w.sL1 == w.nL2) && (w.nK1 == 1 || w.sK1 == w.nK2 * w.sK2); }
+
+static int g_tc_fused_planes = 1;  // "tc_fused_planes": 1 = single-read cluster kernel for operands whose K run is contiguous
+static int g_tc_mode = 1;          // "tc_mode": what fricc_contract does -- 0 never the tensor-core form, 1 cost model, 2 always
+static int g_tc_planes = 6;        // "tc_planes": digit planes fricc_contract expands W into
+static int g_tc_plane_cache = 0;   // "tc_plane_cache": keep the planes of the last operands (see plane_cache_get)
+int tc_mode() { return g_tc_mode; }
+int tc_planes() { return g_tc_planes; }
+int tc_plane_cache() { return g_tc_plane_cache; }
+
+void wslices_build_view(WSlices& ws, const WView& w, int64_t l_begin, int64_t l_count, int S) {
   if (S < 1 || S > TC_MAX_SLICES) fail(FRICC_EINVAL, "digit planes must be 1..%d", TC_MAX_SLICES);
-  if (nK <= 0 || l_count <= 0 || ldw < l_count) fail(FRICC_EINVAL, "bad panel shape");
+  const int64_t nK = w.nK1 * w.nK2;
+  if (nK <= 0 || l_count <= 0) fail(FRICC_EINVAL, "bad operand shape");
   const int64_t Kpad = ceil_div(nK, TC_BK) * TC_BK, n_tiles = ceil_div(l_count, TC_BN);
   const size_t qbytes = (size_t)n_tiles * S * TC_BN * Kpad;
   if (ws.q.n != qbytes) ws.q.alloc(qbytes);
@@ -234,22 +557,39 @@ void wslices_build(WSlices& ws, const double* Wp, int64_t ldw, int64_t nK, int64
     ws.colscale.alloc((size_t)(n_tiles * TC_BN));
   }
   ws.nK = nK; ws.Kpad = Kpad; ws.l_count = l_count; ws.n_tiles = n_tiles; ws.S = S;
+  if (Kpad / TC_BK > 65535) fail(FRICC_EINVAL, "contracted pair too large for the slicing grid");
+  const bool kcontig = w.sK2 == 1 && w.sL2 != 1;
+  if (g_tc_fused_planes && planes_fused_applicable(w, nK) ) {
+    planes_fused_build(ws, w, l_begin);
+    return;
+  }
   DevBuf<unsigned long long> colmax((size_t)l_count);
   colmax.zero();
   const int64_t kpb = std::max<int64_t>(256, ceil_div(nK, 64));
-  dim3 g1((unsigned)ceil_div(l_count, 128), (unsigned)ceil_div(nK, kpb));
-  FRICC_LAUNCH(colmax_kernel, g1, 128, 0, Wp, ldw, nK, l_count, kpb, colmax.p);
+  if (kcontig) {
+    dim3 g1((unsigned)ceil_div(l_count, 8), (unsigned)ceil_div(nK, kpb));
+    FRICC_LAUNCH(colmax_view_kernel<true>, g1, 256, 0, w, nK, l_begin, l_count, kpb, colmax.p);
+  } else {
+    dim3 g1((unsigned)ceil_div(l_count, 128), (unsigned)ceil_div(nK, kpb));
+    FRICC_LAUNCH(colmax_view_kernel<false>, g1, 128, 0, w, nK, l_begin, l_count, kpb, colmax.p);
+  }
   FRICC_LAUNCH(colexp_kernel, (unsigned)ceil_div(n_tiles * TC_BN, 256), 256, 0, colmax.p, l_count, n_tiles * TC_BN,
                ws.expo.p, ws.colscale.p);
   const size_t smem = (size_t)S * TC_BN * 33 * 4;
   static bool attr_set = false;
   if (!attr_set) {
-    FRICC_CUDA(cudaFuncSetAttribute(slice_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_MAX_SLICES * TC_BN * 33 * 4));
+    FRICC_CUDA(cudaFuncSetAttribute(slice_view_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_MAX_SLICES * TC_BN * 33 * 4));
+    FRICC_CUDA(cudaFuncSetAttribute(slice_view_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_MAX_SLICES * TC_BN * 33 * 4));
     attr_set = true;
   }
-  if (Kpad / TC_BK > 65535) fail(FRICC_EINVAL, "contracted pair too large for the slicing grid");
   dim3 g2((unsigned)n_tiles, (unsigned)(Kpad / TC_BK));
-  FRICC_LAUNCH(slice_kernel, g2, 256, smem, Wp, ldw, nK, l_count, Kpad, S, ws.expo.p, ws.q.p);
+  if (kcontig) FRICC_LAUNCH(slice_view_kernel<true>, g2, 256, smem, w, nK, l_begin, l_count, Kpad, S, ws.expo.p, ws.q.p);
+  else FRICC_LAUNCH(slice_view_kernel<false>, g2, 256, smem, w, nK, l_begin, l_count, Kpad, S, ws.expo.p, ws.q.p);
+}
+
+void wslices_build(WSlices& ws, const double* Wp, int64_t ldw, int64_t nK, int64_t l_count, int S) {
+  if (nK <= 0 || l_count <= 0 || ldw < l_count) fail(FRICC_EINVAL, "bad panel shape");
+  wslices_build_view(ws, panel_view(Wp, ldw, nK, 0, l_count), 0, l_count, S);
 }
 
 void wslices_reconstruct(const WSlices& ws, double* Wrec) {
@@ -731,10 +1071,55 @@ static CUtensorMap make_map_i8(const int8_t* base, int64_t rows, int64_t Kpad, i
 static int g_tc_persistent = 1;  // "tc_persistent" option: 1 = one CTA per SM looping over tiles, 0 = one CTA per tile
 void set_tc_option(const char* key, int value) {
   if (strcmp(key, "tc_persistent") == 0) g_tc_persistent = value;
+  else if (strcmp(key, "tc_fused_planes") == 0) g_tc_fused_planes = value;
+  else if (strcmp(key, "tc_mode") == 0) g_tc_mode = value;
+  else if (strcmp(key, "tc_planes") == 0) {
+    if (value < 1 || value > TC_MAX_SLICES) fail(FRICC_EINVAL, "tc_planes must be 1..%d", TC_MAX_SLICES);
+    g_tc_planes = value;
+  } else if (strcmp(key, "tc_plane_cache") == 0) g_tc_plane_cache = value;
+  else fail(FRICC_EINVAL, "unknown option '%s'", key);
 }
 
-void contract_dense(fricc_st* T, const TermSpec& ts, Layout& lay, const WSlices& ws, const double* Wp, int64_t ldw,
-                    int64_t l_begin, double* out, const OutMap& om, double scale, bool overwrite) {
+// CSR remainder x W read through a 4-D view (no panel): out[R, l] += scale * sum_e val_e * W[offK(K_e) + offL(l)].
+// Block = (TL columns) x (TR buckets); a thread owns one (R, l) and walks its bucket.  LCONTIG views use TL = 32 (a
+// warp reads 256 contiguous bytes of a W row); KCONTIG views use TL = 4, TR = 64: the lanes of a warp then read one
+// column's scattered K -- every access its own 32-byte sector either way, but all of a CTA's reads fall into four
+// contiguous K runs, which L2 keeps.  The remainder is the small exact part of an FRI compression; the sampled part
+// never comes through here.
+__global__ void __launch_bounds__(256)
+spmm_csr_view_kernel(const int64_t* __restrict__ rowptr, const uint32_t* __restrict__ kidx,
+                     const double* __restrict__ vals, int64_t nR, const WView w, int64_t l_begin, int64_t l_count,
+                     double* __restrict__ out, OutMap om, double scale) {
+  const int64_t col = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t R = (int64_t)blockIdx.y * blockDim.y + threadIdx.y;
+  if (col >= l_count || R >= nR) return;
+  const int64_t e0 = rowptr[R], e1 = rowptr[R + 1];
+  if (e0 == e1) return;
+  const int64_t l = l_begin + col;
+  const double* base = w.p + view_offL(w, l);
+  double acc = 0.0;
+  for (int64_t e = e0; e < e1; e++) acc = fma(vals[e], __ldg(base + view_offK(w, (int64_t)kidx[e])), acc);
+  const int64_t r1 = R / om.nR2, r2 = R - r1 * om.nR2;
+  const int64_t l1 = l / om.nL2, l2 = l - l1 * om.nL2;
+  out[r1 * om.sR1 + r2 * om.sR2 + l1 * om.sL1 + l2 * om.sL2] += scale * acc;
+}
+
+void spmm_csr_view(const int64_t* rowptr, const uint32_t* kidx, const double* vals, int64_t nR, const WView& w,
+                   int64_t l_begin, int64_t l_count, double* out, const OutMap& om, double scale) {
+  if (nR == 0 || l_count == 0) return;
+  if (view_is_panel(w)) {  // a [K][ld] panel: the streaming kernels of fricc_contract.cu
+    spmm_csr(rowptr, kidx, vals, nR, w.p + l_begin, w.sK2, l_begin, l_count, out, om, scale);
+    return;
+  }
+  const bool kcontig = w.sK2 == 1 && w.sL2 != 1;
+  dim3 block(kcontig ? 4 : 32, kcontig ? 64 : 8);
+  if (ceil_div(nR, block.y) > 65535) fail(FRICC_EINVAL, "spmm: owner pair too large (%lld rows)", (long long)nR);
+  dim3 grid((unsigned)ceil_div(l_count, block.x), (unsigned)ceil_div(nR, block.y));
+  FRICC_LAUNCH(spmm_csr_view_kernel, grid, block, 0, rowptr, kidx, vals, nR, w, l_begin, l_count, out, om, scale);
+}
+
+void contract_dense(fricc_st* T, const TermSpec& ts, Layout& lay, const WSlices& ws, const WView& w, int64_t l_begin,
+                    double* out, const OutMap& om, double scale, bool overwrite) {
   if (ws.nK != lay.nK) fail(FRICC_EINVAL, "digit planes were built for %lld contracted indices, the term has %lld",
                             (long long)ws.nK, (long long)lay.nK);
   dense_form(T, ts, lay);
@@ -762,7 +1147,13 @@ void contract_dense(fricc_st* T, const TermSpec& ts, Layout& lay, const WSlices&
     FRICC_LAUNCH(tc_sign_gemm_kernel, grid, TC_THREADS, smem, tmA, tmB, p);
   }
   if (lay.n_rest != 0)
-    spmm_csr(lay.rest_rowptr.p, lay.rest_kidx.p, lay.rest_vals.p, lay.nR, Wp, ldw, l_begin, ws.l_count, out, om, scale);
+    spmm_csr_view(lay.rest_rowptr.p, lay.rest_kidx.p, lay.rest_vals.p, lay.nR, w, l_begin, ws.l_count, out, om, scale);
+}
+
+void contract_dense(fricc_st* T, const TermSpec& ts, Layout& lay, const WSlices& ws, const double* Wp, int64_t ldw,
+                    int64_t l_begin, double* out, const OutMap& om, double scale, bool overwrite) {
+  contract_dense(T, ts, lay, ws, panel_view(Wp, ldw, ws.nK, l_begin, l_begin + ws.l_count), l_begin, out, om, scale,
+                 overwrite);
 }
 
 }  // namespace fricc

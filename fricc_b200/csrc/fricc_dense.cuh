@@ -18,6 +18,29 @@ struct WSlices {
 
 constexpr int TC_MAX_SLICES = 7;
 
+// The [K][L] operand of a term as a VIEW of the caller's 4-D array: element (K, l) -- K = k1*nK2 + k2 the contracted
+// pair, l = l1*nL2 + l2 the free pair, both GLOBAL indices -- is p[k1*sK1 + k2*sK2 + l1*sL1 + l2*sL2] (element strides).
+struct WView {
+  const double* p;
+  int64_t sK1, sK2, sL1, sL2;
+  int64_t nK1, nK2, nL1, nL2;
+};
+// a [K][ldw] row-major panel holding the columns [l_begin, ...) of an nL-column operand
+WView panel_view(const double* Wp, int64_t ldw, int64_t nK, int64_t l_begin, int64_t nL);
+// the operand of `ts` inside a 4-D array with the given shape / element strides
+WView term_view(const double* W, const int64_t shape[4], const int64_t strides[4], const TermSpec& ts);
+bool view_is_panel(const WView& w);
+// planes of the columns [l_begin, l_begin + l_count) of a view, read where the operand lies (no fp64 panel).  Operands
+// whose contracted run is contiguous (the ladder's native W[a,b,c,d]) go through a single-read cluster kernel.
+void wslices_build_view(WSlices& ws, const WView& w, int64_t l_begin, int64_t l_count, int S);
+void contract_dense(fricc_st* T, const TermSpec& ts, Layout& lay, const WSlices& ws, const WView& w, int64_t l_begin,
+                    double* out_dev, const OutMap& om, double scale, bool overwrite = false);
+void spmm_csr_view(const int64_t* rowptr, const uint32_t* kidx, const double* vals, int64_t nR, const WView& w,
+                   int64_t l_begin, int64_t l_count, double* out_dev, const OutMap& om, double scale);
+int tc_mode();         // option "tc_mode": 0 never / 1 cost model / 2 always -- what fricc_contract does
+int tc_planes();       // option "tc_planes"
+int tc_plane_cache();  // option "tc_plane_cache"
+
 void wslices_build(WSlices& ws, const double* Wp_dev, int64_t ldw, int64_t nK, int64_t l_count, int S);
 // Wrec[K][l_count] = the value the digits represent (fp64), for tests of the expansion
 void wslices_reconstruct(const WSlices& ws, double* Wrec_dev);

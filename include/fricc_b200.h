@@ -58,12 +58,26 @@ int fricc_stream_synchronize(void);
  * L1/shared split (percent shared) those kernels ask for, default 100 = the split the tensor-core kernel runs under,
  * so that both can be resident on one SM; -1 = the device default.                                               */
 int fricc_set_option(const char* key, int value);
+/* "spmm_exact_order": 0 (default) = the fast contraction kernels ((R,K)-sorted buckets, FMA, within 1e-10 of the
+ * reference); 1 = PARITY MODE: every contraction adds the entries of an owner pair in storage order with one rounded
+ * product and one rounded sum per entry straight onto the output element, exactly like the reference's loop nest
+ * (sparse_tensor.cpp:66-73) -- bit-identical outputs, fp64 SpMM only (the tensor-core form is bypassed).
+ * "tc_mode": which form fricc_contract picks -- 0 = always the fp64 SpMM, 1 (default) = the tensor-core form when its
+ * cost model says it wins (an FRI-compressed T with at least half of its entries sampled, a large enough product),
+ * 2 = always the tensor-core form.  "tc_planes": digit planes it expands W into (default 6 = 48 bits per column).
+ * "tc_fused_planes": 1 (default) = operands whose contracted run is contiguous (the ladder's native W[a,b,c,d]) are
+ * expanded by the single-read cluster kernel, 0 = by the two-pass kernels (identical planes).
+ * "tc_plane_cache": 1 = fricc_contract keeps the planes of up to 12 device operands across calls, keyed by address,
+ * shape and strides and guarded by a fingerprint of 4096 sampled elements (for drivers that hand over the same
+ * operands every iteration, fricc/frilccsd.py:171-179); default 0 = planes are rebuilt on every call.               */
+int fricc_plane_cache_clear(void);
 /* "d_parallel": -1 (default) = the parallel D-selection for candidate lists >= 32768 and the one-warp walk below,
  * 0 / 1 = always serial / always parallel (bit-identical).
  * "pivotal_parallel": -1 (default) = the parallel exact pivotal sampler for N >= 65536 and the one-thread chain kernel
  * below, 0 = always the chain kernel, 1 = always the parallel sampler (bit-identical results).
  * fricc_get_stat: counters of the last call -- "pivotal_restarts" (how many times the parallel sampler had to restart
- * behind a run whose predicted start did not match the chain; 0 in the common case).                              */
+ * behind a run whose predicted start did not match the chain; 0 in the common case); "tc_contract_calls" /
+ * "spmm_contract_calls": how many fricc_contract calls since load took the tensor-core form / the fp64 SpMM.      */
 int fricc_get_stat(const char* key, int64_t* value);
 /* number of kernels this library has launched since load (bench.py's "gpu_launches" evidence) */
 int64_t fricc_kernel_launches(void);
@@ -119,7 +133,11 @@ int fricc_st_export(fricc_st_t t, int64_t* flat_idx, double* vals, int mem);
  * out[...] += scale * sum_K T[R,K] * W[...]   for term in
  *   "0101" "2323" "1302" "1202" "1303" "1203" "1323" "0112" "0313" "0113" "0312"   (table in SURVEY.md 8a-3)
  * plus the experimental 2323 variants "taskloop" / "atomic" (sparse_tensor.cpp:445-459), which compute the same sum.
- * W and out are 4-D binary64 arrays with arbitrary element strides (numpy semantics); out is accumulated in place. */
+ * W and out are 4-D binary64 arrays with arbitrary element strides (numpy semantics); out is accumulated in place.
+ * This one call picks the kernel (option "tc_mode"): the bucketed fp64 SpMM, or -- for an FRI-compressed T on a product
+ * large enough -- the tensor-core form, with the int8 digit planes expanded straight from the 4-D operand where it
+ * lies (no [K][L] fp64 copy), so a driver that calls contract_DTSpT gets the same kernel the sharded engine runs.
+ * With every array on the device the call is asynchronous on the library stream.                                    */
 int fricc_contract(const double* W, int w_mem, const int64_t w_shape[4], const int64_t w_strides[4], fricc_st_t T,
                    double* out, int out_mem, const int64_t out_shape[4], const int64_t out_strides[4],
                    const char* term);
