@@ -79,6 +79,10 @@ SIGNATURES = {
                                           c_char_p]),
     "fricc_accumulate_panels": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_char_p, c_void_p, _i64p, _i64p]),
     "fricc_wslices_create": (c_int, [c_void_p, c_int64, c_int64, c_int64, c_int, POINTER(c_void_p)]),
+    "fricc_wslices_create_view": (c_int, [c_void_p, _i64p, _i64p, c_char_p, c_int64, c_int64, c_int,
+                                          POINTER(c_void_p)]),
+    "fricc_contract_planes": (c_int, [c_void_p, c_void_p, _i64p, _i64p, c_int64, c_void_p, c_void_p, _i64p, _i64p,
+                                      c_char_p]),
     "fricc_wslices_update": (c_int, [c_void_p, c_void_p, c_int64]),
     "fricc_wslices_destroy": (c_int, [c_void_p]),
     "fricc_wslices_bytes": (c_int, [c_void_p, _i64p]),

@@ -92,6 +92,9 @@ int create_impl(const double* tensor, int mem, const int64_t dims[4], int64_t m,
   for (int i = 0; i < 4; i++) t->dims[i] = dims[i];
   build_from_compressed(t, c);
   if (largest) t->n_exact = t->nnz;  // no common magnitude to expect
+  // an unknown sampling method leaves S empty and the tail unfilled (fri_utils.cpp:443-444 can never fire): no promise
+  // about the entries behind D -- the tensor-core form then classifies every entry instead of trusting the hint
+  else if (parse_sampling(sampling_method) == Sampling::None) t->n_exact = -1;
   FRICC_CUDA(cudaStreamSynchronize(stream()));  // staged input must outlive the kernels that read it
   *out = t;
   FRICC_API_END
@@ -625,6 +628,26 @@ int fricc_wslices_create(const double* Wp_dev, int64_t ldw, int64_t nK, int64_t 
   FRICC_API_END
 }
 
+int fricc_wslices_create_view(const double* W_dev, const int64_t w_shape[4], const int64_t w_strides[4], const char* term,
+                              int64_t l_begin, int64_t l_count, int n_planes, fricc_wslices_t* out) {
+  FRICC_API_BEGIN
+  if (!W_dev || !w_shape || !w_strides || !out) fail(FRICC_EINVAL, "null argument");
+  const TermSpec* ts = find_term(term);
+  if (!ts) fail(FRICC_EINVAL, "CASE NOT IMPLEMENTED: unknown contraction term '%s'", term ? term : "(null)");
+  const int64_t nL = w_shape[ts->wL[0]] * w_shape[ts->wL[1]];
+  if (l_begin < 0 || l_count <= 0 || l_begin + l_count > nL) fail(FRICC_EINVAL, "column range out of bounds");
+  (void)span_of(w_shape, w_strides);  // rejects negative strides
+  fricc_wslices* h = new fricc_wslices();
+  try {
+    wslices_build_view(h->ws, term_view(W_dev, w_shape, w_strides, *ts), l_begin, l_count, n_planes);
+  } catch (...) {
+    delete h;
+    throw;
+  }
+  *out = h;
+  FRICC_API_END
+}
+
 int fricc_wslices_update(fricc_wslices_t h, const double* Wp_dev, int64_t ldw) {
   FRICC_API_BEGIN
   if (!h || !Wp_dev) fail(FRICC_EINVAL, "null argument");
@@ -734,6 +757,32 @@ int fricc_contract_panel_into_tc(fricc_wslices_t h, const double* Wp_dev, int64_
   om.sL1 = out_strides[ts->oL[0]];
   om.sL2 = out_strides[ts->oL[1]];
   contract_tc_common(h, Wp_dev, ldw, l_begin, T, out_dev, om, ts);
+  FRICC_API_END
+}
+
+int fricc_contract_planes(fricc_wslices_t h, const double* W_dev, const int64_t w_shape[4], const int64_t w_strides[4],
+                          int64_t l_begin, fricc_st_t T, double* out_dev, const int64_t out_shape[4],
+                          const int64_t out_strides[4], const char* term) {
+  FRICC_API_BEGIN
+  check_handle(T);
+  const TermSpec* ts = find_term(term);
+  if (!ts) fail(FRICC_EINVAL, "CASE NOT IMPLEMENTED: unknown contraction term '%s'", term ? term : "(null)");
+  if (!h || !W_dev || !out_dev || !w_shape || !w_strides || !out_shape || !out_strides || l_begin < 0)
+    fail(FRICC_EINVAL, "bad arguments");
+  const int64_t* d = T->dims;
+  for (int q = 0; q < 2; q++) {
+    if (w_shape[ts->wK[q]] != d[ts->tK[q]]) fail(FRICC_EINVAL, "term %s: W does not match T on the contracted pair", ts->name);
+    if (out_shape[ts->oR[q]] != d[ts->tR[q]]) fail(FRICC_EINVAL, "term %s: out does not match T on the owner pair", ts->name);
+    if (out_shape[ts->oL[q]] != w_shape[ts->wL[q]]) fail(FRICC_EINVAL, "term %s: out does not match W on the free pair", ts->name);
+  }
+  const int64_t nL = w_shape[ts->wL[0]] * w_shape[ts->wL[1]];
+  if (l_begin + h->ws.l_count > nL) fail(FRICC_EINVAL, "column range out of bounds");
+  if (T->nnz == 0 || h->ws.l_count == 0) return FRICC_OK;
+  const OutMap om = out_map(*ts, d, out_shape, out_strides);
+  const WView view = term_view(W_dev, w_shape, w_strides, *ts);
+  if (spmm_exact_order()) fail(FRICC_EINVAL, "parity mode (spmm_exact_order) runs through fricc_contract");
+  Layout& lay = get_layout(T, *ts, false);
+  contract_dense(T, *ts, lay, h->ws, view, l_begin, out_dev, om, ts->scale, false);
   FRICC_API_END
 }
 

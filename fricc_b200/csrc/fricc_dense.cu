@@ -729,8 +729,25 @@ __global__ void sign_scatter_kernel(const int64_t* __restrict__ flat, const doub
   const int64_t R = ix[td.r0] * td.d[td.r1] + ix[td.r1];
   const int64_t K = ix[td.k0] * td.d[td.k1] + ix[td.k1];
   const double v = vals[e], c = cmag[0];
-  if (fabs(fabs(v) - c) <= c * 1.7763568394002505e-15 && v != 0.0) A[R * Kpad + K] = v > 0.0 ? (int8_t)1 : (int8_t)-1;
-  else atomicAdd(stragglers, 1ULL);
+  if (fabs(fabs(v) - c) <= c * 1.7763568394002505e-15 && v != 0.0) {
+    // A[R][K] += sign.  A position sampled more than once (the systematic sampler's unmatched samples all land on flat
+    // index 0, fri_utils.cpp:132,149-157) simply carries the multiplicity: the int8 product takes any A in [-127, 127].
+    const int sg = v > 0.0 ? 1 : -1;
+    const int64_t byte = R * Kpad + K;
+    unsigned* word = reinterpret_cast<unsigned*>(A + (byte & ~(int64_t)3));
+    const int sh = 8 * (int)(byte & 3);
+    unsigned old = *word, assumed;
+    bool overflow = false;
+    do {
+      assumed = old;
+      const int cur = (int)(int8_t)((assumed >> sh) & 255u) + sg;
+      if (cur > 127 || cur < -127) { overflow = true; break; }
+      old = atomicCAS(word, assumed, (assumed & ~(255u << sh)) | ((unsigned)(cur & 255) << sh));
+    } while (old != assumed);
+    if (overflow) atomicAdd(stragglers, 1ULL);
+  } else {
+    atomicAdd(stragglers, 1ULL);
+  }
 }
 
 // one CTA per row: sum and non-zero count of the row's bytes
@@ -750,7 +767,7 @@ rowsum_kernel(const int8_t* __restrict__ A, int64_t Kpad, int32_t* __restrict__ 
       for (int b = 0; b < 4; b++) {
         const int v = (int)(int8_t)((unsigned)ws[q] >> (8 * b));
         sum += v;
-        cnt += v != 0;
+        cnt += v < 0 ? -v : v;   // multiplicities: sum_K |A[R][K]| over all rows must equal the number of sampled entries
       }
     }
   }
@@ -768,9 +785,10 @@ rowsum_kernel(const int8_t* __restrict__ A, int64_t Kpad, int32_t* __restrict__ 
   }
 }
 
-// The provenance hint promised "every entry behind the first n_exact is +-c at a distinct position".  If that does not
-// hold (a straggler magnitude, or two entries on one position) the common magnitude is poisoned, so the contraction
-// returns NaN instead of a silently wrong number -- without a host round trip.
+// The provenance hint promised "every entry behind the first n_exact is +-c".  If that does not hold (a straggler
+// magnitude -- e.g. x[0]/0 when an unmatched systematic sample lands on an element of D, where the reference's own sum is
+// inf/nan too -- or opposite signs cancelling on one position, which a compression cannot produce) the common
+// magnitude is poisoned, so the contraction returns NaN instead of a silently wrong number, without a host round trip.
 __global__ void sign_check_kernel(const unsigned long long* __restrict__ stragglers,
                                   const unsigned long long* __restrict__ nnzA, unsigned long long expected,
                                   double* __restrict__ cmag) {

@@ -190,7 +190,19 @@ typedef struct fricc_wslices* fricc_wslices_t; /* digit planes of one W panel (d
 /* planes of the panel columns [0, l_count) of Wp_dev[nK][ldw] */
 int fricc_wslices_create(const double* Wp_dev, int64_t ldw, int64_t nK, int64_t l_count, int n_planes,
                          fricc_wslices_t* out);
+/* planes of the columns [l_begin, l_begin + l_count) of the [K][L] operand of `term`, read where it lies inside the 4-D
+ * device array W (element strides): no fp64 panel is formed.  Operands whose contracted run is contiguous -- the
+ * ladder's native W[a,b,c,d] -- go through a cluster kernel that reads every element from HBM once.                  */
+int fricc_wslices_create_view(const double* W_dev, const int64_t w_shape[4], const int64_t w_strides[4], const char* term,
+                              int64_t l_begin, int64_t l_count, int n_planes, fricc_wslices_t* out);
 int fricc_wslices_update(fricc_wslices_t h, const double* Wp_dev, int64_t ldw); /* re-expand (W changed), same shape */
+/* out[.., l, ..] += scale * sum_K T[R,K] * W[K,l] for the columns l in [l_begin, l_begin + planes' l_count) with planes
+ * the caller keeps (an operand that does not change between iterations: built once with fricc_wslices_create_view);
+ * W_dev is the same 4-D operand, read where it lies for the exact part of T.  (fricc_contract does both steps in one
+ * call; this is the two-step form for drivers that hold on to the planes.)                                           */
+int fricc_contract_planes(fricc_wslices_t h, const double* W_dev, const int64_t w_shape[4], const int64_t w_strides[4],
+                          int64_t l_begin, fricc_st_t T, double* out_dev, const int64_t out_shape[4],
+                          const int64_t out_strides[4], const char* term);
 int fricc_wslices_destroy(fricc_wslices_t h);
 int fricc_wslices_bytes(fricc_wslices_t h, int64_t* bytes);
 /* Wrec_dev[nK][l_count] = the fp64 value the planes represent (for tests of the expansion) */

@@ -209,6 +209,14 @@ class Ref:
             L.ref_parallel_sample.argtypes = [c_long, c_void_p, c_long, c_int, c_void_p]
         self.L = L
 
+    def set_num_threads(self, n):
+        """OpenMP threads of the reference from here on (contractions are bit-identical for any count)."""
+        if hasattr(self.L, "ref_set_num_threads"):
+            self.L.ref_set_num_threads(int(n))
+
+    def reset_rand_calls(self):
+        self.L.ref_reset_rand_calls()
+
     def set_draws(self, draws):
         d = _i32(draws)
         self.L.ref_set_draws(_p(d), d.size)

@@ -58,6 +58,11 @@ void ref_clear_draws(void) {
 long ref_rand_calls(void) { return g_calls; }
 void ref_reset_rand_calls(void) { g_calls = 0; }
 
+// OpenMP threads of the reference for the calls that follow (the contraction kernels give the same bits for any
+// thread count: one owner thread per output pair, sparse_tensor.cpp:62-64; one_norm does not)
+void ref_set_num_threads(int n) { omp_set_num_threads(n > 0 ? n : 1); }
+int ref_get_max_threads(void) { return omp_get_max_threads(); }
+
 double ref_one_norm(const double* x, long n) { return one_norm(std::span<const double>(x, (size_t)n)); }
 
 void ref_argsort(const double* x, long n, long m, long* out) {

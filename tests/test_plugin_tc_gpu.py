@@ -1,0 +1,244 @@
+"""The tensor-core form through the PLUGIN CALL: `py_rccsd.contract_DTSpT` (= fricc_contract, the one symbol the
+reference's drivers call, src/py_rccsd.cpp:50-51) picks the kernel itself and builds the int8 digit planes straight from
+the 4-D operand it is handed (any strides, host or device), so a maintainer who only swaps the module gets the kernel the
+sharded engine runs.  Checked against the oracle at the P6 tolerance (1e-10 relative) with the form forced on
+("tc_mode" 2) and off (0), for every term, at the molecular shapes of BASELINE.json's configs (H2O
+o=5,v=19; N2 o=7,v=53; benzene o=21,v=93 with the clamped m), at a shape that crosses many K blocks and more tiles
+than there are SMs, with heavy-tailed W, and for the single-read plane builder against the two-pass one."""
+import ctypes
+
+import numpy as np
+import pytest
+from conftest import TERMS, synth_t2
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-10
+
+
+@pytest.fixture()
+def tc(rccsd):
+    """contract_DTSpT with the tensor-core form forced; restores the cost model afterwards."""
+    rccsd.set_option("tc_mode", 2)
+    yield rccsd
+    rccsd.set_option("tc_mode", 1)
+    rccsd.set_option("tc_planes", 6)
+    rccsd.set_option("tc_fused_planes", 1)
+    rccsd.set_option("tc_plane_cache", 0)
+
+
+def _fri(rccsd, rng, no, nv, m, method="systematic"):
+    n = no * no * nv * nv
+    t2 = synth_t2(rng, n, "heavier").reshape(no, no, nv, nv)
+    draws = rng.integers(0, 2**31 - 1, size=n).astype(np.int32)
+    T = rccsd.SparseTensor4d(t2, t2.shape, int(m), "fri", method, False, draws=draws)
+    flat, vals = T.export()
+    return T, flat, vals, (no, no, nv, nv)
+
+
+def _close(got, want, tol=TOL):
+    return np.abs(got - want).max() <= tol * max(1.0, np.abs(want).max())
+
+
+@pytest.mark.parametrize("no,nv,m", [(5, 19, 1000), (5, 19, 4000), (7, 53, 50000)])
+@pytest.mark.parametrize("method", ["systematic", "pivotal"])
+def test_molecular_shapes_every_term_both_forms(tc, port, no, nv, m, method):
+    """H2O / cc-pVDZ (o=5, v=19, N=9025: m=1e4 of the literal config is rejected by the reference, fricc/friccsd.py:69-72)
+    and N2 / cc-pVTZ (o=7, v=53, N=137641: m=1e6 rejected) at the clamped m of SURVEY.md 8d."""
+    rccsd = tc
+    rng = np.random.default_rng(no * 1000 + nv + m)
+    T, flat, vals, dims = _fri(rccsd, rng, no, nv, m, method)
+    ext = {"o": no, "v": nv}
+    before = rccsd.get_stat("tc_contract_calls")
+    for term, (wax, oax, _, _) in sorted(TERMS.items()):
+        W = rng.random([ext[c] for c in wax]) - 0.3
+        o0 = rng.random([ext[c] for c in oax])
+        want = o0.copy()
+        port.contract(term, W, flat, vals, dims, want)
+        got = o0.copy()
+        rccsd.contract_DTSpT(W, T, got, term)                 # tensor cores
+        assert _close(got, want), (term, "tc")
+        rccsd.set_option("tc_mode", 0)
+        got2 = o0.copy()
+        rccsd.contract_DTSpT(W, T, got2, term)                # fp64 SpMM
+        rccsd.set_option("tc_mode", 2)
+        assert _close(got2, want), (term, "spmm")
+    assert rccsd.get_stat("tc_contract_calls") - before == len(TERMS)
+
+
+def test_benzene_shape_against_the_compiled_reference(tc, ref):
+    """benzene / cc-pVDZ shape (o=21, v=93, N=3 814 209; the literal m=5e6 is rejected by the reference) at m=1e6:
+    both samplers' compressions bit-identical to the compiled reference, then the ladder and two O^3V^3 / O^4V^2 terms
+    against the reference's own kernels (all host cores; its contractions give the same bits for any thread count)."""
+    import os
+
+    rccsd = tc
+    no, nv, m = 21, 93, 1_000_000
+    rng = np.random.default_rng(2193)
+    shape = (no, no, nv, nv)
+    n = int(np.prod(shape))
+    t2 = synth_t2(rng, n, "heavier").reshape(shape)
+    draws = rng.integers(0, 2**31 - 1, size=n + 8).astype(np.int32)
+    for method in ("systematic", "pivotal"):
+        ref.set_draws(draws)
+        want = ref.fri_compression(t2, m, method, draws)
+        T = rccsd.SparseTensor4d(t2, shape, m, "fri", method, False, draws=draws)
+        flat, vals = T.export()
+        assert np.array_equal(flat, want["idx"]) and np.array_equal(vals, want["vals"]), method
+    ref.set_draws(draws)
+    T_ref = ref.mod.SparseTensor4d(t2, list(shape), m, "fri", "pivotal", False)
+    ref.clear_draws()
+    ref.set_num_threads(os.cpu_count() or 1)
+    try:
+        ext = {"o": no, "v": nv}
+        for term in ("2323", "1302", "0313", "0101"):
+            wax, oax, _, _ = TERMS[term]
+            W = rng.random([ext[c] for c in wax])
+            want = np.zeros([ext[c] for c in oax])
+            ref.mod.contract_DTSpT(W, T_ref, want, term)
+            for mode in (2, 0):
+                rccsd.set_option("tc_mode", mode)
+                got = np.zeros_like(want)
+                rccsd.contract_DTSpT(W, T, got, term)
+                assert _close(got, want), (term, mode)
+            rccsd.set_option("tc_mode", 2)
+    finally:
+        ref.set_num_threads(1)
+
+
+def test_auto_mode_picks_the_tensor_cores_for_a_dense_fri_tensor(rccsd, port):
+    """Default "tc_mode" 1: the cost model sends a 20 %-dense FRI tensor on a (289 x 4096) x (4096 x 4096) product to
+    the tensor cores and a "largest" compression of the same size to the SpMM.  K = 4096 is 32 pipeline blocks, the 192
+    output tiles are more than the 148 persistent CTAs (every CTA loops), and row sums reach ~800."""
+    rng = np.random.default_rng(17)
+    no, nv = 17, 64
+    n = no * no * nv * nv
+    T, flat, vals, dims = _fri(rccsd, rng, no, nv, n // 5)
+    W = rng.random((nv, nv, nv, nv)) - 0.25
+    want = np.zeros(dims)
+    port.contract("2323", W, flat, vals, dims, want)
+    tc0, sp0 = rccsd.get_stat("tc_contract_calls"), rccsd.get_stat("spmm_contract_calls")
+    got = np.zeros(dims)
+    rccsd.contract_DTSpT(W, T, got, "2323")
+    assert rccsd.get_stat("tc_contract_calls") == tc0 + 1
+    assert _close(got, want)
+    t2 = rng.standard_normal(dims)
+    Tl = rccsd.SparseTensor4d(t2, dims, n // 5, "largest")
+    got = np.zeros(dims)
+    rccsd.contract_DTSpT(W, Tl, got, "2323")
+    assert rccsd.get_stat("spmm_contract_calls") == sp0 + 1
+
+
+def test_strided_and_device_operands_through_the_plugin_call(tc, port):
+    import torch
+
+    rccsd = tc
+    rng = np.random.default_rng(23)
+    no, nv = 6, 14
+    T, flat, vals, dims = _fri(rccsd, rng, no, nv, 1500, "pivotal")
+    # FRILCCSD's operands are transposed views (fricc/frilccsd.py:171-174)
+    oooo = rng.random((no, no, no, no))
+    W = oooo.transpose(0, 2, 1, 3)
+    want = np.zeros(dims)
+    port.contract("0101", np.ascontiguousarray(W), flat, vals, dims, want)
+    got = np.zeros(dims)
+    rccsd.contract_DTSpT(W, T, got, "0101")
+    assert _close(got, want)
+    # device tensors, the output a transposed view, an L-slice of the operand (what one rank of the sharded engine passes)
+    Wv = rng.random((nv, nv, nv, nv))
+    want = np.zeros(dims)
+    port.contract("2323", Wv, flat, vals, dims, want)
+    Wd = torch.from_numpy(Wv).cuda()
+    outd = torch.zeros(dims, dtype=torch.float64, device="cuda")
+    for a0, a1 in ((0, 5), (5, nv)):
+        rccsd.contract_DTSpT(Wd[a0:a1], T, outd[:, :, a0:a1, :], "2323")
+    assert _close(outd.cpu().numpy(), want)
+    outT = torch.zeros(no, no, nv, nv, dtype=torch.float64, device="cuda").permute(1, 0, 3, 2)
+    rccsd.contract_DTSpT(Wd, T, outT, "2323")
+    assert _close(outT.cpu().numpy(), want)
+
+
+@pytest.mark.parametrize("planes", [6, 7])
+def test_heavy_tailed_operand(tc, port, planes):
+    """One power-of-two scale per column means an element 10^-6 of its column's largest keeps 48 - 20 = 28 significant
+    bits at 6 planes.  What the contract (P6) bounds is the OUTPUT: the dropped tail is <= 2^-48 of the column maximum per
+    term, i.e. <= nnz_row * 2^-48 * max|W_col| * c absolute -- checked against sum |T||W| as well as against 1e-10."""
+    rccsd = tc
+    rccsd.set_option("tc_planes", planes)
+    rng = np.random.default_rng(31)
+    no, nv = 8, 24
+    T, flat, vals, dims = _fri(rccsd, rng, no, nv, 9000)
+    W = (rng.random((nv, nv, nv, nv)) - 0.5) * 10.0 ** (-6.0 * rng.random((nv, nv, nv, nv)))
+    want = np.zeros(dims)
+    port.contract("2323", W, flat, vals, dims, want)
+    scale = np.zeros(dims)
+    port.contract("2323", np.abs(W), flat, np.abs(vals), dims, scale)
+    got = np.zeros(dims)
+    rccsd.contract_DTSpT(W, T, got, "2323")
+    err = np.abs(got - want)
+    assert err.max() <= TOL * np.abs(want).max()
+    assert (err <= 2.0 ** (-8 * planes + 12) * np.maximum(scale, scale.max() * 1e-3)).all()
+
+
+def _planes(L, check, W, term, l0, lc, S):
+    import torch
+
+    h = ctypes.c_void_p()
+    i64 = lambda v: (ctypes.c_int64 * 4)(*[int(x) for x in v])
+    check(L.fricc_wslices_create_view(ctypes.c_void_p(W.data_ptr()), i64(W.shape), i64(W.stride()), term.encode(), l0, lc, S,
+                                      ctypes.byref(h)))
+    nK = W.shape[2] * W.shape[3]
+    rec = torch.empty(nK, lc, dtype=torch.float64, device="cuda")
+    check(L.fricc_wslices_reconstruct(h, ctypes.c_void_p(rec.data_ptr())))
+    check(L.fricc_wslices_destroy(h))
+    return rec
+
+
+@pytest.mark.parametrize("shape,l0,lc", [((2, 40, 64, 64), 3, 70),        # 4096-long runs: one CTA per column
+                                         ((2, 24, 250, 240), 0, 48),      # 60 000-long runs: clusters of 4
+                                         ((1, 9, 370, 372), 2, 7)])       # 137 640-long runs: clusters of 8, ragged tail
+def test_single_read_plane_builder_equals_the_two_pass_builder(rccsd, shape, l0, lc):
+    """The ladder's native W[a,b,c,d] through the cluster kernel (each column held once in distributed shared memory)
+    gives the same planes as colmax + slice, and both reconstruct W to 2^-48 of each column's largest element."""
+    import torch
+
+    from fricc_b200 import _lib
+
+    L = _lib.lib()
+    g = torch.Generator(device="cuda").manual_seed(shape[2])
+    W = (torch.rand(shape, generator=g, device="cuda", dtype=torch.float64) - 0.5)
+    W *= torch.pow(10.0, -4.0 * torch.rand(shape[0], shape[1], 1, 1, generator=g, device="cuda", dtype=torch.float64))
+    W[0, 1] = 0.0
+    try:
+        rccsd.set_option("tc_fused_planes", 1)
+        fused = _planes(L, _lib.check, W, "2323", l0, lc, 6)
+        rccsd.set_option("tc_fused_planes", 0)
+        twop = _planes(L, _lib.check, W, "2323", l0, lc, 6)
+    finally:
+        rccsd.set_option("tc_fused_planes", 1)
+    assert torch.equal(fused, twop)
+    ref = W.reshape(shape[0] * shape[1], -1)[l0:l0 + lc].t()
+    colmax = ref.abs().max(dim=0).values
+    assert ((fused - ref).abs() <= colmax[None, :] * 2.0 ** -47 + 1e-300).all()
+
+
+def test_plane_cache_follows_the_operand(tc, port):
+    """"tc_plane_cache" 1: same device operand twice -> built once; rewritten in place -> rebuilt (fingerprint)."""
+    import torch
+
+    rccsd = tc
+    rccsd.set_option("tc_plane_cache", 1)
+    rng = np.random.default_rng(41)
+    no, nv = 5, 12
+    T, flat, vals, dims = _fri(rccsd, rng, no, nv, 800)
+    Wd = torch.from_numpy(rng.random((nv, nv, nv, nv))).cuda()
+    for round_ in range(2):
+        want = np.zeros(dims)
+        port.contract("2323", Wd.cpu().numpy(), flat, vals, dims, want)
+        for _ in range(2):
+            out = torch.zeros(dims, dtype=torch.float64, device="cuda")
+            rccsd.contract_DTSpT(Wd, T, out, "2323")
+            assert _close(out.cpu().numpy(), want)
+        Wd.mul_(-1.5).add_(0.1)      # same address, new values
+    from fricc_b200 import _lib
+
+    _lib.check(_lib.lib().fricc_plane_cache_clear())

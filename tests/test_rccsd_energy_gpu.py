@@ -4,9 +4,16 @@ with fricc_b200.py_rccsd as the native module against the same run with the refe
 update_amps, fricc/friccsd.py:41-297).  Tolerance: 1e-8 (the north-star figure, in the units of the synthetic
 Hamiltonian) on every iteration.  PySCF molecules: unavailable in this image (no PySCF).
 
-STATUS: written after the round's GPU budget was spent -- every primitive it calls is covered by the other GPU tests
-(bit-exact compression for equal draws, contractions within 1e-10, glibc rand() stream), but this composition has not
-had its first hardware run; until it has, a failure here is reported as xfail instead of stopping the suite."""
+What "equal m and seed" can promise, measured (round 1: 8 of 9 cases within 1e-8, one pivotal case not; the advisor's
+CPU experiment: a 1-ulp jitter of the contraction outputs moves that case by 3e-4):
+  * systematic sampler: one draw per compression, decisions robust against last-bit differences of the residual --
+    the DEFAULT kernels (FMA, (R,K)-ordered sums, within 1e-10 per contraction) give energies within 1e-8;
+  * pivotal sampler: its last window is rounding-sensitive (src/fri_utils.cpp:81-109: whether the probabilities add up
+    to >= n' decides between the crossing branch and the tail rule), so ONE sample can differ for residuals that agree
+    to 1e-16, and at N = 1600, m = 160 one sample is 3e-4 of the energy.  Equal energies then need equal BITS: the
+    parity mode (option "spmm_exact_order": the reference's own summation order and roundings, bit-identical
+    contractions) on top of the bit-exact compression.  Every pivotal case below runs in that mode and must then
+    agree to the last bit, not just to 1e-8."""
 import ctypes
 
 import numpy as np
@@ -14,8 +21,7 @@ import pytest
 
 import rccsd_driver as D
 
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.xfail(strict=False, reason="first hardware run pending (added after the GPU budget was spent)")]
+pytestmark = pytest.mark.gpu
 
 
 class _RefBackend:
@@ -42,21 +48,50 @@ def _eris(seed, norb, nocc):
     return D.Eris(h, g, c, nocc)
 
 
-@pytest.mark.parametrize("sampling", ["systematic", "pivotal"])
+@pytest.mark.parametrize("sampling,mode", [("systematic", "fast"), ("systematic", "exact"), ("pivotal", "exact")])
 @pytest.mark.parametrize("compressed", [("O^2V^4",), D.ALL_COMPRESSED])
 @pytest.mark.parametrize("seed,norb,nocc,frac", [(4, 9, 3, 0.25), (11, 14, 4, 0.1)])
-def test_energy_parity_at_equal_m_and_seed(rccsd, ref, sampling, compressed, seed, norb, nocc, frac):
+def test_energy_parity_at_equal_m_and_seed(rccsd, ref, sampling, mode, compressed, seed, norb, nocc, frac):
     er = _eris(seed, norb, nocc)
     m = max(1, int(frac * er.ovov.size))
     out = []
-    for B in (_RefBackend(ref), _OurBackend(rccsd)):
-        B.srand(4321)
-        es, t1, t2 = D.run(er, 5, B, m, compressed, "fri", sampling)
-        out.append((np.array(es), t1, t2))
+    ref.clear_draws()
+    rccsd.set_option("spmm_exact_order", 1 if mode == "exact" else 0)
+    try:
+        for B in (_RefBackend(ref), _OurBackend(rccsd)):
+            B.srand(4321)
+            es, t1, t2 = D.run(er, 5, B, m, compressed, "fri", sampling)
+            out.append((np.array(es), t1, t2))
+    finally:
+        rccsd.set_option("spmm_exact_order", 0)
     (e_ref, t1_ref, t2_ref), (e_our, t1_our, t2_our) = out
     assert np.isfinite(e_ref).all()
     assert np.abs(e_our - e_ref).max() <= 1e-8                      # P7: within 1e-8 at equal m and seed
     assert np.abs(t2_our - t2_ref).max() <= 1e-9 * max(1.0, np.abs(t2_ref).max())
+    if mode == "exact":                                             # parity mode: the same bits, iteration after iteration
+        assert np.array_equal(e_our, e_ref) and np.array_equal(t2_our, t2_ref) and np.array_equal(t1_our, t1_ref)
+
+
+def test_pivotal_energy_in_the_fast_mode_is_statistically_equivalent(rccsd, ref):
+    """The fast kernels do not promise the pivotal sampler's bits (module docstring).  What they do promise: every
+    iteration's compression is the reference's for the SAME input (stage-wise bit-exactness, tests/test_compress_gpu.py)
+    and every contraction is within 1e-10, so a fast-mode run is another draw of the same estimator.  Checked here as:
+    the fast-mode trajectory stays within the spread of reference trajectories started from different seeds."""
+    er = _eris(11, 14, 4)
+    m = max(1, int(0.1 * er.ovov.size))
+    ref.clear_draws()
+    finals = []
+    for seed in (1, 2, 3, 4, 5, 6):
+        B = _RefBackend(ref)
+        B.srand(seed)
+        es, _, _ = D.run(er, 5, B, m, ("O^2V^4",), "fri", "pivotal")
+        finals.append(es[-1])
+    B = _OurBackend(rccsd)
+    B.srand(4321)
+    es, _, _ = D.run(er, 5, B, m, ("O^2V^4",), "fri", "pivotal")
+    lo, hi = min(finals), max(finals)
+    spread = max(hi - lo, 1e-12)
+    assert np.isfinite(es).all() and lo - 2 * spread <= es[-1] <= hi + 2 * spread
 
 
 def test_largest_compression_energy_parity(rccsd, ref):
