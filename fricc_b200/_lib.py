@@ -98,6 +98,9 @@ SIGNATURES = {
     "fricc_symm_free": (c_int, [c_void_p]),
     "fricc_push_columns": (c_int, [c_void_p, POINTER(c_void_p), c_int, c_int, c_char_p, _i64p, _i64p, _i64p, c_int64,
                                    c_int64]),
+    "fricc_push_view": (c_int, [c_void_p, POINTER(c_void_p), c_int, c_int, _i64p, _i64p]),
+    "fricc_peer_barrier": (c_int, [POINTER(c_void_p), c_int, c_int, c_uint64]),
+    "fricc_fill_uniform": (c_int, [c_void_p, c_int64, c_uint64, c_uint64]),
     "fricc_scatter_panel": (c_int, [c_void_p, c_int64, c_int64, c_int64, c_char_p, _i64p, c_void_p, POINTER(c_void_p),
                                     c_int, c_int, _i64p, _i64p]),
     "fricc_permute_w": (c_int, [c_void_p, c_int, _i64p, _i64p, c_char_p, c_int64, c_int64, c_void_p]),

@@ -844,6 +844,7 @@ double dense_form(fricc_st* T, const TermSpec& ts, Layout& lay) {
 struct TcParams {
   int64_t nR, l_begin, l_count;
   int S, stages, nkb;
+  int b_group;  // planes fetched by one TMA box (a divisor of S; the box of tmB is b_group * 64 rows)
   int m_tiles, n_tiles;
   const double* colscale;  // [n_tiles*64]  2^(e_l - 7)
   const int32_t* rowsum;   // [Mpad]
@@ -894,20 +895,32 @@ tc_sign_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
   if (warp == 0) {
     // ===== TMA producer: runs ahead into the next tile while the epilogue drains the current one =====
+    // (ring position and phase are carried incrementally: the ncu source view of the first version showed the 64-bit
+    //  `gk % stages`, `gk / stages` of this loop and of the MMA loop -- ~100 dependent instructions per k-block on a
+    //  single warp -- setting a ~800-cycle floor per k-block under the 768 cycles of tensor work)
     if (lane == 0) {
-      int64_t gk = 0;
+      int st = 0;
+      uint32_t ph = 0;      // parity of the "empty" phase to wait for once the ring has wrapped
+      bool wrapped = false;
+      const int bg = p.b_group, nb = S / p.b_group;           // planes per TMA box, boxes per stage
+      const uint32_t box_bytes = (uint32_t)bg * TC_B_PLANE_BYTES;
       for (int64_t t = blockIdx.x; t < total_tiles; t += gridDim.x) {
         const int m_tile = (int)(t % p.m_tiles), n_tile = (int)(t / p.m_tiles);
-        for (int kb = 0; kb < p.nkb; kb++, gk++) {
-          const int st = (int)(gk % stages);
-          const int64_t it = gk / stages;
-          if (it > 0) ptx::mbar_wait(&empty[st], (uint32_t)((it - 1) & 1));
+        const int32_t a_row = m_tile * TC_BM, b_row = n_tile * S * TC_BN;
+        int32_t kcol = 0;
+        for (int kb = 0; kb < p.nkb; kb++, kcol += TC_BK) {
+          if (wrapped) ptx::mbar_wait(&empty[st], ph);
           uint8_t* a_dst = smem + (size_t)st * stage_bytes;
           uint8_t* b_dst = a_dst + TC_A_BYTES;
           ptx::mbar_expect_tx(&full[st], stage_bytes);
-          ptx::tma_load_2d(a_dst, &tmA, &full[st], kb * TC_BK, m_tile * TC_BM);
-          for (int s = 0; s < S; s++)
-            ptx::tma_load_2d(b_dst + (size_t)s * TC_B_PLANE_BYTES, &tmB, &full[st], kb * TC_BK, (n_tile * S + s) * TC_BN);
+          ptx::tma_load_2d(a_dst, &tmA, &full[st], kcol, a_row);
+          for (int g = 0; g < nb; g++)
+            ptx::tma_load_2d(b_dst + (size_t)g * box_bytes, &tmB, &full[st], kcol, b_row + g * bg * TC_BN);
+          if (++st == stages) {
+            st = 0;
+            if (wrapped) ph ^= 1;
+            wrapped = true;
+          }
         }
       }
     }
@@ -917,29 +930,36 @@ tc_sign_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     if (lane == 0) {
       const int n1 = min(S, 4) * TC_BN, n2 = (S - min(S, 4)) * TC_BN;  // planes 0..3 | planes 4..S-1
       const uint32_t idesc1 = umma_idesc_i8(TC_BM, n1), idesc2 = umma_idesc_i8(TC_BM, n2 > 0 ? n2 : 16);
-      int64_t gk = 0;
+      // descriptors differ only in their 14-bit start-address field (units of 16 bytes): advance by plain additions
+      const uint64_t desc0 = umma_desc_sw128(ptx::smem_u32(smem));
+      const uint64_t stage_step = stage_bytes >> 4, b_off = TC_A_BYTES >> 4, b2_off = (TC_A_BYTES + 4 * TC_B_PLANE_BYTES) >> 4;
+      int st = 0;
+      uint32_t ph = 0;
+      uint64_t adesc0 = desc0;
       uint32_t tl = 0;
       for (int64_t t = blockIdx.x; t < total_tiles; t += gridDim.x, tl++) {
         if (tl > 0) {  // the epilogue must have read the previous tile's accumulators out of TMEM
           ptx::mbar_wait(tmem_empty, (tl - 1) & 1);
           ptx::tc_fence_after();
         }
-        for (int kb = 0; kb < p.nkb; kb++, gk++) {
-          const int st = (int)(gk % stages);
-          const int64_t it = gk / stages;
-          ptx::mbar_wait(&full[st], (uint32_t)(it & 1));
+        uint32_t acc = 0;
+        for (int kb = 0; kb < p.nkb; kb++) {
+          ptx::mbar_wait(&full[st], ph);
           ptx::tc_fence_after();
-          const uint32_t a_addr = ptx::smem_u32(smem + (size_t)st * stage_bytes);
-          const uint32_t b_addr = a_addr + TC_A_BYTES;
 #pragma unroll
           for (int k = 0; k < TC_BK / TC_UMMA_K; k++) {
-            const uint32_t acc = (kb | k) != 0 ? 1u : 0u;
-            const uint64_t adesc = umma_desc_sw128(a_addr + k * TC_UMMA_K);
-            ptx::mma_i8(tmem_base, adesc, umma_desc_sw128(b_addr + k * TC_UMMA_K), idesc1, acc);
-            if (n2 > 0)
-              ptx::mma_i8(tmem_base + 256, adesc, umma_desc_sw128(b_addr + 4 * TC_B_PLANE_BYTES + k * TC_UMMA_K), idesc2, acc);
+            const uint64_t adesc = adesc0 + (uint64_t)(k * (TC_UMMA_K >> 4));
+            ptx::mma_i8(tmem_base, adesc, adesc + b_off, idesc1, acc);
+            if (n2 > 0) ptx::mma_i8(tmem_base + 256, adesc, adesc + b2_off, idesc2, acc);
+            acc = 1;
           }
           ptx::mma_commit(&empty[st]);  // the stage may be refilled once these MMAs have read it
+          adesc0 += stage_step;
+          if (++st == stages) {
+            st = 0;
+            ph ^= 1;
+            adesc0 = desc0;
+          }
         }
         ptx::mma_commit(tmem_full);
       }
@@ -1153,8 +1173,10 @@ void contract_dense(fricc_st* T, const TermSpec& ts, Layout& lay, const WSlices&
       attr_smem = 227 * 1024;
     }
     const CUtensorMap tmA = make_map_i8(lay.dense.p, lay.Mpad, lay.Kpad, TC_BM);
-    const CUtensorMap tmB = make_map_i8(ws.q.p, ws.n_tiles * S * TC_BN, ws.Kpad, TC_BN);
+    const int b_group = S % 4 == 0 ? 4 : (S % 3 == 0 ? 3 : (S % 2 == 0 ? 2 : 1));  // box rows <= 256
+    const CUtensorMap tmB = make_map_i8(ws.q.p, ws.n_tiles * S * TC_BN, ws.Kpad, b_group * TC_BN);
     TcParams p;
+    p.b_group = b_group;
     p.nR = lay.nR; p.l_begin = l_begin; p.l_count = ws.l_count;
     p.S = S; p.stages = stages; p.nkb = (int)(lay.Kpad / TC_BK);
     p.colscale = ws.colscale.p; p.rowsum = lay.rowsum.p; p.cmag = lay.cmag.p; p.scale = scale; p.out = out; p.om = om; p.beta = overwrite ? 0 : 1;

@@ -8,6 +8,8 @@
 // one symmetric allocation per rank (cudaMalloc + CUDA IPC), so "the same element on peer p" is base_p + offset.
 // A column is written by its owner only, so no two ranks ever store to the same address; consumers are ordered behind
 // the writers by a stream-ordered barrier (fricc_b200/dist.py).
+#include <algorithm>
+
 #include "fricc_contract.cuh"
 
 namespace fricc {
@@ -84,6 +86,112 @@ void push_columns(const double* out_local, double* const* peer_out, int n_peers,
     prefer_split(push_columns_kernel<1>);
     FRICC_LAUNCH(push_columns_kernel<1>, push_grid(nvb), 256, 0, out_local, pp, n_peers, self, om, nR, l_begin, l_count,
                  nbx, nvb);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// a 4-D strided VIEW of this rank's copy -> the same view in every peer's copy
+// ---------------------------------------------------------------------------------------------------------------
+// The sharded engine (fricc_b200/engine.py) hands the plugin call an L-slice of the output -- a 4-D view with the
+// output's own strides -- and then publishes exactly that view.  Axes are walked in order of ascending stride, the
+// smallest-stride axis along the threads, so the loads and the peer stores are as contiguous as the view allows.
+struct View4 {
+  int64_t n[4];  // extents, n[0] along the smallest stride
+  int64_t s[4];  // element strides, ascending
+};
+
+__global__ void __launch_bounds__(256)
+push_view_kernel(const double* __restrict__ src, PeerPtrs peers, int n_peers, int self, View4 v, int64_t nbx, int64_t nvb) {
+  for (int64_t vb = blockIdx.x; vb < nvb; vb += gridDim.x) {
+    const int64_t by = vb / nbx, bx = vb - by * nbx;
+    const int64_t i0 = bx * 256 + threadIdx.x;
+    if (i0 >= v.n[0]) continue;
+    int64_t r = by;
+    const int64_t i1 = r % v.n[1]; r /= v.n[1];
+    const int64_t i2 = r % v.n[2]; r /= v.n[2];
+    const int64_t o = i0 * v.s[0] + i1 * v.s[1] + i2 * v.s[2] + r * v.s[3];
+    const double x = src[o];
+    for (int d = 1; d < n_peers; d++) {
+      int q = self + d;
+      if (q >= n_peers) q -= n_peers;
+      peers.p[q][o] = x;
+    }
+  }
+}
+
+void push_view(const double* local, double* const* peer, int n_peers, int self, const int64_t shape[4],
+               const int64_t strides[4]) {
+  if (n_peers <= 1) return;
+  if (n_peers > MAX_PEERS) fail(FRICC_EINVAL, "at most %d peers", MAX_PEERS);
+  int order[4] = {0, 1, 2, 3};
+  for (int i = 0; i < 4; i++)  // extent-1 axes last, the rest by ascending stride
+    for (int j = i + 1; j < 4; j++) {
+      const bool ui = shape[order[i]] == 1, uj = shape[order[j]] == 1;
+      if ((ui && !uj) || (ui == uj && strides[order[j]] < strides[order[i]])) std::swap(order[i], order[j]);
+    }
+  View4 v;
+  int64_t total = 1;
+  for (int i = 0; i < 4; i++) {
+    v.n[i] = shape[order[i]];
+    v.s[i] = strides[order[i]];
+    if (v.s[i] < 0) fail(FRICC_EINVAL, "negative strides are not supported");
+    total *= v.n[i];
+  }
+  if (total == 0) return;
+  // merge the two smallest axes when they are contiguous with each other (longer runs per warp)
+  if (v.s[1] == v.n[0] * v.s[0]) {
+    v.n[0] *= v.n[1];
+    v.n[1] = v.n[2]; v.s[1] = v.s[2];
+    v.n[2] = v.n[3]; v.s[2] = v.s[3];
+    v.n[3] = 1; v.s[3] = 0;
+  }
+  PeerPtrs pp;
+  for (int q = 0; q < MAX_PEERS; q++) pp.p[q] = q < n_peers ? peer[q] : nullptr;
+  const int64_t nbx = ceil_div(v.n[0], 256), nvb = nbx * v.n[1] * v.n[2] * v.n[3];
+  prefer_split(push_view_kernel);
+  FRICC_LAUNCH(push_view_kernel, push_grid(nvb), 256, 0, local, pp, n_peers, self, v, nbx, nvb);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// stream-ordered barrier across the ranks of one node, through the symmetric allocation (no NCCL launch)
+// ---------------------------------------------------------------------------------------------------------------
+// flags_q = MAX_PEERS 64-bit epoch counters in rank q's arena.  Barrier number e: rank r stores e into flags_q[r] of every
+// peer q (release, system scope: everything this rank's earlier kernels stored into q's memory is ordered before it),
+// then waits until its own flags[q] >= e for every q (acquire).  The kernel sits on the rank's stream, so work queued
+// behind it starts only when every rank has reached the barrier; the host never blocks.  Each rank spins on ITS OWN GPU.
+__global__ void peer_barrier_kernel(PeerPtrs flags, int n_peers, int self, unsigned long long epoch) {
+  const int q = threadIdx.x;
+  if (q >= n_peers) return;
+  unsigned long long* mine = reinterpret_cast<unsigned long long*>(flags.p[self]);
+  if (q != self) {
+    unsigned long long* theirs = reinterpret_cast<unsigned long long*>(flags.p[q]) + self;
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(theirs), "l"(epoch) : "memory");
+    const long long t0 = clock64();
+    unsigned long long seen = 0;
+    do {
+      asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(seen) : "l"(mine + q) : "memory");
+      if (seen < epoch && clock64() - t0 > 40000000000LL) __trap();  // ~20 s: a rank is gone
+    } while (seen < epoch);
+  }
+}
+
+void peer_barrier(double* const* flags_peer, int n_peers, int self, unsigned long long epoch) {
+  if (n_peers <= 1) return;
+  if (n_peers > MAX_PEERS) fail(FRICC_EINVAL, "at most %d peers", MAX_PEERS);
+  PeerPtrs pp;
+  for (int q = 0; q < MAX_PEERS; q++) pp.p[q] = q < n_peers ? flags_peer[q] : nullptr;
+  FRICC_LAUNCH(peer_barrier_kernel, 1, 32, 0, pp, n_peers, self, epoch);
+}
+
+// counter-based uniform fill: dst[i] = U(0,1) of (seed, first_index + i) -- a synthetic operand whose values depend on
+// the GLOBAL element index only, so that any sharding or sub-sharding of it holds the same numbers (bench.py)
+__global__ void fill_uniform_kernel(double* __restrict__ dst, int64_t n, unsigned long long first, unsigned long long seed) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    unsigned long long z = (first + (unsigned long long)i) * 0x9E3779B97F4A7C15ULL + seed;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+    z ^= z >> 31;
+    dst[i] = (double)(z >> 11) * 1.1102230246251565e-16;  // 2^-53
   }
 }
 
@@ -267,6 +375,36 @@ int fricc_push_columns(const double* out_local_dev, void* const* peer_out_dev, i
   if (n_peers > MAX_PEERS) fail(FRICC_EINVAL, "at most %d peers", MAX_PEERS);
   for (int q = 0; q < n_peers; q++) peers[q] = static_cast<double*>(peer_out_dev[q]);
   push_columns(out_local_dev, peers, n_peers, self, om, nR, l_begin, l_count);
+  FRICC_API_END
+}
+
+int fricc_push_view(const double* view_local_dev, void* const* view_peer_dev, int n_peers, int self,
+                    const int64_t shape[4], const int64_t strides[4]) {
+  FRICC_API_BEGIN
+  if (!view_local_dev || !view_peer_dev || !shape || !strides || n_peers < 1 || self < 0 || self >= n_peers)
+    fail(FRICC_EINVAL, "bad arguments");
+  double* peers[MAX_PEERS];
+  if (n_peers > MAX_PEERS) fail(FRICC_EINVAL, "at most %d peers", MAX_PEERS);
+  for (int q = 0; q < n_peers; q++) peers[q] = static_cast<double*>(view_peer_dev[q]);
+  push_view(view_local_dev, peers, n_peers, self, shape, strides);
+  FRICC_API_END
+}
+
+int fricc_peer_barrier(void* const* flags_peer_dev, int n_peers, int self, uint64_t epoch) {
+  FRICC_API_BEGIN
+  if (!flags_peer_dev || n_peers < 1 || self < 0 || self >= n_peers || n_peers > MAX_PEERS) fail(FRICC_EINVAL, "bad arguments");
+  double* peers[MAX_PEERS];
+  for (int q = 0; q < n_peers; q++) peers[q] = static_cast<double*>(flags_peer_dev[q]);
+  peer_barrier(peers, n_peers, self, (unsigned long long)epoch);
+  FRICC_API_END
+}
+
+int fricc_fill_uniform(double* dst_dev, int64_t n, uint64_t first_index, uint64_t seed) {
+  FRICC_API_BEGIN
+  if (n < 0 || (n > 0 && !dst_dev)) fail(FRICC_EINVAL, "bad arguments");
+  if (n > 0)
+    FRICC_LAUNCH(fill_uniform_kernel, (unsigned)std::min<int64_t>(ceil_div(n, 256), (int64_t)num_sms() * 16), 256, 0, dst_dev, n,
+                 (unsigned long long)first_index, (unsigned long long)seed);
   FRICC_API_END
 }
 

@@ -399,6 +399,7 @@ class SymmArena:
         self._used = 0
 
     def tensor(self, shape, dtype=torch.float64):
+        """A tensor carved from the arena (uninitialised)."""
         n = 1
         for s in shape:
             n *= int(s)
@@ -461,3 +462,90 @@ class SideStream:
 
 # range-sharded compression (x split by contiguous flat-index ranges; all-reduced key histograms): fricc_b200/ranges.py
 from .ranges import compress_ranges, compress_ranges_pair, index_range  # noqa: E402,F401
+
+
+# ======================================================================================================================
+# the sharded step on top of the PLUGIN CALL: every rank hands `py_rccsd.contract_DTSpT` its L-slice of the operand and
+# of the output as plain 4-D views -- the call the reference's drivers make (src/py_rccsd.cpp:50-51) -- and the library
+# picks the kernel (tensor cores for FRI-compressed tensors, planes built straight from the view).  No panels, no
+# term-specific entry points: what a single-GPU user of the module runs is exactly what each rank runs here.
+# ======================================================================================================================
+class ViewEngine:
+    """Views + plugin calls + peer stores.  One instance per rank.
+
+    slice_axis(term): which of the two free-pair axes is cut across the ranks (the longer one; ties: the major one).
+    contract(term, W, T, out, w_range=None): this rank's slice of `term`.  `W` is the FULL operand (replicated small
+        tensors: ovov, Woooo, Wvoov, Wvovo) unless w_range = (lo, hi) says that `W` already IS the slice [lo, hi) of the
+        cut axis (the ladder's vvvv operand, of which a rank only ever holds its part, possibly in sub-shards).
+    publish(term, out, w_range=None): stores the slice of `out` this rank owns into every peer's copy (SymmArena).
+    barrier(): stream-ordered barrier of the ranks through the arena (fricc_peer_barrier), NCCL-free."""
+
+    def __init__(self, comm, device, arena=None, side=None):
+        from . import py_rccsd
+
+        self.comm, self.device, self.arena, self.side = comm, device, arena, side
+        self.py = py_rccsd
+        self.L = _lib.lib()
+        self._epoch = 0
+        self._flags = None
+        if arena is not None and comm.world > 1:
+            self._flags = arena.tensor((16,), dtype=torch.int64).zero_()
+            self._flag_peers = arena.peers_of(self._flags)
+            torch.cuda.synchronize()
+            comm.barrier()          # every rank's counters are zero before anyone stores an epoch
+
+    @staticmethod
+    def slice_axis(term, w_shape):
+        ax = TERM_AXES[term]
+        e0, e1 = w_shape[ax["wL"][0]], w_shape[ax["wL"][1]]
+        return 0 if e0 >= e1 else 1
+
+    def my_range(self, extent):
+        lo, cnt, _ = column_range(extent, self.comm.rank, self.comm.world)
+        return lo, lo + cnt
+
+    def out_view(self, term, out, j, lo, hi):
+        return out.narrow(TERM_AXES[term]["oL"][j], lo, hi - lo)
+
+    def contract(self, term, W, T, out, w_range=None):
+        ax = TERM_AXES[term]
+        if w_range is None:
+            j = self.slice_axis(term, W.shape)
+            lo, hi = self.my_range(W.shape[ax["wL"][j]])
+            if hi <= lo:
+                return None
+            Wv = W.narrow(ax["wL"][j], lo, hi - lo)
+        else:
+            j, (lo, hi), Wv = 0, w_range, W
+            if hi <= lo:
+                return None
+        ov = self.out_view(term, out, j, lo, hi)
+        self.py.contract_DTSpT(Wv, T, ov, term)
+        return ov
+
+    def publish(self, view):
+        """Store a 4-D view of an arena tensor into the same view of every peer's copy (on the side stream if any)."""
+        if view is None or self.arena is None or self.comm.world == 1:
+            return
+        peers = self.arena.peers_of(view)
+
+        def push():
+            check(self.L.fricc_push_view(_ptr(view), peers, self.comm.world, self.comm.rank, i64x4(view.shape),
+                                         i64x4(view.stride())))
+        self.side.run(push) if self.side is not None else push()
+
+    def join(self):
+        if self.side is not None:
+            self.side.join()
+
+    def barrier(self):
+        if self.comm.world == 1:
+            return
+        self.join()
+        if self._flags is None:
+            import torch.distributed as dist
+
+            dist.barrier(group=self.comm.group)
+            return
+        self._epoch += 1
+        check(self.L.fricc_peer_barrier(self._flag_peers, self.comm.world, self.comm.rank, self._epoch))

@@ -171,6 +171,21 @@ int fricc_symm_free(void* ptr);
 int fricc_push_columns(const double* out_local_dev, void* const* peer_out_dev, int n_peers, int self, const char* term,
                        const int64_t t_dims[4], const int64_t out_shape[4], const int64_t out_strides[4],
                        int64_t l_begin, int64_t l_count);
+/* the same exchange for a 4-D strided VIEW (shape, element strides) of this rank's copy of an output -- the L-slice the
+ * sharded engine handed to fricc_contract: every element of the view is stored at the same offset of
+ * view_peer_dev[q] (q != self), the address of the same view in peer q's copy.                                          */
+int fricc_push_view(const double* view_local_dev, void* const* view_peer_dev, int n_peers, int self,
+                    const int64_t shape[4], const int64_t strides[4]);
+/* Stream-ordered barrier of the ranks of one node without an NCCL launch: flags_peer_dev[q] = address, in rank q's
+ * symmetric allocation, of 16 zero-initialised 64-bit counters (the same offset on every rank).  Barrier number `epoch`
+ * (1, 2, 3, ... -- the same sequence on every rank): one small kernel stores the epoch into every peer's counter for
+ * this rank (release: this rank's earlier peer stores are ordered before it) and waits for all peers' epochs in its own
+ * counters.  Work queued on the library stream behind the call starts when every rank has reached it.  One process per
+ * GPU only: two ranks spinning on ONE device can starve each other.                                                   */
+int fricc_peer_barrier(void* const* flags_peer_dev, int n_peers, int self, uint64_t epoch);
+/* synthetic operand for benchmarks: dst[i] = U(0,1) as a function of (seed, first_index + i) only (counter-based), so
+ * any sharding of a tensor filled this way holds the same numbers                                                    */
+int fricc_fill_uniform(double* dst_dev, int64_t n, uint64_t first_index, uint64_t seed);
 /* out_local[.., l, ..] += panel[R][l - l_begin] for this rank's columns (a [nR][ld] panel written by
  * fricc_contract_panel[_tc]); the sums are also stored into every peer's copy when peer_out_dev != NULL.  Transposes
  * through shared memory when out's unit-stride axis is the R-major or L-major index (terms 1302/1202/1303/1203).       */
