@@ -1,31 +1,47 @@
 #!/usr/bin/env python
 """bench.py -- one FRI-CCSD inner-loop iteration (the hot path of jamesETsmith/fri-cc) on synthetic tensors.
 
-Metric (BASELINE.json): FRI-CCSD s/iter at o=40, v=400, m=1e7 on 1/2/4/8 GPUs; ladder HBM GB/s vs peak.
+Metric (BASELINE.json): FRI-CCSD s/iter at o=40, v=400, m=1e7 on 1/2/4/8 GPUs; ladder roofline.
 
-A "step" is one pass of the hot path exactly as fricc/friccsd.py:update_amps drives it with all three contraction
-classes compressed: 2 FRI compressions of T2 (N = o^2 v^2 entries -> m) and the 11 sparse contractions
+A "step" is one pass of the hot path as fricc/friccsd.py:update_amps drives it with all three contraction classes
+compressed: 2 FRI compressions of T2 (N = o^2 v^2 entries -> m) and the 11 sparse contractions
   1323 (ovov -> Woooo), 0112 0313 0113 (ovov -> Wvoov), 0312 (ovov -> Wvovo),
   0101 (Woooo), 2323 (Wvvvv: the particle-particle ladder), 1302 1303 (Wvoov), 1202 1203 (Wvovo)   -> t2new / tmp.
-Multi-GPU: every contraction is sharded along its free index pair (column slices of the [K][L] panel of W); each rank
-accumulates its columns into its own copy of the 4-D output and stores them into every peer's copy over NVLink
-(symmetric allocation, stores issued on a side stream under the next term's kernel; `--exchange nccl` = all-gather of
-panels instead), so every rank holds the full result; strong scaling (fixed problem).  The step's two compressions come
-from one range-sharded pass (every rank scans its contiguous 1/N of T2; `--compress`).  For FRI-compressed tensors the
-contractions run in their tensor-core form (`--planes`, fricc_dense.cu; `--planes 0` = fp64 SpMM).
+
+Operand upkeep -- `--w-mode` (both values are in the line, `value` is the one selected):
+  refreshed (default) the FRICCSD regime: Wvvvv = cc_Wvvvv(t1, t2, eris) is rebuilt EVERY iteration
+            (fricc/friccsd.py:207,227,325-331), so the re-encoding of the ladder operand into int8 digit planes is part
+            of every step and is timed.  The operand is read in its native W[a,b,c,d] layout (no [cd][ab] copy exists
+            on this path any more).  Producing W itself is the caller's dense work and is untimed.
+  invariant the FRILCCSD regime: W is the bare integral block, the same every iteration (fricc/frilccsd.py:171-179);
+            planes are built once, outside the timed region.
+  The small operands (ovov; Woooo / Wvoov / Wvovo, which are outputs of this very step) are re-encoded inside the step
+  in both modes.
+
+Sharding (N > 1, strong scaling): every contraction is cut along its free index pair; a rank hands the plugin call
+`py_rccsd.contract_DTSpT` (= fricc_contract) its slice of the operand and of the output as plain 4-D views
+(fricc_b200/dist.py: ViewEngine) -- the library picks the kernel -- and stores the finished slice into every peer's copy
+over NVLink (symmetric allocation, stores on a side stream under the next term's kernel, three device-side barriers
+per step, no NCCL on the data path).  The step's two compressions come from one range-sharded pass.
 
 Timing: W >= 3 untimed warm-up steps, then K steps; barrier + torch.cuda.synchronize on both sides; CUDA events on the
-launching stream; max over ranks.  Inputs are far larger than L2 (the ladder streams >= 25 GB of W per GPU per step).
-When the ladder's W slice does not fit in HBM (1 GPU: 204.8 GB > 180 GB) it is processed in column sub-shards that are
-re-generated in HBM between timed segments (inputs resident when each timed segment starts); the step time is then
-the sum of the timed segments.  `e2e` repeats the measurement with T2 arriving from pinned host memory and the
-residual going back to pinned host memory inside the timed region (W stays resident: it is 204.8 GB, more than the
-host has, and is iteration-invariant in the linearised driver, fricc/frilccsd.py:171-174).
+launching stream; max over ranks.  Inputs are far larger than L2 (>= 25 GB of W per GPU per step).  When the ladder's W
+slice does not fit in HBM next to its planes (1 GPU: 204.8 GB; 2 GPUs: 102.4 GB + 76.8 GB of planes) it is processed in
+sub-shards that are re-generated in HBM between timed segments; the step time is the sum of the timed segments.
 
-`--impl reference` times the reference's own CPU implementation (oracle/_ref, the unmodified sources compiled by
-oracle/Makefile) on a bounded sample of the same workload and extrapolates by operation count.
+`e2e`: the same step through the plugin calls with T2 arriving from pinned host memory and the residual returning to
+it inside the timed region.  1 GPU: `SparseTensor4d(t2_host, ...)` twice and `contract_DTSpT` eleven times, exactly
+the calls fricc/friccsd.py makes (W and the intermediates are device tensors: Wvvvv is 204.8 GB, more than the host
+has).  N > 1: every rank uploads its 1/N of T2, the range-sharded compression needs nothing else, the contractions are
+the same plugin calls on views, every rank returns its 1/N of the residual.
+
+`--impl reference`: the reference's own CPU implementation (oracle/_ref, the unmodified sources compiled by
+oracle/Makefile) on the box's host cores: the full workload when it fits the host (e.g. --o 21 --v 93 --m 1e6),
+otherwise a set of sample points and a per-term fit  t = alpha * (FMA count) + beta * (index tests)  extrapolated to
+(o, v, m), with the measured points and the fit residuals in the line.
 """
 import argparse
+import ctypes
 import json
 import math
 import os
@@ -38,10 +54,15 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-METRIC = "FRI-CCSD s/iter at o=40,v=400,m=1e7"
 UNIT = "s/iter"
-
 CONTRACTION_ORDER = ["1323", "0112", "0313", "0113", "0312", "0101", "2323", "1302", "1202", "1303", "1203"]
+# checksum of t2new after one step of the default workload (o=40, v=400, m=1e7, systematic, seed 20): the same on
+# every rank and for every GPU count (each output element is computed by one rank in a fixed order)
+EXPECTED_T2NEW_CHECKSUM = None
+
+
+def metric_name(o, v, m):
+    return f"FRI-CCSD s/iter at o={o},v={v},m={m:.0e}".replace("e+0", "e").replace("e+", "e")
 
 
 def parse_args():
@@ -54,31 +75,22 @@ def parse_args():
     p.add_argument("--v", "--nvir", dest="v", type=int, default=400)
     p.add_argument("--m", "--nkeep", dest="m", type=float, default=1e7)
     p.add_argument("--sampling", default="systematic", choices=["systematic", "pivotal"])
-    p.add_argument("--max-panel-gb", type=float, default=26.0, help="largest resident ladder W slice per sub-shard")
+    p.add_argument("--w-mode", default="refreshed", choices=["refreshed", "invariant"],
+                   help="refreshed: the ladder operand is re-encoded inside every step (FRICCSD rebuilds Wvvvv each "
+                        "iteration); invariant: planes built once (FRILCCSD)")
+    p.add_argument("--max-slice-gb", type=float, default=26.0, help="largest resident ladder W sub-shard (fp64 GB)")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
-    p.add_argument("--only-ladder", action="store_true", help="debug: time only the ladder launches")
+    p.add_argument("--no-sweep", action="store_true", help="skip the compression-only sweep (config 5)")
     p.add_argument("--planes", type=int, default=6,
                    help="int8 digit planes of W for the tensor-core form of the contractions (0 = fp64 SpMM only)")
-    p.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
-                   help="N>1: how column slices reach the other ranks: stores into peer memory over NVLink (default) or "
-                        "NCCL all-gather of panels + accumulate")
-    p.add_argument("--compress", default="auto", choices=["auto", "ranges", "pair", "replicated"],
-                   help="how the two compressions of a step are computed: 'ranges' = every rank scans its contiguous 1/N "
-                        "of T2, all-reduced key histograms, norm / D / running sums shared by both draws (systematic "
-                        "sampler; default for it); 'pair' = whole compressions task-parallel on even/odd ranks; "
-                        "'replicated' = both on every rank")
     p.add_argument("--push-inline", action="store_true",
-                   help="N>1, peer exchange: issue the stores into the peers on the compute stream (A/B of the side-stream "
-                        "push that runs them under the next term's kernel)")
-    p.add_argument("--push-ctas", type=int, default=0, help="peer-store kernels: CTAs per SM (0 = library default)")
-    p.add_argument("--no-overlap", action="store_true", help="N>1: one blocking exchange per term (A/B of the pipelined step)")
+                   help="N>1: issue the peer stores on the compute stream (A/B of the side-stream push)")
+    p.add_argument("--nccl-barrier", action="store_true", help="N>1: 4-byte NCCL all-reduce barriers instead of the "
+                                                               "device-side flag barrier (A/B)")
     return p.parse_args()
 
 
-# ======================================================================================================================
-# reference arm / CPU baseline: the reference's own OpenMP implementation on the host cores
-# ======================================================================================================================
 def flops_model(o, v, m):
     """FMAs per term at (o, v, m)."""
     f = {"2323": m * v * v, "0101": m * o * o, "1323": m * o * o}
@@ -87,60 +99,168 @@ def flops_model(o, v, m):
     return f
 
 
-def cpu_reference_sample(o, v, m, sampling, threads):
-    """Time oracle/_ref (kind 'reference') -- or the C restatement (kind 'port') if the compiled reference is not
-    there -- on a bounded sample of the workload and extrapolate each part to (o, v, m) by its operation count."""
-    os.environ["OMP_NUM_THREADS"] = str(threads)
-    import numpy as np
+def scan_model(o, v, m):
+    """Index tests per term: every owner pair scans all m stored entries (src/sparse_tensor.cpp:62-68)."""
+    s = {"2323": o * o * m, "1323": o * o * m, "0101": v * v * m}
+    for t in ("1302", "1202", "1303", "1203", "0112", "0313", "0113", "0312"):
+        s[t] = o * v * m
+    return s
 
+
+def workload_config(args, world):
+    o, v, m = args.o, args.v, int(args.m)
+    regime = ("Wvvvv re-encoded every step (FRICCSD, fricc/friccsd.py:207,325-331)" if args.w_mode == "refreshed" else
+              "Wvvvv iteration-invariant, planes built once (FRILCCSD, fricc/frilccsd.py:171-179)")
+    return {
+        "workload": f"synthetic FRI-CCSD iteration o={o},v={v},m={m}: 2 FRI compressions ({args.sampling}) of T2 "
+                    f"(N={o*o*v*v}) + 11 sparse contractions; {regime}; vvvv operand sharded by (a,b) columns over "
+                    f"{world} GPU(s)",
+        "o": o, "v": v, "m": m, "sampling": args.sampling, "w_mode": args.w_mode,
+        "parallelism": f"free-pair column shards x{world}", "l2": "inputs_larger_than_L2",
+    }
+
+
+# ======================================================================================================================
+# reference arm / CPU baseline: the reference's own OpenMP implementation on the host cores
+# ======================================================================================================================
+def _ref_modules(threads):
+    os.environ["OMP_NUM_THREADS"] = str(threads)
     from oracle import oracle
 
     R = oracle.ref()
-    kind = "reference" if R is not None else "port"
-    P = oracle.port()
-    so, sv = min(o, 40), min(v, 100)
-    sN = so * so * sv * sv
-    sm_comp = max(1, min(int(round(sN * m / (o * o * v * v))), sN))   # same density as the target
-    sm_con = max(1, min(100_000, sN // 10))
-    rng = np.random.default_rng(1)
-    t2 = (rng.standard_normal(sN) * 10.0 ** (-6.0 * rng.random(sN) ** 2)).reshape(so, so, sv, sv)
-    ext = {"o": so, "v": sv}
+    if R is not None:
+        R.set_num_threads(threads)
+    return R, oracle.port()
+
+
+def _time_point(R, P, o, v, m_comp, m_con, sampling, terms, rng, n_comp=2):
+    """Seconds for `n_comp` compressions at (o, v, m_comp) and each contraction term in `terms` at (o, v, m_con), on an
+    FRI-compressed tensor (the layout the drivers hand over)."""
+    import numpy as np
+
     from fricc_b200.dist import TERM_AXES
 
-    times = {}
-    t0 = time.perf_counter()
-    if R is not None:
-        T1 = R.mod.SparseTensor4d(t2, t2.shape, sm_comp, "fri", sampling, False)
-        T2_ = R.mod.SparseTensor4d(t2, t2.shape, sm_comp, "fri", sampling, False)
-        del T1, T2_
-    else:
-        draws = rng.integers(0, 2**31 - 1, size=sN).astype(np.int32)
-        P.fri_compression(t2, sm_comp, sampling, draws)
-        P.fri_compression(t2, sm_comp, sampling, draws)
-    times["compress_x2"] = time.perf_counter() - t0
-    if R is not None:
-        T = R.mod.SparseTensor4d(t2, t2.shape, sm_con, "largest")
-    else:
-        flat, vals = P.largest(t2, sm_con)
-    for term in CONTRACTION_ORDER:
-        ax = TERM_AXES[term]
-        W = rng.random([ext[c] for c in ax["w"]])
-        out = np.zeros([ext[c] for c in ax["out"]])
+    n = o * o * v * v
+    t2 = (rng.standard_normal(n) * 10.0 ** (-6.0 * rng.random(n) ** 2)).reshape(o, o, v, v)
+    out = {}
+    if n_comp:
         t0 = time.perf_counter()
+        for _ in range(n_comp):
+            if R is not None:
+                T = R.mod.SparseTensor4d(t2, list(t2.shape), int(m_comp), "fri", sampling, False)
+            else:
+                P.fri_compression(t2, int(m_comp), sampling, rng.integers(0, 2**31 - 1, size=n).astype(np.int32))
+        out["compress"] = (time.perf_counter() - t0) / n_comp
+    if terms:
         if R is not None:
-            R.mod.contract_DTSpT(W, T, out, term)
+            T = R.mod.SparseTensor4d(t2, list(t2.shape), int(m_con), "fri", "systematic", False)
         else:
-            P.contract(term, W, flat, vals, t2.shape, out)
-        times[term] = time.perf_counter() - t0
-    fs, ft = flops_model(so, sv, sm_con), flops_model(o, v, m)
-    extrap = times["compress_x2"] * (o * o * v * v) / sN   # N log N treated as linear: favours the reference
+            cmp_ = P.fri_compression(t2, int(m_con), "systematic", np.array([12345], dtype=np.int32))
+            flat, vals = cmp_["idx"], cmp_["vals"]
+        ext = {"o": o, "v": v}
+        for term in terms:
+            ax = TERM_AXES[term]
+            W = rng.random([ext[c] for c in ax["w"]])
+            dst = np.zeros([ext[c] for c in ax["out"]])
+            t0 = time.perf_counter()
+            if R is not None:
+                R.mod.contract_DTSpT(W, T, dst, term)
+            else:
+                P.contract(term, W, flat, vals, t2.shape, dst)
+            out[term] = time.perf_counter() - t0
+    return out
+
+
+def cpu_reference_sample(o, v, m, sampling, threads, scale=1.0):
+    """One bounded sample of the reference's CPU path -> seconds per FRI-CCSD iteration at (o, v, m).
+
+    If the workload itself is small enough for the host (W = 8 v^4 bytes <= 4 GB and <= ~3e10 FMAs) it is RUN as it is:
+    2 compressions + the 11 terms at (o, v, m) -- `same_config` true, no model.  Otherwise sample points at o' = min(o, 40),
+    v' in {60, 80, 100, 120} and two m' are timed and each part is fitted and extrapolated:
+      ladder 2323      t = a m v^2 + b o^2 m + c  (FMAs + the o^2 m index tests of the owner scan, sparse_tensor.cpp:62-73)
+      0101             t = a m o^2 + b v^2 m + c
+      1323, O^3V^3     t = a * (FMAs + index tests)   (both scale alike: one coefficient)
+      compression      t = g N log2 N               (the full merge sort of N pairs is 77 % of it)
+    `scale` < 1 shrinks the sample (warm-up steps)."""
+    import numpy as np
+
+    R, P = _ref_modules(threads)
+    kind = "reference" if R is not None else "port"
+    rng = np.random.default_rng(1)
+    N = o * o * v * v
+    fm = flops_model(o, v, m)
+    total_fma = sum(fm.values())
+    if 8.0 * v ** 4 <= 4e9 and total_fma <= 3e10 and scale >= 1.0:
+        pt = _time_point(R, P, o, v, m, m, sampling, CONTRACTION_ORDER, rng, n_comp=2)
+        total = 2 * pt["compress"] + sum(pt[t] for t in CONTRACTION_ORDER)
+        sample = (f"oracle/{'_ref' if R is not None else 'port'}: the workload itself -- 2x SparseTensor4d(fri,{sampling}) + "
+                  f"the 11 contract_DTSpT terms at o={o},v={v},m={int(m)}; {total:.2f} s")
+        return dict(kind=kind, cores=threads, sample=sample, measured_s=total, extrapolated_s=total, same_config=True,
+                    parts={k: round(x, 4) for k, x in pt.items()}, fit=None)
+    so = min(o, 40)
+    vs = [vv for vv in (60, 80, 100, 120) if vv <= max(v, 60)]
+    if scale < 1.0:
+        vs, m_lo, m_hi = [40, 60], 2e4, 4e4
+    else:
+        m_lo, m_hi = 5e4, 2e5
+    points = []
+    t_start = time.perf_counter()
+    # ladder: every v' at m_lo, one more at m_hi (separates the v^2 term from the o^2 scan term)
+    lad = [(vv, m_lo) for vv in vs] + [(vs[min(1, len(vs) - 1)], m_hi)]
+    for vv, mm in lad:
+        pt = _time_point(R, P, so, vv, mm, mm, sampling, ["2323", "0101", "1323"], rng, n_comp=0)
+        points.append(dict(o=so, v=vv, m=int(mm), **{k: round(x, 5) for k, x in pt.items()}))
+    # O^3V^3 terms: one coefficient each, two points
+    o3 = ["1302", "1202", "1303", "1203", "0112", "0313", "0113", "0312"]
+    for vv, mm in ((vs[min(1, len(vs) - 1)], m_lo), (vs[-1], m_hi)):
+        pt = _time_point(R, P, so, vv, mm, mm, sampling, o3, rng, n_comp=0)
+        points.append(dict(o=so, v=vv, m=int(mm), **{k: round(x, 5) for k, x in pt.items()}))
+    # compression at two sizes, the target's density
+    for vv in (vs[0], vs[-2] if len(vs) > 2 else vs[-1]):
+        n = so * so * vv * vv
+        mc = max(1, min(int(round(n * m / N)), n))
+        pt = _time_point(R, P, so, vv, mc, 0, sampling, [], rng, n_comp=1)
+        points.append(dict(o=so, v=vv, m_comp=mc, N=n, compress=round(pt["compress"], 5)))
+    measured = time.perf_counter() - t_start
+
+    def lstsq_nonneg(rows, ys):
+        A, y = np.array(rows, dtype=float), np.array(ys, dtype=float)
+        coef, *_ = np.linalg.lstsq(A, y, rcond=None)
+        if (coef < 0).any():            # drop the negative feature and refit the other
+            keep = [i for i in range(A.shape[1]) if coef[i] >= 0] or [0]
+            c2, *_ = np.linalg.lstsq(A[:, keep], y, rcond=None)
+            coef = np.zeros(A.shape[1])
+            coef[keep] = np.maximum(c2, 0.0)
+        pred = A @ coef
+        resid = float(np.max(np.abs(pred - y) / np.maximum(y, 1e-12)))
+        return coef, resid
+
+    fit, extrap = {}, 0.0
     for term in CONTRACTION_ORDER:
-        extrap += times[term] * ft[term] / fs[term]
-    sample = (f"oracle/{'_ref' if R is not None else 'port'}: 2x SparseTensor4d(fri,{sampling}) at o={so},v={sv},"
-              f"m={sm_comp} + the 11 contract_DTSpT terms at o={so},v={sv},m={sm_con}; measured {sum(times.values()):.2f} s;"
-              f" extrapolated to o={o},v={v},m={int(m)} per part by FMA count (contractions) and N (compression)")
-    return dict(kind=kind, cores=threads, sample=sample, measured_s=sum(times.values()), extrapolated_s=extrap,
-                parts={k: round(x, 4) for k, x in times.items()})
+        pts = [p_ for p_ in points if term in p_]
+        if term in ("2323", "0101"):
+            # + a constant per call (thread start-up, first touch of the output): keeps it out of the per-FMA rate
+            rows = [[flops_model(p_["o"], p_["v"], p_["m"])[term], scan_model(p_["o"], p_["v"], p_["m"])[term], 1.0] for p_ in pts]
+            target = [fm[term], scan_model(o, v, m)[term], 1.0]
+        else:
+            rows = [[flops_model(p_["o"], p_["v"], p_["m"])[term] + scan_model(p_["o"], p_["v"], p_["m"])[term]] for p_ in pts]
+            target = [fm[term] + scan_model(o, v, m)[term]]
+        coef, resid = lstsq_nonneg(rows, [p_[term] for p_ in pts])
+        t_term = float(np.dot(coef, target))
+        fit[term] = dict(ns_per_unit=[round(float(c) * 1e9, 4) for c in coef[:2]], max_rel_residual=round(resid, 3),
+                         extrapolated_s=round(t_term, 3))
+        extrap += t_term
+    cp = [p_ for p_ in points if "compress" in p_]
+    coef, resid = lstsq_nonneg([[p_["N"] * math.log2(p_["N"])] for p_ in cp], [p_["compress"] for p_ in cp])
+    t_comp = 2.0 * float(coef[0]) * N * math.log2(N)
+    fit["compress_x2"] = dict(ns_per_NlogN=round(float(coef[0]) * 1e9, 5), max_rel_residual=round(resid, 3),
+                              extrapolated_s=round(t_comp, 3))
+    extrap += t_comp
+    sample = (f"oracle/{'_ref' if R is not None else 'port'}: {len(points)} sample points at o={so}, v in {vs}, "
+              f"m in {{{int(m_lo)}, {int(m_hi)}}} on FRI-compressed tensors ({measured:.1f} s measured); per-term fit "
+              f"t = a*FMAs + b*index_tests (compression: g*N*log2 N) extrapolated to o={o},v={v},m={int(m)}")
+    return dict(kind=kind, cores=threads, sample=sample, measured_s=measured, extrapolated_s=extrap, same_config=False,
+                parts=None, fit=fit, points=points)
 
 
 def run_reference_arm(args):
@@ -149,396 +269,32 @@ def run_reference_arm(args):
         return
     threads = os.cpu_count() or 1
     o, v, m = args.o, args.v, int(args.m)
-    vals, meas = [], []
-    for it in range(args.warmup + args.steps):
+    for _ in range(max(args.warmup, 0)):
+        cpu_reference_sample(o, v, m, args.sampling, threads, scale=0.25)   # warm-up: page cache, thread pool
+    vals, meas, r = [], [], None
+    for _ in range(max(args.steps, 1)):
         r = cpu_reference_sample(o, v, m, args.sampling, threads)
-        if it >= args.warmup:
-            vals.append(r["extrapolated_s"])
-            meas.append(r["measured_s"])
+        vals.append(r["extrapolated_s"])
+        meas.append(r["measured_s"])
     value = sum(vals) / len(vals)
+    cfg = workload_config(args, args.gpus)
+    cfg["same_config"] = bool(r["same_config"])
     line = {
-        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": 1e3 * sum(meas) / len(meas), "higher_is_better": False,
-        "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": workload_config(args, args.gpus),
+        "impl": "reference", "metric": metric_name(o, v, m), "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sum(meas) / len(meas), "higher_is_better": False,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": cfg,
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": r["cores"], "kind": r["kind"], "sample": r["sample"]},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0,
+        "gpu_launches": 0, "fit": r["fit"], "sample_points": r.get("points"), "parts_s": r["parts"],
+        "per_step_values": [round(x, 3) for x in vals],
     }
     print(json.dumps(line))
-
-
-def workload_config(args, world):
-    o, v, m = args.o, args.v, int(args.m)
-    return {
-        "workload": f"synthetic FRI-CCSD iteration o={o},v={v},m={m}: 2 FRI compressions ({args.sampling}) of T2 "
-                    f"(N={o*o*v*v}) + 11 sparse contractions; vvvv panel sharded by (a,b) columns over {world} GPU(s)",
-        "o": o, "v": v, "m": m, "sampling": args.sampling, "parallelism": f"free-pair column shards x{world}",
-        "l2": "inputs_larger_than_L2",
-    }
 
 
 # ======================================================================================================================
 # the B200 arm
 # ======================================================================================================================
-class Iteration:
-    """Device-resident synthetic FRI-CCSD iteration, one instance per rank."""
-
-    def __init__(self, args, comm, device):
-        import torch
-
-        from fricc_b200 import dist as fd
-
-        self.torch, self.fd = torch, fd
-        self.args, self.comm, self.device = args, comm, device
-        o, v = args.o, args.v
-        self.o, self.v, self.m = o, v, int(args.m)
-        self.N = o * o * v * v
-        g = torch.Generator(device=device)
-        g.manual_seed(20)
-        # heavy-tailed amplitudes (a few dominant entries -> non-empty D), identical on every rank
-        u = torch.rand(self.N, generator=g, device=device, dtype=torch.float64)
-        z = torch.randn(self.N, generator=g, device=device, dtype=torch.float64)
-        self.t2 = (z * torch.pow(10.0, -6.0 * u * u)).reshape(o, o, v, v).contiguous()
-        del u, z
-        self.terms = {t: fd.ShardedTerm(t, o, v, comm, device) for t in CONTRACTION_ORDER}
-        # tensor-core form when T is dense enough for it to win (fricc_dense.cu: break-even ~1.3 % at 6 planes)
-        self.planes = args.planes if (args.planes > 0 and self.m / self.N >= 0.015) else 0
-        for t in self.terms.values():
-            t.auto_planes = self.planes
-        # ---- dense operands (U(0,1) like the reference's tests, fricc/tests/test_sparse_tensors.py:78)
-        self.ovov = torch.rand(o, v, o, v, generator=g, device=device, dtype=torch.float64)
-        # iteration-invariant operand -> its panels are permuted once, outside the timed region
-        for t in ("1323", "0112", "0313"):
-            self.terms[t].permute_from(self.ovov)
-        # terms that read the same operand through the same (K, L) axes share one panel
-        self.terms["0113"].set_panel(self.terms["0112"].panel, planes_from=self.terms["0112"])
-        self.terms["0312"].set_panel(self.terms["0313"].panel, planes_from=self.terms["0313"])
-        self.peer = comm.world > 1 and args.exchange == "peer" and not args.no_overlap and not args.only_ladder
-        self.side = None
-        if self.peer:
-            # the outputs live in one symmetric allocation per rank: every rank stores its columns into all copies
-            nb = 8 * (o ** 4 + 2 * v * o * o * v + 4 * o * o * v * v) + 8 * 4096
-            self.arena = fd.SymmArena(nb, comm, device)
-            mk = lambda *shape: self.arena.tensor(shape).zero_()
-        else:
-            self.arena = None
-            mk = lambda *shape: torch.zeros(*shape, device=device, dtype=torch.float64)
-        self.Wklij = mk(o, o, o, o)
-        self.Wakic = mk(v, o, o, v)
-        self.Wakci = mk(v, o, v, o)
-        self.t2new = mk(o, o, v, v)
-        self.tmp = [mk(o, o, v, v) for _ in range(3)]
-        self.flag = torch.zeros(1, device=device, dtype=torch.float32)
-        # ---- the ladder operand: this rank's (a,b)-column slice of Wp[(c,d)][(a,b)], possibly in sub-shards
-        lad = self.terms["2323"]
-        max_cols = max(1, int(args.max_panel_gb * 1e9 / (8 * lad.nK)))
-        self.sub = []
-        c = 0
-        while c < lad.lcnt:
-            w = min(max_cols, lad.lcnt - c)
-            self.sub.append((c, w))
-            c += w
-        self.lad_width = max((w for _, w in self.sub), default=1)
-        self.lad_panel = torch.empty(lad.nK * self.lad_width, device=device, dtype=torch.float64)
-        self.resident = len(self.sub) <= 1
-        self.plane_build_ms = []
-        if self.resident and self.sub:
-            self.fill_ladder_panel(0)
-        self.draws = torch.randint(0, 2**31 - 1, (64,), generator=torch.Generator().manual_seed(5)).numpy().astype("int32")
-        self.draw_pos = 0
-        self.ladder_events = []
-        self.stage_events = []
-
-    def fill_ladder_panel(self, s):
-        """(Re)generate sub-shard s of the ladder panel in HBM -- an INPUT, not part of the timed work."""
-        torch = self.torch
-        c, w = self.sub[s]
-        lad = self.terms["2323"]
-        g = torch.Generator(device=self.device)
-        g.manual_seed(1000 + lad.l0 + c)
-        view = self.lad_panel[: lad.nK * w]
-        # chunked fill keeps the generator's temporary small
-        step = 1 << 28
-        for a in range(0, view.numel(), step):
-            view[a: a + step].uniform_(0.0, 1.0, generator=g)
-        if self.planes > 0:
-            # the digit planes are a re-encoding of this INPUT (like its [K][L] permutation): built with it, untimed,
-            # and reported separately (`ladder_plane_build_ms`)
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-            if lad.planes is not None and lad._planes_lcnt == w:
-                lad.refresh_planes(self.lad_panel)
-            else:
-                lad.build_planes(self.planes, panel=self.lad_panel, lcnt=w)
-            e1.record()
-            self.plane_build_ms.append((e0, e1))
-
-    def compress(self, t2):
-        d = self.draws[self.draw_pos % 32:]
-        self.draw_pos += 1
-        return self.fd.compress(t2, self.m, "fri", self.args.sampling, draws=d if self.args.sampling == "systematic" else None)
-
-    def ladder_local(self, T, timer=None):
-        """Particle-particle ladder on this rank's column slice (into t2new directly when there is one rank)."""
-        torch = self.torch
-        lad = self.terms["2323"]
-        L = lad.L
-        single = self.comm.world == 1   # one rank: accumulate straight into t2new (no panel, no gather)
-        if not single:
-            if lad.out_panel is None:
-                lad.out_panel = torch.empty(lad.nR * lad.lc, dtype=torch.float64, device=self.device)
-            lad.out_panel.zero_()
-        for s, (c, w) in enumerate(self.sub):
-            if not self.resident:
-                if timer:
-                    timer.pause()
-                self.fill_ladder_panel(s)
-                if timer:
-                    timer.resume()
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-            if single:
-                lad.local_into(T, self.t2new, panel=self.lad_panel, l0=lad.l0 + c, lcnt=w)
-            else:
-                if lad.planes is not None and lad._planes_lcnt == w and lad.use_tc(T):
-                    self.fd.check(L.fricc_contract_panel_tc(lad.planes, self.fd._ptr(self.lad_panel), w, lad.l0 + c, T._h,
-                                                            ctypes_ptr(lad.out_panel, c), lad.lc, b"2323", 0))
-                else:
-                    self.fd.check(L.fricc_contract_panel(self.fd._ptr(self.lad_panel), w, lad.l0 + c, w, T._h,
-                                                         ctypes_ptr(lad.out_panel, c), lad.lc, b"2323"))
-            e1.record()
-            self.ladder_events.append((e0, e1, w))
-
-    def ladder(self, T, timer=None):
-        self.ladder_local(T, timer)
-        if self.comm.world > 1:
-            self.terms["2323"].exchange_and_accumulate(T, self.t2new)
-
-    def mark(self, name):
-        e = self.torch.cuda.Event(enable_timing=True)
-        e.record()
-        self.stage_events.append((name, e))
-
-    def compress_mode(self):
-        c = self.args.compress
-        if c == "auto":
-            if self.args.sampling == "systematic":
-                return "ranges"
-            return "pair" if (self.comm.world > 1 and not self.args.no_overlap) else "replicated"
-        return c
-
-    def step(self, t2, timer=None):
-        self.mark("begin")
-        mode = self.compress_mode()
-        if mode == "ranges":
-            # every rank scans only its contiguous 1/N of T2 (a view: T2 is replicated); the two compressions differ
-            # only in the draw, so norm, D and the running sums of p are computed once (fricc_b200/ranges.py)
-            d = (self.draws[self.draw_pos % 32:], self.draws[(self.draw_pos + 1) % 32:])
-            self.draw_pos += 2
-            flat = t2.view(-1)
-            j0, cnt = self.fd.index_range(flat.numel(), self.comm.rank, self.comm.world)
-            T, T_alt = self.fd.compress_ranges_pair(flat[j0:j0 + cnt], j0, tuple(t2.shape), self.m, self.comm, "fri",
-                                                    "systematic", draws=d)
-        elif mode == "pair" and self.comm.world > 1:
-            # task-parallel: even ranks compress with the first draws, odd ranks with the second, entries broadcast
-            d = None
-            if self.args.sampling == "systematic":
-                d = (self.draws[self.draw_pos % 32:], self.draws[(self.draw_pos + 1) % 32:])
-            self.draw_pos += 2
-            T, T_alt = self.fd.compress_pair(t2, self.m, self.comm, "fri", self.args.sampling, draws=d)
-        else:
-            T = self.compress(t2)
-            T_alt = self.compress(t2)
-        self.mark("compress_x2")
-        if self.peer:
-            return self.step_peer(T, T_alt, timer)
-        if self.comm.world > 1 and not self.args.only_ladder and not self.args.no_overlap:
-            return self.step_pipelined(T, T_alt, timer)
-        tm = self.terms
-        if not self.args.only_ladder:
-            self.Wklij.zero_(); self.Wakic.zero_(); self.Wakci.zero_()
-            self.t2new.zero_()
-            for t in self.tmp:
-                t.zero_()
-            self.mark("zero_outputs")
-            tm["1323"](T_alt, self.Wklij)
-            self.mark("1323")
-            tm["0112"](T_alt, self.Wakic)
-            self.mark("0112")
-            tm["0313"](T_alt, self.Wakic)
-            self.mark("0313")
-            tm["0113"](T_alt, self.Wakic)
-            self.mark("0113")
-            tm["0312"](T_alt, self.Wakci)
-            self.mark("0312")
-            tm["0101"](T, self.t2new, W=self.Wklij)
-            self.mark("0101")
-        self.ladder(T, timer)
-        self.mark("2323_incl_regen" if not self.resident else "2323")
-        if not self.args.only_ladder:
-            tm["1302"](T, self.tmp[0], W=self.Wakic)
-            self.mark("1302")
-            tm["1202"](T, self.tmp[0], W=self.Wakci)
-            self.mark("1202")
-            tm["1303"].set_panel(tm["1302"].panel, planes_from=tm["1302"])   # same Wvoov panel (K=(k,c), L=(a,i))
-            tm["1203"].set_panel(tm["1202"].panel, planes_from=tm["1202"])   # same Wvovo panel
-            tm["1303"](T, self.tmp[1])
-            self.mark("1303")
-            tm["1203"](T, self.tmp[2])
-            self.mark("1203")
-        return T
-
-    def rank_barrier(self):
-        """Stream-ordered barrier (a 4-byte NCCL all-reduce): everything every rank queued before it -- including its
-        stores into this rank's memory -- has completed when the work queued behind it starts.  Does not block the host."""
-        import torch.distributed as dist
-
-        dist.all_reduce(self.flag, group=self.comm.group)
-
-    def step_peer(self, T, T_alt, timer=None):
-        """N > 1, exchange over peer memory: every term accumulates its L-columns straight into this rank's copy of the
-        4-D output and the finished columns are stored into every peer's copy over NVLink (fricc_peer.cu) -- no panels,
-        no all-gather, no re-accumulation pass.  Three barriers order consumers behind writers:
-          B0 after the outputs are zeroed (a peer must not zero what was already pushed to it),
-          B1 before Woooo / Wvoov / Wvovo are read as operands and before 0101 (column axis (i,j)) accumulates onto the
-             ladder's t2new (column axis (a,b)): an output must be complete everywhere before a term with a different
-             column axis adds to it,
-          B2 at the end of the step."""
-        tm, dims, push = self.terms, (self.o, self.o, self.v, self.v), self.fd.push_columns
-        if self.side is None and not self.args.push_inline:
-            self.side = self.fd.SideStream(self.device)
-        S = None if self.args.push_inline else self.side   # peer stores run on it, under the next term's kernel
-        self.Wklij.zero_(); self.Wakic.zero_(); self.Wakci.zero_()
-        self.t2new.zero_()
-        for t in self.tmp:
-            t.zero_()
-        self.rank_barrier()
-        self.mark("zero_outputs_B0")
-        A = self.arena
-        # the ladder first: its 2 GB push then hides under the ovov terms; the o^4-sized output goes last, so that
-        # only its (tiny) push is exposed in front of the barrier
-        lad = tm["2323"]
-        for s_, (c, w) in enumerate(self.sub):
-            if not self.resident:
-                if timer:
-                    timer.pause()
-                self.fill_ladder_panel(s_)
-                if timer:
-                    timer.resume()
-            e0, e1 = self.torch.cuda.Event(enable_timing=True), self.torch.cuda.Event(enable_timing=True)
-            e0.record()
-            lad.local_into(T, self.t2new, panel=self.lad_panel, l0=lad.l0 + c, lcnt=w)
-            e1.record()
-            self.ladder_events.append((e0, e1, w))
-        push(lad, dims, self.t2new, A, side=S)
-        self.mark("2323" if self.resident else "2323_incl_regen")
-        tm["0112"].accumulate(T_alt, self.Wakic, also=(tm["0313"], tm["0113"]), arena=A, side=S)
-        self.mark("0112_0313_0113")
-        tm["0312"].accumulate(T_alt, self.Wakci, arena=A, side=S)
-        self.mark("0312")
-        tm["1323"].accumulate(T_alt, self.Wklij, arena=A, side=S)
-        self.mark("1323")
-        if S is not None:
-            S.join()
-        self.rank_barrier()
-        self.mark("B1")
-        tm["1302"].permute_from(self.Wakic); tm["1202"].permute_from(self.Wakci)
-        tm["1302"].accumulate(T, self.tmp[0], also=(tm["1202"],), arena=A, side=S)
-        self.mark("1302_1202")
-        tm["1303"].set_panel(tm["1302"].panel, planes_from=tm["1302"]); tm["1303"].accumulate(T, self.tmp[1], arena=A, side=S)
-        self.mark("1303")
-        tm["1203"].set_panel(tm["1202"].panel, planes_from=tm["1202"]); tm["1203"].accumulate(T, self.tmp[2], arena=A, side=S)
-        self.mark("1203")
-        tm["0101"].permute_from(self.Wklij); tm["0101"].accumulate(T, self.t2new, arena=A, side=S)
-        self.mark("0101")
-        if S is not None:
-            S.join()
-        self.rank_barrier()
-        self.mark("B2")
-        return T
-
-    def step_pipelined(self, T, T_alt, timer=None):
-        """N > 1: the same 11 contractions, ordered so that every all-gather (NCCL, its own stream) runs under the next
-        term's SpMM, and terms that feed the same output through the same (R, L) map share one panel and one exchange
-        (0112+0313+0113 -> Wvoov, 1302+1202 -> tmp).  Data dependences: 0101 reads Woooo (1323), 1302/1303 read Wvoov,
-        1202/1203 read Wvovo (0312)."""
-        tm = self.terms
-        self.Wklij.zero_(); self.Wakic.zero_(); self.Wakci.zero_()
-        self.t2new.zero_()
-        for t in self.tmp:
-            t.zero_()
-        self.mark("zero_outputs")
-        tm["1323"].local(T_alt); tm["1323"].start_exchange()
-        self.mark("1323_local")
-        tm["0112"].local(T_alt)
-        tm["0313"].local(T_alt, into=tm["0112"])
-        tm["0113"].local(T_alt, into=tm["0112"])
-        tm["0112"].start_exchange()
-        self.mark("0112_0313_0113_local")
-        tm["0312"].local(T_alt); tm["0312"].start_exchange()
-        self.mark("0312_local")
-        self.ladder_local(T, timer)                       # the long one: hides the three gathers above
-        tm["2323"].start_exchange()
-        self.mark("2323_local" if self.resident else "2323_local_incl_regen")
-        tm["1323"].finish(T_alt, self.Wklij)
-        tm["0112"].finish(T_alt, self.Wakic)
-        tm["0312"].finish(T_alt, self.Wakci)
-        self.mark("finish_Woooo_Wvoov_Wvovo")
-        tm["0101"].permute_from(self.Wklij); tm["0101"].local(T); tm["0101"].start_exchange()
-        self.mark("0101_local")
-        tm["1302"].permute_from(self.Wakic); tm["1302"].local(T)
-        tm["1202"].permute_from(self.Wakci); tm["1202"].local(T, into=tm["1302"])
-        tm["1302"].start_exchange()
-        self.mark("1302_1202_local")
-        tm["2323"].finish(T, self.t2new)
-        self.mark("finish_2323")
-        tm["1303"].set_panel(tm["1302"].panel, planes_from=tm["1302"]); tm["1303"].local(T); tm["1303"].start_exchange()
-        self.mark("1303_local")
-        tm["0101"].finish(T, self.t2new)
-        tm["1203"].set_panel(tm["1202"].panel, planes_from=tm["1202"]); tm["1203"].local(T); tm["1203"].start_exchange()
-        self.mark("finish_0101_1203_local")
-        tm["1302"].finish(T, self.tmp[0])
-        tm["1303"].finish(T, self.tmp[1])
-        tm["1203"].finish(T, self.tmp[2])
-        self.mark("finish_tmp0_tmp1_tmp2")
-        return T
-
-    def stage_breakdown(self, steps):
-        """ms per step spent between consecutive marks (rank-local; includes any exchange inside the stage)."""
-        self.torch.cuda.synchronize()
-        out = {}
-        for (n0, e0), (n1, e1) in zip(self.stage_events, self.stage_events[1:]):
-            if n1 == "begin":
-                continue
-            out[n1] = out.get(n1, 0.0) + e0.elapsed_time(e1)
-        self.stage_events.clear()
-        return {k: round(x / steps, 3) for k, x in out.items()}
-
-
-def ncu_traffic_per_launch(which="spmm_ladder"):
-    """dram__bytes_read.sum + dram__bytes_write.sum of ONE ladder launch (1600 x 20000-column slice, m=1e7), from the
-    committed `ncu --set full` capture (profiles/ncu_full_*_spmm_ladder.csv, newest round); None if absent."""
-    import csv
-    import glob
-
-    files = sorted(glob.glob(os.path.join(ROOT, "profiles", f"ncu_full_r*_{which}.csv")))
-    if not files:
-        return None
-    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
-    tot = 0.0
-    try:
-        for row in csv.DictReader(open(files[-1])):
-            if row["metric"] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
-                tot += float(row["value"]) * scale[row["unit"]]
-    except Exception:
-        return None
-    return tot or None
-
-
-def ctypes_ptr(t, elem_offset=0):
-    import ctypes
-
+def _ptr(t, elem_offset=0):
     return ctypes.c_void_p(int(t.data_ptr()) + 8 * int(elem_offset))
 
 
@@ -564,6 +320,304 @@ class SegmentTimer:
     def total_ms(self):
         self.torch.cuda.synchronize()
         return sum(a.elapsed_time(b) for a, b in self.segments)
+
+
+class Iteration:
+    """Device-resident synthetic FRI-CCSD iteration, one instance per rank (ViewEngine: plugin calls on views)."""
+
+    def __init__(self, args, comm, device):
+        import torch
+
+        from fricc_b200 import _lib
+        from fricc_b200 import dist as fd
+        from fricc_b200 import py_rccsd
+
+        self.torch, self.fd, self.py, self.lib = torch, fd, py_rccsd, _lib.lib()
+        self.check = _lib.check
+        self.args, self.comm, self.device = args, comm, device
+        o, v = args.o, args.v
+        self.o, self.v, self.m = o, v, int(args.m)
+        self.N = o * o * v * v
+        g = torch.Generator(device=device)
+        g.manual_seed(20)
+        # heavy-tailed amplitudes, identical on every rank
+        u = torch.rand(self.N, generator=g, device=device, dtype=torch.float64)
+        z = torch.randn(self.N, generator=g, device=device, dtype=torch.float64)
+        self.t2 = (z * torch.pow(10.0, -6.0 * u * u)).reshape(o, o, v, v).contiguous()
+        del u, z
+        # U(0,1) operands like the reference's tests (fricc/tests/test_sparse_tensors.py:78)
+        self.ovov = torch.rand(o, v, o, v, generator=g, device=device, dtype=torch.float64)
+        self.tc = args.planes > 0
+        py_rccsd.set_option("tc_mode", 1 if self.tc else 0)
+        if self.tc:
+            py_rccsd.set_option("tc_planes", args.planes)
+        self.multi = comm.world > 1
+        self.side = None
+        if self.multi:
+            nb = 8 * (o ** 4 + 2 * v * o * o * v + 4 * o * o * v * v) + 8 * 4096
+            self.arena = fd.SymmArena(nb, comm, device)
+            mk = lambda *shape: self.arena.tensor(shape).zero_()
+            if not args.push_inline:
+                self.side = fd.SideStream(device)
+        else:
+            self.arena = None
+            mk = lambda *shape: torch.zeros(*shape, device=device, dtype=torch.float64)
+        self.Wklij = mk(o, o, o, o)
+        self.Wakic = mk(v, o, o, v)
+        self.Wakci = mk(v, o, v, o)
+        self.t2new = mk(o, o, v, v)
+        self.tmp = [mk(o, o, v, v) for _ in range(3)]
+        self.eng = fd.ViewEngine(comm, device, None if args.nccl_barrier else self.arena, self.side)
+        if args.nccl_barrier:
+            self.eng.arena = self.arena          # peer stores still go through the arena; only the barrier is NCCL
+        # ---- the ladder operand: this rank's a-range of the NATIVE W[a,b,c,d], possibly in sub-shards
+        self.a_lo, self.a_hi = self.eng.my_range(v)
+        na = max(0, self.a_hi - self.a_lo)
+        per_a = 8.0 * v ** 3
+        # resident needs W (8 B) and its planes (S B) per element next to everything else
+        na_sub = max(1, int(args.max_slice_gb * 1e9 / per_a))
+        self.sub = []
+        a = self.a_lo
+        while a < self.a_hi:
+            w = min(na_sub, self.a_hi - a)
+            self.sub.append((a, a + w))
+            a += w
+        self.resident = len(self.sub) <= 1
+        width = max((b - a for a, b in self.sub), default=1)
+        self.Wlad = torch.empty(width, v, v, v, device=device, dtype=torch.float64)
+        self.planes = None                      # fricc_wslices_t of the sub-shard currently in Wlad
+        self.plane_ms, self.ladder_ms = [], []
+        self.cur_sub = -1
+        if self.sub:
+            self.fill_sub(0)
+            if self.tc and args.w_mode == "invariant":
+                self.build_planes(0)
+        self.draws = torch.randint(0, 2**31 - 1, (64,), generator=torch.Generator().manual_seed(5)).numpy().astype("int32")
+        self.draw_pos = 0
+        self.stage_events = []
+
+    # -- the ladder operand ---------------------------------------------------------------------------------------
+    def wsub(self, s):
+        a, b = self.sub[s]
+        return self.Wlad[: b - a]
+
+    def fill_sub(self, s):
+        """(Re)generate sub-shard s of W in HBM -- an INPUT (the caller's dense work), not part of the timed step.
+        Values depend on the GLOBAL element index only, so every sharding holds the same tensor."""
+        a, b = self.sub[s]
+        n = (b - a) * self.v ** 3
+        self.check(self.lib.fricc_fill_uniform(_ptr(self.Wlad), n, a * self.v ** 3, 1000))
+        self.cur_sub = s
+
+    def build_planes(self, s, timed=False):
+        """int8 digit planes of sub-shard s, straight from the native layout (single-read cluster kernel)."""
+        torch, fd = self.torch, self.fd
+        W = self.wsub(s)
+        cols = W.shape[0] * self.v
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        if self.planes is not None and self._planes_cols == cols:
+            self.check(self.lib.fricc_wslices_update_view(self.planes, _ptr(W), fd.i64x4(W.shape), fd.i64x4(W.stride()),
+                                                          b"2323", 0))
+        else:
+            if self.planes is not None:
+                self.lib.fricc_wslices_destroy(self.planes)
+            h = ctypes.c_void_p()
+            self.check(self.lib.fricc_wslices_create_view(_ptr(W), fd.i64x4(W.shape), fd.i64x4(W.stride()), b"2323", 0, cols,
+                                                          self.args.planes, ctypes.byref(h)))
+            self.planes, self._planes_cols = h, cols
+        e1.record()
+        if timed:
+            self.plane_ms.append((e0, e1, cols))
+
+    def ladder(self, T, timer=None, plugin=False):
+        """2323 on this rank's a-range.  `plugin`: through contract_DTSpT (planes built inside the call); otherwise the
+        same two kernels as two explicit steps, so that each can be timed on its own."""
+        torch, fd = self.torch, self.fd
+        refreshed = self.args.w_mode == "refreshed"
+        for s, (a, b) in enumerate(self.sub):
+            if self.cur_sub != s:
+                if timer:
+                    timer.pause()
+                self.fill_sub(s)
+                if self.tc and not refreshed:
+                    self.build_planes(s)
+                if timer:
+                    timer.resume()
+            W = self.wsub(s)
+            ov = self.t2new[:, :, a:b, :]
+            if plugin or not self.tc:
+                if self.tc and not refreshed:
+                    self.check(self.lib.fricc_contract_planes(self.planes, _ptr(W), fd.i64x4(W.shape), fd.i64x4(W.stride()), 0,
+                                                              T._h, _ptr(ov), fd.i64x4(ov.shape), fd.i64x4(ov.stride()), b"2323"))
+                else:
+                    self.py.contract_DTSpT(W, T, ov, "2323")
+                continue
+            if refreshed:
+                self.build_planes(s, timed=True)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            self.check(self.lib.fricc_contract_planes(self.planes, _ptr(W), fd.i64x4(W.shape), fd.i64x4(W.stride()), 0, T._h,
+                                                      _ptr(ov), fd.i64x4(ov.shape), fd.i64x4(ov.stride()), b"2323"))
+            e1.record()
+            self.ladder_ms.append((e0, e1, (b - a) * self.v))
+        if self.sub:
+            return self.t2new[:, :, self.a_lo:self.a_hi, :]
+        return None
+
+    # -- the step ---------------------------------------------------------------------------------------------------
+    def mark(self, name):
+        e = self.torch.cuda.Event(enable_timing=True)
+        e.record()
+        self.stage_events.append((name, e))
+
+    def compress_mode(self):
+        if self.args.sampling == "systematic":
+            return "ranges"
+        return "pair" if self.multi else "replicated"
+
+    def compress_two(self, t2_slice, j0, full=None):
+        """The step's two compressions.  t2_slice = this rank's contiguous flat range [j0, j0+len) of T2 (systematic:
+        all a rank needs); full = the whole T2 (pivotal)."""
+        fd = self.fd
+        if self.compress_mode() == "ranges":
+            d = (self.draws[self.draw_pos % 32:], self.draws[(self.draw_pos + 1) % 32:])
+            self.draw_pos += 2
+            return fd.compress_ranges_pair(t2_slice, j0, (self.o, self.o, self.v, self.v), self.m, self.comm, "fri",
+                                           "systematic", draws=d)
+        if self.multi:
+            return fd.compress_pair(full, self.m, self.comm, "fri", self.args.sampling, draws=None)
+        return (fd.compress(full, self.m, "fri", self.args.sampling), fd.compress(full, self.m, "fri", self.args.sampling))
+
+    def contractions(self, T, T_alt, timer=None, plugin=False):
+        eng, c = self.eng, self.eng.contract
+        self.Wklij.zero_(); self.Wakic.zero_(); self.Wakci.zero_()
+        self.t2new.zero_()
+        for t in self.tmp:
+            t.zero_()
+        eng.barrier()                                            # B0: nobody stores into a copy that is still being zeroed
+        self.mark("zero_outputs_B0")
+        # the ladder first: its 2 GB of peer stores then hide under the ovov terms
+        eng.publish(self.ladder(T, timer, plugin))
+        self.mark("2323" if self.resident else "2323_incl_regen")
+        c("0112", self.ovov, T_alt, self.Wakic)
+        c("0313", self.ovov, T_alt, self.Wakic)
+        eng.publish(c("0113", self.ovov, T_alt, self.Wakic))
+        self.mark("0112_0313_0113")
+        eng.publish(c("0312", self.ovov, T_alt, self.Wakci))
+        self.mark("0312")
+        eng.publish(c("1323", self.ovov, T_alt, self.Wklij))
+        self.mark("1323")
+        eng.barrier()                                            # B1: Woooo / Wvoov / Wvovo and the ladder's t2new are complete everywhere
+        self.mark("B1")
+        c("1302", self.Wakic, T, self.tmp[0])
+        eng.publish(c("1202", self.Wakci, T, self.tmp[0]))
+        self.mark("1302_1202")
+        eng.publish(c("1303", self.Wakic, T, self.tmp[1]))
+        self.mark("1303")
+        eng.publish(c("1203", self.Wakci, T, self.tmp[2]))
+        self.mark("1203")
+        eng.publish(c("0101", self.Wklij, T, self.t2new))
+        self.mark("0101")
+        eng.barrier()                                            # B2: the step's outputs are complete on every rank
+        self.mark("B2")
+
+    def step(self, t2, timer=None):
+        self.mark("begin")
+        flat = t2.view(-1)
+        j0, cnt = self.fd.index_range(flat.numel(), self.comm.rank, self.comm.world)
+        T, T_alt = self.compress_two(flat[j0:j0 + cnt], j0, full=t2)
+        self.mark("compress_x2")
+        self.contractions(T, T_alt, timer, plugin=False)
+        return T
+
+    def stage_breakdown(self, steps):
+        self.torch.cuda.synchronize()
+        out = {}
+        for (n0, e0), (n1, e1) in zip(self.stage_events, self.stage_events[1:]):
+            if n1 == "begin":
+                continue
+            out[n1] = out.get(n1, 0.0) + e0.elapsed_time(e1)
+        self.stage_events.clear()
+        return {k: round(x / steps, 3) for k, x in out.items()}
+
+
+def compression_sweep(comm, device, torch, fd, sizes=(1.0e8, 2.56e8, 1.0e9), m=10_000_000, reps=3):
+    """BASELINE config 5: compression only (top-m select + D + sampler) of a synthetic heavy-tailed T2 of N entries, at
+    THIS run's GPU count.  systematic: range-sharded (every rank holds and scans N/G entries); pivotal: the walk is not
+    range-sharded -- one rank's time for one compression of the full tensor.  ms = median of `reps`, max over ranks."""
+    import numpy as np
+    import torch.distributed as dist
+
+    from fricc_b200 import ranges
+    from fricc_b200.py_rccsd import SparseTensor4d
+
+    out = []
+    world, rank = comm.world, comm.rank
+    draw = np.array([123456789], dtype=np.int32)
+    peak = 6650.0
+    try:
+        peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).get("hbm_gbs", peak))
+    except Exception:
+        pass
+
+    def timed(fn):
+        ts = []
+        for it in range(1 + reps):
+            if world > 1:
+                dist.barrier()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            fn()
+            e1.record()
+            torch.cuda.synchronize()
+            t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=device)
+            if world > 1:
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            if it > 0:
+                ts.append(float(t.item()))
+        ts.sort()
+        return ts[len(ts) // 2]
+
+    for size in sizes:
+        v = int(round((size / 1600) ** 0.5))
+        n = 1600 * v * v
+        dims = (40, 40, v, v)
+        mm = min(m, n)
+        j0, cnt = ranges.index_range(n, rank, world)
+        g = torch.Generator(device=device)
+        g.manual_seed(20 + rank)
+        u = torch.rand(cnt, generator=g, device=device, dtype=torch.float64)
+        z = torch.randn(cnt, generator=g, device=device, dtype=torch.float64)
+        x = (z * torch.pow(10.0, -6.0 * u * u)).contiguous()
+        del u, z
+        ms = timed(lambda: ranges.compress_ranges(x, j0, dims, mm, comm, "fri", "systematic", draws=draw))
+        bcomp = 16.0 * n + 16.0 * mm
+        out.append({"N": n, "m": mm, "sampler": "systematic", "how": f"range-sharded over {world} GPU(s)",
+                    "ms_per_compression": round(ms, 3), "elements_per_s": n / (ms * 1e-3),
+                    "frac_of_measured_hbm": bcomp / (ms * 1e-3) / 1e9 / (peak * world)})
+        del x
+        if rank == 0 and n <= 3.0e8:
+            g.manual_seed(20)
+            u = torch.rand(n, generator=g, device=device, dtype=torch.float64)
+            z = torch.randn(n, generator=g, device=device, dtype=torch.float64)
+            xf = (z * torch.pow(10.0, -6.0 * u * u)).reshape(dims).contiguous()
+            del u, z
+        else:
+            xf = None
+        # pivotal: one rank, the others wait in the barrier (its walk is sequential in index order and not sharded)
+        def piv():
+            if xf is not None:
+                SparseTensor4d(xf, dims, mm, "fri", "pivotal", False)
+        if n <= 3.0e8:
+            ms = timed(piv)
+            out.append({"N": n, "m": mm, "sampler": "pivotal", "how": "one GPU (the pivotal walk is not range-sharded)",
+                        "ms_per_compression": round(ms, 3), "elements_per_s": n / (ms * 1e-3),
+                        "frac_of_measured_hbm": bcomp / (ms * 1e-3) / 1e9 / peak})
+        del xf
+        torch.cuda.empty_cache()
+    return out
 
 
 def start_clock_sampler(gpu_index):
@@ -601,10 +655,29 @@ def stop_clock_sampler(proc, path):
                 reasons.add(nme)
     os.unlink(path)
     sm.sort()
-    # median over the upper half of the samples = under load (the sampler also sees the idle gaps)
-    load = sm[len(sm) // 2:] if sm else []
+    load = sm[len(sm) // 2:] if sm else []      # upper half of the samples = under load (the sampler also sees idle gaps)
     return {"sm_mhz": (load[len(load) // 2] if load else None), "sm_max_mhz": (max(mx) if mx else None),
             "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def ncu_traffic_per_launch(which):
+    """dram__bytes_read.sum + dram__bytes_write.sum of ONE launch from the newest committed `ncu --set full` summary
+    profiles/ncu_full_r*_<which>.csv; None if absent."""
+    import csv
+    import glob
+
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", f"ncu_full_r*_{which}.csv")))
+    if not files:
+        return None
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
+    tot = 0.0
+    try:
+        for row in csv.DictReader(open(files[-1])):
+            if row["metric"] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                tot += float(row["value"]) * scale[row["unit"]]
+    except Exception:
+        return None
+    return tot or None
 
 
 def run_b200_arm(args):
@@ -616,11 +689,13 @@ def run_b200_arm(args):
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
                "--master-addr", "127.0.0.1", "--master-port", "29533", os.path.abspath(__file__)] + sys.argv[1:]
         sys.exit(subprocess.call(cmd))
+    import numpy as np
     import torch
     import torch.distributed as dist
 
     from fricc_b200 import _lib
     from fricc_b200 import dist as fd
+    from fricc_b200 import py_rccsd
 
     _lib.require_cuda()
     torch.cuda.set_device(local_rank)
@@ -632,164 +707,237 @@ def run_b200_arm(args):
     comm = fd.Comm(rank, world)
     fd.use_torch_stream()
     L = _lib.lib()
-
-    if args.push_ctas > 0:
-        _lib.check(L.fricc_set_option(b"push_ctas_per_sm", args.push_ctas))
     it = Iteration(args, comm, device)
     o, v, m = it.o, it.v, it.m
-    lad = it.terms["2323"]
 
     def sync_all():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
+    def timed_steps(step_fn, steps):
+        sync_all()
+        timer = SegmentTimer(torch)
+        timer.resume()
+        for _ in range(steps):
+            step_fn(timer)
+        timer.pause()
+        sync_all()
+        return timer.total_ms()
+
     # ---- warm-up
     for _ in range(max(args.warmup, 0)):
         it.step(it.t2)
     sync_all()
-    it.ladder_events.clear()
-    it.stage_events.clear()
+    it.ladder_ms.clear(); it.plane_ms.clear(); it.stage_events.clear()
 
     # ---- timed: device-resident inputs
     proc, cpath = start_clock_sampler(local_rank) if rank == 0 else (None, "")
     launches0 = L.fricc_kernel_launches()
-    sync_all()
-    timer = SegmentTimer(torch)
-    timer.resume()
-    for _ in range(args.steps):
-        T = it.step(it.t2, timer)
-    timer.pause()
-    sync_all()
-    ms = timer.total_ms()
+    tc0 = py_rccsd.get_stat("tc_contract_calls")
+    ms = timed_steps(lambda timer: it.step(it.t2, timer), args.steps)
     launches = L.fricc_kernel_launches() - launches0
+    tc_calls = py_rccsd.get_stat("tc_contract_calls") - tc0
     clocks = stop_clock_sampler(proc, cpath) if rank == 0 else None
     stage_ms = it.stage_breakdown(args.steps)
-    # checksums of the step's outputs (after the last timed step): identical between the pipelined and the blocking
-    # schedule, between ranks, and between GPU counts up to summation order
-    checks = {k: float(v.double().sum().item()) for k, v in
+    checks = {k: float(x.double().sum().item()) for k, x in
               (("t2new", it.t2new), ("tmp0", it.tmp[0]), ("tmp1", it.tmp[1]), ("tmp2", it.tmp[2]),
                ("Wvoov", it.Wakic), ("Wvovo", it.Wakci), ("Woooo", it.Wklij))}
-    lad_ms = [a.elapsed_time(b) for a, b, _ in it.ladder_events]
-    lad_cols = [w for _, _, w in it.ladder_events]
-    it.ladder_events.clear()
-    nD = None
+    torch.cuda.synchronize()
+    lad_ms = [a.elapsed_time(b) for a, b, _ in it.ladder_ms]
+    lad_cols = [c for _, _, c in it.ladder_ms]
+    pl_ms = [a.elapsed_time(b) for a, b, _ in it.plane_ms]
+    pl_cols = [c for _, _, c in it.plane_ms]
+    it.ladder_ms.clear(); it.plane_ms.clear()
 
-    # ---- e2e: T2 from pinned host memory, residual back to pinned host memory, inside the timed region
-    e2e = None
+    # ---- the other operand regime, for the record (same kernels, planes in or out of the step)
+    other_ms = None
+    if it.tc and it.sub:
+        other = "invariant" if args.w_mode == "refreshed" else "refreshed"
+        args.w_mode = other
+        if other == "invariant":
+            it.build_planes(it.cur_sub)
+        it.step(it.t2)
+        other_ms = timed_steps(lambda timer: it.step(it.t2, timer), max(1, min(args.steps, 2))) / max(1, min(args.steps, 2))
+        args.w_mode = "refreshed" if other == "invariant" else "invariant"
+        it.ladder_ms.clear(); it.plane_ms.clear(); it.stage_events.clear()
+
+    # ---- e2e: T2 from pinned host memory through the plugin calls, residual back to pinned host memory
+    e2e_ms = 0.0
     if not args.no_e2e:
-        # every rank moves only ITS 1/world slice over PCIe; the full T2 is assembled over NVLink (NCCL all-gather) and
-        # each rank returns its slice of the residual -- h2d/d2h bytes below are the totals over all ranks
         nel = it.t2.numel()
-        per = -(-nel // world)
-        lo, hi = min(rank * per, nel), min((rank + 1) * per, nel)
-        h_t2 = torch.empty(per, dtype=torch.float64, pin_memory=True)
-        h_t2[: hi - lo].copy_(it.t2.view(-1)[lo:hi])
-        h_out = torch.empty(per, dtype=torch.float64, pin_memory=True)
-        d_slice = torch.zeros(per, dtype=torch.float64, device=device)
-        d_full = torch.empty(per * world, dtype=torch.float64, device=device)
-        sync_all()
-        t2timer = SegmentTimer(torch)
-        t2timer.resume()
-        for _ in range(args.steps):
-            d_slice.copy_(h_t2, non_blocking=True)
-            if world > 1:
-                dist.all_gather_into_tensor(d_full, d_slice)
-            else:
-                d_full = d_slice
-            it.step(d_full[:nel].view(it.t2.shape), t2timer)
-            h_out[: hi - lo].copy_(it.t2new.view(-1)[lo:hi], non_blocking=True)
-        t2timer.pause()
-        sync_all()
-        e2e_ms = t2timer.total_ms()
-        it.ladder_events.clear()
-        it.stage_events.clear()
+        if world == 1:
+            # exactly the calls fricc/friccsd.py makes: SparseTensor4d(host array) x2, contract_DTSpT x11
+            h_t2 = torch.empty(it.t2.shape, dtype=torch.float64, pin_memory=True)
+            h_t2.copy_(it.t2)
+            h_np = h_t2.numpy()
+            h_out = torch.empty(it.t2.shape, dtype=torch.float64, pin_memory=True)
+            draws = it.draws
+
+            def e2e_step(timer):
+                it.mark("begin")
+                d0, d1 = draws[it.draw_pos % 32:], draws[(it.draw_pos + 1) % 32:]
+                it.draw_pos += 2
+                sys_ = args.sampling == "systematic"
+                T = py_rccsd.SparseTensor4d(h_np, h_np.shape, m, "fri", args.sampling, False, draws=d0 if sys_ else None)
+                T_alt = py_rccsd.SparseTensor4d(h_np, h_np.shape, m, "fri", args.sampling, False, draws=d1 if sys_ else None)
+                it.mark("compress_x2")
+                it.contractions(T, T_alt, timer, plugin=True)
+                h_out.copy_(it.t2new, non_blocking=True)
+            h2d = 2 * nel * 8
+            d2h = nel * 8
+        else:
+            j0, cnt = fd.index_range(nel, rank, world)
+            h_t2 = torch.empty(cnt, dtype=torch.float64, pin_memory=True)
+            h_t2.copy_(it.t2.view(-1)[j0:j0 + cnt])
+            h_out = torch.empty(cnt, dtype=torch.float64, pin_memory=True)
+            d_slice = torch.empty(cnt, dtype=torch.float64, device=device)
+            pivotal_full = torch.empty(nel, dtype=torch.float64, device=device) if args.sampling != "systematic" else None
+
+            def e2e_step(timer):
+                it.mark("begin")
+                d_slice.copy_(h_t2, non_blocking=True)
+                full = None
+                if pivotal_full is not None:          # the pivotal walk needs the whole tensor: assemble it over NVLink
+                    sizes = [fd.index_range(nel, r, world)[1] for r in range(world)]
+                    dist.all_gather(list(pivotal_full.split(sizes)), d_slice)
+                    full = pivotal_full.view(it.t2.shape)
+                T, T_alt = it.compress_two(d_slice, j0, full=full)
+                it.mark("compress_x2")
+                it.contractions(T, T_alt, timer, plugin=True)
+                h_out.copy_(it.t2new.view(-1)[j0:j0 + cnt], non_blocking=True)
+            h2d = nel * 8
+            d2h = nel * 8
+        e2e_step(None)
+        e2e_ms = timed_steps(e2e_step, args.steps)
+        e2e_stage_ms = it.stage_breakdown(args.steps)
+        it.ladder_ms.clear(); it.plane_ms.clear()
+
+    # ---- compression-only sweep (config 5) at this GPU count, outside the timed regions
+    sweep = None
+    if not args.no_sweep:
+        it.Wlad = None
+        if it.planes is not None:
+            L.fricc_wslices_destroy(it.planes)
+            it.planes = None
+        torch.cuda.empty_cache()
+        sweep = compression_sweep(comm, device, torch, fd)
+
+    # ---- measured int8 peak on this device (rank 0, nothing else running)
+    peak_burst = peak_sust = None
+    if rank == 0 and it.tc:
+        p = ctypes.c_double(0.0)
+        _lib.check(L.fricc_int8_peak(0.02, ctypes.byref(p)))
+        peak_burst = p.value
+        _lib.check(L.fricc_int8_peak(1.5, ctypes.byref(p)))
+        peak_sust = p.value
+
     # ---- reduce over ranks (max of times, sum of launches)
-    stats = torch.tensor([ms, e2e_ms if not args.no_e2e else 0.0, float(launches)], dtype=torch.float64, device=device)
+    stats = torch.tensor([ms, e2e_ms, float(launches), other_ms or 0.0], dtype=torch.float64, device=device)
     if world > 1:
         mx = stats.clone()
         dist.all_reduce(mx, op=dist.ReduceOp.MAX)
         sm_ = stats.clone()
         dist.all_reduce(sm_, op=dist.ReduceOp.SUM)
-        ms, e2e_ms, launches = float(mx[0]), float(mx[1]), int(sm_[2])
+        ms, e2e_ms, launches, other_ms = float(mx[0]), float(mx[1]), int(sm_[2]), (float(mx[3]) if other_ms else None)
     if rank == 0:
-        import json as _json
-
         peaks = {}
         try:
-            peaks = _json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
         except Exception:
             pass
-        peak = float(peaks.get("hbm_gbs", 6650.0))
-        peak_kind = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
-        tc = it.planes > 0
-        if tc:
-            # dominant kernel: tc_sign_gemm_kernel on the ladder (int8 tensor cores).  Algorithmic work per launch:
-            # 2 * rows * cols * nK * planes int8 operations (the dense sign-matrix x digit-plane product, unpadded).
-            # Peak: int8 runs at twice the bf16 rate on B200 (4.5 vs 2.25 POP/s nominal), so 2 x the MEASURED cuBLAS bf16
-            # figure; the ladder launches sit inside a long step -> the sustained (power-capped) figure.
-            alg = [2.0 * lad.nR * c * lad.nK * it.planes for c in lad_cols]
-            ach = sum(alg) / (sum(lad_ms) * 1e-3) / 1e12 if lad_ms else 0.0
-            bf16 = float(peaks.get("bf16_tflops_sustained", 1400.0))
-            peak = 2.0 * bf16
-            peak_kind = ("2 x measured bf16_tflops_sustained (MEASURED_PEAKS.json); int8 = 2 x bf16 rate" if
-                         "bf16_tflops_sustained" in peaks else "2 x fallback 1400 TFLOP/s sustained bf16")
-            roof = {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
+        hbm = float(peaks.get("hbm_gbs", 6650.0))
+        hbm_kind = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
+        nK = v * v
+        lad_rows = o * o
+        if it.tc and lad_ms:
+            # dominant kernel: tc_sign_gemm_kernel (+ the fp64 remainder launch) on the ladder.  Work per launch: the dense
+            # sign-matrix x digit-plane product, 2 * rows * nK * cols * planes int8 operations (unpadded).  Peak: measured on
+            # this device in this run by fricc_int8_peak (back-to-back tcgen05.mma.kind::i8 on resident operands) -- the
+            # sustained figure, the kernel sits inside a long step.
+            alg = [2.0 * lad_rows * nK * c * args.planes for c in lad_cols]
+            ach = sum(alg) / (sum(lad_ms) * 1e-3) / 1e12
+            useful = sum(2.0 * m * c for c in lad_cols) / (sum(lad_ms) * 1e-3) / 1e12
+            roof = {"bound": "tensor", "achieved": ach, "peak": peak_sust, "unit": "TFLOP/s", "frac": ach / peak_sust,
                     "traffic": ncu_traffic_per_launch("tc_ladder"),
-                    "kernel": f"tc_sign_gemm_kernel (ladder 2323, int8 tcgen05.mma, {it.planes} digit planes)",
-                    "peak_source": peak_kind, "peak_burst": 2.0 * float(peaks.get("bf16_tflops", 1590.0)),
-                    "unit_note": "int8 TOP/s (2 x MAC)",
-                    "fp64_equivalent_algorithmic_gbs": sum(8.0 * m * c for c in lad_cols) / (sum(lad_ms) * 1e-3) / 1e9
-                    if lad_ms else None}
-        else:
-            # dominant kernel: spmm_rows_kernel on the ladder; algorithmic bytes per launch:
-            # 8*m*cols (one W row slice per nonzero) + 8*o^2*cols (one R2 write) + 12*m (packed entries)
+                    "kernel": f"tc_sign_gemm_kernel (ladder 2323, tcgen05.mma.kind::i8, {args.planes} digit planes)",
+                    "peak_source": "measured in this run: fricc_int8_peak, 1.5 s of back-to-back tcgen05.mma.kind::i8 "
+                                   "(M=128,N=256,K=32) on operands resident in shared memory, one CTA per SM (under the power cap)",
+                    "peak_burst": peak_burst, "peak_nominal_note": "2 x measured bf16_tflops_sustained = "
+                    f"{2.0 * float(peaks.get('bf16_tflops_sustained', 1400.0)):.0f}",
+                    "unit_note": "int8 TOP/s (2 x MAC) of the dense product = tensor-pipe utilisation",
+                    "useful_tflops_fp64_equivalent": useful,
+                    "useful_note": "2*m*cols fp64 FMA-equivalents per launch: the work the reference's loop nest does",
+                    "fp64_equivalent_algorithmic_gbs": sum(8.0 * m * c for c in lad_cols) / (sum(lad_ms) * 1e-3) / 1e9,
+                    "launches_timed": len(lad_ms), "avg_launch_ms": sum(lad_ms) / len(lad_ms),
+                    "algorithmic_per_launch": sum(alg) / len(alg)}
+        elif lad_ms:
             alg = [8.0 * m * c + 8.0 * o * o * c + 12.0 * m for c in lad_cols]
-            ach = sum(alg) / (sum(lad_ms) * 1e-3) / 1e9 if lad_ms else 0.0
-            roof = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+            ach = sum(alg) / (sum(lad_ms) * 1e-3) / 1e9
+            roof = {"bound": "hbm", "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm,
                     "traffic": ncu_traffic_per_launch("spmm_ladder"), "kernel": "spmm_rows_wide_kernel<2> (ladder 2323)",
-                    "peak_source": peak_kind}
-        roof.update(launches_timed=len(lad_ms), avg_launch_ms=(sum(lad_ms) / len(lad_ms)) if lad_ms else None,
-                    algorithmic_per_launch=(sum(alg) / len(alg)) if alg else None)
+                    "peak_source": hbm_kind, "launches_timed": len(lad_ms), "avg_launch_ms": sum(lad_ms) / len(lad_ms),
+                    "algorithmic_per_launch": sum(alg) / len(alg)}
+        else:
+            roof = None
         s_per_iter = ms * 1e-3 / args.steps
         line = {
-            "metric": METRIC, "value": s_per_iter, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "metric": metric_name(o, v, m), "value": s_per_iter, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": False, "scaling": "strong",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": workload_config(args, world),
-            "roofline": roof,
-            "clocks": clocks, "gpu_launches": int(launches),
-            "ladder_ms_per_step": sum(lad_ms) / args.steps, "stage_ms_per_step": stage_ms, "output_checksums": checks,
-            "schedule": ("single rank" if world == 1 else "blocking NCCL exchange per term" if args.no_overlap else
-                         "peer memory: each rank accumulates its columns in place and stores them into every peer's copy "
-                         "over NVLink" + (" on the compute stream" if args.push_inline else " on a side stream under the next term's kernel") +
-                         "; 3 stream-ordered barriers per step, no NCCL on the data path" if it.peer else
-                         "pipelined: NCCL all-gathers overlap the next term's kernel; 7 exchanges for 11 terms"),
+            "roofline": roof, "clocks": clocks, "gpu_launches": int(launches),
+            "ladder_ms_per_step": sum(lad_ms) / args.steps if lad_ms else None, "stage_ms_per_step": stage_ms,
+            "output_checksums": checks,
+            "schedule": ("single rank: plugin calls (py_rccsd.contract_DTSpT) on the full operands" if world == 1 else
+                         "plugin calls on L-slice views; each rank stores its finished slice into every peer's copy over "
+                         "NVLink" + (" on the compute stream" if args.push_inline else " on a side stream under the next term's kernel") +
+                         "; 3 " + ("NCCL 4-byte all-reduce" if args.nccl_barrier else "device-side flag") + " barriers per step, no NCCL on the data path"),
             "timed_segments": "whole steps" if it.resident else
-                              f"sum of segments; ladder W regenerated in HBM between {len(it.sub)} column sub-shards",
+                              f"sum of segments; the ladder's W is regenerated in HBM between {len(it.sub)} sub-shards (an input)",
         }
+        if other_ms is not None:
+            other = "invariant" if args.w_mode == "refreshed" else "refreshed"
+            line["value_by_w_mode"] = {args.w_mode: s_per_iter, other: other_ms * 1e-3}
+        if pl_ms:
+            palg = sum((8.0 + args.planes) * nK * c for c in pl_cols)
+            line["roofline_planes"] = {
+                "bound": "hbm", "kernel": "planes_fused_kernel (ladder operand -> int8 digit planes, single read)",
+                "achieved": palg / (sum(pl_ms) * 1e-3) / 1e9, "peak": hbm, "unit": "GB/s",
+                "frac": palg / (sum(pl_ms) * 1e-3) / 1e9 / hbm, "peak_source": hbm_kind,
+                "avg_launch_ms": sum(pl_ms) / len(pl_ms), "launches_timed": len(pl_ms),
+                "algorithmic_per_launch": palg / len(pl_ms), "traffic": ncu_traffic_per_launch("planes_fused")}
         line["config"]["ladder_subshards"] = len(it.sub)
         line["config"]["compression"] = {
             "ranges": "range-sharded: each rank scans its contiguous 1/N of T2, all-reduced key histograms, exact sums "
                       "carried rank to rank; norm, D and running sums shared by the step's two draws",
             "pair": "task-parallel: even ranks compute the first compression, odd ranks the second, entries broadcast",
             "replicated": "both compressions on every rank"}[it.compress_mode()]
-        line["config"]["precision"] = ("fp64 results: W expanded error-free into int8 digit planes (tail 2^-48 of each column's "
-                                       "largest element), exact int32 accumulation, fp64 recombination; measured max "
-                                       "deviation from the fp64 SpMM 7e-15 relative (profiles/tc_vs_fp64_r01_H_1gpu.jsonl)"
-                                       ) if tc else "fp64 FMA"
-        line["config"]["contraction_kernel"] = (f"int8 tensor cores, {it.planes} digit planes + fp64 remainder" if tc
-                                                else "fp64 bucketed SpMM")
-        if tc and it.plane_build_ms:
-            pb = [a.elapsed_time(b) for a, b in it.plane_build_ms]
-            line["ladder_plane_build_ms"] = {"per_build": sum(pb) / len(pb), "builds": len(pb),
-                                             "note": "untimed: re-encoding of the iteration-invariant ladder operand"}
+        line["config"]["precision"] = (
+            f"fp64 results via {args.planes}x8-bit block fixed point: each column of W (one power-of-two scale per column) is "
+            f"expanded into {args.planes} int8 digit planes, tail <= 2^-{8 * args.planes} of the column's largest element per "
+            "term, exact int32 accumulation, fp64 recombination; contraction parity <= 1e-10 relative (tests/test_plugin_tc_gpu.py, "
+            "incl. heavy-tailed W)") if it.tc else "fp64 FMA"
+        line["config"]["contraction_kernel"] = (f"int8 tensor cores, {args.planes} digit planes + fp64 remainder, chosen by "
+                                                f"fricc_contract's cost model ({tc_calls} of the timed plugin calls)"
+                                                if it.tc else "fp64 bucketed SpMM")
         if not args.no_e2e:
-            line["e2e"] = {"value": e2e_ms * 1e-3 / args.steps, "unit": UNIT,
-                           "h2d_bytes_per_step": int(it.t2.numel() * 8), "d2h_bytes_per_step": int(it.t2new.numel() * 8)}
+            line["e2e"] = {"value": e2e_ms * 1e-3 / args.steps, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+                           "d2h_bytes_per_step": int(d2h), "stage_ms_per_step": e2e_stage_ms,
+                           "through": ("plugin call: py_rccsd.SparseTensor4d(host T2) x2 + contract_DTSpT x11 (W and the "
+                                       "intermediates are device tensors), residual to pinned host memory" if world == 1 else
+                                       "each rank: its 1/N of T2 from pinned host memory, range-sharded compression, "
+                                       "py_rccsd.contract_DTSpT on L-slice views, its 1/N of the residual back")}
+        if sweep is not None:
+            line["compress_sweep"] = sweep
+        default_cfg = (o, v, m, args.sampling) == (40, 400, 10_000_000, "systematic") and args.planes == 6
+        if default_cfg and EXPECTED_T2NEW_CHECKSUM is not None:
+            rel = abs(checks["t2new"] - EXPECTED_T2NEW_CHECKSUM) / abs(EXPECTED_T2NEW_CHECKSUM)
+            line["t2new_checksum_vs_stored"] = {"rel_diff": rel, "ok": rel <= 1e-12}
+            assert rel <= 1e-9, f"t2new checksum {checks['t2new']!r} differs from the stored {EXPECTED_T2NEW_CHECKSUM!r}"
         if world == 1 and not args.no_cpu_baseline:
             r = cpu_reference_sample(o, v, m, args.sampling, os.cpu_count() or 1)
             line["cpu_baseline"] = {"value": r["extrapolated_s"], "unit": UNIT, "cores": r["cores"], "kind": r["kind"],
-                                    "sample": r["sample"]}
+                                    "sample": r["sample"], "same_config": r["same_config"]}
         print(json.dumps(line))
     if world > 1:
         dist.barrier()

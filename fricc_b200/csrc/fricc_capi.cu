@@ -648,6 +648,26 @@ int fricc_wslices_create_view(const double* W_dev, const int64_t w_shape[4], con
   FRICC_API_END
 }
 
+int fricc_wslices_update_view(fricc_wslices_t h, const double* W_dev, const int64_t w_shape[4], const int64_t w_strides[4],
+                              const char* term, int64_t l_begin) {
+  FRICC_API_BEGIN
+  if (!h || !W_dev || !w_shape || !w_strides) fail(FRICC_EINVAL, "null argument");
+  const TermSpec* ts = find_term(term);
+  if (!ts) fail(FRICC_EINVAL, "CASE NOT IMPLEMENTED: unknown contraction term '%s'", term ? term : "(null)");
+  const int64_t nL = w_shape[ts->wL[0]] * w_shape[ts->wL[1]];
+  if (l_begin < 0 || l_begin + h->ws.l_count > nL) fail(FRICC_EINVAL, "column range out of bounds");
+  if (w_shape[ts->wK[0]] * w_shape[ts->wK[1]] != h->ws.nK) fail(FRICC_EINVAL, "contracted pair does not match the planes");
+  wslices_build_view(h->ws, term_view(W_dev, w_shape, w_strides, *ts), l_begin, h->ws.l_count, h->ws.S);
+  FRICC_API_END
+}
+
+int fricc_int8_peak(double seconds, double* tops) {
+  FRICC_API_BEGIN
+  if (!tops || !(seconds > 0.0)) fail(FRICC_EINVAL, "bad arguments");
+  *tops = int8_peak_tops(seconds);
+  FRICC_API_END
+}
+
 int fricc_wslices_update(fricc_wslices_t h, const double* Wp_dev, int64_t ldw) {
   FRICC_API_BEGIN
   if (!h || !Wp_dev) fail(FRICC_EINVAL, "null argument");

@@ -277,7 +277,7 @@ __global__ void reconstruct_kernel(const int8_t* __restrict__ q, const double* _
 // one cluster barrier, and the digits are cut straight out of shared memory -- every element is read from HBM ONCE.
 // While the digits of column c are written, the freed chunks are already being refilled with column c + 1.
 // Traffic = 8 bytes read + S bytes written per element: the algorithmic minimum.
-constexpr int PF_THREADS = 256;
+constexpr int PF_THREADS = 512;     // 16 warps per SM: the digit cutting is issue-bound, not load-bound, at 8
 constexpr int PF_CHUNK = 2048;      // doubles per chunk (16 KB)
 constexpr int PF_MAX_CHUNKS = 13;   // 208 KB of the 227 KB
 
@@ -317,7 +317,7 @@ __global__ void __launch_bounds__(PF_THREADS, 1) planes_fused_kernel(const PfPar
   double* ring = reinterpret_cast<double*>(pf_smem);                                   // [n_chunks][PF_CHUNK]
   uint64_t* full = reinterpret_cast<uint64_t*>(pf_smem + (size_t)p.n_chunks * PF_CHUNK * 8);  // [n_chunks]
   unsigned long long* slots = reinterpret_cast<unsigned long long*>(full + PF_MAX_CHUNKS);   // [2][8] maxima of the cluster
-  unsigned long long* red = slots + 16;                                                // [8] warp maxima
+  unsigned long long* red = slots + 16;                                                // [16] warp maxima
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint32_t rank = ptx::cluster_ctarank();
   const int64_t cluster_id = blockIdx.x / p.C, n_clusters = gridDim.x / p.C;
@@ -405,23 +405,28 @@ __global__ void __launch_bounds__(PF_THREADS, 1) planes_fused_kernel(const PfPar
         const bool two = i4 + 2 < cnt;   // cnt is even: a tail of two is possible
         if (two) v23 = *reinterpret_cast<const double2*>(ring + off + i4 + 2);
         const double wv[4] = {v01.x, v01.y, v23.x, v23.y};
-        uint32_t pack[TC_MAX_SLICES];
-#pragma unroll
-        for (int s = 0; s < TC_MAX_SLICES; s++) pack[s] = 0;
+        uint32_t lo[4], hi[4];
 #pragma unroll
         for (int i = 0; i < 4; i++) {
           long long qi = 0;
           if (i < 2 || two) {
-            qi = (fast_scale ? llrint(wv[i] * mul) : llrint(scalbn(wv[i], sh))) + half;
+            qi = (fast_scale ? __double2ll_rn(wv[i] * mul) : llrint(scalbn(wv[i], sh))) + half;
             qi = qi > top ? top : (qi < 0 ? 0 : qi);
           }
-#pragma unroll
-          for (int s = 0; s < TC_MAX_SLICES; s++)
-            if (s < S) pack[s] |= (uint32_t)((qi >> (8 * (S - 1 - s))) & 255) << (8 * i);
+          lo[i] = (uint32_t)qi;
+          hi[i] = (uint32_t)((unsigned long long)qi >> 32);
         }
+        // plane s holds byte (S-1-s) of the digit string; one word = that byte of 4 consecutive K: three byte permutes
 #pragma unroll
-        for (int s = 0; s < TC_MAX_SLICES; s++)
-          if (s < S) *reinterpret_cast<uint32_t*>(qcol + (int64_t)s * TC_BN * p.Kpad + off + i4) = pack[s];
+        for (int s = 0; s < TC_MAX_SLICES; s++) {
+          if (s < S) {
+            const int j = S - 1 - s;
+            const uint32_t sel = (uint32_t)(j & 3) | ((uint32_t)(4 + (j & 3)) << 4);
+            const uint32_t t01 = j < 4 ? __byte_perm(lo[0], lo[1], sel) : __byte_perm(hi[0], hi[1], sel);
+            const uint32_t t23 = j < 4 ? __byte_perm(lo[2], lo[3], sel) : __byte_perm(hi[2], hi[3], sel);
+            *reinterpret_cast<uint32_t*>(qcol + (int64_t)s * TC_BN * p.Kpad + off + i4) = __byte_perm(t01, t23, 0x5410);
+          }
+        }
       }
       __syncthreads();  // every thread has read chunk j
       if (tid == 0 && next < p.l_count) {
@@ -458,7 +463,7 @@ static void planes_fused_build(WSlices& ws, const WView& w, int64_t l_begin) {
   p.segK = (int)(ceil_div(ceil_div(ws.nK, C), 16) * 16);
   p.n_chunks = (int)ceil_div(p.segK, PF_CHUNK);
   p.q = ws.q.p; p.expo = ws.expo.p; p.colscale = ws.colscale.p;
-  const size_t smem = (size_t)p.n_chunks * PF_CHUNK * 8 + PF_MAX_CHUNKS * 8 + 16 * 8 + 8 * 8;
+  const size_t smem = (size_t)p.n_chunks * PF_CHUNK * 8 + PF_MAX_CHUNKS * 8 + 16 * 8 + 16 * 8;
   static size_t attr_smem = 0;
   if (smem > attr_smem) {
     FRICC_CUDA(cudaFuncSetAttribute(planes_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
@@ -1116,6 +1121,79 @@ void set_tc_option(const char* key, int value) {
     g_tc_planes = value;
   } else if (strcmp(key, "tc_plane_cache") == 0) g_tc_plane_cache = value;
   else fail(FRICC_EINVAL, "unknown option '%s'", key);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// measured int8 peak: the roofline denominator of tc_sign_gemm_kernel, taken on the device the benchmark runs on
+// ---------------------------------------------------------------------------------------------------------------
+// One CTA per SM, A (128 x 128 B) and B (256 x 128 B) tiles resident in shared memory, one thread issuing
+// tcgen05.mma.kind::i8 M=128 N=256 K=32 back to back into two 256-column accumulators: no loads, no epilogue.
+__global__ void __launch_bounds__(128) int8_peak_kernel(int iters) {
+  extern __shared__ uint8_t peak_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(peak_raw) + 1023) & ~(uintptr_t)1023);
+  __shared__ uint64_t bar;
+  __shared__ uint32_t tmem_slot;
+  const int tid = threadIdx.x, warp = tid >> 5;
+  for (int i = tid; i < (128 + 256) * 128 / 4; i += 128) reinterpret_cast<uint32_t*>(smem)[i] = 0x01ff0201u * (uint32_t)(i + 1);
+  if (tid == 0) {
+    ptx::mbar_init(&bar, 1);
+    ptx::fence_barrier_init();
+  }
+  ptx::fence_proxy_async();
+  if (warp == 0) ptx::tmem_alloc(&tmem_slot, 512);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem = tmem_slot;
+  if (tid == 0) {
+    const uint32_t id = umma_idesc_i8(128, 256);
+    const uint64_t ad0 = umma_desc_sw128(ptx::smem_u32(smem)), bd0 = umma_desc_sw128(ptx::smem_u32(smem) + 128 * 128);
+    uint32_t parity = 0;
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        ptx::mma_i8(tmem, ad0 + 2 * k, bd0 + 2 * k, id, 1);
+        ptx::mma_i8(tmem + 256, ad0 + 2 * k, bd0 + 2 * k, id, 1);
+      }
+      if ((it & 15) == 15 || it == iters - 1) {  // bound the queue
+        ptx::mma_commit(&bar);
+        ptx::mbar_wait(&bar, parity);
+        parity ^= 1;
+      }
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem, 512);
+  }
+}
+
+double int8_peak_tops(double seconds) {
+  const size_t smem = (128 + 256) * 128 + 1024;
+  static bool attr = false;
+  if (!attr) {
+    FRICC_CUDA(cudaFuncSetAttribute(int8_peak_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr = true;
+  }
+  const int sms = num_sms();
+  cudaEvent_t e0, e1;
+  FRICC_CUDA(cudaEventCreate(&e0));
+  FRICC_CUDA(cudaEventCreate(&e1));
+  FRICC_LAUNCH(int8_peak_kernel, sms, 128, smem, 2000);  // warm-up
+  // 8 instructions of 128 clocks per iteration at ~1.9 GHz: ~0.54 us per iteration
+  const int iters = (int)std::max(2000.0, std::min(2.0e8, seconds / 0.54e-6));
+  FRICC_CUDA(cudaEventRecord(e0, stream()));
+  FRICC_LAUNCH(int8_peak_kernel, sms, 128, smem, iters);
+  FRICC_CUDA(cudaEventRecord(e1, stream()));
+  FRICC_CUDA(cudaEventSynchronize(e1));
+  float ms = 0.f;
+  FRICC_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  const double macs = (double)sms * iters * 8.0 * 128.0 * 256.0 * 32.0;
+  return 2.0 * macs / ((double)ms * 1e-3) / 1e12;
 }
 
 // CSR remainder x W read through a 4-D view (no panel): out[R, l] += scale * sum_e val_e * W[offK(K_e) + offL(l)].

@@ -37,6 +37,8 @@ void contract_dense(fricc_st* T, const TermSpec& ts, Layout& lay, const WSlices&
                     double* out_dev, const OutMap& om, double scale, bool overwrite = false);
 void spmm_csr_view(const int64_t* rowptr, const uint32_t* kidx, const double* vals, int64_t nR, const WView& w,
                    int64_t l_begin, int64_t l_count, double* out_dev, const OutMap& om, double scale);
+// int8 TOP/s of back-to-back tcgen05.mma.kind::i8 on resident operands, over a run of about `seconds`
+double int8_peak_tops(double seconds);
 int tc_mode();         // option "tc_mode": 0 never / 1 cost model / 2 always -- what fricc_contract does
 int tc_planes();       // option "tc_planes"
 int tc_plane_cache();  // option "tc_plane_cache"

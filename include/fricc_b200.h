@@ -210,6 +210,14 @@ int fricc_wslices_create(const double* Wp_dev, int64_t ldw, int64_t nK, int64_t 
  * ladder's native W[a,b,c,d] -- go through a cluster kernel that reads every element from HBM once.                  */
 int fricc_wslices_create_view(const double* W_dev, const int64_t w_shape[4], const int64_t w_strides[4], const char* term,
                               int64_t l_begin, int64_t l_count, int n_planes, fricc_wslices_t* out);
+/* re-expand in place (the operand changed, same shape and column count): what a driver that rebuilds W every iteration
+ * calls (fricc/friccsd.py:207,325-331)                                                                               */
+int fricc_wslices_update_view(fricc_wslices_t h, const double* W_dev, const int64_t w_shape[4], const int64_t w_strides[4],
+                              const char* term, int64_t l_begin);
+/* measured int8 tensor-core peak of the current device: back-to-back tcgen05.mma.kind::i8 (M=128, N=256, K=32) on
+ * operands resident in shared memory, one CTA per SM, for about `seconds` -> int8 TOP/s (2 x MAC).  bench.py's
+ * denominator for the tensor-core kernel's roofline (short run = burst clocks, seconds = under the power cap).        */
+int fricc_int8_peak(double seconds, double* tops);
 int fricc_wslices_update(fricc_wslices_t h, const double* Wp_dev, int64_t ldw); /* re-expand (W changed), same shape */
 /* out[.., l, ..] += scale * sum_K T[R,K] * W[K,l] for the columns l in [l_begin, l_begin + planes' l_count) with planes
  * the caller keeps (an operand that does not change between iterations: built once with fricc_wslices_create_view);
