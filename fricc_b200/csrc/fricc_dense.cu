@@ -27,6 +27,7 @@
 #include <cuda.h>  // CUtensorMap + enums only; the encoder is fetched with cudaGetDriverEntryPoint (no -lcuda)
 
 #include <algorithm>
+#include <cmath>
 
 namespace fricc {
 
@@ -56,6 +57,10 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
 }
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// arrive on a barrier of another CTA of the cluster (address from mapa)
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
   uint32_t ok;
@@ -108,6 +113,63 @@ __device__ __forceinline__ void mma_i8(uint32_t tmem_d, uint64_t adesc, uint64_t
 __device__ __forceinline__ void mma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
                : "memory");
+}
+// ---- CTA-pair (cta_group::2) forms ---------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+// shared::cluster address of `smem_addr` (a shared::cta address of this CTA) in CTA `rank` of the cluster
+__device__ __forceinline__ uint32_t mapa(uint32_t smem_addr, uint32_t rank) {
+  uint32_t a;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(a) : "r"(smem_addr), "r"(rank));
+  return a;
+}
+__device__ __forceinline__ void cluster_sync() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// TMA load into THIS CTA's shared memory whose bytes are counted on a barrier of the pair's leader CTA
+__device__ __forceinline__ void tma_load_2d_pair(void* smem_dst, const void* tm, uint32_t bar_cluster_addr, int32_t c0, int32_t c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(tm)), "r"(bar_cluster_addr), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_alloc_pair(uint32_t* slot, uint32_t cols) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(slot)), "r"(cols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_pair(uint32_t addr, uint32_t cols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
+}
+// D[tmem of both CTAs] (+)= A[256 rows: 128 from each CTA's smem] * B[N rows: N/2 from each CTA's smem], issued by the leader
+__device__ __forceinline__ void mma_i8_pair(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// arrive on the barrier at this shared-memory offset in BOTH CTAs of the pair once the MMAs issued so far have completed
+__device__ __forceinline__ void mma_commit_pair(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+               ::"r"(smem_u32(bar)), "h"((uint16_t)3)
+               : "memory");
+}
+__device__ __forceinline__ void red_add_f64(double* p, double v) {
+  asm volatile("red.relaxed.gpu.global.add.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory");
+}
+__device__ __forceinline__ int ld_acquire_gpu(const int* p) {
+  int v;
+  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void red_release_gpu_add(int* p, int v) {
+  asm volatile("red.release.gpu.global.add.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 // 32 lanes x 8 consecutive 32-bit columns -> 8 registers per thread (thread i of the warp <-> lane base+i)
 __device__ __forceinline__ void tmem_ld_x8(uint32_t taddr, int32_t (&r)[8]) {
@@ -291,11 +353,6 @@ struct PfParams {
 };
 
 namespace ptx {
-__device__ __forceinline__ uint32_t cluster_ctarank() {
-  uint32_t r;
-  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
-  return r;
-}
 __device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
 __device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
 // store a 64-bit value into the SAME shared-memory variable of CTA `rank` of this cluster
@@ -312,22 +369,81 @@ __device__ __forceinline__ void bulk_load_1d(void* smem_dst, const void* gsrc, u
 }
 }  // namespace ptx
 
+// digits of 4 consecutive K of one column -> one 32-bit word per plane.  S <= 6: the 8S-bit digit string is taken from the
+// mantissa of  fma(w, 2^sh, 2^52 + 2^(8S-1))  -- exact product, ONE rounding to the integer grid (ties to even, the same
+// result as llrint(scalbn(w, sh)) + 2^(8S-1)), no 64-bit conversion or clamp: the only value above the top code is
+// 2^(8S) itself (an element that rounds up to +2^e), and it becomes all-ones bytes.
+template <int S>
+__device__ __forceinline__ void cut4(const double (&wv)[4], double mul, int8_t* __restrict__ dst, int64_t plane_stride) {
+  uint32_t lo[4], hi[4];
+  if constexpr (S <= 6) {
+    const double magic = 4503599627370496.0 + (double)(1LL << (8 * S - 1));
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      const double x = fma(wv[i], mul, magic);
+      lo[i] = (uint32_t)__double2loint(x);
+      hi[i] = (uint32_t)__double2hiint(x);
+      const uint32_t ovf = S <= 3 ? (lo[i] >> (8 * S)) & 1u : (S == 4 ? hi[i] & 1u : (hi[i] >> (8 * S - 32)) & 1u);
+      const uint32_t m = 0u - ovf;
+      lo[i] |= m;
+      hi[i] |= m;
+    }
+  } else {
+    const long long half = 1LL << (8 * S - 1), top = (1LL << (8 * S)) - 1;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      long long qi = __double2ll_rn(wv[i] * mul) + half;
+      qi = qi > top ? top : (qi < 0 ? 0 : qi);
+      lo[i] = (uint32_t)qi;
+      hi[i] = (uint32_t)((unsigned long long)qi >> 32);
+    }
+  }
+  // plane s holds byte (S-1-s) of the digit string; one word = that byte of 4 consecutive K: three byte permutes
+#pragma unroll
+  for (int s = 0; s < S; s++) {
+    const int j = S - 1 - s;
+    const uint32_t sel = (uint32_t)(j & 3) | ((uint32_t)(4 + (j & 3)) << 4);
+    const uint32_t t01 = j < 4 ? __byte_perm(lo[0], lo[1], sel) : __byte_perm(hi[0], hi[1], sel);
+    const uint32_t t23 = j < 4 ? __byte_perm(lo[2], lo[3], sel) : __byte_perm(hi[2], hi[3], sel);
+    *reinterpret_cast<uint32_t*>(dst + (int64_t)s * plane_stride) = __byte_perm(t01, t23, 0x5410);
+  }
+}
+
+// columns whose scale 2^sh is not a normal double (|e| near the ends of the exponent range): same digits by scalbn
+template <int S>
+__device__ __noinline__ void cut4_slow(double w0, double w1, double w2, double w3, int sh, int8_t* __restrict__ dst,
+                                       int64_t plane_stride) {
+  const long long half = 1LL << (8 * S - 1), top = (1LL << (8 * S)) - 1;
+  const long long qi[4] = {digit_string(w0, sh, half, top), digit_string(w1, sh, half, top), digit_string(w2, sh, half, top),
+                           digit_string(w3, sh, half, top)};
+  for (int s = 0; s < S; s++) {
+    uint32_t word = 0;
+    for (int i = 0; i < 4; i++) word |= (uint32_t)((qi[i] >> (8 * (S - 1 - s))) & 255) << (8 * i);
+    *reinterpret_cast<uint32_t*>(dst + (int64_t)s * plane_stride) = word;
+  }
+}
+
+// The ring: PF_MAX_CHUNKS slots used as a FIFO over the CTA's chunk stream (column after column), so up to
+// PF_MAX_CHUNKS - n_chunks chunks of the NEXT column are already in flight while the current one is still being read
+// for its maximum, and every slot is refilled as soon as its digits are cut.
+template <int S>
 __global__ void __launch_bounds__(PF_THREADS, 1) planes_fused_kernel(const PfParams p) {
   extern __shared__ __align__(128) uint8_t pf_smem[];
-  double* ring = reinterpret_cast<double*>(pf_smem);                                   // [n_chunks][PF_CHUNK]
-  uint64_t* full = reinterpret_cast<uint64_t*>(pf_smem + (size_t)p.n_chunks * PF_CHUNK * 8);  // [n_chunks]
-  unsigned long long* slots = reinterpret_cast<unsigned long long*>(full + PF_MAX_CHUNKS);   // [2][8] maxima of the cluster
-  unsigned long long* red = slots + 16;                                                // [16] warp maxima
+  double* ring = reinterpret_cast<double*>(pf_smem);                                        // [PF_MAX_CHUNKS][PF_CHUNK]
+  uint64_t* full = reinterpret_cast<uint64_t*>(pf_smem + (size_t)PF_MAX_CHUNKS * PF_CHUNK * 8);  // [PF_MAX_CHUNKS]
+  unsigned long long* slots = reinterpret_cast<unsigned long long*>(full + PF_MAX_CHUNKS);  // [2][8] maxima of the cluster
+  unsigned long long* red = slots + 16;                                                     // [16] warp maxima
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint32_t rank = ptx::cluster_ctarank();
   const int64_t cluster_id = blockIdx.x / p.C, n_clusters = gridDim.x / p.C;
   const int64_t k_lo = (int64_t)rank * p.segK;
   const int64_t my_n = max((int64_t)0, min(p.nK, k_lo + p.segK) - k_lo);  // K held by this CTA (even)
-  const int S = p.S;
-  const long long half = 1LL << (8 * S - 1), top = (1LL << (8 * S)) - 1;
+  const int nc = (int)((my_n + PF_CHUNK - 1) / PF_CHUNK);                 // chunks per column in this CTA (<= PF_MAX_CHUNKS)
+  const int64_t plane_stride = (int64_t)TC_BN * p.Kpad;
+  const int64_t n_cols = cluster_id < p.l_count ? (p.l_count - cluster_id + n_clusters - 1) / n_clusters : 0;
 
   if (tid == 0) {
-    for (int j = 0; j < p.n_chunks; j++) ptx::mbar_init(&full[j], 1);
+    for (int j = 0; j < PF_MAX_CHUNKS; j++) ptx::mbar_init(&full[j], 1);
     ptx::fence_barrier_init();
   }
   __syncthreads();
@@ -335,34 +451,44 @@ __global__ void __launch_bounds__(PF_THREADS, 1) planes_fused_kernel(const PfPar
   ptx::cluster_arrive();
   ptx::cluster_wait();
 
-  auto issue = [&](int64_t col, int j) {  // thread 0: refill chunk j with this CTA's part of column `col`
-    const int64_t off = (int64_t)j * PF_CHUNK;
-    const int64_t cnt = min((int64_t)PF_CHUNK, my_n - off);
-    if (cnt <= 0) return;
-    const double* src = p.w.p + view_offL(p.w, p.l_begin + col) + k_lo + off;
-    ptx::mbar_expect_tx(&full[j], (uint32_t)(cnt * 8));
-    ptx::bulk_load_1d(ring + off, src, (uint32_t)(cnt * 8), &full[j]);
+  // producer state (thread 0): the next chunk to request = chunk iss_j of this CTA's iss_it-th column, into slot iss_slot
+  int64_t iss_it = 0;
+  int iss_j = 0, iss_slot = 0, in_flight = 0;   // in_flight: slots requested and not yet released by the cutting pass
+  auto pump = [&]() {
+    while (in_flight < PF_MAX_CHUNKS && iss_it < n_cols && nc > 0) {
+      const int64_t off = (int64_t)iss_j * PF_CHUNK;
+      const int64_t cnt = min((int64_t)PF_CHUNK, my_n - off);
+      const double* src = p.w.p + view_offL(p.w, p.l_begin + cluster_id + iss_it * n_clusters) + k_lo + off;
+      ptx::mbar_expect_tx(&full[iss_slot], (uint32_t)(cnt * 8));
+      ptx::bulk_load_1d(ring + (size_t)iss_slot * PF_CHUNK, src, (uint32_t)(cnt * 8), &full[iss_slot]);
+      in_flight++;
+      if (++iss_slot == PF_MAX_CHUNKS) iss_slot = 0;
+      if (++iss_j == nc) { iss_j = 0; iss_it++; }
+    }
   };
+  if (tid == 0) pump();
 
+  int slot0 = 0;        // slot of chunk 0 of the current column
+  uint32_t par0 = 0;    // its mbarrier phase parity
   int64_t col = cluster_id;
-  if (tid == 0 && col < p.l_count)
-    for (int j = 0; j < p.n_chunks; j++) issue(col, j);
-
-  for (uint32_t it = 0; col < p.l_count; col += n_clusters, it++) {
-    const uint32_t par = it & 1;
+  for (int64_t it = 0; it < n_cols; it++, col += n_clusters) {
+    const uint32_t par = (uint32_t)(it & 1);
     // ---- pass 1: largest magnitude of this CTA's part, chunk by chunk as the copies land
     unsigned long long mx = 0;
-    for (int j = 0; j < p.n_chunks; j++) {
-      const int64_t off = (int64_t)j * PF_CHUNK;
-      const int cnt = (int)min((int64_t)PF_CHUNK, my_n - off);
-      if (cnt <= 0) break;
-      ptx::mbar_wait(&full[j], par);
-      const double2* c2 = reinterpret_cast<const double2*>(ring + off);
-      for (int i = tid; i < cnt / 2; i += PF_THREADS) {
-        const double2 v = c2[i];
-        const unsigned long long a = abs_key(v.x), b = abs_key(v.y);
-        mx = a > mx ? a : mx;
-        mx = b > mx ? b : mx;
+    {
+      int sl = slot0;
+      uint32_t ph = par0;
+      for (int j = 0; j < nc; j++) {
+        const int cnt = (int)min((int64_t)PF_CHUNK, my_n - (int64_t)j * PF_CHUNK);
+        ptx::mbar_wait(&full[sl], ph);
+        const double2* c2 = reinterpret_cast<const double2*>(ring + (size_t)sl * PF_CHUNK);
+        for (int i = tid; i < cnt / 2; i += PF_THREADS) {
+          const double2 v = c2[i];
+          const unsigned long long a = abs_key(v.x), b = abs_key(v.y);
+          mx = a > mx ? a : mx;
+          mx = b > mx ? b : mx;
+        }
+        if (++sl == PF_MAX_CHUNKS) { sl = 0; ph ^= 1; }
       }
     }
     for (int o = 16; o > 0; o >>= 1) {
@@ -391,55 +517,42 @@ __global__ void __launch_bounds__(PF_THREADS, 1) planes_fused_kernel(const PfPar
     const int sh = 8 * S - 1 - e;
     const bool fast_scale = sh > -1000 && sh < 1000;
     const double mul = fast_scale ? ldexp(1.0, sh) : 0.0;  // exact power of two: w * mul == scalbn(w, sh)
-    // ---- pass 2: digits out of shared memory; chunk j is refilled with the next column as soon as it has been read
+    // ---- pass 2: digits out of shared memory; a slot is handed back to the producer as soon as it has been read
     const int64_t tile = col / TC_BN, c_in = col - tile * TC_BN;
-    int8_t* qcol = p.q + ((tile * S) * TC_BN + c_in) * p.Kpad + k_lo;  // plane s: + s * TC_BN * Kpad
-    const int64_t next = col + n_clusters;
-    for (int j = 0; j < p.n_chunks; j++) {
-      const int64_t off = (int64_t)j * PF_CHUNK;
-      const int cnt = (int)min((int64_t)PF_CHUNK, my_n - off);
-      if (cnt <= 0) break;
-      for (int i4 = tid * 4; i4 < cnt; i4 += PF_THREADS * 4) {
-        const double2 v01 = *reinterpret_cast<const double2*>(ring + off + i4);
-        double2 v23 = make_double2(0.0, 0.0);
-        const bool two = i4 + 2 < cnt;   // cnt is even: a tail of two is possible
-        if (two) v23 = *reinterpret_cast<const double2*>(ring + off + i4 + 2);
-        const double wv[4] = {v01.x, v01.y, v23.x, v23.y};
-        uint32_t lo[4], hi[4];
-#pragma unroll
-        for (int i = 0; i < 4; i++) {
-          long long qi = 0;
-          if (i < 2 || two) {
-            qi = (fast_scale ? __double2ll_rn(wv[i] * mul) : llrint(scalbn(wv[i], sh))) + half;
-            qi = qi > top ? top : (qi < 0 ? 0 : qi);
-          }
-          lo[i] = (uint32_t)qi;
-          hi[i] = (uint32_t)((unsigned long long)qi >> 32);
+    int8_t* qcol = p.q + ((tile * S) * TC_BN + c_in) * p.Kpad + k_lo;  // plane s: + s * plane_stride
+    {
+      int sl = slot0;
+      for (int j = 0; j < nc; j++) {
+        const int64_t off = (int64_t)j * PF_CHUNK;
+        const int cnt = (int)min((int64_t)PF_CHUNK, my_n - off);
+        const double* chunk = ring + (size_t)sl * PF_CHUNK;
+        const int i4 = tid * 4;
+        if (i4 < cnt) {
+          const double2 v01 = *reinterpret_cast<const double2*>(chunk + i4);
+          double2 v23 = make_double2(0.0, 0.0);
+          if (i4 + 2 < cnt) v23 = *reinterpret_cast<const double2*>(chunk + i4 + 2);   // cnt is even: a tail of two is possible
+          const double wv[4] = {v01.x, v01.y, v23.x, v23.y};
+          if (fast_scale) cut4<S>(wv, mul, qcol + off + i4, plane_stride);
+          else cut4_slow<S>(wv[0], wv[1], wv[2], wv[3], sh, qcol + off + i4, plane_stride);
         }
-        // plane s holds byte (S-1-s) of the digit string; one word = that byte of 4 consecutive K: three byte permutes
-#pragma unroll
-        for (int s = 0; s < TC_MAX_SLICES; s++) {
-          if (s < S) {
-            const int j = S - 1 - s;
-            const uint32_t sel = (uint32_t)(j & 3) | ((uint32_t)(4 + (j & 3)) << 4);
-            const uint32_t t01 = j < 4 ? __byte_perm(lo[0], lo[1], sel) : __byte_perm(hi[0], hi[1], sel);
-            const uint32_t t23 = j < 4 ? __byte_perm(lo[2], lo[3], sel) : __byte_perm(hi[2], hi[3], sel);
-            *reinterpret_cast<uint32_t*>(qcol + (int64_t)s * TC_BN * p.Kpad + off + i4) = __byte_perm(t01, t23, 0x5410);
-          }
+        __syncthreads();  // every thread has read the slot
+        if (tid == 0) {
+          ptx::fence_proxy_async();
+          in_flight--;
+          pump();
         }
-      }
-      __syncthreads();  // every thread has read chunk j
-      if (tid == 0 && next < p.l_count) {
-        ptx::fence_proxy_async();
-        issue(next, j);
+        if (++sl == PF_MAX_CHUNKS) sl = 0;
       }
     }
     // zero the K padding of this column's rows (the CTA that holds the end of the run)
     if (k_lo + my_n == p.nK && my_n > 0) {
       const int64_t pad0 = (p.nK + 3) & ~(int64_t)3;
       for (int64_t k = pad0 + tid * 4; k < p.Kpad; k += PF_THREADS * 4)
-        for (int s = 0; s < S; s++) *reinterpret_cast<uint32_t*>(qcol - k_lo + (int64_t)s * TC_BN * p.Kpad + k) = 0u;
+        for (int s = 0; s < S; s++) *reinterpret_cast<uint32_t*>(qcol - k_lo + (int64_t)s * plane_stride + k) = 0u;
     }
+    // advance the column's first slot / parity by nc positions of the FIFO
+    slot0 += nc;
+    if (slot0 >= PF_MAX_CHUNKS) { slot0 -= PF_MAX_CHUNKS; par0 ^= 1; }
   }
   // nobody may exit while a peer can still store into its shared memory
   ptx::cluster_arrive();
@@ -463,11 +576,16 @@ static void planes_fused_build(WSlices& ws, const WView& w, int64_t l_begin) {
   p.segK = (int)(ceil_div(ceil_div(ws.nK, C), 16) * 16);
   p.n_chunks = (int)ceil_div(p.segK, PF_CHUNK);
   p.q = ws.q.p; p.expo = ws.expo.p; p.colscale = ws.colscale.p;
-  const size_t smem = (size_t)p.n_chunks * PF_CHUNK * 8 + PF_MAX_CHUNKS * 8 + 16 * 8 + 16 * 8;
-  static size_t attr_smem = 0;
-  if (smem > attr_smem) {
-    FRICC_CUDA(cudaFuncSetAttribute(planes_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
-    attr_smem = 227 * 1024;
+  const size_t smem = (size_t)PF_MAX_CHUNKS * PF_CHUNK * 8 + PF_MAX_CHUNKS * 8 + 16 * 8 + 16 * 8;
+  typedef void (*PfKernel)(const PfParams);
+  static const PfKernel kernels[TC_MAX_SLICES] = {planes_fused_kernel<1>, planes_fused_kernel<2>, planes_fused_kernel<3>,
+                                                  planes_fused_kernel<4>, planes_fused_kernel<5>, planes_fused_kernel<6>,
+                                                  planes_fused_kernel<7>};
+  static bool attr_set[TC_MAX_SLICES] = {false, false, false, false, false, false, false};
+  const PfKernel kernel = kernels[p.S - 1];
+  if (!attr_set[p.S - 1]) {
+    FRICC_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
+    attr_set[p.S - 1] = true;
   }
   // the tail tiles' unused column slots carry exponent 0 / scale 2^-7 like the two-pass builder leaves them
   FRICC_LAUNCH(colexp_kernel, (unsigned)ceil_div(ws.n_tiles * TC_BN, 256), 256, 0, (const unsigned long long*)nullptr,
@@ -486,11 +604,11 @@ static void planes_fused_build(WSlices& ws, const WView& w, int64_t l_begin) {
   // persistent clusters: as many as can be co-resident (a cluster waiting for SMs would run its columns alone at the end)
   cfg.gridDim = dim3((unsigned)(num_sms() / C * C));
   int max_clusters = 0;
-  FRICC_CUDA(cudaOccupancyMaxActiveClusters(&max_clusters, planes_fused_kernel, &cfg));
+  FRICC_CUDA(cudaOccupancyMaxActiveClusters(&max_clusters, kernel, &cfg));
   if (max_clusters < 1) fail(FRICC_ECUDA, "planes_fused_kernel: no cluster of %d CTAs fits on this device", C);
   const int64_t n_clusters = std::min<int64_t>(max_clusters, ws.l_count);
   cfg.gridDim = dim3((unsigned)(n_clusters * C));
-  FRICC_CUDA(cudaLaunchKernelEx(&cfg, planes_fused_kernel, p));
+  FRICC_CUDA(cudaLaunchKernelEx(&cfg, kernel, p));
   check_launch("planes_fused_kernel");
 }
 
@@ -847,7 +965,7 @@ double dense_form(fricc_st* T, const TermSpec& ts, Layout& lay) {
 // the tensor-core kernel
 // ---------------------------------------------------------------------------------------------------------------
 struct TcParams {
-  int64_t nR, l_begin, l_count;
+  int64_t nR, Mpad, l_begin, l_count;
   int S, stages, nkb;
   int b_group;  // planes fetched by one TMA box (a divisor of S; the box of tmB is b_group * 64 rows)
   int m_tiles, n_tiles;
@@ -858,7 +976,134 @@ struct TcParams {
   double* out;
   OutMap om;
   int beta;  // 1: out += result (read-modify-write); 0: out = result (the caller knows out holds nothing yet)
+  int band;  // raster: row tiles are walked in bands of `band`; inside a band the column tile is the slow index (tc_tile)
+  int sync_shift, sync_lag;  // pair kernel's soft lockstep: a milestone every 2^sync_shift k-blocks, wait for the one sync_lag back
+  int debug; // measurement only ("tc_debug"): 1 = every CTA loads tile (0,0): all operand bytes come from L2 hits, results are garbage
 };
+
+// Tile order.  The CTAs (or CTA pairs) that run at the same time hold consecutive tile numbers, and every k-block they
+// pull one sign tile per distinct ROW tile and one plane tile per distinct COLUMN tile through L2.  Walking the row
+// tiles in bands of `band` (column tile slow inside a band) makes that concurrent set a band x P/band rectangle instead
+// of a P x 1 strip: for the O^3V^3 terms (63 row tiles of 256) 9 x 32 KB + 8 x 48 KB = 0.7 MB of distinct bytes per
+// k-block instead of 2 MB, and a band's sign rows (32 MB) stay in L2 while its column tiles stream by.
+__device__ __forceinline__ void tc_tile(int64_t t, int m_tiles, int n_tiles, int band, int& m_tile, int& n_tile) {
+  const int64_t per_band = (int64_t)band * n_tiles;
+  const int b = (int)(t / per_band);
+  const int64_t r = t - (int64_t)b * per_band;
+  const int mb = min(band, m_tiles - b * band);
+  n_tile = (int)(r / mb);
+  m_tile = b * band + (int)(r - (int64_t)n_tile * mb);
+}
+
+// ===== epilogue (8 warps, warp ids 2..9): TMEM -> fp64 recombination of the planes -> out =====
+// Shared by the one-CTA and the CTA-pair kernels: `rows_per_tile` rows of the sign matrix per tile of which this CTA's
+// TMEM lanes hold [row_off, row_off + 128); tmem_empty_cluster != 0: the "accumulators drained" barrier lives in the
+// pair's leader CTA and is reached through its shared::cluster address.
+__device__ __forceinline__ void tc_epilogue(const TcParams& p, uint32_t tmem_base, int warp, int lane, int64_t first_tile,
+                                            int64_t tile_stride, int m_tiles, int rows_per_tile, int row_off,
+                                            uint64_t* tmem_full, uint64_t* tmem_empty, uint32_t tmem_empty_cluster) {
+  const int S = p.S;
+  const int64_t total_tiles = (int64_t)m_tiles * p.n_tiles;
+  {
+  const int q = warp & 3;                // the TMEM lane quarter this warp may access
+  const int half = (warp - 2) >> 2;      // two warps per quarter: column chunks 0..3 | 4..7
+  const double coef = p.scale * p.cmag[0];
+  const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
+  uint32_t tl = 0;
+  for (int64_t t = first_tile; t < total_tiles; t += tile_stride, tl++) {
+    int m_tile, n_tile;
+    tc_tile(t, m_tiles, p.n_tiles, p.band, m_tile, n_tile);
+    const int64_t R = (int64_t)m_tile * rows_per_tile + row_off + q * 32 + lane;
+    const bool row_ok = R < p.nR;
+    int64_t rbase = 0;
+    if (row_ok) {
+      const int64_t r1 = R / p.om.nR2, r2 = R - r1 * p.om.nR2;
+      rbase = r1 * p.om.sR1 + r2 * p.om.sR2;
+    }
+    // first column of this warp's half of the tile, split into the (major, minor) pair of the free index
+    const int c_first = half * (TC_BN / 2);
+    const int64_t l_first = p.l_begin + (int64_t)n_tile * TC_BN + c_first;
+    int64_t l1 = l_first / p.om.nL2, l2 = l_first - l1 * p.om.nL2;
+    const int ncol = (int)min((int64_t)TC_BN, p.l_count - (int64_t)n_tile * TC_BN);
+    if (p.beta && row_ok) {
+      // read-modify-write: pull this thread's output elements towards L2 while the main loop runs
+      int64_t a1 = l1, a2 = l2;
+      for (int c = c_first; c < min(ncol, c_first + TC_BN / 2); c++) {
+        if (p.om.sL2 != 1 || (c & 3) == 0)
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(p.out + rbase + a1 * p.om.sL1 + a2 * p.om.sL2));
+        if (++a2 == p.om.nL2) { a2 = 0; a1++; }
+      }
+    }
+    const int off0 = R < p.Mpad ? 128 * p.rowsum[R] : 0;  // the 2^e_l offset, units of plane 0
+    ptx::mbar_wait(tmem_full, tl & 1);
+    ptx::tc_fence_after();
+    for (int j = half * 4; j < half * 4 + 4; j++) {
+      int32_t r[TC_MAX_SLICES][8];
+#pragma unroll
+      for (int s = 0; s < TC_MAX_SLICES; s++)
+        if (s < S) ptx::tmem_ld_x8(lane_addr + (uint32_t)(s * TC_BN + j * 8), r[s]);
+      ptx::tmem_ld_wait();
+      if (j == half * 4 + 3) {
+        // last read of this tile's accumulators by this warp: hand TMEM back to the MMA issuer
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) {
+          if (tmem_empty_cluster) ptx::mbar_arrive_cluster(tmem_empty_cluster);
+          else ptx::mbar_arrive(tmem_empty);
+        }
+      }
+      double v[8];
+#pragma unroll
+      for (int i = 0; i < 8; i++) {
+        double tt = 0.0;
+#pragma unroll
+        for (int s = TC_MAX_SLICES - 1; s >= 1; s--)
+          if (s < S) tt = (tt + (double)r[s][i]) * 0.00390625;
+        tt += (double)(r[0][i] - off0);
+        const double cs = (j * 8 + i < ncol) ? p.colscale[n_tile * TC_BN + j * 8 + i] : 0.0;
+        v[i] = coef * cs * tt;
+      }
+      double* o8 = p.out + rbase + l1 * p.om.sL1 + l2 * p.om.sL2;
+      const bool contiguous = p.om.sL2 == 1 && l2 + 8 <= p.om.nL2 && j * 8 + 8 <= ncol &&
+                              (reinterpret_cast<uintptr_t>(o8) & 15) == 0;
+      if (contiguous) {
+        if (row_ok) {
+          if (p.beta) {
+            // out += v: no other thread of this launch touches these elements and launches on one stream are ordered,
+            // so a reduction at L2 gives the bits of load-add-store without the warp waiting for the load
+#pragma unroll
+            for (int i = 0; i < 8; i++) ptx::red_add_f64(o8 + i, v[i]);
+          } else {
+            double2* o2 = reinterpret_cast<double2*>(o8);
+#pragma unroll
+            for (int i = 0; i < 4; i++) o2[i] = make_double2(v[2 * i], v[2 * i + 1]);
+          }
+        }
+        l2 += 8;
+        if (l2 == p.om.nL2) { l2 = 0; l1++; }
+      } else {
+        double* oe[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+          oe[i] = p.out + rbase + l1 * p.om.sL1 + l2 * p.om.sL2;
+          if (++l2 == p.om.nL2) { l2 = 0; l1++; }
+        }
+        if (row_ok) {
+          if (p.beta) {
+#pragma unroll
+            for (int i = 0; i < 8; i++)
+              if (j * 8 + i < ncol) ptx::red_add_f64(oe[i], v[i]);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 8; i++)
+              if (j * 8 + i < ncol) *oe[i] = v[i];
+          }
+        }
+      }
+    }
+  }
+  }
+}
 
 __global__ void __maxnreg__(128)  // 320 threads x 128 = 40 960 registers: leaves 24 576 for three 256-thread peer-store CTAs (fricc_peer.cu)
 tc_sign_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const TcParams p) {
@@ -910,8 +1155,9 @@ tc_sign_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const int bg = p.b_group, nb = S / p.b_group;           // planes per TMA box, boxes per stage
       const uint32_t box_bytes = (uint32_t)bg * TC_B_PLANE_BYTES;
       for (int64_t t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-        const int m_tile = (int)(t % p.m_tiles), n_tile = (int)(t / p.m_tiles);
-        const int32_t a_row = m_tile * TC_BM, b_row = n_tile * S * TC_BN;
+        int m_tile, n_tile;
+        tc_tile(t, p.m_tiles, p.n_tiles, p.band, m_tile, n_tile);
+        const int32_t a_row = p.debug ? 0 : m_tile * TC_BM, b_row = p.debug ? 0 : n_tile * S * TC_BN;
         int32_t kcol = 0;
         for (int kb = 0; kb < p.nkb; kb++, kcol += TC_BK) {
           if (wrapped) ptx::mbar_wait(&empty[st], ph);
@@ -971,110 +1217,183 @@ tc_sign_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
     __syncwarp();
   } else {
-    // ===== epilogue (8 warps): TMEM -> fp64 recombination of the planes -> out =====
-    const int q = warp & 3;                // the TMEM lane quarter this warp may access
-    const int half = (warp - 2) >> 2;      // two warps per quarter: column chunks 0..3 | 4..7
-    const double coef = p.scale * p.cmag[0];
-    const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
-    uint32_t tl = 0;
-    for (int64_t t = blockIdx.x; t < total_tiles; t += gridDim.x, tl++) {
-      const int m_tile = (int)(t % p.m_tiles), n_tile = (int)(t / p.m_tiles);
-      const int64_t R = (int64_t)m_tile * TC_BM + q * 32 + lane;
-      const bool row_ok = R < p.nR;
-      int64_t rbase = 0;
-      if (row_ok) {
-        const int64_t r1 = R / p.om.nR2, r2 = R - r1 * p.om.nR2;
-        rbase = r1 * p.om.sR1 + r2 * p.om.sR2;
-      }
-      // first column of this warp's half of the tile, split into the (major, minor) pair of the free index
-      const int c_first = half * (TC_BN / 2);
-      const int64_t l_first = p.l_begin + (int64_t)n_tile * TC_BN + c_first;
-      int64_t l1 = l_first / p.om.nL2, l2 = l_first - l1 * p.om.nL2;
-      const int ncol = (int)min((int64_t)TC_BN, p.l_count - (int64_t)n_tile * TC_BN);
-      if (p.beta && row_ok) {
-        // read-modify-write: pull this thread's output elements towards L2 while the main loop runs
-        int64_t a1 = l1, a2 = l2;
-        for (int c = c_first; c < min(ncol, c_first + TC_BN / 2); c++) {
-          if (p.om.sL2 != 1 || (c & 3) == 0)
-            asm volatile("prefetch.global.L2 [%0];" ::"l"(p.out + rbase + a1 * p.om.sL1 + a2 * p.om.sL2));
-          if (++a2 == p.om.nL2) { a2 = 0; a1++; }
-        }
-      }
-      const int off0 = 128 * p.rowsum[(int64_t)m_tile * TC_BM + q * 32 + lane];  // the 2^e_l offset, units of plane 0
-      ptx::mbar_wait(tmem_full, tl & 1);
-      ptx::tc_fence_after();
-      for (int j = half * 4; j < half * 4 + 4; j++) {
-        int32_t r[TC_MAX_SLICES][8];
-#pragma unroll
-        for (int s = 0; s < TC_MAX_SLICES; s++)
-          if (s < S) ptx::tmem_ld_x8(lane_addr + (uint32_t)(s * TC_BN + j * 8), r[s]);
-        ptx::tmem_ld_wait();
-        if (j == half * 4 + 3) {
-          // last read of this tile's accumulators by this warp: hand TMEM back to the MMA issuer
-          ptx::tc_fence_before();
-          __syncwarp();
-          if (lane == 0) ptx::mbar_arrive(tmem_empty);
-        }
-        double v[8];
-#pragma unroll
-        for (int i = 0; i < 8; i++) {
-          double tt = 0.0;
-#pragma unroll
-          for (int s = TC_MAX_SLICES - 1; s >= 1; s--)
-            if (s < S) tt = (tt + (double)r[s][i]) * 0.00390625;
-          tt += (double)(r[0][i] - off0);
-          const double cs = (j * 8 + i < ncol) ? p.colscale[n_tile * TC_BN + j * 8 + i] : 0.0;
-          v[i] = coef * cs * tt;
-        }
-        double* o8 = p.out + rbase + l1 * p.om.sL1 + l2 * p.om.sL2;
-        const bool contiguous = p.om.sL2 == 1 && l2 + 8 <= p.om.nL2 && j * 8 + 8 <= ncol &&
-                                (reinterpret_cast<uintptr_t>(o8) & 15) == 0;
-        if (contiguous) {
-          if (row_ok) {
-            double2* o2 = reinterpret_cast<double2*>(o8);
-            if (p.beta) {
-              double2 old[4];
-#pragma unroll
-              for (int i = 0; i < 4; i++) old[i] = o2[i];
-#pragma unroll
-              for (int i = 0; i < 4; i++) o2[i] = make_double2(old[i].x + v[2 * i], old[i].y + v[2 * i + 1]);
-            } else {
-#pragma unroll
-              for (int i = 0; i < 4; i++) o2[i] = make_double2(v[2 * i], v[2 * i + 1]);
-            }
-          }
-          l2 += 8;
-          if (l2 == p.om.nL2) { l2 = 0; l1++; }
-        } else {
-          double* oe[8];
-#pragma unroll
-          for (int i = 0; i < 8; i++) {
-            oe[i] = p.out + rbase + l1 * p.om.sL1 + l2 * p.om.sL2;
-            if (++l2 == p.om.nL2) { l2 = 0; l1++; }
-          }
-          if (row_ok) {
-            if (p.beta) {
-              double old[8];
-#pragma unroll
-              for (int i = 0; i < 8; i++) old[i] = (j * 8 + i < ncol) ? *oe[i] : 0.0;
-#pragma unroll
-              for (int i = 0; i < 8; i++)
-                if (j * 8 + i < ncol) *oe[i] = old[i] + v[i];
-            } else {
-#pragma unroll
-              for (int i = 0; i < 8; i++)
-                if (j * 8 + i < ncol) *oe[i] = v[i];
-            }
-          }
-        }
-      }
-    }
+    tc_epilogue(p, tmem_base, warp, lane, blockIdx.x, gridDim.x, p.m_tiles, TC_BM, 0, tmem_full, tmem_empty, 0u);
   }
   ptx::tc_fence_before();
   __syncthreads();
   if (warp == 1) {
     ptx::tc_fence_after();
     ptx::tmem_dealloc(tmem_base, TC_TMEM_COLS);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// the CTA-pair form (cta_group::2): two CTAs on the two SMs of a TPC share one 256-row tile
+// ---------------------------------------------------------------------------------------------------------------
+// Why: the one-CTA kernel is bound by SHARED-MEMORY bandwidth, not by the tensor pipe.  Per 128-deep k-block it has TMA
+// write 16 + 8 S KB and the MMAs read the same bytes back: 128 KB at S = 6 against 768 cycles of tensor work is
+// 171 B/clk, and the SM moves 128 B/clk -- the measured 69-70 % pipe utilisation at S = 6 (and the ~650-cycle k-block
+// at S = 3, where 80 KB / 128 B/clk = 640) is exactly that ratio (profiles/ncu_full_r02_*).  In a pair each CTA stages
+// its own 128 rows of the sign matrix but only HALF of the plane rows of every MMA (the hardware feeds both tensor
+// cores from both halves), so the k-block costs 2 x (16 + 4 S) = 80 KB of shared-memory traffic per SM: 104 B/clk.
+// It also halves what each SM pulls from L2 for the planes.
+//   rows:     tile = 256 rows; CTA rank r holds rows [256 m + 128 r, +128) in its TMEM lanes
+//   planes:   MMA 1 covers planes 0..3 (N = 64 min(S,4)), MMA 2 planes 4..S-1; CTA r stages rows [r N/2, (r+1) N/2) of each
+//   barriers: full[] lives in the leader (both CTAs' TMA bytes are counted there), empty[] / tmem_full are signalled in
+//             both CTAs by the leader's multicast commit, tmem_empty lives in the leader (2 x 8 epilogue warps arrive)
+// Soft lockstep (p.sync != nullptr): CTAs that share a plane tile (same column tile, different row tiles) or a sign
+// tile (same row tile) only find it in L2 if they walk K at the same pace; left alone they drift apart and the planes
+// are re-read from HBM (118 GB instead of 19 GB per launch in the first measurement).  Every 2^sync_shift k-blocks a
+// leader's producer counts itself in and waits -- bounded, then gives up for good -- until everybody has passed the
+// milestone sync_lag before: a hint for the cache, never a dependency.
+
+__global__ void __cluster_dims__(2, 1, 1) __maxnreg__(128)
+tc_sign_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB1,
+                         const __grid_constant__ CUtensorMap tmB2, const TcParams p, int* __restrict__ sync) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const int S = p.S, stages = p.stages;
+  const int n1 = min(S, 4) * TC_BN, n2 = (S - min(S, 4)) * TC_BN;
+  const uint32_t b1_bytes = (uint32_t)(n1 / 2) * TC_BK, b2_bytes = (uint32_t)(n2 / 2) * TC_BK;
+  const uint32_t stage_bytes = TC_A_BYTES + b1_bytes + b2_bytes;   // per CTA
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + (size_t)stages * stage_bytes);
+  uint64_t* empty = full + stages;
+  uint64_t* tmem_full = empty + stages;
+  uint64_t* tmem_empty = tmem_full + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 1);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = ptx::cluster_ctarank();
+  const bool leader = rank == 0;
+  const int64_t pair = blockIdx.x >> 1, npairs = gridDim.x >> 1;
+  const int m_tiles = p.m_tiles;     // 256-row tiles
+  const int64_t total_tiles = (int64_t)m_tiles * p.n_tiles;
+
+  if (threadIdx.x == 0) {
+    ptx::prefetch_tensormap(&tmA);
+    ptx::prefetch_tensormap(&tmB1);
+    if (n2 > 0) ptx::prefetch_tensormap(&tmB2);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int s = 0; s < stages; s++) {
+        ptx::mbar_init(&full[s], 1);
+        ptx::mbar_init(&empty[s], 1);
+      }
+      ptx::mbar_init(tmem_full, 1);
+      ptx::mbar_init(tmem_empty, 2 * TC_EPI_WARPS);
+      ptx::fence_barrier_init();
+    }
+    __syncwarp();
+    ptx::tmem_alloc_pair(tmem_slot, TC_TMEM_COLS);
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::cluster_sync();   // the peer's barriers exist before anything is signalled across the pair
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===== TMA producer (both CTAs): own 128 rows of A, own half of the plane rows of each MMA =====
+    if (lane == 0) {
+      const uint32_t full_leader = ptx::mapa(ptx::smem_u32(&full[0]), 0);
+      int st = 0;
+      uint32_t ph = 0;
+      bool wrapped = false;
+      int64_t gk = 0;                         // k-blocks issued by this CTA so far (all tiles)
+      bool sync_on = sync != nullptr && leader;
+      const int64_t full_rounds = total_tiles / npairs, rem = total_tiles % npairs;
+      for (int64_t t = pair; t < total_tiles; t += npairs) {
+        int m_tile, n_tile;
+        tc_tile(t, m_tiles, p.n_tiles, p.band, m_tile, n_tile);
+        const int32_t a_row = (p.debug ? 0 : m_tile * 2 * TC_BM) + (int32_t)rank * TC_BM;
+        const int32_t b_row0 = p.debug ? 0 : n_tile * S * TC_BN;
+        const int32_t b1_row = b_row0 + (int32_t)rank * (n1 / 2), b2_row = b_row0 + n1 + (int32_t)rank * (n2 / 2);
+        int32_t kcol = 0;
+        for (int kb = 0; kb < p.nkb; kb++, kcol += TC_BK, gk++) {
+          if (sync_on && (gk & ((1 << p.sync_shift) - 1)) == 0) {
+            const int64_t j = gk >> p.sync_shift;
+            ptx::red_release_gpu_add(sync + j, 1);
+            if (j >= p.sync_lag) {
+              const int64_t jj = j - p.sync_lag;
+              const int64_t round = (jj << p.sync_shift) / p.nkb;          // which of a pair's tiles milestone jj lies in
+              const int expected = (int)(round < full_rounds ? npairs : rem);
+              if (ptx::ld_acquire_gpu(sync + jj) < expected) {
+                const long long t0 = clock64();
+                while (ptx::ld_acquire_gpu(sync + jj) < expected) {
+                  if (clock64() - t0 > 200000) {  // ~0.1 ms: somebody is not running alongside us; stop waiting for good
+                    sync_on = false;
+                    break;
+                  }
+                }
+              }
+            }
+          }
+          if (wrapped) ptx::mbar_wait(&empty[st], ph);
+          uint8_t* a_dst = smem + (size_t)st * stage_bytes;
+          const uint32_t bar = full_leader + 8u * (uint32_t)st;
+          if (leader) ptx::mbar_expect_tx(&full[st], 2 * stage_bytes);
+          ptx::tma_load_2d_pair(a_dst, &tmA, bar, kcol, a_row);
+          ptx::tma_load_2d_pair(a_dst + TC_A_BYTES, &tmB1, bar, kcol, b1_row);
+          if (n2 > 0) ptx::tma_load_2d_pair(a_dst + TC_A_BYTES + b1_bytes, &tmB2, bar, kcol, b2_row);
+          if (++st == stages) {
+            st = 0;
+            if (wrapped) ph ^= 1;
+            wrapped = true;
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ===== MMA issuer: one thread of the leader CTA drives both tensor cores =====
+    if (leader && lane == 0) {
+      const uint32_t idesc1 = umma_idesc_i8(2 * TC_BM, n1), idesc2 = umma_idesc_i8(2 * TC_BM, n2 > 0 ? n2 : 32);
+      const uint64_t desc0 = umma_desc_sw128(ptx::smem_u32(smem));
+      const uint64_t stage_step = stage_bytes >> 4, b_off = TC_A_BYTES >> 4, b2_off = (TC_A_BYTES + b1_bytes) >> 4;
+      int st = 0;
+      uint32_t ph = 0;
+      uint64_t adesc0 = desc0;
+      uint32_t tl = 0;
+      for (int64_t t = pair; t < total_tiles; t += npairs, tl++) {
+        if (tl > 0) {  // both CTAs' epilogues must have read the previous tile's accumulators out of TMEM
+          ptx::mbar_wait(tmem_empty, (tl - 1) & 1);
+          ptx::tc_fence_after();
+        }
+        uint32_t acc = 0;
+        for (int kb = 0; kb < p.nkb; kb++) {
+          ptx::mbar_wait(&full[st], ph);
+          ptx::tc_fence_after();
+#pragma unroll
+          for (int k = 0; k < TC_BK / TC_UMMA_K; k++) {
+            const uint64_t adesc = adesc0 + (uint64_t)(k * (TC_UMMA_K >> 4));
+            ptx::mma_i8_pair(tmem_base, adesc, adesc + b_off, idesc1, acc);
+            if (n2 > 0) ptx::mma_i8_pair(tmem_base + 256, adesc, adesc + b2_off, idesc2, acc);
+            acc = 1;
+          }
+          ptx::mma_commit_pair(&empty[st]);
+          adesc0 += stage_step;
+          if (++st == stages) {
+            st = 0;
+            ph ^= 1;
+            adesc0 = desc0;
+          }
+        }
+        ptx::mma_commit_pair(tmem_full);
+      }
+    }
+    __syncwarp();
+  } else {
+    const uint32_t tmem_empty_leader = ptx::mapa(ptx::smem_u32(tmem_empty), 0);
+    tc_epilogue(p, tmem_base, warp, lane, pair, npairs, m_tiles, 2 * TC_BM, (int)rank * TC_BM, tmem_full, tmem_empty,
+                tmem_empty_leader);
+  }
+  // neither CTA may leave while the other can still touch its shared memory, barriers or TMEM
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::cluster_sync();
+  if (warp == 1) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc_pair(tmem_base, TC_TMEM_COLS);
   }
 }
 
@@ -1112,8 +1431,19 @@ static CUtensorMap make_map_i8(const int8_t* base, int64_t rows, int64_t Kpad, i
 }
 
 static int g_tc_persistent = 1;  // "tc_persistent" option: 1 = one CTA per SM looping over tiles, 0 = one CTA per tile
+static int g_tc_pair = 1;        // "tc_pair": 1 = CTA-pair kernel (cta_group::2, 256-row tiles), 0 = the one-CTA kernel
+static int g_tc_sync_shift = 2, g_tc_sync_lag = 2;  // "tc_sync_shift", "tc_sync_lag": granularity of the soft lockstep
+static int g_tc_band = 0;        // "tc_band": row tiles per raster band (0 = chosen from the tile sizes)
+static int g_tc_debug = 0;       // "tc_debug": measurement only, see TcParams::debug
+static int g_tc_lockstep = 1;    // "tc_lockstep": pair kernel's soft K-lockstep between the CTAs (an L2 hint)
 void set_tc_option(const char* key, int value) {
   if (strcmp(key, "tc_persistent") == 0) g_tc_persistent = value;
+  else if (strcmp(key, "tc_pair") == 0) g_tc_pair = value;
+  else if (strcmp(key, "tc_lockstep") == 0) g_tc_lockstep = value;
+  else if (strcmp(key, "tc_debug") == 0) g_tc_debug = value;
+  else if (strcmp(key, "tc_band") == 0) g_tc_band = std::max(0, value);
+  else if (strcmp(key, "tc_sync_shift") == 0) g_tc_sync_shift = std::max(0, std::min(value, 10));
+  else if (strcmp(key, "tc_sync_lag") == 0) g_tc_sync_lag = std::max(1, value);
   else if (strcmp(key, "tc_fused_planes") == 0) g_tc_fused_planes = value;
   else if (strcmp(key, "tc_mode") == 0) g_tc_mode = value;
   else if (strcmp(key, "tc_planes") == 0) {
@@ -1250,19 +1580,63 @@ void contract_dense(fricc_st* T, const TermSpec& ts, Layout& lay, const WSlices&
       FRICC_CUDA(cudaFuncSetAttribute(tc_sign_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
       attr_smem = 227 * 1024;
     }
-    const CUtensorMap tmA = make_map_i8(lay.dense.p, lay.Mpad, lay.Kpad, TC_BM);
-    const int b_group = S % 4 == 0 ? 4 : (S % 3 == 0 ? 3 : (S % 2 == 0 ? 2 : 1));  // box rows <= 256
-    const CUtensorMap tmB = make_map_i8(ws.q.p, ws.n_tiles * S * TC_BN, ws.Kpad, b_group * TC_BN);
     TcParams p;
-    p.b_group = b_group;
-    p.nR = lay.nR; p.l_begin = l_begin; p.l_count = ws.l_count;
-    p.S = S; p.stages = stages; p.nkb = (int)(lay.Kpad / TC_BK);
-    p.colscale = ws.colscale.p; p.rowsum = lay.rowsum.p; p.cmag = lay.cmag.p; p.scale = scale; p.out = out; p.om = om; p.beta = overwrite ? 0 : 1;
-    p.m_tiles = (int)(lay.Mpad / TC_BM);
+    p.nR = lay.nR; p.Mpad = lay.Mpad; p.l_begin = l_begin; p.l_count = ws.l_count;
+    p.S = S; p.nkb = (int)(lay.Kpad / TC_BK);
+    p.colscale = ws.colscale.p; p.rowsum = lay.rowsum.p; p.cmag = lay.cmag.p; p.scale = scale; p.out = out; p.om = om; p.beta = overwrite ? 0 : 1; p.debug = g_tc_debug; p.sync_shift = 4; p.sync_lag = 2;
     p.n_tiles = (int)ws.n_tiles;
-    const int64_t total = (int64_t)p.m_tiles * p.n_tiles;
-    const unsigned grid = (unsigned)(g_tc_persistent ? std::min<int64_t>(total, num_sms()) : total);
-    FRICC_LAUNCH(tc_sign_gemm_kernel, grid, TC_THREADS, smem, tmA, tmB, p);
+    const CUtensorMap tmA = make_map_i8(lay.dense.p, lay.Mpad, lay.Kpad, TC_BM);
+    const int sms = num_sms();
+    if (g_tc_pair && sms >= 2) {
+      // CTA pairs: 256-row tiles, each CTA stages half of the plane rows of each MMA
+      const int n1 = std::min(S, 4) * TC_BN, n2 = (S - std::min(S, 4)) * TC_BN;
+      const uint32_t pair_stage = TC_A_BYTES + (uint32_t)(n1 / 2 + n2 / 2) * TC_BK;
+      p.stages = (int)std::min<uint32_t>(8, (220u * 1024u) / pair_stage);
+      p.b_group = 0;
+      p.m_tiles = (int)ceil_div(lay.nR, 2 * TC_BM);
+      {  // band x (pairs / band) rectangle of concurrent tiles minimising band * 32 KB + (pairs / band) * 8 S KB
+        const double ideal = std::sqrt((double)(sms / 2) * (double)(n1 + n2) * TC_BK / (2.0 * TC_A_BYTES));
+        const int want = g_tc_band > 0 ? g_tc_band : std::max(1, (int)(ideal + 0.5));
+        const int nb = (int)ceil_div(p.m_tiles, want);
+        p.band = (int)ceil_div(p.m_tiles, nb);
+      }
+      const size_t psmem = (size_t)p.stages * pair_stage + 1024 + 256;
+      static bool attr_set = false;
+      if (!attr_set) {
+        FRICC_CUDA(cudaFuncSetAttribute(tc_sign_gemm_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
+        attr_set = true;
+      }
+      const CUtensorMap tmB1 = make_map_i8(ws.q.p, ws.n_tiles * S * TC_BN, ws.Kpad, n1 / 2);
+      const CUtensorMap tmB2 = n2 > 0 ? make_map_i8(ws.q.p, ws.n_tiles * S * TC_BN, ws.Kpad, n2 / 2) : tmB1;
+      const int64_t total = (int64_t)p.m_tiles * p.n_tiles;
+      const int64_t npairs = std::min<int64_t>(total, sms / 2);
+      DevBuf<int> sync;
+      int* sync_p = nullptr;
+      if (g_tc_lockstep && npairs > 1) {
+        const int64_t rounds = ceil_div(total, npairs);
+        p.sync_shift = g_tc_sync_shift;
+        p.sync_lag = g_tc_sync_lag;
+        sync.alloc((size_t)((rounds * p.nkb >> p.sync_shift) + 2));
+        sync.zero();
+        sync_p = sync.p;
+      }
+      FRICC_LAUNCH(tc_sign_gemm_pair_kernel, (unsigned)(2 * npairs), TC_THREADS, psmem, tmA, tmB1, tmB2, p, sync_p);
+    } else {
+      const int b_group = S % 4 == 0 ? 4 : (S % 3 == 0 ? 3 : (S % 2 == 0 ? 2 : 1));  // box rows <= 256
+      const CUtensorMap tmB = make_map_i8(ws.q.p, ws.n_tiles * S * TC_BN, ws.Kpad, b_group * TC_BN);
+      p.b_group = b_group;
+      p.stages = stages;
+      p.m_tiles = (int)(lay.Mpad / TC_BM);
+      {
+        const double ideal = std::sqrt((double)sms * (double)S * TC_B_PLANE_BYTES / (double)TC_A_BYTES);
+        const int want = g_tc_band > 0 ? g_tc_band : std::max(1, (int)(ideal + 0.5));
+        const int nb = (int)ceil_div(p.m_tiles, want);
+        p.band = (int)ceil_div(p.m_tiles, nb);
+      }
+      const int64_t total = (int64_t)p.m_tiles * p.n_tiles;
+      const unsigned grid = (unsigned)(g_tc_persistent ? std::min<int64_t>(total, sms) : total);
+      FRICC_LAUNCH(tc_sign_gemm_kernel, grid, TC_THREADS, smem, tmA, tmB, p);
+    }
   }
   if (lay.n_rest != 0)
     spmm_csr_view(lay.rest_rowptr.p, lay.rest_kidx.p, lay.rest_vals.p, lay.nR, w, l_begin, ws.l_count, out, om, scale);

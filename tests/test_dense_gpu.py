@@ -220,3 +220,34 @@ def test_false_provenance_hint_poisons_instead_of_lying(rccsd, port):
     port.contract("2323", st.panel.cpu().numpy().reshape(nv, nv, nv, nv).transpose(2, 3, 0, 1), fdup, vdup,
                   (no, no, nv, nv), want)
     assert np.abs(outd3.cpu().numpy() - want).max() <= TOL * np.abs(want).max()
+
+
+@pytest.mark.parametrize("term,no,nv", [("2323", 13, 17), ("1302", 6, 40), ("0312", 18, 23)])
+def test_pair_and_one_cta_kernels_agree_bitwise(rccsd, port, term, no, nv):
+    """tc_sign_gemm_pair_kernel (cta_group::2, 256-row tiles, soft lockstep) against tc_sign_gemm_kernel: the integer
+    accumulation is exact and the epilogue arithmetic is the same code, so the outputs must be the same BITS; both within
+    1e-10 of the oracle.  Shapes: rows % 256 in (128, 256) and in (0, 128), several row tiles, ragged column tiles."""
+    rng = np.random.default_rng(no * 100 + nv)
+    T, flat, vals, dims = _fri_tensor(rccsd, rng, no, nv, 0.3)
+    ext = {"o": no, "v": nv}
+    waxes, oaxes, _, _ = TERMS[term]
+    W = rng.random([ext[c] for c in waxes]) - 0.4
+    out0 = rng.random([ext[c] for c in oaxes])
+    want = out0.copy()
+    port.contract(term, W, flat, vals, dims, want)
+    got = {}
+    rccsd.set_option("tc_mode", 2)
+    try:
+        for pair, lockstep in ((0, 0), (1, 0), (1, 1)):
+            rccsd.set_option("tc_pair", pair)
+            rccsd.set_option("tc_lockstep", lockstep)
+            out = out0.copy()
+            rccsd.contract_DTSpT(W, T, out, term)
+            got[(pair, lockstep)] = out
+    finally:
+        rccsd.set_option("tc_mode", 1)
+        rccsd.set_option("tc_pair", 1)
+        rccsd.set_option("tc_lockstep", 1)
+    for k, out in got.items():
+        assert np.abs(out - want).max() <= TOL * max(1.0, np.abs(want).max()), k
+    assert np.array_equal(got[(0, 0)], got[(1, 0)]) and np.array_equal(got[(1, 0)], got[(1, 1)])

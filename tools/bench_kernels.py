@@ -29,7 +29,11 @@ def main():
     ap.add_argument("--planes", default="6,3,2")
     ap.add_argument("--reps", type=int, default=3)
     ap.add_argument("--skip-two-pass", action="store_true")
+    ap.add_argument("--debug", action="store_true", help="also time the kernels with every CTA loading tile 0 (L2-hit ceiling)")
+    ap.add_argument("--bands", default="0,1000,4", help="tc_band values for the O^3V^3 term (0 = automatic, 1000 = one band)")
+    ap.add_argument("--sync", default="4:2", help="lockstep variants shift:lag,...")
     a = ap.parse_args()
+    a.sync = [tuple(int(x) for x in v.split(":")) for v in a.sync.split(",") if v]
     import torch
 
     from fricc_b200 import _lib
@@ -103,13 +107,42 @@ def main():
             check(L.fricc_contract_planes(h, ptr(W), i64(W.shape), i64(W.stride()), 0, T._h, ptr(outv), i64(outv.shape),
                                           i64(outv.stride()), b"2323"))
 
-        ms = timed(gemm, a.reps)
         rows = o * o
         ops = 2.0 * rows * nK * cols * S
-        print(json.dumps({"kernel": "tc_sign_gemm_kernel + remainder", "planes": S, "rows": rows, "nK": nK, "cols": cols,
-                          "ms": round(ms, 3), "int8_tops_unpadded": round(ops / (ms * 1e-3) / 1e12, 1),
-                          "stage_bytes": 16384 + S * 8192, "mma_clk_per_kblock": 128 * S}), flush=True)
+        variants = [(0, 0, 0, 4, 2), (1, 0, 0, 4, 2)] + [(1, 1, 0, sh, lag) for sh, lag in a.sync]
+        if a.debug:
+            variants += [(0, 0, 1, 4, 2), (1, 0, 1, 4, 2)]
+        for pair, lock, dbg, sh, lag in variants:
+            check(L.fricc_set_option(b"tc_pair", pair))
+            check(L.fricc_set_option(b"tc_lockstep", lock))
+            check(L.fricc_set_option(b"tc_debug", dbg))
+            check(L.fricc_set_option(b"tc_sync_shift", sh))
+            check(L.fricc_set_option(b"tc_sync_lag", lag))
+            ms = timed(gemm, a.reps)
+            print(json.dumps({"kernel": ("tc_sign_gemm_pair_kernel" if pair else "tc_sign_gemm_kernel") + " + remainder",
+                              "lockstep": [lock, 1 << sh, lag], "all_ctas_load_tile_0": dbg, "planes": S, "rows": rows, "nK": nK, "cols": cols,
+                              "ms": round(ms, 3), "int8_tops_unpadded": round(ops / (ms * 1e-3) / 1e12, 1)}), flush=True)
+        check(L.fricc_set_option(b"tc_pair", 1))
+        check(L.fricc_set_option(b"tc_lockstep", 1))
+        check(L.fricc_set_option(b"tc_debug", 0))
+        check(L.fricc_set_option(b"tc_sync_shift", 2))
+        check(L.fricc_set_option(b"tc_sync_lag", 2))
         check(L.fricc_wslices_destroy(h))
+    del W, out
+    torch.cuda.empty_cache()
+    # an O^3V^3 term through the plugin call (planes + sign matrix + tensor-core kernel + remainder), per raster band
+    from fricc_b200 import py_rccsd
+    Wv = torch.rand(v, o, o, v, device=dev, dtype=torch.float64, generator=g)
+    tmp = torch.zeros(o, o, v, v, device=dev, dtype=torch.float64)
+    py_rccsd.set_option("tc_mode", 2)
+    for band in [int(x) for x in a.bands.split(",") if x]:
+        check(L.fricc_set_option(b"tc_band", band))
+        ms = timed(lambda: py_rccsd.contract_DTSpT(Wv, T, tmp, "1302"), a.reps)
+        ops = 2.0 * (o * v) ** 3 * 6
+        print(json.dumps({"term": "1302 via contract_DTSpT (planes + sign matrix + pair kernel + remainder)", "band": band,
+                          "ms": round(ms, 3), "int8_tops_unpadded": round(ops / (ms * 1e-3) / 1e12, 1)}), flush=True)
+    check(L.fricc_set_option(b"tc_band", 0))
+    py_rccsd.set_option("tc_mode", 1)
 
 
 if __name__ == "__main__":
