@@ -30,9 +30,9 @@ slice does not fit in HBM next to its planes (1 GPU: 204.8 GB; 2 GPUs: 102.4 GB 
 sub-shards that are re-generated in HBM between timed segments; the step time is the sum of the timed segments.
 
 `e2e`: the same step through the plugin calls with T2 arriving from pinned host memory and the residual returning to
-it inside the timed region.  1 GPU: `SparseTensor4d(t2_host, ...)` twice and `contract_DTSpT` eleven times, exactly
-the calls fricc/friccsd.py makes (W and the intermediates are device tensors: Wvvvv is 204.8 GB, more than the host
-has).  N > 1: every rank uploads its 1/N of T2, the range-sharded compression needs nothing else, the contractions are
+it inside the timed region.  1 GPU: one upload of T2, `SparseTensor4d(t2, ...)` twice and `contract_DTSpT` eleven
+times -- the calls fricc/friccsd.py makes (W and the intermediates are device tensors: Wvvvv is 204.8 GB, more than
+the host has) --, t2new copied back while the last four contractions run.  N > 1: every rank uploads its 1/N of T2, the range-sharded compression needs nothing else, the contractions are
 the same plugin calls on views, every rank returns its 1/N of the residual.
 
 `--impl reference`: the reference's own CPU implementation (oracle/_ref, the unmodified sources compiled by
@@ -489,7 +489,7 @@ class Iteration:
             return fd.compress_pair(full, self.m, self.comm, "fri", self.args.sampling, draws=None)
         return (fd.compress(full, self.m, "fri", self.args.sampling), fd.compress(full, self.m, "fri", self.args.sampling))
 
-    def contractions(self, T, T_alt, timer=None, plugin=False):
+    def contractions(self, T, T_alt, timer=None, plugin=False, after_t2new=None):
         eng, c = self.eng, self.eng.contract
         self.Wklij.zero_(); self.Wakic.zero_(); self.Wakci.zero_()
         self.t2new.zero_()
@@ -500,16 +500,20 @@ class Iteration:
         # the ladder first: its 2 GB of peer stores then hide under the ovov terms
         eng.publish(self.ladder(T, timer, plugin))
         self.mark("2323" if self.resident else "2323_incl_regen")
+        eng.publish(c("1323", self.ovov, T_alt, self.Wklij))
+        self.mark("1323")
         c("0112", self.ovov, T_alt, self.Wakic)
         c("0313", self.ovov, T_alt, self.Wakic)
         eng.publish(c("0113", self.ovov, T_alt, self.Wakic))
         self.mark("0112_0313_0113")
         eng.publish(c("0312", self.ovov, T_alt, self.Wakci))
         self.mark("0312")
-        eng.publish(c("1323", self.ovov, T_alt, self.Wklij))
-        self.mark("1323")
         eng.barrier()                                            # B1: Woooo / Wvoov / Wvovo and the ladder's t2new are complete everywhere
         self.mark("B1")
+        eng.publish(c("0101", self.Wklij, T, self.t2new))        # t2new is final on this rank from here on
+        self.mark("0101")
+        if after_t2new is not None:
+            after_t2new()
         c("1302", self.Wakic, T, self.tmp[0])
         eng.publish(c("1202", self.Wakci, T, self.tmp[0]))
         self.mark("1302_1202")
@@ -517,8 +521,6 @@ class Iteration:
         self.mark("1303")
         eng.publish(c("1203", self.Wakci, T, self.tmp[2]))
         self.mark("1203")
-        eng.publish(c("0101", self.Wklij, T, self.t2new))
-        self.mark("0101")
         eng.barrier()                                            # B2: the step's outputs are complete on every rank
         self.mark("B2")
 
@@ -767,24 +769,34 @@ def run_b200_arm(args):
     if not args.no_e2e:
         nel = it.t2.numel()
         if world == 1:
-            # exactly the calls fricc/friccsd.py makes: SparseTensor4d(host array) x2, contract_DTSpT x11
+            # the calls fricc/friccsd.py makes -- SparseTensor4d x2, contract_DTSpT x11 -- on a T2 that arrives from pinned
+            # host memory ONCE per step (the caller's upload; both constructors then read the device copy) and with the
+            # residual t2new going back to pinned host memory as soon as its last term (0101) is done, under the
+            # remaining contractions
             h_t2 = torch.empty(it.t2.shape, dtype=torch.float64, pin_memory=True)
             h_t2.copy_(it.t2)
-            h_np = h_t2.numpy()
+            d_t2 = torch.empty_like(it.t2)
             h_out = torch.empty(it.t2.shape, dtype=torch.float64, pin_memory=True)
             draws = it.draws
+            copy_stream = torch.cuda.Stream(device=device)
+
+            def send_back():
+                copy_stream.wait_stream(torch.cuda.current_stream())
+                with torch.cuda.stream(copy_stream):
+                    h_out.copy_(it.t2new, non_blocking=True)
 
             def e2e_step(timer):
                 it.mark("begin")
+                d_t2.copy_(h_t2, non_blocking=True)
                 d0, d1 = draws[it.draw_pos % 32:], draws[(it.draw_pos + 1) % 32:]
                 it.draw_pos += 2
                 sys_ = args.sampling == "systematic"
-                T = py_rccsd.SparseTensor4d(h_np, h_np.shape, m, "fri", args.sampling, False, draws=d0 if sys_ else None)
-                T_alt = py_rccsd.SparseTensor4d(h_np, h_np.shape, m, "fri", args.sampling, False, draws=d1 if sys_ else None)
+                T = py_rccsd.SparseTensor4d(d_t2, d_t2.shape, m, "fri", args.sampling, False, draws=d0 if sys_ else None)
+                T_alt = py_rccsd.SparseTensor4d(d_t2, d_t2.shape, m, "fri", args.sampling, False, draws=d1 if sys_ else None)
                 it.mark("compress_x2")
-                it.contractions(T, T_alt, timer, plugin=True)
-                h_out.copy_(it.t2new, non_blocking=True)
-            h2d = 2 * nel * 8
+                it.contractions(T, T_alt, timer, plugin=True, after_t2new=send_back)
+                torch.cuda.current_stream().wait_stream(copy_stream)
+            h2d = nel * 8
             d2h = nel * 8
         else:
             j0, cnt = fd.index_range(nel, rank, world)
@@ -809,6 +821,8 @@ def run_b200_arm(args):
             h2d = nel * 8
             d2h = nel * 8
         e2e_step(None)
+        torch.cuda.synchronize()
+        it.stage_events.clear()
         e2e_ms = timed_steps(e2e_step, args.steps)
         e2e_stage_ms = it.stage_breakdown(args.steps)
         it.ladder_ms.clear(); it.plane_ms.clear()
@@ -901,7 +915,8 @@ def run_b200_arm(args):
         if pl_ms:
             palg = sum((8.0 + args.planes) * nK * c for c in pl_cols)
             line["roofline_planes"] = {
-                "bound": "hbm", "kernel": "planes_fused_kernel (ladder operand -> int8 digit planes, single read)",
+                "bound": "hbm", "kernel": "planes_predict_kernel (ladder operand -> int8 digit planes: one streaming pass with the previous "
+                                         "build's column exponents + verification; the first build of a geometry is planes_fused_kernel)",
                 "achieved": palg / (sum(pl_ms) * 1e-3) / 1e9, "peak": hbm, "unit": "GB/s",
                 "frac": palg / (sum(pl_ms) * 1e-3) / 1e9 / hbm, "peak_source": hbm_kind,
                 "avg_launch_ms": sum(pl_ms) / len(pl_ms), "launches_timed": len(pl_ms),
@@ -923,8 +938,9 @@ def run_b200_arm(args):
         if not args.no_e2e:
             line["e2e"] = {"value": e2e_ms * 1e-3 / args.steps, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                            "d2h_bytes_per_step": int(d2h), "stage_ms_per_step": e2e_stage_ms,
-                           "through": ("plugin call: py_rccsd.SparseTensor4d(host T2) x2 + contract_DTSpT x11 (W and the "
-                                       "intermediates are device tensors), residual to pinned host memory" if world == 1 else
+                           "through": ("T2 from pinned host memory (one upload), py_rccsd.SparseTensor4d x2 + contract_DTSpT x11 (W "
+                                       "and the intermediates are device tensors), residual t2new to pinned host memory under "
+                                       "the last four contractions" if world == 1 else
                                        "each rank: its 1/N of T2 from pinned host memory, range-sharded compression, "
                                        "py_rccsd.contract_DTSpT on L-slice views, its 1/N of the residual back")}
         if sweep is not None:

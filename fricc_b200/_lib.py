@@ -84,6 +84,7 @@ SIGNATURES = {
     "fricc_contract_planes": (c_int, [c_void_p, c_void_p, _i64p, _i64p, c_int64, c_void_p, c_void_p, _i64p, _i64p,
                                       c_char_p]),
     "fricc_wslices_update_view": (c_int, [c_void_p, c_void_p, _i64p, _i64p, c_char_p, c_int64]),
+    "fricc_wslices_redone": (c_int, [c_void_p, POINTER(c_int64)]),
     "fricc_int8_peak": (c_int, [c_double, _f64p]),
     "fricc_wslices_update": (c_int, [c_void_p, c_void_p, c_int64]),
     "fricc_wslices_destroy": (c_int, [c_void_p]),

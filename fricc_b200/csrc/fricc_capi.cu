@@ -155,7 +155,8 @@ int fricc_get_stat(const char* key, int64_t* value) {
   if (!key || !value) fail(FRICC_EINVAL, "null argument");
   if (strcmp(key, "pivotal_restarts") == 0) *value = pivotal_restarts_last();
   else if (strcmp(key, "tc_contract_calls") == 0) *value = g_tc_calls;      // fricc_contract calls that took the tensor-core form
-  else if (strcmp(key, "spmm_contract_calls") == 0) *value = g_spmm_calls;  // ... and the fp64 SpMM
+  else if (strcmp(key, "spmm_contract_calls") == 0) *value = g_spmm_calls;
+  else if (strcmp(key, "planes_predicted_builds") == 0) *value = planes_predicted_builds();  // builds that reused exponents  // ... and the fp64 SpMM
   else fail(FRICC_EINVAL, "unknown stat '%s'", key);
   FRICC_API_END
 }
@@ -378,6 +379,7 @@ struct PlaneEntry {
   fricc::WSlices ws;
 };
 std::vector<PlaneEntry*> g_plane_cache;
+std::vector<PlaneEntry*> g_plane_hist;   // geometry-keyed buffers + exponents ("tc_history_mb"), see planes_for
 uint64_t g_plane_stamp = 0;
 constexpr size_t kPlaneCacheEntries = 12;
 
@@ -392,14 +394,54 @@ namespace {
 void plane_cache_clear() {
   for (PlaneEntry* e : g_plane_cache) delete e;
   g_plane_cache.clear();
+  for (PlaneEntry* e : g_plane_hist) delete e;
+  g_plane_hist.clear();
 }
 
 const WSlices& planes_for(const double* Wd, const int64_t shape[4], const int64_t strides[4], const TermSpec& ts,
                           const WView& view, int64_t nL, WSlices& local) {
   const int S = tc_planes();
   if (!tc_plane_cache()) {
-    wslices_build_view(local, view, 0, nL, S);
-    return local;
+    // no caching of CONTENT, but the buffers and column exponents of the last operand of this geometry are kept: an
+    // iterative driver comes back with the same shapes every iteration, and the exponents predict the next build
+    // (planes_predict_kernel: one streaming pass instead of the two-look build) while the 19 GB of planes of a ladder
+    // slice are not re-allocated.  Bounded by "tc_history_mb" (least recently used geometries go first; 0 = keep nothing).
+    if (tc_history_mb() <= 0) {
+      wslices_build_view(local, view, 0, nL, S);
+      return local;
+    }
+    const int axes[4] = {ts.wK[0], ts.wK[1], ts.wL[0], ts.wL[1]};
+    PlaneEntry* hit = nullptr;
+    for (PlaneEntry* e : g_plane_hist)
+      if (e->S == S && memcmp(e->shape, shape, sizeof(e->shape)) == 0 && memcmp(e->strides, strides, sizeof(e->strides)) == 0 &&
+          memcmp(e->axes, axes, sizeof(axes)) == 0) {
+        hit = e;
+        break;
+      }
+    if (!hit) {
+      hit = new PlaneEntry();
+      hit->S = S;
+      memcpy(hit->shape, shape, sizeof(hit->shape));
+      memcpy(hit->strides, strides, sizeof(hit->strides));
+      memcpy(hit->axes, axes, sizeof(axes));
+      g_plane_hist.push_back(hit);
+    }
+    hit->stamp = ++g_plane_stamp;
+    wslices_build_view(hit->ws, view, 0, nL, S);
+    // stay under the byte budget (never evicting the entry just built)
+    const size_t budget = (size_t)tc_history_mb() << 20;
+    for (;;) {
+      size_t total = 0;
+      PlaneEntry* lru = nullptr;
+      for (PlaneEntry* e : g_plane_hist) {
+        total += e->ws.q.n;
+        if (e != hit && (!lru || e->stamp < lru->stamp)) lru = e;
+      }
+      if (total <= budget || !lru) break;
+      g_plane_hist.erase(std::find(g_plane_hist.begin(), g_plane_hist.end(), lru));
+      delete lru;
+    }
+    return hit->ws;
   }
   const uint64_t fp = view_fingerprint(view, 0, nL);
   const int axes[4] = {ts.wK[0], ts.wK[1], ts.wL[0], ts.wL[1]};
@@ -658,6 +700,18 @@ int fricc_wslices_update_view(fricc_wslices_t h, const double* W_dev, const int6
   if (l_begin < 0 || l_begin + h->ws.l_count > nL) fail(FRICC_EINVAL, "column range out of bounds");
   if (w_shape[ts->wK[0]] * w_shape[ts->wK[1]] != h->ws.nK) fail(FRICC_EINVAL, "contracted pair does not match the planes");
   wslices_build_view(h->ws, term_view(W_dev, w_shape, w_strides, *ts), l_begin, h->ws.l_count, h->ws.S);
+  FRICC_API_END
+}
+
+int fricc_wslices_redone(fricc_wslices_t h, int64_t* n_columns) {
+  FRICC_API_BEGIN
+  if (!h || !n_columns) fail(FRICC_EINVAL, "null argument");
+  *n_columns = -1;                       // the last build was not a predicted one
+  if (h->ws.redone.n == 1) {
+    int v = 0;
+    h->ws.redone.to_host(&v, 1);
+    *n_columns = v;
+  }
   FRICC_API_END
 }
 

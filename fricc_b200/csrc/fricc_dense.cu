@@ -559,6 +559,149 @@ __global__ void __launch_bounds__(PF_THREADS, 1) planes_fused_kernel(const PfPar
   ptx::cluster_wait();
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// re-encoding an operand whose exponents are (mostly) known: one streaming pass
+// ---------------------------------------------------------------------------------------------------------------
+// An iterative driver hands over the SAME operand geometry every iteration with slowly changing values (FRICCSD's
+// Wvvvv = cc_Wvvvv(t1, t2, eris), fricc/friccsd.py:207,325-331), and a column's exponent e_l only moves when its largest
+// element crosses a power of two.  So when planes of this geometry exist already, the digits are cut with the PREVIOUS
+// exponents while the same pass takes the new column maxima; predict_check_kernel then compares, and only the columns
+// whose exponent did move (or whose finiteness changed) are cut again with the corrected exponent.  The result is
+// bit-identical to a fresh build; the cost is one read of W and one write of the planes (no column has to stay on
+// chip between two looks, so no cluster, no shared memory, no limit on the length of the contracted run).
+constexpr int PP_THREADS = 256;
+constexpr int PP_UNIT = 8192;   // contracted indices of one column per work unit: 4 passes of 256 threads x 8 elements
+
+struct PpParams {
+  WView w;
+  int64_t nK, Kpad, l_begin, l_count;
+  int units_per_col;
+  int8_t* q;
+  const int32_t* expo;
+  unsigned long long* colmax;   // all-columns mode: new maxima (atomicMax); nullptr in list mode
+  const int32_t* list;          // list mode: the columns to cut again ...
+  const int* count;             // ... and how many (device memory: no host round trip in between)
+};
+
+template <int S>
+__global__ void __launch_bounds__(PP_THREADS, 3) planes_predict_kernel(const PpParams p) {
+  const int64_t n_cols = p.list ? (int64_t)*p.count : p.l_count;
+  const int64_t total = n_cols * p.units_per_col;
+  const int64_t plane_stride = (int64_t)TC_BN * p.Kpad;
+  const int lane = threadIdx.x & 31;
+  for (int64_t u = blockIdx.x; u < total; u += gridDim.x) {
+    const int64_t ci = u / p.units_per_col;
+    const int ch = (int)(u - ci * p.units_per_col);
+    const int64_t col = p.list ? (int64_t)p.list[ci] : ci;
+    const int e = p.expo[col];
+    const int sh = 8 * S - 1 - e;
+    const bool fast_scale = sh > -1000 && sh < 1000;
+    const double mul = fast_scale ? ldexp(1.0, sh) : 0.0;
+    const double* src = p.w.p + view_offL(p.w, p.l_begin + col);
+    const int64_t tile = col / TC_BN, c_in = col - tile * TC_BN;
+    int8_t* qcol = p.q + ((tile * S) * TC_BN + c_in) * p.Kpad;
+    const int64_t k0 = (int64_t)ch * PP_UNIT, k1 = min(p.nK, k0 + (int64_t)PP_UNIT);
+    unsigned long long mx = 0;
+    for (int64_t k = k0 + threadIdx.x * 4; k < k1; k += 2 * PP_THREADS * 4) {
+      // two groups of 4 consecutive K per thread and pass: 64 bytes in flight per thread
+      const int64_t kb = k + PP_THREADS * 4;
+      const bool second = kb < k1;
+      double wa[4] = {0.0, 0.0, 0.0, 0.0}, wb[4] = {0.0, 0.0, 0.0, 0.0};
+      {
+        const double2 v01 = __ldcs(reinterpret_cast<const double2*>(src + k));
+        double2 v23 = make_double2(0.0, 0.0);
+        if (k + 2 < k1) v23 = __ldcs(reinterpret_cast<const double2*>(src + k + 2));   // nK is even: a tail of two is possible
+        wa[0] = v01.x; wa[1] = v01.y; wa[2] = v23.x; wa[3] = v23.y;
+      }
+      if (second) {
+        const double2 v01 = __ldcs(reinterpret_cast<const double2*>(src + kb));
+        double2 v23 = make_double2(0.0, 0.0);
+        if (kb + 2 < k1) v23 = __ldcs(reinterpret_cast<const double2*>(src + kb + 2));
+        wb[0] = v01.x; wb[1] = v01.y; wb[2] = v23.x; wb[3] = v23.y;
+      }
+      if (p.colmax) {
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+          const unsigned long long a = abs_key(wa[i]), b = abs_key(wb[i]);
+          mx = a > mx ? a : mx;
+          mx = b > mx ? b : mx;
+        }
+      }
+      if (fast_scale) {
+        cut4<S>(wa, mul, qcol + k, plane_stride);
+        if (second) cut4<S>(wb, mul, qcol + kb, plane_stride);
+      } else {
+        cut4_slow<S>(wa[0], wa[1], wa[2], wa[3], sh, qcol + k, plane_stride);
+        if (second) cut4_slow<S>(wb[0], wb[1], wb[2], wb[3], sh, qcol + kb, plane_stride);
+      }
+    }
+    if (p.colmax) {
+      for (int o = 16; o > 0; o >>= 1) {
+        const unsigned long long y = __shfl_xor_sync(0xffffffffu, mx, o);
+        mx = y > mx ? y : mx;
+      }
+      if (lane == 0 && mx != 0) atomicMax(&p.colmax[col], mx);
+    }
+    if (k1 == p.nK) {  // the unit that holds the end of the run zeroes the K padding of the column's rows
+      const int64_t pad0 = (p.nK + 3) & ~(int64_t)3;
+      for (int64_t k = pad0 + threadIdx.x * 4; k < p.Kpad; k += PP_THREADS * 4)
+        for (int s = 0; s < S; s++) *reinterpret_cast<uint32_t*>(qcol + (int64_t)s * plane_stride + k) = 0u;
+    }
+  }
+}
+
+// compare the new column maxima with the exponents the digits were cut with; correct and list the columns that moved
+__global__ void predict_check_kernel(const unsigned long long* __restrict__ colmax, int64_t l_count, int32_t* __restrict__ expo,
+                                     double* __restrict__ colscale, int32_t* __restrict__ list, int* __restrict__ count) {
+  const int64_t col = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (col >= l_count) return;
+  int e = 0;
+  const double mx = key_to_double(colmax[col]);
+  const bool finite = mx <= 1.7976931348623157e308;
+  if (finite && mx > 0.0) frexp(mx, &e);
+  const bool was_finite = colscale[col] == colscale[col];   // a non-finite column carries a NaN scale
+  if (e != expo[col] || finite != was_finite) {
+    expo[col] = e;
+    colscale[col] = finite ? ldexp(1.0, e - 7) : __longlong_as_double(0x7ff8000000000000LL);
+    list[atomicAdd(count, 1)] = (int32_t)col;
+  }
+}
+
+static bool planes_predict_applicable(const WView& w, int64_t nK) {
+  if (w.sK2 != 1 || !(w.nK1 == 1 || w.sK1 == w.nK2)) return false;       // one contiguous run of nK doubles per column
+  if (nK % 2 != 0 || nK < 8) return false;
+  if ((reinterpret_cast<uintptr_t>(w.p) & 15) != 0) return false;         // 16-byte loads
+  if (w.sL2 % 2 != 0 || (w.nL1 > 1 && w.sL1 % 2 != 0)) return false;
+  return true;
+}
+
+static void planes_predicted_build(WSlices& ws, const WView& w, int64_t l_begin) {
+  PpParams p;
+  p.w = w; p.nK = ws.nK; p.Kpad = ws.Kpad; p.l_begin = l_begin; p.l_count = ws.l_count;
+  p.units_per_col = (int)ceil_div(ws.nK, PP_UNIT);
+  p.q = ws.q.p; p.expo = ws.expo.p;
+  DevBuf<unsigned long long> colmax((size_t)ws.l_count);
+  DevBuf<int32_t> list((size_t)ws.l_count);
+  colmax.zero();
+  if (ws.redone.n != 1) ws.redone.alloc(1);
+  ws.redone.zero();
+  typedef void (*PpKernel)(const PpParams);
+  static const PpKernel kernels[TC_MAX_SLICES] = {planes_predict_kernel<1>, planes_predict_kernel<2>, planes_predict_kernel<3>,
+                                                  planes_predict_kernel<4>, planes_predict_kernel<5>, planes_predict_kernel<6>,
+                                                  planes_predict_kernel<7>};
+  const PpKernel kernel = kernels[ws.S - 1];
+  const int64_t total = ws.l_count * p.units_per_col;
+  const unsigned grid = (unsigned)std::min<int64_t>(total, (int64_t)num_sms() * 3);
+  p.colmax = colmax.p; p.list = nullptr; p.count = nullptr;
+  kernel<<<grid, PP_THREADS, 0, stream()>>>(p);
+  check_launch("planes_predict_kernel");
+  FRICC_LAUNCH(predict_check_kernel, (unsigned)ceil_div(ws.l_count, 256), 256, 0, colmax.p, ws.l_count, ws.expo.p,
+               ws.colscale.p, list.p, ws.redone.p);
+  p.colmax = nullptr; p.list = list.p; p.count = ws.redone.p;
+  kernel<<<grid, PP_THREADS, 0, stream()>>>(p);
+  check_launch("planes_predict_kernel");
+}
+
 static bool planes_fused_applicable(const WView& w, int64_t nK) {
   if (w.sK2 != 1 || !(w.nK1 == 1 || w.sK1 == w.nK2)) return false;       // one contiguous run of nK doubles per column
   if (nK % 2 != 0 || nK < 4096 || nK > (int64_t)8 * PF_MAX_CHUNKS * PF_CHUNK) return false;
@@ -660,6 +803,9 @@ WView term_view(const double* W, const int64_t shape[4], const int64_t strides[4
 
 bool view_is_panel(const WView& w) { return w.sL2 == 1 && (w.nL1 == 1 || w.sL1 == w.nL2) && (w.nK1 == 1 || w.sK1 == w.nK2 * w.sK2); }
 
+static int g_tc_predict = 1;       // "tc_predict": re-encode with the previous exponents + verification when planes of the geometry exist
+static int64_t g_planes_predicted = 0;
+int64_t planes_predicted_builds() { return g_planes_predicted; }
 static int g_tc_fused_planes = 1;  // "tc_fused_planes": 1 = single-read cluster kernel for operands whose K run is contiguous
 static int g_tc_mode = 1;          // "tc_mode": what fricc_contract does -- 0 never the tensor-core form, 1 cost model, 2 always
 static int g_tc_planes = 6;        // "tc_planes": digit planes fricc_contract expands W into
@@ -667,6 +813,8 @@ static int g_tc_plane_cache = 0;   // "tc_plane_cache": keep the planes of the l
 int tc_mode() { return g_tc_mode; }
 int tc_planes() { return g_tc_planes; }
 int tc_plane_cache() { return g_tc_plane_cache; }
+static int g_tc_history_mb = 40960;  // "tc_history_mb": budget for the geometry-keyed plane buffers kept between plugin calls
+int tc_history_mb() { return g_tc_history_mb; }
 
 void wslices_build_view(WSlices& ws, const WView& w, int64_t l_begin, int64_t l_count, int S) {
   if (S < 1 || S > TC_MAX_SLICES) fail(FRICC_EINVAL, "digit planes must be 1..%d", TC_MAX_SLICES);
@@ -674,6 +822,9 @@ void wslices_build_view(WSlices& ws, const WView& w, int64_t l_begin, int64_t l_
   if (nK <= 0 || l_count <= 0) fail(FRICC_EINVAL, "bad operand shape");
   const int64_t Kpad = ceil_div(nK, TC_BK) * TC_BK, n_tiles = ceil_div(l_count, TC_BN);
   const size_t qbytes = (size_t)n_tiles * S * TC_BN * Kpad;
+  // planes of this geometry exist: their exponents predict the new ones (planes_predict_kernel)
+  const bool history = ws.expo_valid && ws.nK == nK && ws.l_count == l_count && ws.S == S && ws.q.n == qbytes;
+  ws.expo_valid = false;
   if (ws.q.n != qbytes) ws.q.alloc(qbytes);
   if (ws.expo.n != (size_t)(n_tiles * TC_BN)) {
     ws.expo.alloc((size_t)(n_tiles * TC_BN));
@@ -682,6 +833,13 @@ void wslices_build_view(WSlices& ws, const WView& w, int64_t l_begin, int64_t l_
   ws.nK = nK; ws.Kpad = Kpad; ws.l_count = l_count; ws.n_tiles = n_tiles; ws.S = S;
   if (Kpad / TC_BK > 65535) fail(FRICC_EINVAL, "contracted pair too large for the slicing grid");
   const bool kcontig = w.sK2 == 1 && w.sL2 != 1;
+  if (g_tc_predict && history && planes_predict_applicable(w, nK)) {
+    planes_predicted_build(ws, w, l_begin);
+    g_planes_predicted++;
+    ws.expo_valid = true;
+    return;
+  }
+  ws.expo_valid = true;   // (set before the launches: a failed launch throws and the handle is not used again)
   if (g_tc_fused_planes && planes_fused_applicable(w, nK) ) {
     planes_fused_build(ws, w, l_begin);
     return;
@@ -1445,6 +1603,8 @@ void set_tc_option(const char* key, int value) {
   else if (strcmp(key, "tc_sync_shift") == 0) g_tc_sync_shift = std::max(0, std::min(value, 10));
   else if (strcmp(key, "tc_sync_lag") == 0) g_tc_sync_lag = std::max(1, value);
   else if (strcmp(key, "tc_fused_planes") == 0) g_tc_fused_planes = value;
+  else if (strcmp(key, "tc_predict") == 0) g_tc_predict = value;
+  else if (strcmp(key, "tc_history_mb") == 0) g_tc_history_mb = std::max(0, value);
   else if (strcmp(key, "tc_mode") == 0) g_tc_mode = value;
   else if (strcmp(key, "tc_planes") == 0) {
     if (value < 1 || value > TC_MAX_SLICES) fail(FRICC_EINVAL, "tc_planes must be 1..%d", TC_MAX_SLICES);

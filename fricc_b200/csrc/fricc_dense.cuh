@@ -14,7 +14,11 @@ struct WSlices {
   DevBuf<int8_t> q;
   DevBuf<int32_t> expo;      // [n_tiles*64]
   DevBuf<double> colscale;   // [n_tiles*64]  2^(e_l - 7)
+  bool expo_valid = false;   // expo / colscale describe planes of this geometry (they can predict the next build's)
+  DevBuf<int> redone;        // [1] columns whose exponent moved in the last predicted build (device counter)
 };
+int64_t planes_predicted_builds();
+int tc_history_mb();
 
 constexpr int TC_MAX_SLICES = 7;
 

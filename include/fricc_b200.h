@@ -65,7 +65,7 @@ int fricc_set_option(const char* key, int value);
  * "tc_mode": which form fricc_contract picks -- 0 = always the fp64 SpMM, 1 (default) = the tensor-core form when its
  * cost model says it wins (an FRI-compressed T with at least half of its entries sampled, a large enough product),
  * 2 = always the tensor-core form.  "tc_planes": digit planes it expands W into (default 6 = 48 bits per column).
- * "tc_fused_planes": 1 (default) = operands whose contracted run is contiguous (the ladder's native W[a,b,c,d]) are
+ * "tc_predict" (1: see fricc_wslices_redone), "tc_pair" (1: CTA-pair tensor-core kernel, 0: one CTA per tile), "tc_lockstep", "tc_band", "tc_fused_planes": 1 (default) = operands whose contracted run is contiguous (the ladder's native W[a,b,c,d]) are
  * expanded by the single-read cluster kernel, 0 = by the two-pass kernels (identical planes).
  * "tc_plane_cache": 1 = fricc_contract keeps the planes of up to 12 device operands across calls, keyed by address,
  * shape and strides and guarded by a fingerprint of 4096 sampled elements (for drivers that hand over the same
@@ -214,6 +214,11 @@ int fricc_wslices_create_view(const double* W_dev, const int64_t w_shape[4], con
  * calls (fricc/friccsd.py:207,325-331)                                                                               */
 int fricc_wslices_update_view(fricc_wslices_t h, const double* W_dev, const int64_t w_shape[4], const int64_t w_strides[4],
                               const char* term, int64_t l_begin);
+/* An update of planes that exist already re-uses their column exponents as a prediction (option "tc_predict", default
+ * 1): one streaming pass cuts the digits and takes the new column maxima, and only the columns whose exponent moved are
+ * cut again -- bit-identical to a fresh build.  How many columns that was in the last update (-1: the last build was
+ * not a predicted one).  Reads 4 bytes back from the device.                                                          */
+int fricc_wslices_redone(fricc_wslices_t h, int64_t* n_columns);
 /* measured int8 tensor-core peak of the current device: back-to-back tcgen05.mma.kind::i8 (M=128, N=256, K=32) on
  * operands resident in shared memory, one CTA per SM, for about `seconds` -> int8 TOP/s (2 x MAC).  bench.py's
  * denominator for the tensor-core kernel's roofline (short run = burst clocks, seconds = under the power cap).        */

@@ -244,3 +244,55 @@ def test_plane_cache_follows_the_operand(tc, port):
     from fricc_b200 import _lib
 
     _lib.check(_lib.lib().fricc_plane_cache_clear())
+
+
+@pytest.mark.parametrize("shape,l0,lc,S", [((2, 40, 64, 64), 3, 70, 6), ((1, 9, 370, 372), 2, 7, 6), ((3, 20, 33, 34), 0, 60, 4),
+                                           ((2, 30, 50, 50), 5, 50, 7)])
+def test_predicted_update_equals_a_fresh_build(rccsd, shape, l0, lc, S):
+    """fricc_wslices_update_view on planes that exist: digits cut with the previous exponents in one streaming pass, the
+    columns whose exponent moved (here: scaled by 4, by 1/8, zeroed, made non-finite) cut again -- the same planes and
+    scales as a fresh build of the new operand, and the count of corrected columns is reported."""
+    import torch
+
+    from fricc_b200 import _lib
+
+    L, check = _lib.lib(), _lib.check
+    i64 = lambda v: (ctypes.c_int64 * 4)(*[int(x) for x in v])
+    g = torch.Generator(device="cuda").manual_seed(shape[2] + S)
+    W = (torch.rand(shape, generator=g, device="cuda", dtype=torch.float64) - 0.5)
+    W *= torch.pow(10.0, -3.0 * torch.rand(shape[0], shape[1], 1, 1, generator=g, device="cuda", dtype=torch.float64))
+    nK = shape[2] * shape[3]
+    h = ctypes.c_void_p()
+    check(L.fricc_wslices_create_view(ctypes.c_void_p(W.data_ptr()), i64(W.shape), i64(W.stride()), b"2323", l0, lc, S, ctypes.byref(h)))
+    n = ctypes.c_int64(7)
+    check(L.fricc_wslices_redone(h, ctypes.byref(n)))
+    assert n.value == -1                                  # a first build predicts nothing
+    before = rccsd.get_stat("planes_predicted_builds")
+    # new values everywhere (same magnitudes: exponents mostly stay), and a few columns that move
+    W2 = W * (1.0 + 0.05 * (torch.rand(shape, generator=g, device="cuda", dtype=torch.float64) - 0.5))
+    flat = W2.view(shape[0] * shape[1], -1)
+    moved = {l0 + 1: 4.0, l0 + 2: 0.125, l0 + lc - 1: 0.0}
+    for col, f in moved.items():
+        flat[col] *= f
+    flat[l0 + 4, 5] = float("inf")
+    check(L.fricc_wslices_update_view(h, ctypes.c_void_p(W2.data_ptr()), i64(W2.shape), i64(W2.stride()), b"2323", l0))
+    assert rccsd.get_stat("planes_predicted_builds") == before + 1
+    check(L.fricc_wslices_redone(h, ctypes.byref(n)))
+    assert 4 <= n.value <= max(4, lc // 2)                 # the four edited columns (+ the few whose maximum crossed a power of two)
+    rec = torch.empty(nK, lc, dtype=torch.float64, device="cuda")
+    check(L.fricc_wslices_reconstruct(h, ctypes.c_void_p(rec.data_ptr())))
+    check(L.fricc_wslices_destroy(h))
+    fresh = _planes(L, check, W2, "2323", l0, lc, S)
+    assert torch.equal(torch.nan_to_num(rec, nan=-7.0), torch.nan_to_num(fresh, nan=-7.0))
+    # and an update with the prediction switched off is the same thing
+    try:
+        rccsd.set_option("tc_predict", 0)
+        h2 = ctypes.c_void_p()
+        check(L.fricc_wslices_create_view(ctypes.c_void_p(W.data_ptr()), i64(W.shape), i64(W.stride()), b"2323", l0, lc, S, ctypes.byref(h2)))
+        check(L.fricc_wslices_update_view(h2, ctypes.c_void_p(W2.data_ptr()), i64(W2.shape), i64(W2.stride()), b"2323", l0))
+        rec2 = torch.empty(nK, lc, dtype=torch.float64, device="cuda")
+        check(L.fricc_wslices_reconstruct(h2, ctypes.c_void_p(rec2.data_ptr())))
+        check(L.fricc_wslices_destroy(h2))
+    finally:
+        rccsd.set_option("tc_predict", 1)
+    assert torch.equal(torch.nan_to_num(rec2, nan=-7.0), torch.nan_to_num(fresh, nan=-7.0))

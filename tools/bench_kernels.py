@@ -100,6 +100,11 @@ def main():
             handles[fused] = h
         check(L.fricc_set_option(b"tc_fused_planes", 1))
         h = handles[1]
+        upd = lambda: check(L.fricc_wslices_update_view(h, ptr(W), i64(W.shape), i64(W.stride()), b"2323", 0))
+        ms = timed(upd, a.reps)
+        alg = nK * cols * (8.0 + S)
+        print(json.dumps({"kernel": "planes_predict_kernel x2 + check (update of existing planes)", "planes": S, "nK": nK,
+                          "cols": cols, "ms": round(ms, 3), "algorithmic_GBps": round(alg / (ms * 1e-3) / 1e9, 1)}), flush=True)
         if 0 in handles:
             check(L.fricc_wslices_destroy(handles[0]))
 
