@@ -7,6 +7,8 @@ A "step" is one pass of the hot path as fricc/friccsd.py:update_amps drives it w
 compressed: 2 FRI compressions of T2 (N = o^2 v^2 entries -> m) and the 11 sparse contractions
   1323 (ovov -> Woooo), 0112 0313 0113 (ovov -> Wvoov), 0312 (ovov -> Wvovo),
   0101 (Woooo), 2323 (Wvvvv: the particle-particle ladder), 1302 1303 (Wvoov), 1202 1203 (Wvovo)   -> t2new / tmp.
+Two pairs that go into one array back to back run as one dense product each (0112 + 0113, 1302 + 1202:
+py_rccsd.contract_DTSpT_pair, an extension of the reference's surface; --no-fuse issues the eleven plain calls).
 
 Operand upkeep -- `--w-mode` (both values are in the line, `value` is the one selected):
   refreshed (default) the FRICCSD regime: Wvvvv = cc_Wvvvv(t1, t2, eris) is rebuilt EVERY iteration
@@ -21,7 +23,7 @@ Operand upkeep -- `--w-mode` (both values are in the line, `value` is the one se
 Sharding (N > 1, strong scaling): every contraction is cut along its free index pair; a rank hands the plugin call
 `py_rccsd.contract_DTSpT` (= fricc_contract) its slice of the operand and of the output as plain 4-D views
 (fricc_b200/dist.py: ViewEngine) -- the library picks the kernel -- and stores the finished slice into every peer's copy
-over NVLink (symmetric allocation, stores on a side stream under the next term's kernel, three device-side barriers
+over NVLink (symmetric allocation, stores on a side stream under the next term's kernel, two device-side barriers
 per step, no NCCL on the data path).  The step's two compressions come from one range-sharded pass.
 
 Timing: W >= 3 untimed warm-up steps, then K steps; barrier + torch.cuda.synchronize on both sides; CUDA events on the
@@ -58,7 +60,7 @@ UNIT = "s/iter"
 CONTRACTION_ORDER = ["1323", "0112", "0313", "0113", "0312", "0101", "2323", "1302", "1202", "1303", "1203"]
 # checksum of t2new after one step of the default workload (o=40, v=400, m=1e7, systematic, seed 20): the same on
 # every rank and for every GPU count (each output element is computed by one rank in a fixed order)
-EXPECTED_T2NEW_CHECKSUM = None
+EXPECTED_T2NEW_CHECKSUM = 3286248761.738817
 
 
 def metric_name(o, v, m):
@@ -86,6 +88,12 @@ def parse_args():
                    help="int8 digit planes of W for the tensor-core form of the contractions (0 = fp64 SpMM only)")
     p.add_argument("--push-inline", action="store_true",
                    help="N>1: issue the peer stores on the compute stream (A/B of the side-stream push)")
+    p.add_argument("--no-fuse", action="store_true",
+                   help="issue 0112/0113 and 1302/1202 as the eleven separate plugin calls of the reference's driver instead of "
+                        "the two fused pairs (py_rccsd.contract_DTSpT_pair)")
+    p.add_argument("--as-rank-of", type=int, default=0,
+                   help="profiling aid (1 GPU): do rank 0's share of the contractions of an N-rank job, without the exchange; "
+                        "the line is marked and is not a benchmark value")
     p.add_argument("--nccl-barrier", action="store_true", help="N>1: 4-byte NCCL all-reduce barriers instead of the "
                                                                "device-side flag barrier (A/B)")
     return p.parse_args()
@@ -325,7 +333,7 @@ class SegmentTimer:
 class Iteration:
     """Device-resident synthetic FRI-CCSD iteration, one instance per rank (ViewEngine: plugin calls on views)."""
 
-    def __init__(self, args, comm, device):
+    def __init__(self, args, comm, device, view_comm=None):
         import torch
 
         from fricc_b200 import _lib
@@ -348,6 +356,7 @@ class Iteration:
         # U(0,1) operands like the reference's tests (fricc/tests/test_sparse_tensors.py:78)
         self.ovov = torch.rand(o, v, o, v, generator=g, device=device, dtype=torch.float64)
         self.tc = args.planes > 0
+        self.fuse = self.tc and not args.no_fuse
         py_rccsd.set_option("tc_mode", 1 if self.tc else 0)
         if self.tc:
             py_rccsd.set_option("tc_planes", args.planes)
@@ -367,7 +376,7 @@ class Iteration:
         self.Wakci = mk(v, o, v, o)
         self.t2new = mk(o, o, v, v)
         self.tmp = [mk(o, o, v, v) for _ in range(3)]
-        self.eng = fd.ViewEngine(comm, device, None if args.nccl_barrier else self.arena, self.side)
+        self.eng = fd.ViewEngine(view_comm or comm, device, None if args.nccl_barrier else self.arena, self.side)
         if args.nccl_barrier:
             self.eng.arena = self.arena          # peer stores still go through the arena; only the barrier is NCCL
         # ---- the ladder operand: this rank's a-range of the NATIVE W[a,b,c,d], possibly in sub-shards
@@ -491,35 +500,48 @@ class Iteration:
 
     def contractions(self, T, T_alt, timer=None, plugin=False, after_t2new=None):
         eng, c = self.eng, self.eng.contract
-        self.Wklij.zero_(); self.Wakic.zero_(); self.Wakci.zero_()
-        self.t2new.zero_()
-        for t in self.tmp:
-            t.zero_()
-        eng.barrier()                                            # B0: nobody stores into a copy that is still being zeroed
-        self.mark("zero_outputs_B0")
+        # every output accumulates from zero; a rank zeroes only the part it computes -- the rest of its copy is overwritten
+        # by its peers' stores, and nobody stores into a slice its owner still works on, so no barrier is needed here
+        # (the previous step's B2 has made sure that nobody still reads last step's outputs)
+        for view in (eng.own_view("2323", None, self.t2new, w_range=(self.a_lo, self.a_hi)),
+                     eng.own_view("0113", self.ovov.shape, self.Wakic), eng.own_view("0312", self.ovov.shape, self.Wakci),
+                     eng.own_view("1323", self.ovov.shape, self.Wklij), eng.own_view("1302", self.Wakic.shape, self.tmp[0]),
+                     eng.own_view("1303", self.Wakic.shape, self.tmp[1]), eng.own_view("1203", self.Wakci.shape, self.tmp[2])):
+            if view is not None:
+                view.zero_()
+        self.mark("zero_own_slices")
         # the ladder first: its 2 GB of peer stores then hide under the ovov terms
         eng.publish(self.ladder(T, timer, plugin))
         self.mark("2323" if self.resident else "2323_incl_regen")
-        eng.publish(c("1323", self.ovov, T_alt, self.Wklij))
-        self.mark("1323")
-        c("0112", self.ovov, T_alt, self.Wakic)
-        c("0313", self.ovov, T_alt, self.Wakic)
-        eng.publish(c("0113", self.ovov, T_alt, self.Wakic))
+        if self.fuse:      # 0112 + 0113 read the same operand view: one weighted sign matrix, one dense product
+            eng.contract_pair("0112", "0113", self.ovov, self.ovov, T_alt, self.Wakic)
+        else:
+            c("0112", self.ovov, T_alt, self.Wakic)
+            c("0113", self.ovov, T_alt, self.Wakic)
+        eng.publish(c("0313", self.ovov, T_alt, self.Wakic))
         self.mark("0112_0313_0113")
         eng.publish(c("0312", self.ovov, T_alt, self.Wakci))
         self.mark("0312")
+        eng.publish(c("1323", self.ovov, T_alt, self.Wklij))      # the smallest output last: its stores are all B1 waits for
+        self.mark("1323")
         eng.barrier()                                            # B1: Woooo / Wvoov / Wvovo and the ladder's t2new are complete everywhere
         self.mark("B1")
         eng.publish(c("0101", self.Wklij, T, self.t2new))        # t2new is final on this rank from here on
         self.mark("0101")
         if after_t2new is not None:
             after_t2new()
-        c("1302", self.Wakic, T, self.tmp[0])
-        eng.publish(c("1202", self.Wakci, T, self.tmp[0]))
+        if self.fuse:      # 1302 + 1202 share the sign matrix: planes of 2 Wvoov - Wvovo, one dense product
+            eng.publish(eng.contract_pair("1302", "1202", self.Wakic, self.Wakci, T, self.tmp[0]))
+        else:
+            c("1302", self.Wakic, T, self.tmp[0])
+            eng.publish(c("1202", self.Wakci, T, self.tmp[0]))
         self.mark("1302_1202")
         eng.publish(c("1303", self.Wakic, T, self.tmp[1]))
         self.mark("1303")
-        eng.publish(c("1203", self.Wakci, T, self.tmp[2]))
+        if self.multi:
+            eng.contract_in_parts("1203", self.Wakci, T, self.tmp[2], parts=2)   # last before B2: halve what B2 waits for
+        else:
+            c("1203", self.Wakci, T, self.tmp[2])
         self.mark("1203")
         eng.barrier()                                            # B2: the step's outputs are complete on every rank
         self.mark("B2")
@@ -709,7 +731,8 @@ def run_b200_arm(args):
     comm = fd.Comm(rank, world)
     fd.use_torch_stream()
     L = _lib.lib()
-    it = Iteration(args, comm, device)
+    view_comm = fd.Comm(0, args.as_rank_of) if (args.as_rank_of > 1 and world == 1) else None
+    it = Iteration(args, comm, device, view_comm)
     o, v, m = it.o, it.v, it.m
 
     def sync_all():
@@ -902,6 +925,7 @@ def run_b200_arm(args):
             roof = None
         s_per_iter = ms * 1e-3 / args.steps
         line = {
+            **({"NOT_A_BENCHMARK": f"rank 0's share of a {args.as_rank_of}-rank job, no exchange (--as-rank-of)"} if view_comm else {}),
             "metric": metric_name(o, v, m), "value": s_per_iter, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": False, "scaling": "strong",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": workload_config(args, world),
@@ -911,7 +935,7 @@ def run_b200_arm(args):
             "schedule": ("single rank: plugin calls (py_rccsd.contract_DTSpT) on the full operands" if world == 1 else
                          "plugin calls on L-slice views; each rank stores its finished slice into every peer's copy over "
                          "NVLink" + (" on the compute stream" if args.push_inline else " on a side stream under the next term's kernel") +
-                         "; 3 " + ("NCCL 4-byte all-reduce" if args.nccl_barrier else "device-side flag") + " barriers per step, no NCCL on the data path"),
+                         "; 2 " + ("NCCL 4-byte all-reduce" if args.nccl_barrier else "device-side flag") + " barriers per step, no NCCL on the data path"),
             "timed_segments": "whole steps" if it.resident else
                               f"sum of segments; the ladder's W is regenerated in HBM between {len(it.sub)} sub-shards (an input)",
         }
@@ -938,6 +962,9 @@ def run_b200_arm(args):
             f"expanded into {args.planes} int8 digit planes, tail <= 2^-{8 * args.planes} of the column's largest element per "
             "term, exact int32 accumulation, fp64 recombination; contraction parity <= 1e-10 relative (tests/test_plugin_tc_gpu.py, "
             "incl. heavy-tailed W)") if it.tc else "fp64 FMA"
+        line["config"]["fused_pairs"] = ("0112+0113 (one weighted sign matrix) and 1302+1202 (planes of 2 Wvoov - Wvovo) through "
+                                         "py_rccsd.contract_DTSpT_pair: 9 dense products for the 11 terms" if it.fuse else
+                                         "none: eleven plugin calls")
         line["config"]["contraction_kernel"] = (f"int8 tensor cores, {args.planes} digit planes + fp64 remainder, chosen by "
                                                 f"fricc_contract's cost model ({tc_calls} of the timed plugin calls)"
                                                 if it.tc else "fp64 bucketed SpMM")
@@ -952,7 +979,7 @@ def run_b200_arm(args):
         if sweep is not None:
             line["compress_sweep"] = sweep
         default_cfg = (o, v, m, args.sampling) == (40, 400, 10_000_000, "systematic") and args.planes == 6
-        if default_cfg and EXPECTED_T2NEW_CHECKSUM is not None:
+        if default_cfg and EXPECTED_T2NEW_CHECKSUM is not None and view_comm is None:
             rel = abs(checks["t2new"] - EXPECTED_T2NEW_CHECKSUM) / abs(EXPECTED_T2NEW_CHECKSUM)
             line["t2new_checksum_vs_stored"] = {"rel_diff": rel, "ok": rel <= 1e-12}
             assert rel <= 1e-9, f"t2new checksum {checks['t2new']!r} differs from the stored {EXPECTED_T2NEW_CHECKSUM!r}"

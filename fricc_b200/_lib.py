@@ -85,6 +85,8 @@ SIGNATURES = {
                                       c_char_p]),
     "fricc_wslices_update_view": (c_int, [c_void_p, c_void_p, _i64p, _i64p, c_char_p, c_int64]),
     "fricc_wslices_redone": (c_int, [c_void_p, POINTER(c_int64)]),
+    "fricc_contract_pair": (c_int, [c_void_p, _i64p, _i64p, c_void_p, _i64p, _i64p, c_void_p, c_void_p, _i64p, _i64p, c_char_p,
+                                    c_char_p]),
     "fricc_int8_peak": (c_int, [c_double, _f64p]),
     "fricc_wslices_update": (c_int, [c_void_p, c_void_p, c_int64]),
     "fricc_wslices_destroy": (c_int, [c_void_p]),

@@ -1,5 +1,6 @@
 // fricc_capi.cu -- the extern "C" surface declared in include/fricc_b200.h.
 #include <algorithm>
+#include <cmath>
 #include <numeric>
 
 #include "fricc_common.cuh"
@@ -19,7 +20,7 @@ void set_push_carveout(int pct);   // fricc_peer.cu: L1/shared split the peer-st
 
 using namespace fricc;
 
-static int64_t g_tc_calls = 0, g_spmm_calls = 0;
+static int64_t g_tc_calls = 0, g_spmm_calls = 0, g_fused_pairs = 0;
 
 namespace {
 
@@ -156,6 +157,7 @@ int fricc_get_stat(const char* key, int64_t* value) {
   if (strcmp(key, "pivotal_restarts") == 0) *value = pivotal_restarts_last();
   else if (strcmp(key, "tc_contract_calls") == 0) *value = g_tc_calls;      // fricc_contract calls that took the tensor-core form
   else if (strcmp(key, "spmm_contract_calls") == 0) *value = g_spmm_calls;
+  else if (strcmp(key, "fused_pairs") == 0) *value = g_fused_pairs;   // fricc_contract_pair calls that ran as ONE dense product
   else if (strcmp(key, "planes_predicted_builds") == 0) *value = planes_predicted_builds();  // builds that reused exponents  // ... and the fp64 SpMM
   else fail(FRICC_EINVAL, "unknown stat '%s'", key);
   FRICC_API_END
@@ -484,11 +486,21 @@ bool use_tensor_cores(fricc_st* T, int64_t nR, int64_t nK, int64_t nL, bool pane
   const double m = (double)T->nnz, nS = (double)(T->nnz - T->n_exact);
   if (2.0 * nS < m || nK < 256 || nL < 64 || nR < 32) return false;
   const double S = tc_planes();
-  const double Mpad = (double)(ceil_div(nR, 128) * 128), Kpad = (double)(ceil_div(nK, 128) * 128),
-               Lpad = (double)(ceil_div(nL, 64) * 64);
-  const double t_spmm = m * (double)nL / 2.7e12 + (panel_in_place ? 0.0 : 16.0 * (double)nK * (double)nL / 3.0e12);
-  const double t_tc = Mpad * Kpad * Lpad * S / 1.5e15 + (double)nK * (double)nL * (16.0 + S) / 3.0e12 +
-                      Mpad * Kpad / 1.0e12 + (m - nS) * (double)nL / 1.0e12 + 30e-6;
+  const double Mpad = (double)(ceil_div(nR, 128) * 128), Kpad = (double)(ceil_div(nK, 128) * 128);
+  // fp64 SpMM: ~2.7e12 FMA/s on wide column ranges, about half of that on a few hundred columns, plus the (R,K) bucket
+  // sort of the entries that only this form needs (~0.8 ms at m = 1e7)
+  const double spmm_rate = nL >= 2048 ? 2.7e12 : 1.5e12;
+  const double t_spmm = m * (double)nL / spmm_rate + m * 0.8e-10 +
+                        (panel_in_place ? 0.0 : 16.0 * (double)nK * (double)nL / 3.0e12);
+  // the pair kernel works in whole rounds of (256 rows x 64 columns) tiles over SMs/2 CTA pairs, 128 S cycles of tensor
+  // work per 128-deep k-block at ~1.6 GHz under the power cap (a 200-column slice of a 1600-row term is ONE round that
+  // leaves most pairs idle: the SpMM wins there); then the sign matrix (sort-free scatter + row sums), the planes and
+  // the fp64 remainder of the exact entries
+  const double tiles = (double)ceil_div(nR, 256) * (double)ceil_div(nL, 64);
+  const double rounds = std::ceil(tiles / std::max(1, num_sms() / 2));
+  const double t_tc = rounds * (Kpad / 128.0) * (128.0 * S) / 1.6e9 +
+                      (double)nK * (double)nL * (16.0 + S) / 3.0e12 + Mpad * Kpad / 1.0e12 + 0.3e-3 +
+                      (m - nS) * (double)nL / 1.0e12;
   return t_tc < t_spmm;
 }
 
@@ -563,6 +575,79 @@ int fricc_contract(const double* W, int w_mem, const int64_t w_shape[4], const i
   }
   if (out_mem != FRICC_DEVICE) out_stage.to_host(out, (size_t)o_span);
   // (all-device calls return without synchronising: scratch buffers are stream-ordered allocations)
+  FRICC_API_END
+}
+
+int fricc_contract_pair(const double* W_a, const int64_t a_shape[4], const int64_t a_strides[4], const double* W_b,
+                        const int64_t b_shape[4], const int64_t b_strides[4], fricc_st_t T, double* out,
+                        const int64_t out_shape[4], const int64_t out_strides[4], const char* term_a, const char* term_b) {
+  FRICC_API_BEGIN
+  check_handle(T);
+  if (!W_a || !W_b || !out || !a_shape || !a_strides || !b_shape || !b_strides || !out_shape || !out_strides)
+    fail(FRICC_EINVAL, "null argument");
+  const TermSpec* ta0 = find_term(term_a);
+  const TermSpec* tb0 = find_term(term_b);
+  if (!ta0 || !tb0) fail(FRICC_EINVAL, "CASE NOT IMPLEMENTED: unknown contraction term");
+  // the two plain calls: what this function must equal, and what it falls back to
+  auto two_calls = [&]() {
+    int rc = fricc_contract(W_a, FRICC_DEVICE, a_shape, a_strides, T, out, FRICC_DEVICE, out_shape, out_strides, term_a);
+    if (rc != FRICC_OK) return rc;
+    return fricc_contract(W_b, FRICC_DEVICE, b_shape, b_strides, T, out, FRICC_DEVICE, out_shape, out_strides, term_b);
+  };
+  const TermSpec tsa = oriented(*ta0, out_strides), tsb = oriented(*tb0, out_strides);
+  const bool same_out = memcmp(tsa.oR, tsb.oR, sizeof(tsa.oR)) == 0 && memcmp(tsa.oL, tsb.oL, sizeof(tsa.oL)) == 0;
+  const bool same_t = memcmp(tsa.tR, tsb.tR, sizeof(tsa.tR)) == 0 && memcmp(tsa.tK, tsb.tK, sizeof(tsa.tK)) == 0;
+  const bool same_w = W_a == W_b && memcmp(a_shape, b_shape, 4 * sizeof(int64_t)) == 0 &&
+                      memcmp(a_strides, b_strides, 4 * sizeof(int64_t)) == 0 &&
+                      memcmp(tsa.wK, tsb.wK, sizeof(tsa.wK)) == 0 && memcmp(tsa.wL, tsb.wL, sizeof(tsa.wL)) == 0;
+  // small-integer ratio of the prefactors: s_a = sigma q_a, s_b = sigma q_b
+  const double sigma = std::min(std::fabs(tsa.scale), std::fabs(tsb.scale));
+  const double qa = tsa.scale / sigma, qb = tsb.scale / sigma;
+  const bool int_ratio = sigma > 0.0 && qa == std::nearbyint(qa) && qb == std::nearbyint(qb) && std::fabs(qa) <= 8 && std::fabs(qb) <= 8;
+  const int64_t* d = T->dims;
+  const int64_t nK = a_shape[tsa.wK[0]] * a_shape[tsa.wK[1]], nL = a_shape[tsa.wL[0]] * a_shape[tsa.wL[1]];
+  const int64_t nR = d[tsa.tR[0]] * d[tsa.tR[1]];
+  const bool shapes_ok = b_shape[tsb.wK[0]] * b_shape[tsb.wK[1]] == nK && b_shape[tsb.wL[0]] == a_shape[tsa.wL[0]] &&
+                         b_shape[tsb.wL[1]] == a_shape[tsa.wL[1]] && d[tsb.tR[0]] * d[tsb.tR[1]] == nR;
+  if (!same_out || !int_ratio || !shapes_ok || !(same_t || same_w) || T->n_exact < 0 || nK == 0 || nL == 0 || T->nnz == 0 ||
+      !use_tensor_cores(T, nR, nK, nL, false))
+    return two_calls();
+  // shape agreement of each term with T / out: let the plain path report it
+  for (int q = 0; q < 2; q++)
+    if (a_shape[tsa.wK[q]] != d[tsa.tK[q]] || b_shape[tsb.wK[q]] != d[tsb.tK[q]] || out_shape[tsa.oR[q]] != d[tsa.tR[q]] ||
+        out_shape[tsa.oL[q]] != a_shape[tsa.wL[q]])
+      return two_calls();
+  (void)span_of(a_shape, a_strides);
+  (void)span_of(b_shape, b_strides);
+  (void)span_of(out_shape, out_strides);
+  const OutMap om = out_map(tsa, d, out_shape, out_strides);
+  g_tc_calls++;
+  g_fused_pairs++;
+  if (same_w) {
+    // one operand view, (R, K) from different axes of T: one weighted sign matrix
+    const WView view = term_view(W_a, a_shape, a_strides, tsa);
+    WSlices local;
+    const WSlices& ws = planes_for(W_a, a_shape, a_strides, tsa, view, nL, local);
+    get_layout(T, tsa, false);
+    get_layout(T, tsb, false);                       // (the second call may move the first entry: fetch both again)
+    Layout& la = get_layout(T, tsa, false);
+    Layout& lb = get_layout(T, tsb, false);
+    contract_dense_pair(T, tsa, la, (int)qa, tsb, lb, (int)qb, sigma, ws, view, 0, out, om);
+  } else {
+    // one sign matrix, two operands: planes of the combined panel  q_a W_a[K][L] + q_b W_b[K][L]
+    DevBuf<double> pa((size_t)(nK * nL)), pb((size_t)(nK * nL));
+    permute_w(W_a, a_shape, a_strides, tsa, 0, nL, pa.p);
+    permute_w(W_b, b_shape, b_strides, tsb, 0, nL, pb.p);
+    panel_axpby(pa.p, pa.p, qa, pb.p, qb, nK * nL);
+    const int64_t pshape[4] = {1, nK, 1, nL}, pstrides[4] = {nK * nL, nL, nL, 1};
+    TermSpec tp = tsa;                                // the panel as a 4-D operand: K = axes (0,1), L = axes (2,3)
+    tp.wK[0] = 0; tp.wK[1] = 1; tp.wL[0] = 2; tp.wL[1] = 3;
+    const WView view = panel_view(pa.p, nL, nK, 0, nL);
+    WSlices local;
+    const WSlices& ws = planes_for(nullptr, pshape, pstrides, tp, view, nL, local);
+    Layout& lay = get_layout(T, tsa, false);
+    contract_dense(T, tsa, lay, ws, view, 0, out, om, sigma, false);
+  }
   FRICC_API_END
 }
 

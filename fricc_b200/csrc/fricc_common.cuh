@@ -172,6 +172,7 @@ struct Layout {
   // compression carries the same magnitude c = r/n') as a dense int8 sign matrix A[Mpad][Kpad]; everything else (the
   // exactly preserved set D, duplicates) stays a CSR remainder that goes through the fp64 SpMM.
   bool dense_built = false;
+  bool rest_built = false;     // cmag + rest_* are valid (possibly without the sign matrix: fused pairs)
   int64_t Mpad = 0, Kpad = 0;
   DevBuf<int8_t> dense;        // [Mpad][Kpad], K-major
   DevBuf<double> cmag;         // [1]  c

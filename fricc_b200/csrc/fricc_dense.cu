@@ -998,7 +998,7 @@ struct TDims {
 
 __global__ void sign_scatter_kernel(const int64_t* __restrict__ flat, const double* __restrict__ vals, int64_t first,
                                     int64_t m, TDims td, const double* __restrict__ cmag, int64_t Kpad,
-                                    int8_t* __restrict__ A, unsigned long long* __restrict__ stragglers) {
+                                    int8_t* __restrict__ A, unsigned long long* __restrict__ stragglers, int weight) {
   const int64_t e = first + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= m) return;
   int64_t f = flat[e];
@@ -1013,7 +1013,7 @@ __global__ void sign_scatter_kernel(const int64_t* __restrict__ flat, const doub
   if (fabs(fabs(v) - c) <= c * 1.7763568394002505e-15 && v != 0.0) {
     // A[R][K] += sign.  A position sampled more than once (the systematic sampler's unmatched samples all land on flat
     // index 0, fri_utils.cpp:132,149-157) simply carries the multiplicity: the int8 product takes any A in [-127, 127].
-    const int sg = v > 0.0 ? 1 : -1;
+    const int sg = v > 0.0 ? weight : -weight;   // weight 1, or the integer coefficient of this term in a fused pair
     const int64_t byte = R * Kpad + K;
     unsigned* word = reinterpret_cast<unsigned*>(A + (byte & ~(int64_t)3));
     const int sh = 8 * (int)(byte & 3);
@@ -1076,6 +1076,19 @@ __global__ void sign_check_kernel(const unsigned long long* __restrict__ straggl
   if (stragglers[0] != 0 || nnzA[0] != expected) cmag[0] = __longlong_as_double(0x7ff8000000000000LL);
 }
 
+// cmag + the CSR remainder of an FRI tensor's exactly preserved entries, without the sign matrix (fused pairs scatter
+// two terms into ONE matrix of their own)
+static void rest_form(fricc_st* T, const TermSpec& ts, Layout& lay) {
+  if (lay.rest_built || lay.dense_built) return;
+  lay.Mpad = ceil_div(lay.nR, TC_BM) * TC_BM;
+  lay.Kpad = ceil_div(lay.nK, TC_BK) * TC_BK;
+  lay.cmag.alloc(1);
+  FRICC_LAUNCH(cmag_kernel, 1, 1, 0, T->vals.p, T->nnz, lay.cmag.p);
+  lay.n_rest = T->n_exact;
+  build_csr(T, ts, 0, T->n_exact, lay.nR, lay.nK, lay.rest_rowptr, lay.rest_kidx, lay.rest_vals);
+  lay.rest_built = true;
+}
+
 double dense_form(fricc_st* T, const TermSpec& ts, Layout& lay) {
   const int64_t m = T->nnz;
   if (!lay.dense_built) {
@@ -1083,10 +1096,13 @@ double dense_form(fricc_st* T, const TermSpec& ts, Layout& lay) {
     lay.Kpad = ceil_div(lay.nK, TC_BK) * TC_BK;
     lay.dense.alloc((size_t)(lay.Mpad * lay.Kpad));
     lay.dense.zero();
-    lay.cmag.alloc(1);
+    const bool have_rest = lay.rest_built;
+    if (!have_rest) {
+      lay.cmag.alloc(1);
+      FRICC_LAUNCH(cmag_kernel, 1, 1, 0, T->vals.p, m, lay.cmag.p);
+    }
     lay.rowsum.alloc((size_t)lay.Mpad);
     lay.rowsum.zero();
-    FRICC_LAUNCH(cmag_kernel, 1, 1, 0, T->vals.p, m, lay.cmag.p);
     if (T->n_exact >= 0) {
       const int64_t nS = m - T->n_exact;
       DevBuf<unsigned long long> counters(2);
@@ -1094,12 +1110,15 @@ double dense_form(fricc_st* T, const TermSpec& ts, Layout& lay) {
       if (nS > 0) {
         TDims td{{T->dims[0], T->dims[1], T->dims[2], T->dims[3]}, ts.tR[0], ts.tR[1], ts.tK[0], ts.tK[1]};
         FRICC_LAUNCH(sign_scatter_kernel, (unsigned)ceil_div(nS, 256), 256, 0, T->flat.p, T->vals.p, T->n_exact, m, td,
-                     lay.cmag.p, lay.Kpad, lay.dense.p, counters.p);
+                     lay.cmag.p, lay.Kpad, lay.dense.p, counters.p, 1);
         FRICC_LAUNCH(rowsum_kernel, (unsigned)lay.nR, 256, 0, lay.dense.p, lay.Kpad, lay.rowsum.p, counters.p + 1);
         FRICC_LAUNCH(sign_check_kernel, 1, 1, 0, counters.p, counters.p + 1, (unsigned long long)nS, lay.cmag.p);
       }
-      lay.n_rest = T->n_exact;
-      build_csr(T, ts, 0, T->n_exact, lay.nR, lay.nK, lay.rest_rowptr, lay.rest_kidx, lay.rest_vals);
+      if (!have_rest) {
+        lay.n_rest = T->n_exact;
+        build_csr(T, ts, 0, T->n_exact, lay.nR, lay.nK, lay.rest_rowptr, lay.rest_kidx, lay.rest_vals);
+        lay.rest_built = true;
+      }
     } else {
       // unknown provenance: classify every entry of the sorted layout (duplicates and other magnitudes -> remainder)
       get_layout(T, ts, true);
@@ -1724,12 +1743,10 @@ void spmm_csr_view(const int64_t* rowptr, const uint32_t* kidx, const double* va
   FRICC_LAUNCH(spmm_csr_view_kernel, grid, block, 0, rowptr, kidx, vals, nR, w, l_begin, l_count, out, om, scale);
 }
 
-void contract_dense(fricc_st* T, const TermSpec& ts, Layout& lay, const WSlices& ws, const WView& w, int64_t l_begin,
-                    double* out, const OutMap& om, double scale, bool overwrite) {
-  if (ws.nK != lay.nK) fail(FRICC_EINVAL, "digit planes were built for %lld contracted indices, the term has %lld",
-                            (long long)ws.nK, (long long)lay.nK);
-  dense_form(T, ts, lay);
-  if (lay.n_rest != T->nnz) {
+// out (+)= scale * cmag * (A x planes): the tensor-core launch for a sign matrix A[Mpad][Kpad] with row sums
+static void tc_launch(const int8_t* dense, const int32_t* rowsum, const double* cmag, int64_t nR, int64_t Mpad, int64_t Kpad,
+                      const WSlices& ws, int64_t l_begin, double* out, const OutMap& om, double scale, bool overwrite) {
+  {
     const int S = ws.S;
     const uint32_t stage_bytes = TC_A_BYTES + (uint32_t)S * TC_B_PLANE_BYTES;
     int stages = (int)std::min<uint32_t>(6, (220u * 1024u) / stage_bytes);
@@ -1741,11 +1758,11 @@ void contract_dense(fricc_st* T, const TermSpec& ts, Layout& lay, const WSlices&
       attr_smem = 227 * 1024;
     }
     TcParams p;
-    p.nR = lay.nR; p.Mpad = lay.Mpad; p.l_begin = l_begin; p.l_count = ws.l_count;
-    p.S = S; p.nkb = (int)(lay.Kpad / TC_BK);
-    p.colscale = ws.colscale.p; p.rowsum = lay.rowsum.p; p.cmag = lay.cmag.p; p.scale = scale; p.out = out; p.om = om; p.beta = overwrite ? 0 : 1; p.debug = g_tc_debug; p.sync_shift = 4; p.sync_lag = 2;
+    p.nR = nR; p.Mpad = Mpad; p.l_begin = l_begin; p.l_count = ws.l_count;
+    p.S = S; p.nkb = (int)(Kpad / TC_BK);
+    p.colscale = ws.colscale.p; p.rowsum = rowsum; p.cmag = cmag; p.scale = scale; p.out = out; p.om = om; p.beta = overwrite ? 0 : 1; p.debug = g_tc_debug; p.sync_shift = 4; p.sync_lag = 2;
     p.n_tiles = (int)ws.n_tiles;
-    const CUtensorMap tmA = make_map_i8(lay.dense.p, lay.Mpad, lay.Kpad, TC_BM);
+    const CUtensorMap tmA = make_map_i8(dense, Mpad, Kpad, TC_BM);
     const int sms = num_sms();
     if (g_tc_pair && sms >= 2) {
       // CTA pairs: 256-row tiles, each CTA stages half of the plane rows of each MMA
@@ -1753,7 +1770,7 @@ void contract_dense(fricc_st* T, const TermSpec& ts, Layout& lay, const WSlices&
       const uint32_t pair_stage = TC_A_BYTES + (uint32_t)(n1 / 2 + n2 / 2) * TC_BK;
       p.stages = (int)std::min<uint32_t>(8, (220u * 1024u) / pair_stage);
       p.b_group = 0;
-      p.m_tiles = (int)ceil_div(lay.nR, 2 * TC_BM);
+      p.m_tiles = (int)ceil_div(nR, 2 * TC_BM);
       {  // band x (pairs / band) rectangle of concurrent tiles minimising band * 32 KB + (pairs / band) * 8 S KB
         const double ideal = std::sqrt((double)(sms / 2) * (double)(n1 + n2) * TC_BK / (2.0 * TC_A_BYTES));
         const int want = g_tc_band > 0 ? g_tc_band : std::max(1, (int)(ideal + 0.5));
@@ -1786,7 +1803,7 @@ void contract_dense(fricc_st* T, const TermSpec& ts, Layout& lay, const WSlices&
       const CUtensorMap tmB = make_map_i8(ws.q.p, ws.n_tiles * S * TC_BN, ws.Kpad, b_group * TC_BN);
       p.b_group = b_group;
       p.stages = stages;
-      p.m_tiles = (int)(lay.Mpad / TC_BM);
+      p.m_tiles = (int)(Mpad / TC_BM);
       {
         const double ideal = std::sqrt((double)sms * (double)S * TC_B_PLANE_BYTES / (double)TC_A_BYTES);
         const int want = g_tc_band > 0 ? g_tc_band : std::max(1, (int)(ideal + 0.5));
@@ -1798,8 +1815,75 @@ void contract_dense(fricc_st* T, const TermSpec& ts, Layout& lay, const WSlices&
       FRICC_LAUNCH(tc_sign_gemm_kernel, grid, TC_THREADS, smem, tmA, tmB, p);
     }
   }
+}
+
+void contract_dense(fricc_st* T, const TermSpec& ts, Layout& lay, const WSlices& ws, const WView& w, int64_t l_begin,
+                    double* out, const OutMap& om, double scale, bool overwrite) {
+  if (ws.nK != lay.nK) fail(FRICC_EINVAL, "digit planes were built for %lld contracted indices, the term has %lld",
+                            (long long)ws.nK, (long long)lay.nK);
+  dense_form(T, ts, lay);
+  if (lay.n_rest != T->nnz)
+    tc_launch(lay.dense.p, lay.rowsum.p, lay.cmag.p, lay.nR, lay.Mpad, lay.Kpad, ws, l_begin, out, om, scale, overwrite);
   if (lay.n_rest != 0)
     spmm_csr_view(lay.rest_rowptr.p, lay.rest_kidx.p, lay.rest_vals.p, lay.nR, w, l_begin, ws.l_count, out, om, scale);
+}
+
+__global__ void panel_axpby_kernel(double* __restrict__ dst, const double* __restrict__ a, double qa,
+                                   const double* __restrict__ b, double qb, int64_t n) {
+  const int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 2;
+  if (i + 1 < n) {
+    const double2 x = *reinterpret_cast<const double2*>(a + i), y = *reinterpret_cast<const double2*>(b + i);
+    *reinterpret_cast<double2*>(dst + i) = make_double2(qa * x.x + qb * y.x, qa * x.y + qb * y.y);
+  } else if (i < n) {
+    dst[i] = qa * a[i] + qb * b[i];
+  }
+}
+// dst = qa * a + qb * b over n doubles (16-byte aligned buffers of the stream-ordered pool)
+void panel_axpby(double* dst, const double* a, double qa, const double* b, double qb, int64_t n) {
+  if (n <= 0) return;
+  FRICC_LAUNCH(panel_axpby_kernel, (unsigned)ceil_div(ceil_div(n, 2), 256), 256, 0, dst, a, qa, b, qb, n);
+}
+
+// Two terms that read the SAME operand view and write through the SAME output map, but take (R, K) from different axes
+// of T (0112 + 0113 -> Wvoov):  out += s1 A1 W + s2 A2 W = sigma (q1 A1 + q2 A2) W  with small integers q.  Both terms'
+// signs are scattered -- weighted -- into one int8 matrix (|entries| <= |q1| + |q2| times the multiplicity), so the pair
+// costs ONE dense product.  The exact entries go through the fp64 remainder term by term as usual.  FRI tensors only
+// (n_exact >= 0).  An entry of one term may land on the position of an entry of the other (T[i,l,x,y] and T[i,l,y,x]):
+// the weighted sum at that position is exactly what the two products add up to.
+void contract_dense_pair(fricc_st* T, const TermSpec& ts1, Layout& lay1, int q1, const TermSpec& ts2, Layout& lay2, int q2,
+                         double sigma, const WSlices& ws, const WView& w, int64_t l_begin, double* out, const OutMap& om) {
+  if (T->n_exact < 0) fail(FRICC_EINVAL, "fused pair needs an FRI tensor (known number of exact entries)");
+  if (lay1.nR != lay2.nR || lay1.nK != lay2.nK || ws.nK != lay1.nK) fail(FRICC_EINVAL, "fused pair: shapes do not match");
+  rest_form(T, ts1, lay1);
+  rest_form(T, ts2, lay2);
+  const int64_t m = T->nnz, nS = m - T->n_exact;
+  if (nS > 0) {
+    const int64_t Mpad = lay1.Mpad, Kpad = lay1.Kpad;
+    DevBuf<int8_t> dense((size_t)(Mpad * Kpad));
+    dense.zero();
+    DevBuf<int32_t> rowsum((size_t)Mpad);
+    rowsum.zero();
+    DevBuf<unsigned long long> counters(2);
+    counters.zero();
+    DevBuf<double> cmag(1);
+    FRICC_CUDA(cudaMemcpyAsync(cmag.p, lay1.cmag.p, sizeof(double), cudaMemcpyDeviceToDevice, stream()));
+    const TermSpec* tss[2] = {&ts1, &ts2};
+    const int qs[2] = {q1, q2};
+    for (int t = 0; t < 2; t++) {
+      TDims td{{T->dims[0], T->dims[1], T->dims[2], T->dims[3]}, tss[t]->tR[0], tss[t]->tR[1], tss[t]->tK[0], tss[t]->tK[1]};
+      FRICC_LAUNCH(sign_scatter_kernel, (unsigned)ceil_div(nS, 256), 256, 0, T->flat.p, T->vals.p, T->n_exact, m, td,
+                   cmag.p, Kpad, dense.p, counters.p, qs[t]);
+    }
+    FRICC_LAUNCH(rowsum_kernel, (unsigned)lay1.nR, 256, 0, dense.p, Kpad, rowsum.p, counters.p + 1);
+    // an entry that is not +-c (false provenance hint) or a byte overflow poisons the result; the |A| count is not
+    // checked here: positions shared by the two terms may cancel
+    FRICC_LAUNCH(sign_check_kernel, 1, 1, 0, counters.p, counters.p, 0ULL, cmag.p);
+    tc_launch(dense.p, rowsum.p, cmag.p, lay1.nR, Mpad, Kpad, ws, l_begin, out, om, sigma, false);
+  }
+  if (lay1.n_rest != 0)
+    spmm_csr_view(lay1.rest_rowptr.p, lay1.rest_kidx.p, lay1.rest_vals.p, lay1.nR, w, l_begin, ws.l_count, out, om, sigma * q1);
+  if (lay2.n_rest != 0)
+    spmm_csr_view(lay2.rest_rowptr.p, lay2.rest_kidx.p, lay2.rest_vals.p, lay2.nR, w, l_begin, ws.l_count, out, om, sigma * q2);
 }
 
 void contract_dense(fricc_st* T, const TermSpec& ts, Layout& lay, const WSlices& ws, const double* Wp, int64_t ldw,

@@ -37,6 +37,10 @@ bool view_is_panel(const WView& w);
 // planes of the columns [l_begin, l_begin + l_count) of a view, read where the operand lies (no fp64 panel).  Operands
 // whose contracted run is contiguous (the ladder's native W[a,b,c,d]) go through a single-read cluster kernel.
 void wslices_build_view(WSlices& ws, const WView& w, int64_t l_begin, int64_t l_count, int S);
+void panel_axpby(double* dst, const double* a, double qa, const double* b, double qb, int64_t n);
+// two terms on the same operand view and output map, (R, K) from different axes of T: one dense product (fricc_dense.cu)
+void contract_dense_pair(fricc_st* T, const TermSpec& ts1, Layout& lay1, int q1, const TermSpec& ts2, Layout& lay2, int q2,
+                         double sigma, const WSlices& ws, const WView& w, int64_t l_begin, double* out, const OutMap& om);
 void contract_dense(fricc_st* T, const TermSpec& ts, Layout& lay, const WSlices& ws, const WView& w, int64_t l_begin,
                     double* out_dev, const OutMap& om, double scale, bool overwrite = false);
 void spmm_csr_view(const int64_t* rowptr, const uint32_t* kidx, const double* vals, int64_t nR, const WView& w,

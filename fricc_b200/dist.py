@@ -523,6 +523,48 @@ class ViewEngine:
         self.py.contract_DTSpT(Wv, T, ov, term)
         return ov
 
+    def own_view(self, term, w_shape, out, w_range=None):
+        """The part of `out` this rank computes for `term` (None if its range is empty): what has to be zero before the
+        term accumulates -- the rest of a rank's copy is overwritten by its peers' stores."""
+        ax = TERM_AXES[term]
+        if w_range is None:
+            j = self.slice_axis(term, w_shape)
+            lo, hi = self.my_range(w_shape[ax["wL"][j]])
+        else:
+            j, (lo, hi) = 0, w_range
+        return self.out_view(term, out, j, lo, hi) if hi > lo else None
+
+    def contract_pair(self, term_a, term_b, W_a, W_b, T, out):
+        """This rank's slice of two terms that go into the same output through the same slicing, as one fused call
+        (py_rccsd.contract_DTSpT_pair)."""
+        axa, axb = TERM_AXES[term_a], TERM_AXES[term_b]
+        j = self.slice_axis(term_a, W_a.shape)
+        if j != self.slice_axis(term_b, W_b.shape) or axa["oL"] != axb["oL"]:
+            raise ValueError(f"terms {term_a} and {term_b} are not sliced alike")
+        lo, hi = self.my_range(W_a.shape[axa["wL"][j]])
+        if hi <= lo:
+            return None
+        ov = self.out_view(term_a, out, j, lo, hi)
+        self.py.contract_DTSpT_pair(W_a.narrow(axa["wL"][j], lo, hi - lo), W_b.narrow(axb["wL"][j], lo, hi - lo), T, ov,
+                                    term_a, term_b)
+        return ov
+
+    def contract_in_parts(self, term, W, T, out, parts=2):
+        """`contract` + `publish` with this rank's range cut into `parts`: the stores of one part run under the kernel of
+        the next, so that only the last part's stores are left when the term is the last one before a barrier."""
+        ax = TERM_AXES[term]
+        j = self.slice_axis(term, W.shape)
+        lo, hi = self.my_range(W.shape[ax["wL"][j]])
+        parts = max(1, min(int(parts), hi - lo))
+        for q in range(parts):
+            a = lo + (hi - lo) * q // parts
+            b = lo + (hi - lo) * (q + 1) // parts
+            if b <= a:
+                continue
+            ov = self.out_view(term, out, j, a, b)
+            self.py.contract_DTSpT(W.narrow(ax["wL"][j], a, b - a), T, ov, term)
+            self.publish(ov)
+
     def publish(self, view):
         """Store a 4-D view of an arena tensor into the same view of every peer's copy (on the side stream if any)."""
         if view is None or self.arena is None or self.comm.world == 1:
@@ -545,7 +587,8 @@ class ViewEngine:
         if self._flags is None:
             import torch.distributed as dist
 
-            dist.barrier(group=self.comm.group)
+            if dist.is_available() and dist.is_initialized():
+                dist.barrier(group=self.comm.group)
             return
         self._epoch += 1
         check(self.L.fricc_peer_barrier(self._flag_peers, self.comm.world, self.comm.rank, self._epoch))

@@ -292,6 +292,24 @@ def contract_DTSpT(W, T, ouput, term):
     return _contract(W, T, ouput, term)
 
 
+def contract_DTSpT_pair(W_a, W_b, T, ouput, term_a, term_b):
+    """``contract_DTSpT(W_a, T, ouput, term_a); contract_DTSpT(W_b, T, ouput, term_b)`` -- as ONE dense product when the two
+    terms allow it (include/fricc_b200.h: fricc_contract_pair): the pairs the reference's drivers issue back to back into
+    one array, 0112 + 0113 (same operand, fricc/friccsd.py:347-356), 0113 + 0313, 1302 + 1202 (:252-258).  An extension of
+    the reference's surface.  Device tensors take the fused path; anything else is the two plain calls."""
+    if not isinstance(T, SparseTensor4d):
+        raise TypeError("contract_DTSpT_pair(): T must be a SparseTensor4d")
+    if not (_is_cuda_tensor(W_a) and _is_cuda_tensor(W_b) and _is_cuda_tensor(ouput)):
+        _contract(W_a, T, ouput, term_a)
+        return _contract(W_b, T, ouput, term_b)
+    a, b = _strided4(W_a, "W_a"), _strided4(W_b, "W_b")
+    o = _strided4(ouput, "ouput", writeable=True)
+    check(_lib.lib().fricc_contract_pair(a.ptr, i64x4(a.shape), i64x4(a.strides), b.ptr, i64x4(b.shape), i64x4(b.strides),
+                                         T._h, o.ptr, i64x4(o.shape), i64x4(o.strides), str(term_a).encode(),
+                                         str(term_b).encode()))
+    return None
+
+
 def contract_DTSpT_experimental(W, T, ouput, term):
     """The reference's alternative 2323 kernels (``"taskloop"``, ``"atomic"``; src/sparse_tensor.cpp:445-459) differ only
     in CPU threading; both names run the same GPU ladder kernel here."""

@@ -58,6 +58,20 @@ int fricc_stream_synchronize(void);
  * L1/shared split (percent shared) those kernels ask for, default 100 = the split the tensor-core kernel runs under,
  * so that both can be resident on one SM; -1 = the device default.                                               */
 int fricc_set_option(const char* key, int value);
+/* Two contractions into the SAME output with the same T as ONE dense product where the algebra allows it (an extension;
+ * the reference's drivers make the two calls one after the other, e.g. fricc/friccsd.py:347-356 (0112, 0113 -> Wvoov) and
+ * :252-258 (1302, 1202 -> tmp)).  All arrays on the device.  Fused when the output maps agree, the prefactors are in a
+ * small-integer ratio and either
+ *   - both terms read the same operand view and differ in which axes of T form (R, K): the signs of both are scattered,
+ *     weighted, into one int8 matrix  (0112 + 0113:  out += 0.5 (2 A_0113 - A_0112) W), or
+ *   - both terms take (R, K) from the same axes of T and read different operands: planes of the combined panel
+ *     (1302 + 1202:  out += A (2 Wvoov - Wvovo); 0113 + 0313 likewise);
+ * otherwise -- or when the tensor-core form would not be chosen -- exactly the two fricc_contract calls.  The result
+ * equals the two calls up to fp64 rounding of the combination (tests/test_plugin_tc_gpu.py).
+ * fricc_get_stat("fused_pairs") counts the calls that ran fused.                                                         */
+int fricc_contract_pair(const double* W_a_dev, const int64_t a_shape[4], const int64_t a_strides[4], const double* W_b_dev,
+                        const int64_t b_shape[4], const int64_t b_strides[4], fricc_st_t T, double* out_dev,
+                        const int64_t out_shape[4], const int64_t out_strides[4], const char* term_a, const char* term_b);
 /* "spmm_exact_order": 0 (default) = the fast contraction kernels ((R,K)-sorted buckets, FMA, within 1e-10 of the
  * reference); 1 = PARITY MODE: every contraction adds the entries of an owner pair in storage order with one rounded
  * product and one rounded sum per entry straight onto the output element, exactly like the reference's loop nest

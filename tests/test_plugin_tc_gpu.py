@@ -296,3 +296,65 @@ def test_predicted_update_equals_a_fresh_build(rccsd, shape, l0, lc, S):
     finally:
         rccsd.set_option("tc_predict", 1)
     assert torch.equal(torch.nan_to_num(rec2, nan=-7.0), torch.nan_to_num(fresh, nan=-7.0))
+
+
+@pytest.mark.parametrize("ta,tb", [("0112", "0113"), ("0113", "0313"), ("1302", "1202")])
+@pytest.mark.parametrize("no,nv,sliced", [(5, 19, False), (9, 30, True)])
+def test_fused_pair_equals_the_two_calls(tc, port, ta, tb, no, nv, sliced):
+    """contract_DTSpT_pair: the pairs the drivers issue back to back into one array, as ONE dense product (a weighted
+    sign matrix for 0112 + 0113, planes of the combined operand for 0113 + 0313 and 1302 + 1202) -- against the oracle's
+    two contractions, on whole operands and on the L-slice views a rank of the sharded step hands over."""
+    import torch
+
+    rccsd = tc
+    rng = np.random.default_rng(no * 77 + nv + int(ta))
+    T, flat, vals, dims = _fri(rccsd, rng, no, nv, int(0.3 * no * no * nv * nv), kind="diff")
+    ext = {"o": no, "v": nv}
+    (wa_axes, o_axes, _, _), (wb_axes, ob_axes, _, _) = TERMS[ta], TERMS[tb]
+    assert o_axes == ob_axes
+    Wa = rng.random([ext[c] for c in wa_axes]) - 0.4
+    # 0112 + 0113 and 0113 + 0313 read the same ovov block (the second pair through two different views of it)
+    Wb = Wa if wa_axes == wb_axes else rng.random([ext[c] for c in wb_axes]) - 0.6
+    out0 = rng.random([ext[c] for c in o_axes])
+    want = out0.copy()
+    port.contract(ta, Wa, flat, vals, dims, want)
+    port.contract(tb, Wb, flat, vals, dims, want)
+    da = torch.from_numpy(Wa).cuda()
+    db = da if Wb is Wa else torch.from_numpy(Wb).cuda()
+    got = torch.from_numpy(out0).cuda()
+    before = rccsd.get_stat("fused_pairs")
+    if not sliced:
+        rccsd.contract_DTSpT_pair(da, db, T, got, ta, tb)
+        calls = 1
+    else:
+        from fricc_b200 import dist as fd
+
+        calls = 0
+        for r in range(3):                           # three ranks' slices, one after the other on this GPU
+            eng = fd.ViewEngine.__new__(fd.ViewEngine)
+            eng.comm, eng.device, eng.arena, eng.side, eng.py = fd.Comm(r, 3), None, None, None, rccsd
+            calls += eng.contract_pair(ta, tb, da, db, T, got) is not None
+    assert rccsd.get_stat("fused_pairs") == before + calls
+    assert _close(got.cpu().numpy(), want)
+    # and the pair on host arrays is simply the two calls
+    host = out0.copy()
+    rccsd.contract_DTSpT_pair(Wa, Wb, T, host, ta, tb)
+    assert _close(host, want)
+
+
+def test_pair_that_cannot_fuse_falls_back_to_two_calls(tc, port):
+    import torch
+
+    rccsd = tc
+    rng = np.random.default_rng(8)
+    no, nv = 5, 12
+    T, flat, vals, dims = _fri(rccsd, rng, no, nv, 2000, kind="diff")
+    Wvoov, Wvovo = rng.random((nv, no, no, nv)), rng.random((nv, no, nv, no))
+    want = np.zeros((no, no, nv, nv))
+    port.contract("1303", Wvoov, flat, vals, dims, want)       # 1303 and 1203 write through different output maps
+    port.contract("1203", Wvovo, flat, vals, dims, want)
+    got = torch.zeros(no, no, nv, nv, dtype=torch.float64, device="cuda")
+    before = rccsd.get_stat("fused_pairs")
+    rccsd.contract_DTSpT_pair(torch.from_numpy(Wvoov).cuda(), torch.from_numpy(Wvovo).cuda(), T, got, "1303", "1203")
+    assert rccsd.get_stat("fused_pairs") == before
+    assert _close(got.cpu().numpy(), want)

@@ -57,8 +57,11 @@ def test_slices_tile_the_contraction(port, term, world):
     covered = torch.zeros_like(got)
     for r in range(world):
         eng = _engine(port, r, world)
+        own = eng.own_view(term, Wt.shape, got)
         ov = eng.contract(term, Wt, T, got)
+        assert (own is None) == (ov is None)
         if ov is not None:
+            assert own.data_ptr() == ov.data_ptr() and own.shape == ov.shape and own.stride() == ov.stride()
             assert ov.data_ptr() >= got.data_ptr()               # a view of the output, not a copy
             j = eng.slice_axis(term, Wt.shape)
             lo, hi = eng.my_range(Wt.shape[fd.TERM_AXES[term]["wL"][j]])
@@ -92,3 +95,16 @@ def test_cut_axis_is_the_longer_free_axis():
         j = fd.ViewEngine.slice_axis(term, shape)
         e = [shape[ax["wL"][0]], shape[ax["wL"][1]]]
         assert e[j] == max(e) and (e[0] != e[1] or j == 0)
+
+
+@pytest.mark.parametrize("parts", [1, 2, 3])
+def test_contract_in_parts_is_the_same_contraction(port, parts):
+    rng = np.random.default_rng(5)
+    no, nv = 3, 8
+    W, out0, T = _case(rng, "1203", no, nv, 70)
+    want = out0.copy()
+    port.contract("1203", W, T[0], T[1], T[2], want)
+    got = torch.from_numpy(out0.copy())
+    for r in range(2):
+        _engine(port, r, 2).contract_in_parts("1203", torch.from_numpy(W), T, got, parts=parts)
+    assert np.abs(got.numpy() - want).max() <= 1e-12 * np.abs(want).max()

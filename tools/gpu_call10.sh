@@ -3,7 +3,7 @@
 cd "$GRAFT_REPO_ROOT" 2>/dev/null || cd /root/repo
 mkdir -p gpurun_out
 rm -f gpurun_out/summary.txt
-for n in 8 4; do
+for n in ${NS:-8}; do
 ( time timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 2951$n bench.py --gpus $n --steps 5 --warmup 3 ) > gpurun_out/bench_n$n.json 2> gpurun_out/bench_n$n.err; echo "bench$n rc=$?" >> gpurun_out/summary.txt
 tail -n 4 gpurun_out/bench_n$n.err
 python - $n <<'PY'
