@@ -381,6 +381,7 @@ struct PlaneEntry {
   fricc::WSlices ws;
 };
 std::vector<PlaneEntry*> g_plane_cache;
+WSlices* g_pair_planes = nullptr;        // planes of the combined operand of the last fused pair (fricc_contract_pair)
 std::vector<PlaneEntry*> g_plane_hist;   // geometry-keyed buffers + exponents ("tc_history_mb"), see planes_for
 uint64_t g_plane_stamp = 0;
 constexpr size_t kPlaneCacheEntries = 12;
@@ -398,6 +399,8 @@ void plane_cache_clear() {
   g_plane_cache.clear();
   for (PlaneEntry* e : g_plane_hist) delete e;
   g_plane_hist.clear();
+  delete g_pair_planes;
+  g_pair_planes = nullptr;
 }
 
 const WSlices& planes_for(const double* Wd, const int64_t shape[4], const int64_t strides[4], const TermSpec& ts,
@@ -634,19 +637,19 @@ int fricc_contract_pair(const double* W_a, const int64_t a_shape[4], const int64
     Layout& lb = get_layout(T, tsb, false);
     contract_dense_pair(T, tsa, la, (int)qa, tsb, lb, (int)qb, sigma, ws, view, 0, out, om);
   } else {
-    // one sign matrix, two operands: planes of the combined panel  q_a W_a[K][L] + q_b W_b[K][L]
-    DevBuf<double> pa((size_t)(nK * nL)), pb((size_t)(nK * nL));
-    permute_w(W_a, a_shape, a_strides, tsa, 0, nL, pa.p);
-    permute_w(W_b, b_shape, b_strides, tsb, 0, nL, pb.p);
-    panel_axpby(pa.p, pa.p, qa, pb.p, qb, nK * nL);
-    const int64_t pshape[4] = {1, nK, 1, nL}, pstrides[4] = {nK * nL, nL, nL, 1};
-    TermSpec tp = tsa;                                // the panel as a 4-D operand: K = axes (0,1), L = axes (2,3)
-    tp.wK[0] = 0; tp.wK[1] = 1; tp.wL[0] = 2; tp.wL[1] = 3;
-    const WView view = panel_view(pa.p, nL, nK, 0, nL);
-    WSlices local;
-    const WSlices& ws = planes_for(nullptr, pshape, pstrides, tp, view, nL, local);
+    // one sign matrix, two operands: planes of the combination q_a W_a + q_b W_b, cut straight from the two views (no fp64
+    // copy of it); the exact entries take the fp64 remainder on each view
+    const WView va = term_view(W_a, a_shape, a_strides, tsa), vb = term_view(W_b, b_shape, b_strides, tsb);
+    if (!g_pair_planes) g_pair_planes = new WSlices();   // buffers kept between calls (one geometry at a time)
+    WSlices& pair_planes = *g_pair_planes;
+    wslices_build_view2(pair_planes, va, qa, vb, qb, 0, nL, tc_planes());
     Layout& lay = get_layout(T, tsa, false);
-    contract_dense(T, tsa, lay, ws, view, 0, out, om, sigma, false);
+    dense_form(T, tsa, lay);
+    contract_dense_signs(T, lay, pair_planes, 0, out, om, sigma);
+    if (lay.n_rest != 0) {
+      contract_rest(lay, va, 0, nL, out, om, sigma * qa);
+      contract_rest(lay, vb, 0, nL, out, om, sigma * qb);
+    }
   }
   FRICC_API_END
 }

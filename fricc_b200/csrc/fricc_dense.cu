@@ -81,6 +81,23 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     if (clock64() - t0 > 20000000000LL) __trap();  // ~10 s
   }
 }
+// the epilogue warps wait a whole main loop (~1 ms) for the accumulators: let the hardware park them for up to 20 us per
+// try instead of polling (they were 80 % of the pair kernel's stall samples and the kernel runs power-capped)
+__device__ __forceinline__ void mbar_wait_parked(uint64_t* bar, uint32_t parity) {
+  const long long t0 = clock64();
+  for (;;) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity), "r"(20000u)
+        : "memory");
+    if (ok) return;
+    if (clock64() - t0 > 20000000000LL) __trap();
+  }
+}
 __device__ __forceinline__ void prefetch_tensormap(const void* tm) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(tm)) : "memory");
 }
@@ -214,17 +231,21 @@ __device__ __forceinline__ int64_t view_offL(const WView& w, int64_t l) {
 
 // LCONTIG: thread = column, a CTA row of threads walks K; KCONTIG: warp = column, lanes walk K
 template <bool KCONTIG>
-__global__ void colmax_view_kernel(const WView w, int64_t nK, int64_t l_begin, int64_t l_count, int64_t k_per_block,
-                                   unsigned long long* __restrict__ colmax) {
+__global__ void colmax_view_kernel(const WView w, const WView w2, double q1, double q2, int64_t nK, int64_t l_begin,
+                                   int64_t l_count, int64_t k_per_block, unsigned long long* __restrict__ colmax) {
+  // w2.p != nullptr: the operand is the combination q1 * w + q2 * w2 of two views with the same (K, L) extents
   const int64_t k0 = (int64_t)blockIdx.y * k_per_block, k1 = min(nK, k0 + k_per_block);
   if (KCONTIG) {
     const int64_t col = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (col >= l_count) return;
     const int lane = threadIdx.x & 31;
     const double* base = w.p + view_offL(w, l_begin + col);
+    const double* base2 = w2.p ? w2.p + view_offL(w2, l_begin + col) : nullptr;
     unsigned long long mx = 0;
     for (int64_t k = k0 + lane; k < k1; k += 32) {
-      const unsigned long long key = abs_key(base[view_offK(w, k)]);
+      double v = base[view_offK(w, k)];
+      if (base2) v = q1 * v + q2 * base2[view_offK(w2, k)];
+      const unsigned long long key = abs_key(v);
       mx = key > mx ? key : mx;
     }
     for (int o = 16; o > 0; o >>= 1) {
@@ -236,10 +257,13 @@ __global__ void colmax_view_kernel(const WView w, int64_t nK, int64_t l_begin, i
     const int64_t col = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (col >= l_count) return;
     const double* base = w.p + view_offL(w, l_begin + col);
+    const double* base2 = w2.p ? w2.p + view_offL(w2, l_begin + col) : nullptr;
     unsigned long long mx = 0;
     int64_t ka = k0 / w.nK2, kb = k0 - ka * w.nK2;
     for (int64_t k = k0; k < k1; k++) {
-      const unsigned long long key = abs_key(base[ka * w.sK1 + kb * w.sK2]);
+      double v = base[ka * w.sK1 + kb * w.sK2];
+      if (base2) v = q1 * v + q2 * base2[ka * w2.sK1 + kb * w2.sK2];
+      const unsigned long long key = abs_key(v);
       mx = key > mx ? key : mx;
       if (++kb == w.nK2) { kb = 0; ka++; }
     }
@@ -278,8 +302,8 @@ __device__ __forceinline__ long long digit_string(double w, int sh, long long ha
 //   KCONTIG: thread (kw = t & 31, cq = t >> 5): a warp reads 128 consecutive K (1 KB) of one column.
 template <bool KCONTIG>
 __global__ void __launch_bounds__(256)
-slice_view_kernel(const WView w, int64_t nK, int64_t l_begin, int64_t l_count, int64_t Kpad, int S,
-                  const int32_t* __restrict__ expo, int8_t* __restrict__ q) {
+slice_view_kernel(const WView w, const WView w2, double q1, double q2, int64_t nK, int64_t l_begin, int64_t l_count,
+                  int64_t Kpad, int S, const int32_t* __restrict__ expo, int8_t* __restrict__ q) {
   extern __shared__ uint32_t sq[];  // [S][64][33]
   const int64_t tile = blockIdx.x, kb = blockIdx.y;
   const long long half = 1LL << (8 * S - 1), top = (1LL << (8 * S)) - 1;
@@ -290,6 +314,7 @@ slice_view_kernel(const WView w, int64_t nK, int64_t l_begin, int64_t l_count, i
     const bool col_ok = l < l_count;
     const int sh = 8 * S - 1 - (col_ok ? expo[l] : 0);
     const double* base = w.p + (col_ok ? view_offL(w, l_begin + l) : 0);
+    const double* base2 = (w2.p && col_ok) ? w2.p + view_offL(w2, l_begin + l) : nullptr;
     uint32_t pack[TC_MAX_SLICES];
 #pragma unroll
     for (int s = 0; s < TC_MAX_SLICES; s++) pack[s] = 0;
@@ -298,7 +323,11 @@ slice_view_kernel(const WView w, int64_t nK, int64_t l_begin, int64_t l_count, i
 #pragma unroll
     for (int i = 0; i < 4; i++) {
       long long qi = 0;
-      if (col_ok && K0 + i < nK) qi = digit_string(base[ka * w.sK1 + kr * w.sK2], sh, half, top);
+      if (col_ok && K0 + i < nK) {
+        double v = base[ka * w.sK1 + kr * w.sK2];
+        if (base2) v = q1 * v + q2 * base2[ka * w2.sK1 + kr * w2.sK2];
+        qi = digit_string(v, sh, half, top);
+      }
       if (++kr == w.nK2) { kr = 0; ka++; }
 #pragma unroll
       for (int s = 0; s < TC_MAX_SLICES; s++)
@@ -816,14 +845,18 @@ int tc_plane_cache() { return g_tc_plane_cache; }
 static int g_tc_history_mb = 40960;  // "tc_history_mb": budget for the geometry-keyed plane buffers kept between plugin calls
 int tc_history_mb() { return g_tc_history_mb; }
 
-void wslices_build_view(WSlices& ws, const WView& w, int64_t l_begin, int64_t l_count, int S) {
+static void wslices_build_impl(WSlices& ws, const WView& w, const WView& w2, double q1, double q2, int64_t l_begin,
+                               int64_t l_count, int S) {
+  const bool two = w2.p != nullptr;
+  if (two && (w.nK1 != w2.nK1 || w.nK2 != w2.nK2 || w.nL1 != w2.nL1 || w.nL2 != w2.nL2))
+    fail(FRICC_EINVAL, "combined operand: the two views must have the same (K, L) extents");
   if (S < 1 || S > TC_MAX_SLICES) fail(FRICC_EINVAL, "digit planes must be 1..%d", TC_MAX_SLICES);
   const int64_t nK = w.nK1 * w.nK2;
   if (nK <= 0 || l_count <= 0) fail(FRICC_EINVAL, "bad operand shape");
   const int64_t Kpad = ceil_div(nK, TC_BK) * TC_BK, n_tiles = ceil_div(l_count, TC_BN);
   const size_t qbytes = (size_t)n_tiles * S * TC_BN * Kpad;
   // planes of this geometry exist: their exponents predict the new ones (planes_predict_kernel)
-  const bool history = ws.expo_valid && ws.nK == nK && ws.l_count == l_count && ws.S == S && ws.q.n == qbytes;
+  const bool history = !two && ws.expo_valid && ws.nK == nK && ws.l_count == l_count && ws.S == S && ws.q.n == qbytes;
   ws.expo_valid = false;
   if (ws.q.n != qbytes) ws.q.alloc(qbytes);
   if (ws.expo.n != (size_t)(n_tiles * TC_BN)) {
@@ -839,8 +872,8 @@ void wslices_build_view(WSlices& ws, const WView& w, int64_t l_begin, int64_t l_
     ws.expo_valid = true;
     return;
   }
-  ws.expo_valid = true;   // (set before the launches: a failed launch throws and the handle is not used again)
-  if (g_tc_fused_planes && planes_fused_applicable(w, nK) ) {
+  ws.expo_valid = !two;   // (set before the launches: a failed launch throws and the handle is not used again)
+  if (!two && g_tc_fused_planes && planes_fused_applicable(w, nK) ) {
     planes_fused_build(ws, w, l_begin);
     return;
   }
@@ -849,10 +882,10 @@ void wslices_build_view(WSlices& ws, const WView& w, int64_t l_begin, int64_t l_
   const int64_t kpb = std::max<int64_t>(256, ceil_div(nK, 64));
   if (kcontig) {
     dim3 g1((unsigned)ceil_div(l_count, 8), (unsigned)ceil_div(nK, kpb));
-    FRICC_LAUNCH(colmax_view_kernel<true>, g1, 256, 0, w, nK, l_begin, l_count, kpb, colmax.p);
+    FRICC_LAUNCH(colmax_view_kernel<true>, g1, 256, 0, w, w2, q1, q2, nK, l_begin, l_count, kpb, colmax.p);
   } else {
     dim3 g1((unsigned)ceil_div(l_count, 128), (unsigned)ceil_div(nK, kpb));
-    FRICC_LAUNCH(colmax_view_kernel<false>, g1, 128, 0, w, nK, l_begin, l_count, kpb, colmax.p);
+    FRICC_LAUNCH(colmax_view_kernel<false>, g1, 128, 0, w, w2, q1, q2, nK, l_begin, l_count, kpb, colmax.p);
   }
   FRICC_LAUNCH(colexp_kernel, (unsigned)ceil_div(n_tiles * TC_BN, 256), 256, 0, colmax.p, l_count, n_tiles * TC_BN,
                ws.expo.p, ws.colscale.p);
@@ -864,8 +897,21 @@ void wslices_build_view(WSlices& ws, const WView& w, int64_t l_begin, int64_t l_
     attr_set = true;
   }
   dim3 g2((unsigned)n_tiles, (unsigned)(Kpad / TC_BK));
-  if (kcontig) FRICC_LAUNCH(slice_view_kernel<true>, g2, 256, smem, w, nK, l_begin, l_count, Kpad, S, ws.expo.p, ws.q.p);
-  else FRICC_LAUNCH(slice_view_kernel<false>, g2, 256, smem, w, nK, l_begin, l_count, Kpad, S, ws.expo.p, ws.q.p);
+  if (kcontig) FRICC_LAUNCH(slice_view_kernel<true>, g2, 256, smem, w, w2, q1, q2, nK, l_begin, l_count, Kpad, S, ws.expo.p, ws.q.p);
+  else FRICC_LAUNCH(slice_view_kernel<false>, g2, 256, smem, w, w2, q1, q2, nK, l_begin, l_count, Kpad, S, ws.expo.p, ws.q.p);
+}
+
+void wslices_build_view(WSlices& ws, const WView& w, int64_t l_begin, int64_t l_count, int S) {
+  WView none{};
+  none.p = nullptr;
+  wslices_build_impl(ws, w, none, 1.0, 0.0, l_begin, l_count, S);
+}
+
+// planes of the combination q1 * w + q2 * w2 of two views of the same (K, L) extents (fused pairs that share the sign
+// matrix: 1302 + 1202 -> planes of 2 Wvoov - Wvovo); no fp64 copy of the combination is formed
+void wslices_build_view2(WSlices& ws, const WView& w, double q1, const WView& w2, double q2, int64_t l_begin, int64_t l_count,
+                         int S) {
+  wslices_build_impl(ws, w, w2, q1, q2, l_begin, l_count, S);
 }
 
 void wslices_build(WSlices& ws, const double* Wp, int64_t ldw, int64_t nK, int64_t l_count, int S) {
@@ -1212,7 +1258,7 @@ __device__ __forceinline__ void tc_epilogue(const TcParams& p, uint32_t tmem_bas
       }
     }
     const int off0 = R < p.Mpad ? 128 * p.rowsum[R] : 0;  // the 2^e_l offset, units of plane 0
-    ptx::mbar_wait(tmem_full, tl & 1);
+    ptx::mbar_wait_parked(tmem_full, tl & 1);
     ptx::tc_fence_after();
     for (int j = half * 4; j < half * 4 + 4; j++) {
       int32_t r[TC_MAX_SLICES][8];
@@ -1826,6 +1872,18 @@ void contract_dense(fricc_st* T, const TermSpec& ts, Layout& lay, const WSlices&
     tc_launch(lay.dense.p, lay.rowsum.p, lay.cmag.p, lay.nR, lay.Mpad, lay.Kpad, ws, l_begin, out, om, scale, overwrite);
   if (lay.n_rest != 0)
     spmm_csr_view(lay.rest_rowptr.p, lay.rest_kidx.p, lay.rest_vals.p, lay.nR, w, l_begin, ws.l_count, out, om, scale);
+}
+
+// the two halves of contract_dense for callers that bring their own planes / operand views (fused pairs)
+void contract_dense_signs(fricc_st* T, Layout& lay, const WSlices& ws, int64_t l_begin, double* out, const OutMap& om, double scale) {
+  if (ws.nK != lay.nK) fail(FRICC_EINVAL, "digit planes were built for %lld contracted indices, the term has %lld",
+                            (long long)ws.nK, (long long)lay.nK);
+  if (lay.n_rest != T->nnz)
+    tc_launch(lay.dense.p, lay.rowsum.p, lay.cmag.p, lay.nR, lay.Mpad, lay.Kpad, ws, l_begin, out, om, scale, false);
+}
+void contract_rest(Layout& lay, const WView& w, int64_t l_begin, int64_t l_count, double* out, const OutMap& om, double scale) {
+  if (lay.n_rest != 0)
+    spmm_csr_view(lay.rest_rowptr.p, lay.rest_kidx.p, lay.rest_vals.p, lay.nR, w, l_begin, l_count, out, om, scale);
 }
 
 __global__ void panel_axpby_kernel(double* __restrict__ dst, const double* __restrict__ a, double qa,

@@ -37,6 +37,11 @@ bool view_is_panel(const WView& w);
 // planes of the columns [l_begin, l_begin + l_count) of a view, read where the operand lies (no fp64 panel).  Operands
 // whose contracted run is contiguous (the ladder's native W[a,b,c,d]) go through a single-read cluster kernel.
 void wslices_build_view(WSlices& ws, const WView& w, int64_t l_begin, int64_t l_count, int S);
+void wslices_build_view2(WSlices& ws, const WView& w, double q1, const WView& w2, double q2, int64_t l_begin, int64_t l_count,
+                         int S);
+double dense_form(fricc_st* T, const TermSpec& ts, Layout& lay);
+void contract_dense_signs(fricc_st* T, Layout& lay, const WSlices& ws, int64_t l_begin, double* out, const OutMap& om, double scale);
+void contract_rest(Layout& lay, const WView& w, int64_t l_begin, int64_t l_count, double* out, const OutMap& om, double scale);
 void panel_axpby(double* dst, const double* a, double qa, const double* b, double qb, int64_t n);
 // two terms on the same operand view and output map, (R, K) from different axes of T: one dense product (fricc_dense.cu)
 void contract_dense_pair(fricc_st* T, const TermSpec& ts1, Layout& lay1, int q1, const TermSpec& ts2, Layout& lay2, int q2,
