@@ -86,6 +86,12 @@ def parse_args():
     p.add_argument("--no-sweep", action="store_true", help="skip the compression-only sweep (config 5)")
     p.add_argument("--planes", type=int, default=6,
                    help="int8 digit planes of W for the tensor-core form of the contractions (0 = fp64 SpMM only)")
+    p.add_argument("--last-term-parts", type=int, default=1,
+                   help="N>1: the last term before the closing barrier is issued in this many parts, each part's peer stores "
+                        "running under the next part's kernel (A/B; 1 since the stores go through the copy engines)")
+    p.add_argument("--push-kernel", action="store_true", help="N>1: peer stores by the SM store kernel only (A/B of the copy engines)")
+    p.add_argument("--no-overlap-planes", action="store_true",
+                   help="encode the ladder operand after the compression instead of beside it, on a second stream (A/B)")
     p.add_argument("--push-inline", action="store_true",
                    help="N>1: issue the peer stores on the compute stream (A/B of the side-stream push)")
     p.add_argument("--no-fuse", action="store_true",
@@ -368,6 +374,7 @@ class Iteration:
             mk = lambda *shape: self.arena.tensor(shape).zero_()
             if not args.push_inline:
                 self.side = fd.SideStream(device)
+            py_rccsd.set_option("push_copy_engine", 0 if args.push_kernel else 1)
         else:
             self.arena = None
             mk = lambda *shape: torch.zeros(*shape, device=device, dtype=torch.float64)
@@ -397,6 +404,8 @@ class Iteration:
         self.planes = None                      # fricc_wslices_t of the sub-shard currently in Wlad
         self.plane_ms, self.ladder_ms = [], []
         self.cur_sub = -1
+        self.prebuilt = -1
+        self.plane_side = fd.SideStream(device) if self.tc and not args.no_overlap_planes else None
         if self.sub:
             self.fill_sub(0)
             if self.tc and args.w_mode == "invariant":
@@ -418,13 +427,15 @@ class Iteration:
         self.check(self.lib.fricc_fill_uniform(_ptr(self.Wlad), n, a * self.v ** 3, 1000))
         self.cur_sub = s
 
-    def build_planes(self, s, timed=False):
-        """int8 digit planes of sub-shard s, straight from the native layout (single-read cluster kernel)."""
+    def build_planes(self, s, timed=False, stream=None):
+        """int8 digit planes of sub-shard s, straight from the native layout (single-read cluster kernel).  `stream`:
+        the stream the library is currently issuing on when that is not torch's current one (events go there)."""
         torch, fd = self.torch, self.fd
         W = self.wsub(s)
         cols = W.shape[0] * self.v
+        stream = stream or torch.cuda.current_stream()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
+        e0.record(stream)
         if self.planes is not None and self._planes_cols == cols:
             self.check(self.lib.fricc_wslices_update_view(self.planes, _ptr(W), fd.i64x4(W.shape), fd.i64x4(W.stride()),
                                                           b"2323", 0))
@@ -435,9 +446,9 @@ class Iteration:
             self.check(self.lib.fricc_wslices_create_view(_ptr(W), fd.i64x4(W.shape), fd.i64x4(W.stride()), b"2323", 0, cols,
                                                           self.args.planes, ctypes.byref(h)))
             self.planes, self._planes_cols = h, cols
-        e1.record()
+        e1.record(stream)
         if timed:
-            self.plane_ms.append((e0, e1, cols))
+            self.plane_ms.append((e0, e1, cols, stream != torch.cuda.current_stream()))
 
     def ladder(self, T, timer=None, plugin=False):
         """2323 on this rank's a-range.  `plugin`: through contract_DTSpT (planes built inside the call); otherwise the
@@ -462,7 +473,10 @@ class Iteration:
                 else:
                     self.py.contract_DTSpT(W, T, ov, "2323")
                 continue
-            if refreshed:
+            if refreshed and self.prebuilt == s:
+                self.plane_side.join()           # encoded on the side stream while T2 was being compressed
+                self.prebuilt = -1
+            elif refreshed:
                 self.build_planes(s, timed=True)
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
@@ -539,7 +553,7 @@ class Iteration:
         eng.publish(c("1303", self.Wakic, T, self.tmp[1]))
         self.mark("1303")
         if self.multi:
-            eng.contract_in_parts("1203", self.Wakci, T, self.tmp[2], parts=2)   # last before B2: halve what B2 waits for
+            eng.contract_in_parts("1203", self.Wakci, T, self.tmp[2], parts=self.args.last_term_parts)   # last before B2
         else:
             c("1203", self.Wakci, T, self.tmp[2])
         self.mark("1203")
@@ -548,6 +562,17 @@ class Iteration:
 
     def step(self, t2, timer=None):
         self.mark("begin")
+        if self.plane_side is not None and self.sub and self.args.w_mode == "refreshed":
+            # the ladder operand does not depend on T2: its first sub-shard is encoded on a second stream while the
+            # compression (short kernels, host round trips and, N>1, small collectives) leaves most of the GPU idle
+            if self.cur_sub != 0:
+                if timer:
+                    timer.pause()
+                self.fill_sub(0)
+                if timer:
+                    timer.resume()
+            self.plane_side.run(lambda: self.build_planes(0, timed=True, stream=self.plane_side.stream))
+            self.prebuilt = 0
         flat = t2.view(-1)
         j0, cnt = self.fd.index_range(flat.numel(), self.comm.rank, self.comm.world)
         T, T_alt = self.compress_two(flat[j0:j0 + cnt], j0, full=t2)
@@ -766,10 +791,26 @@ def run_b200_arm(args):
     clocks = stop_clock_sampler(proc, cpath) if rank == 0 else None
     stage_ms = it.stage_breakdown(args.steps)
     torch.cuda.synchronize()
+    waits_by_rank = None
+    if world > 1 and not args.as_rank_of:
+        # what each rank waits at the two barriers: tells rank imbalance (one rank waits little) from stores still in flight
+        t = torch.tensor([stage_ms.get("B1", 0.0), stage_ms.get("B2", 0.0)], device=device, dtype=torch.float64)
+        allw = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(allw, t)
+        waits_by_rank = {"B1": [round(float(x[0]), 3) for x in allw], "B2": [round(float(x[1]), 3) for x in allw]}
     lad_ms = [a.elapsed_time(b) for a, b, _ in it.ladder_ms]
     lad_cols = [c for _, _, c in it.ladder_ms]
-    pl_ms = [a.elapsed_time(b) for a, b, _ in it.plane_ms]
-    pl_cols = [c for _, _, c in it.plane_ms]
+    pl_over_ms = [a.elapsed_time(b) for a, b, _, ov in it.plane_ms if ov]
+    solo = [(a, b, c) for a, b, c, ov in it.plane_ms if not ov]
+    if it.tc and it.sub and args.w_mode == "refreshed" and not solo:
+        # every timed encode ran beside the compression: time the kernel ALONE for its roofline line (untimed extra)
+        it.plane_ms.clear()
+        for _ in range(3):
+            it.build_planes(it.cur_sub, timed=True)
+        torch.cuda.synchronize()
+        solo = [(a, b, c) for a, b, c, _ in it.plane_ms]
+    pl_ms = [a.elapsed_time(b) for a, b, _ in solo]
+    pl_cols = [c for _, _, c in solo]
     it.ladder_ms.clear(); it.plane_ms.clear()
 
     # ---- one more (untimed) step from a fixed position of the draw sequence: its outputs do not depend on --steps /
@@ -929,12 +970,13 @@ def run_b200_arm(args):
             "metric": metric_name(o, v, m), "value": s_per_iter, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": False, "scaling": "strong",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": workload_config(args, world),
-            "roofline": roof, "clocks": clocks, "gpu_launches": int(launches),
+            "roofline": roof, "clocks": clocks, "gpu_launches": int(launches), "peer_copies": int(py_rccsd.get_stat("push_copies")),
             "ladder_ms_per_step": sum(lad_ms) / args.steps if lad_ms else None, "stage_ms_per_step": stage_ms,
-            "output_checksums": checks,
+            "output_checksums": checks, "barrier_wait_ms_by_rank": waits_by_rank,
             "schedule": ("single rank: plugin calls (py_rccsd.contract_DTSpT) on the full operands" if world == 1 else
                          "plugin calls on L-slice views; each rank stores its finished slice into every peer's copy over "
-                         "NVLink" + (" on the compute stream" if args.push_inline else " on a side stream under the next term's kernel") +
+                         "NVLink" + ("" if args.push_kernel else " (copy engines where the slice is made of rows >= 4 KB, a store kernel otherwise)") +
+                         (" on the compute stream" if args.push_inline else " on a side stream under the next term's kernel") +
                          "; 2 " + ("NCCL 4-byte all-reduce" if args.nccl_barrier else "device-side flag") + " barriers per step, no NCCL on the data path"),
             "timed_segments": "whole steps" if it.resident else
                               f"sum of segments; the ladder's W is regenerated in HBM between {len(it.sub)} sub-shards (an input)",
@@ -950,8 +992,13 @@ def run_b200_arm(args):
                 "achieved": palg / (sum(pl_ms) * 1e-3) / 1e9, "peak": hbm, "unit": "GB/s",
                 "frac": palg / (sum(pl_ms) * 1e-3) / 1e9 / hbm, "peak_source": hbm_kind,
                 "avg_launch_ms": sum(pl_ms) / len(pl_ms), "launches_timed": len(pl_ms),
+                "avg_launch_ms_beside_the_compression": (sum(pl_over_ms) / len(pl_over_ms)) if pl_over_ms else None,
                 "algorithmic_per_launch": palg / len(pl_ms), "traffic": ncu_traffic_per_launch("planes_fused")}
         line["config"]["ladder_subshards"] = len(it.sub)
+        line["config"]["ladder_planes"] = (
+            "encoded inside the step" + (": the first sub-shard on a second stream beside the compression of T2 (W does not depend "
+                                         "on T2), the others in line" if it.plane_side is not None else ", in line")
+            if args.w_mode == "refreshed" and it.tc else "built once outside the step" if it.tc else None)
         line["config"]["compression"] = {
             "ranges": "range-sharded: each rank scans its contiguous 1/N of T2, all-reduced key histograms, exact sums "
                       "carried rank to rank; norm, D and running sums shared by the step's two draws",

@@ -16,6 +16,9 @@ int64_t launches();
 void reset_device_cache();
 void set_push_ctas_per_sm(int n);  // fricc_peer.cu: grid cap of the peer-store kernels (CTAs per SM)
 void set_push_carveout(int pct);   // fricc_peer.cu: L1/shared split the peer-store kernels ask for (-1: default)
+void set_push_copy_engine(int on);  // fricc_peer.cu: long-row views go through cudaMemcpy(2D)Async instead of the store kernel
+void set_push_min_row_bytes(int n);
+int64_t push_copies();
 }  // namespace fricc
 
 using namespace fricc;
@@ -145,6 +148,8 @@ int fricc_set_option(const char* key, int value) {
   else if (key && strcmp(key, "d_parallel") == 0) set_d_parallel(value);
   else if (key && strcmp(key, "push_ctas_per_sm") == 0) set_push_ctas_per_sm(value);
   else if (key && strcmp(key, "push_carveout") == 0) set_push_carveout(value);
+  else if (key && strcmp(key, "push_copy_engine") == 0) set_push_copy_engine(value);
+  else if (key && strcmp(key, "push_min_row_bytes") == 0) set_push_min_row_bytes(value);
   else if (key && strncmp(key, "spmm_", 5) == 0) set_spmm_option(key, value);
   else if (key && strncmp(key, "tc_", 3) == 0) set_tc_option(key, value);
   else fail(FRICC_EINVAL, "unknown option '%s'", key ? key : "(null)");
@@ -158,6 +163,7 @@ int fricc_get_stat(const char* key, int64_t* value) {
   else if (strcmp(key, "tc_contract_calls") == 0) *value = g_tc_calls;      // fricc_contract calls that took the tensor-core form
   else if (strcmp(key, "spmm_contract_calls") == 0) *value = g_spmm_calls;
   else if (strcmp(key, "fused_pairs") == 0) *value = g_fused_pairs;   // fricc_contract_pair calls that ran as ONE dense product
+  else if (strcmp(key, "push_copies") == 0) *value = push_copies();   // cudaMemcpy(2D)Async calls issued by fricc_push_view
   else if (strcmp(key, "planes_predicted_builds") == 0) *value = planes_predicted_builds();  // builds that reused exponents  // ... and the fp64 SpMM
   else fail(FRICC_EINVAL, "unknown stat '%s'", key);
   FRICC_API_END

@@ -1655,7 +1655,7 @@ static CUtensorMap make_map_i8(const int8_t* base, int64_t rows, int64_t Kpad, i
 
 static int g_tc_persistent = 1;  // "tc_persistent" option: 1 = one CTA per SM looping over tiles, 0 = one CTA per tile
 static int g_tc_pair = 1;        // "tc_pair": 1 = CTA-pair kernel (cta_group::2, 256-row tiles), 0 = the one-CTA kernel
-static int g_tc_sync_shift = 2, g_tc_sync_lag = 2;  // "tc_sync_shift", "tc_sync_lag": granularity of the soft lockstep
+static int g_tc_sync_shift = 4, g_tc_sync_lag = 2;  // "tc_sync_shift", "tc_sync_lag": granularity of the soft lockstep
 static int g_tc_band = 0;        // "tc_band": row tiles per raster band (0 = chosen from the tile sizes)
 static int g_tc_debug = 0;       // "tc_debug": measurement only, see TcParams::debug
 static int g_tc_lockstep = 1;    // "tc_lockstep": pair kernel's soft K-lockstep between the CTAs (an L2 hint)

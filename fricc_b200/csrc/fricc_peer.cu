@@ -57,6 +57,12 @@ static int g_push_ctas_per_sm = 2;  // 2 x 256 threads x 32 registers fit beside
 static int g_push_carveout = 100;  // percent of the L1/shared array configured as shared memory; -1 = leave the default
 void set_push_ctas_per_sm(int n) { g_push_ctas_per_sm = n < 1 ? 1 : n; }
 void set_push_carveout(int pct) { g_push_carveout = pct; }
+static int g_push_copy_engine = 1;          // "push_copy_engine": views of long contiguous rows go through cudaMemcpy(2D)Async
+static int64_t g_push_min_row_bytes = 4096;  // shorter rows: the store kernel
+static int64_t g_push_copies = 0;
+void set_push_copy_engine(int on) { g_push_copy_engine = on ? 1 : 0; }
+void set_push_min_row_bytes(int n) { g_push_min_row_bytes = n < 8 ? 8 : n; }
+int64_t push_copies() { return g_push_copies; }
 // An SM runs CTAs of two kernels side by side only under ONE L1/shared split.  The tensor-core kernel needs ~198 KB of
 // shared memory, i.e. the maximum-shared split; these kernels ask for the same split so that they can share the SMs
 // with it instead of waiting for them to drain.
@@ -138,12 +144,37 @@ void push_view(const double* local, double* const* peer, int n_peers, int self, 
     total *= v.n[i];
   }
   if (total == 0) return;
-  // merge the two smallest axes when they are contiguous with each other (longer runs per warp)
-  if (v.s[1] == v.n[0] * v.s[0]) {
-    v.n[0] *= v.n[1];
-    v.n[1] = v.n[2]; v.s[1] = v.s[2];
-    v.n[2] = v.n[3]; v.s[2] = v.s[3];
-    v.n[3] = 1; v.s[3] = 0;
+  // merge neighbouring axes that are contiguous with each other (longer runs per warp / per copy row)
+  int nd = 4;
+  while (nd > 1 && v.n[nd - 1] == 1) nd--;
+  for (int i = 0; i + 1 < nd;) {
+    if (v.s[i + 1] == v.n[i] * v.s[i]) {
+      v.n[i] *= v.n[i + 1];
+      for (int j = i + 1; j + 1 < nd; j++) { v.n[j] = v.n[j + 1]; v.s[j] = v.s[j + 1]; }
+      nd--;
+      v.n[nd] = 1; v.s[nd] = 0;
+    } else {
+      i++;
+    }
+  }
+  // Views made of long contiguous rows go through the COPY ENGINES: one (2-D) device-to-device copy per peer on the
+  // library's stream.  They need no SM, so they run at link speed under a tensor-core kernel that occupies every SM --
+  // where the store kernel below only trickles (measured: its stores were still draining at the step's barriers).
+  if (g_push_copy_engine && v.s[0] == 1 && v.n[0] * 8 >= g_push_min_row_bytes && (nd <= 2 || (nd == 3 && v.n[2] <= 64))) {
+    const int64_t outer = nd == 3 ? v.n[2] : 1;
+    for (int d = 1; d < n_peers; d++) {
+      const int q = (self + d) % n_peers;
+      for (int64_t k = 0; k < outer; k++) {
+        const int64_t off = nd == 3 ? k * v.s[2] : 0;
+        if (nd == 1)
+          FRICC_CUDA(cudaMemcpyAsync(peer[q] + off, local + off, (size_t)v.n[0] * 8, cudaMemcpyDefault, stream()));
+        else
+          FRICC_CUDA(cudaMemcpy2DAsync(peer[q] + off, (size_t)v.s[1] * 8, local + off, (size_t)v.s[1] * 8, (size_t)v.n[0] * 8,
+                                       (size_t)v.n[1], cudaMemcpyDefault, stream()));
+      }
+    }
+    g_push_copies += (n_peers - 1) * outer;
+    return;
   }
   PeerPtrs pp;
   for (int q = 0; q < MAX_PEERS; q++) pp.p[q] = q < n_peers ? peer[q] : nullptr;

@@ -473,7 +473,7 @@ from .ranges import compress_ranges, compress_ranges_pair, index_range  # noqa: 
 class ViewEngine:
     """Views + plugin calls + peer stores.  One instance per rank.
 
-    slice_axis(term): which of the two free-pair axes is cut across the ranks (the longer one; ties: the major one).
+    slice_axis(term, shape, world): which of the two free-pair axes is cut across the ranks (see there).
     contract(term, W, T, out, w_range=None): this rank's slice of `term`.  `W` is the FULL operand (replicated small
         tensors: ovov, Woooo, Wvoov, Wvovo) unless w_range = (lo, hi) says that `W` already IS the slice [lo, hi) of the
         cut axis (the ladder's vvvv operand, of which a rank only ever holds its part, possibly in sub-shards).
@@ -494,11 +494,20 @@ class ViewEngine:
             torch.cuda.synchronize()
             comm.barrier()          # every rank's counters are zero before anyone stores an epoch
 
+    MIN_ROW_BYTES = 4096          # rows a copy engine moves at link speed (fricc_push_view's own threshold)
+
     @staticmethod
-    def slice_axis(term, w_shape):
+    def slice_axis(term, w_shape, world=1):
+        """0 or 1: which axis of the free pair is cut.  The longer one (ties: the major one) -- except when that would
+        cut the OUTPUT along its innermost axis into rows shorter than MIN_ROW_BYTES while the other axis splits evenly
+        among the ranks: then the other one, so that a rank's slice of the output is made of long contiguous rows (peer
+        stores through the copy engines, contiguous runs for the kernels' own loads and stores)."""
         ax = TERM_AXES[term]
-        e0, e1 = w_shape[ax["wL"][0]], w_shape[ax["wL"][1]]
-        return 0 if e0 >= e1 else 1
+        e = (w_shape[ax["wL"][0]], w_shape[ax["wL"][1]])
+        j = 0 if e[0] >= e[1] else 1
+        if world > 1 and ax["oL"][j] == 3 and -(-e[j] // world) * 8 < ViewEngine.MIN_ROW_BYTES and e[1 - j] % world == 0:
+            j = 1 - j
+        return j
 
     def my_range(self, extent):
         lo, cnt, _ = column_range(extent, self.comm.rank, self.comm.world)
@@ -510,7 +519,7 @@ class ViewEngine:
     def contract(self, term, W, T, out, w_range=None):
         ax = TERM_AXES[term]
         if w_range is None:
-            j = self.slice_axis(term, W.shape)
+            j = self.slice_axis(term, W.shape, self.comm.world)
             lo, hi = self.my_range(W.shape[ax["wL"][j]])
             if hi <= lo:
                 return None
@@ -528,7 +537,7 @@ class ViewEngine:
         term accumulates -- the rest of a rank's copy is overwritten by its peers' stores."""
         ax = TERM_AXES[term]
         if w_range is None:
-            j = self.slice_axis(term, w_shape)
+            j = self.slice_axis(term, w_shape, self.comm.world)
             lo, hi = self.my_range(w_shape[ax["wL"][j]])
         else:
             j, (lo, hi) = 0, w_range
@@ -538,8 +547,8 @@ class ViewEngine:
         """This rank's slice of two terms that go into the same output through the same slicing, as one fused call
         (py_rccsd.contract_DTSpT_pair)."""
         axa, axb = TERM_AXES[term_a], TERM_AXES[term_b]
-        j = self.slice_axis(term_a, W_a.shape)
-        if j != self.slice_axis(term_b, W_b.shape) or axa["oL"] != axb["oL"]:
+        j = self.slice_axis(term_a, W_a.shape, self.comm.world)
+        if j != self.slice_axis(term_b, W_b.shape, self.comm.world) or axa["oL"] != axb["oL"]:
             raise ValueError(f"terms {term_a} and {term_b} are not sliced alike")
         lo, hi = self.my_range(W_a.shape[axa["wL"][j]])
         if hi <= lo:
@@ -553,7 +562,7 @@ class ViewEngine:
         """`contract` + `publish` with this rank's range cut into `parts`: the stores of one part run under the kernel of
         the next, so that only the last part's stores are left when the term is the last one before a barrier."""
         ax = TERM_AXES[term]
-        j = self.slice_axis(term, W.shape)
+        j = self.slice_axis(term, W.shape, self.comm.world)
         lo, hi = self.my_range(W.shape[ax["wL"][j]])
         parts = max(1, min(int(parts), hi - lo))
         for q in range(parts):

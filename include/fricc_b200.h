@@ -56,7 +56,10 @@ int fricc_stream_synchronize(void);
  * "push_ctas_per_sm": grid cap of the peer-store kernels (default 2 CTAs per SM: NVLink-bound, and it leaves thread
  * slots and registers to the contraction kernel that runs concurrently on the compute stream); "push_carveout": the
  * L1/shared split (percent shared) those kernels ask for, default 100 = the split the tensor-core kernel runs under,
- * so that both can be resident on one SM; -1 = the device default.                                               */
+ * so that both can be resident on one SM; -1 = the device default.  "push_copy_engine": 1 (default) = fricc_push_view
+ * moves views that collapse to contiguous rows of at least "push_min_row_bytes" (default 4096) with one
+ * cudaMemcpy(2D)Async per peer -- the copy engines need no SM, so the stores run at link speed under a tensor-core
+ * kernel that occupies every SM; 0 = always the store kernel (same bytes in the same places).                    */
 int fricc_set_option(const char* key, int value);
 /* Two contractions into the SAME output with the same T as ONE dense product where the algebra allows it (an extension;
  * the reference's drivers make the two calls one after the other, e.g. fricc/friccsd.py:347-356 (0112, 0113 -> Wvoov) and
@@ -79,7 +82,7 @@ int fricc_contract_pair(const double* W_a_dev, const int64_t a_shape[4], const i
  * "tc_mode": which form fricc_contract picks -- 0 = always the fp64 SpMM, 1 (default) = the tensor-core form when its
  * cost model says it wins (an FRI-compressed T with at least half of its entries sampled, a large enough product),
  * 2 = always the tensor-core form.  "tc_planes": digit planes it expands W into (default 6 = 48 bits per column).
- * "tc_predict" (1: see fricc_wslices_redone), "tc_pair" (1: CTA-pair tensor-core kernel, 0: one CTA per tile), "tc_lockstep", "tc_band", "tc_fused_planes": 1 (default) = operands whose contracted run is contiguous (the ladder's native W[a,b,c,d]) are
+ * "tc_predict" (1: see fricc_wslices_redone), "tc_pair" (1: CTA-pair tensor-core kernel, 0: one CTA per tile), "tc_lockstep" (1) with "tc_sync_shift" (4: a milestone every 16 k-blocks) and "tc_sync_lag" (2), "tc_band", "tc_fused_planes": 1 (default) = operands whose contracted run is contiguous (the ladder's native W[a,b,c,d]) are
  * expanded by the single-read cluster kernel, 0 = by the two-pass kernels (identical planes).
  * "tc_plane_cache": 1 = fricc_contract keeps the planes of up to 12 device operands across calls, keyed by address,
  * shape and strides and guarded by a fingerprint of 4096 sampled elements (for drivers that hand over the same
@@ -187,7 +190,8 @@ int fricc_push_columns(const double* out_local_dev, void* const* peer_out_dev, i
                        int64_t l_begin, int64_t l_count);
 /* the same exchange for a 4-D strided VIEW (shape, element strides) of this rank's copy of an output -- the L-slice the
  * sharded engine handed to fricc_contract: every element of the view is stored at the same offset of
- * view_peer_dev[q] (q != self), the address of the same view in peer q's copy.                                          */
+ * view_peer_dev[q] (q != self), the address of the same view in peer q's copy.  Long-row views go through the copy
+ * engines, the rest through a store kernel ("push_copy_engine" above); stat "push_copies" counts the copies issued. */
 int fricc_push_view(const double* view_local_dev, void* const* view_peer_dev, int n_peers, int self,
                     const int64_t shape[4], const int64_t strides[4]);
 /* Stream-ordered barrier of the ranks of one node without an NCCL launch: flags_peer_dev[q] = address, in rank q's

@@ -63,7 +63,7 @@ def test_slices_tile_the_contraction(port, term, world):
         if ov is not None:
             assert own.data_ptr() == ov.data_ptr() and own.shape == ov.shape and own.stride() == ov.stride()
             assert ov.data_ptr() >= got.data_ptr()               # a view of the output, not a copy
-            j = eng.slice_axis(term, Wt.shape)
+            j = eng.slice_axis(term, Wt.shape, world)
             lo, hi = eng.my_range(Wt.shape[fd.TERM_AXES[term]["wL"][j]])
             covered.narrow(fd.TERM_AXES[term]["oL"][j], lo, hi - lo).add_(1.0)
     assert np.abs(got.numpy() - want).max() <= 1e-12 * np.abs(want).max()
@@ -92,9 +92,25 @@ def test_presliced_ladder_operand(port, world):
 def test_cut_axis_is_the_longer_free_axis():
     for term, ax in fd.TERM_AXES.items():
         shape = [{"o": 4, "v": 9}[c] for c in ax["w"]]
-        j = fd.ViewEngine.slice_axis(term, shape)
-        e = [shape[ax["wL"][0]], shape[ax["wL"][1]]]
-        assert e[j] == max(e) and (e[0] != e[1] or j == 0)
+        for world in (1, 3):                                     # 4 occupied orbitals do not split evenly among 3 ranks
+            j = fd.ViewEngine.slice_axis(term, shape, world)
+            e = [shape[ax["wL"][0]], shape[ax["wL"][1]]]
+            assert e[j] == max(e) and (e[0] != e[1] or j == 0)
+
+
+def test_cut_axis_avoids_short_output_rows_when_the_other_axis_splits_evenly():
+    """Headline shape on 8 ranks: cutting v would leave 400-byte rows in Wvoov (0112, 0113, 0313) and in tmp2 (1203);
+    o = 40 splits evenly, so those terms are cut along o and every rank's output slice is contiguous."""
+    dims = {"o": 40, "v": 400}
+    switched = set()
+    for term, ax in fd.TERM_AXES.items():
+        shape = [dims[c] for c in ax["w"]]
+        j1, j8 = fd.ViewEngine.slice_axis(term, shape, 1), fd.ViewEngine.slice_axis(term, shape, 8)
+        if j1 != j8:
+            switched.add(term)
+            assert ax["oL"][j1] == 3 and ax["oL"][j8] != 3
+        assert fd.ViewEngine.slice_axis(term, shape, 7) == j1    # 40 does not split among 7: the longer axis stays
+    assert switched == {"0112", "0113", "0313", "1203"}
 
 
 @pytest.mark.parametrize("parts", [1, 2, 3])

@@ -130,7 +130,7 @@ def main():
         check(L.fricc_set_option(b"tc_pair", 1))
         check(L.fricc_set_option(b"tc_lockstep", 1))
         check(L.fricc_set_option(b"tc_debug", 0))
-        check(L.fricc_set_option(b"tc_sync_shift", 2))
+        check(L.fricc_set_option(b"tc_sync_shift", 4))
         check(L.fricc_set_option(b"tc_sync_lag", 2))
         check(L.fricc_wslices_destroy(h))
     del W, out
