@@ -86,12 +86,15 @@ def parse_args():
     p.add_argument("--no-sweep", action="store_true", help="skip the compression-only sweep (config 5)")
     p.add_argument("--planes", type=int, default=6,
                    help="int8 digit planes of W for the tensor-core form of the contractions (0 = fp64 SpMM only)")
-    p.add_argument("--last-term-parts", type=int, default=1,
+    p.add_argument("--last-term-parts", type=int, default=2,
                    help="N>1: the last term before the closing barrier is issued in this many parts, each part's peer stores "
-                        "running under the next part's kernel (A/B; 1 since the stores go through the copy engines)")
-    p.add_argument("--push-kernel", action="store_true", help="N>1: peer stores by the SM store kernel only (A/B of the copy engines)")
-    p.add_argument("--no-overlap-planes", action="store_true",
-                   help="encode the ladder operand after the compression instead of beside it, on a second stream (A/B)")
+                        "running under the next part's kernel")
+    p.add_argument("--push-copy-engine", action="store_true",
+                   help="N>1: peer stores of long-row slices through cudaMemcpy(2D)Async instead of the store kernel (A/B; "
+                        "measured slower for the whole step, see fricc_peer.cu)")
+    p.add_argument("--overlap-planes", action="store_true",
+                   help="encode the ladder's first sub-shard on a second, lower-priority stream beside the compression "
+                        "instead of after it (A/B)")
     p.add_argument("--push-inline", action="store_true",
                    help="N>1: issue the peer stores on the compute stream (A/B of the side-stream push)")
     p.add_argument("--no-fuse", action="store_true",
@@ -373,8 +376,9 @@ class Iteration:
             self.arena = fd.SymmArena(nb, comm, device)
             mk = lambda *shape: self.arena.tensor(shape).zero_()
             if not args.push_inline:
-                self.side = fd.SideStream(device)
-            py_rccsd.set_option("push_copy_engine", 0 if args.push_kernel else 1)
+                # (same priority as the step's own stream, which --overlap-planes raises)
+                self.side = fd.SideStream(device, priority=-1 if args.overlap_planes else 0)
+            py_rccsd.set_option("push_copy_engine", 1 if args.push_copy_engine else 0)
         else:
             self.arena = None
             mk = lambda *shape: torch.zeros(*shape, device=device, dtype=torch.float64)
@@ -405,7 +409,7 @@ class Iteration:
         self.plane_ms, self.ladder_ms = [], []
         self.cur_sub = -1
         self.prebuilt = -1
-        self.plane_side = fd.SideStream(device) if self.tc and not args.no_overlap_planes else None
+        self.plane_side = fd.SideStream(device) if self.tc and args.overlap_planes else None
         if self.sub:
             self.fill_sub(0)
             if self.tc and args.w_mode == "invariant":
@@ -646,6 +650,16 @@ def compression_sweep(comm, device, torch, fd, sizes=(1.0e8, 2.56e8, 1.0e9), m=1
         out.append({"N": n, "m": mm, "sampler": "systematic", "how": f"range-sharded over {world} GPU(s)",
                     "ms_per_compression": round(ms, 3), "elements_per_s": n / (ms * 1e-3),
                     "frac_of_measured_hbm": bcomp / (ms * 1e-3) / 1e9 / (peak * world)})
+        # the chunked pivotal sampler (Alg. A.2, fri_utils.cpp:176-362) with one chunk per rank: the pivotal family's
+        # range-sharded form (no state crosses a chunk boundary); library rand() stream, every rank's copy in step
+        try:
+            ms = timed(lambda: ranges.compress_ranges(x, j0, dims, mm, comm, "fri", "parallel"))
+            out.append({"N": n, "m": mm, "sampler": "parallel (chunked pivotal, Alg. A.2)",
+                        "how": f"range-sharded over {world} GPU(s), one chunk per rank",
+                        "ms_per_compression": round(ms, 3), "elements_per_s": n / (ms * 1e-3),
+                        "frac_of_measured_hbm": bcomp / (ms * 1e-3) / 1e9 / (peak * world)})
+        except Exception as e:       # e.g. the reference's own exit when a one-chunk budget is a hair off an integer
+            out.append({"N": n, "m": mm, "sampler": "parallel (chunked pivotal, Alg. A.2)", "error": str(e)[:200]})
         del x
         if rank == 0 and n <= 3.0e8:
             g.manual_seed(20)
@@ -730,6 +744,17 @@ def ncu_traffic_per_launch(which):
 
 
 def run_b200_arm(args):
+    if args.overlap_planes and not getattr(args, "_on_priority_stream", False):
+        # the step's own stream gets the higher priority, so that the short kernels of the compression are scheduled
+        # ahead of the pending blocks of the plane encode that runs beside them on the (default-priority) second stream
+        import torch
+
+        args._on_priority_stream = True
+        local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+        if int(os.environ.get("WORLD_SIZE", "1")) > 1 or args.gpus <= 1:
+            torch.cuda.set_device(local_rank)
+            with torch.cuda.stream(torch.cuda.Stream(device=local_rank, priority=-1)):
+                return run_b200_arm(args)
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -975,7 +1000,7 @@ def run_b200_arm(args):
             "output_checksums": checks, "barrier_wait_ms_by_rank": waits_by_rank,
             "schedule": ("single rank: plugin calls (py_rccsd.contract_DTSpT) on the full operands" if world == 1 else
                          "plugin calls on L-slice views; each rank stores its finished slice into every peer's copy over "
-                         "NVLink" + ("" if args.push_kernel else " (copy engines where the slice is made of rows >= 4 KB, a store kernel otherwise)") +
+                         "NVLink" + (" (copy engines where the slice is made of rows >= 4 KB, a store kernel otherwise)" if args.push_copy_engine else "") +
                          (" on the compute stream" if args.push_inline else " on a side stream under the next term's kernel") +
                          "; 2 " + ("NCCL 4-byte all-reduce" if args.nccl_barrier else "device-side flag") + " barriers per step, no NCCL on the data path"),
             "timed_segments": "whole steps" if it.resident else

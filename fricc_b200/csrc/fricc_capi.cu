@@ -1170,6 +1170,22 @@ int fricc_shard_emit_systematic(fricc_shard_t s, int64_t n_sample, int32_t draw,
   FRICC_API_END
 }
 
+int fricc_shard_sample_chunk(fricc_shard_t s, int64_t budget, double t, double a, double chunk_norm, const int32_t* draws,
+                             int64_t n_draws, int64_t* n_consumed, int64_t* S_dev) {
+  FRICC_API_BEGIN
+  check_shard(s);
+  if (s->ps.absval) fail(FRICC_EINVAL, "fricc_shard_use_probabilities first");
+  if (budget > 0 && !S_dev) fail(FRICC_EINVAL, "null sample buffer");
+  DrawSource ds;
+  ds.from_stream = (draws == nullptr);
+  ds.host = draws;
+  ds.n = draws ? n_draws : 0;
+  int64_t used = 0;
+  sample_chunk(s->ps, s->n, s->j0, budget, t, a, chunk_norm, ds, &used, S_dev);
+  if (n_consumed) *n_consumed = used;
+  FRICC_API_END
+}
+
 int fricc_shard_check(fricc_shard_t s) {
   FRICC_API_BEGIN
   check_shard(s);

@@ -56,6 +56,11 @@ void sample_pivotal_probs(int64_t n_sample, const double* p_dev, int64_t n, cons
 void parallel_sample(int64_t n_sample, const double* p_dev, int64_t n, int n_chunks, const DrawSource& draws,
                      int64_t* consumed, int64_t* S_dev);
 
+// the per-chunk part of parallel_sample for ONE chunk held by this rank (fri_utils.cpp:296-356); budgets by the caller
+struct PSrc;
+void sample_chunk(const PSrc& ps, int64_t n, int64_t j0, int64_t g, double t, double a, double norm, const DrawSource& draws,
+                  int64_t* consumed, int64_t* S_dev);
+
 // final state of a pivotal walk (device struct shared by the chain kernel and the parallel sampler)
 struct PivotalState {
   double a;           // running sum after the last visited element

@@ -57,7 +57,7 @@ static int g_push_ctas_per_sm = 2;  // 2 x 256 threads x 32 registers fit beside
 static int g_push_carveout = 100;  // percent of the L1/shared array configured as shared memory; -1 = leave the default
 void set_push_ctas_per_sm(int n) { g_push_ctas_per_sm = n < 1 ? 1 : n; }
 void set_push_carveout(int pct) { g_push_carveout = pct; }
-static int g_push_copy_engine = 1;          // "push_copy_engine": views of long contiguous rows go through cudaMemcpy(2D)Async
+static int g_push_copy_engine = 0;          // "push_copy_engine": 1 = views of long contiguous rows go through cudaMemcpy(2D)Async
 static int64_t g_push_min_row_bytes = 4096;  // shorter rows: the store kernel
 static int64_t g_push_copies = 0;
 void set_push_copy_engine(int on) { g_push_copy_engine = on ? 1 : 0; }
@@ -157,9 +157,12 @@ void push_view(const double* local, double* const* peer, int n_peers, int self, 
       i++;
     }
   }
-  // Views made of long contiguous rows go through the COPY ENGINES: one (2-D) device-to-device copy per peer on the
-  // library's stream.  They need no SM, so they run at link speed under a tensor-core kernel that occupies every SM --
-  // where the store kernel below only trickles (measured: its stores were still draining at the step's barriers).
+  // Optional ("push_copy_engine" = 1): views made of long contiguous rows through the COPY ENGINES, one (2-D) device-to-
+  // device copy per peer on the library's stream.  They need no SM, so the terms they run under are not slowed down
+  // (8 GPUs, headline shape: the four terms before the first barrier 10.2 ms instead of 15.8) -- but the copies
+  // themselves drain late (barrier waits 4.3 + 5-10 ms instead of 0.35 + 2.1) and, with the host running far ahead,
+  // the terms behind the first barrier stalled for tens of ms in the measurement; the step as a whole was slower
+  // (0.080 s against 0.071), so the store kernel stays the default.
   if (g_push_copy_engine && v.s[0] == 1 && v.n[0] * 8 >= g_push_min_row_bytes && (nd <= 2 || (nd == 3 && v.n[2] <= 64))) {
     const int64_t outer = nd == 3 ? v.n[2] : 1;
     for (int d = 1; d < n_peers; d++) {

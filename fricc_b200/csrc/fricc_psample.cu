@@ -25,16 +25,8 @@ namespace fricc {
 
 // fri_utils.cpp:303-322.  q: this call's private copy of the probabilities (the reference copies every chunk into
 // qj[j], :196-198,219), modified in place.
-__global__ void rescale_chunks_kernel(double* __restrict__ q, int64_t step, int64_t rem, int n_chunks,
-                                      const double* __restrict__ t, const double* __restrict__ a,
-                                      const int64_t* __restrict__ g, const double* __restrict__ norms) {
-  const int j = blockIdx.x * blockDim.x + threadIdx.x;
-  if (j >= n_chunks) return;
-  const int64_t len = step + (j + 1 == n_chunks ? rem : 0);
-  double* qj = q + (int64_t)j * step;
-  double sj = norms[j];
-  const double gj = (double)g[j], tj = t[j];
-  if (gj > a[j]) {
+__device__ void rescale_chunk(double* __restrict__ qj, int64_t len, double tj, double aj, double gj, double sj) {
+  if (gj > aj) {
     for (int64_t i = 0; i < len; i++) {
       const double qi = qj[i];
       double y = __ddiv_rn(qi, tj);
@@ -46,7 +38,7 @@ __global__ void rescale_chunks_kernel(double* __restrict__ q, int64_t step, int6
       }
       qj[i] = y;
     }
-  } else if (gj < a[j]) {
+  } else if (gj < aj) {
     const double omt = __dsub_rn(1., tj);
     for (int64_t i = 0; i < len; i++) {
       const double qi = qj[i];
@@ -60,6 +52,23 @@ __global__ void rescale_chunks_kernel(double* __restrict__ q, int64_t step, int6
       qj[i] = y;
     }
   }
+}
+
+__global__ void rescale_chunks_kernel(double* __restrict__ q, int64_t step, int64_t rem, int n_chunks,
+                                      const double* __restrict__ t, const double* __restrict__ a,
+                                      const int64_t* __restrict__ g, const double* __restrict__ norms) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n_chunks) return;
+  rescale_chunk(q + (int64_t)j * step, step + (j + 1 == n_chunks ? rem : 0), t[j], a[j], (double)g[j], norms[j]);
+}
+
+// one chunk, its budget by value (the rank-distributed form below)
+__global__ void rescale_one_chunk_kernel(double* __restrict__ q, int64_t len, double t, double a, double g, double norm) {
+  if (blockIdx.x == 0 && threadIdx.x == 0) rescale_chunk(q, len, t, a, g, norm);
+}
+
+__global__ void materialize_kernel(PSrc ps, int64_t n, double* __restrict__ q) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) q[i] = ps(i);
 }
 
 __global__ void add_offset_kernel(int64_t* __restrict__ S, int64_t count, int64_t offset) {
@@ -179,6 +188,38 @@ void parallel_sample(int64_t n_sample, const double* p_dev, int64_t n, int n_chu
   }
   FRICC_CUDA(cudaStreamSynchronize(stream()));
   *consumed = used;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Alg. A.2 with the chunks on DIFFERENT RANKS (parallel_sample as the distributed sampler).  A rank
+// holds one chunk: the probabilities `ps` of its n elements (implicit: |x| / r * n' with D zeroed, or explicit).  The
+// budget arithmetic -- |q|_1, |q_j|_1, a_j, t_j, g_j, the pivotal draw over the fractional parts (fri_utils.cpp:191-275)
+// -- needs one double per rank and is done by the caller (fricc_b200/ranges.py) with the exact sums of fricc_escan.cu;
+// this is the per-chunk part (:296-356): copy, rescale the leading probabilities to the integer mass g, sample_pivotal,
+// offset by the chunk's first flat index.  No state crosses the chunk boundary, which is what lets the chunks run on
+// different GPUs at the same time; each takes its own draws (the reference's threads share rand() in a race).
+// ---------------------------------------------------------------------------------------------------------------------
+void sample_chunk(const PSrc& ps, int64_t n, int64_t j0, int64_t g, double t, double a, double norm, const DrawSource& draws,
+                  int64_t* consumed, int64_t* S_dev) {
+  *consumed = 0;
+  if (n < 1) {
+    if (g != 0) fail(FRICC_ECOUNT, "sample_chunk: an empty chunk with a non-zero budget");
+    return;
+  }
+  if (g < 0 || g > n) fail(FRICC_ECOUNT, "sample_chunk: budget %lld outside [0, %lld]", (long long)g, (long long)n);
+  DevBuf<double> q((size_t)n);
+  FRICC_LAUNCH(materialize_kernel, (unsigned)std::min<int64_t>(ceil_div(n, 256), (int64_t)num_sms() * 8), 256, 0, ps, n, q.p);
+  FRICC_LAUNCH(rescale_one_chunk_kernel, 1, 32, 0, q.p, n, t, a, (double)g, norm);
+  int64_t u = 0;
+  if (n == 1 || g == 0) {
+    u = trivial_pivotal(g, q.p, n);
+    if (draws.from_stream && u > 0) rand_skip(u);
+  } else {
+    sample_pivotal_probs(g, q.p, n, draws, &u, S_dev);
+    if (j0 > 0) FRICC_LAUNCH(add_offset_kernel, (unsigned)ceil_div(g, 256), 256, 0, S_dev, g, j0);
+  }
+  FRICC_CUDA(cudaStreamSynchronize(stream()));  // q is a temporary of this scope
+  *consumed = u;
 }
 
 }  // namespace fricc

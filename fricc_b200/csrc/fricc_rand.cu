@@ -7,7 +7,7 @@
 //     r[i] = r[i-31]                                                          i = 31..33
 //     r[i] = r[i-31] + r[i-3]  (mod 2^32)                                     i >= 34
 //     k-th output of rand() = r[k + 344] >> 1
-// (tests/test_rand.py checks this against the C library's srand()/rand()).
+// (tests/test_capi_symbols.py checks this against the C library's srand()/rand()).
 //
 // Pivotal sampling consumes one draw per visited element (2.56e8 at the headline shape), far too many to produce on the
 // host, so the same stream is also generated ON THE DEVICE: the recurrence is linear over Z/2^32 with characteristic

@@ -443,8 +443,8 @@ class SideStream:
     side stream, ordered behind everything queued on the current stream so far; join(): the current stream waits for
     everything issued on the side stream (call it before a barrier, or before the pushed output is written again)."""
 
-    def __init__(self, device):
-        self.stream = torch.cuda.Stream(device=device)
+    def __init__(self, device, priority=0):
+        self.stream = torch.cuda.Stream(device=device, priority=priority)
         self.L = _lib.lib()
 
     def run(self, fn):
@@ -461,7 +461,7 @@ class SideStream:
 
 
 # range-sharded compression (x split by contiguous flat-index ranges; all-reduced key histograms): fricc_b200/ranges.py
-from .ranges import compress_ranges, compress_ranges_pair, index_range  # noqa: E402,F401
+from .ranges import compress_ranges, compress_ranges_pair, index_range, chunk_range  # noqa: E402,F401
 
 
 # ======================================================================================================================

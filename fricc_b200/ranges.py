@@ -14,6 +14,7 @@ What crosses NVLink per compression (m entries kept, G ranks):
 All arithmetic is in libfricc_b200.so (fricc_shard.cu, fricc_escan.cu); torch moves bytes.
 """
 import ctypes
+import math
 
 import numpy as np
 import torch
@@ -37,6 +38,82 @@ def index_range(n_total, rank, world):
     base, extra = divmod(int(n_total), int(world))
     j0 = rank * base + min(rank, extra)
     return j0, base + (1 if rank < extra else 0)
+
+
+def chunk_range(n_total, rank, world):
+    """parallel_sample's own chunking (fri_utils.cpp:183-184,215-218): `world` chunks of n // world elements, the last
+    one takes the remainder.  The ranges compress_ranges(..., sampling_method="parallel") has to be given for its result
+    to be the reference's parallel_sample with `world` threads."""
+    step, rem = divmod(int(n_total), int(world))
+    return rank * step, step + (rem if rank == world - 1 else 0)
+
+
+class _Solo:
+    """A communicator of one: exact_sum(shard, _SOLO) is the exact left-to-right sum of THIS shard alone."""
+    rank, world, group = 0, 1, None
+
+
+_SOLO = _Solo()
+
+
+def pivotal_host(n_sample, probs, draws):
+    """sample_pivotal (fri_utils.cpp:63-127) on a handful of numbers -- the fractional budgets of parallel_sample's
+    chunks (:268), one per rank -- in host arithmetic (IEEE double, the reference's operations in its order).
+    draws: rand() values, consumed one per element visited.  Returns (S, draws consumed); the reference's two exits
+    (acceptance probability outside [0,1]; wrong number of samples) are raised as FriccError."""
+    probs = [float(p) for p in probs]
+    S, i, used = [], 0, 0
+    if not probs:
+        raise _lib.FriccError(_lib.EINVAL, "pivotal_host: empty probability vector")
+    a = probs[0]
+    last = len(probs) - 1
+    for j in range(1, len(probs)):
+        a += probs[j]
+        if used >= len(draws):
+            raise _lib.FriccError(_lib.EDRAWS, "parallel sampling: not enough budget draws (one per rank after the first)")
+        rn = int(draws[used]) / 2147483647.0
+        used += 1
+        if a < 1.0:
+            if a != 0.0 and rn < probs[j] / a:       # 0/0 is NaN in the reference: the comparison is false
+                i = j
+        else:
+            a -= 1.0
+            pa = (1.0 - probs[j]) / (1.0 - a)
+            if pa > 1 or pa < 0:
+                raise _lib.FriccError(_lib.EPIVOTAL, "ERROR IN PIVOTAL SAMPLING: acceptance probability outside [0,1] "
+                                                     "(reference: fri_utils.cpp:84-94)")
+            if rn < pa:
+                S.append(i)
+                i = j
+            else:
+                S.append(j)
+        if len(S) == n_sample:
+            break
+        if j == last:
+            if abs(a - 1.0) < 1e-5:
+                S.append(i)
+            else:
+                raise _lib.FriccError(_lib.ECOUNT, "ERROR IN PIVOTAL SAMPLING: the walk ended short of n_sample "
+                                                   "(reference: fri_utils.cpp:106-118)")
+    if len(S) != n_sample:
+        raise _lib.FriccError(_lib.ECOUNT, "ERROR IN PIVOTAL SAMPLING: wrong number of samples (reference: fri_utils.cpp:121-124)")
+    return S, used
+
+
+def chunk_budgets(n_sample, norms, q_norm, budget_draws):
+    """parallel_sample's budget arithmetic (fri_utils.cpp:214-275) for chunks with exact 1-norms `norms`, |q|_1 = q_norm:
+    a_j = n_sample * |q_j| / |q|, t_j = a_j - floor(a_j), g_j = floor(a_j), and the c = n_sample - sum(g) spare samples go
+    to the chunks picked by sample_pivotal(c, t).  Returns (a, t, g, draws consumed).  Pure host logic."""
+    a = [n_sample * float(nj) / q_norm for nj in norms]
+    t = [aj - math.floor(aj) for aj in a]
+    g = [int(math.floor(aj)) for aj in a]
+    c = int(n_sample) - sum(g)
+    if c < 0:
+        raise _lib.FriccError(_lib.ECOUNT, "parallel_sample: the integer budgets exceed n_sample")
+    picked, used = pivotal_host(c, t, budget_draws)
+    for j in picked:
+        g[j] += 1
+    return a, t, g, used
 
 
 def locate_threshold(hist_fn, want, small_bin=SMALL_BIN):
@@ -185,6 +262,90 @@ def global_candidates(shard, comm, want):
     return keys[:want], idx[:want]
 
 
+def _sample_systematic(shard, comm, nsamp, nD, idx, flat, mm, count, draws):
+    """sample_systematic (fri_utils.cpp:129-159) over p = |x| / r * n', p[D] = 0 (never materialised): the running sums of
+    p are computed once and shared by the `count` draws.  Fills flat[k*mm + ...] with this rank's part; returns the draws
+    one compression consumes (1)."""
+    L = shard.L
+    the_draws = []
+    for k in range(count):
+        if draws is None:
+            d = (ctypes.c_int32 * 1)()
+            check(L.fricc_rand_fill(d, 1))
+            the_draws.append(int(d[0]))
+        else:
+            d = np.asarray(draws[k]).reshape(-1)
+            if d.size < 1:
+                raise _lib.FriccError(_lib.EDRAWS, "systematic sampling needs one draw")
+            the_draws.append(int(d[0]))
+    if nsamp > 0:
+        exact_sum(shard, comm)          # exact running sums of p at the chunk starts: shared by all draws
+    for k in range(count):
+        if nD > 0 and comm.rank == 0:   # summed over ranks below: rank 0 contributes D
+            flat[k * mm: k * mm + nD] = idx[:nD]
+        if nsamp > 0:
+            check(L.fricc_shard_emit_systematic(shard.h, nsamp, the_draws[k], _ptr(flat[k * mm + nD:])))
+    return 1
+
+
+def _sample_parallel(shard, comm, nsamp, nD, idx, flat, mm, count, draws):
+    """parallel_sample (fri_utils.cpp:176-362, "Alg. A.2") with ONE CHUNK PER RANK over the same probabilities: exact
+    |q|_1 over all ranks and |q_j|_1 per chunk (the scan stages), budgets on the host (chunk_budgets), then every rank
+    rescales and samples its own chunk with the parallel pivotal sampler -- no state crosses a chunk boundary, so the
+    ranks run at the same time.
+
+    draws: None -> the library's rand() stream.  Every rank's copy advances by (world - 1) + N per compression: the
+    budget draw reads the first world - 1 values, chunk j reads from position (world - 1) + j0 on (it consumes fewer than
+    its length), so the chunks' draws never overlap and the result does not depend on which rank finishes first (the
+    reference's threads share rand() in a race, :345).  Or, per compression, a pair (budget_draws, chunk_draws) of int32
+    arrays: the values for the budget draw (same on every rank) and for THIS rank's chunk.
+    Returns ((budget draws consumed, this chunk's draws consumed) of the last compression, first error or None)."""
+    L, dev = shard.L, shard.x.device
+    rank, world = comm.rank, comm.world
+    consumed, failure = (0, 0), None
+    norms = q_norm = None
+    if nsamp > 0:
+        q_norm = float(exact_sum(shard, comm).item())                 # one_norm(q), :191
+        own = exact_sum(shard, _SOLO)                                  # one_norm(qj[j]), :221
+        if world > 1:
+            allg = torch.empty(world, dtype=torch.float64, device=dev)
+            comm.all_gather(allg, own)
+            norms = allg.cpu().tolist()
+        else:
+            norms = [float(own.item())]
+    for k in range(count):
+        if nD > 0 and rank == 0:
+            flat[k * mm: k * mm + nD] = idx[:nD]
+        if nsamp == 0:
+            continue
+        if draws is None:
+            nb = world - 1
+            bd = (ctypes.c_int32 * max(nb, 1))()
+            if nb > 0:
+                check(L.fricc_rand_fill(bd, nb))
+            budget_draws, chunk_draws = [int(v) for v in bd[:nb]], None
+        else:
+            budget_draws = np.asarray(draws[k][0], dtype=np.int32).reshape(-1)
+            chunk_draws = np.ascontiguousarray(np.asarray(draws[k][1], dtype=np.int32).reshape(-1))
+        used = ctypes.c_int64(0)
+        try:
+            a, t, g, used0 = chunk_budgets(nsamp, norms, q_norm, budget_draws)
+            lb = sum(g[:rank])
+            if chunk_draws is None:
+                check(L.fricc_rand_skip(shard.j0))
+                dptr, dn = None, 0
+            else:
+                dptr, dn = ctypes.c_void_p(chunk_draws.ctypes.data), chunk_draws.size
+            check(L.fricc_shard_sample_chunk(shard.h, g[rank], t[rank], a[rank], norms[rank], dptr, dn, ctypes.byref(used),
+                                             _ptr(flat[k * mm + nD + lb:])))
+            consumed = (used0, int(used.value))
+        except _lib.FriccError as e:          # raised on every rank after the collectives below (compress_ranges_multi)
+            failure = failure or e
+        if chunk_draws is None:
+            check(L.fricc_rand_skip(shard.n_total - shard.j0 - int(used.value)))
+    return consumed, failure
+
+
 def compress_ranges(x_local, j0, dims, m, comm, compression="fri", sampling_method="systematic", draws=None):
     """SparseTensor4d(tensor, dims, m, compression, sampling_method) for a tensor whose flattened elements
     [j0, j0 + x_local.numel()) live on this rank (CUDA, float64, contiguous).  Every rank returns the full, identical
@@ -192,8 +353,11 @@ def compress_ranges(x_local, j0, dims, m, comm, compression="fri", sampling_meth
 
     draws: None -> the library's glibc-compatible rand() stream (every rank advances its copy by the one draw the
     reference's systematic sampler consumes); or an int32 array whose first element is that draw.
-    sampling_method "pivotal" is not range-sharded (its walk carries four state words and one draw per element; use
-    dist.compress_pair, which runs whole compressions task-parallel) and raises NotImplementedError."""
+    sampling_method "parallel": the chunked pivotal sampler (parallel_sample, "Alg. A.2", fri_utils.cpp:176-362) with one
+    chunk per rank -- see _sample_parallel for the draws; with ranges from chunk_range() the samples are the reference's
+    parallel_sample with `world` threads running in chunk order.
+    sampling_method "pivotal" (ONE ordered walk over all N elements) is not range-sharded: use dist.compress_pair, which
+    runs whole compressions task-parallel; here it raises NotImplementedError."""
     return compress_ranges_multi(x_local, j0, dims, m, comm, compression, sampling_method,
                                  draws=None if draws is None else [draws], count=1)[0]
 
@@ -220,9 +384,10 @@ def compress_ranges_multi(x_local, j0, dims, m, comm, compression="fri", samplin
         raise ValueError(f"need 0 <= m <= N (m={m}, N={n_total})")   # the reference's driver check, friccsd.py:69-72
     if compression not in ("fri", "largest"):
         raise ValueError(f"unknown compression '{compression}'")
-    if compression == "fri" and sampling_method != "systematic":
-        raise NotImplementedError("range-sharded compression implements the systematic sampler; use dist.compress_pair "
-                                  "for pivotal")
+    if compression == "fri" and sampling_method not in ("systematic", "parallel"):
+        raise NotImplementedError("range-sharded compression implements the systematic sampler and the chunked pivotal "
+                                  "sampler ('parallel', Alg. A.2 with one chunk per rank); the single ordered pivotal walk "
+                                  "is not range-sharded -- use dist.compress_pair for it")
     if x_local.dtype != torch.float64 or not x_local.is_cuda or not x_local.is_contiguous():
         raise TypeError("x_local must be a contiguous CUDA float64 tensor")
     if draws is not None and len(draws) < count:
@@ -232,7 +397,7 @@ def compress_ranges_multi(x_local, j0, dims, m, comm, compression="fri", samplin
     shard = _Shard(x_local.view(-1), j0, n_total)
     mm = max(m, 1)
     try:
-        consumed = 0
+        consumed, failure = 0, None
         # the `count` index / value lists side by side: ONE all-reduce each
         flat = torch.zeros(count * mm, dtype=torch.int64, device=dev)
         vals = torch.zeros(count * mm, dtype=torch.float64, device=dev)
@@ -260,27 +425,11 @@ def compress_ranges_multi(x_local, j0, dims, m, comm, compression="fri", samplin
             if nD > 0:
                 key_cut, idx_cut = (int(v) for v in torch.stack([keys[nD - 1], idx[nD - 1]]).cpu().tolist())
             nsamp = m - nD
-            # ---- sample_systematic (fri_utils.cpp:129-159) over p = |x| / r * n', p[D] = 0 (never materialised)
-            the_draws = []
-            for k in range(count):
-                if draws is None:
-                    d = (ctypes.c_int32 * 1)()
-                    check(L.fricc_rand_fill(d, 1))
-                    the_draws.append(int(d[0]))
-                else:
-                    d = np.asarray(draws[k]).reshape(-1)
-                    if d.size < 1:
-                        raise _lib.FriccError(_lib.EDRAWS, "systematic sampling needs one draw")
-                    the_draws.append(int(d[0]))
-            consumed = 1
             check(L.fricc_shard_use_probabilities(shard.h, r, nsamp, ctypes.c_uint64(key_cut), ctypes.c_uint64(idx_cut)))
-            if nsamp > 0:
-                exact_sum(shard, comm)          # exact running sums of p at the chunk starts: shared by all draws
-            for k in range(count):
-                if nD > 0 and comm.rank == 0:   # summed over ranks below: rank 0 contributes D
-                    flat[k * mm: k * mm + nD] = idx[:nD]
-                if nsamp > 0:
-                    check(L.fricc_shard_emit_systematic(shard.h, nsamp, the_draws[k], _ptr(flat[k * mm + nD:])))
+            if sampling_method == "parallel":
+                consumed, failure = _sample_parallel(shard, comm, nsamp, nD, idx, flat, mm, count, draws)
+            else:
+                consumed = _sample_systematic(shard, comm, nsamp, nD, idx, flat, mm, count, draws)
             _all_reduce(comm, flat)
             n_exact = nD
         for k in range(count):
@@ -288,8 +437,10 @@ def compress_ranges_multi(x_local, j0, dims, m, comm, compression="fri", samplin
         _all_reduce(comm, vals)
         # a kernel error on any rank (some p > 1: fri_utils.cpp:383-395) is raised on every rank
         err = torch.zeros(1, dtype=torch.int64, device=dev)
-        msg = None
-        if compression == "fri":
+        msg = failure
+        if failure is not None:
+            err += 1
+        if compression == "fri" and failure is None:
             try:
                 check(L.fricc_shard_check(shard.h))
             except _lib.FriccError as e:

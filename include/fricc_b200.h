@@ -56,10 +56,10 @@ int fricc_stream_synchronize(void);
  * "push_ctas_per_sm": grid cap of the peer-store kernels (default 2 CTAs per SM: NVLink-bound, and it leaves thread
  * slots and registers to the contraction kernel that runs concurrently on the compute stream); "push_carveout": the
  * L1/shared split (percent shared) those kernels ask for, default 100 = the split the tensor-core kernel runs under,
- * so that both can be resident on one SM; -1 = the device default.  "push_copy_engine": 1 (default) = fricc_push_view
+ * so that both can be resident on one SM; -1 = the device default.  "push_copy_engine": 1 = fricc_push_view
  * moves views that collapse to contiguous rows of at least "push_min_row_bytes" (default 4096) with one
- * cudaMemcpy(2D)Async per peer -- the copy engines need no SM, so the stores run at link speed under a tensor-core
- * kernel that occupies every SM; 0 = always the store kernel (same bytes in the same places).                    */
+ * cudaMemcpy(2D)Async per peer (copy engines, no SM); 0 (default) = always the store kernel (same bytes in the same
+ * places; measured faster for the step as a whole, see fricc_peer.cu).                                           */
 int fricc_set_option(const char* key, int value);
 /* Two contractions into the SAME output with the same T as ONE dense product where the algebra allows it (an extension;
  * the reference's drivers make the two calls one after the other, e.g. fricc/friccsd.py:347-356 (0112, 0113 -> Wvoov) and
@@ -190,8 +190,8 @@ int fricc_push_columns(const double* out_local_dev, void* const* peer_out_dev, i
                        int64_t l_begin, int64_t l_count);
 /* the same exchange for a 4-D strided VIEW (shape, element strides) of this rank's copy of an output -- the L-slice the
  * sharded engine handed to fricc_contract: every element of the view is stored at the same offset of
- * view_peer_dev[q] (q != self), the address of the same view in peer q's copy.  Long-row views go through the copy
- * engines, the rest through a store kernel ("push_copy_engine" above); stat "push_copies" counts the copies issued. */
+ * view_peer_dev[q] (q != self), the address of the same view in peer q's copy.  A store kernel by default; with
+ * "push_copy_engine" = 1 long-row views go through the copy engines (stat "push_copies" counts the copies issued).  */
 int fricc_push_view(const double* view_local_dev, void* const* view_peer_dev, int n_peers, int self,
                     const int64_t shape[4], const int64_t strides[4]);
 /* Stream-ordered barrier of the ranks of one node without an NCCL launch: flags_peer_dev[q] = address, in rank q's
@@ -323,6 +323,15 @@ int fricc_shard_scan_resolve(fricc_shard_t s, const double* carry_in_dev, double
  * elements, as GLOBAL flat indices, into S_dev[n_sample] (zero-initialised by the caller; summed over ranks).
  * draw = the rand() value of lin_space_add_const (fri_utils.cpp:47).                                                */
 int fricc_shard_emit_systematic(fricc_shard_t s, int64_t n_sample, int32_t draw, int64_t* S_dev);
+/* Alg. A.2 (parallel_sample, fri_utils.cpp:176-362) with ONE CHUNK PER RANK -- the order-independent distributed sampler
+ * of SURVEY.md 8 f-4.  The shard is the chunk; the caller has done the budget arithmetic of :191-275 (exact |q|_1 over
+ * all ranks and |q_j|_1 of this chunk with the scan stages above, a_j = n_sample*|q_j|/|q|, t_j = frac(a_j), the integer
+ * budget g_j after the pivotal draw over the t's).  This call is :296-356 for the chunk: copy of the probabilities,
+ * leading ones rescaled to the mass `budget`, sample_pivotal, indices offset by j0 -> S_dev[0 .. budget).  draws: this
+ * chunk's own uniform draws (host int32, rand() values), or NULL = the library's rand() stream at its current position
+ * (the caller positions each rank's copy with fricc_rand_skip).  n_consumed: draws the chunk's walk took.           */
+int fricc_shard_sample_chunk(fricc_shard_t s, int64_t budget, double t, double a, double chunk_norm, const int32_t* draws,
+                             int64_t n_draws, int64_t* n_consumed, int64_t* S_dev);
 /* raises the reference's error if a kernel of this shard flagged one (some p > 1: fri_utils.cpp:383-395)            */
 int fricc_shard_check(fricc_shard_t s);
 /* (key, global flat index) of every element with key >= key_min, appended in arbitrary order; *count_dev = how many

@@ -54,11 +54,12 @@ def main():
     flat, vals = T.export()
     host_w = {t: rng.random([ext[c] for c in TERMS[t][0]]) for t in TERMS}
     ok = True
-    # (kernel form, peer stores on a side stream, shortest row the copy engines take: 4096 = these small slices all go
-    #  through the store kernel, 8 = every slice that collapses to rows goes through cudaMemcpy(2D)Async)
-    for tc_mode, side, min_row in ((0, False, 4096), (2, True, 4096), (2, True, 8)):
+    # (kernel form, peer stores on a side stream, copy engines: 0 = every slice through the store kernel (the default),
+    #  1 = every slice that collapses to rows of >= 8 bytes through cudaMemcpy(2D)Async)
+    for tc_mode, side, copy_engine in ((0, False, 0), (2, True, 0), (2, True, 1)):
         py_rccsd.set_option("tc_mode", tc_mode)
-        py_rccsd.set_option("push_min_row_bytes", min_row)
+        py_rccsd.set_option("push_copy_engine", copy_engine)
+        py_rccsd.set_option("push_min_row_bytes", 8)
         copies0 = py_rccsd.get_stat("push_copies")
         arena = fd.SymmArena(8 * (8 * no * no * nv * nv + no ** 4) + 65536, comm, device)
         side_stream = fd.SideStream(device) if side else None
@@ -92,8 +93,8 @@ def main():
                     print(f"rank {rank}: term {t} tc_mode {tc_mode} rep {rep}: max err {np.abs(got - want).max():.3e}", flush=True)
                 ok &= bool(good)
             dist.barrier()                               # nobody re-zeroes while a peer is still reading its copy
-        if world > 1 and (py_rccsd.get_stat("push_copies") > copies0) != (min_row == 8):
-            print(f"rank {rank}: copy-engine path {'not ' if min_row == 8 else ''}taken with push_min_row_bytes={min_row}", flush=True)
+        if world > 1 and (py_rccsd.get_stat("push_copies") > copies0) != (copy_engine == 1):
+            print(f"rank {rank}: copy-engine path {'not ' if copy_engine else ''}taken with push_copy_engine={copy_engine}", flush=True)
             ok = False
         del outs, eng
         torch.cuda.synchronize()
@@ -101,6 +102,7 @@ def main():
         arena.close()
     py_rccsd.set_option("tc_mode", 1)
     py_rccsd.set_option("push_min_row_bytes", 4096)
+    py_rccsd.set_option("push_copy_engine", 0)
     flag = torch.tensor([1 if ok else 0])
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     if rank == 0:

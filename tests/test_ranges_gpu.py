@@ -45,6 +45,39 @@ def test_single_rank_stages_vs_oracle(rccsd, port, kind, dims, frac):
     assert np.array_equal(vals.view(np.int64), want["vals"].view(np.int64))
 
 
+@pytest.mark.parametrize("kind", ["heavy", "uniform"])
+@pytest.mark.parametrize("dims,frac", [((4, 4, 9, 9), 0.2), ((7, 7, 40, 40), 0.05)])
+def test_single_chunk_parallel_sampler_vs_oracle(rccsd, port, kind, dims, frac):
+    """sampling_method="parallel" with one rank = the reference's parallel_sample with one thread behind the same D and
+    probabilities (the multi-rank form is in dist_ranges_worker.py)."""
+    import torch
+
+    from fricc_b200 import _lib
+    from fricc_b200 import dist as fd
+    from fricc_b200 import ranges
+
+    rng = np.random.default_rng(sum(kind.encode()) * 7 + sum(dims))
+    n = int(np.prod(dims))
+    x = synth_t2(rng, n, kind)
+    m = max(1, int(frac * n))
+    draws = rng.integers(0, 2**31 - 1, size=n).astype(np.int32)
+    D, r = port.get_d_largest(x, m)
+    nsamp = m - D.size
+    p = port.make_probability_vector(x, nsamp, D, r)
+    try:
+        S, used = port.parallel_sample(nsamp, p, 1, draws)
+    except Exception:
+        # n' * |q| / |q| came out a hair off an integer: the reference's one-element budget walk exits (fri_utils.cpp:121)
+        with pytest.raises(_lib.FriccError):
+            ranges.compress_ranges(torch.from_numpy(x).cuda(), 0, dims, m, fd.Comm(), "fri", "parallel", draws=(draws[:0], draws))
+        return
+    T = ranges.compress_ranges(torch.from_numpy(x).cuda(), 0, dims, m, fd.Comm(), "fri", "parallel", draws=(draws[:0], draws))
+    flat, vals = T.export()
+    assert np.array_equal(flat, np.concatenate([D, S]))
+    assert np.array_equal(vals.view(np.int64), np.concatenate([x[D], x[S] / p[S]]).view(np.int64))
+    assert T.consumed_draws == (0, used)
+
+
 def test_carry_in_scan_is_the_sequential_sum(rccsd):
     """The staged scan with a non-zero exact carry: sum(x[:k]) carried into the shard x[k:] must give the plain
     left-to-right fp64 sum of all of x (one_norm, fri_utils.cpp:164-171) for every split point."""
