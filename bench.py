@@ -89,9 +89,9 @@ def parse_args():
     p.add_argument("--last-term-parts", type=int, default=2,
                    help="N>1: the last term before the closing barrier is issued in this many parts, each part's peer stores "
                         "running under the next part's kernel")
-    p.add_argument("--push-copy-engine", action="store_true",
-                   help="N>1: peer stores of long-row slices through cudaMemcpy(2D)Async instead of the store kernel (A/B; "
-                        "measured slower for the whole step, see fricc_peer.cu)")
+    p.add_argument("--push-copy-engine", type=int, default=0,
+                   help="N>1: peer stores of long-row slices through cudaMemcpy(2D)Async instead of the store kernel (A/B): "
+                        "1 = on the side stream, 2 = one private stream per peer (see fricc_peer.cu)")
     p.add_argument("--overlap-planes", action="store_true",
                    help="encode the ladder's first sub-shard on a second, lower-priority stream beside the compression "
                         "instead of after it (A/B)")
@@ -378,7 +378,7 @@ class Iteration:
             if not args.push_inline:
                 # (same priority as the step's own stream, which --overlap-planes raises)
                 self.side = fd.SideStream(device, priority=-1 if args.overlap_planes else 0)
-            py_rccsd.set_option("push_copy_engine", 1 if args.push_copy_engine else 0)
+            py_rccsd.set_option("push_copy_engine", args.push_copy_engine)
         else:
             self.arena = None
             mk = lambda *shape: torch.zeros(*shape, device=device, dtype=torch.float64)
@@ -586,12 +586,15 @@ class Iteration:
 
     def stage_breakdown(self, steps):
         self.torch.cuda.synchronize()
-        out = {}
+        out, worst = {}, {}
         for (n0, e0), (n1, e1) in zip(self.stage_events, self.stage_events[1:]):
             if n1 == "begin":
                 continue
-            out[n1] = out.get(n1, 0.0) + e0.elapsed_time(e1)
+            dt = e0.elapsed_time(e1)
+            out[n1] = out.get(n1, 0.0) + dt
+            worst[n1] = max(worst.get(n1, 0.0), dt)
         self.stage_events.clear()
+        self.stage_worst = {k: round(x, 3) for k, x in worst.items()}    # the slowest single step, per stage
         return {k: round(x / steps, 3) for k, x in out.items()}
 
 
@@ -920,6 +923,7 @@ def run_b200_arm(args):
         it.stage_events.clear()
         e2e_ms = timed_steps(e2e_step, args.steps)
         e2e_stage_ms = it.stage_breakdown(args.steps)
+        e2e_stage_worst = it.stage_worst
         it.ladder_ms.clear(); it.plane_ms.clear()
 
     # ---- compression-only sweep (config 5) at this GPU count, outside the timed regions
@@ -1042,7 +1046,7 @@ def run_b200_arm(args):
                                                 if it.tc else "fp64 bucketed SpMM")
         if not args.no_e2e:
             line["e2e"] = {"value": e2e_ms * 1e-3 / args.steps, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
-                           "d2h_bytes_per_step": int(d2h), "stage_ms_per_step": e2e_stage_ms,
+                           "d2h_bytes_per_step": int(d2h), "stage_ms_per_step": e2e_stage_ms, "stage_ms_slowest_step": e2e_stage_worst,
                            "through": ("T2 from pinned host memory (one upload), py_rccsd.SparseTensor4d x2 + contract_DTSpT x11 (W "
                                        "and the intermediates are device tensors), residual t2new to pinned host memory under "
                                        "the last four contractions" if world == 1 else

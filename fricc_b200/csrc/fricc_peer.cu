@@ -60,7 +60,7 @@ void set_push_carveout(int pct) { g_push_carveout = pct; }
 static int g_push_copy_engine = 0;          // "push_copy_engine": 1 = views of long contiguous rows go through cudaMemcpy(2D)Async
 static int64_t g_push_min_row_bytes = 4096;  // shorter rows: the store kernel
 static int64_t g_push_copies = 0;
-void set_push_copy_engine(int on) { g_push_copy_engine = on ? 1 : 0; }
+void set_push_copy_engine(int on) { g_push_copy_engine = on < 0 ? 0 : on; }
 void set_push_min_row_bytes(int n) { g_push_min_row_bytes = n < 8 ? 8 : n; }
 int64_t push_copies() { return g_push_copies; }
 // An SM runs CTAs of two kernels side by side only under ONE L1/shared split.  The tensor-core kernel needs ~198 KB of
@@ -165,15 +165,37 @@ void push_view(const double* local, double* const* peer, int n_peers, int self, 
   // (0.080 s against 0.071), so the store kernel stays the default.
   if (g_push_copy_engine && v.s[0] == 1 && v.n[0] * 8 >= g_push_min_row_bytes && (nd <= 2 || (nd == 3 && v.n[2] <= 64))) {
     const int64_t outer = nd == 3 ? v.n[2] : 1;
+    // "push_copy_engine" = 2: one private stream per peer, forked from and joined back into the library's stream, so
+    // that the copies to different peers run on different engines at the same time (one stream serialises them).
+    const bool fan = g_push_copy_engine >= 2;
+    static cudaStream_t fan_stream[MAX_PEERS] = {};
+    static cudaEvent_t fan_fork = nullptr, fan_done[MAX_PEERS] = {};
+    if (fan) {
+      if (!fan_fork) FRICC_CUDA(cudaEventCreateWithFlags(&fan_fork, cudaEventDisableTiming));
+      FRICC_CUDA(cudaEventRecord(fan_fork, stream()));
+    }
     for (int d = 1; d < n_peers; d++) {
       const int q = (self + d) % n_peers;
+      cudaStream_t st = stream();
+      if (fan) {
+        if (!fan_stream[q]) {
+          FRICC_CUDA(cudaStreamCreateWithFlags(&fan_stream[q], cudaStreamNonBlocking));
+          FRICC_CUDA(cudaEventCreateWithFlags(&fan_done[q], cudaEventDisableTiming));
+        }
+        st = fan_stream[q];
+        FRICC_CUDA(cudaStreamWaitEvent(st, fan_fork, 0));
+      }
       for (int64_t k = 0; k < outer; k++) {
         const int64_t off = nd == 3 ? k * v.s[2] : 0;
         if (nd == 1)
-          FRICC_CUDA(cudaMemcpyAsync(peer[q] + off, local + off, (size_t)v.n[0] * 8, cudaMemcpyDefault, stream()));
+          FRICC_CUDA(cudaMemcpyAsync(peer[q] + off, local + off, (size_t)v.n[0] * 8, cudaMemcpyDefault, st));
         else
           FRICC_CUDA(cudaMemcpy2DAsync(peer[q] + off, (size_t)v.s[1] * 8, local + off, (size_t)v.s[1] * 8, (size_t)v.n[0] * 8,
-                                       (size_t)v.n[1], cudaMemcpyDefault, stream()));
+                                       (size_t)v.n[1], cudaMemcpyDefault, st));
+      }
+      if (fan) {
+        FRICC_CUDA(cudaEventRecord(fan_done[q], st));
+        FRICC_CUDA(cudaStreamWaitEvent(stream(), fan_done[q], 0));
       }
     }
     g_push_copies += (n_peers - 1) * outer;

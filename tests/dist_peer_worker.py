@@ -55,8 +55,9 @@ def main():
     host_w = {t: rng.random([ext[c] for c in TERMS[t][0]]) for t in TERMS}
     ok = True
     # (kernel form, peer stores on a side stream, copy engines: 0 = every slice through the store kernel (the default),
-    #  1 = every slice that collapses to rows of >= 8 bytes through cudaMemcpy(2D)Async)
-    for tc_mode, side, copy_engine in ((0, False, 0), (2, True, 0), (2, True, 1)):
+    #  1 = every slice that collapses to rows of >= 8 bytes through cudaMemcpy(2D)Async, 2 = the same on one private
+    #  stream per peer)
+    for tc_mode, side, copy_engine in ((0, False, 0), (2, True, 0), (2, True, 1), (2, True, 2)):
         py_rccsd.set_option("tc_mode", tc_mode)
         py_rccsd.set_option("push_copy_engine", copy_engine)
         py_rccsd.set_option("push_min_row_bytes", 8)
@@ -93,7 +94,7 @@ def main():
                     print(f"rank {rank}: term {t} tc_mode {tc_mode} rep {rep}: max err {np.abs(got - want).max():.3e}", flush=True)
                 ok &= bool(good)
             dist.barrier()                               # nobody re-zeroes while a peer is still reading its copy
-        if world > 1 and (py_rccsd.get_stat("push_copies") > copies0) != (copy_engine == 1):
+        if world > 1 and (py_rccsd.get_stat("push_copies") > copies0) != (copy_engine >= 1):
             print(f"rank {rank}: copy-engine path {'not ' if copy_engine else ''}taken with push_copy_engine={copy_engine}", flush=True)
             ok = False
         del outs, eng
