@@ -92,6 +92,10 @@ def parse_args():
     p.add_argument("--push-copy-engine", type=int, default=0,
                    help="N>1: peer stores of long-row slices through cudaMemcpy(2D)Async instead of the store kernel (A/B): "
                         "1 = on the side stream, 2 = one private stream per peer (see fricc_peer.cu)")
+    p.add_argument("--uniform-carveout", type=int, default=-1,
+                   help="N>1: every library kernel asks for this L1/shared split (percent shared; 100 = the split of the "
+                        "tensor-core and peer-store kernels), so that the short kernels of a term can share SMs with the "
+                        "peer stores of the previous one (A/B; -1 = the driver's choice per kernel)")
     p.add_argument("--overlap-planes", action="store_true",
                    help="encode the ladder's first sub-shard on a second, lower-priority stream beside the compression "
                         "instead of after it (A/B)")
@@ -379,6 +383,7 @@ class Iteration:
                 # (same priority as the step's own stream, which --overlap-planes raises)
                 self.side = fd.SideStream(device, priority=-1 if args.overlap_planes else 0)
             py_rccsd.set_option("push_copy_engine", args.push_copy_engine)
+            py_rccsd.set_option("uniform_carveout", args.uniform_carveout)
         else:
             self.arena = None
             mk = lambda *shape: torch.zeros(*shape, device=device, dtype=torch.float64)

@@ -18,6 +18,7 @@ void set_push_ctas_per_sm(int n);  // fricc_peer.cu: grid cap of the peer-store 
 void set_push_carveout(int pct);   // fricc_peer.cu: L1/shared split the peer-store kernels ask for (-1: default)
 void set_push_copy_engine(int on);  // fricc_peer.cu: long-row views go through cudaMemcpy(2D)Async instead of the store kernel
 void set_push_min_row_bytes(int n);
+void set_uniform_carveout(int pct);  // fricc_runtime.cu
 int64_t push_copies();
 }  // namespace fricc
 
@@ -150,6 +151,7 @@ int fricc_set_option(const char* key, int value) {
   else if (key && strcmp(key, "push_carveout") == 0) set_push_carveout(value);
   else if (key && strcmp(key, "push_copy_engine") == 0) set_push_copy_engine(value);
   else if (key && strcmp(key, "push_min_row_bytes") == 0) set_push_min_row_bytes(value);
+  else if (key && strcmp(key, "uniform_carveout") == 0) set_uniform_carveout(value);
   else if (key && strncmp(key, "spmm_", 5) == 0) set_spmm_option(key, value);
   else if (key && strncmp(key, "tc_", 3) == 0) set_tc_option(key, value);
   else fail(FRICC_EINVAL, "unknown option '%s'", key ? key : "(null)");

@@ -53,8 +53,20 @@ cudaStream_t stream();
 void count_launch(int64_t n = 1);
 void check_launch(const char* what);  // cudaGetLastError after a launch + count it
 
+// "uniform_carveout" option (>= 0): every kernel launched through FRICC_LAUNCH asks for the same L1/shared split (percent
+// shared).  CTAs of kernels that want different splits cannot share an SM; with the peer-store kernel resident on every
+// SM (it asks for the tensor-core kernel's split so that the two can run together) the short kernels of the next term
+// otherwise wait for it.  -1 (default): each kernel keeps the driver's choice.
+int uniform_carveout();
 #define FRICC_LAUNCH(name, grid, block, smem, ...)                  \
   do {                                                              \
+    if (::fricc::uniform_carveout() >= 0) {                         \
+      static int fricc_carveout_ = -2;                              \
+      if (fricc_carveout_ != ::fricc::uniform_carveout()) {         \
+        fricc_carveout_ = ::fricc::uniform_carveout();              \
+        cudaFuncSetAttribute(name, cudaFuncAttributePreferredSharedMemoryCarveout, fricc_carveout_); \
+      }                                                             \
+    }                                                               \
     name<<<(grid), (block), (smem), ::fricc::stream()>>>(__VA_ARGS__); \
     ::fricc::check_launch(#name);                                   \
   } while (0)

@@ -24,6 +24,9 @@ void fail(int code, const char* fmt, ...) {
   throw Error(code, buf);
 }
 
+static int g_uniform_carveout = -1;
+int uniform_carveout() { return g_uniform_carveout; }
+void set_uniform_carveout(int pct) { g_uniform_carveout = pct < 0 ? -1 : (pct > 100 ? 100 : pct); }
 cudaStream_t stream() { return g_stream; }
 void set_stream(cudaStream_t s) { g_stream = s; }
 void count_launch(int64_t n) { g_launches.fetch_add(n, std::memory_order_relaxed); }

@@ -226,22 +226,14 @@ int radix_sort_pairs(uint64_t* k[2], uint64_t* v[2], int64_t n, const std::vecto
   dl.n = (int)digits.size();
   for (int i = 0; i < dl.n; i++) dl.d[i] = digits[i];
 
-  // which digits actually discriminate?
-  DevBuf<unsigned long long> ghist((size_t)dl.n * 256);
-  ghist.zero();
-  int gblocks = (int)std::min<int64_t>(ceil_div(n, 256 * 8), (int64_t)num_sms() * 8);
-  FRICC_LAUNCH(rs_global_hist, gblocks, 256, dl.n * 256 * sizeof(unsigned), k[0], v[0], n, dl, ghist.p);
-  std::vector<unsigned long long> h((size_t)dl.n * 256);
-  ghist.to_host(h.data(), h.size());
-
+  // Every digit gets its pass.  (An earlier version read a global histogram back to skip digits on which all keys
+  // agree: one blocking device-to-host copy per sort -- seven per iteration on the contraction path, each a host
+  // synchronisation, and each queued behind whatever else the device-to-host engine was doing.  The callers' digit
+  // lists are already cut to the key range, so a skippable digit is rare; the host now never waits here.)
   const int nblocks = (int)ceil_div(n, RS_TILE);
   DevBuf<uint32_t> counts((size_t)256 * nblocks);
   int cur = 0;
   for (int g = 0; g < dl.n; g++) {
-    bool trivial = false;
-    for (int b = 0; b < 256; b++)
-      if (h[(size_t)g * 256 + b] == (unsigned long long)n) trivial = true;
-    if (trivial) continue;
     FRICC_LAUNCH(rs_block_hist, nblocks, RS_THREADS, 0, k[cur], v[cur], n, dl.d[g], counts.p, nblocks);
     exclusive_scan_u32(counts.p, (int64_t)256 * nblocks);
     FRICC_LAUNCH(rs_scatter, nblocks, RS_THREADS, 0, k[cur], v[cur], k[cur ^ 1], v[cur ^ 1], n, dl.d[g], counts.p,
