@@ -82,6 +82,11 @@ def parse_args():
                         "iteration); invariant: planes built once (FRILCCSD)")
     p.add_argument("--max-slice-gb", type=float, default=26.0, help="largest resident ladder W sub-shard (fp64 GB)")
     p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--no-clocks", action="store_true", help="diagnostic: do not run the nvidia-smi clock sampler")
+    p.add_argument("--clock-period-ms", type=int, default=200, help="sampling period of the nvidia-smi clock sampler")
+    p.add_argument("--stall-trace", type=float, default=0.0,
+                   help="diagnostic: dump the main thread's Python stack to stderr whenever it has sat in one place for "
+                        "this many milliseconds outside the compression (finds a host-side stall)")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--no-sweep", action="store_true", help="skip the compression-only sweep (config 5)")
     p.add_argument("--planes", type=int, default=6,
@@ -501,7 +506,7 @@ class Iteration:
     def mark(self, name):
         e = self.torch.cuda.Event(enable_timing=True)
         e.record()
-        self.stage_events.append((name, e))
+        self.stage_events.append((name, e, time.perf_counter()))
 
     def compress_mode(self):
         if self.args.sampling == "systematic":
@@ -591,15 +596,19 @@ class Iteration:
 
     def stage_breakdown(self, steps):
         self.torch.cuda.synchronize()
-        out, worst = {}, {}
-        for (n0, e0), (n1, e1) in zip(self.stage_events, self.stage_events[1:]):
+        out, worst, host = {}, {}, {}
+        for (n0, e0, h0), (n1, e1, h1) in zip(self.stage_events, self.stage_events[1:]):
             if n1 == "begin":
                 continue
             dt = e0.elapsed_time(e1)
             out[n1] = out.get(n1, 0.0) + dt
-            worst[n1] = max(worst.get(n1, 0.0), dt)
+            if dt >= worst.get(n1, 0.0):
+                # host_ms: what the HOST spent issuing the stage (it runs ahead of the device): a device time far above
+                # both the stage's average and its host time is a stall on the device side, not late launches
+                worst[n1], host[n1] = dt, (h1 - h0) * 1e3
         self.stage_events.clear()
         self.stage_worst = {k: round(x, 3) for k, x in worst.items()}    # the slowest single step, per stage
+        self.stage_worst_host = {k: round(x, 3) for k, x in host.items()}
         return {k: round(x / steps, 3) for k, x in out.items()}
 
 
@@ -691,19 +700,60 @@ def compression_sweep(comm, device, torch, fd, sizes=(1.0e8, 2.56e8, 1.0e9), m=1
     return out
 
 
-def start_clock_sampler(gpu_index):
+def start_stall_trace(it, limit_ms):
+    """Diagnostic watchdog thread: when the main thread has not passed a stage mark for `limit_ms` and is not inside the
+    compression (whose read-backs legitimately wait for the device), print where it is."""
+    import threading
+    import traceback
+
+    main_id = threading.main_thread().ident
+
+    def watch():
+        last, since, reported = None, time.perf_counter(), False
+        while True:
+            time.sleep(0.02)
+            key = len(it.stage_events)
+            now = time.perf_counter()
+            if key != last:
+                last, since, reported = key, now, False
+                continue
+            name = it.stage_events[-1][0] if it.stage_events else ""
+            if not reported and (now - since) * 1e3 > limit_ms and name not in ("begin", "B2", ""):
+                frame = sys._current_frames().get(main_id)
+                sys.stderr.write(f"[stall-trace] {1e3 * (now - since):.0f} ms behind mark '{name}':\n" +
+                                 "".join(traceback.format_stack(frame)[-6:]))
+                sys.stderr.flush()
+                reported = True
+
+    threading.Thread(target=watch, daemon=True).start()
+
+
+def start_clock_sampler(gpu_index, period_ms=200):
     path = tempfile.NamedTemporaryFile(prefix="clocks_", suffix=".csv", delete=False).name
+    # started BEFORE the warm-up steps: nvidia-smi's start-up (NVML attaches every GPU of the box) then falls into the
+    # warm-up, not into the timed region; the samples are cut to the timed window by their timestamps afterwards
     q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap,timestamp")
     try:
         proc = subprocess.Popen(["nvidia-smi", "-i", str(gpu_index), f"--query-gpu={q}", "--format=csv,noheader,nounits",
-                                 "-lms", "200"], stdout=open(path, "w"), stderr=subprocess.DEVNULL)
+                                 "-lms", str(int(period_ms))], stdout=open(path, "w"), stderr=subprocess.DEVNULL)
     except Exception:
         return None, path
     return proc, path
 
 
-def stop_clock_sampler(proc, path):
+def _smi_time(text):
+    import datetime
+
+    try:
+        return datetime.datetime.strptime(text.strip(), "%Y/%m/%d %H:%M:%S.%f").timestamp()
+    except Exception:
+        return None
+
+
+def stop_clock_sampler(proc, path, window=None):
+    """window = (t0, t1) in time.time() seconds: only samples taken inside it count (all of them if the timestamps
+    cannot be read or none falls inside)."""
     if proc is None:
         return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
     proc.terminate()
@@ -713,7 +763,15 @@ def stop_clock_sampler(proc, path):
         proc.kill()
     sm, mx, reasons = [], [], set()
     names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-    for line in open(path):
+    lines = [ln for ln in open(path)]
+    if window is not None:
+        inside = []
+        for ln in lines:
+            ts = _smi_time(ln.split(",")[-1]) if ln.count(",") >= 7 else None
+            if ts is not None and window[0] - 0.2 <= ts <= window[1] + 0.2:
+                inside.append(ln)
+        lines = inside or lines
+    for line in lines:
         f = [x.strip() for x in line.split(",")]
         if len(f) < 7:
             continue
@@ -808,21 +866,28 @@ def run_b200_arm(args):
         sync_all()
         return timer.total_ms()
 
-    # ---- warm-up
+    # ---- warm-up (the clock sampler starts here; only its samples from the timed window are used)
+    proc, cpath = start_clock_sampler(local_rank, args.clock_period_ms) if (rank == 0 and not args.no_clocks) else (None, "")
+    if args.stall_trace > 0:
+        start_stall_trace(it, args.stall_trace)
     for _ in range(max(args.warmup, 0)):
         it.step(it.t2)
     sync_all()
     it.ladder_ms.clear(); it.plane_ms.clear(); it.stage_events.clear()
 
     # ---- timed: device-resident inputs
-    proc, cpath = start_clock_sampler(local_rank) if rank == 0 else (None, "")
     launches0 = L.fricc_kernel_launches()
     tc0 = py_rccsd.get_stat("tc_contract_calls")
+    alloc0, hits0 = py_rccsd.get_stat("alloc_driver_calls"), py_rccsd.get_stat("alloc_cache_hits")
+    wall0 = time.time()
     ms = timed_steps(lambda timer: it.step(it.t2, timer), args.steps)
+    wall1 = time.time()
     launches = L.fricc_kernel_launches() - launches0
     tc_calls = py_rccsd.get_stat("tc_contract_calls") - tc0
-    clocks = stop_clock_sampler(proc, cpath) if rank == 0 else None
+    alloc_calls, alloc_hits = py_rccsd.get_stat("alloc_driver_calls") - alloc0, py_rccsd.get_stat("alloc_cache_hits") - hits0
+    clocks = stop_clock_sampler(proc, cpath, (wall0, wall1)) if rank == 0 else None
     stage_ms = it.stage_breakdown(args.steps)
+    stage_worst, stage_worst_host = it.stage_worst, it.stage_worst_host
     torch.cuda.synchronize()
     waits_by_rank = None
     if world > 1 and not args.as_rank_of:
@@ -1006,6 +1071,11 @@ def run_b200_arm(args):
             "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": workload_config(args, world),
             "roofline": roof, "clocks": clocks, "gpu_launches": int(launches), "peer_copies": int(py_rccsd.get_stat("push_copies")),
             "ladder_ms_per_step": sum(lad_ms) / args.steps if lad_ms else None, "stage_ms_per_step": stage_ms,
+            "stage_ms_slowest_step": stage_worst, "stage_host_issue_ms_of_that_step": stage_worst_host,
+            "scratch_allocations_in_timed_region": {"cudaMallocAsync_calls": int(alloc_calls), "served_from_cached_blocks": int(alloc_hits),
+                                                    "note": "rank 0; the library keeps freed scratch blocks per stream, so a steady-state "
+                                                            "step does not enter the driver (a cudaMallocAsync that has to map memory "
+                                                            "queues behind nvidia-smi's queries and can stall the host for 0.03-2.7 s)"},
             "output_checksums": checks, "barrier_wait_ms_by_rank": waits_by_rank,
             "schedule": ("single rank: plugin calls (py_rccsd.contract_DTSpT) on the full operands" if world == 1 else
                          "plugin calls on L-slice views; each rank stores its finished slice into every peer's copy over "
@@ -1076,6 +1146,10 @@ def run_b200_arm(args):
 
 def main():
     args = parse_args()
+    if os.environ.get("FRICC_BENCH_NOGC"):      # diagnostic
+        import gc
+
+        gc.disable()
     if args.impl == "reference":
         run_reference_arm(args)
     else:

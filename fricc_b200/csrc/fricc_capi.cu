@@ -19,6 +19,10 @@ void set_push_carveout(int pct);   // fricc_peer.cu: L1/shared split the peer-st
 void set_push_copy_engine(int on);  // fricc_peer.cu: long-row views go through cudaMemcpy(2D)Async instead of the store kernel
 void set_push_min_row_bytes(int n);
 void set_uniform_carveout(int pct);  // fricc_runtime.cu
+void set_alloc_cache_mb(int mb);     // fricc_runtime.cu: bytes of freed scratch blocks kept for the next call (0: none)
+void release_cached_blocks();
+int64_t alloc_driver_calls();
+int64_t alloc_cache_hits();
 int64_t push_copies();
 }  // namespace fricc
 
@@ -152,6 +156,8 @@ int fricc_set_option(const char* key, int value) {
   else if (key && strcmp(key, "push_copy_engine") == 0) set_push_copy_engine(value);
   else if (key && strcmp(key, "push_min_row_bytes") == 0) set_push_min_row_bytes(value);
   else if (key && strcmp(key, "uniform_carveout") == 0) set_uniform_carveout(value);
+  else if (key && strcmp(key, "alloc_cache_mb") == 0) set_alloc_cache_mb(value);
+  else if (key && strcmp(key, "release_cached") == 0) release_cached_blocks();
   else if (key && strncmp(key, "spmm_", 5) == 0) set_spmm_option(key, value);
   else if (key && strncmp(key, "tc_", 3) == 0) set_tc_option(key, value);
   else fail(FRICC_EINVAL, "unknown option '%s'", key ? key : "(null)");
@@ -165,6 +171,8 @@ int fricc_get_stat(const char* key, int64_t* value) {
   else if (strcmp(key, "tc_contract_calls") == 0) *value = g_tc_calls;      // fricc_contract calls that took the tensor-core form
   else if (strcmp(key, "spmm_contract_calls") == 0) *value = g_spmm_calls;
   else if (strcmp(key, "fused_pairs") == 0) *value = g_fused_pairs;   // fricc_contract_pair calls that ran as ONE dense product
+  else if (strcmp(key, "alloc_driver_calls") == 0) *value = alloc_driver_calls();   // cudaMallocAsync calls so far
+  else if (strcmp(key, "alloc_cache_hits") == 0) *value = alloc_cache_hits();       // allocations served from cached blocks
   else if (strcmp(key, "push_copies") == 0) *value = push_copies();   // cudaMemcpy(2D)Async calls issued by fricc_push_view
   else if (strcmp(key, "planes_predicted_builds") == 0) *value = planes_predicted_builds();  // builds that reused exponents  // ... and the fp64 SpMM
   else fail(FRICC_EINVAL, "unknown stat '%s'", key);

@@ -25,15 +25,28 @@ struct Error : public std::runtime_error {
 void set_last_error(const std::string& msg);
 [[noreturn]] void fail(int code, const char* fmt, ...);
 
+// Diagnostic: with FRICC_TRACE_SLOW_MS=<ms> in the environment every runtime call / launch / allocation that keeps the
+// HOST longer than that is reported on stderr (finds what a stalled plugin call was waiting in).  Off: one load + branch.
+double slow_trace_ms();  // < 0: off
+struct SlowScope {
+  const char* what;
+  const char* file;
+  int line;
+  long long t0;
+  SlowScope(const char* w, const char* f, int l);
+  ~SlowScope();
+};
+
 #define FRICC_CUDA(expr)                                                                              \
   do {                                                                                                \
+    ::fricc::SlowScope _slow(#expr, __FILE__, __LINE__);                                              \
     cudaError_t _e = (expr);                                                                          \
     if (_e != cudaSuccess)                                                                            \
       ::fricc::fail(FRICC_ECUDA, "CUDA error %s at %s:%d: %s", cudaGetErrorName(_e), __FILE__, __LINE__, \
                     cudaGetErrorString(_e));                                                          \
   } while (0)
 
-#define FRICC_API_BEGIN try {
+#define FRICC_API_BEGIN try { ::fricc::SlowScope _slow_api(__func__, "C-ABI call, whole", 0);
 #define FRICC_API_END                                  \
   }                                                    \
   catch (const ::fricc::Error& e) {                    \
@@ -67,7 +80,10 @@ int uniform_carveout();
         cudaFuncSetAttribute(name, cudaFuncAttributePreferredSharedMemoryCarveout, fricc_carveout_); \
       }                                                             \
     }                                                               \
-    name<<<(grid), (block), (smem), ::fricc::stream()>>>(__VA_ARGS__); \
+    {                                                               \
+      ::fricc::SlowScope _slow("launch " #name, __FILE__, __LINE__); \
+      name<<<(grid), (block), (smem), ::fricc::stream()>>>(__VA_ARGS__); \
+    }                                                               \
     ::fricc::check_launch(#name);                                   \
   } while (0)
 

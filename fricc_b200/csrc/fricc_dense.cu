@@ -722,12 +722,12 @@ static void planes_predicted_build(WSlices& ws, const WView& w, int64_t l_begin)
   const int64_t total = ws.l_count * p.units_per_col;
   const unsigned grid = (unsigned)std::min<int64_t>(total, (int64_t)num_sms() * 3);
   p.colmax = colmax.p; p.list = nullptr; p.count = nullptr;
-  kernel<<<grid, PP_THREADS, 0, stream()>>>(p);
+  { SlowScope slow("launch planes_predict", __FILE__, __LINE__); kernel<<<grid, PP_THREADS, 0, stream()>>>(p); }
   check_launch("planes_predict_kernel");
   FRICC_LAUNCH(predict_check_kernel, (unsigned)ceil_div(ws.l_count, 256), 256, 0, colmax.p, ws.l_count, ws.expo.p,
                ws.colscale.p, list.p, ws.redone.p);
   p.colmax = nullptr; p.list = list.p; p.count = ws.redone.p;
-  kernel<<<grid, PP_THREADS, 0, stream()>>>(p);
+  { SlowScope slow("launch planes_predict", __FILE__, __LINE__); kernel<<<grid, PP_THREADS, 0, stream()>>>(p); }
   check_launch("planes_predict_kernel");
 }
 

@@ -59,7 +59,13 @@ int fricc_stream_synchronize(void);
  * so that both can be resident on one SM; -1 = the device default.  "push_copy_engine": 1 = fricc_push_view
  * moves views that collapse to contiguous rows of at least "push_min_row_bytes" (default 4096) with one
  * cudaMemcpy(2D)Async per peer (copy engines, no SM); 0 (default) = always the store kernel (same bytes in the same
- * places; measured faster for the step as a whole, see fricc_peer.cu).                                           */
+ * places; measured faster for the step as a whole, see fricc_peer.cu).
+ * "alloc_cache_mb": bytes of freed per-call scratch (sign matrices, CSR remainders, sort buffers; blocks up to 2 GB) the
+ * library keeps per (device, stream) and hands out again by size instead of going back to cudaMallocAsync -- default
+ * 24576, 0 = none.  A steady-state iteration then makes no allocation call at all: a cudaMallocAsync that has to map
+ * memory enters the kernel driver and queues behind e.g. `nvidia-smi -lms` queries (measured: 0.03 - 2.7 s host stalls).
+ * "release_cached" (any value): give every cached block back now.  Stats "alloc_driver_calls" / "alloc_cache_hits".
+ * Environment: FRICC_TRACE_SLOW_MS=<ms> reports every runtime call that keeps the host longer than that on stderr.  */
 int fricc_set_option(const char* key, int value);
 /* Two contractions into the SAME output with the same T as ONE dense product where the algebra allows it (an extension;
  * the reference's drivers make the two calls one after the other, e.g. fricc/friccsd.py:347-356 (0112, 0113 -> Wvoov) and
