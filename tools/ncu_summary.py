@@ -1,7 +1,8 @@
 #!/usr/bin/env python
 """Summarise an `ncu --set full` report as the metric,unit,value CSV kept under profiles/ (one kernel launch).
 
-  python tools/ncu_summary.py gpurun_out/prof.ncu-rep profiles/ncu_full_rNN_name.csv [--top-stalls 12]
+  python tools/ncu_summary.py gpurun_out/prof.ncu-rep profiles/ncu_full_rNN_name.csv [--top-stalls 12] [--launch N]
+(--launch N: only the N-th launch of the report, counted from 0 -- one file per kernel)
 Reads the report with `ncu -i ... --page raw --csv` (and `--page source --csv` for the most-sampled instructions)."""
 import csv
 import io
@@ -31,7 +32,8 @@ def run(args):
 def main():
     rep, out = sys.argv[1], sys.argv[2]
     top = int(sys.argv[sys.argv.index("--top-stalls") + 1]) if "--top-stalls" in sys.argv else 10
-    rows = list(csv.reader(io.StringIO(run(["ncu", "-i", rep, "--page", "raw", "--csv"]))))
+    pick = ["--launch-skip", sys.argv[sys.argv.index("--launch") + 1], "--launch-count", "1"] if "--launch" in sys.argv else []
+    rows = list(csv.reader(io.StringIO(run(["ncu", "-i", rep, "--page", "raw", "--csv"] + pick))))
     hdr, units = rows[0], rows[1]
     lines = ["metric,unit,value"]
     for launch in rows[2:]:
@@ -41,13 +43,13 @@ def main():
             if h in KEEP and rec.get(h, "") != "":
                 lines.append(f"{h},{u},{rec[h]}")
     try:
-        src = list(csv.reader(io.StringIO(run(["ncu", "-i", rep, "--page", "source", "--csv"]))))
+        src = list(csv.reader(io.StringIO(run(["ncu", "-i", rep, "--page", "source", "--csv"] + pick))))
         h = src[1]
         ia, isrc, isamp, iex = h.index("Address"), h.index("Source"), h.index("# Samples"), h.index("Instructions Executed")
         data = [(int(r[isamp] or 0), r[ia][-5:], r[isrc].strip(), r[iex]) for r in src[2:] if len(r) > isamp and (r[isamp] or "0").isdigit()]
         tot = sum(d[0] for d in data) or 1
         lines.append(f"stall_samples_total,sample,{tot}")
-        for smp, addr, ins, ex in sorted(data, reverse=True)[:top]:
+        for smp, addr, ins, ex in sorted(set(data), reverse=True)[:top]:
             lines.append(f'"most sampled: {addr} {ins[:70]} (executed {ex})",pct_of_samples,{100.0 * smp / tot:.2f}')
     except Exception as e:  # noqa: BLE001
         lines.append(f'"source page unavailable: {e}",,')
