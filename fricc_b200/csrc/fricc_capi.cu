@@ -1180,6 +1180,18 @@ int fricc_shard_emit_systematic(fricc_shard_t s, int64_t n_sample, int32_t draw,
   FRICC_API_END
 }
 
+int fricc_shard_emit_systematic_multi(fricc_shard_t s, int64_t n_sample, const int32_t* draws, int n_draws, int64_t* S_dev,
+                                      int64_t stride) {
+  FRICC_API_BEGIN
+  check_shard(s);
+  if (s->ps.absval) fail(FRICC_EINVAL, "fricc_shard_use_probabilities first");
+  if (n_draws < 0 || (n_draws > 0 && (!draws || !S_dev))) fail(FRICC_EINVAL, "bad arguments");
+  std::vector<double> rn((size_t)n_draws);
+  for (int d = 0; d < n_draws; d++) rn[d] = (double)draws[d] / 2147483647.0;  // (double)rand() / RAND_MAX   (fri_utils.cpp:47)
+  shard_scan_emit_multi(s->scan, n_sample, rn.data(), n_draws, S_dev, stride);
+  FRICC_API_END
+}
+
 int fricc_shard_sample_chunk(fricc_shard_t s, int64_t budget, double t, double a, double chunk_norm, const int32_t* draws,
                              int64_t n_draws, int64_t* n_consumed, int64_t* S_dev) {
   FRICC_API_BEGIN

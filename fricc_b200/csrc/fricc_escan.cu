@@ -13,6 +13,8 @@
 //   E4  escan_emit_kernel     per chunk, from its exact start: exact running sums of all elements -> systematic samples
 //
 // Compiled with -fmad=false (the probabilities are computed exactly as the reference does).
+#include <algorithm>
+
 #include "fricc_exact.cuh"
 #include "fricc_fri.cuh"
 #include "fricc_mscan.cuh"
@@ -104,10 +106,22 @@ escan_map_kernel(PSrc ps, int64_t n, const double* __restrict__ approx_excl, con
   const int k = usable ? fx_binade(c0) : 0;
   EMap m = emap_identity();
   if (usable) {
+    const double* src = ps.values() + base;
+    if (base + ES_E <= n && (reinterpret_cast<uintptr_t>(src) & 15) == 0) {   // 16-byte loads of the thread's 8 elements
+      double xv[ES_E];
 #pragma unroll
-    for (int q = 0; q < ES_E; q++) {
-      int64_t j = base + q;
-      if (j < n) m = emap_compose(m, emap_of(ps(j), k));
+      for (int q = 0; q < ES_E; q += 2) {
+        const double2 t = *reinterpret_cast<const double2*>(src + q);
+        xv[q] = t.x; xv[q + 1] = t.y;
+      }
+#pragma unroll
+      for (int q = 0; q < ES_E; q++) m = emap_compose(m, emap_of(ps.of_value(xv[q], base + q), k));
+    } else {
+#pragma unroll
+      for (int q = 0; q < ES_E; q++) {
+        int64_t j = base + q;
+        if (j < n) m = emap_compose(m, emap_of(ps(j), k));
+      }
     }
   }
   EMap inc = warp_incl_scan_emap(m);
@@ -313,26 +327,106 @@ escan_resolve_kernel(PSrc ps, int64_t n, const ChunkMap* __restrict__ maps, int6
 }
 
 // ---- E4 ----------------------------------------------------------------------------------------------------------
+// Up to EMIT_MAX_DRAWS systematic draws from one pass: the exact running sums do not depend on the draw.
+struct EmitDraws {
+  int nd;
+  double rn[EMIT_MAX_DRAWS];
+  int64_t* S[EMIT_MAX_DRAWS];
+};
+
+// Fast path (a full chunk whose running sum starts normal and stays inside its binade -- all but a few dozen chunks of
+// a tensor): everything in registers.  A thread owns ES_E consecutive elements, keeps their one-element maps from the
+// first pass (A and the tie flag; B of a one-element map is 0), gets its exact start from the CTA scan and applies the
+// kept maps.  Samples are then located per SAMPLE, not per element: the thread's elements cover [excl, incl_last), the
+// samples inside are i in [first_sample(excl), first_sample(incl_last)), and sample i lands on the first element whose
+// inclusive sum exceeds uk_i = fl(i + rn) -- the same comparisons as the per-element interval test of the general path
+// (fri_utils.cpp:147-157), since i -> uk_i is non-decreasing.  ncu (profiles/ncu_full_r02_escan_emit.csv) had the
+// general path issue-bound at ~390 instructions per element with 16-way shared-memory bank conflicts on the
+// thread-contiguous reads; this path needs neither the staging buffers nor the second evaluation of the maps.
 __global__ void __launch_bounds__(ES_THREADS)
-escan_emit_kernel(PSrc ps, int64_t n, const double* __restrict__ exact_in, int64_t nsamp, double rn,
-                  int64_t* __restrict__ S) {
+escan_emit_kernel(PSrc ps, int64_t n, const double* __restrict__ exact_in, int64_t nsamp, EmitDraws dr) {
   __shared__ double pbuf[ES_CHUNK];
   __shared__ double cs[ES_CHUNK];
   __shared__ ChunkScratch sc;
   const int64_t base = (int64_t)blockIdx.x * ES_CHUNK;
   const int cnt = (int)min((int64_t)ES_CHUNK, n - base);
+  const double c_in = exact_in[blockIdx.x];
+  if (cnt == ES_CHUNK && fx_is_normal_positive(c_in)) {   // uniform over the CTA
+    const int k = fx_binade(c_in);
+    const int64_t C0 = fx_to_state(c_in);
+    const int64_t j0 = base + (int64_t)threadIdx.x * ES_E;
+    double xv[ES_E];
+    const double* src = ps.values() + j0;
+    if ((reinterpret_cast<uintptr_t>(src) & 15) == 0) {
+#pragma unroll
+      for (int q = 0; q < ES_E; q += 2) {
+        const double2 t = *reinterpret_cast<const double2*>(src + q);
+        xv[q] = t.x; xv[q + 1] = t.y;
+      }
+    } else {
+#pragma unroll
+      for (int q = 0; q < ES_E; q++) xv[q] = src[q];
+    }
+    int64_t A[ES_E];
+    unsigned even = 0;
+    EMap mine = emap_identity();
+#pragma unroll
+    for (int q = 0; q < ES_E; q++) {
+      const EMap m = emap_of(ps.of_value(xv[q], j0 + q), k);
+      A[q] = m.A;
+      even |= (unsigned)m.even << q;
+      mine = emap_compose(mine, m);
+    }
+    const EMap ex = block_excl_scan_emap(mine, sc.warp_maps);
+    const int64_t S0 = emap_apply(ex, C0);
+    int64_t st[ES_E];
+    int64_t S = S0;
+#pragma unroll
+    for (int q = 0; q < ES_E; q++) {
+      S = emap_apply(EMap{A[q], 0, (int32_t)((even >> q) & 1u)}, S);
+      st[q] = S;
+    }
+    // the states only grow, so the CTA's last one tells whether the sum left the binade anywhere in the chunk
+    if (!__syncthreads_or(st[ES_E - 1] >= FX_TWO53)) {
+      const double excl = fx_from_state(S0, k);
+      double incl[ES_E];
+#pragma unroll
+      for (int q = 0; q < ES_E; q++) incl[q] = fx_from_state(st[q], k);
+      if (incl[ES_E - 1] > excl) {
+#pragma unroll
+        for (int d = 0; d < EMIT_MAX_DRAWS; d++) {
+          if (d >= dr.nd) break;
+          const double rn = dr.rn[d];
+          const int64_t lo = first_sample_at_or_above(excl, rn, nsamp);
+          const int64_t hi = first_sample_at_or_above(incl[ES_E - 1], rn, nsamp);
+          for (int64_t i = lo; i < hi; i++) {
+            const double uk = __dadd_rn((double)i, rn);
+            int q = 0;
+#pragma unroll
+            for (int t = 0; t < ES_E - 1; t++) q += (incl[t] <= uk) ? 1 : 0;
+            dr.S[d][i] = ps.j0 + j0 + q;
+          }
+        }
+      }
+      return;
+    }
+    __syncthreads();  // sc.warp_maps is reused below
+  }
   for (int k = threadIdx.x; k < cnt; k += ES_THREADS) pbuf[k] = ps(base + k);
   __syncthreads();
-  const double c_in = exact_in[blockIdx.x];
   chunk_exact_scan(pbuf, cnt, c_in, cs, &sc);
   // interval of element j is [excl, incl): samples i with excl <= uk_i < incl land on j   (fri_utils.cpp:147-157)
   for (int k = threadIdx.x; k < cnt; k += ES_THREADS) {
     double incl = cs[k];
     double excl = k ? cs[k - 1] : c_in;
     if (incl > excl) {
-      int64_t lo = first_sample_at_or_above(excl, rn, nsamp);
-      int64_t hi = first_sample_at_or_above(incl, rn, nsamp);
-      for (int64_t i = lo; i < hi; i++) S[i] = ps.j0 + base + k;
+#pragma unroll
+      for (int d = 0; d < EMIT_MAX_DRAWS; d++) {
+        if (d >= dr.nd) break;
+        int64_t lo = first_sample_at_or_above(excl, dr.rn[d], nsamp);
+        int64_t hi = first_sample_at_or_above(incl, dr.rn[d], nsamp);
+        for (int64_t i = lo; i < hi; i++) dr.S[d][i] = ps.j0 + base + k;
+      }
     }
   }
 }
@@ -410,10 +504,21 @@ void shard_scan_resolve(ShardScan* s, const double* carry_in_dev, double* carry_
                carry_in_dev, carry_out_dev, s->pl.stats.p);
 }
 
-void shard_scan_emit(ShardScan* s, int64_t nsamp, double rn, int64_t* S_dev) {
+void shard_scan_emit_multi(ShardScan* s, int64_t nsamp, const double* rn, int n_draws, int64_t* S_dev, int64_t stride) {
   if (s->n <= 0 || nsamp <= 0) return;
-  FRICC_LAUNCH(escan_emit_kernel, (unsigned)s->pl.nchunks, ES_THREADS, 0, s->ps, s->n, s->pl.exact_in.p, nsamp, rn,
-               S_dev);
+  for (int d0 = 0; d0 < n_draws; d0 += EMIT_MAX_DRAWS) {
+    EmitDraws dr{};
+    dr.nd = std::min(EMIT_MAX_DRAWS, n_draws - d0);
+    for (int d = 0; d < dr.nd; d++) {
+      dr.rn[d] = rn[d0 + d];
+      dr.S[d] = S_dev + (int64_t)(d0 + d) * stride;
+    }
+    FRICC_LAUNCH(escan_emit_kernel, (unsigned)s->pl.nchunks, ES_THREADS, 0, s->ps, s->n, s->pl.exact_in.p, nsamp, dr);
+  }
+}
+
+void shard_scan_emit(ShardScan* s, int64_t nsamp, double rn, int64_t* S_dev) {
+  shard_scan_emit_multi(s, nsamp, &rn, 1, S_dev, 0);
 }
 
 int shard_scan_errors(ShardScan* s) {
@@ -438,7 +543,11 @@ void systematic_parallel(const PSrc& ps, int64_t n, int64_t nsamp, double rn, in
   if (n <= 0 || nsamp <= 0) return;
   EscanPlan pl;
   escan_prepare(ps, n, pl);
-  FRICC_LAUNCH(escan_emit_kernel, (unsigned)pl.nchunks, ES_THREADS, 0, ps, n, pl.exact_in.p, nsamp, rn, S_dev);
+  EmitDraws dr{};
+  dr.nd = 1;
+  dr.rn[0] = rn;
+  dr.S[0] = S_dev;
+  FRICC_LAUNCH(escan_emit_kernel, (unsigned)pl.nchunks, ES_THREADS, 0, ps, n, pl.exact_in.p, nsamp, dr);
   if (err_flags_out) pl.err.to_host(err_flags_out, 1);
   else FRICC_CUDA(cudaStreamSynchronize(stream()));
 }

@@ -21,6 +21,16 @@ struct PSrc {
   uint64_t idx_cut;
   int absval;           // 1: return |x| (one_norm)
   int64_t j0 = 0;       // flat index of x[0] (range-sharded compression: x is the shard [j0, j0+n) of the tensor)
+  // the addend of element j given its value (x[j], or probs[j] for an explicit vector)
+  __device__ __forceinline__ double of_value(double xv, int64_t j) const {
+    if (probs) return xv;
+    if (absval) return fabs(xv);
+    uint64_t key = abs_key(xv);
+    bool inD = key > key_cut || (key == key_cut && (uint64_t)(j + j0) <= idx_cut);
+    if (inD) return 0.0;
+    return __dmul_rn(__ddiv_rn(fabs(xv), r), nprime);
+  }
+  __device__ __forceinline__ const double* values() const { return probs ? probs : x; }
   __device__ __forceinline__ double operator()(int64_t j) const {
     if (probs) return probs[j];
     double xv = x[j];
@@ -64,6 +74,10 @@ void shard_scan_maps(ShardScan* s, const double* approx_carry_dev);
 void shard_scan_resolve(ShardScan* s, const double* carry_in_dev, double* carry_out_dev);
 // E4: systematic samples owned by the shard's elements, written as GLOBAL flat indices into S_dev[nsamp]
 void shard_scan_emit(ShardScan* s, int64_t nsamp, double rn, int64_t* S_dev);
+// the same for up to EMIT_MAX_DRAWS draws from ONE pass over the shard (the running sums do not depend on the draw):
+// draw d writes S_dev + d * stride
+constexpr int EMIT_MAX_DRAWS = 4;
+void shard_scan_emit_multi(ShardScan* s, int64_t nsamp, const double* rn, int n_draws, int64_t* S_dev, int64_t stride);
 int shard_scan_errors(ShardScan* s);  // ERRF_* raised so far (synchronises)
 
 }  // namespace fricc

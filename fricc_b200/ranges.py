@@ -283,8 +283,9 @@ def _sample_systematic(shard, comm, nsamp, nD, idx, flat, mm, count, draws):
     for k in range(count):
         if nD > 0 and comm.rank == 0:   # summed over ranks below: rank 0 contributes D
             flat[k * mm: k * mm + nD] = idx[:nD]
-        if nsamp > 0:
-            check(L.fricc_shard_emit_systematic(shard.h, nsamp, the_draws[k], _ptr(flat[k * mm + nD:])))
+    if nsamp > 0:                       # all draws from one pass over the shard
+        d = (ctypes.c_int32 * count)(*the_draws)
+        check(L.fricc_shard_emit_systematic_multi(shard.h, nsamp, d, count, _ptr(flat[nD:]), mm))
     return 1
 
 

@@ -329,6 +329,11 @@ int fricc_shard_scan_resolve(fricc_shard_t s, const double* carry_in_dev, double
  * elements, as GLOBAL flat indices, into S_dev[n_sample] (zero-initialised by the caller; summed over ranks).
  * draw = the rand() value of lin_space_add_const (fri_utils.cpp:47).                                                */
 int fricc_shard_emit_systematic(fricc_shard_t s, int64_t n_sample, int32_t draw, int64_t* S_dev);
+/* The same for n_draws consecutive compressions of the same tensor from ONE pass (fricc/friccsd.py:100-136 compresses
+ * the same t2 twice; the running sums of p do not depend on the draw): draw d fills S_dev + d * stride.  Identical to
+ * n_draws calls of fricc_shard_emit_systematic.                                                                     */
+int fricc_shard_emit_systematic_multi(fricc_shard_t s, int64_t n_sample, const int32_t* draws, int n_draws, int64_t* S_dev,
+                                      int64_t stride);
 /* Alg. A.2 (parallel_sample, fri_utils.cpp:176-362) with ONE CHUNK PER RANK -- the order-independent distributed sampler
  * of SURVEY.md 8 f-4.  The shard is the chunk; the caller has done the budget arithmetic of :191-275 (exact |q|_1 over
  * all ranks and |q_j|_1 of this chunk with the scan stages above, a_j = n_sample*|q_j|/|q|, t_j = frac(a_j), the integer
