@@ -106,6 +106,8 @@ def parse_args():
                         "instead of after it (A/B)")
     p.add_argument("--push-inline", action="store_true",
                    help="N>1: issue the peer stores on the compute stream (A/B of the side-stream push)")
+    p.add_argument("--no-constant-eris", action="store_true",
+                   help="A/B: do not declare the ovov integrals constant (their digit planes are then rebuilt in every step)")
     p.add_argument("--no-fuse", action="store_true",
                    help="issue 0112/0113 and 1302/1202 as the eleven separate plugin calls of the reference's driver instead of "
                         "the two fused pairs (py_rccsd.contract_DTSpT_pair)")
@@ -378,6 +380,10 @@ class Iteration:
         py_rccsd.set_option("tc_mode", 1 if self.tc else 0)
         if self.tc:
             py_rccsd.set_option("tc_planes", args.planes)
+            if not args.no_constant_eris:
+                # the integrals (eris.ovov, read by 0112/0113/0313/0312/1323) never change between iterations in either
+                # driver: declared constant, their digit planes are built in the first (warm-up) step and kept
+                py_rccsd.constant_operand(self.ovov, True)
         self.multi = comm.world > 1
         self.side = None
         if self.multi:
@@ -1113,6 +1119,10 @@ def run_b200_arm(args):
             f"expanded into {args.planes} int8 digit planes, tail <= 2^-{8 * args.planes} of the column's largest element per "
             "term, exact int32 accumulation, fp64 recombination; contraction parity <= 1e-10 relative (tests/test_plugin_tc_gpu.py, "
             "incl. heavy-tailed W)") if it.tc else "fp64 FMA"
+        line["config"]["constant_operands"] = (
+            "eris.ovov declared constant (py_rccsd.constant_operand): its digit planes are built once, "
+            f"{py_rccsd.get_stat('constant_plane_hits')} plugin calls reused them" if (it.tc and not args.no_constant_eris)
+            else "none declared")
         line["config"]["fused_pairs"] = ("0112+0113 (one weighted sign matrix) and 1302+1202 (planes of 2 Wvoov - Wvovo) through "
                                          "py_rccsd.contract_DTSpT_pair: 9 dense products for the 11 terms" if it.fuse else
                                          "none: eleven plugin calls")

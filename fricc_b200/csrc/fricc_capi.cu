@@ -28,7 +28,7 @@ int64_t push_copies();
 
 using namespace fricc;
 
-static int64_t g_tc_calls = 0, g_spmm_calls = 0, g_fused_pairs = 0;
+static int64_t g_tc_calls = 0, g_spmm_calls = 0, g_fused_pairs = 0, g_const_plane_hits = 0;
 
 namespace {
 
@@ -170,6 +170,7 @@ int fricc_get_stat(const char* key, int64_t* value) {
   if (strcmp(key, "pivotal_restarts") == 0) *value = pivotal_restarts_last();
   else if (strcmp(key, "tc_contract_calls") == 0) *value = g_tc_calls;      // fricc_contract calls that took the tensor-core form
   else if (strcmp(key, "spmm_contract_calls") == 0) *value = g_spmm_calls;
+  else if (strcmp(key, "constant_plane_hits") == 0) *value = g_const_plane_hits;   // plugin calls that reused the planes of a declared-constant operand
   else if (strcmp(key, "fused_pairs") == 0) *value = g_fused_pairs;   // fricc_contract_pair calls that ran as ONE dense product
   else if (strcmp(key, "alloc_driver_calls") == 0) *value = alloc_driver_calls();   // cudaMallocAsync calls so far
   else if (strcmp(key, "alloc_cache_hits") == 0) *value = alloc_cache_hits();       // allocations served from cached blocks
@@ -397,6 +398,11 @@ struct PlaneEntry {
   fricc::WSlices ws;
 };
 std::vector<PlaneEntry*> g_plane_cache;
+// Operands the caller has declared constant (fricc_constant_operand): address ranges, and their planes keyed by
+// (address, shape, strides, K/L axes, planes) -- no fingerprint, no read-back: the declaration is the guarantee.
+struct ConstRange { const double* lo; const double* hi; };
+std::vector<ConstRange> g_const_ranges;
+std::vector<PlaneEntry*> g_plane_const;
 WSlices* g_pair_planes = nullptr;        // planes of the combined operand of the last fused pair (fricc_contract_pair)
 std::vector<PlaneEntry*> g_plane_hist;   // geometry-keyed buffers + exponents ("tc_history_mb"), see planes_for
 uint64_t g_plane_stamp = 0;
@@ -410,7 +416,27 @@ uint64_t view_fingerprint(const WView& w, int64_t l_begin, int64_t l_count);  //
 
 namespace {
 
+bool is_constant_operand(const double* p) {
+  if (!p) return false;
+  for (const ConstRange& r : g_const_ranges)
+    if (p >= r.lo && p < r.hi) return true;
+  return false;
+}
+
+void const_planes_drop(const double* lo, const double* hi) {   // entries whose operand starts inside [lo, hi)
+  for (size_t i = 0; i < g_plane_const.size();) {
+    if (g_plane_const[i]->p >= lo && g_plane_const[i]->p < hi) {
+      delete g_plane_const[i];
+      g_plane_const.erase(g_plane_const.begin() + (long)i);
+    } else {
+      i++;
+    }
+  }
+}
+
 void plane_cache_clear() {
+  for (PlaneEntry* e : g_plane_const) delete e;
+  g_plane_const.clear();
   for (PlaneEntry* e : g_plane_cache) delete e;
   g_plane_cache.clear();
   for (PlaneEntry* e : g_plane_hist) delete e;
@@ -422,6 +448,25 @@ void plane_cache_clear() {
 const WSlices& planes_for(const double* Wd, const int64_t shape[4], const int64_t strides[4], const TermSpec& ts,
                           const WView& view, int64_t nL, WSlices& local) {
   const int S = tc_planes();
+  if (is_constant_operand(Wd)) {
+    // declared constant by the caller (the ERI blocks of a CC driver, fricc/friccsd.py:347-378 pass eris.ovov to five
+    // of the eleven terms in every iteration): planes are built on first use and kept
+    const int axes[4] = {ts.wK[0], ts.wK[1], ts.wL[0], ts.wL[1]};
+    for (PlaneEntry* e : g_plane_const)
+      if (e->p == Wd && e->S == S && memcmp(e->shape, shape, sizeof(e->shape)) == 0 &&
+          memcmp(e->strides, strides, sizeof(e->strides)) == 0 && memcmp(e->axes, axes, sizeof(axes)) == 0) {
+        g_const_plane_hits++;
+        return e->ws;
+      }
+    PlaneEntry* e = new PlaneEntry();
+    e->p = Wd; e->S = S;
+    memcpy(e->shape, shape, sizeof(e->shape));
+    memcpy(e->strides, strides, sizeof(e->strides));
+    memcpy(e->axes, axes, sizeof(axes));
+    g_plane_const.push_back(e);
+    wslices_build_view(e->ws, view, 0, nL, S);
+    return e->ws;
+  }
   if (!tc_plane_cache()) {
     // no caching of CONTENT, but the buffers and column exponents of the last operand of this geometry are kept: an
     // iterative driver comes back with the same shapes every iteration, and the exponents predict the next build
@@ -667,6 +712,21 @@ int fricc_contract_pair(const double* W_a, const int64_t a_shape[4], const int64
       contract_rest(lay, vb, 0, nL, out, om, sigma * qb);
     }
   }
+  FRICC_API_END
+}
+
+int fricc_constant_operand(const double* p, int64_t n_elements, int on) {
+  FRICC_API_BEGIN
+  if (!p || n_elements <= 0) fail(FRICC_EINVAL, "bad arguments");
+  const double* lo = p;
+  const double* hi = p + n_elements;
+  // planes built from anything inside the range are dropped either way: a new declaration starts from the current content
+  const_planes_drop(lo, hi);
+  for (size_t i = 0; i < g_const_ranges.size();) {
+    if (g_const_ranges[i].lo < hi && lo < g_const_ranges[i].hi) g_const_ranges.erase(g_const_ranges.begin() + (long)i);
+    else i++;
+  }
+  if (on) g_const_ranges.push_back(ConstRange{lo, hi});
   FRICC_API_END
 }
 

@@ -346,6 +346,12 @@ def kernel(eris, t1=None, t2=None, max_cycle=50, tol=1e-8, tolnormt=1e-6, m_keep
     eccsd = energy(t1, t2, eris)
     energies = [eccsd]
     wbuf = torch.empty_like(eris.vvvv)       # Wvvvv is rebuilt into the same buffer every cycle
+    # the integrals never change during the loop: with the B200 backend the digit planes of eris.ovov (five of the
+    # eleven terms read it, :347-378) are then built in the first cycle and kept
+    declared = None
+    if compressed and eris.ovov.is_cuda and hasattr(backend or _backend(), "constant_operand"):
+        declared = backend or _backend()
+        declared.constant_operand(eris.ovov, True)
     t1_sum = t2_sum = None
     n_avg = 0
     conv = False
@@ -369,6 +375,8 @@ def kernel(eris, t1=None, t2=None, max_cycle=50, tol=1e-8, tolnormt=1e-6, m_keep
             break                                           # "FAILED THERE ARE NANS"
         if abs(eccsd - eold) > 1e5:
             break                                           # "FAILED BECAUSE dE = ..."
+    if declared is not None:
+        declared.constant_operand(eris.ovov, False)
     average = None
     if average_from is not None and n_avg > 0:
         t1a, t2a = t1_sum / n_avg, t2_sum / n_avg

@@ -310,6 +310,21 @@ def contract_DTSpT_pair(W_a, W_b, T, ouput, term_a, term_b):
     return None
 
 
+def constant_operand(W, on=True):
+    """Declare the CUDA tensor `W` (its whole storage span) constant between plugin calls, or withdraw that (`on=False`).
+    The drivers hand ``eris.ovov`` -- integrals that never change -- to five of the eleven terms in every iteration
+    (fricc/friccsd.py:347-378); the digit planes of a declared operand's views are built on first use and kept
+    (include/fricc_b200.h: fricc_constant_operand).  Call it again after rewriting the array.  An extension of the
+    reference's surface; results are bit-identical with and without it."""
+    if not _is_cuda_tensor(W):
+        raise TypeError("constant_operand(): a CUDA tensor is needed (host arrays are staged per call)")
+    span = 1 + sum((int(n) - 1) * int(st) for n, st in zip(W.shape, W.stride())) if W.numel() else 0
+    if span <= 0:
+        return None
+    check(_lib.lib().fricc_constant_operand(c_void_p(int(W.data_ptr())), int(span), 1 if on else 0))
+    return None
+
+
 def contract_DTSpT_experimental(W, T, ouput, term):
     """The reference's alternative 2323 kernels (``"taskloop"``, ``"atomic"``; src/sparse_tensor.cpp:445-459) differ only
     in CPU threading; both names run the same GPU ladder kernel here."""

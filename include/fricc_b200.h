@@ -94,6 +94,14 @@ int fricc_contract_pair(const double* W_a_dev, const int64_t a_shape[4], const i
  * shape and strides and guarded by a fingerprint of 4096 sampled elements (for drivers that hand over the same
  * operands every iteration, fricc/frilccsd.py:171-179); default 0 = planes are rebuilt on every call.               */
 int fricc_plane_cache_clear(void);
+/* Declare the n_elements doubles at device address p CONSTANT until further notice (on = 1) or withdraw that (on = 0).
+ * The ERI blocks of a coupled-cluster driver never change between iterations -- fricc/friccsd.py:347-378 hands
+ * eris.ovov to five of the eleven terms in every cycle -- so the digit planes of any view that starts inside a declared
+ * range are built on first use and kept, keyed by (address, shape, strides, contracted/free axes, planes); no
+ * fingerprint and no read-back, the declaration is the guarantee.  Declaring a range again (after rewriting it) or
+ * withdrawing it drops its planes; so does fricc_plane_cache_clear.  Stat "constant_plane_hits".  An extension of the
+ * plugin surface (py_rccsd.constant_operand); results are bit-identical to undeclared calls.                         */
+int fricc_constant_operand(const double* p, int64_t n_elements, int on);
 /* "d_parallel": -1 (default) = the parallel D-selection for candidate lists >= 32768 and the one-warp walk below,
  * 0 / 1 = always serial / always parallel (bit-identical).
  * "pivotal_parallel": -1 (default) = the parallel exact pivotal sampler for N >= 65536 and the one-thread chain kernel

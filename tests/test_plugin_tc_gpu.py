@@ -246,6 +246,68 @@ def test_plane_cache_follows_the_operand(tc, port):
     _lib.check(_lib.lib().fricc_plane_cache_clear())
 
 
+def test_constant_operand_planes_are_built_once_and_follow_the_declaration(tc, port):
+    """py_rccsd.constant_operand (fricc_constant_operand): the ovov integrals of a CC driver never change, so the planes
+    of their views are kept -- same bits as undeclared calls for every term that reads ovov, on the whole operand and on
+    a narrowed view (a rank's slice); a declaration made again after rewriting the array picks up the new content, a
+    withdrawn one goes back to building per call."""
+    import torch
+
+    rccsd = tc
+    rng = np.random.default_rng(77)
+    no, nv = 6, 13
+    T, flat, vals, dims = _fri(rccsd, rng, no, nv, 1500)
+    ovov = torch.from_numpy(rng.random((no, nv, no, nv)) - 0.4).cuda()
+    ext = {"o": no, "v": nv}
+    terms = ("0112", "0113", "0313", "0312", "1323")
+
+    def run(W):
+        outs = {}
+        for term in terms:
+            out = torch.zeros([ext[c] for c in TERMS[term][1]], dtype=torch.float64, device="cuda")
+            rccsd.contract_DTSpT(W, T, out, term)
+            outs[term] = out
+        return outs
+
+    plain = run(ovov)
+    rccsd.constant_operand(ovov, True)
+    try:
+        h0 = rccsd.get_stat("constant_plane_hits")
+        first = run(ovov)                                   # builds (terms that read the same view share one build)
+        h1 = rccsd.get_stat("constant_plane_hits")
+        again = run(ovov)
+        h2 = rccsd.get_stat("constant_plane_hits")
+        assert h2 - h1 == len(terms) and h1 - h0 < len(terms)
+        for term in terms:
+            assert torch.equal(first[term], plain[term]) and torch.equal(again[term], plain[term]), term
+            want = np.zeros(plain[term].shape)
+            port.contract(term, ovov.cpu().numpy(), flat, vals, dims, want)
+            assert _close(plain[term].cpu().numpy(), want), term
+        # a rank's slice of the operand starts inside the declared range: its planes are kept too
+        part = ovov.narrow(2, 2, 3)
+        out_a = torch.zeros(nv, 3, nv, no, dtype=torch.float64, device="cuda")
+        out_b = torch.zeros_like(out_a)
+        rccsd.contract_DTSpT(part, T, out_a, "0312")
+        h3 = rccsd.get_stat("constant_plane_hits")
+        rccsd.contract_DTSpT(part, T, out_b, "0312")
+        assert rccsd.get_stat("constant_plane_hits") == h3 + 1 and torch.equal(out_a, out_b)
+        assert torch.equal(out_a, plain["0312"].narrow(1, 2, 3))
+        # rewritten in place: the old planes would be wrong -- the caller declares again
+        ovov.mul_(-1.25).add_(0.05)
+        rccsd.constant_operand(ovov, True)
+        fresh = run(ovov)
+        rccsd.constant_operand(ovov, False)
+        undeclared = run(ovov)
+        for term in terms:
+            assert torch.equal(fresh[term], undeclared[term]), term
+            assert not torch.equal(fresh[term], plain[term]), term
+        h4 = rccsd.get_stat("constant_plane_hits")
+        run(ovov)
+        assert rccsd.get_stat("constant_plane_hits") == h4     # withdrawn: built per call again
+    finally:
+        rccsd.constant_operand(ovov, False)
+
+
 @pytest.mark.parametrize("shape,l0,lc,S", [((2, 40, 64, 64), 3, 70, 6), ((1, 9, 370, 372), 2, 7, 6), ((3, 20, 33, 34), 0, 60, 4),
                                            ((2, 30, 50, 50), 5, 50, 7)])
 def test_predicted_update_equals_a_fresh_build(rccsd, shape, l0, lc, S):
