@@ -976,9 +976,25 @@ def run_b200_arm(args):
             j0, cnt = fd.index_range(nel, rank, world)
             h_t2 = torch.empty(cnt, dtype=torch.float64, pin_memory=True)
             h_t2.copy_(it.t2.view(-1)[j0:j0 + cnt])
-            h_out = torch.empty(cnt, dtype=torch.float64, pin_memory=True)
             d_slice = torch.empty(cnt, dtype=torch.float64, device=device)
             pivotal_full = torch.empty(nel, dtype=torch.float64, device=device) if args.sampling != "systematic" else None
+            # the residual goes back in the pieces the ranks OWN: a rank's slice of t2new for 0101 (a contiguous i-range)
+            # holds the whole ladder contribution after B1 and is final on this rank once its own 0101 is done, so its
+            # read-back runs on a copy stream under the remaining contractions (the slices of all ranks tile t2new)
+            own = it.eng.own_view("0101", it.Wklij.shape, it.t2new)
+            early = own is None or own.is_contiguous()
+            if early:
+                h_out = torch.empty(own.numel() if own is not None else 0, dtype=torch.float64, pin_memory=True)
+            else:
+                h_out = torch.empty(cnt, dtype=torch.float64, pin_memory=True)
+            copy_stream = torch.cuda.Stream(device=device)
+
+            def send_back():
+                if own is None:
+                    return
+                copy_stream.wait_stream(torch.cuda.current_stream())
+                with torch.cuda.stream(copy_stream):
+                    h_out.copy_(own.view(-1), non_blocking=True)
 
             def e2e_step(timer):
                 it.mark("begin")
@@ -990,8 +1006,11 @@ def run_b200_arm(args):
                     full = pivotal_full.view(it.t2.shape)
                 T, T_alt = it.compress_two(d_slice, j0, full=full)
                 it.mark("compress_x2")
-                it.contractions(T, T_alt, timer, plugin=True)
-                h_out.copy_(it.t2new.view(-1)[j0:j0 + cnt], non_blocking=True)
+                it.contractions(T, T_alt, timer, plugin=True, after_t2new=send_back if early else None)
+                if early:
+                    torch.cuda.current_stream().wait_stream(copy_stream)
+                else:
+                    h_out.copy_(it.t2new.view(-1)[j0:j0 + cnt], non_blocking=True)
             h2d = nel * 8
             d2h = nel * 8
         e2e_step(None)
@@ -1136,7 +1155,8 @@ def run_b200_arm(args):
                                        "and the intermediates are device tensors), residual t2new to pinned host memory under "
                                        "the last four contractions" if world == 1 else
                                        "each rank: its 1/N of T2 from pinned host memory, range-sharded compression, "
-                                       "py_rccsd.contract_DTSpT on L-slice views, its 1/N of the residual back")}
+                                       "py_rccsd.contract_DTSpT on L-slice views, its own 1/N of the residual (the i-range "
+                                       "its 0101 call completes) back to pinned host memory under the remaining contractions")}
         if sweep is not None:
             line["compress_sweep"] = sweep
         default_cfg = (o, v, m, args.sampling) == (40, 400, 10_000_000, "systematic") and args.planes == 6
