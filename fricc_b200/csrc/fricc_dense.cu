@@ -598,6 +598,7 @@ __global__ void __launch_bounds__(PF_THREADS, 1) planes_fused_kernel(const PfPar
 // whose exponent did move (or whose finiteness changed) are cut again with the corrected exponent.  The result is
 // bit-identical to a fresh build; the cost is one read of W and one write of the planes (no column has to stay on
 // chip between two looks, so no cluster, no shared memory, no limit on the length of the contracted run).
+static int g_tc_predict_persistent = 0;  // "tc_predict_persistent": see planes_predict
 constexpr int PP_THREADS = 256;
 constexpr int PP_UNIT = 8192;   // contracted indices of one column per work unit: 4 passes of 256 threads x 8 elements
 
@@ -720,14 +721,20 @@ static void planes_predicted_build(WSlices& ws, const WView& w, int64_t l_begin)
                                                   planes_predict_kernel<7>};
   const PpKernel kernel = kernels[ws.S - 1];
   const int64_t total = ws.l_count * p.units_per_col;
-  const unsigned grid = (unsigned)std::min<int64_t>(total, (int64_t)num_sms() * 3);
+  // one 64 KB unit per block by default ("tc_predict_persistent" 1 = a persistent grid-stride grid): a build that runs
+  // on a second stream beside higher-priority kernels (bench.py encodes the ladder operand beside the compression of
+  // T2) leaves an SM as soon as a unit is done, so the other stream's kernels get in -- persistent blocks hold every SM
+  // until the whole operand is encoded.  Alone the short blocks are no slower (7.7 vs 8.2 ms per 25.6 GB slice).
+  const unsigned grid = (unsigned)(g_tc_predict_persistent ? std::min<int64_t>(total, (int64_t)num_sms() * 3)
+                                                           : std::min<int64_t>(total, (int64_t)0x7fffffff));
   p.colmax = colmax.p; p.list = nullptr; p.count = nullptr;
   { SlowScope slow("launch planes_predict", __FILE__, __LINE__); kernel<<<grid, PP_THREADS, 0, stream()>>>(p); }
   check_launch("planes_predict_kernel");
   FRICC_LAUNCH(predict_check_kernel, (unsigned)ceil_div(ws.l_count, 256), 256, 0, colmax.p, ws.l_count, ws.expo.p,
                ws.colscale.p, list.p, ws.redone.p);
   p.colmax = nullptr; p.list = list.p; p.count = ws.redone.p;
-  { SlowScope slow("launch planes_predict", __FILE__, __LINE__); kernel<<<grid, PP_THREADS, 0, stream()>>>(p); }
+  const unsigned grid2 = (unsigned)std::min<int64_t>(total, (int64_t)num_sms() * 3);   // usually no column at all
+  { SlowScope slow("launch planes_predict", __FILE__, __LINE__); kernel<<<grid2, PP_THREADS, 0, stream()>>>(p); }
   check_launch("planes_predict_kernel");
 }
 
@@ -1669,6 +1676,7 @@ void set_tc_option(const char* key, int value) {
   else if (strcmp(key, "tc_sync_lag") == 0) g_tc_sync_lag = std::max(1, value);
   else if (strcmp(key, "tc_fused_planes") == 0) g_tc_fused_planes = value;
   else if (strcmp(key, "tc_predict") == 0) g_tc_predict = value;
+  else if (strcmp(key, "tc_predict_persistent") == 0) g_tc_predict_persistent = value;
   else if (strcmp(key, "tc_history_mb") == 0) g_tc_history_mb = std::max(0, value);
   else if (strcmp(key, "tc_mode") == 0) g_tc_mode = value;
   else if (strcmp(key, "tc_planes") == 0) {

@@ -88,7 +88,7 @@ int fricc_contract_pair(const double* W_a_dev, const int64_t a_shape[4], const i
  * "tc_mode": which form fricc_contract picks -- 0 = always the fp64 SpMM, 1 (default) = the tensor-core form when its
  * cost model says it wins (an FRI-compressed T with at least half of its entries sampled, a large enough product),
  * 2 = always the tensor-core form.  "tc_planes": digit planes it expands W into (default 6 = 48 bits per column).
- * "tc_predict" (1: see fricc_wslices_redone), "tc_pair" (1: CTA-pair tensor-core kernel, 0: one CTA per tile), "tc_lockstep" (1) with "tc_sync_shift" (4: a milestone every 16 k-blocks) and "tc_sync_lag" (2), "tc_band", "tc_fused_planes": 1 (default) = operands whose contracted run is contiguous (the ladder's native W[a,b,c,d]) are
+ * "tc_predict" (1: see fricc_wslices_redone), "tc_predict_persistent" (0: the re-encoding kernel runs one 64 KB unit per block so that kernels of another stream get in between; 1: persistent blocks), "tc_pair" (1: CTA-pair tensor-core kernel, 0: one CTA per tile), "tc_lockstep" (1) with "tc_sync_shift" (4: a milestone every 16 k-blocks) and "tc_sync_lag" (2), "tc_band", "tc_fused_planes": 1 (default) = operands whose contracted run is contiguous (the ladder's native W[a,b,c,d]) are
  * expanded by the single-read cluster kernel, 0 = by the two-pass kernels (identical planes).
  * "tc_plane_cache": 1 = fricc_contract keeps the planes of up to 12 device operands across calls, keyed by address,
  * shape and strides and guarded by a fingerprint of 4096 sampled elements (for drivers that hand over the same
