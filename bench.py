@@ -1124,7 +1124,7 @@ def run_b200_arm(args):
                 "frac": palg / (sum(pl_ms) * 1e-3) / 1e9 / hbm, "peak_source": hbm_kind,
                 "avg_launch_ms": sum(pl_ms) / len(pl_ms), "launches_timed": len(pl_ms),
                 "avg_launch_ms_beside_the_compression": (sum(pl_over_ms) / len(pl_over_ms)) if pl_over_ms else None,
-                "algorithmic_per_launch": palg / len(pl_ms), "traffic": ncu_traffic_per_launch("planes_fused")}
+                "algorithmic_per_launch": palg / len(pl_ms), "traffic": ncu_traffic_per_launch("planes_predict")}
         line["config"]["ladder_subshards"] = len(it.sub)
         line["config"]["ladder_planes"] = (
             "encoded inside the step" + (": the first sub-shard on a second stream beside the compression of T2 (W does not depend "
