@@ -17,8 +17,12 @@ Operand upkeep -- `--w-mode` (both values are in the line, `value` is the one se
             on this path any more).  Producing W itself is the caller's dense work and is untimed.
   invariant the FRILCCSD regime: W is the bare integral block, the same every iteration (fricc/frilccsd.py:171-179);
             planes are built once, outside the timed region.
-  The small operands (ovov; Woooo / Wvoov / Wvovo, which are outputs of this very step) are re-encoded inside the step
-  in both modes.
+  In both modes the ladder's first sub-shard is encoded on a second stream BESIDE the compression of T2 (W does not
+  depend on T2; --no-overlap-planes for the A/B).  Woooo / Wvoov / Wvovo are outputs of this very step and are
+  re-encoded inside it in both modes.  The ovov integrals never change between iterations in either driver
+  (fricc/friccsd.py:316,348-356,372 pass eris.ovov to five of the eleven terms): they are declared constant
+  (py_rccsd.constant_operand), so their planes are built in the first warm-up step and kept (--no-constant-eris for
+  the A/B).
 
 Sharding (N > 1, strong scaling): every contraction is cut along its free index pair; a rank hands the plugin call
 `py_rccsd.contract_DTSpT` (= fricc_contract) its slice of the operand and of the output as plain 4-D views
@@ -34,8 +38,16 @@ sub-shards that are re-generated in HBM between timed segments; the step time is
 `e2e`: the same step through the plugin calls with T2 arriving from pinned host memory and the residual returning to
 it inside the timed region.  1 GPU: one upload of T2, `SparseTensor4d(t2, ...)` twice and `contract_DTSpT` eleven
 times -- the calls fricc/friccsd.py makes (W and the intermediates are device tensors: Wvvvv is 204.8 GB, more than
-the host has) --, t2new copied back while the last four contractions run.  N > 1: every rank uploads its 1/N of T2, the range-sharded compression needs nothing else, the contractions are
-the same plugin calls on views, every rank returns its 1/N of the residual.
+the host has) --, t2new copied back while the last four contractions run.  N > 1: every rank uploads its 1/N of T2,
+the range-sharded compression needs nothing else, the contractions are the same plugin calls on views, and every rank
+reads back the 1/N of the residual it owns (the i-range its own 0101 call completes) on a copy stream under the
+remaining contractions.
+
+Measurement hygiene: the nvidia-smi clock sampler starts before the warm-up and its samples are cut to the timed
+window; `stage_ms_slowest_step` / `stage_host_issue_ms_of_that_step` show the slowest instance of every stage next to
+the host time spent issuing it; `scratch_allocations_in_timed_region` counts the library's driver allocation calls
+(0 in steady state: freed scratch blocks are cached, see fricc_runtime.cu -- a cudaMallocAsync that has to map memory
+queues behind nvidia-smi's queries and used to stall single steps by up to 2.7 s).
 
 `--impl reference`: the reference's own CPU implementation (oracle/_ref, the unmodified sources compiled by
 oracle/Makefile) on the box's host cores: the full workload when it fits the host (e.g. --o 21 --v 93 --m 1e6),
@@ -1112,6 +1124,15 @@ def run_b200_arm(args):
             "timed_segments": "whole steps" if it.resident else
                               f"sum of segments; the ladder's W is regenerated in HBM between {len(it.sub)} sub-shards (an input)",
         }
+        if it.tc:
+            # achieved int8 rate of the O^3V^3 stages (whole stage: planes of the operand, sign matrix, tensor-core kernel,
+            # fp64 remainder), rank 0's share: 2 * (o v)^3 / N * planes operations per dense product
+            prod = {"0112_0313_0113": 2 if it.fuse else 3, "0312": 1, "1302_1202": 1 if it.fuse else 2, "1303": 1, "1203": 1}
+            per = 2.0 * float(o * v) ** 3 / world * args.planes
+            line["o3v3_stage_int8_tops"] = {
+                k: round(n * per / (stage_ms[k] * 1e-3) / 1e12, 1) for k, n in prod.items() if stage_ms.get(k, 0.0) > 0.0}
+            line["o3v3_stage_int8_tops_note"] = ("dense products per stage " + json.dumps(prod) + "; unpadded int8 operations of the "
+                                                 "whole stage on rank 0 over its CUDA-event time; the ladder's kernel-only figure is roofline.achieved")
         if other_ms is not None:
             other = "invariant" if args.w_mode == "refreshed" else "refreshed"
             line["value_by_w_mode"] = {args.w_mode: s_per_iter, other: other_ms * 1e-3}
