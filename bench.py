@@ -439,6 +439,7 @@ class Iteration:
         self.plane_ms, self.ladder_ms = [], []
         self.cur_sub = -1
         self.prebuilt = -1
+        self.prepared_plugin = -1
         self.plane_side = fd.SideStream(device) if self.tc and args.overlap_planes else None
         if self.sub:
             self.fill_sub(0)
@@ -501,6 +502,9 @@ class Iteration:
             W = self.wsub(s)
             ov = self.t2new[:, :, a:b, :]
             if plugin or not self.tc:
+                if self.prepared_plugin == s:
+                    self.plane_side.join()       # py_rccsd.prepare_operand ran on the side stream during upload + compression
+                    self.prepared_plugin = -1
                 if self.tc and not refreshed:
                     self.check(self.lib.fricc_contract_planes(self.planes, _ptr(W), fd.i64x4(W.shape), fd.i64x4(W.stride()), 0,
                                                               T._h, _ptr(ov), fd.i64x4(ov.shape), fd.i64x4(ov.stride()), b"2323"))
@@ -593,6 +597,23 @@ class Iteration:
         self.mark("1203")
         eng.barrier()                                            # B2: the step's outputs are complete on every rank
         self.mark("B2")
+
+    def prepare_ladder_operand(self, timer=None):
+        """e2e (plugin calls only): encode the ladder's first sub-shard on the second stream NOW -- W does not depend on
+        T2, which is still on its way from the host -- through py_rccsd.prepare_operand; the coming
+        contract_DTSpT(W, T, t2new[..], "2323") then finds its planes ready."""
+        if self.plane_side is None or not self.sub or self.args.w_mode != "refreshed":
+            return
+        if self.cur_sub != 0:
+            if timer:
+                timer.pause()
+            self.fill_sub(0)
+            if timer:
+                timer.resume()
+        a, b = self.sub[0]
+        W, ov = self.wsub(0), self.t2new[:, :, a:b, :]
+        self.plane_side.run(lambda: self.py.prepare_operand(W, ov, "2323"))
+        self.prepared_plugin = 0
 
     def step(self, t2, timer=None):
         self.mark("begin")
@@ -975,6 +996,7 @@ def run_b200_arm(args):
 
             def e2e_step(timer):
                 it.mark("begin")
+                it.prepare_ladder_operand(timer)
                 d_t2.copy_(h_t2, non_blocking=True)
                 d0, d1 = draws[it.draw_pos % 32:], draws[(it.draw_pos + 1) % 32:]
                 it.draw_pos += 2
@@ -1012,6 +1034,7 @@ def run_b200_arm(args):
 
             def e2e_step(timer):
                 it.mark("begin")
+                it.prepare_ladder_operand(timer)
                 d_slice.copy_(h_t2, non_blocking=True)
                 full = None
                 if pivotal_full is not None:          # the pivotal walk needs the whole tensor: assemble it over NVLink
@@ -1176,10 +1199,14 @@ def run_b200_arm(args):
                            "d2h_bytes_per_step": int(d2h), "stage_ms_per_step": e2e_stage_ms, "stage_ms_slowest_step": e2e_stage_worst,
                            "through": ("T2 from pinned host memory (one upload), py_rccsd.SparseTensor4d x2 + contract_DTSpT x11 (W "
                                        "and the intermediates are device tensors), residual t2new to pinned host memory under "
-                                       "the last four contractions" if world == 1 else
+                                       "the last four contractions; the ladder's first sub-shard is encoded ahead of its call "
+                                       "(py_rccsd.prepare_operand, second stream) while T2 is uploaded and compressed" if world == 1 else
                                        "each rank: its 1/N of T2 from pinned host memory, range-sharded compression, "
                                        "py_rccsd.contract_DTSpT on L-slice views, its own 1/N of the residual (the i-range "
-                                       "its 0101 call completes) back to pinned host memory under the remaining contractions")}
+                                       "its 0101 call completes) back to pinned host memory under the remaining contractions; "
+                                       "the ladder operand is encoded ahead of its call (py_rccsd.prepare_operand, second stream) "
+                                       "while T2 is uploaded and compressed"),
+                           "prepared_plane_hits": int(py_rccsd.get_stat("prepared_plane_hits"))}
         if sweep is not None:
             line["compress_sweep"] = sweep
         default_cfg = (o, v, m, args.sampling) == (40, 400, 10_000_000, "systematic") and args.planes == 6

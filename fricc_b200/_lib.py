@@ -129,6 +129,7 @@ SIGNATURES = {
     "fricc_shard_scan_resolve": (c_int, [c_void_p, c_void_p, c_void_p]),
     "fricc_shard_emit_systematic": (c_int, [c_void_p, c_int64, c_int32, c_void_p]),
     "fricc_constant_operand": (c_int, [c_void_p, c_int64, c_int]),
+    "fricc_prepare_operand": (c_int, [c_void_p, _i64p, _i64p, _i64p, c_char_p]),
     "fricc_shard_emit_systematic_multi": (c_int, [c_void_p, c_int64, c_void_p, c_int, c_void_p, c_int64]),
     "fricc_shard_sample_chunk": (c_int, [c_void_p, c_int64, c_double, c_double, c_double, c_void_p, c_int64, _i64p, c_void_p]),
     "fricc_shard_check": (c_int, [c_void_p]),

@@ -28,7 +28,7 @@ int64_t push_copies();
 
 using namespace fricc;
 
-static int64_t g_tc_calls = 0, g_spmm_calls = 0, g_fused_pairs = 0, g_const_plane_hits = 0;
+static int64_t g_tc_calls = 0, g_spmm_calls = 0, g_fused_pairs = 0, g_const_plane_hits = 0, g_prepared_hits = 0;
 
 namespace {
 
@@ -170,6 +170,7 @@ int fricc_get_stat(const char* key, int64_t* value) {
   if (strcmp(key, "pivotal_restarts") == 0) *value = pivotal_restarts_last();
   else if (strcmp(key, "tc_contract_calls") == 0) *value = g_tc_calls;      // fricc_contract calls that took the tensor-core form
   else if (strcmp(key, "spmm_contract_calls") == 0) *value = g_spmm_calls;
+  else if (strcmp(key, "prepared_plane_hits") == 0) *value = g_prepared_hits;   // tensor-core calls that found their planes prepared
   else if (strcmp(key, "constant_plane_hits") == 0) *value = g_const_plane_hits;   // plugin calls that reused the planes of a declared-constant operand
   else if (strcmp(key, "fused_pairs") == 0) *value = g_fused_pairs;   // fricc_contract_pair calls that ran as ONE dense product
   else if (strcmp(key, "alloc_driver_calls") == 0) *value = alloc_driver_calls();   // cudaMallocAsync calls so far
@@ -395,6 +396,7 @@ struct PlaneEntry {
   int S = 0;
   uint64_t print = 0;
   uint64_t stamp = 0;
+  const double* prepared = nullptr;   // history entries: the operand fricc_prepare_operand encoded these planes from
   fricc::WSlices ws;
 };
 std::vector<PlaneEntry*> g_plane_cache;
@@ -446,7 +448,7 @@ void plane_cache_clear() {
 }
 
 const WSlices& planes_for(const double* Wd, const int64_t shape[4], const int64_t strides[4], const TermSpec& ts,
-                          const WView& view, int64_t nL, WSlices& local) {
+                          const WView& view, int64_t nL, WSlices& local, bool prepare_only = false) {
   const int S = tc_planes();
   if (is_constant_operand(Wd)) {
     // declared constant by the caller (the ERI blocks of a CC driver, fricc/friccsd.py:347-378 pass eris.ovov to five
@@ -493,7 +495,14 @@ const WSlices& planes_for(const double* Wd, const int64_t shape[4], const int64_
       g_plane_hist.push_back(hit);
     }
     hit->stamp = ++g_plane_stamp;
+    if (Wd && hit->prepared == Wd && !prepare_only) {
+      // encoded ahead of this call by fricc_prepare_operand (on whatever stream the caller chose): used once
+      hit->prepared = nullptr;
+      g_prepared_hits++;
+      return hit->ws;
+    }
     wslices_build_view(hit->ws, view, 0, nL, S);
+    hit->prepared = prepare_only ? Wd : nullptr;
     // stay under the byte budget (never evicting the entry just built)
     const size_t budget = (size_t)tc_history_mb() << 20;
     for (;;) {
@@ -628,6 +637,9 @@ int fricc_contract(const double* W, int w_mem, const int64_t w_shape[4], const i
     contract_dense(T, *ts, lay, ws, view, 0, od, om, ts->scale, false);
   } else {
     g_spmm_calls++;
+    if (w_mem == FRICC_DEVICE)
+      for (PlaneEntry* e : g_plane_hist)
+        if (e->prepared == W) e->prepared = nullptr;   // prepared for a call that did not take the tensor-core form
     DevBuf<double> panel;
     const double* Wp = Wd.p;
     if (!in_place) {
@@ -712,6 +724,23 @@ int fricc_contract_pair(const double* W_a, const int64_t a_shape[4], const int64
       contract_rest(lay, vb, 0, nL, out, om, sigma * qb);
     }
   }
+  FRICC_API_END
+}
+
+int fricc_prepare_operand(const double* W_dev, const int64_t w_shape[4], const int64_t w_strides[4],
+                          const int64_t out_strides[4], const char* term) {
+  FRICC_API_BEGIN
+  if (!W_dev || !w_shape || !w_strides || !out_strides) fail(FRICC_EINVAL, "null argument");
+  const TermSpec* ts0 = find_term(term);
+  if (!ts0) fail(FRICC_EINVAL, "CASE NOT IMPLEMENTED: unknown contraction term '%s'", term ? term : "(null)");
+  const TermSpec ts = oriented(*ts0, out_strides);
+  const int64_t nK = w_shape[ts.wK[0]] * w_shape[ts.wK[1]], nL = w_shape[ts.wL[0]] * w_shape[ts.wL[1]];
+  if (nK == 0 || nL == 0) return FRICC_OK;
+  (void)span_of(w_shape, w_strides);
+  if (tc_plane_cache() || tc_history_mb() <= 0) return FRICC_OK;   // content cache: nothing to prepare; no history: nowhere to keep it
+  const WView view = term_view(W_dev, w_shape, w_strides, ts);
+  WSlices local;
+  (void)planes_for(W_dev, w_shape, w_strides, ts, view, nL, local, /*prepare_only=*/!is_constant_operand(W_dev));
   FRICC_API_END
 }
 

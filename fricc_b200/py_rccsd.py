@@ -325,6 +325,21 @@ def constant_operand(W, on=True):
     return None
 
 
+def prepare_operand(W, ouput, term):
+    """Encode the digit planes of the CUDA tensor `W` for the coming ``contract_DTSpT(W, T, ouput, term)`` now, on the
+    library's current stream (include/fricc_b200.h: fricc_prepare_operand) -- e.g. on a second stream while T2 is still
+    on its way to the GPU: Wvvvv does not depend on it (fricc/friccsd.py:207).  `ouput` is only looked at for its
+    strides (which of the two free axes is the minor one decides the orientation of the planes).  The next call that
+    takes the tensor-core form on the same operand uses these planes, once; order the streams yourself and do not write
+    `W` in between.  An extension of the reference's surface; results are bit-identical with and without it."""
+    if not (_is_cuda_tensor(W) and _is_cuda_tensor(ouput)):
+        raise TypeError("prepare_operand(): CUDA tensors are needed (host arrays are staged per call)")
+    w = _strided4(W, "W")
+    o = _strided4(ouput, "ouput", writeable=True)
+    check(_lib.lib().fricc_prepare_operand(w.ptr, i64x4(w.shape), i64x4(w.strides), i64x4(o.strides), str(term).encode()))
+    return None
+
+
 def contract_DTSpT_experimental(W, T, ouput, term):
     """The reference's alternative 2323 kernels (``"taskloop"``, ``"atomic"``; src/sparse_tensor.cpp:445-459) differ only
     in CPU threading; both names run the same GPU ladder kernel here."""

@@ -102,6 +102,16 @@ int fricc_plane_cache_clear(void);
  * withdrawing it drops its planes; so does fricc_plane_cache_clear.  Stat "constant_plane_hits".  An extension of the
  * plugin surface (py_rccsd.constant_operand); results are bit-identical to undeclared calls.                         */
 int fricc_constant_operand(const double* p, int64_t n_elements, int on);
+/* Encode the digit planes of a device operand AHEAD of the fricc_contract / fricc_contract_pair call that will read
+ * it, on the library's current stream (fricc_set_stream) -- e.g. a second stream while T2 is still being uploaded and
+ * compressed: the ladder operand Wvvvv does not depend on T2 (fricc/friccsd.py:207 builds it from t1 and the
+ * integrals).  The next call that takes the tensor-core form on the same operand (address, shape, strides, term axes,
+ * orientation given by out_strides) uses these planes instead of building its own -- once; the caller orders the two
+ * streams (the contraction must wait for the preparation) and must not write W in between.  A call that takes the
+ * fp64 form drops the preparation.  Results are bit-identical with and without it.  Stat "prepared_plane_hits".
+ * An extension of the plugin surface (py_rccsd.prepare_operand).                                                    */
+int fricc_prepare_operand(const double* W_dev, const int64_t w_shape[4], const int64_t w_strides[4],
+                          const int64_t out_strides[4], const char* term);
 /* "d_parallel": -1 (default) = the parallel D-selection for candidate lists >= 32768 and the one-warp walk below,
  * 0 / 1 = always serial / always parallel (bit-identical).
  * "pivotal_parallel": -1 (default) = the parallel exact pivotal sampler for N >= 65536 and the one-thread chain kernel

@@ -246,6 +246,54 @@ def test_plane_cache_follows_the_operand(tc, port):
     _lib.check(_lib.lib().fricc_plane_cache_clear())
 
 
+def test_prepared_operand_is_used_once_and_only_by_the_tensor_core_form(tc, port):
+    """py_rccsd.prepare_operand (fricc_prepare_operand): planes encoded ahead of the call on a second stream are what the
+    next tensor-core call on that operand uses -- once, same bits; a call that takes the fp64 form drops them, so a later
+    tensor-core call on a rewritten operand cannot see stale planes."""
+    import torch
+
+    from fricc_b200 import dist as fd
+
+    rccsd = tc
+    rng = np.random.default_rng(91)
+    no, nv = 6, 20
+    T, flat, vals, dims = _fri(rccsd, rng, no, nv, 2500)
+    W = torch.from_numpy(rng.random((7, nv, nv, nv)) - 0.45).cuda()          # a rank's a-range of Wvvvv
+    fd.use_torch_stream()
+
+    def ladder():
+        out = torch.zeros(no, no, nv, nv, dtype=torch.float64, device="cuda")
+        ov = out[:, :, 3:10, :]
+        rccsd.contract_DTSpT(W, T, ov, "2323")
+        return out
+
+    plain = ladder()
+    side = fd.SideStream(torch.device("cuda"))
+    out = torch.zeros(no, no, nv, nv, dtype=torch.float64, device="cuda")
+    ov = out[:, :, 3:10, :]
+    h0 = rccsd.get_stat("prepared_plane_hits")
+    side.run(lambda: rccsd.prepare_operand(W, ov, "2323"))
+    side.join()
+    rccsd.contract_DTSpT(W, T, ov, "2323")
+    assert rccsd.get_stat("prepared_plane_hits") == h0 + 1
+    assert torch.equal(out, plain)
+    assert torch.equal(ladder(), plain) and rccsd.get_stat("prepared_plane_hits") == h0 + 1     # used once
+    # prepared, then the fp64 form runs on it: dropped
+    side.run(lambda: rccsd.prepare_operand(W, ov, "2323"))
+    side.join()
+    rccsd.set_option("tc_mode", 0)
+    spmm = ladder()
+    rccsd.set_option("tc_mode", 2)
+    assert _close(spmm.cpu().numpy(), plain.cpu().numpy())
+    W.mul_(-0.75).add_(0.02)
+    fresh = ladder()
+    assert rccsd.get_stat("prepared_plane_hits") == h0 + 1
+    rccsd.set_option("tc_mode", 0)
+    spmm2 = ladder()
+    rccsd.set_option("tc_mode", 2)
+    assert _close(fresh.cpu().numpy(), spmm2.cpu().numpy()) and not _close(fresh.cpu().numpy(), plain.cpu().numpy())
+
+
 def test_constant_operand_planes_are_built_once_and_follow_the_declaration(tc, port):
     """py_rccsd.constant_operand (fricc_constant_operand): the ovov integrals of a CC driver never change, so the planes
     of their views are kept -- same bits as undeclared calls for every term that reads ovov, on the whole operand and on
