@@ -134,7 +134,10 @@ static void release_cached_locked(size_t keep_bytes) {
     auto it = std::prev(best->end());
     g_cached_bytes -= it->first;
     g_block_bytes.erase(it->second);
-    cudaFreeAsync(it->second, st);
+    // a block of the stream the library is issuing on goes back in stream order; one cached under another stream (which
+    // may not even exist any more) is not ordered against that stream's work by a free on this one: cudaFree waits
+    if (st == g_stream) cudaFreeAsync(it->second, st);
+    else cudaFree(it->second);
     best->erase(it);
   }
 }
