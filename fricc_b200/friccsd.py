@@ -355,28 +355,30 @@ def kernel(eris, t1=None, t2=None, max_cycle=50, tol=1e-8, tolnormt=1e-6, m_keep
     t1_sum = t2_sum = None
     n_avg = 0
     conv = False
-    for istep in range(max_cycle):
-        t1new, t2new = update_amps(t1, t2, eris, m_keep, compressed, compression, sampling, as_reference=as_reference,
-                                   backend=backend, wvvvv_buffer=wbuf)
-        normt = amplitude_norm(t1new, t2new, t1, t2)
-        t1, t2 = t1new, t2new
-        eold, eccsd = eccsd, energy(t1, t2, eris)
-        energies.append(eccsd)
-        if callback is not None:
-            callback(istep, eccsd, eccsd - eold, normt)
-        if average_from is not None and istep + 1 >= average_from:
-            t1_sum = t1.clone() if t1_sum is None else t1_sum.add_(t1)
-            t2_sum = t2.clone() if t2_sum is None else t2_sum.add_(t2)
-            n_avg += 1
-        if abs(eccsd - eold) < tol and normt < tolnormt:
-            conv = True
-            break
-        if eccsd != eccsd or eold != eold:
-            break                                           # "FAILED THERE ARE NANS"
-        if abs(eccsd - eold) > 1e5:
-            break                                           # "FAILED BECAUSE dE = ..."
-    if declared is not None:
-        declared.constant_operand(eris.ovov, False)
+    try:
+        for istep in range(max_cycle):
+            t1new, t2new = update_amps(t1, t2, eris, m_keep, compressed, compression, sampling, as_reference=as_reference,
+                                       backend=backend, wvvvv_buffer=wbuf)
+            normt = amplitude_norm(t1new, t2new, t1, t2)
+            t1, t2 = t1new, t2new
+            eold, eccsd = eccsd, energy(t1, t2, eris)
+            energies.append(eccsd)
+            if callback is not None:
+                callback(istep, eccsd, eccsd - eold, normt)
+            if average_from is not None and istep + 1 >= average_from:
+                t1_sum = t1.clone() if t1_sum is None else t1_sum.add_(t1)
+                t2_sum = t2.clone() if t2_sum is None else t2_sum.add_(t2)
+                n_avg += 1
+            if abs(eccsd - eold) < tol and normt < tolnormt:
+                conv = True
+                break
+            if eccsd != eccsd or eold != eold:
+                break                                           # "FAILED THERE ARE NANS"
+            if abs(eccsd - eold) > 1e5:
+                break                                           # "FAILED BECAUSE dE = ..."
+    finally:
+        if declared is not None:
+            declared.constant_operand(eris.ovov, False)
     average = None
     if average_from is not None and n_avg > 0:
         t1a, t2a = t1_sum / n_avg, t2_sum / n_avg
