@@ -88,3 +88,27 @@ def test_rand_skip_is_a_jump_ahead_of_the_same_stream():
         _lib.check(L.fricc_rand_fill(got.ctypes.data_as(p32), 200))
         assert (got == want).all(), (seed, skip)
         assert L.fricc_rand_consumed() == skip + 200
+
+
+def test_plane_extensions_reject_host_arrays_and_bad_arguments():
+    """constant_operand / prepare_operand are about DEVICE operands (host arrays are staged per call, there is nothing to
+    keep or to prepare): the mirror raises TypeError, the C-ABI reports bad arguments by status code."""
+    import numpy as np
+
+    from fricc_b200 import py_rccsd
+
+    w = np.zeros((2, 3, 2, 3))
+    with pytest.raises(TypeError):
+        py_rccsd.constant_operand(w)
+    with pytest.raises(TypeError):
+        py_rccsd.prepare_operand(w, np.zeros((3, 3, 2, 2)), "0112")
+    L = _lib.lib()
+    assert L.fricc_constant_operand(None, 10, 1) == _lib.EINVAL
+    assert L.fricc_constant_operand(ctypes.c_void_p(4096), 0, 1) == _lib.EINVAL
+    i4 = _lib.i64x4((2, 2, 2, 2))
+    assert L.fricc_prepare_operand(None, i4, i4, i4, b"2323") == _lib.EINVAL
+    assert L.fricc_prepare_operand(ctypes.c_void_p(4096), i4, i4, i4, b"9999") == _lib.EINVAL
+    assert b"unknown contraction term" in L.fricc_last_error()
+    # declaring and withdrawing a range touches no memory: allowed without a device
+    assert L.fricc_constant_operand(ctypes.c_void_p(4096), 16, 1) == 0
+    assert L.fricc_constant_operand(ctypes.c_void_p(4096), 16, 0) == 0
