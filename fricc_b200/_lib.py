@@ -110,6 +110,7 @@ SIGNATURES = {
                                     c_int, c_int, _i64p, _i64p]),
     "fricc_permute_w": (c_int, [c_void_p, c_int, _i64p, _i64p, c_char_p, c_int64, c_int64, c_void_p]),
     "fricc_one_norm": (c_int, [c_void_p, c_int, c_int64, _f64p]),
+    "fricc_one_norm_static": (c_int, [c_void_p, c_int64, c_void_p, c_int]),
     "fricc_argsort": (c_int, [c_void_p, c_int, c_int64, c_int64, c_void_p]),
     "fricc_get_d_largest": (c_int, [c_void_p, c_int, c_int64, c_int64, c_void_p, _i64p, _f64p]),
     "fricc_make_probability_vector": (c_int, [c_void_p, c_int, c_int64, c_int64, c_void_p, c_int64, c_double,

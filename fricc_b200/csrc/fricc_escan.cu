@@ -676,4 +676,157 @@ void d_greedy_parallel(const uint64_t* keys, int64_t cand, int64_t n_sample, dou
   *r_out = r;
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------------
+// fricc_one_norm_static: the exact one_norm with its working memory in a fixed device array of this library.
+//
+// Who needs it.  Every other entry point takes its working buffers from the library's block cache, i.e. in the end from
+// cudaMallocAsync.  Some programs that drive this library may not do that while they run:
+//   - a coupled-cluster driver that has handed (nearly) all of the 180 GB to its own arena -- Wvvvv alone is 205 GB at
+//     v = 400, sharded to fill each GPU -- has nothing left for the library's pool to grow into, and a failed
+//     cudaMallocAsync in the middle of an iteration is not something it can recover from;
+//   - a host thread inside a latency-critical section (an MPI/NCCL progress loop, a real-time monitor): an allocation
+//     that has to map memory enters the kernel driver, where this project measured stalls of 0.03 - 2.7 s behind other
+//     processes' queries (block cache);
+//   - a process confined to a fixed memory budget by its launcher (MPS memory limits, a container's device quota), for
+//     which every byte must be accounted for before the run starts.
+// For those callers the convergence check of an iteration -- |t2new - t2|_1, the one_norm of fri_utils.cpp:164-171 --
+// can go through this entry point: same kernels (E1-E3 above), same bits, but the chunk sums, chunk maps and carries
+// live in g_norm_scratch below.  The library image carries that array, so every GPU that loads the library holds the
+// 1.3 MB from load to exit whether or not this entry point is ever called.
+//
+// Limits and rules:
+//   - n <= FRICC_ONE_NORM_STATIC_MAX_N (2^26 elements = 512 MB of doubles = 32768 chunks); larger inputs are refused
+//     with FRICC_EINVAL, they are not split (a split sum would still be exact, but the caller should decide that);
+//   - x must already be on the device (a host array would need a staging buffer, i.e. an allocation);
+//   - there is ONE array per GPU and every call uses it: two calls that may overlap on the GPU (different streams
+//     without an ordering between them, or two host threads) race on it and return garbage.  Calls on one stream are
+//     safe -- stream order separates them;
+//   - the array keeps what the previous call left there.  The pipeline overwrites all it reads (E1 writes the chunk
+//     sums, E2 the maps, E3 the carries) except the one extra addend behind the chunk sums and the error word, which
+//     are cleared with cudaMemsetAsync at the start of every call;
+//   - the first call on each device looks up the array's device address (cudaGetSymbolAddress, with that device
+//     current) and keeps it; that look-up may initialise the module on the device, so make the first call on a device
+//     during set-up, before any stream capture is begun.  Later calls only launch kernels, one memset and -- for a host
+//     result -- one 8-byte copy.
+// No cudaMalloc*, cudaFree*, DevBuf or library allocator is reached from here.
+// ---------------------------------------------------------------------------------------------------------------------
+constexpr int64_t NS_MAX_N = (int64_t)FRICC_ONE_NORM_STATIC_MAX_N;
+constexpr int64_t NS_MAX_CHUNKS = (NS_MAX_N + ES_CHUNK - 1) / ES_CHUNK;  // 32768
+constexpr size_t ns_round256(size_t b) { return (b + 255) / 256 * 256; }
+constexpr size_t NS_OFF_APPROX = 0;                                                                  // double[chunks + 1]
+constexpr size_t NS_OFF_MAPS = NS_OFF_APPROX + ns_round256((NS_MAX_CHUNKS + 1) * sizeof(double));    // ChunkMap[chunks]
+constexpr size_t NS_OFF_EXACT = NS_OFF_MAPS + ns_round256(NS_MAX_CHUNKS * sizeof(ChunkMap));         // double[chunks]
+constexpr size_t NS_OFF_TOTAL = NS_OFF_EXACT + ns_round256(NS_MAX_CHUNKS * sizeof(double));          // double
+constexpr size_t NS_OFF_FLAGS = NS_OFF_TOTAL + 256;                                                  // int err, int stats
+constexpr size_t NS_BYTES = NS_OFF_FLAGS + 256;                                                      // 1 311 488 bytes
+
+// In host code this name is only a handle for cudaGetSymbolAddress: it is NOT a device address and must never be
+// passed to a kernel or a memset.
+static __device__ __align__(256) unsigned char g_norm_scratch[NS_BYTES];
+
+constexpr int NS_MAX_DEVICES = 64;
+static unsigned char* g_norm_scratch_addr[NS_MAX_DEVICES];  // per device: the array's address on that device, 0 = not looked up
+
+static unsigned char* norm_scratch_on_current_device() {
+  int dev = -1;
+  FRICC_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= NS_MAX_DEVICES) fail(FRICC_EINVAL, "one_norm_static: device ordinal %d not supported", dev);
+  unsigned char* p = __atomic_load_n(&g_norm_scratch_addr[dev], __ATOMIC_ACQUIRE);
+  if (!p) {
+    void* q = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&q, g_norm_scratch);  // the current device's copy of the array
+    if (e != cudaSuccess || !q) {
+      cudaGetLastError();
+      fail(FRICC_ECUDA, "one_norm_static: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+    }
+    p = static_cast<unsigned char*>(q);
+    __atomic_store_n(&g_norm_scratch_addr[dev], p, __ATOMIC_RELEASE);  // racing first calls store the same value
+  }
+  return p;
+}
+
+// exclusive running sum of d[0..n) in place by ONE block (n <= 32769 here: at most 33 rounds).  These sums only predict
+// the binade of the exact running sum at each chunk start; E3 checks every prediction, so their rounding is free.
+constexpr int NS_SCAN_THREADS = 1024;
+__global__ void __launch_bounds__(NS_SCAN_THREADS) ns_excl_scan_kernel(double* __restrict__ d, int64_t n) {
+  __shared__ double s_warp[32];
+  __shared__ double s_carry;
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) s_carry = 0.0;
+  __syncthreads();
+  for (int64_t base = 0; base < n; base += NS_SCAN_THREADS) {
+    const int64_t i = base + threadIdx.x;
+    const double v = (i < n) ? d[i] : 0.0;
+    double inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const double t = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= (unsigned)o) inc += t;
+    }
+    if (lane == 31) s_warp[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+      double w = s_warp[lane];
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const double t = __shfl_up_sync(0xffffffffu, w, o);
+        if (lane >= (unsigned)o) w += t;
+      }
+      s_warp[lane] = w;
+    }
+    __syncthreads();
+    const double carry = s_carry;
+    const double before = carry + (warp ? s_warp[warp - 1] : 0.0) + (inc - v);
+    const double round_total = s_warp[31];
+    if (i < n) d[i] = before;
+    __syncthreads();
+    if (threadIdx.x == 0) s_carry = carry + round_total;
+    __syncthreads();
+  }
+}
+
+static void one_norm_static(const double* x_dev, int64_t n, double* norm, int norm_mem) {
+  if (n < 0 || !norm || (n > 0 && !x_dev)) fail(FRICC_EINVAL, "one_norm_static: bad arguments");
+  if (norm_mem != FRICC_HOST && norm_mem != FRICC_DEVICE) fail(FRICC_EINVAL, "one_norm_static: norm_mem must be FRICC_HOST or FRICC_DEVICE");
+  if (n > NS_MAX_N)
+    fail(FRICC_EINVAL,
+         "one_norm_static: n = %lld exceeds FRICC_ONE_NORM_STATIC_MAX_N = %lld (the fixed scratch array holds %lld chunks); "
+         "use fricc_one_norm, or sum ranges of at most that many elements",
+         (long long)n, (long long)NS_MAX_N, (long long)NS_MAX_CHUNKS);
+  unsigned char* base = norm_scratch_on_current_device();  // first call on this device: the address look-up
+  double* approx = reinterpret_cast<double*>(base + NS_OFF_APPROX);
+  ChunkMap* maps = reinterpret_cast<ChunkMap*>(base + NS_OFF_MAPS);
+  double* exact_in = reinterpret_cast<double*>(base + NS_OFF_EXACT);
+  double* total = reinterpret_cast<double*>(base + NS_OFF_TOTAL);
+  int* err = reinterpret_cast<int*>(base + NS_OFF_FLAGS);
+  int* stats = err + 1;
+  double* result_dev = (norm_mem == FRICC_DEVICE) ? norm : total;
+  if (n == 0) {
+    FRICC_CUDA(cudaMemsetAsync(result_dev, 0, sizeof(double), stream()));  // the empty sum is +0.0
+  } else {
+    const int64_t nchunks = ceil_div(n, ES_CHUNK);
+    PSrc ps{nullptr, x_dev, 0, 0, 0, 0, 1};
+    // what must start at zero: the addend behind the last chunk sum, and the error/statistics words (left-overs of the
+    // previous call otherwise)
+    FRICC_CUDA(cudaMemsetAsync(approx + nchunks, 0, sizeof(double), stream()));
+    FRICC_CUDA(cudaMemsetAsync(err, 0, 2 * sizeof(int), stream()));
+    FRICC_LAUNCH(escan_approx_kernel, (unsigned)nchunks, ES_THREADS, 0, ps, n, approx, err);
+    FRICC_LAUNCH(ns_excl_scan_kernel, 1, NS_SCAN_THREADS, 0, approx, nchunks + 1);
+    FRICC_LAUNCH(escan_map_kernel, (unsigned)nchunks, ES_THREADS, 0, ps, n, (const double*)approx, (const double*)nullptr, maps);
+    FRICC_LAUNCH(escan_resolve_kernel, 1, RS_THREADS, 0, ps, n, (const ChunkMap*)maps, nchunks, exact_in,
+                 (const double*)nullptr, result_dev, stats);
+  }
+  if (norm_mem == FRICC_HOST) {
+    FRICC_CUDA(cudaMemcpyAsync(norm, result_dev, sizeof(double), cudaMemcpyDeviceToHost, stream()));
+    FRICC_CUDA(cudaStreamSynchronize(stream()));
+  }
+}
+
 }  // namespace fricc
+
+extern "C" int fricc_one_norm_static(const double* x_dev, int64_t n, double* norm, int norm_mem) {
+  FRICC_API_BEGIN
+  ::fricc::one_norm_static(x_dev, n, norm, norm_mem);
+  FRICC_API_END
+}

@@ -366,6 +366,29 @@ def one_norm(x):
     return r.value
 
 
+def one_norm_static(x, out=None):
+    """one_norm for callers that must not allocate device memory while they run (an extension; the reference has no
+    counterpart).  A driver whose own arena fills the GPU, a thread that cannot afford to block in the kernel driver,
+    or a process under a fixed device-memory budget uses this instead of one_norm: the working memory of the exact
+    scan is a fixed 1.3 MB array inside the library, not a pooled buffer.  x: a CUDA float64 array of at most
+    FRICC_ONE_NORM_STATIC_MAX_N = 2**26 elements (more -> ValueError).  out: None -> the sum is returned as a float (the
+    stream is synchronised); a 1-element CUDA float64 tensor -> written there asynchronously, returned as is.
+    All calls on a GPU share the one array: keep them on one stream (overlapping calls race), and make the first call on
+    each device during set-up, before any stream capture.  Bit-identical to one_norm."""
+    xa = _Arr(x, "x", c_contiguous=True)
+    if xa.mem != FRICC_DEVICE:
+        raise TypeError("one_norm_static: x must be a CUDA array (staging a host array would allocate)")
+    if out is None:
+        r = c_double(0.0)
+        check(_lib.lib().fricc_one_norm_static(xa.ptr, xa.size, ctypes.addressof(r), FRICC_HOST))
+        return r.value
+    oa = _Arr(out, "out", c_contiguous=True)
+    if oa.mem != FRICC_DEVICE or oa.size != 1:
+        raise TypeError("one_norm_static: out must be a 1-element CUDA float64 tensor")
+    check(_lib.lib().fricc_one_norm_static(xa.ptr, xa.size, oa.ptr, FRICC_DEVICE))
+    return out
+
+
 def get_d_largest(x, n_sample):
     """-> (D, remaining_norm)   (fri_utils.cpp:400-437).  Positional order is (x, n_sample) as in the C++ signature."""
     xa = _flat_f64(x, "x")

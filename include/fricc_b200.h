@@ -293,6 +293,24 @@ int fricc_permute_w(const double* W, int w_mem, const int64_t w_shape[4], const 
 /* ---- stage-wise FRI utilities (reference: include/fri_utils.hpp:8-32) ------------------------------------------ */
 /* one_norm (fri_utils.cpp:164-171): sum |x_i| accumulated in index order (bit-identical to the 1-thread reference) */
 int fricc_one_norm(const double* x, int mem, int64_t n, double* norm);
+/* The same sum for callers that must not allocate device memory while they run.  NO COUNTERPART IN THE REFERENCE (a host
+ * code; its one_norm has no working memory at all).  Meant for a driver whose own arena already fills the GPU, for a
+ * host thread that cannot afford a trip into the kernel driver (an allocation that maps memory can stall for seconds
+ * behind other processes' queries), and for processes held to a fixed device-memory budget.  The chunk sums, chunk maps
+ * and carries of the exact scan live in a fixed 1.3 MB array inside the library image (present on every GPU that loads
+ * the library, until exit) instead of the block cache; the call issues kernels, two small memsets and -- for a host
+ * result -- one 8-byte copy, and reaches no cudaMalloc/cudaFree variant and no allocating routine.
+ *   x_dev    device pointer (a host array would need staging, i.e. an allocation), n <= FRICC_ONE_NORM_STATIC_MAX_N;
+ *            larger n -> FRICC_EINVAL with a message that names the limit
+ *   norm     where the sum goes: norm_mem = FRICC_DEVICE -> written by the last kernel, the call stays asynchronous on
+ *            the library stream; FRICC_HOST -> copied back, the stream is synchronised
+ * Bit-identical to fricc_one_norm.  All calls on a GPU share the one array and it keeps the previous call's contents:
+ * what has to start at zero is cleared by every call, and calls are safe one after another on one stream, but two calls
+ * that can overlap on the GPU (two streams without an ordering, two host threads) race on it.  The first call on each
+ * device looks up the array's address there (cudaGetSymbolAddress under the current device) and keeps it: make that
+ * first call during set-up, before any stream capture is started.                                                     */
+#define FRICC_ONE_NORM_STATIC_MAX_N (1 << 26)
+int fricc_one_norm_static(const double* x_dev, int64_t n, double* norm, int norm_mem);
 /* argsort (fri_utils.cpp:11-36): indices of the m largest |x| in descending |x| (ties: ascending index)            */
 int fricc_argsort(const double* x, int mem, int64_t n, int64_t m, int64_t* idx_out_host);
 /* get_d_largest (fri_utils.cpp:400-437) */
