@@ -92,21 +92,30 @@ static void init_pool() {
 // `nvidia-smi -lms` clock sampler.  Measured on B200 with the tracer above: cudaMallocAsync calls of 30 ms ... 2.7 s
 // inside fricc_contract, a few per hundred steps, each one long enough to drain the device (the host runs only ~300 ms
 // ahead).  With the cache a steady-state step makes NO allocation call at all: freed blocks are kept per
-// (device, stream) and handed out again by size.
+// device and handed out again by size.
 //
-// Ordering: a block freed while the library issues on stream S is only reused by allocations made while it issues on S,
-// so every use of the block is ordered behind the previous owner's work exactly as with cudaFreeAsync(p, S).
+// Ordering and ownership (round 3).  Every block remembers the device it was allocated on.  A block is cached under
+// THAT device -- never under whatever device happens to be current -- and a free that arrives while another device is
+// current does not cache at all (cudaFree, which needs no stream).  When a block is freed an event is recorded on the
+// stream the library issues on at that moment (the point cudaFreeAsync(p, S) would have ordered the free at) and kept
+// with the block; whoever takes the block out again makes its own stream wait for that event.  So reuse is ordered
+// behind the previous owner's work whichever stream asks, and a stream handle that is destroyed and whose value the
+// driver hands out again cannot inherit blocks without an ordering (the cache used to be keyed by the raw handle).
 // ---------------------------------------------------------------------------------------------------------------------
-struct CacheKey {
-  int dev;
-  cudaStream_t stream;
-  bool operator<(const CacheKey& o) const { return dev != o.dev ? dev < o.dev : stream < o.stream; }
+struct BlockInfo {
+  size_t bytes;
+  int dev;  // device the block was allocated on
+};
+struct CachedBlock {
+  void* p;
+  cudaEvent_t freed;  // recorded behind the last owner's work
 };
 // (heap objects that are never destroyed: buffers owned by static objects of other translation units are released
 // during process exit, after this unit's own statics would be gone)
 static std::mutex& g_cache_mu = *new std::mutex;
-static std::unordered_map<void*, size_t>& g_block_bytes = *new std::unordered_map<void*, size_t>;   // live or cached block -> size
-static std::map<CacheKey, std::multimap<size_t, void*>>& g_cached = *new std::map<CacheKey, std::multimap<size_t, void*>>;  // free blocks by size
+static std::unordered_map<void*, BlockInfo>& g_block_bytes = *new std::unordered_map<void*, BlockInfo>;   // live or cached block -> size, device
+static std::map<int, std::multimap<size_t, CachedBlock>>& g_cached = *new std::map<int, std::multimap<size_t, CachedBlock>>;  // device -> free blocks by size
+static std::map<int, std::vector<cudaEvent_t>>& g_event_pool = *new std::map<int, std::vector<cudaEvent_t>>;  // device -> idle events
 static size_t g_cached_bytes = 0;
 static size_t g_cache_cap = (size_t)24 << 30;       // "alloc_cache_mb": total bytes kept (0 = no caching)
 static size_t g_cache_max_block = (size_t)2 << 30;  // larger blocks (digit planes of a ladder slice) go back to the driver
@@ -123,22 +132,48 @@ static size_t round_block(size_t bytes) {
   return (bytes + step - 1) & ~(step - 1);
 }
 
+// an event of device `dev` (which must be current); nullptr if the runtime refuses (e.g. during process exit)
+static cudaEvent_t take_event_locked(int dev) {
+  auto& pool = g_event_pool[dev];
+  if (!pool.empty()) {
+    cudaEvent_t e = pool.back();
+    pool.pop_back();
+    return e;
+  }
+  cudaEvent_t e = nullptr;
+  if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) {
+    cudaGetLastError();
+    return nullptr;
+  }
+  return e;
+}
+
 static void release_cached_locked(size_t keep_bytes) {
   // give the largest blocks back to the driver first, until at most keep_bytes stay cached
+  int cur = -1;
+  if (cudaGetDevice(&cur) != cudaSuccess) { cudaGetLastError(); cur = -1; }
   while (g_cached_bytes > keep_bytes) {
-    std::multimap<size_t, void*>* best = nullptr;
-    cudaStream_t st = nullptr;
+    std::multimap<size_t, CachedBlock>* best = nullptr;
+    int bdev = -1;
     for (auto& kv : g_cached)
-      if (!kv.second.empty() && (!best || kv.second.rbegin()->first > best->rbegin()->first)) { best = &kv.second; st = kv.first.stream; }
+      if (!kv.second.empty() && (!best || kv.second.rbegin()->first > best->rbegin()->first)) { best = &kv.second; bdev = kv.first; }
     if (!best) break;
     auto it = std::prev(best->end());
+    const CachedBlock b = it->second;
     g_cached_bytes -= it->first;
-    g_block_bytes.erase(it->second);
-    // a block of the stream the library is issuing on goes back in stream order; one cached under another stream (which
-    // may not even exist any more) is not ordered against that stream's work by a free on this one: cudaFree waits
-    if (st == g_stream) cudaFreeAsync(it->second, st);
-    else cudaFree(it->second);
+    g_block_bytes.erase(b.p);
     best->erase(it);
+    if (bdev == cur && cudaStreamWaitEvent(g_stream, b.freed, 0) == cudaSuccess) {
+      // a block of the current device goes back in stream order, behind the work its last owner had queued
+      cudaFreeAsync(b.p, g_stream);
+      g_event_pool[bdev].push_back(b.freed);
+    } else {
+      // another device is current (or the stream refused the wait): cudaFree needs no stream and waits by itself
+      cudaGetLastError();
+      cudaFree(b.p);
+      cudaEventDestroy(b.freed);
+    }
+    cudaGetLastError();
   }
 }
 
@@ -159,17 +194,26 @@ void* dev_alloc(size_t bytes) {
   int dev = 0;
   cudaGetDevice(&dev);
   {
-    std::lock_guard<std::mutex> lk(g_cache_mu);
-    auto f = g_cached.find(CacheKey{dev, g_stream});
+    std::unique_lock<std::mutex> lk(g_cache_mu);
+    auto f = g_cached.find(dev);
     if (f != g_cached.end()) {
       auto it = f->second.lower_bound(want);
       // a larger block will do if it wastes little (blocks of one size class differ by < 12.5 %; small ones may take 2x)
       if (it != f->second.end() && it->first <= want + (want >= ((size_t)64 << 20) ? want / 8 : want)) {
-        void* p = it->second;
+        const CachedBlock b = it->second;
         g_cached_bytes -= it->first;
         f->second.erase(it);
+        // the new owner's stream waits for the previous owner's work (a no-op on the device when it is the same stream);
+        // the wait is taken at this moment, so the event can be recorded again by the next free straight away
+        const cudaError_t we = cudaStreamWaitEvent(g_stream, b.freed, 0);
+        g_event_pool[dev].push_back(b.freed);
+        lk.unlock();
+        if (we != cudaSuccess) {
+          cudaGetLastError();
+          FRICC_CUDA(cudaDeviceSynchronize());  // no stream-side ordering to be had: order by waiting
+        }
         g_alloc_hits.fetch_add(1, std::memory_order_relaxed);
-        return p;
+        return b.p;
       }
     }
   }
@@ -191,24 +235,45 @@ void* dev_alloc(size_t bytes) {
   }
   g_alloc_calls.fetch_add(1, std::memory_order_relaxed);
   std::lock_guard<std::mutex> lk(g_cache_mu);
-  g_block_bytes[p] = want;
+  g_block_bytes[p] = BlockInfo{want, dev};
   return p;
 }
 
 void dev_free(void* p) {
   if (!p) return;
-  int dev = 0;
-  cudaGetDevice(&dev);
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess) { cudaGetLastError(); dev = -1; }
   std::lock_guard<std::mutex> lk(g_cache_mu);
   auto it = g_block_bytes.find(p);
-  const size_t bytes = it == g_block_bytes.end() ? 0 : it->second;
-  if (bytes == 0 || bytes > g_cache_max_block || g_cache_cap == 0) {
-    if (it != g_block_bytes.end()) g_block_bytes.erase(it);
+  const bool known = it != g_block_bytes.end();
+  const size_t bytes = known ? it->second.bytes : 0;
+  const int owner = known ? it->second.dev : dev;
+  if (owner != dev) {
+    // freed while another device is current: g_stream belongs to that other device, so neither a stream-ordered free nor
+    // an event on it can order anything for this block
+    if (known) g_block_bytes.erase(it);
+    SlowScope slow("cudaFree (block of another device)", __FILE__, __LINE__);
+    cudaFree(p);
+    cudaGetLastError();
+    return;
+  }
+  cudaEvent_t ev = nullptr;
+  const bool cacheable = bytes != 0 && bytes <= g_cache_max_block && g_cache_cap != 0;
+  if (cacheable) {
+    ev = take_event_locked(dev);
+    if (ev && cudaEventRecord(ev, g_stream) != cudaSuccess) {
+      cudaGetLastError();
+      g_event_pool[dev].push_back(ev);
+      ev = nullptr;
+    }
+  }
+  if (!ev) {
+    if (known) g_block_bytes.erase(it);
     SlowScope slow("cudaFreeAsync", __FILE__, __LINE__);
     cudaFreeAsync(p, g_stream);
     return;
   }
-  g_cached[CacheKey{dev, g_stream}].emplace(bytes, p);
+  g_cached[dev].emplace(bytes, CachedBlock{p, ev});
   g_cached_bytes += bytes;
   if (g_cached_bytes > g_cache_cap) release_cached_locked(g_cache_cap - g_cache_cap / 4);
 }

@@ -61,7 +61,8 @@ int fricc_stream_synchronize(void);
  * cudaMemcpy(2D)Async per peer (copy engines, no SM); 0 (default) = always the store kernel (same bytes in the same
  * places; measured faster for the step as a whole, see fricc_peer.cu).
  * "alloc_cache_mb": bytes of freed per-call scratch (sign matrices, CSR remainders, sort buffers; blocks up to 2 GB) the
- * library keeps per (device, stream) and hands out again by size instead of going back to cudaMallocAsync -- default
+ * library keeps per device (each block with an event recorded at its free; the stream that takes it out again waits for
+ * that event, so reuse is ordered whichever stream asks) and hands out again by size instead of going back to cudaMallocAsync -- default
  * 24576, 0 = none.  A steady-state iteration then makes no allocation call at all: a cudaMallocAsync that has to map
  * memory enters the kernel driver and queues behind e.g. `nvidia-smi -lms` queries (measured: 0.03 - 2.7 s host stalls).
  * "release_cached" (any value): give every cached block back now.  Stats "alloc_driver_calls" / "alloc_cache_hits".
