@@ -289,6 +289,11 @@ def _sample_systematic(shard, comm, nsamp, nD, idx, flat, mm, count, draws):
     return 1
 
 
+_PEER_ERRORS = {_lib.EPROB: "ERROR MAKING PROBABILITY VECTOR", _lib.EPIVOTAL: "ERROR IN PIVOTAL SAMPLING",
+                _lib.ECOUNT: "sampler produced the wrong number of samples", _lib.EDRAWS: "draw buffer too short",
+                _lib.EINVAL: "bad argument", _lib.ECUDA: "CUDA error"}
+
+
 def _sample_parallel(shard, comm, nsamp, nD, idx, flat, mm, count, draws):
     """parallel_sample (fri_utils.cpp:176-362, "Alg. A.2") with ONE CHUNK PER RANK over the same probabilities: exact
     |q|_1 over all ranks and |q_j|_1 per chunk (the scan stages), budgets on the host (chunk_budgets), then every rank
@@ -321,6 +326,9 @@ def _sample_parallel(shard, comm, nsamp, nD, idx, flat, mm, count, draws):
             continue
         if draws is None:
             nb = world - 1
+            # every rank's copy of the stream ends this compression exactly (world - 1) + N draws further on, whatever
+            # happens in between (a failing rank that stopped short would leave the copies at different positions)
+            stream_end = int(L.fricc_rand_consumed()) + nb + shard.n_total
             bd = (ctypes.c_int32 * max(nb, 1))()
             if nb > 0:
                 check(L.fricc_rand_fill(bd, nb))
@@ -343,7 +351,7 @@ def _sample_parallel(shard, comm, nsamp, nD, idx, flat, mm, count, draws):
         except _lib.FriccError as e:          # raised on every rank after the collectives below (compress_ranges_multi)
             failure = failure or e
         if chunk_draws is None:
-            check(L.fricc_rand_skip(shard.n_total - shard.j0 - int(used.value)))
+            check(L.fricc_rand_skip(max(0, stream_end - int(L.fricc_rand_consumed()))))
     return consumed, failure
 
 
@@ -437,24 +445,28 @@ def compress_ranges_multi(x_local, j0, dims, m, comm, compression="fri", samplin
             check(L.fricc_shard_values(shard.h, _ptr(flat[k * mm:]), m, n_exact, _ptr(vals[k * mm:])))
         _all_reduce(comm, vals)
         # a kernel error on any rank (some p > 1: fri_utils.cpp:383-395) is raised on every rank
-        err = torch.zeros(1, dtype=torch.int64, device=dev)
+        # (the status code travels, negated, through a max-reduction: peers raise the same kind of error, not a generic one)
         msg = failure
-        if failure is not None:
-            err += 1
         if compression == "fri" and failure is None:
             try:
                 check(L.fricc_shard_check(shard.h))
             except _lib.FriccError as e:
-                err += 1
                 msg = e
+        err = torch.full((1,), 0 if msg is None else -int(msg.code), dtype=torch.int64, device=dev)
         _all_reduce(comm, err, "max")
-        if int(err.item()):
-            raise msg if msg is not None else _lib.FriccError(_lib.EPROB, "ERROR MAKING PROBABILITY VECTOR on another rank")
+        code = -int(err.item())
+        if code:
+            raise msg if msg is not None else _lib.FriccError(code, f"{_PEER_ERRORS.get(code, 'error')} on another rank")
         out = []
         for k in range(count):
             T = SparseTensor4d.from_coo(flat[k * mm: k * mm + m], vals[k * mm: k * mm + m], dims)
             check(L.fricc_st_set_n_exact(T._h, int(n_exact)))
-            T.consumed_draws = consumed
+            # consumed_draws: always an int -- the draws THIS rank's samplers read in the last compression (1 for the
+            # systematic sampler; budget draws + this chunk's draws for "parallel", whose split is consumed_draws_parts)
+            if isinstance(consumed, tuple):
+                T.consumed_draws, T.consumed_draws_parts = int(consumed[0]) + int(consumed[1]), consumed
+            else:
+                T.consumed_draws, T.consumed_draws_parts = int(consumed), None
             out.append(T)
         return out
     finally:

@@ -55,7 +55,7 @@ def parallel_cases(rng, rank, world, comm):
         mine = torch.from_numpy(x[j0:j0 + cnt].copy()).cuda()
         T = ranges.compress_ranges(mine, j0, dims, m, comm, "fri", "parallel", draws=(budget, chunk_draws[rank]))
         used = [None] * world
-        dist.all_gather_object(used, T.consumed_draws)
+        dist.all_gather_object(used, T.consumed_draws_parts)
         D, r = P.get_d_largest(x, m)
         nsamp = m - D.size
         flat, vals = T.export()

@@ -75,7 +75,7 @@ def test_single_chunk_parallel_sampler_vs_oracle(rccsd, port, kind, dims, frac):
     flat, vals = T.export()
     assert np.array_equal(flat, np.concatenate([D, S]))
     assert np.array_equal(vals.view(np.int64), np.concatenate([x[D], x[S] / p[S]]).view(np.int64))
-    assert T.consumed_draws == (0, used)
+    assert T.consumed_draws_parts == (0, used) and T.consumed_draws == used
 
 
 def test_carry_in_scan_is_the_sequential_sum(rccsd):
