@@ -18,6 +18,8 @@ void set_push_ctas_per_sm(int n);  // fricc_peer.cu: grid cap of the peer-store 
 void set_push_carveout(int pct);   // fricc_peer.cu: L1/shared split the peer-store kernels ask for (-1: default)
 void set_push_copy_engine(int on);  // fricc_peer.cu: long-row views go through cudaMemcpy(2D)Async instead of the store kernel
 void set_push_min_row_bytes(int n);
+void set_peer_barrier_timeout_s(int s);       // fricc_peer.cu: how long a barrier waits for a missing rank (0 = for ever)
+unsigned long long peer_barrier_timed_out();  // epoch of the first barrier that gave up since the last check (clears it)
 void set_uniform_carveout(int pct);  // fricc_runtime.cu
 void set_alloc_cache_mb(int mb);     // fricc_runtime.cu: bytes of freed scratch blocks kept for the next call (0: none)
 void release_cached_blocks();
@@ -140,6 +142,9 @@ int fricc_set_stream(void* s) {
 int fricc_stream_synchronize(void) {
   FRICC_API_BEGIN
   FRICC_CUDA(cudaStreamSynchronize(stream()));
+  if (const unsigned long long e = peer_barrier_timed_out())
+    fail(FRICC_ECUDA, "fricc_peer_barrier number %llu gave up waiting for a peer (option \"peer_barrier_timeout_s\"): "
+                      "results queued behind it are void", e);
   FRICC_API_END
 }
 int64_t fricc_kernel_launches(void) { return fricc::launches(); }
@@ -155,6 +160,7 @@ int fricc_set_option(const char* key, int value) {
   else if (key && strcmp(key, "push_carveout") == 0) set_push_carveout(value);
   else if (key && strcmp(key, "push_copy_engine") == 0) set_push_copy_engine(value);
   else if (key && strcmp(key, "push_min_row_bytes") == 0) set_push_min_row_bytes(value);
+  else if (key && strcmp(key, "peer_barrier_timeout_s") == 0) set_peer_barrier_timeout_s(value);
   else if (key && strcmp(key, "uniform_carveout") == 0) set_uniform_carveout(value);
   else if (key && strcmp(key, "alloc_cache_mb") == 0) set_alloc_cache_mb(value);
   else if (key && strcmp(key, "release_cached") == 0) release_cached_blocks();
@@ -175,6 +181,7 @@ int fricc_get_stat(const char* key, int64_t* value) {
   else if (strcmp(key, "fused_pairs") == 0) *value = g_fused_pairs;   // fricc_contract_pair calls that ran as ONE dense product
   else if (strcmp(key, "alloc_driver_calls") == 0) *value = alloc_driver_calls();   // cudaMallocAsync calls so far
   else if (strcmp(key, "alloc_cache_hits") == 0) *value = alloc_cache_hits();       // allocations served from cached blocks
+  else if (strcmp(key, "peer_barrier_timeouts") == 0) *value = (int64_t)peer_barrier_timed_out();   // epoch of the first barrier that gave up (0 = none); clears it
   else if (strcmp(key, "push_copies") == 0) *value = push_copies();   // cudaMemcpy(2D)Async calls issued by fricc_push_view
   else if (strcmp(key, "planes_predicted_builds") == 0) *value = planes_predicted_builds();  // builds that reused exponents  // ... and the fp64 SpMM
   else fail(FRICC_EINVAL, "unknown stat '%s'", key);
@@ -398,7 +405,29 @@ struct PlaneEntry {
   uint64_t stamp = 0;
   const double* prepared = nullptr;   // history entries: the operand fricc_prepare_operand encoded these planes from
   fricc::WSlices ws;
+  // History entries are shared by every operand of one geometry and may be rebuilt on one stream (fricc_prepare_operand
+  // on the caller's second stream) while a contraction on another stream still reads them, or read before the build on
+  // the other stream has finished.  Two events close both holes inside the library, whatever the caller's own stream
+  // discipline is: `ready` is recorded behind every build and waited for by the stream of every reader; `last_use` is
+  // recorded behind every reader and waited for by the stream of the next build.
+  cudaEvent_t ready = nullptr, last_use = nullptr;
+  static void mark(cudaEvent_t& ev) {   // record on the library's stream (event created on first use)
+    if (!ev) FRICC_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    FRICC_CUDA(cudaEventRecord(ev, fricc::stream()));
+  }
+  static void wait(cudaEvent_t ev) {    // the library's stream waits (nothing to wait for before the first record)
+    if (ev) FRICC_CUDA(cudaStreamWaitEvent(fricc::stream(), ev, 0));
+  }
+  ~PlaneEntry() {
+    if (ready) cudaEventDestroy(ready);
+    if (last_use) cudaEventDestroy(last_use);
+  }
 };
+PlaneEntry* g_planes_in_use = nullptr;   // the history entry planes_for handed out last (its reader records last_use)
+void planes_used() {
+  if (g_planes_in_use) PlaneEntry::mark(g_planes_in_use->last_use);
+  g_planes_in_use = nullptr;
+}
 std::vector<PlaneEntry*> g_plane_cache;
 // Operands the caller has declared constant (fricc_constant_operand): address ranges, and their planes keyed by
 // (address, shape, strides, K/L axes, planes) -- no fingerprint, no read-back: the declaration is the guarantee.
@@ -443,6 +472,7 @@ void plane_cache_clear() {
   g_plane_cache.clear();
   for (PlaneEntry* e : g_plane_hist) delete e;
   g_plane_hist.clear();
+  g_planes_in_use = nullptr;
   delete g_pair_planes;
   g_pair_planes = nullptr;
 }
@@ -450,6 +480,7 @@ void plane_cache_clear() {
 const WSlices& planes_for(const double* Wd, const int64_t shape[4], const int64_t strides[4], const TermSpec& ts,
                           const WView& view, int64_t nL, WSlices& local, bool prepare_only = false) {
   const int S = tc_planes();
+  g_planes_in_use = nullptr;
   if (is_constant_operand(Wd)) {
     // declared constant by the caller (the ERI blocks of a CC driver, fricc/friccsd.py:347-378 pass eris.ovov to five
     // of the eleven terms in every iteration): planes are built on first use and kept
@@ -499,10 +530,15 @@ const WSlices& planes_for(const double* Wd, const int64_t shape[4], const int64_
       // encoded ahead of this call by fricc_prepare_operand (on whatever stream the caller chose): used once
       hit->prepared = nullptr;
       g_prepared_hits++;
+      PlaneEntry::wait(hit->ready);       // the reader's stream is ordered behind the encoding
+      g_planes_in_use = hit;
       return hit->ws;
     }
+    PlaneEntry::wait(hit->last_use);      // the build overwrites planes a reader on another stream may still be using
     wslices_build_view(hit->ws, view, 0, nL, S);
+    PlaneEntry::mark(hit->ready);
     hit->prepared = prepare_only ? Wd : nullptr;
+    g_planes_in_use = prepare_only ? nullptr : hit;
     // stay under the byte budget (never evicting the entry just built)
     const size_t budget = (size_t)tc_history_mb() << 20;
     for (;;) {
@@ -514,6 +550,7 @@ const WSlices& planes_for(const double* Wd, const int64_t shape[4], const int64_
       }
       if (total <= budget || !lru) break;
       g_plane_hist.erase(std::find(g_plane_hist.begin(), g_plane_hist.end(), lru));
+      if (g_planes_in_use == lru) g_planes_in_use = nullptr;
       delete lru;
     }
     return hit->ws;
@@ -635,6 +672,7 @@ int fricc_contract(const double* W, int w_mem, const int64_t w_shape[4], const i
     const WSlices& ws = planes_for(w_mem == FRICC_DEVICE ? W : nullptr, w_shape, w_strides, *ts, view, nL, local);
     Layout& lay = get_layout(T, *ts, false);
     contract_dense(T, *ts, lay, ws, view, 0, od, om, ts->scale, false);
+    planes_used();
   } else {
     g_spmm_calls++;
     if (w_mem == FRICC_DEVICE)
@@ -691,7 +729,10 @@ int fricc_contract_pair(const double* W_a, const int64_t a_shape[4], const int64
   // shape agreement of each term with T / out: let the plain path report it
   for (int q = 0; q < 2; q++)
     if (a_shape[tsa.wK[q]] != d[tsa.tK[q]] || b_shape[tsb.wK[q]] != d[tsb.tK[q]] || out_shape[tsa.oR[q]] != d[tsa.tR[q]] ||
-        out_shape[tsa.oL[q]] != a_shape[tsa.wL[q]])
+        out_shape[tsa.oL[q]] != a_shape[tsa.wL[q]] ||
+        // term b axis by axis as well: on the same-operand path its owner pair comes from OTHER axes of T than term a's,
+        // and the product test above lets a T whose two extents are swapped against out (3,4 vs 4,3) through
+        out_shape[tsb.oR[q]] != d[tsb.tR[q]] || out_shape[tsb.oL[q]] != b_shape[tsb.wL[q]])
       return two_calls();
   (void)span_of(a_shape, a_strides);
   (void)span_of(b_shape, b_strides);
@@ -709,6 +750,7 @@ int fricc_contract_pair(const double* W_a, const int64_t a_shape[4], const int64
     Layout& la = get_layout(T, tsa, false);
     Layout& lb = get_layout(T, tsb, false);
     contract_dense_pair(T, tsa, la, (int)qa, tsb, lb, (int)qb, sigma, ws, view, 0, out, om);
+    planes_used();
   } else {
     // one sign matrix, two operands: planes of the combination q_a W_a + q_b W_b, cut straight from the two views (no fp64
     // copy of it); the exact entries take the fp64 remainder on each view

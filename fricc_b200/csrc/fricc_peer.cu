@@ -215,18 +215,40 @@ void push_view(const double* local, double* const* peer, int n_peers, int self, 
 // peer q (release, system scope: everything this rank's earlier kernels stored into q's memory is ordered before it),
 // then waits until its own flags[q] >= e for every q (acquire).  The kernel sits on the rank's stream, so work queued
 // behind it starts only when every rank has reached the barrier; the host never blocks.  Each rank spins on ITS OWN GPU.
-__global__ void peer_barrier_kernel(PeerPtrs flags, int n_peers, int self, unsigned long long epoch) {
+// A rank that never arrives: by default the wait gives up after g_barrier_timeout_s (option "peer_barrier_timeout_s",
+// default 300; 0 = wait for ever).  It does NOT trap -- a trap destroys the CUDA context of a healthy rank whose peer
+// is merely slow (first-iteration plane build of a 25 GB slice, a host stall) -- it records the epoch in
+// g_barrier_timed_out and lets the stream run on; fricc_stream_synchronize and fricc_get_stat("peer_barrier_timeouts")
+// read the word and the former turns it into an error, so the host learns that results behind that barrier are void.
+static __device__ unsigned long long g_barrier_timed_out;  // epoch of the first barrier that gave up since the last check
+static int g_barrier_timeout_s = 300;
+static bool g_barrier_used = false;
+void set_peer_barrier_timeout_s(int s) { g_barrier_timeout_s = s < 0 ? 0 : s; }
+
+__global__ void peer_barrier_kernel(PeerPtrs flags, int n_peers, int self, unsigned long long epoch,
+                                    unsigned long long timeout_ns) {
   const int q = threadIdx.x;
   if (q >= n_peers) return;
   unsigned long long* mine = reinterpret_cast<unsigned long long*>(flags.p[self]);
   if (q != self) {
     unsigned long long* theirs = reinterpret_cast<unsigned long long*>(flags.p[q]) + self;
+    // peer stores of earlier kernels on this stream -- and of a joined side stream -- are complete at the kernel boundary;
+    // the fence makes that explicit for every scope before the flag goes out
+    __threadfence_system();
     asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(theirs), "l"(epoch) : "memory");
-    const long long t0 = clock64();
+    unsigned long long t0, now;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
     unsigned long long seen = 0;
+    unsigned spins = 0;
     do {
       asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(seen) : "l"(mine + q) : "memory");
-      if (seen < epoch && clock64() - t0 > 40000000000LL) __trap();  // ~20 s: a rank is gone
+      if (seen < epoch && timeout_ns && (++spins & 1023u) == 0) {
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+        if (now - t0 > timeout_ns) {
+          atomicCAS(&g_barrier_timed_out, 0ULL, epoch);
+          break;
+        }
+      }
     } while (seen < epoch);
   }
 }
@@ -236,7 +258,23 @@ void peer_barrier(double* const* flags_peer, int n_peers, int self, unsigned lon
   if (n_peers > MAX_PEERS) fail(FRICC_EINVAL, "at most %d peers", MAX_PEERS);
   PeerPtrs pp;
   for (int q = 0; q < MAX_PEERS; q++) pp.p[q] = q < n_peers ? flags_peer[q] : nullptr;
-  FRICC_LAUNCH(peer_barrier_kernel, 1, 32, 0, pp, n_peers, self, epoch);
+  g_barrier_used = true;
+  FRICC_LAUNCH(peer_barrier_kernel, 1, 32, 0, pp, n_peers, self, epoch,
+               (unsigned long long)g_barrier_timeout_s * 1000000000ULL);
+}
+
+// epoch of the first barrier that gave up since the last call (0 = none); clears the word.  Synchronises the stream.
+unsigned long long peer_barrier_timed_out() {
+  if (!g_barrier_used) return 0;
+  unsigned long long h = 0;
+  FRICC_CUDA(cudaMemcpyFromSymbolAsync(&h, g_barrier_timed_out, sizeof(h), 0, cudaMemcpyDeviceToHost, stream()));
+  FRICC_CUDA(cudaStreamSynchronize(stream()));
+  if (h) {
+    const unsigned long long zero = 0;
+    FRICC_CUDA(cudaMemcpyToSymbolAsync(g_barrier_timed_out, &zero, sizeof(zero), 0, cudaMemcpyHostToDevice, stream()));
+    FRICC_CUDA(cudaStreamSynchronize(stream()));
+  }
+  return h;
 }
 
 // counter-based uniform fill: dst[i] = U(0,1) of (seed, first_index + i) -- a synthetic operand whose values depend on

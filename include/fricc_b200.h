@@ -224,7 +224,10 @@ int fricc_push_view(const double* view_local_dev, void* const* view_peer_dev, in
  * (1, 2, 3, ... -- the same sequence on every rank): one small kernel stores the epoch into every peer's counter for
  * this rank (release: this rank's earlier peer stores are ordered before it) and waits for all peers' epochs in its own
  * counters.  Work queued on the library stream behind the call starts when every rank has reached it.  One process per
- * GPU only: two ranks spinning on ONE device can starve each other.                                                   */
+ * GPU only: two ranks spinning on ONE device can starve each other.  A rank that never arrives: after option
+ * "peer_barrier_timeout_s" seconds (default 300; 0 = wait for ever) the wait gives up WITHOUT trapping (the context
+ * survives), records the epoch, and the next fricc_stream_synchronize returns FRICC_ECUDA naming it
+ * (fricc_get_stat("peer_barrier_timeouts") reads and clears the same word).                                            */
 int fricc_peer_barrier(void* const* flags_peer_dev, int n_peers, int self, uint64_t epoch);
 /* synthetic operand for benchmarks: dst[i] = U(0,1) as a function of (seed, first_index + i) only (counter-based), so
  * any sharding of a tensor filled this way holds the same numbers                                                    */

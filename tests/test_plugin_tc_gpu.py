@@ -468,3 +468,26 @@ def test_pair_that_cannot_fuse_falls_back_to_two_calls(tc, port):
     rccsd.contract_DTSpT_pair(torch.from_numpy(Wvoov).cuda(), torch.from_numpy(Wvovo).cuda(), T, got, "1303", "1203")
     assert rccsd.get_stat("fused_pairs") == before
     assert _close(got.cpu().numpy(), want)
+
+
+def test_pair_with_a_mismatched_tensor_reports_the_plain_calls_error(tc):
+    """A T whose extents do not fit term b axis by axis must get the error the two plain calls give, never a fused
+    product with the wrong owner split (round-2 advice: the fused path checked term b's owner pair only by its product)."""
+    import torch
+
+    rccsd = tc
+    rng = np.random.default_rng(81)
+    no, nv = 6, 14
+    W = torch.from_numpy(rng.random((no, nv, no, nv))).cuda()          # ovov, read by 0112 and 0113
+    for dims in [(no, no, nv, nv + 1), (no, no, nv + 1, nv), (no + 1, no, nv, nv)]:
+        x = rng.random(dims) - 0.5
+        T = rccsd.SparseTensor4d(x, dims, int(0.6 * x.size), "fri", "systematic")
+        out = torch.zeros(nv, no, no, nv, dtype=torch.float64, device="cuda")
+        before = rccsd.get_stat("fused_pairs")
+        with pytest.raises(ValueError):
+            rccsd.contract_DTSpT_pair(W, W, T, out, "0112", "0113")
+        assert rccsd.get_stat("fused_pairs") == before
+        plain = torch.zeros_like(out)
+        with pytest.raises(ValueError):
+            rccsd.contract_DTSpT(W, T, plain, "0112")
+            rccsd.contract_DTSpT(W, T, plain, "0113")
