@@ -94,6 +94,9 @@ def parse_args():
                         "iteration); invariant: planes built once (FRILCCSD)")
     p.add_argument("--max-slice-gb", type=float, default=26.0, help="largest resident ladder W sub-shard (fp64 GB)")
     p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--no-pairs", action="store_true",
+                   help="skip the small configurations both arms run in full (measured_configs / same_config_pairs)")
+    p.add_argument("--no-spot-check", action="store_true", help="skip the host fp64 recomputation of random output elements")
     p.add_argument("--no-clocks", action="store_true", help="diagnostic: do not run the nvidia-smi clock sampler")
     p.add_argument("--clock-period-ms", type=int, default=200, help="sampling period of the nvidia-smi clock sampler")
     p.add_argument("--stall-trace", type=float, default=0.0,
@@ -213,6 +216,21 @@ def _time_point(R, P, o, v, m_comp, m_con, sampling, terms, rng, n_comp=2):
     return out
 
 
+# host-feasible configurations that BOTH arms run in full: a measured, same-config pair beside the extrapolated headline
+# (BASELINE.json config 2's benzene shape, and the largest o = 40 shape whose 11 terms the host finishes in about a minute)
+SAME_CONFIG_PAIRS = [(21, 93, 1_000_000), (40, 120, 1_000_000)]
+
+
+def measure_full_config(R, P, o, v, m, sampling):
+    """The reference's CPU path RUN IN FULL at (o, v, m): 2 x SparseTensor4d(fri) + the 11 contract_DTSpT terms, no model."""
+    import numpy as np
+
+    pt = _time_point(R, P, o, v, m, m, sampling, CONTRACTION_ORDER, np.random.default_rng(2), n_comp=2)
+    total = 2 * pt["compress"] + sum(pt[t] for t in CONTRACTION_ORDER)
+    return {"o": o, "v": v, "m": int(m), "sampling": sampling, "cpu_s": total, "same_config": True,
+            "parts_s": {k: round(x, 4) for k, x in pt.items()}}
+
+
 def cpu_reference_sample(o, v, m, sampling, threads, scale=1.0):
     """One bounded sample of the reference's CPU path -> seconds per FRI-CCSD iteration at (o, v, m).
 
@@ -330,6 +348,11 @@ def run_reference_arm(args):
         "gpu_launches": 0, "fit": r["fit"], "sample_points": r.get("points"), "parts_s": r["parts"],
         "per_step_values": [round(x, 3) for x in vals],
     }
+    if not args.no_pairs:
+        R, P = _ref_modules(threads)
+        line["measured_configs"] = [measure_full_config(R, P, o2, v2, m2, args.sampling) for o2, v2, m2 in SAME_CONFIG_PAIRS]
+        for c in line["measured_configs"]:
+            c["cores"], c["kind"] = threads, ("reference" if R is not None else "port")
     print(json.dumps(line))
 
 
@@ -633,6 +656,7 @@ class Iteration:
         T, T_alt = self.compress_two(flat[j0:j0 + cnt], j0, full=t2)
         self.mark("compress_x2")
         self.contractions(T, T_alt, timer, plugin=False)
+        self.last_pair = (T, T_alt)
         return T
 
     def stage_breakdown(self, steps):
@@ -651,6 +675,140 @@ class Iteration:
         self.stage_worst = {k: round(x, 3) for k, x in worst.items()}    # the slowest single step, per stage
         self.stage_worst_host = {k: round(x, 3) for k, x in host.items()}
         return {k: round(x / steps, 3) for k, x in out.items()}
+
+
+# ---- host spot check of a step's outputs (outside the timed region) ---------------------------------------------------
+# term -> (prefactor, W indices, T indices, output indices): the einsum strings of the reference's own tests
+# (fricc/tests/test_sparse_tensors.py:48-269), i.e. what src/sparse_tensor.cpp:12-346 computes term by term
+SPOT_TERMS = {"2323": (1.0, "abcd", "ijcd", "ijab"), "0101": (1.0, "klij", "klab", "ijab"),
+              "1302": (2.0, "akic", "kjcb", "ijab"), "1202": (-1.0, "akci", "kjcb", "ijab"),
+              "1303": (1.0, "akic", "kjbc", "ijab"), "1203": (1.0, "bkci", "kjac", "ijab"),
+              "1323": (1.0, "kcld", "ijcd", "klij"), "0112": (-0.5, "ldkc", "ilda", "akic"),
+              "0313": (-0.5, "lckd", "ilad", "akic"), "0113": (1.0, "ldkc", "ilad", "akic"),
+              "0312": (-0.5, "lckd", "ilda", "akci")}
+
+
+def fill_uniform_host(idx, seed):
+    """fricc_fill_uniform on the host: the value at GLOBAL element index idx (uint64 array) -- a function of (seed, idx) only."""
+    import numpy as np
+
+    with np.errstate(over="ignore"):
+        z = idx.astype(np.uint64) * np.uint64(0x9E3779B97F4A7C15) + np.uint64(seed)
+        z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        z = z ^ (z >> np.uint64(31))
+    return (z >> np.uint64(11)).astype(np.float64) * 1.1102230246251565e-16
+
+
+def spot_check_outputs(it, torch, n_t2new=256, n_other=64, seed=77):
+    """Recompute randomly chosen elements of every output of the last step ON THE HOST in fp64, straight from the term
+    definitions: the exported entries of T / T_alt (fricc_st_export), the ladder operand from the index-defined generator
+    behind fricc_fill_uniform, the other operands read element-wise from the arrays the step was given (ovov) or produced
+    one stage earlier (Woooo, Wvoov, Wvovo -- each of which is itself spot-checked against ovov and T_alt, so the chain
+    is checked stage by stage).  Independent of the library's kernels, layouts and plane expansion.
+    -> {"points", "max_rel" (|got - want| / |want|), "max_rel_to_abs_sum" (/ sum |terms|: the error bound's own scale)}"""
+    import numpy as np
+
+    o, v = it.o, it.v
+    T, T_alt = it.last_pair
+    ent = {}
+    for name, S in (("T", T), ("T_alt", T_alt)):
+        flat, vals = S.export()
+        flat = np.asarray(flat, dtype=np.int64)
+        r, b = np.divmod(flat, v)
+        r, a = np.divmod(r, v)
+        i, j = np.divmod(r, o)
+        ent[name] = ([i.astype(np.int32), j.astype(np.int32), a.astype(np.int32), b.astype(np.int32)], np.asarray(vals))
+
+    def ladder_w(ix):
+        a, b, c, d = (np.asarray(q, dtype=np.uint64) for q in ix)
+        vv = np.uint64(v)
+        return fill_uniform_host(((a * vv + b) * vv + c) * vv + d, 1000)
+
+    def from_device(t):
+        def get(ix):
+            if len(ix[0]) == 0:
+                return np.zeros(0)
+            dev = tuple(torch.as_tensor(np.asarray(q, dtype=np.int64), device=t.device) for q in ix)
+            return t[dev].cpu().numpy()
+        return get
+
+    ovov, Wklij, Wakic, Wakci = (from_device(t) for t in (it.ovov, it.Wklij, it.Wakic, it.Wakci))
+    outputs = [("t2new", it.t2new, n_t2new, [("2323", ladder_w, "T"), ("0101", Wklij, "T")]),
+               ("Woooo", it.Wklij, n_other, [("1323", ovov, "T_alt")]),
+               ("Wvoov", it.Wakic, n_other, [("0112", ovov, "T_alt"), ("0113", ovov, "T_alt"), ("0313", ovov, "T_alt")]),
+               ("Wvovo", it.Wakci, n_other, [("0312", ovov, "T_alt")]),
+               ("tmp0", it.tmp[0], n_other, [("1302", Wakic, "T"), ("1202", Wakci, "T")]),
+               ("tmp1", it.tmp[1], n_other, [("1303", Wakic, "T")]),
+               ("tmp2", it.tmp[2], n_other, [("1203", Wakci, "T")])]
+    rng = np.random.default_rng(seed)
+    worst_rel, worst_abs, n_points, per_out = 0.0, 0.0, 0, {}
+    for name, out, count, terms in outputs:
+        pts = np.stack([rng.integers(0, n, size=count) for n in out.shape], axis=1)
+        got = out[tuple(torch.as_tensor(pts[:, q], device=out.device) for q in range(4))].cpu().numpy()
+        w_rel = w_abs = 0.0
+        for pt, g in zip(pts, got):
+            want = scale_sum = 0.0
+            for term, get_w, which in terms:
+                pref, w_idx, t_idx, o_idx = SPOT_TERMS[term]
+                fixed = dict(zip(o_idx, (int(q) for q in pt)))
+                tix, tv = ent[which]
+                mask = None
+                for q, c in enumerate(t_idx):
+                    if c in fixed:
+                        mq = tix[q] == fixed[c]
+                        mask = mq if mask is None else (mask & mq)
+                sel = np.nonzero(mask)[0]
+                val = dict((c, np.full(sel.size, x, dtype=np.int64)) for c, x in fixed.items())
+                for q, c in enumerate(t_idx):
+                    if c not in fixed:
+                        val[c] = tix[q][sel].astype(np.int64)
+                prod = get_w([val[c] for c in w_idx]) * tv[sel]
+                want += pref * float(np.sum(prod))
+                scale_sum += abs(pref) * float(np.sum(np.abs(prod)))
+            err = abs(float(g) - want)
+            if want != 0.0:
+                w_rel = max(w_rel, err / abs(want))
+            if scale_sum != 0.0:
+                w_abs = max(w_abs, err / scale_sum)
+            elif err != 0.0:
+                w_rel = w_abs = float("inf")
+            n_points += 1
+        per_out[name] = {"points": int(count), "max_rel": w_rel, "max_rel_to_abs_sum": w_abs}
+        worst_rel, worst_abs = max(worst_rel, w_rel), max(worst_abs, w_abs)
+    return {"points": n_points, "max_rel": worst_rel, "max_rel_to_abs_sum": worst_abs, "by_output": per_out,
+            "how": "host fp64 recomputation of random output elements from the exported T / T_alt and the term definitions; "
+                   "ladder operand from the index-defined generator of fricc_fill_uniform (see spot_check_outputs)"}
+
+
+def compress_parity_at_scale(it):
+    """The two compressions of the verification step against the oracle AT THE WORKLOAD'S OWN SIZE (part of the
+    cpu_baseline leg: rank 0, N = 1, outside every timed region).  T2 goes to the host, the C port of the reference runs
+    get_d_largest / make_probability_vector once and sample_systematic once per draw (fri_utils.cpp:400-437, :367-398,
+    :129-159; the composition is fri_compression, :439-522), and the exported index lists and values of T and T_alt must
+    equal it bit for bit."""
+    import numpy as np
+
+    from oracle import oracle
+
+    t0 = time.time()
+    P = oracle.port()
+    x = it.t2.reshape(-1).cpu().numpy()
+    D, r = P.get_d_largest(x, it.m)
+    D = np.asarray(D, dtype=np.int64)
+    nsamp = it.m - D.size
+    p = P.make_probability_vector(x, nsamp, D, r)
+    idx_equal = vals_equal = True
+    for S_gpu, draw in zip(it.last_pair, (it.draws[0:1], it.draws[1:2])):
+        S, _ = P.sample_systematic(nsamp, p, draw)
+        S = np.asarray(S, dtype=np.int64)
+        flat, vals = S_gpu.export()
+        idx_equal &= bool(np.array_equal(np.asarray(flat, dtype=np.int64), np.concatenate([D, S])))
+        want = np.concatenate([x[D], x[S] / p[S]])
+        vals_equal &= bool(np.array_equal(np.asarray(vals).view(np.int64), want.view(np.int64)))
+    return {"N": int(x.size), "m": int(it.m), "n_exact": int(D.size), "compressions": 2, "sampler": "systematic",
+            "idx_equal": idx_equal, "vals_equal": vals_equal, "oracle": "oracle/fricc_oracle.c (C port, 1 thread)",
+            "oracle_seconds": time.time() - t0}
 
 
 def compression_sweep(comm, device, torch, fd, sizes=(1.0e8, 2.56e8, 1.0e9), m=10_000_000, reps=3):
@@ -830,12 +988,19 @@ def stop_clock_sampler(proc, path, window=None):
             "reasons": sorted(reasons), "samples": len(sm)}
 
 
+NCU_CAPTURE_CONFIG = {"o": 40, "v": 400, "m": 10_000_000, "planes": 6}
+_run_matches_ncu_capture = False   # set by run_b200_arm: the committed captures were taken at the default workload on one GPU
+
+
 def ncu_traffic_per_launch(which):
     """dram__bytes_read.sum + dram__bytes_write.sum of ONE launch from the newest committed `ncu --set full` summary
-    profiles/ncu_full_r*_<which>.csv; None if absent."""
+    profiles/ncu_full_r*_<which>.csv; None if absent -- and None whenever this run's (o, v, m, planes, GPUs) is not the
+    configuration those captures were taken at (a per-launch byte count of another shape says nothing about this one)."""
     import csv
     import glob
 
+    if not _run_matches_ncu_capture:
+        return None
     files = sorted(glob.glob(os.path.join(ROOT, "profiles", f"ncu_full_r*_{which}.csv")))
     if not files:
         return None
@@ -851,6 +1016,10 @@ def ncu_traffic_per_launch(which):
 
 
 def run_b200_arm(args):
+    global _run_matches_ncu_capture
+    _run_matches_ncu_capture = ((args.o, args.v, int(args.m), args.planes) ==
+                                (NCU_CAPTURE_CONFIG["o"], NCU_CAPTURE_CONFIG["v"], NCU_CAPTURE_CONFIG["m"], NCU_CAPTURE_CONFIG["planes"])
+                                and int(os.environ.get("WORLD_SIZE", "1")) == 1 and not getattr(args, "as_rank_of", 0))
     if args.overlap_planes and not getattr(args, "_on_priority_stream", False):
         # the step's own stream gets the higher priority, so that the short kernels of the compression are scheduled
         # ahead of the pending blocks of the plane encode that runs beside them on the (default-priority) second stream
@@ -961,6 +1130,12 @@ def run_b200_arm(args):
               (("t2new", it.t2new), ("tmp0", it.tmp[0]), ("tmp1", it.tmp[1]), ("tmp2", it.tmp[2]),
                ("Wvoov", it.Wakic), ("Wvovo", it.Wakci), ("Woooo", it.Wklij))}
 
+    spot = parity = None
+    if rank == 0 and view_comm is None and not args.no_spot_check:
+        spot = spot_check_outputs(it, torch)
+    if (rank == 0 and world == 1 and view_comm is None and not args.no_cpu_baseline and args.sampling == "systematic"
+            and it.N <= 300_000_000):
+        parity = compress_parity_at_scale(it)
     # ---- the other operand regime, for the record (same kernels, planes in or out of the step)
     other_ms = None
     if it.tc and it.sub:
@@ -1206,10 +1381,37 @@ def run_b200_arm(args):
                                        "its 0101 call completes) back to pinned host memory under the remaining contractions; "
                                        "the ladder operand is encoded ahead of its call (py_rccsd.prepare_operand, second stream) "
                                        "while T2 is uploaded and compressed"),
+                           "outputs_read_back": "t2new only (a device-resident caller: tmp0..2, which the reference driver "
+                                                "symmetrises on the host, fricc/friccsd.py:252-284, stay in HBM; a numpy caller that "
+                                                "wants all four O2V2 arrays on the host pays 4x these d2h bytes)",
                            "prepared_plane_hits": int(py_rccsd.get_stat("prepared_plane_hits"))}
         if sweep is not None:
             line["compress_sweep"] = sweep
+        if spot is not None:
+            # the evidence at this scale that does not rest on a stored value: random elements of all seven outputs of the
+            # verification step against a host recomputation (tolerance of north_star: 1e-10 of the terms' own scale)
+            line["spot_check"] = spot
+            line["spot_check_max_rel"] = spot["max_rel"]
+            assert spot["max_rel_to_abs_sum"] <= 1e-10, f"spot check failed: {spot}"
+        if parity is not None:
+            line["compress_parity_at_scale"] = parity
+            assert parity["idx_equal"] and parity["vals_equal"], f"compression differs from the oracle: {parity}"
         default_cfg = (o, v, m, args.sampling) == (40, 400, 10_000_000, "systematic") and args.planes == 6
+        if default_cfg and world == 1 and view_comm is None and not args.no_pairs:
+            # the same small configurations the reference arm runs in full (its "measured_configs"), each in a fresh process
+            # of this script on this GPU: a measured same-config pair beside the extrapolated headline
+            pairs = []
+            for o2, v2, m2 in SAME_CONFIG_PAIRS:
+                cmd = [sys.executable, os.path.abspath(__file__), "--o", str(o2), "--v", str(v2), "--m", str(m2), "--steps", "10",
+                       "--warmup", "3", "--sampling", args.sampling, "--no-cpu-baseline", "--no-pairs", "--no-sweep", "--no-clocks"]
+                try:
+                    res = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+                    sub = json.loads(res.stdout.strip().splitlines()[-1])
+                    pairs.append({"o": o2, "v": v2, "m": m2, "gpu_s": sub["value"], "gpu_e2e_s": sub.get("e2e", {}).get("value"),
+                                  "spot_check_max_rel": sub.get("spot_check_max_rel"), "n_gpus": 1})
+                except Exception as e:   # reported, never fatal for the headline line
+                    pairs.append({"o": o2, "v": v2, "m": m2, "error": repr(e)[:300]})
+            line["same_config_pairs"] = pairs
         if default_cfg and EXPECTED_T2NEW_CHECKSUM is not None and view_comm is None:
             rel = abs(checks["t2new"] - EXPECTED_T2NEW_CHECKSUM) / abs(EXPECTED_T2NEW_CHECKSUM)
             line["t2new_checksum_vs_stored"] = {"rel_diff": rel, "ok": rel <= 1e-12}

@@ -120,9 +120,31 @@ def srand(seed):
     check(_lib.lib().fricc_srand(int(seed) & 0xFFFFFFFF))
 
 
+_options = {}            # what set_option was last given, per key (the library holds the authoritative values)
+_warned_pivotal = False
+
+
+def _warn_pivotal_fast_mode(T):
+    """Once per process: a tensor sampled with the ORDERED pivotal walk is being contracted by the fast kernels.  Those
+    are within 1e-10 of the reference per call, but they add an owner pair's entries in another order, and the last
+    pivotal window (fri_utils.cpp:81-109) turns such last-bit differences of t2 into a different sample now and then: CC
+    energies then agree with the reference's at equal seed only statistically, not to 1e-8.
+    set_option("spmm_exact_order", 1) restores seed parity (bit-identical contractions, 3-5x slower)."""
+    global _warned_pivotal
+    if _warned_pivotal or getattr(T, "sampling_method", None) != "pivotal" or _options.get("spmm_exact_order", 0):
+        return
+    _warned_pivotal = True
+    import warnings
+
+    warnings.warn('fricc_b200: SparseTensor4d sampled with "pivotal" contracted by the fast kernels -- equal-seed energies '
+                  'match the reference only statistically; set_option("spmm_exact_order", 1) for seed parity '
+                  "(see DESIGN.md section 2)", UserWarning, stacklevel=3)
+
+
 def set_option(key, value):
     """Library switches (include/fricc_b200.h: fricc_set_option), e.g. ``set_option("escan", 0)``."""
     check(_lib.lib().fricc_set_option(str(key).encode(), int(value)))
+    _options[str(key)] = int(value)
 
 
 def get_stat(key):
@@ -181,6 +203,8 @@ class SparseTensor4d:
             raise TypeError("__init__(): m must be an integer")
         dptr, dn, keep = _draws_arg(draws)
         consumed = c_int64(0)
+        if params["compression"] == "fri":
+            self.sampling_method = params["sampling_method"]      # remembered for _warn_pivotal_fast_mode
         if dptr is None:
             before = rand_consumed()
             check(self._L.fricc_st_create(t.ptr, t.mem, i64x4(dims), int(m), params["compression"].encode(),
@@ -280,6 +304,7 @@ def _contract(W, T, ouput, term):
         raise TypeError("contract_DTSpT(): T must be a SparseTensor4d")
     if not isinstance(term, str):
         raise TypeError("contract_DTSpT(): term must be a str")
+    _warn_pivotal_fast_mode(T)
     w = _strided4(W, "W")
     o = _strided4(ouput, "ouput", writeable=True)
     check(_lib.lib().fricc_contract(w.ptr, w.mem, i64x4(w.shape), i64x4(w.strides), T._h, o.ptr, o.mem,

@@ -70,3 +70,56 @@ def test_operation_count_models(bench):
     total = f if isinstance(f, (int, float)) else sum(f.values()) if isinstance(f, dict) else sum(f)
     m, o, v = 1e7, 40, 400
     assert total == pytest.approx(m * v * v + 8 * m * o * v + 2 * m * o * o, rel=1e-12)
+
+
+def test_spot_check_recomputes_every_output_from_the_term_definitions():
+    """bench.spot_check_outputs on a tiny CPU stand-in of the bench engine: outputs built with np.einsum from the dense
+    form of T / T_alt pass at rounding level, and a single wrong element anywhere in an output is flagged when hit."""
+    import types
+
+    import numpy as np
+    import torch
+
+    import bench
+
+    o, v = 3, 5
+    rng = np.random.default_rng(3)
+
+    class FakeT:
+        def __init__(self, n_entries):
+            self.flat = rng.choice(o * o * v * v, size=n_entries, replace=False).astype(np.int64)
+            self.vals = rng.standard_normal(n_entries)
+
+        def export(self):
+            return self.flat, self.vals
+
+        def dense(self):
+            d = np.zeros(o * o * v * v)
+            d[self.flat] = self.vals
+            return d.reshape(o, o, v, v)
+
+    T, T_alt = FakeT(90), FakeT(70)
+    W = bench.fill_uniform_host(np.arange(v ** 4, dtype=np.uint64), 1000).reshape(v, v, v, v)
+    assert 0.0 <= W.min() and W.max() < 1.0 and len(np.unique(W)) == v ** 4
+    ovov = rng.random((o, v, o, v))
+    d, da = T.dense(), T_alt.dense()
+
+    def ein(term, Wop, Td):
+        pref, w_idx, t_idx, o_idx = bench.SPOT_TERMS[term]
+        return pref * np.einsum(f"{w_idx},{t_idx}->{o_idx}", Wop, Td)
+
+    Wklij = ein("1323", ovov, da)
+    Wakic = ein("0112", ovov, da) + ein("0113", ovov, da) + ein("0313", ovov, da)
+    Wakci = ein("0312", ovov, da)
+    t2new = ein("2323", W, d) + ein("0101", Wklij, d)
+    tmp = [ein("1302", Wakic, d) + ein("1202", Wakci, d), ein("1303", Wakic, d), ein("1203", Wakci, d)]
+    tt = lambda a: torch.from_numpy(np.ascontiguousarray(a))
+    it = types.SimpleNamespace(o=o, v=v, last_pair=(T, T_alt), ovov=tt(ovov), Wklij=tt(Wklij), Wakic=tt(Wakic),
+                               Wakci=tt(Wakci), t2new=tt(t2new), tmp=[tt(x) for x in tmp])
+    res = bench.spot_check_outputs(it, torch, n_t2new=40, n_other=20)
+    assert res["points"] == 40 + 6 * 20
+    assert res["max_rel_to_abs_sum"] < 1e-14
+    it.tmp[1] = it.tmp[1] + 1e-6                      # every element off: must be seen
+    bad = bench.spot_check_outputs(it, torch, n_t2new=8, n_other=8)
+    assert bad["by_output"]["tmp1"]["max_rel_to_abs_sum"] > 1e-9
+    assert bad["by_output"]["tmp0"]["max_rel_to_abs_sum"] < 1e-14

@@ -491,3 +491,34 @@ def test_pair_with_a_mismatched_tensor_reports_the_plain_calls_error(tc):
         with pytest.raises(ValueError):
             rccsd.contract_DTSpT(W, T, plain, "0112")
             rccsd.contract_DTSpT(W, T, plain, "0113")
+
+
+def test_pivotal_with_fast_contractions_warns_once(tc):
+    """The default kernels meet 1e-10 per call but not equal-seed 1e-8 energies with the pivotal sampler:
+    the mirror says so once per process, and not at all in parity mode or for the systematic sampler."""
+    import warnings
+
+    from fricc_b200 import py_rccsd
+
+    rccsd = tc
+    rng = np.random.default_rng(4)
+    no, nv = 4, 9
+    x = rng.random((no, no, nv, nv)) - 0.5
+    W = rng.random((nv, nv, nv, nv))
+    out = np.zeros((no, no, nv, nv))
+    Ts = rccsd.SparseTensor4d(x, x.shape, 300, "fri", "systematic")
+    Tp = rccsd.SparseTensor4d(x, x.shape, 300, "fri", "pivotal")
+    py_rccsd._warned_pivotal = False
+    try:
+        with warnings.catch_warnings(record=True) as rec:
+            warnings.simplefilter("always")
+            rccsd.contract_DTSpT(W, Ts, out, "2323")
+            rccsd.set_option("spmm_exact_order", 1)
+            rccsd.contract_DTSpT(W, Tp, out, "2323")
+            rccsd.set_option("spmm_exact_order", 0)
+            assert not [w for w in rec if "pivotal" in str(w.message)]
+            rccsd.contract_DTSpT(W, Tp, out, "2323")
+            rccsd.contract_DTSpT(W, Tp, out, "2323")
+            assert len([w for w in rec if "spmm_exact_order" in str(w.message)]) == 1
+    finally:
+        rccsd.set_option("spmm_exact_order", 0)
